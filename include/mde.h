@@ -1,0 +1,183 @@
+/* libmde.so — C-ABI of the B200-native depth-inference forward path.
+ *
+ * The reference (buzzpranav/Monodepth-Estimation) is pure Python/PyTorch and has no FFI
+ * of its own; its boundary for this path is the nn.Module surface
+ * (models/model.py:18,32; models/enhanced_model.py:120,152).  This header is the op layer a
+ * Python (ctypes) or C++ host binds instead of the ATen/cuDNN/cuBLAS calls listed in
+ * SURVEY.md §2a.  Each entry point names the reference lines it replaces.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer (cudaMalloc'ed by the caller; PyTorch owns all
+ *     buffers); the kernels never allocate and never synchronise the host;
+ *   - every call enqueues work on `stream` (a cudaStream_t) and returns immediately;
+ *   - return value: MDE_OK or a negative mde_status; mde_last_error() gives the message
+ *     of the last failure on the calling thread.  Unsupported shapes are errors — there is
+ *     no fallback path;
+ *   - "bf16" arguments are raw bfloat16 bit patterns (uint16_t);
+ *   - "padded NHWC" = bf16 tensor [B][h+2][w+2][C] whose 1-pixel border holds the
+ *     REFLECTION of the interior (so a reflect-pad 3x3 conv reads it directly and a
+ *     zero-pad conv addresses the interior through TMA out-of-bounds zero fill).
+ */
+#ifndef MDE_H_
+#define MDE_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct CUstream_st* mde_stream_t; /* == cudaStream_t */
+typedef uint16_t mde_bf16;
+
+enum mde_status {
+  MDE_OK = 0,
+  MDE_ERR_BAD_ARGUMENT = -1, /* shape / alignment / null pointer */
+  MDE_ERR_UNSUPPORTED = -2,  /* configuration not built */
+  MDE_ERR_CUDA = -3,         /* a CUDA runtime/driver call failed */
+  MDE_ERR_DEVICE = -4        /* current device is not sm_100 */
+};
+
+/* Epilogues of mde_gemm_bf16 (what is fused behind the tensor-core main loop). */
+enum mde_gemm_epilogue {
+  MDE_EPI_BIAS_BF16 = 0,      /* out bf16[M,ldo]  = acc + bias                              */
+  MDE_EPI_BIAS_GELU_BF16 = 1, /* out bf16[M,ldo]  = gelu_erf(acc + bias)      (tv:MLPBlock) */
+  MDE_EPI_BIAS_RESID_F32 = 2, /* out f32[M,ldo]   = acc + bias + resid[M,ldo] (tv:115,120)  */
+  MDE_EPI_BIAS_F32 = 3,       /* out f32[M,ldo]   = acc + bias                              */
+  MDE_EPI_PATCH_EMBED = 4,    /* rows (b,p) -> token row b*197+1+p, + bias + pos_emb; also writes the CLS rows */
+  MDE_EPI_QKV_SPLIT = 5       /* q*(1/8), k -> [B*12][197][64]; v -> transposed [B*12][64][MDE_VT_PITCH] */
+};
+
+enum mde_activation { MDE_ACT_NONE = 0, MDE_ACT_ELU = 1, MDE_ACT_SIGMOID = 2 };
+enum mde_padding { MDE_PAD_REFLECT = 0, MDE_PAD_ZERO = 1 };
+
+#define MDE_VIT_SEQ 197        /* tokens per image: 14*14 patches + CLS                      */
+#define MDE_VIT_DIM 768
+#define MDE_VIT_HEADS 12
+#define MDE_VT_PITCH 208       /* row pitch (elements) of the transposed V buffer            */
+#define MDE_RANGE_SCRATCH_FLOATS (6 * 1024)
+
+int mde_version(void);
+const char* mde_last_error(void);
+/* MDE_OK iff the current CUDA device is compute capability 10.x. */
+int mde_device_check(void);
+/* Number of SMs of the current device (148 on B200). */
+int mde_sm_count(void);
+
+/* ---- encoder.py:129-135: eval BatchNorm2d(3) + whole-batch range heuristic ------------
+ * One pass over x[B,3,H,W] (per-channel min/max), then a 1-block kernel that evaluates the
+ * reference's two data-dependent branches ON DEVICE (no host sync) and emits the combined
+ * per-channel affine  y = a_c * x + b_c  as affine6 = {a0,a1,a2,b0,b1,b2}.
+ * bn4x3 = {weight[3], bias[3], running_mean[3], running_var[3]}.  scratch: MDE_RANGE_SCRATCH_FLOATS floats. */
+int mde_input_range(const float* x, int B, int H, int W, const float* bn4x3, float eps,
+                    float* scratch, float* affine6, mde_stream_t stream);
+
+/* ---- F.interpolate(mode='bilinear', align_corners=False) on fp32 NCHW ------------------
+ * model.py:51-54 (pad-to-/16 resize), enhanced_model.py:95-96 (rgb -> 14x15). */
+int mde_resize_bilinear_nchw(const float* src, int B, int C, int Hs, int Ws, float* dst, int Hd, int Wd,
+                             mde_stream_t stream);
+
+/* ---- encoder.py:139-144 + tv:_process_input: resize to 224^2 (bilinear, align_corners=False),
+ * apply affine6, and lay the result out as the patch-embedding GEMM's A operand:
+ * patches bf16 [B*196][768], column = c*256 + ky*16 + kx. */
+int mde_preprocess_patchify(const float* x, int B, int H, int W, const float* affine6, mde_bf16* patches,
+                            mde_stream_t stream);
+
+/* ---- tcgen05 GEMM: D[M,N] = epilogue(A[M,K] * W[N,K]^T), bf16 in, fp32 accumulate --------
+ * Replaces conv_proj (tv:277), in_proj / out_proj (tv:113), mlp.0 / mlp.3 (tv:118) and
+ * channel_reduce (encoder.py:164).  A row-major [M][lda], W row-major [N][ldw] (K contiguous).
+ * Requirements: K % 64 == 0, N % 128 == 0, lda/ldw % 8 == 0, 16-byte aligned pointers.
+ * aux0/aux1/aux2 depend on the epilogue:
+ *   RESID_F32 : aux0 = resid f32[M][ldo]
+ *   PATCH_EMBED: aux0 = pos_embedding f32[197][768], aux1 = class_token f32[768]; out f32[B*197][768]
+ *   QKV_SPLIT : out = q bf16, aux0 = k bf16, aux1 = vt bf16 (layouts above); M = B*197 */
+int mde_gemm_bf16(const mde_bf16* A, int lda, const mde_bf16* W, int ldw, int M, int N, int K, int epilogue,
+                  const float* bias, void* out, int ldo, const void* aux0, const void* aux1,
+                  mde_stream_t stream);
+
+/* ---- LayerNorm over the last dim (tv:112,117; eps 1e-6), fp32 in, bf16 out ------------- */
+int mde_layernorm_bf16(const float* x, int rows, int dim, const float* gamma, const float* beta, float eps,
+                       mde_bf16* out, mde_stream_t stream);
+
+/* ---- ViT self-attention core (tv:113, nn.MultiheadAttention, 12 heads x 64, S=197) -----
+ * softmax(q k^T) v per (image, head) with q pre-scaled by 1/8; tcgen05 for both products,
+ * softmax fused in between.  q,k: [B*12][197][64]; vt: [B*12][64][MDE_VT_PITCH];
+ * out bf16 [B*197][768] (token-major, head h in columns 64h..64h+63). */
+int mde_vit_attention(const mde_bf16* q, const mde_bf16* k, const mde_bf16* vt, int B, mde_bf16* out,
+                      mde_stream_t stream);
+
+/* ---- encoder.py:69-110: token sequence -> grid rows, as the channel_reduce GEMM's A operand.
+ * tokens f32 [B][197][768].  strip_cls=1: rows = tokens 1..196 (G=196, exact 224^2 input);
+ * strip_cls=0: rows = tokens 0..196 then zero rows up to G (G=210, the 14x15 grid). out bf16 [B*G][768]. */
+int mde_tokens_to_grid_bf16(const float* tokens, int B, int strip_cls, int G, mde_bf16* out, mde_stream_t stream);
+
+/* ---- encoder.py:167 F.instance_norm (eps 1e-5, biased variance, no affine) over the G = gh*gw
+ * positions of x f32 [B][G][C]; writes channels [out_coff, out_coff+C) of the padded NHWC bf16
+ * tensor [B][gh+2][gw+2][out_cstride] and, if non-null, the flat copy bf16 [B*G][C]. */
+int mde_instnorm_nhwc(const float* x, int B, int gh, int gw, int C, float eps, mde_bf16* out_padded,
+                      int out_cstride, int out_coff, mde_bf16* out_flat, mde_stream_t stream);
+
+/* ---- 3x3 (or 1x1) convolution as a tcgen05 implicit GEMM over padded NHWC ----------------
+ * decoder.py:8-34 (reflect pad + conv + folded eval-BN + ELU), decoder.py:86-88,166 (zero-pad
+ * heads + sigmoid), enhanced_model.py:45-54,87-103 (zero-pad convs + ELU / 1x1 heads).
+ *   in      : padded NHWC bf16 [B][h+2][w+2][in_cstride], channels [0,cin) are read
+ *             (cin a multiple of 64, or 32, or 16)
+ *   wpacked : bf16 [cout_pad][ksize*ksize*cin], k = (ky*ksize+kx)*cin + c, BN scale folded in;
+ *             cout_pad = cout rounded up to a multiple of 16
+ *   bias    : f32 [cout_pad] (conv bias with BN shift folded in)
+ *   out_bf16: padded NHWC bf16 [B][h+2][w+2][out_cstride], written at channels
+ *             [out_coff, out_coff+cout) including the reflected border, or NULL
+ *   out_f32 : f32 [B][h][w][cout] (unpadded), or NULL          — exactly one of the two */
+int mde_conv_nhwc(const mde_bf16* in, int B, int h, int w, int cin, int in_cstride, const mde_bf16* wpacked, const float* bias,
+                  int cout, int ksize, int padding, int activation, mde_bf16* out_bf16, int out_cstride,
+                  int out_coff, float* out_f32, mde_stream_t stream);
+
+/* ---- decoder.py:118-145: x2 bilinear upsample (align_corners=True) of `a`, optional bilinear
+ * resize (align_corners=True) of the skip branch `s` to the same size, channel concat.
+ * a: padded NHWC [B][h+2][w+2][ca]; s: padded NHWC [B][hs+2][ws+2][cs] or NULL (cs=0);
+ * out: padded NHWC [B][2h+2][2w+2][ca+cs] (border reflected). */
+int mde_upsample2x_concat_nhwc(const mde_bf16* a, int B, int h, int w, int ca, const mde_bf16* s, int hs, int ws,
+                               int cs, mde_bf16* out, mde_stream_t stream);
+
+/* ---- enhanced_model.py:95-98: rgb image f32 [B,3,H,W] -> bilinear (align_corners=False) to the gh x gw
+ * grid, written as channels [out_coff, out_coff+3) of a padded NHWC bf16 tensor; channels up to
+ * out_coff+cfill are zero-filled (K padding of the 259-channel refinement conv). */
+int mde_rgb_to_grid_nhwc(const float* x, int B, int H, int W, int gh, int gw, mde_bf16* out_padded, int out_cstride,
+                         int out_coff, int cfill, mde_stream_t stream);
+
+/* ---- output stage: model.py:89-100, enhanced_model.py:266-277, layers.py:16-25 ----------
+ * For each of n_maps low-resolution fp32 maps [B][hs][ws]: multiply by `mul`, resize to
+ * [B][H][W] (bilinear, align_corners=False) into dst_disp and, where dst_depth != NULL, also
+ * write 1/(min_disp + (max_disp-min_disp)*disp) of the RESIZED value. */
+typedef struct mde_map_desc {
+  const float* src;
+  int hs, ws;
+  float mul;
+  float* dst_disp;  /* may be NULL */
+  float* dst_disp2; /* optional second copy (("disp_fused",0) aliases ("disp",0)), may be NULL */
+  float* dst_depth; /* may be NULL */
+} mde_map_desc;
+#define MDE_MAX_MAPS 8
+int mde_resize_maps(const mde_map_desc* maps, int n_maps, int B, int H, int W, float min_disp, float max_disp,
+                    mde_stream_t stream);
+
+/* ---- enhanced_model.py:20-39 SelfAttentionBlock on a 14x15 (or 14x14) grid -----------------
+ * x: flat bf16 [B*G][256] (instance-normed features); qkv: f32 [B*G][384] = the 1x1 projections
+ * q(32)|k(32)|v(256)|pad(64) incl. bias (one mde_gemm_bf16 with MDE_EPI_BIAS_F32);
+ * out = gamma * (v softmax(q^T k)^T) + x, written as padded NHWC bf16 [B][gh+2][gw+2][256].
+ * gamma is read from device memory (f32[1]). */
+int mde_spatial_attention(const mde_bf16* x, const float* qkv, int B, int gh, int gw, const float* gamma,
+                          mde_bf16* out_padded, mde_stream_t stream);
+
+/* ---- enhanced_model.py:199-215,244-263: low-resolution tail of the enhanced forward --------
+ * refinement f32 [B][gh][gw] -> bilinear (align False) to disp0's size, added to disp0;
+ * disp_unrefined = disp0 (unscaled); scaled maps d_k*mul; fused = sum_k softmax(w)_k *
+ * resize(d_k*mul -> disp0 size).  d0,d1,d2: f32 [B][h0<<k][w0<<k].
+ * Outputs (f32 [B][h0][w0]): fused. */
+int mde_enh_fuse(const float* d0, const float* d1, const float* d2, const float* refinement, int B, int h0,
+                 int w0, int gh, int gw, float mul, const float* fusion_w3, float* fused, mde_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MDE_H_ */

@@ -1,0 +1,94 @@
+"""ctypes binding of ``libmde.so`` (the C-ABI declared in ``include/mde.h``).
+
+The product path has no fallback: if the library is missing or the device is not
+sm_100, calls raise.  ``lib()`` loads (and, if the sources are newer or the .so is
+absent and nvcc exists, builds) the shared object once per process.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import threading
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+SO_PATH = os.path.join(HERE, "libmde.so")
+
+MDE_OK = 0
+EPI_BIAS_BF16, EPI_BIAS_GELU_BF16, EPI_BIAS_RESID_F32, EPI_BIAS_F32, EPI_PATCH_EMBED, EPI_QKV_SPLIT = range(6)
+ACT_NONE, ACT_ELU, ACT_SIGMOID = range(3)
+PAD_REFLECT, PAD_ZERO = range(2)
+VIT_SEQ, VIT_DIM, VIT_HEADS, VT_PITCH = 197, 768, 12, 208
+RANGE_SCRATCH_FLOATS = 6 * 1024
+MAX_MAPS = 8
+
+_p, _i, _f = C.c_void_p, C.c_int, C.c_float
+
+
+class MapDesc(C.Structure):
+    _fields_ = [("src", _p), ("hs", _i), ("ws", _i), ("mul", _f), ("dst_disp", _p), ("dst_disp2", _p), ("dst_depth", _p)]
+
+
+# name -> argtypes (every function returns int status unless listed in _RESTYPES)
+SIGNATURES = {
+    "mde_version": [],
+    "mde_last_error": [],
+    "mde_device_check": [],
+    "mde_sm_count": [],
+    "mde_input_range": [_p, _i, _i, _i, _p, _f, _p, _p, _p],
+    "mde_resize_bilinear_nchw": [_p, _i, _i, _i, _i, _p, _i, _i, _p],
+    "mde_preprocess_patchify": [_p, _i, _i, _i, _p, _p, _p],
+    "mde_gemm_bf16": [_p, _i, _p, _i, _i, _i, _i, _i, _p, _p, _i, _p, _p, _p],
+    "mde_layernorm_bf16": [_p, _i, _i, _p, _p, _f, _p, _p],
+    "mde_vit_attention": [_p, _p, _p, _i, _p, _p],
+    "mde_tokens_to_grid_bf16": [_p, _i, _i, _i, _p, _p],
+    "mde_instnorm_nhwc": [_p, _i, _i, _i, _i, _f, _p, _i, _i, _p, _p],
+    "mde_conv_nhwc": [_p, _i, _i, _i, _i, _i, _p, _p, _i, _i, _i, _i, _p, _i, _i, _p, _p],
+    "mde_upsample2x_concat_nhwc": [_p, _i, _i, _i, _i, _p, _i, _i, _i, _p, _p],
+    "mde_rgb_to_grid_nhwc": [_p, _i, _i, _i, _i, _i, _p, _i, _i, _i, _p],
+    "mde_resize_maps": [C.POINTER(MapDesc), _i, _i, _i, _i, _f, _f, _p],
+    "mde_spatial_attention": [_p, _p, _i, _i, _i, _p, _p, _p],
+    "mde_enh_fuse": [_p, _p, _p, _p, _i, _i, _i, _i, _i, _f, _p, _p, _p],
+}
+_RESTYPES = {"mde_last_error": C.c_char_p}
+
+_lock = threading.Lock()
+_lib = None
+
+
+class MdeError(RuntimeError):
+    pass
+
+
+def load(build_if_needed: bool = True):
+    """Return the loaded CDLL with prototypes set (no device work)."""
+    global _lib
+    with _lock:
+        if _lib is not None:
+            return _lib
+        if build_if_needed:
+            from .build import build
+
+            try:
+                build()
+            except Exception:
+                if not os.path.exists(SO_PATH):
+                    raise
+        if not os.path.exists(SO_PATH):
+            raise MdeError(f"{SO_PATH} is missing: run `python monodepth-estimation_b200/build.py` (needs nvcc)")
+        lib = C.CDLL(SO_PATH)
+        for name, argtypes in SIGNATURES.items():
+            fn = getattr(lib, name)  # AttributeError here == header/library mismatch
+            fn.argtypes = argtypes
+            fn.restype = _RESTYPES.get(name, C.c_int)
+        _lib = lib
+        return lib
+
+
+def check(status: int, what: str = ""):
+    if status != MDE_OK:
+        msg = load().mde_last_error()
+        raise MdeError(f"{what} failed with status {status}: {msg.decode() if msg else '?'}")
+
+
+def call(name: str, *args):
+    check(getattr(load(), name)(*args), name)

@@ -1,0 +1,324 @@
+// Attention kernels.
+//  * vit_attn_kernel   — tv:113 nn.MultiheadAttention core for ViT-B/16 (S=197, 12 heads x 64):
+//    one CTA per (image, head); Q/K/V^T tiles arrive by TMA (out-of-bounds rows zero-filled, so
+//    the 197-token sequence needs no padded copy), S = Q K^T and O = P V run on tcgen05 with
+//    the accumulators in TMEM, and the softmax is fused in between: each of the 128 threads owns
+//    one query row (one TMEM lane), reads its scores with tcgen05.ld, and writes the
+//    un-normalised bf16 probabilities straight into the swizzled K-major smem tile that the
+//    second MMA consumes.  1/rowsum is applied in the output epilogue.
+//  * spatial_attn_kernel — enhanced_model.py:20-39 on the 14x15 grid (G<=224 positions,
+//    32-dim q/k, 256-dim v): tiny (25 MFLOP/image), fp32 CUDA-core kernel.
+#include "common.h"
+#include "ptx.cuh"
+
+namespace mde {
+
+constexpr int kS = MDE_VIT_SEQ;   // 197
+constexpr int kKeys = 208;        // keys padded to a multiple of 16 (UMMA N)
+constexpr int kQBytes = 128 * 128;            // one 128-row Q tile, 64 bf16 per row
+constexpr int kKBytes = kKeys * 128;          // 26624
+constexpr int kKBytesPad = 27 * 1024;
+constexpr int kVBytes = 64 * 128;             // one k-block of V^T: 64 d-rows x 64 keys
+constexpr int kPBytes = 128 * 128;            // one k-block of P: 128 rows x 64 keys
+constexpr int kOffK = 2 * kQBytes;
+constexpr int kOffV = kOffK + kKBytesPad;
+constexpr int kOffP = kOffV + 4 * kVBytes;
+constexpr int kOffBar = kOffP + 4 * kPBytes;
+constexpr int kAttnSmem = kOffBar + 64 + 1024;
+constexpr uint32_t kTmemCols = 512;
+constexpr uint32_t kTmemO = 256;  // O accumulator column offset (S occupies [0,208))
+
+struct alignas(64) AttnParams {
+  CUtensorMap tmQ, tmK, tmV;
+  bf16* out;
+  int B;
+};
+
+__global__ void __launch_bounds__(128, 1) vit_attn_kernel(const __grid_constant__ AttnParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
+  uint8_t* sQ = smem;
+  uint8_t* sK = smem + kOffK;
+  uint8_t* sV = smem + kOffV;
+  uint8_t* sP = smem + kOffP;
+  uint64_t* bar_load = reinterpret_cast<uint64_t*>(smem + kOffBar);
+  uint64_t* bar_s = bar_load + 1;
+  uint64_t* bar_o = bar_load + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_load + 3);
+
+  const int tid = threadIdx.x, warp = tid >> 5;
+  const int slab = blockIdx.x;  // b * 12 + head
+  const int b = slab / MDE_VIT_HEADS, hd = slab - b * MDE_VIT_HEADS;
+
+  if (warp == 0) {
+    if (elect_one()) {
+      tma_prefetch_desc(&p.tmQ);
+      tma_prefetch_desc(&p.tmK);
+      tma_prefetch_desc(&p.tmV);
+      mbar_init(bar_load, 1);
+      mbar_init(bar_s, 1);
+      mbar_init(bar_o, 1);
+      fence_barrier_init();
+    }
+    __syncwarp();
+    tmem_alloc(tmem_slot, kTmemCols);
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (tid == 0) {
+    mbar_expect_tx(bar_load, 2 * kQBytes + kKBytes + 4 * kVBytes);
+    tma_load_3d(sQ, &p.tmQ, bar_load, 0, 0, slab);
+    tma_load_3d(sQ + kQBytes, &p.tmQ, bar_load, 0, 128, slab);
+    tma_load_3d(sK, &p.tmK, bar_load, 0, 0, slab);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) tma_load_3d(sV + j * kVBytes, &p.tmV, bar_load, 64 * j, 0, slab);
+  }
+  mbar_wait(bar_load, 0);
+
+  const uint32_t t_row = tmem_base + (static_cast<uint32_t>(warp * 32) << 16);  // this thread's TMEM lane
+  const uint32_t sw = static_cast<uint32_t>(tid & 7);                            // swizzle phase of row tid
+  uint8_t* p_row = sP + tid * 128;
+  constexpr float kLog2e = 1.4426950408889634f;
+
+#pragma unroll 1
+  for (int mt = 0; mt < 2; ++mt) {
+    // ---- S = Q_mt K^T  (128 x 208, K = 64)
+    if (tid == 0) {
+      tc_fence_after();
+      constexpr uint32_t idesc_s = umma_idesc_bf16(128, kKeys);
+      const uint64_t da = umma_smem_desc_kmajor<128>(smem_u32(sQ + mt * kQBytes));
+      const uint64_t db = umma_smem_desc_kmajor<128>(smem_u32(sK));
+#pragma unroll
+      for (int k = 0; k < 4; ++k) umma_bf16_ss(tmem_base, da + 2 * k, db + 2 * k, idesc_s, k != 0);
+      umma_commit(bar_s);
+    }
+    mbar_wait(bar_s, mt & 1);
+    tc_fence_after();
+
+    // ---- row softmax over the 197 real keys (columns >= 197 are zero-filled K rows: masked)
+    float mx = -INFINITY;
+#pragma unroll 1
+    for (int c = 0; c < 6; ++c) {
+      uint32_t r[32];
+      tmem_ld_32x32b_x32(t_row + c * 32, r);
+      tmem_ld_wait();
+#pragma unroll
+      for (int j = 0; j < 32; ++j) mx = fmaxf(mx, __uint_as_float(r[j]));
+    }
+    {
+      uint32_t r[16];
+      tmem_ld_32x32b_x16(t_row + 192, r);
+      tmem_ld_wait();
+#pragma unroll
+      for (int j = 0; j < kS - 192; ++j) mx = fmaxf(mx, __uint_as_float(r[j]));
+    }
+    const float mxs = mx * kLog2e;
+    float sum = 0.0f;
+#pragma unroll 1
+    for (int c = 0; c < 6; ++c) {
+      uint32_t r[32];
+      tmem_ld_32x32b_x32(t_row + c * 32, r);
+      tmem_ld_wait();
+      float e[32];
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        e[j] = fast_ex2(fmaf(__uint_as_float(r[j]), kLog2e, -mxs));
+        sum += e[j];
+      }
+      uint8_t* blk = p_row + (c >> 1) * kPBytes;
+#pragma unroll
+      for (int g = 0; g < 4; ++g) {
+        const uint32_t chunk = static_cast<uint32_t>((c & 1) * 4 + g);
+        *reinterpret_cast<uint4*>(blk + ((chunk ^ sw) << 4)) =
+            make_uint4(pack_bf16x2(e[8 * g], e[8 * g + 1]), pack_bf16x2(e[8 * g + 2], e[8 * g + 3]),
+                       pack_bf16x2(e[8 * g + 4], e[8 * g + 5]), pack_bf16x2(e[8 * g + 6], e[8 * g + 7]));
+      }
+    }
+    {
+      uint32_t r[16];
+      tmem_ld_32x32b_x16(t_row + 192, r);
+      tmem_ld_wait();
+      float e[16];
+#pragma unroll
+      for (int j = 0; j < 16; ++j) {
+        e[j] = (j < kS - 192) ? fast_ex2(fmaf(__uint_as_float(r[j]), kLog2e, -mxs)) : 0.0f;
+        sum += e[j];
+      }
+      uint8_t* blk = p_row + 3 * kPBytes;
+#pragma unroll
+      for (int g = 0; g < 2; ++g)
+        *reinterpret_cast<uint4*>(blk + ((static_cast<uint32_t>(g) ^ sw) << 4)) =
+            make_uint4(pack_bf16x2(e[8 * g], e[8 * g + 1]), pack_bf16x2(e[8 * g + 2], e[8 * g + 3]),
+                       pack_bf16x2(e[8 * g + 4], e[8 * g + 5]), pack_bf16x2(e[8 * g + 6], e[8 * g + 7]));
+    }
+    const float inv = 1.0f / sum;
+    fence_proxy_async_smem();  // generic-proxy smem writes -> visible to the tensor core (async proxy)
+    tc_fence_before();
+    __syncthreads();
+
+    // ---- O = P V  (128 x 64, K = 208 = 3 x 64 + 16)
+    if (tid == 0) {
+      tc_fence_after();
+      constexpr uint32_t idesc_o = umma_idesc_bf16(128, 64);
+#pragma unroll
+      for (int kb = 0; kb < 4; ++kb) {
+        const uint64_t da = umma_smem_desc_kmajor<128>(smem_u32(sP + kb * kPBytes));
+        const uint64_t db = umma_smem_desc_kmajor<128>(smem_u32(sV + kb * kVBytes));
+        const int nk = kb < 3 ? 4 : 1;
+        for (int k = 0; k < nk; ++k) umma_bf16_ss(tmem_base + kTmemO, da + 2 * k, db + 2 * k, idesc_o, (kb | k) != 0);
+      }
+      umma_commit(bar_o);
+    }
+    mbar_wait(bar_o, mt & 1);
+    tc_fence_after();
+
+    const int t = mt * 128 + tid;
+#pragma unroll 1
+    for (int c = 0; c < 2; ++c) {
+      uint32_t r[32];
+      tmem_ld_32x32b_x32(t_row + kTmemO + c * 32, r);
+      tmem_ld_wait();
+      if (t < kS) {
+        uint4* dst = reinterpret_cast<uint4*>(p.out + ((size_t)b * kS + t) * MDE_VIT_DIM + hd * 64 + c * 32);
+#pragma unroll
+        for (int g = 0; g < 4; ++g)
+          dst[g] = make_uint4(pack_bf16x2(__uint_as_float(r[8 * g]) * inv, __uint_as_float(r[8 * g + 1]) * inv),
+                              pack_bf16x2(__uint_as_float(r[8 * g + 2]) * inv, __uint_as_float(r[8 * g + 3]) * inv),
+                              pack_bf16x2(__uint_as_float(r[8 * g + 4]) * inv, __uint_as_float(r[8 * g + 5]) * inv),
+                              pack_bf16x2(__uint_as_float(r[8 * g + 6]) * inv, __uint_as_float(r[8 * g + 7]) * inv));
+      }
+    }
+    tc_fence_before();
+    __syncthreads();  // S columns and the P tile are free for the next query tile
+  }
+  tc_fence_after();
+  if (warp == 0) tmem_dealloc(tmem_base, kTmemCols);
+}
+
+// ------------------------------------------------------------------ spatial self-attention (enhanced_model.py:20-39)
+constexpr int kSaQ = 8;        // queries per block
+constexpr int kSaMaxG = 224;   // grid positions supported (14x15 = 210, 14x14 = 196)
+constexpr int kSaLd = 384;     // row pitch of the fp32 q|k|v projection buffer
+
+__global__ void __launch_bounds__(256) spatial_attn_kernel(const bf16* __restrict__ x, const float* __restrict__ qkv, int gh, int gw,
+                                                           const float* __restrict__ gamma_p, bf16* __restrict__ out) {
+  __shared__ float sK[kSaMaxG][33];
+  __shared__ float sQ[kSaQ][32];
+  __shared__ float sA[kSaQ][kSaMaxG];
+  const int G = gh * gw;
+  const int b = blockIdx.y, q0 = blockIdx.x * kSaQ;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const float* base = qkv + (size_t)b * G * kSaLd;
+  for (int i = tid; i < G * 32; i += 256) sK[i >> 5][i & 31] = base[(size_t)(i >> 5) * kSaLd + 32 + (i & 31)];
+  {
+    const int i = tid >> 5, d = tid & 31;
+    sQ[i][d] = (q0 + i < G) ? base[(size_t)(q0 + i) * kSaLd + d] : 0.0f;
+  }
+  __syncthreads();
+  // energy[i][j] = q_i . k_j (no scaling, enhanced_model.py:28); warp i owns query i
+  {
+    const int i = warp;
+    float mx = -INFINITY;
+    for (int j = lane; j < G; j += 32) {
+      float e = 0.0f;
+#pragma unroll
+      for (int d = 0; d < 32; ++d) e = fmaf(sQ[i][d], sK[j][d], e);
+      sA[i][j] = e;
+      mx = fmaxf(mx, e);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    float sum = 0.0f;
+    for (int j = lane; j < G; j += 32) {
+      const float e = __expf(sA[i][j] - mx);
+      sA[i][j] = e;
+      sum += e;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+    const float inv = 1.0f / sum;
+    for (int j = lane; j < G; j += 32) sA[i][j] *= inv;
+  }
+  __syncthreads();
+  // out[i][c] = sum_j att[i][j] * v[j][c]; thread = channel c (coalesced v reads)
+  float acc[kSaQ];
+#pragma unroll
+  for (int i = 0; i < kSaQ; ++i) acc[i] = 0.0f;
+  const float* vcol = base + 64 + tid;
+  for (int j = 0; j < G; ++j) {
+    const float v = vcol[(size_t)j * kSaLd];
+#pragma unroll
+    for (int i = 0; i < kSaQ; ++i) acc[i] = fmaf(sA[i][j], v, acc[i]);
+  }
+  const float gamma = *gamma_p;
+  const int H2 = gh + 2, W2 = gw + 2;
+#pragma unroll 1
+  for (int i = 0; i < kSaQ; ++i) {
+    const int g = q0 + i;
+    if (g >= G) break;
+    const float xin = __bfloat162float(x[((size_t)b * G + g) * 256 + tid]);
+    const bf16 v = __float2bfloat16_rn(fmaf(gamma, acc[i], xin));
+    const int y = g / gw, xx = g - y * gw;
+    int ys[3], xs[3], ny = 0, nx = 0;
+    ys[ny++] = y + 1;
+    if (y == 1) ys[ny++] = 0;
+    if (y == gh - 2) ys[ny++] = gh + 1;
+    xs[nx++] = xx + 1;
+    if (xx == 1) xs[nx++] = 0;
+    if (xx == gw - 2) xs[nx++] = gw + 1;
+    for (int iy = 0; iy < ny; ++iy)
+      for (int ix = 0; ix < nx; ++ix) out[(((size_t)b * H2 + ys[iy]) * W2 + xs[ix]) * 256 + tid] = v;
+  }
+}
+
+}  // namespace mde
+
+using namespace mde;
+
+extern "C" int mde_vit_attention(const mde_bf16* q, const mde_bf16* k, const mde_bf16* vt, int B, mde_bf16* out, mde_stream_t stream) {
+  MDE_CHECK_ARG(q && k && vt && out && B > 0, "mde_vit_attention: bad arguments");
+  MDE_CHECK_ARG(((uintptr_t)q | (uintptr_t)k | (uintptr_t)vt | (uintptr_t)out) % 16 == 0, "mde_vit_attention: pointers must be 16-byte aligned");
+  AttnParams p;
+  memset(&p, 0, sizeof(p));
+  const uint64_t slabs = (uint64_t)B * MDE_VIT_HEADS;
+  {
+    const uint64_t dims[3] = {64, (uint64_t)kS, slabs};
+    const uint64_t strides[2] = {128, (uint64_t)kS * 128};
+    const uint32_t boxq[3] = {64, 128, 1};
+    const uint32_t boxk[3] = {64, (uint32_t)kKeys, 1};
+    int rc = encode_tmap_bf16(&p.tmQ, q, 3, dims, strides, boxq, 128);
+    if (rc != MDE_OK) return rc;
+    rc = encode_tmap_bf16(&p.tmK, k, 3, dims, strides, boxk, 128);
+    if (rc != MDE_OK) return rc;
+  }
+  {
+    const uint64_t dims[3] = {(uint64_t)kS, 64, slabs};
+    const uint64_t strides[2] = {(uint64_t)MDE_VT_PITCH * 2, (uint64_t)64 * MDE_VT_PITCH * 2};
+    const uint32_t box[3] = {64, 64, 1};
+    int rc = encode_tmap_bf16(&p.tmV, vt, 3, dims, strides, box, 128);
+    if (rc != MDE_OK) return rc;
+  }
+  p.out = reinterpret_cast<bf16*>(out);
+  p.B = B;
+  static bool attr_set = false;
+  if (!attr_set) {
+    MDE_CHECK_CUDA(cudaFuncSetAttribute(vit_attn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kAttnSmem));
+    attr_set = true;
+  }
+  vit_attn_kernel<<<(unsigned)slabs, 128, kAttnSmem, stream>>>(p);
+  MDE_CHECK_LAUNCH();
+  return MDE_OK;
+}
+
+extern "C" int mde_spatial_attention(const mde_bf16* x, const float* qkv, int B, int gh, int gw, const float* gamma, mde_bf16* out_padded,
+                                     mde_stream_t stream) {
+  MDE_CHECK_ARG(x && qkv && gamma && out_padded && B > 0 && gh >= 3 && gw >= 3, "mde_spatial_attention: bad arguments");
+  MDE_CHECK_ARG(gh * gw <= kSaMaxG, "mde_spatial_attention: grid %dx%d exceeds %d positions", gh, gw, kSaMaxG);
+  spatial_attn_kernel<<<dim3(ceil_div(gh * gw, kSaQ), B), 256, 0, stream>>>(reinterpret_cast<const bf16*>(x), qkv, gh, gw, gamma,
+                                                                            reinterpret_cast<bf16*>(out_padded));
+  MDE_CHECK_LAUNCH();
+  return MDE_OK;
+}

@@ -1,0 +1,51 @@
+// Internal host-side helpers shared by the .cu files of libmde.so (error reporting, TMA
+// tensor-map encoding through the driver entry point, device properties).
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/mde.h"
+
+namespace mde {
+
+// thread-local message behind mde_last_error()
+void set_error(const char* fmt, ...);
+
+#define MDE_CHECK_ARG(cond, ...)        \
+  do {                                  \
+    if (!(cond)) {                      \
+      ::mde::set_error(__VA_ARGS__);    \
+      return MDE_ERR_BAD_ARGUMENT;      \
+    }                                   \
+  } while (0)
+
+#define MDE_CHECK_CUDA(expr)                                                                     \
+  do {                                                                                           \
+    cudaError_t err__ = (expr);                                                                  \
+    if (err__ != cudaSuccess) {                                                                  \
+      ::mde::set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(err__), __FILE__, __LINE__); \
+      return MDE_ERR_CUDA;                                                                       \
+    }                                                                                            \
+  } while (0)
+
+// Launch-error check that does not synchronise (safe inside CUDA-graph capture).
+#define MDE_CHECK_LAUNCH()                                                                       \
+  do {                                                                                           \
+    cudaError_t err__ = cudaGetLastError();                                                      \
+    if (err__ != cudaSuccess) {                                                                  \
+      ::mde::set_error("kernel launch failed: %s (%s:%d)", cudaGetErrorString(err__), __FILE__, __LINE__); \
+      return MDE_ERR_CUDA;                                                                       \
+    }                                                                                            \
+  } while (0)
+
+int sm_count();  // SMs of the current device (cached per device)
+
+// Encode a bf16 tiled tensor map.  dims/box are innermost-first; strides_bytes has rank-1
+// entries (strides of dims 1..rank-1).  swizzle_bytes in {32, 64, 128}.  Returns MDE_OK or error.
+int encode_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims,
+                     const uint64_t* strides_bytes, const uint32_t* box, int swizzle_bytes);
+
+static inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
+
+}  // namespace mde

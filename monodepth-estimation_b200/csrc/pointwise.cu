@@ -1,0 +1,581 @@
+// HBM-bound kernels of the path: input range scan, resampling, patchify, LayerNorm, instance norm,
+// upsample+concat, and the output stage.  All are coalesced / 16-byte vectorised, grid-stride over
+// a multiple of the SM count, fp32 arithmetic, no host synchronisation.
+#include <float.h>
+
+#include "common.h"
+#include "ptx.cuh"
+
+namespace mde {
+
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+__device__ __forceinline__ float warp_min(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fminf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// torch's area_pixel_compute_source_index for bilinear, align_corners=False (UpSample.h)
+__device__ __forceinline__ void src_index_acf(float scale, int dst, int in_size, int& i0, int& i1, float& l1) {
+  float s = scale * (dst + 0.5f) - 0.5f;
+  s = s < 0.0f ? 0.0f : s;
+  i0 = (int)s;
+  if (i0 > in_size - 1) i0 = in_size - 1;
+  i1 = i0 + (i0 < in_size - 1 ? 1 : 0);
+  l1 = s - (float)i0;
+}
+// align_corners=True
+__device__ __forceinline__ void src_index_act(float scale, int dst, int in_size, int& i0, int& i1, float& l1) {
+  const float s = scale * dst;
+  i0 = (int)s;
+  if (i0 > in_size - 1) i0 = in_size - 1;
+  i1 = i0 + (i0 < in_size - 1 ? 1 : 0);
+  l1 = s - (float)i0;
+}
+
+// ------------------------------------------------------------------ input range (encoder.py:129-135)
+__global__ void __launch_bounds__(256) minmax_kernel(const float4* __restrict__ x4, long long n4, int hw4, float* __restrict__ partials) {
+  float mn[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, mx[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+  const long long per = (n4 + gridDim.x - 1) / gridDim.x;
+  const long long beg = per * blockIdx.x;
+  long long end = beg + per;
+  if (end > n4) end = n4;
+  for (long long i = beg + threadIdx.x; i < end; i += blockDim.x) {
+    const float4 v = __ldg(x4 + i);
+    const int c = (int)((i / hw4) % 3);
+    const float lo = fminf(fminf(v.x, v.y), fminf(v.z, v.w));
+    const float hi = fmaxf(fmaxf(v.x, v.y), fmaxf(v.z, v.w));
+#pragma unroll
+    for (int k = 0; k < 3; ++k)
+      if (c == k) {
+        mn[k] = fminf(mn[k], lo);
+        mx[k] = fmaxf(mx[k], hi);
+      }
+  }
+  __shared__ float red[8][6];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    const float a = warp_min(mn[k]), b = warp_max(mx[k]);
+    if (lane == 0) {
+      red[warp][k] = a;
+      red[warp][3 + k] = b;
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x < 6) {
+    float r = red[0][threadIdx.x];
+    for (int w = 1; w < 8; ++w) r = threadIdx.x < 3 ? fminf(r, red[w][threadIdx.x]) : fmaxf(r, red[w][threadIdx.x]);
+    partials[blockIdx.x * 6 + threadIdx.x] = r;
+  }
+}
+
+__global__ void range_finalize_kernel(const float* __restrict__ partials, int nparts, const float* __restrict__ bn, float eps,
+                                      float* __restrict__ affine6) {
+  // one warp; lane k<6 reduces statistic k
+  __shared__ float st[6];
+  if (threadIdx.x < 6) {
+    float r = partials[threadIdx.x];
+    for (int i = 1; i < nparts; ++i) {
+      const float v = partials[i * 6 + threadIdx.x];
+      r = threadIdx.x < 3 ? fminf(r, v) : fmaxf(r, v);
+    }
+    st[threadIdx.x] = r;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float a[3], b[3], gmin = FLT_MAX, gmax = -FLT_MAX;
+    for (int c = 0; c < 3; ++c) {
+      const float w = bn[c], bias = bn[3 + c], mean = bn[6 + c], var = bn[9 + c];
+      const float invstd = 1.0f / sqrtf(var + eps);
+      a[c] = w * invstd;
+      b[c] = bias - mean * a[c];
+      const float y0 = a[c] * st[c] + b[c], y1 = a[c] * st[3 + c] + b[c];
+      gmin = fminf(gmin, fminf(y0, y1));
+      gmax = fmaxf(gmax, fmaxf(y0, y1));
+    }
+    if (gmax > 1.0f) {  // encoder.py:132-133
+      for (int c = 0; c < 3; ++c) {
+        a[c] /= 255.0f;
+        b[c] /= 255.0f;
+      }
+      gmin /= 255.0f;
+      gmax /= 255.0f;
+    }
+    if (gmin >= 0.0f && gmax <= 1.0f) {  // encoder.py:134-135
+      for (int c = 0; c < 3; ++c) {
+        a[c] *= 2.0f;
+        b[c] = 2.0f * b[c] - 1.0f;
+      }
+    }
+    for (int c = 0; c < 3; ++c) {
+      affine6[c] = a[c];
+      affine6[3 + c] = b[c];
+    }
+  }
+}
+
+// ------------------------------------------------------------------ generic fp32 NCHW bilinear (align_corners=False)
+__global__ void __launch_bounds__(256) resize_nchw_kernel(const float* __restrict__ src, int planes, int Hs, int Ws, float* __restrict__ dst,
+                                                          int Hd, int Wd) {
+  const float sh = (float)Hs / (float)Hd, sw = (float)Ws / (float)Wd;
+  const long long total = (long long)planes * Hd * Wd;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int X = (int)(i % Wd);
+    const int Y = (int)((i / Wd) % Hd);
+    const long long pl = i / ((long long)Wd * Hd);
+    int y0, y1, x0, x1;
+    float ly, lx;
+    src_index_acf(sh, Y, Hs, y0, y1, ly);
+    src_index_acf(sw, X, Ws, x0, x1, lx);
+    const float* p = src + pl * (long long)Hs * Ws;
+    const float v00 = __ldg(p + (long long)y0 * Ws + x0), v01 = __ldg(p + (long long)y0 * Ws + x1);
+    const float v10 = __ldg(p + (long long)y1 * Ws + x0), v11 = __ldg(p + (long long)y1 * Ws + x1);
+    dst[i] = (1.0f - ly) * ((1.0f - lx) * v00 + lx * v01) + ly * ((1.0f - lx) * v10 + lx * v11);
+  }
+}
+
+// ------------------------------------------------------------------ resize->224^2 + affine + patchify (encoder.py:139-144, tv:277)
+// one thread = 8 consecutive kx of one (b, patch, c, ky): one 16-byte store of the GEMM A operand
+__global__ void __launch_bounds__(256) patchify_kernel(const float* __restrict__ x, int B, int H, int W, const float* __restrict__ affine6,
+                                                       bf16* __restrict__ patches) {
+  const float sh = (float)H / 224.0f, sw = (float)W / 224.0f;
+  const bool identity = (H == 224 && W == 224);
+  const long long total = (long long)B * 196 * 96;  // 768 / 8 groups per patch row
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int grp = (int)(i % 96);
+    const long long row = i / 96;  // b*196 + patch
+    const int patch = (int)(row % 196);
+    const int b = (int)(row / 196);
+    const int c = grp >> 5, ky = (grp >> 1) & 15, kx0 = (grp & 1) * 8;
+    const int Y = (patch / 14) * 16 + ky, X0 = (patch % 14) * 16 + kx0;
+    const float a = __ldg(affine6 + c), bb = __ldg(affine6 + 3 + c);
+    const float* p = x + ((long long)b * 3 + c) * H * W;
+    float v[8];
+    if (identity) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v[j] = __ldg(p + (long long)Y * W + X0 + j);
+    } else {
+      int y0, y1;
+      float ly;
+      src_index_acf(sh, Y, H, y0, y1, ly);
+      const float* r0 = p + (long long)y0 * W;
+      const float* r1 = p + (long long)y1 * W;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        int x0, x1;
+        float lx;
+        src_index_acf(sw, X0 + j, W, x0, x1, lx);
+        v[j] = (1.0f - ly) * ((1.0f - lx) * __ldg(r0 + x0) + lx * __ldg(r0 + x1)) + ly * ((1.0f - lx) * __ldg(r1 + x0) + lx * __ldg(r1 + x1));
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v[j] = fmaf(a, v[j], bb);
+    *reinterpret_cast<uint4*>(patches + row * 768 + grp * 8) =
+        make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
+  }
+}
+
+// ------------------------------------------------------------------ LayerNorm (tv:112,117) fp32 -> bf16, one warp per row
+template <int DIM>
+__global__ void __launch_bounds__(256) layernorm_kernel(const float* __restrict__ x, int rows, const float* __restrict__ gamma,
+                                                        const float* __restrict__ beta, float eps, bf16* __restrict__ out) {
+  constexpr int PER = DIM / 256;  // 8-element groups per lane
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int row = blockIdx.x * 8 + warp;
+  if (row >= rows) return;
+  const float4* xr = reinterpret_cast<const float4*>(x + (size_t)row * DIM);
+  float v[PER * 8];
+  float s = 0.0f;
+#pragma unroll
+  for (int j = 0; j < PER; ++j) {
+    const float4 a = __ldg(xr + (j * 32 + lane) * 2), b = __ldg(xr + (j * 32 + lane) * 2 + 1);
+    v[8 * j + 0] = a.x; v[8 * j + 1] = a.y; v[8 * j + 2] = a.z; v[8 * j + 3] = a.w;
+    v[8 * j + 4] = b.x; v[8 * j + 5] = b.y; v[8 * j + 6] = b.z; v[8 * j + 7] = b.w;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) s += v[8 * j + k];
+  }
+  const float mean = warp_sum(s) * (1.0f / DIM);
+  float q = 0.0f;
+#pragma unroll
+  for (int k = 0; k < PER * 8; ++k) {
+    const float d = v[k] - mean;
+    q = fmaf(d, d, q);
+  }
+  const float rstd = 1.0f / sqrtf(warp_sum(q) * (1.0f / DIM) + eps);
+  const float4* g4 = reinterpret_cast<const float4*>(gamma);
+  const float4* b4 = reinterpret_cast<const float4*>(beta);
+  uint4* o = reinterpret_cast<uint4*>(out + (size_t)row * DIM);
+#pragma unroll
+  for (int j = 0; j < PER; ++j) {
+    const int g = (j * 32 + lane) * 2;
+    const float4 ga = __ldg(g4 + g), gb = __ldg(g4 + g + 1), ba = __ldg(b4 + g), bb = __ldg(b4 + g + 1);
+    const float y0 = (v[8 * j + 0] - mean) * rstd * ga.x + ba.x, y1 = (v[8 * j + 1] - mean) * rstd * ga.y + ba.y;
+    const float y2 = (v[8 * j + 2] - mean) * rstd * ga.z + ba.z, y3 = (v[8 * j + 3] - mean) * rstd * ga.w + ba.w;
+    const float y4 = (v[8 * j + 4] - mean) * rstd * gb.x + bb.x, y5 = (v[8 * j + 5] - mean) * rstd * gb.y + bb.y;
+    const float y6 = (v[8 * j + 6] - mean) * rstd * gb.z + bb.z, y7 = (v[8 * j + 7] - mean) * rstd * gb.w + bb.w;
+    o[j * 32 + lane] = make_uint4(pack_bf16x2(y0, y1), pack_bf16x2(y2, y3), pack_bf16x2(y4, y5), pack_bf16x2(y6, y7));
+  }
+}
+
+// ------------------------------------------------------------------ tokens -> grid rows (encoder.py:69-110), fp32 -> bf16
+__global__ void __launch_bounds__(256) tokens_to_grid_kernel(const float* __restrict__ tok, int B, int strip, int G, bf16* __restrict__ out) {
+  const int T = MDE_VIT_SEQ - strip;  // tokens copied per image
+  const long long total = (long long)B * G * 96;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int grp = (int)(i % 96);
+    const long long row = i / 96;
+    const int g = (int)(row % G), b = (int)(row / G);
+    uint4 o = make_uint4(0, 0, 0, 0);
+    if (g < T) {
+      const float4* s = reinterpret_cast<const float4*>(tok + ((long long)b * MDE_VIT_SEQ + g + strip) * MDE_VIT_DIM + grp * 8);
+      const float4 a = __ldg(s), c = __ldg(s + 1);
+      o = make_uint4(pack_bf16x2(a.x, a.y), pack_bf16x2(a.z, a.w), pack_bf16x2(c.x, c.y), pack_bf16x2(c.z, c.w));
+    }
+    *reinterpret_cast<uint4*>(out + row * MDE_VIT_DIM + grp * 8) = o;
+  }
+}
+
+// ------------------------------------------------------------------ instance norm (encoder.py:167) -> padded NHWC bf16
+// grid (C/64, B), block 256 = 64 channels x 4 row lanes
+__global__ void __launch_bounds__(256) instnorm_kernel(const float* __restrict__ x, int gh, int gw, int C, float eps, bf16* __restrict__ outp,
+                                                       int cstride, int coff, bf16* __restrict__ outf) {
+  const int G = gh * gw;
+  const int cl = threadIdx.x & 63, rl = threadIdx.x >> 6;
+  const int c = blockIdx.x * 64 + cl, b = blockIdx.y;
+  const float* xb = x + (size_t)b * G * C + c;
+  __shared__ float red[4][64];
+  float s = 0.0f;
+  for (int g = rl; g < G; g += 4) s += xb[(size_t)g * C];
+  red[rl][cl] = s;
+  __syncthreads();
+  const float mean = (red[0][cl] + red[1][cl] + red[2][cl] + red[3][cl]) / (float)G;
+  __syncthreads();
+  float q = 0.0f;
+  for (int g = rl; g < G; g += 4) {
+    const float d = xb[(size_t)g * C] - mean;
+    q = fmaf(d, d, q);
+  }
+  red[rl][cl] = q;
+  __syncthreads();
+  const float var = (red[0][cl] + red[1][cl] + red[2][cl] + red[3][cl]) / (float)G;  // biased, like F.instance_norm
+  const float rstd = 1.0f / sqrtf(var + eps);
+  const int H2 = gh + 2, W2 = gw + 2;
+  for (int g = rl; g < G; g += 4) {
+    const bf16 v = __float2bfloat16_rn((xb[(size_t)g * C] - mean) * rstd);
+    if (outf) outf[((size_t)b * G + g) * C + c] = v;
+    const int y = g / gw, xx = g - y * gw;
+    int ys[3], xs[3], ny = 0, nx = 0;
+    ys[ny++] = y + 1;
+    if (y == 1) ys[ny++] = 0;
+    if (y == gh - 2) ys[ny++] = gh + 1;
+    xs[nx++] = xx + 1;
+    if (xx == 1) xs[nx++] = 0;
+    if (xx == gw - 2) xs[nx++] = gw + 1;
+    for (int iy = 0; iy < ny; ++iy)
+      for (int ix = 0; ix < nx; ++ix) outp[(((size_t)b * H2 + ys[iy]) * W2 + xs[ix]) * cstride + coff + c] = v;
+  }
+}
+
+// ------------------------------------------------------------------ x2 upsample (align_corners=True) + skip resize + concat
+__device__ __forceinline__ void bf16x8_to_float(const uint4& u, float (&f)[8]) {
+  const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const float2 t = __bfloat1622float2(h[k]);
+    f[2 * k] = t.x;
+    f[2 * k + 1] = t.y;
+  }
+}
+__device__ __forceinline__ int reflect_idx(int i, int n) {  // ReflectionPad2d(1) source index for padded coordinate i-1
+  return i < 0 ? -i : (i >= n ? 2 * n - 2 - i : i);
+}
+
+__global__ void __launch_bounds__(256) upsample_concat_kernel(const bf16* __restrict__ a, int B, int h, int w, int ca, const bf16* __restrict__ s,
+                                                              int hs, int ws, int cs, bf16* __restrict__ out) {
+  const int Ho = 2 * h, Wo = 2 * w, ct = ca + cs, groups = ct / 8;
+  const float sya = (float)(h - 1) / (float)(Ho - 1), sxa = (float)(w - 1) / (float)(Wo - 1);
+  const float sys = cs ? (float)(hs - 1) / (float)(Ho - 1) : 0.0f, sxs = cs ? (float)(ws - 1) / (float)(Wo - 1) : 0.0f;
+  const long long total = (long long)B * (Ho + 2) * (Wo + 2) * groups;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int grp = (int)(i % groups);
+    long long px = i / groups;
+    const int Xp = (int)(px % (Wo + 2));
+    px /= (Wo + 2);
+    const int Yp = (int)(px % (Ho + 2));
+    const int b = (int)(px / (Ho + 2));
+    const int oy = reflect_idx(Yp - 1, Ho), ox = reflect_idx(Xp - 1, Wo);
+    const int c0 = grp * 8;
+    const bf16* src;
+    int y0, y1, x0, x1, sw2, shw, cc, cstr;
+    float ly, lx;
+    if (c0 < ca) {
+      src_index_act(sya, oy, h, y0, y1, ly);
+      src_index_act(sxa, ox, w, x0, x1, lx);
+      src = a + (size_t)b * (h + 2) * (w + 2) * ca;
+      sw2 = w + 2; shw = 0; cc = c0; cstr = ca;
+    } else {
+      src_index_act(sys, oy, hs, y0, y1, ly);
+      src_index_act(sxs, ox, ws, x0, x1, lx);
+      src = s + (size_t)b * (hs + 2) * (ws + 2) * cs;
+      sw2 = ws + 2; shw = 0; cc = c0 - ca; cstr = cs;
+    }
+    (void)shw;
+    const uint4 u00 = __ldg(reinterpret_cast<const uint4*>(src + ((size_t)(y0 + 1) * sw2 + x0 + 1) * cstr + cc));
+    const uint4 u01 = __ldg(reinterpret_cast<const uint4*>(src + ((size_t)(y0 + 1) * sw2 + x1 + 1) * cstr + cc));
+    const uint4 u10 = __ldg(reinterpret_cast<const uint4*>(src + ((size_t)(y1 + 1) * sw2 + x0 + 1) * cstr + cc));
+    const uint4 u11 = __ldg(reinterpret_cast<const uint4*>(src + ((size_t)(y1 + 1) * sw2 + x1 + 1) * cstr + cc));
+    float f00[8], f01[8], f10[8], f11[8], r[8];
+    bf16x8_to_float(u00, f00);
+    bf16x8_to_float(u01, f01);
+    bf16x8_to_float(u10, f10);
+    bf16x8_to_float(u11, f11);
+#pragma unroll
+    for (int k = 0; k < 8; ++k)
+      r[k] = (1.0f - ly) * ((1.0f - lx) * f00[k] + lx * f01[k]) + ly * ((1.0f - lx) * f10[k] + lx * f11[k]);
+    *reinterpret_cast<uint4*>(out + (((size_t)b * (Ho + 2) + Yp) * (Wo + 2) + Xp) * ct + c0) =
+        make_uint4(pack_bf16x2(r[0], r[1]), pack_bf16x2(r[2], r[3]), pack_bf16x2(r[4], r[5]), pack_bf16x2(r[6], r[7]));
+  }
+}
+
+// ------------------------------------------------------------------ rgb -> grid channels of a padded NHWC buffer (enhanced_model.py:95-98)
+__global__ void __launch_bounds__(256) rgb_to_grid_kernel(const float* __restrict__ x, int B, int H, int W, int gh, int gw, bf16* __restrict__ out,
+                                                          int cstride, int coff, int cfill) {
+  const float sh = (float)H / (float)gh, sw = (float)W / (float)gw;
+  const int total = B * gh * gw;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int xx = i % gw, y = (i / gw) % gh, b = i / (gw * gh);
+    int y0, y1, x0, x1;
+    float ly, lx;
+    src_index_acf(sh, y, H, y0, y1, ly);
+    src_index_acf(sw, xx, W, x0, x1, lx);
+    bf16* dst = out + (((size_t)b * (gh + 2) + y + 1) * (gw + 2) + xx + 1) * cstride + coff;
+    for (int c = 0; c < cfill; ++c) {
+      float v = 0.0f;
+      if (c < 3) {
+        const float* p = x + ((size_t)b * 3 + c) * H * W;
+        v = (1.0f - ly) * ((1.0f - lx) * __ldg(p + (size_t)y0 * W + x0) + lx * __ldg(p + (size_t)y0 * W + x1)) +
+            ly * ((1.0f - lx) * __ldg(p + (size_t)y1 * W + x0) + lx * __ldg(p + (size_t)y1 * W + x1));
+      }
+      dst[c] = __float2bfloat16_rn(v);
+    }
+  }
+}
+
+// ------------------------------------------------------------------ output stage (model.py:89-100, enhanced_model.py:266-277, layers.py:16-25)
+struct MapTable {
+  mde_map_desc m[MDE_MAX_MAPS];
+  int n;
+};
+
+template <bool VEC4>
+__global__ void __launch_bounds__(256) resize_maps_kernel(const __grid_constant__ MapTable tab, int B, int H, int W, float min_disp, float disp_range) {
+  constexpr int PX = VEC4 ? 4 : 1;
+  const int wq = W / PX;
+  const long long per_map = (long long)B * H * wq;
+  const long long total = per_map * tab.n;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int mi = (int)(i / per_map);
+    long long r = i - (long long)mi * per_map;
+    const int xq = (int)(r % wq);
+    r /= wq;
+    const int Y = (int)(r % H), b = (int)(r / H);
+    const mde_map_desc& d = tab.m[mi];
+    const float sh = (float)d.hs / (float)H, sw = (float)d.ws / (float)W;
+    int y0, y1;
+    float ly;
+    src_index_acf(sh, Y, d.hs, y0, y1, ly);
+    const float* r0 = d.src + ((size_t)b * d.hs + y0) * d.ws;
+    const float* r1 = d.src + ((size_t)b * d.hs + y1) * d.ws;
+    float o[PX], dep[PX];
+#pragma unroll
+    for (int j = 0; j < PX; ++j) {
+      int x0, x1;
+      float lx;
+      src_index_acf(sw, xq * PX + j, d.ws, x0, x1, lx);
+      const float v00 = __ldg(r0 + x0) * d.mul, v01 = __ldg(r0 + x1) * d.mul, v10 = __ldg(r1 + x0) * d.mul, v11 = __ldg(r1 + x1) * d.mul;
+      o[j] = (1.0f - ly) * ((1.0f - lx) * v00 + lx * v01) + ly * ((1.0f - lx) * v10 + lx * v11);
+      dep[j] = 1.0f / (min_disp + disp_range * o[j]);
+    }
+    const size_t off = ((size_t)b * H + Y) * W + (size_t)xq * PX;
+    if constexpr (VEC4) {
+      if (d.dst_disp) __stcs(reinterpret_cast<float4*>(d.dst_disp + off), make_float4(o[0], o[1], o[2], o[3]));
+      if (d.dst_disp2) __stcs(reinterpret_cast<float4*>(d.dst_disp2 + off), make_float4(o[0], o[1], o[2], o[3]));
+      if (d.dst_depth) __stcs(reinterpret_cast<float4*>(d.dst_depth + off), make_float4(dep[0], dep[1], dep[2], dep[3]));
+    } else {
+      if (d.dst_disp) d.dst_disp[off] = o[0];
+      if (d.dst_disp2) d.dst_disp2[off] = o[0];
+      if (d.dst_depth) d.dst_depth[off] = dep[0];
+    }
+  }
+}
+
+// ------------------------------------------------------------------ enhanced low-res tail (enhanced_model.py:199-215,244-263)
+__device__ __forceinline__ float bilinear_acf(const float* p, int hs, int ws, int Hd, int Wd, int Y, int X, float mul) {
+  int y0, y1, x0, x1;
+  float ly, lx;
+  src_index_acf((float)hs / (float)Hd, Y, hs, y0, y1, ly);
+  src_index_acf((float)ws / (float)Wd, X, ws, x0, x1, lx);
+  const float v00 = p[(size_t)y0 * ws + x0] * mul, v01 = p[(size_t)y0 * ws + x1] * mul, v10 = p[(size_t)y1 * ws + x0] * mul,
+              v11 = p[(size_t)y1 * ws + x1] * mul;
+  return (1.0f - ly) * ((1.0f - lx) * v00 + lx * v01) + ly * ((1.0f - lx) * v10 + lx * v11);
+}
+
+__global__ void __launch_bounds__(256) enh_fuse_kernel(const float* __restrict__ d0, const float* __restrict__ d1, const float* __restrict__ d2,
+                                                       const float* __restrict__ refn, int B, int h0, int w0, int gh, int gw, float mul,
+                                                       const float* __restrict__ fw, float* __restrict__ fused) {
+  // softmax over the three fusion weights (enhanced_model.py:70)
+  const float a0 = fw[0], a1 = fw[1], a2 = fw[2];
+  const float m = fmaxf(a0, fmaxf(a1, a2));
+  const float e0 = expf(a0 - m), e1 = expf(a1 - m), e2 = expf(a2 - m);
+  const float inv = 1.0f / (e0 + e1 + e2);
+  const float w_0 = e0 * inv, w_1 = e1 * inv, w_2 = e2 * inv;
+  const int total = B * h0 * w0;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int X = i % w0, Y = (i / w0) % h0, b = i / (w0 * h0);
+    const float r = (gh != h0 || gw != w0) ? bilinear_acf(refn + (size_t)b * gh * gw, gh, gw, h0, w0, Y, X, 1.0f)
+                                           : refn[((size_t)b * gh + Y) * gw + X];
+    const float s0 = (d0[i] + r) * mul;
+    const float s1 = bilinear_acf(d1 + (size_t)b * 4 * h0 * w0, 2 * h0, 2 * w0, h0, w0, Y, X, mul);
+    const float s2 = bilinear_acf(d2 + (size_t)b * 16 * h0 * w0, 4 * h0, 4 * w0, h0, w0, Y, X, mul);
+    fused[i] = w_0 * s0 + w_1 * s1 + w_2 * s2;
+  }
+}
+
+static inline int grid_for(long long work_items, int threads) {
+  long long blocks = (work_items + threads - 1) / threads;
+  const long long cap = (long long)sm_count() * 16;
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  return (int)blocks;
+}
+
+}  // namespace mde
+
+using namespace mde;
+
+extern "C" int mde_input_range(const float* x, int B, int H, int W, const float* bn4x3, float eps, float* scratch, float* affine6,
+                               mde_stream_t stream) {
+  MDE_CHECK_ARG(x && bn4x3 && scratch && affine6, "mde_input_range: null pointer");
+  MDE_CHECK_ARG(B > 0 && H > 0 && W > 0 && ((long long)H * W) % 4 == 0, "mde_input_range: H*W must be a positive multiple of 4 (H=%d W=%d)", H, W);
+  MDE_CHECK_ARG((uintptr_t)x % 16 == 0, "mde_input_range: x must be 16-byte aligned");
+  const long long n4 = (long long)B * 3 * H * W / 4;
+  int parts = sm_count() * 4;
+  if (parts > 1024) parts = 1024;
+  if (parts > n4) parts = (int)n4;
+  minmax_kernel<<<parts, 256, 0, stream>>>(reinterpret_cast<const float4*>(x), n4, H * W / 4, scratch);
+  MDE_CHECK_LAUNCH();
+  range_finalize_kernel<<<1, 32, 0, stream>>>(scratch, parts, bn4x3, eps, affine6);
+  MDE_CHECK_LAUNCH();
+  return MDE_OK;
+}
+
+extern "C" int mde_resize_bilinear_nchw(const float* src, int B, int C, int Hs, int Ws, float* dst, int Hd, int Wd, mde_stream_t stream) {
+  MDE_CHECK_ARG(src && dst && B > 0 && C > 0 && Hs > 0 && Ws > 0 && Hd > 0 && Wd > 0, "mde_resize_bilinear_nchw: bad arguments");
+  const long long total = (long long)B * C * Hd * Wd;
+  resize_nchw_kernel<<<grid_for(total, 256), 256, 0, stream>>>(src, B * C, Hs, Ws, dst, Hd, Wd);
+  MDE_CHECK_LAUNCH();
+  return MDE_OK;
+}
+
+extern "C" int mde_preprocess_patchify(const float* x, int B, int H, int W, const float* affine6, mde_bf16* patches, mde_stream_t stream) {
+  MDE_CHECK_ARG(x && affine6 && patches && B > 0 && H > 0 && W > 0, "mde_preprocess_patchify: bad arguments");
+  MDE_CHECK_ARG((uintptr_t)patches % 16 == 0, "mde_preprocess_patchify: patches must be 16-byte aligned");
+  const long long total = (long long)B * 196 * 96;
+  patchify_kernel<<<grid_for(total, 256), 256, 0, stream>>>(x, B, H, W, affine6, reinterpret_cast<bf16*>(patches));
+  MDE_CHECK_LAUNCH();
+  return MDE_OK;
+}
+
+extern "C" int mde_layernorm_bf16(const float* x, int rows, int dim, const float* gamma, const float* beta, float eps, mde_bf16* out,
+                                  mde_stream_t stream) {
+  MDE_CHECK_ARG(x && gamma && beta && out && rows > 0, "mde_layernorm_bf16: bad arguments");
+  MDE_CHECK_ARG(((uintptr_t)x | (uintptr_t)out | (uintptr_t)gamma | (uintptr_t)beta) % 16 == 0, "mde_layernorm_bf16: pointers must be 16-byte aligned");
+  if (dim != 768) {
+    set_error("mde_layernorm_bf16: dim=%d not built (768 only)", dim);
+    return MDE_ERR_UNSUPPORTED;
+  }
+  layernorm_kernel<768><<<ceil_div(rows, 8), 256, 0, stream>>>(x, rows, gamma, beta, eps, reinterpret_cast<bf16*>(out));
+  MDE_CHECK_LAUNCH();
+  return MDE_OK;
+}
+
+extern "C" int mde_tokens_to_grid_bf16(const float* tokens, int B, int strip_cls, int G, mde_bf16* out, mde_stream_t stream) {
+  MDE_CHECK_ARG(tokens && out && B > 0, "mde_tokens_to_grid_bf16: bad arguments");
+  MDE_CHECK_ARG((strip_cls == 0 || strip_cls == 1) && G >= MDE_VIT_SEQ - strip_cls, "mde_tokens_to_grid_bf16: G=%d too small", G);
+  const long long total = (long long)B * G * 96;
+  tokens_to_grid_kernel<<<grid_for(total, 256), 256, 0, stream>>>(tokens, B, strip_cls, G, reinterpret_cast<bf16*>(out));
+  MDE_CHECK_LAUNCH();
+  return MDE_OK;
+}
+
+extern "C" int mde_instnorm_nhwc(const float* x, int B, int gh, int gw, int C, float eps, mde_bf16* out_padded, int out_cstride, int out_coff,
+                                 mde_bf16* out_flat, mde_stream_t stream) {
+  MDE_CHECK_ARG(x && out_padded && B > 0 && gh >= 3 && gw >= 3, "mde_instnorm_nhwc: bad arguments");
+  MDE_CHECK_ARG(C % 64 == 0 && out_coff + C <= out_cstride, "mde_instnorm_nhwc: C must be a multiple of 64 and fit the output stride");
+  instnorm_kernel<<<dim3(C / 64, B), 256, 0, stream>>>(x, gh, gw, C, eps, reinterpret_cast<bf16*>(out_padded), out_cstride, out_coff,
+                                                       reinterpret_cast<bf16*>(out_flat));
+  MDE_CHECK_LAUNCH();
+  return MDE_OK;
+}
+
+extern "C" int mde_upsample2x_concat_nhwc(const mde_bf16* a, int B, int h, int w, int ca, const mde_bf16* s, int hs, int ws, int cs,
+                                          mde_bf16* out, mde_stream_t stream) {
+  MDE_CHECK_ARG(a && out && B > 0 && h >= 2 && w >= 2 && ca > 0 && ca % 8 == 0, "mde_upsample2x_concat_nhwc: bad arguments");
+  MDE_CHECK_ARG((s == nullptr) == (cs == 0) && cs % 8 == 0, "mde_upsample2x_concat_nhwc: skip tensor / cs mismatch");
+  if (s) MDE_CHECK_ARG(hs >= 2 && ws >= 2, "mde_upsample2x_concat_nhwc: bad skip size");
+  const long long total = (long long)B * (2 * h + 2) * (2 * w + 2) * ((ca + cs) / 8);
+  upsample_concat_kernel<<<grid_for(total, 256), 256, 0, stream>>>(reinterpret_cast<const bf16*>(a), B, h, w, ca, reinterpret_cast<const bf16*>(s),
+                                                                   hs, ws, cs, reinterpret_cast<bf16*>(out));
+  MDE_CHECK_LAUNCH();
+  return MDE_OK;
+}
+
+extern "C" int mde_rgb_to_grid_nhwc(const float* x, int B, int H, int W, int gh, int gw, mde_bf16* out_padded, int out_cstride, int out_coff,
+                                    int cfill, mde_stream_t stream) {
+  MDE_CHECK_ARG(x && out_padded && B > 0 && cfill >= 3 && out_coff + cfill <= out_cstride, "mde_rgb_to_grid_nhwc: bad arguments");
+  rgb_to_grid_kernel<<<grid_for((long long)B * gh * gw, 256), 256, 0, stream>>>(x, B, H, W, gh, gw, reinterpret_cast<bf16*>(out_padded),
+                                                                               out_cstride, out_coff, cfill);
+  MDE_CHECK_LAUNCH();
+  return MDE_OK;
+}
+
+extern "C" int mde_resize_maps(const mde_map_desc* maps, int n_maps, int B, int H, int W, float min_disp, float max_disp, mde_stream_t stream) {
+  MDE_CHECK_ARG(maps && n_maps >= 1 && n_maps <= MDE_MAX_MAPS && B > 0 && H > 0 && W > 0, "mde_resize_maps: bad arguments");
+  MapTable tab;
+  tab.n = n_maps;
+  bool vec = (W % 4 == 0);
+  for (int i = 0; i < n_maps; ++i) {
+    tab.m[i] = maps[i];
+    MDE_CHECK_ARG(maps[i].src && maps[i].hs > 0 && maps[i].ws > 0, "mde_resize_maps: map %d has no source", i);
+    const uintptr_t al = (uintptr_t)maps[i].dst_disp | (uintptr_t)maps[i].dst_disp2 | (uintptr_t)maps[i].dst_depth;
+    if (al % 16 != 0) vec = false;
+  }
+  const float range = max_disp - min_disp;
+  if (vec) {
+    const long long total = (long long)n_maps * B * H * (W / 4);
+    resize_maps_kernel<true><<<grid_for(total, 256), 256, 0, stream>>>(tab, B, H, W, min_disp, range);
+  } else {
+    const long long total = (long long)n_maps * B * H * W;
+    resize_maps_kernel<false><<<grid_for(total, 256), 256, 0, stream>>>(tab, B, H, W, min_disp, range);
+  }
+  MDE_CHECK_LAUNCH();
+  return MDE_OK;
+}
+
+extern "C" int mde_enh_fuse(const float* d0, const float* d1, const float* d2, const float* refinement, int B, int h0, int w0, int gh, int gw,
+                            float mul, const float* fusion_w3, float* fused, mde_stream_t stream) {
+  MDE_CHECK_ARG(d0 && d1 && d2 && refinement && fusion_w3 && fused && B > 0 && h0 > 0 && w0 > 0, "mde_enh_fuse: bad arguments");
+  enh_fuse_kernel<<<grid_for((long long)B * h0 * w0, 256), 256, 0, stream>>>(d0, d1, d2, refinement, B, h0, w0, gh, gw, mul, fusion_w3, fused);
+  MDE_CHECK_LAUNCH();
+  return MDE_OK;
+}

@@ -1,0 +1,321 @@
+"""Forward-path orchestration: one ``DepthEngine`` per model instance.
+
+The engine owns (a) the packed kernel weights (re-derived whenever a parameter tensor
+changes or the module moves), (b) one pre-allocated ``Workspace`` per input geometry and
+(c) optionally a CUDA graph of the whole ViT + decoder section per geometry, so a forward is
+``range/patchify`` -> graph replay -> output kernel, with no host synchronisation anywhere
+(the reference's ``x.max() > 1.0`` host branch, encoder.py:132-135, is evaluated on device).
+
+Reference call stack being replaced: ``model.py:32-102`` / ``enhanced_model.py:152-279`` ->
+``encoder.py:112-187`` -> torchvision ViT -> ``decoder.py:90-173``.
+"""
+from __future__ import annotations
+
+import os
+
+import torch
+
+from . import _lib as L
+from . import ops
+from .packing import pack_conv, pack_decoder, pack_encoder, pack_enhanced
+
+BF16, F32 = torch.bfloat16, torch.float32
+HOOKS = (2, 5, 8, 11)
+DEC_CH = (256, 128, 64, 32, 16)
+
+
+def grid_shape(Hp: int, Wp: int):
+    """encoder.py:69-110 for T=197 tokens: (gh, gw, strip_cls)."""
+    h, w = Hp // 16, Wp // 16
+    if h * w == 196:
+        return h, w, True
+    if h * w == 197:
+        raise ValueError("inputs whose /16 grid has exactly 197 cells (a 1x197 strip) are not supported")
+    return 14, 15, False  # int(sqrt(197)) x ceil(197/14), CLS kept, 13 zero cells appended
+
+
+def _fingerprint(module):
+    return tuple((t.data_ptr(), t._version, t.device.index) for t in list(module.parameters()) + list(module.buffers()))
+
+
+class Workspace:
+    """All intermediates of one forward for a fixed (B, Hp, Wp); allocated once."""
+
+    def __init__(self, dev, B, H0, W0, enhanced):
+        Hp, Wp = H0, W0
+        if H0 % 16 or W0 % 16:  # model.py:51-54
+            Hp, Wp = (H0 // 16 + 1) * 16, (W0 // 16 + 1) * 16
+        if (Hp * Wp) % 4:
+            raise ValueError("unsupported input size")
+        self.B, self.H0, self.W0, self.Hp, self.Wp = B, H0, W0, Hp, Wp
+        self.gh, self.gw, self.strip = grid_shape(Hp, Wp)
+        gh, gw = self.gh, self.gw
+        G = gh * gw
+        M = B * L.VIT_SEQ
+        e = lambda *s, dt=BF16: torch.empty(*s, device=dev, dtype=dt)
+        z = lambda *s, dt=BF16: torch.zeros(*s, device=dev, dtype=dt)
+        self.xp = e(B, 3, Hp, Wp, dt=F32) if (Hp, Wp) != (H0, W0) else None
+        self.scratch = e(L.RANGE_SCRATCH_FLOATS, dt=F32)
+        self.affine = e(6, dt=F32)
+        self.patches = e(B * 196, 768)
+        self.xa, self.xb = e(M, 768, dt=F32), e(M, 768, dt=F32)
+        self.taps = [e(M, 768, dt=F32) for _ in range(4)]
+        self.h = e(M, 768)
+        self.q, self.k = e(B * 12 * L.VIT_SEQ * 64), e(B * 12 * L.VIT_SEQ * 64)
+        self.vt = z(B * 12 * 64 * L.VT_PITCH)
+        self.attn = e(M, 768)
+        self.mlp = e(M, 3072)
+        self.grid_a = e(B * G, 768)
+        self.reduced = e(B * G, 256, dt=F32)
+        c0 = 320 if enhanced else 256  # feature 0 carries the 3 rgb + 61 zero channels of the refinement conv
+        self.feats = [z(B, gh + 2, gw + 2, c0)] + [e(B, gh + 2, gw + 2, 256) for _ in range(3)]
+        # decoder
+        self.d_init = e(B, gh + 2, gw + 2, 256)
+        self.d_a, self.d_s, self.d_cat, self.d_x, self.disp = [], [], [], [], []
+        h, w = gh, gw
+        for i in range(4):
+            co = DEC_CH[i + 1]
+            self.d_a.append(e(B, h + 2, w + 2, co))
+            self.d_s.append(e(B, gh + 2, gw + 2, co) if i < 3 else None)
+            h, w = 2 * h, 2 * w
+            self.d_cat.append(e(B, h + 2, w + 2, co * (2 if i < 3 else 1)))
+            self.d_x.append(e(B, h + 2, w + 2, co))
+            self.disp.append(e(B, h, w, dt=F32))
+        self.d_x3b = e(B, h + 2, w + 2, 16)  # mars_adapt output
+        if enhanced:
+            self.flat = [None, e(B * G, 256), e(B * G, 256), None]
+            self.qkv = e(B * G, 384, dt=F32)
+            self.enh = [None, e(B, gh + 2, gw + 2, 256), e(B, gh + 2, gw + 2, 256), None]
+            self.u1, self.u2 = e(B, gh + 2, gw + 2, 128), e(B, gh + 2, gw + 2, 128)
+            self.r1, self.r2 = e(B, gh + 2, gw + 2, 256), e(B, gh + 2, gw + 2, 128)
+            self.unc = e(B, gh, gw, dt=F32)
+            self.refn = e(B, gh, gw, dt=F32)
+            self.fused = e(B, 2 * gh, 2 * gw, dt=F32)
+        self.graph = None
+        self.graph_scale = None
+
+
+class DepthEngine:
+    def __init__(self, module, kind: str):
+        self.module = module
+        self.kind = kind
+        self.enhanced = kind == "enhanced"
+        self._fp = None
+        self._w = None
+        self._ws = {}
+        # CUDA graphs remove ~150 launch latencies per forward; MDE_NO_GRAPH=1 runs eagerly (debugging)
+        self.use_graph = os.environ.get("MDE_NO_GRAPH", "0") != "1"
+        self.launches_per_forward = 0
+
+    # ------------------------------------------------------------------ weights
+    def weights(self):
+        fp = _fingerprint(self.module)
+        if fp != self._fp:
+            dev = next(self.module.parameters()).device
+            if dev.type != "cuda":
+                raise RuntimeError("the model must live on a CUDA (sm_100) device: there is no CPU path — call model.to('cuda')")
+            with torch.cuda.device(dev):
+                ops.device_check()
+                sd = self.module.state_dict()
+                w = {"enc": pack_encoder(sd), "dec": pack_decoder(sd)}
+                if self.enhanced:
+                    w["enh"] = pack_enhanced(sd)
+            self._w, self._fp = w, fp
+            for ws in self._ws.values():
+                ws.graph = None
+        return self._w
+
+    def workspace(self, dev, B, H0, W0):
+        key = (dev.index, B, H0, W0)
+        ws = self._ws.get(key)
+        if ws is None:
+            if len(self._ws) >= 4:  # bound the cache
+                self._ws.pop(next(iter(self._ws)))
+            ws = self._ws[key] = Workspace(dev, B, H0, W0, self.enhanced)
+        return ws
+
+    # ------------------------------------------------------------------ stages
+    def _pre(self, ws, w, x):
+        """pad-to-/16 resize (model.py:51-54), range heuristic (encoder.py:129-135), resize->224 + patchify."""
+        xin = x
+        if ws.xp is not None:
+            xin = ops.resize_bilinear_nchw(x, ws.Hp, ws.Wp, out=ws.xp)
+        ops.input_range(xin, w["enc"]["bn4x3"], 1e-5, ws.scratch, ws.affine)
+        ops.preprocess_patchify(xin, ws.affine, ws.patches)
+        n = 3 + (ws.xp is not None)
+        if self.enhanced:
+            ops.rgb_to_grid(xin, ws.gh, ws.gw, ws.feats[0], 256, 64)  # enhanced_model.py:95-98
+            n += 1
+        return n
+
+    def _vit(self, ws, w, want=None):
+        enc, B = w["enc"], ws.B
+        n = 0
+        ops.gemm(ws.patches, enc["patch_w"], enc["patch_b"], L.EPI_PATCH_EMBED, ws.xa, enc["pos"], enc["cls"])
+        n += 1
+        # residual stream: x_in --(attention)--> x_mid --(MLP)--> x_out.  x_in is dead once the out-proj
+        # epilogue has read it, so two working buffers suffice; hooked layers (encoder.py:44-50) write
+        # x_out straight into their tap buffer, which then serves as the next layer's x_in (no copy).
+        work = (ws.xa, ws.xb)
+        x_in = ws.xa
+        for i, ly in enumerate(enc["layers"]):
+            x_mid = work[1] if x_in is work[0] else work[0]
+            x_out = ws.taps[HOOKS.index(i)] if i in HOOKS else (work[0] if x_mid is work[1] else work[1])
+            ops.layernorm(x_in, ly["ln1_w"], ly["ln1_b"], 1e-6, ws.h)
+            ops.gemm(ws.h, ly["qkv_w"], ly["qkv_b"], L.EPI_QKV_SPLIT, ws.q, ws.k, ws.vt)
+            ops.vit_attention(ws.q, ws.k, ws.vt, B, ws.attn)
+            ops.gemm(ws.attn, ly["proj_w"], ly["proj_b"], L.EPI_BIAS_RESID_F32, x_mid, x_in)
+            ops.layernorm(x_mid, ly["ln2_w"], ly["ln2_b"], 1e-6, ws.h)
+            ops.gemm(ws.h, ly["fc1_w"], ly["fc1_b"], L.EPI_BIAS_GELU_BF16, ws.mlp)
+            ops.gemm(ws.mlp, ly["fc2_w"], ly["fc2_b"], L.EPI_BIAS_RESID_F32, x_out, x_mid)
+            n += 7
+            if want is not None and i == 0:
+                want["block0_q"] = ws.q.clone()
+                want["block0_attn"] = ws.attn.clone()
+                want["block0_out"] = x_out.clone()
+            x_in = x_out
+        return n
+
+    def _features(self, ws, w):
+        enc, B, gh, gw = w["enc"], ws.B, ws.gh, ws.gw
+        G = gh * gw
+        n = 0
+        for i in range(4):
+            ops.tokens_to_grid(ws.taps[i], B, ws.strip, G, ws.grid_a)
+            rw, rb = enc["reduce"][i]
+            ops.gemm(ws.grid_a, rw, rb, L.EPI_BIAS_F32, ws.reduced)
+            flat = ws.flat[i] if self.enhanced else None
+            ops.instnorm_nhwc(ws.reduced, B, gh, gw, 256, 1e-5, ws.feats[i], 0, flat)
+            n += 3
+        return n
+
+    def _conv(self, inp, h, w_, cin, wb, cout, act, out=None, out_f32=None, ksize=3, pad=L.PAD_REFLECT):
+        ops.conv_nhwc(inp, h, w_, cin, wb[0], wb[1], cout, ksize, pad, act, out_bf16=out, out_f32=out_f32)
+
+    def _enhanced_pre_decoder(self, ws, w):
+        """enhanced_model.py:183-196: attention on features 1,2; uncertainty + refinement heads on feature 0."""
+        enh, B, gh, gw = w["enh"], ws.B, ws.gh, ws.gw
+        n = 0
+        for i in (1, 2):
+            pw, pb, gamma = enh["attn"][str(i)]
+            ops.gemm(ws.flat[i], pw, pb, L.EPI_BIAS_F32, ws.qkv)
+            ops.spatial_attention(ws.flat[i], ws.qkv, B, gh, gw, gamma, ws.enh[i])
+            n += 2
+        f0 = ws.feats[0]
+        self._conv(f0, gh, gw, 256, enh["unc1"], 128, L.ACT_ELU, out=ws.u1, pad=L.PAD_ZERO)
+        self._conv(ws.u1, gh, gw, 128, enh["unc2"], 128, L.ACT_ELU, out=ws.u2, pad=L.PAD_ZERO)
+        self._conv(ws.u2, gh, gw, 128, enh["unc3"], 1, L.ACT_SIGMOID, out_f32=ws.unc, ksize=1)
+        self._conv(f0, gh, gw, 320, enh["ref1"], 256, L.ACT_ELU, out=ws.r1, pad=L.PAD_ZERO)
+        self._conv(ws.r1, gh, gw, 256, enh["ref2"], 128, L.ACT_ELU, out=ws.r2, pad=L.PAD_ZERO)
+        self._conv(ws.r2, gh, gw, 128, enh["ref3"], 1, L.ACT_NONE, out_f32=ws.refn, ksize=1)
+        return n + 6
+
+    def _decoder(self, ws, w, feats):
+        """decoder.py:90-173."""
+        dec, gh, gw = w["dec"], ws.gh, ws.gw
+        n = 0
+        self._conv(feats[3], gh, gw, 256, dec["init_conv"], 256, L.ACT_ELU, out=ws.d_init)
+        n += 1
+        x, h, w_ = ws.d_init, gh, gw
+        for i in range(4):
+            ci, co = DEC_CH[i], DEC_CH[i + 1]
+            self._conv(x, h, w_, ci, dec[f"upconv_{i}_0"], co, L.ACT_ELU, out=ws.d_a[i])
+            s = None
+            if i < 3:
+                s = ws.d_s[i]
+                self._conv(feats[2 - i], gh, gw, 256, dec[f"skip_{i}"], co, L.ACT_ELU, out=s)
+                n += 1
+            ops.upsample2x_concat(ws.d_a[i], h, w_, s, gh, gw, ws.d_cat[i])
+            h, w_ = 2 * h, 2 * w_
+            self._conv(ws.d_cat[i], h, w_, ws.d_cat[i].shape[-1], dec[f"upconv_{i}_1"], co, L.ACT_ELU, out=ws.d_x[i])
+            x = ws.d_x[i]
+            n += 3
+            if i == 3:
+                self._conv(x, h, w_, 16, dec["mars_adapt"], 16, L.ACT_ELU, out=ws.d_x3b)
+                x = ws.d_x3b
+                n += 1
+            self._conv(x, h, w_, co, dec[f"dispconv_{i}"], 1, L.ACT_SIGMOID, out_f32=ws.disp[i], pad=L.PAD_ZERO)
+            n += 1
+        return n
+
+    def _body(self, ws, w, scale, want=None):
+        """Everything between the input kernels and the output kernel (graph-captured)."""
+        n = self._vit(ws, w, want)
+        n += self._features(ws, w)
+        feats = ws.feats
+        if self.enhanced:
+            n += self._enhanced_pre_decoder(ws, w)
+            feats = [ws.feats[0], ws.enh[1], ws.enh[2], ws.feats[3]]
+        n += self._decoder(ws, w, feats)
+        if self.enhanced:
+            mul = 1.0 if scale is None else scale
+            ops.enh_fuse(ws.disp[0], ws.disp[1], ws.disp[2], ws.refn, ws.B, 2 * ws.gh, 2 * ws.gw, ws.gh, ws.gw, mul, w["enh"]["fusion_w"], ws.fused)
+            n += 1
+        return n
+
+    def _post(self, ws, scale):
+        """model.py:89-100 / enhanced_model.py:266-277 + layers.py:16-25 — one kernel writes every output map."""
+        B, H0, W0 = ws.B, ws.H0, ws.W0
+        dev = ws.scratch.device
+        new = lambda: torch.empty(B, 1, H0, W0, device=dev, dtype=F32)
+        mul = 1.0 if scale is None else scale
+        out = {}
+        if not self.enhanced:
+            maps = []
+            for i in range(4):
+                out[("disp", i)] = new()
+                maps.append((ws.disp[i], mul, out[("disp", i)], None))
+            ops.resize_maps(maps, B, H0, W0)
+            return out, 1
+        for i in range(4):
+            out[("disp", i)] = new()
+        out[("uncertainty", 0)] = new()
+        out[("disp_unrefined", 0)] = new()
+        # ("disp_fused",0) holds the same values as ("disp",0) (enhanced_model.py:259-263); one buffer, two keys
+        out[("disp_fused", 0)] = out[("disp", 0)]
+        for i in range(4):
+            out[("depth", i)] = new()
+        maps = [(ws.fused, 1.0, out[("disp", 0)], out[("depth", 0)])]
+        maps += [(ws.disp[i], mul, out[("disp", i)], out[("depth", i)]) for i in (1, 2, 3)]
+        maps += [(ws.unc, 1.0, out[("uncertainty", 0)], None), (ws.disp[0], 1.0, out[("disp_unrefined", 0)], None)]
+        ops.resize_maps(maps, B, H0, W0, 1 / 100.0, 1 / 0.1)
+        return out, 1
+
+    # ------------------------------------------------------------------ forward
+    def forward(self, x, scale, want=None):
+        w = self.weights()
+        dev = next(self.module.parameters()).device
+        if not x.is_cuda or x.device != dev:
+            raise RuntimeError(f"input is on {x.device} but the model is on {dev}")
+        if x.dtype != F32 or not x.is_contiguous():
+            x = x.to(F32).contiguous()
+        B, _, H0, W0 = x.shape
+        with torch.cuda.device(dev):
+            ws = self.workspace(dev, B, H0, W0)
+            n = self._pre(ws, w, x)
+            if want is not None or not self.use_graph:
+                n += self._body(ws, w, scale, want)
+            else:
+                if ws.graph is None or ws.graph_scale != scale:
+                    ws.body_launches = self._body(ws, w, scale)  # warm-up run (also the first result)
+                    torch.cuda.current_stream().synchronize()
+                    g = torch.cuda.CUDAGraph()
+                    with torch.cuda.graph(g):
+                        self._body(ws, w, scale)
+                    ws.graph, ws.graph_scale = g, scale
+                ws.graph.replay()
+                n += ws.body_launches
+            out, k = self._post(ws, scale)
+            self.launches_per_forward = n + k
+            if want is not None:
+                want["ws"] = ws
+        return out
+
+
+# ---------------------------------------------------------------------- refinement.py modules
+def texture_refine_forward(module, depth_map, rgb_image):
+    raise NotImplementedError("TextureAwareRefinementModule (refinement.py:57-107) is not built yet (SURVEY.md §8 a18)")
+
+
+def depth_fusion_forward(module, depth_scales):
+    raise NotImplementedError("MultiScaleDepthFusion (refinement.py:131-183) is not built yet (SURVEY.md §8 a19)")

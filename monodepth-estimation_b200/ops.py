@@ -1,0 +1,142 @@
+"""Tensor-level wrappers over the C-ABI (``include/mde.h``).
+
+Each function takes CUDA torch tensors, checks dtype/contiguity, and enqueues the kernel on
+``torch.cuda.current_stream()``.  PyTorch is used only to own device memory and streams; no
+torch operator runs here.  Outputs are allocated by the caller (``engine.Workspace``) or, for
+test convenience, by the wrapper when ``out`` is omitted.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+
+from . import _lib as L
+
+BF16, F32 = torch.bfloat16, torch.float32
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _ptr(t, dtype=None):
+    if t is None:
+        return C.c_void_p(0)
+    if not t.is_cuda:
+        raise ValueError("mde ops need CUDA tensors (there is no CPU path)")
+    if not t.is_contiguous():
+        raise ValueError("mde ops need contiguous tensors")
+    if dtype is not None and t.dtype != dtype:
+        raise ValueError(f"expected {dtype}, got {t.dtype}")
+    return C.c_void_p(t.data_ptr())
+
+
+def device_check():
+    L.call("mde_device_check")
+
+
+def sm_count() -> int:
+    return int(L.load().mde_sm_count())
+
+
+def input_range(x, bn4x3, eps, scratch=None, affine=None):
+    B, _, H, W = x.shape
+    scratch = scratch if scratch is not None else torch.empty(L.RANGE_SCRATCH_FLOATS, device=x.device, dtype=F32)
+    affine = affine if affine is not None else torch.empty(6, device=x.device, dtype=F32)
+    L.call("mde_input_range", _ptr(x, F32), B, H, W, _ptr(bn4x3, F32), float(eps), _ptr(scratch, F32), _ptr(affine, F32), _stream())
+    return affine
+
+
+def resize_bilinear_nchw(src, Hd, Wd, out=None):
+    B, Cc, Hs, Ws = src.shape
+    out = out if out is not None else torch.empty(B, Cc, Hd, Wd, device=src.device, dtype=F32)
+    L.call("mde_resize_bilinear_nchw", _ptr(src, F32), B, Cc, Hs, Ws, _ptr(out, F32), Hd, Wd, _stream())
+    return out
+
+
+def preprocess_patchify(x, affine, out=None):
+    B, _, H, W = x.shape
+    out = out if out is not None else torch.empty(B * 196, 768, device=x.device, dtype=BF16)
+    L.call("mde_preprocess_patchify", _ptr(x, F32), B, H, W, _ptr(affine, F32), _ptr(out, BF16), _stream())
+    return out
+
+
+def gemm(a, w, bias, epilogue, out, aux0=None, aux1=None, M=None):
+    """out = epilogue(a[M,K] @ w[N,K]^T); see ``mde_gemm_bf16`` for the aux operands."""
+    M = a.shape[0] if M is None else M
+    K = a.shape[1]
+    N = w.shape[0]
+    ldo = out.shape[-1] if epilogue <= L.EPI_BIAS_F32 else 0
+    L.call("mde_gemm_bf16", _ptr(a, BF16), a.stride(0), _ptr(w, BF16), w.stride(0), M, N, K, epilogue, _ptr(bias, F32), _ptr(out), ldo,
+           _ptr(aux0), _ptr(aux1), _stream())
+    return out
+
+
+def layernorm(x, gamma, beta, eps, out=None):
+    rows, dim = x.shape
+    out = out if out is not None else torch.empty(rows, dim, device=x.device, dtype=BF16)
+    L.call("mde_layernorm_bf16", _ptr(x, F32), rows, dim, _ptr(gamma, F32), _ptr(beta, F32), float(eps), _ptr(out, BF16), _stream())
+    return out
+
+
+def vit_attention(q, k, vt, B, out=None):
+    out = out if out is not None else torch.empty(B * L.VIT_SEQ, L.VIT_DIM, device=q.device, dtype=BF16)
+    L.call("mde_vit_attention", _ptr(q, BF16), _ptr(k, BF16), _ptr(vt, BF16), B, _ptr(out, BF16), _stream())
+    return out
+
+
+def tokens_to_grid(tokens, B, strip_cls, G, out=None):
+    out = out if out is not None else torch.empty(B * G, L.VIT_DIM, device=tokens.device, dtype=BF16)
+    L.call("mde_tokens_to_grid_bf16", _ptr(tokens, F32), B, int(strip_cls), G, _ptr(out, BF16), _stream())
+    return out
+
+
+def instnorm_nhwc(x, B, gh, gw, Cc, eps, out_padded, out_coff=0, out_flat=None):
+    L.call("mde_instnorm_nhwc", _ptr(x, F32), B, gh, gw, Cc, float(eps), _ptr(out_padded, BF16), out_padded.shape[-1], out_coff,
+           _ptr(out_flat, BF16), _stream())
+    return out_padded
+
+
+def conv_nhwc(inp, h, w, cin, wpacked, bias, cout, ksize, padding, act, out_bf16=None, out_coff=0, out_f32=None):
+    B = inp.shape[0]
+    L.call("mde_conv_nhwc", _ptr(inp, BF16), B, h, w, cin, inp.shape[-1], _ptr(wpacked, BF16), _ptr(bias, F32), cout, ksize, padding, act,
+           _ptr(out_bf16, BF16), 0 if out_bf16 is None else out_bf16.shape[-1], out_coff, _ptr(out_f32, F32), _stream())
+    return out_bf16 if out_bf16 is not None else out_f32
+
+
+def upsample2x_concat(a, h, w, s, hs, ws, out):
+    B, ca = a.shape[0], a.shape[-1]
+    cs = 0 if s is None else s.shape[-1]
+    L.call("mde_upsample2x_concat_nhwc", _ptr(a, BF16), B, h, w, ca, _ptr(s, BF16), hs, ws, cs, _ptr(out, BF16), _stream())
+    return out
+
+
+def rgb_to_grid(x, gh, gw, out_padded, out_coff, cfill):
+    B, _, H, W = x.shape
+    L.call("mde_rgb_to_grid_nhwc", _ptr(x, F32), B, H, W, gh, gw, _ptr(out_padded, BF16), out_padded.shape[-1], out_coff, cfill, _stream())
+    return out_padded
+
+
+def resize_maps(maps, B, H, W, min_disp=0.01, max_disp=10.0):
+    """maps: list of (src [B,hs,ws] f32, mul, dst_disp|None, dst_depth|None)."""
+    arr = (L.MapDesc * len(maps))()
+    for i, (src, mul, dd, dz) in enumerate(maps):
+        arr[i].src = src.data_ptr()
+        arr[i].hs, arr[i].ws = src.shape[-2], src.shape[-1]
+        arr[i].mul = float(mul)
+        arr[i].dst_disp = dd.data_ptr() if dd is not None else None
+        arr[i].dst_disp2 = None
+        arr[i].dst_depth = dz.data_ptr() if dz is not None else None
+    L.call("mde_resize_maps", arr, len(maps), B, H, W, float(min_disp), float(max_disp), _stream())
+
+
+def spatial_attention(x_flat, qkv, B, gh, gw, gamma, out_padded):
+    L.call("mde_spatial_attention", _ptr(x_flat, BF16), _ptr(qkv, F32), B, gh, gw, _ptr(gamma, F32), _ptr(out_padded, BF16), _stream())
+    return out_padded
+
+
+def enh_fuse(d0, d1, d2, refinement, B, h0, w0, gh, gw, mul, fusion_w, fused):
+    L.call("mde_enh_fuse", _ptr(d0, F32), _ptr(d1, F32), _ptr(d2, F32), _ptr(refinement, F32), B, h0, w0, gh, gw, float(mul),
+           _ptr(fusion_w, F32), _ptr(fused, F32), _stream())
+    return fused
