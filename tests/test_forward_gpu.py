@@ -1,0 +1,116 @@
+"""GPU: the drop-in model classes (C-ABI kernels underneath) against
+ (a) the CPU fp32 oracle on the same synthetic weights/inputs, and
+ (b) the committed golden vectors produced by the real reference.
+Tolerances are the north_star's: depth rel-L2 <= 1e-2, uncertainty max-abs <= 1e-2 (bf16 storage,
+fp32 accumulate, vs the fp32 reference)."""
+import pytest
+import torch
+
+from helpers import DEPTH_REL_L2, UNCERTAINTY_MAX_ABS, cached_model, load_golden, max_abs, rel_l2, synth_images
+from oracle import depth_oracle as O
+from oracle.cases import CASES, key_name, stride_for
+
+pytestmark = pytest.mark.gpu
+
+
+def check_outputs(got, ref, where):
+    assert set(got) == set(ref), (set(got) ^ set(ref))
+    for k in ref:
+        g, r = got[k].float().cpu(), ref[k]
+        assert g.shape == r.shape, (k, g.shape, r.shape)
+        assert torch.isfinite(g).all(), k
+        if k[0] == "uncertainty":
+            assert max_abs(g, r) <= UNCERTAINTY_MAX_ABS, (where, k, max_abs(g, r))
+        else:
+            assert rel_l2(g, r) <= DEPTH_REL_L2, (where, k, rel_l2(g, r))
+        if k[0] == "disp":  # what the callers compute, run_mars_depth.py:137
+            assert rel_l2(1 / g.clamp(min=1e-6), 1 / r.clamp(min=1e-6)) <= DEPTH_REL_L2, (where, k, "1/disp")
+
+
+@pytest.mark.parametrize("name", ["std_224_b2_none", "std_256x320_b1_ingalt", "std_256_b1_byte_other", "std_256_b1_signed_none",
+                                  "std_160x200_b2_ing", "enh_224_b2_none", "enh_320x256_b1_sat", "std_518_b1_rover", "enh_518_b1_roverh"])
+def test_model_vs_oracle(name):
+    kind, B, H, W, ikind, md, wseed, iseed = CASES[name]
+    x = synth_images(B, H, W, iseed, ikind)
+    m_cpu = cached_model(kind, wseed)
+    with torch.no_grad():
+        fwd = O.standard_forward if kind == "standard" else O.enhanced_forward
+        ref = fwd(m_cpu.state_dict(), x, md)
+    m = cached_model(kind, wseed, "cuda")
+    got = m(x.cuda(), md)
+    check_outputs(got, ref, name)
+    for v in got.values():
+        assert v.shape == (B, 1, H, W) and v.dtype == torch.float32 and v.is_cuda
+
+
+@pytest.mark.parametrize("name", ["std_1024_b1_rover", "enh_1024_b1_rover", "std_518_b1_rover", "enh_518_b1_roverh", "enh_224_b2_none"])
+def test_model_vs_reference_golden(name):
+    kind, B, H, W, ikind, md, wseed, iseed = CASES[name]
+    gold = load_golden(name)
+    m = cached_model(kind, wseed, "cuda")
+    got = m(synth_images(B, H, W, iseed, ikind).cuda(), md)
+    for k, v in got.items():
+        n = key_name(k)
+        ref = torch.from_numpy(gold[n])
+        sy, sx = stride_for(v.shape[2]), stride_for(v.shape[3])
+        g = v[:, :, ::sy, ::sx].float().cpu()
+        if k[0] == "uncertainty":
+            assert max_abs(g, ref) <= UNCERTAINTY_MAX_ABS, (k, max_abs(g, ref))
+        else:
+            assert rel_l2(g, ref) <= DEPTH_REL_L2, (k, rel_l2(g, ref))
+
+
+def test_batch_shard_invariance():
+    """Images are independent: forward(B=4) == cat(forward(2), forward(2)) bit for bit."""
+    m = cached_model("enhanced", 0, "cuda")
+    x = synth_images(4, 256, 256, 77).cuda()
+    md = {"source": "rover"}
+    full = m(x, md)
+    a, b = m(x[:2].contiguous(), md), m(x[2:].contiguous(), md)
+    for k in full:
+        assert torch.equal(full[k], torch.cat([a[k], b[k]])), k
+
+
+def test_graph_and_eager_agree_and_repeat():
+    import monodepth_estimation_b200.engine as E
+
+    m = cached_model("standard", 0, "cuda")
+    x = synth_images(2, 320, 320, 78).cuda()
+    eng = m._get_engine()
+    eng.use_graph = False
+    eager = m(x, None)
+    eng.use_graph = True
+    g1 = m(x, None)
+    g2 = m(x, None)  # graph replay
+    for k in eager:
+        assert torch.equal(eager[k], g1[k]) and torch.equal(g1[k], g2[k]), k
+    assert eng.launches_per_forward > 100
+
+
+def test_metadata_scales_and_reload():
+    """Source scaling is applied after the sigmoid (model.py:89-92); load_state_dict re-packs the weights."""
+    m = cached_model("standard", 0, "cuda")
+    x = synth_images(1, 224, 224, 79).cuda()
+    base = m(x, None)
+    sat = m(x, {"source": "satellite"})
+    assert rel_l2(sat[("disp", 0)], base[("disp", 0)] * 0.01) < 1e-6
+    from helpers import build_model
+
+    m2 = build_model("standard", 3, "cuda")
+    o3 = m2(x, None)
+    m2.load_state_dict(cached_model("standard", 0).state_dict())
+    o0 = m2(x, None)
+    assert torch.equal(o0[("disp", 0)], base[("disp", 0)]) and not torch.equal(o3[("disp", 0)], o0[("disp", 0)])
+
+
+def test_errors_are_loud():
+    from helpers import build_model
+
+    m = cached_model("standard", 0, "cuda")
+    with pytest.raises(RuntimeError):
+        m(torch.rand(1, 3, 224, 224), None)  # CPU tensor: no fallback
+    m_cpu = build_model("standard", 0)
+    with pytest.raises(RuntimeError):
+        m_cpu(torch.rand(1, 3, 224, 224), None)
+    with pytest.raises(ValueError):
+        m(torch.rand(1, 1, 224, 224).cuda(), None)

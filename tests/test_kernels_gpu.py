@@ -1,0 +1,317 @@
+"""GPU: every C-ABI kernel against a plain PyTorch fp32 statement of the same op, on seeded inputs.
+
+The kernels compute in bf16 storage / fp32 accumulate, so tolerances are bf16-level
+(2^-8 relative per rounding); each test states its own."""
+import math
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+from helpers import from_padded_nhwc, max_abs, rel_l2, to_padded_nhwc
+
+pytestmark = pytest.mark.gpu
+
+BF16 = torch.bfloat16
+
+
+def _mods():
+    from monodepth_estimation_b200 import _lib as L
+    from monodepth_estimation_b200 import ops
+
+    return L, ops
+
+
+def _rand(*shape, seed=0, scale=1.0, dtype=torch.float32):
+    g = torch.Generator(device="cpu").manual_seed(seed)
+    return (torch.randn(*shape, generator=g) * scale).to(dtype).cuda()
+
+
+# --------------------------------------------------------------------------- GEMM
+@pytest.mark.parametrize("M,N,K", [(128, 128, 64), (300, 256, 128), (1000, 768, 768), (197 * 3, 2304, 768), (333, 384, 256), (260, 768, 3072)])
+def test_gemm_bias_f32(M, N, K):
+    L, ops = _mods()
+    a, w, b = _rand(M, K, seed=1, dtype=BF16), _rand(N, K, seed=2, scale=K ** -0.5, dtype=BF16), _rand(N, seed=3)
+    out = torch.full((M, N), float("nan"), device="cuda")
+    ops.gemm(a, w, b, L.EPI_BIAS_F32, out)
+    ref = a.float() @ w.float().t() + b
+    assert rel_l2(out, ref) < 1e-5, rel_l2(out, ref)
+
+
+def test_gemm_bias_bf16_and_gelu():
+    L, ops = _mods()
+    M, N, K = 500, 3072, 768
+    a, w, b = _rand(M, K, seed=4, dtype=BF16), _rand(N, K, seed=5, scale=K ** -0.5, dtype=BF16), _rand(N, seed=6)
+    ref = a.float() @ w.float().t() + b
+    out = torch.empty(M, N, device="cuda", dtype=BF16)
+    ops.gemm(a, w, b, L.EPI_BIAS_BF16, out)
+    assert rel_l2(out.float(), ref) < 4e-3
+    ops.gemm(a, w, b, L.EPI_BIAS_GELU_BF16, out)
+    assert rel_l2(out.float(), F.gelu(ref)) < 4e-3
+    assert max_abs(out.float(), F.gelu(ref)) < 3e-2
+
+
+def test_gemm_residual_f32_and_row_tail():
+    L, ops = _mods()
+    M, N, K = 197 * 2 + 5, 768, 768  # M not a multiple of 128: TMA zero-fills, epilogue masks
+    a, w, b = _rand(M, K, seed=7, dtype=BF16), _rand(N, K, seed=8, scale=K ** -0.5, dtype=BF16), _rand(N, seed=9)
+    r = _rand(M, N, seed=10)
+    out = torch.full((M + 3, N), 7.0, device="cuda")
+    ops.gemm(a, w, b, L.EPI_BIAS_RESID_F32, out, r, M=M)
+    ref = a.float() @ w.float().t() + b + r
+    assert rel_l2(out[:M], ref) < 1e-5
+    assert float((out[M:] - 7.0).abs().max()) == 0.0  # rows beyond M untouched
+
+
+def test_gemm_patch_embed_epilogue():
+    L, ops = _mods()
+    B = 3
+    a, w, b = _rand(B * 196, 768, seed=11, dtype=BF16), _rand(768, 768, seed=12, scale=768 ** -0.5, dtype=BF16), _rand(768, seed=13)
+    pos, cls = _rand(197, 768, seed=14, scale=0.02), _rand(768, seed=15, scale=0.02)
+    out = torch.empty(B * 197, 768, device="cuda")
+    ops.gemm(a, w, b, L.EPI_PATCH_EMBED, out, pos, cls)
+    tok = (a.float() @ w.float().t() + b).view(B, 196, 768)
+    ref = torch.cat([cls.view(1, 1, 768).expand(B, -1, -1), tok], 1) + pos
+    assert rel_l2(out.view(B, 197, 768), ref) < 1e-5
+
+
+def test_gemm_qkv_split_epilogue():
+    L, ops = _mods()
+    B = 2
+    M = B * 197
+    a, w, b = _rand(M, 768, seed=16, dtype=BF16), _rand(2304, 768, seed=17, scale=768 ** -0.5, dtype=BF16), _rand(2304, seed=18)
+    q = torch.empty(B * 12 * 197 * 64, device="cuda", dtype=BF16)
+    k = torch.empty_like(q)
+    vt = torch.zeros(B * 12 * 64 * L.VT_PITCH, device="cuda", dtype=BF16)
+    ops.gemm(a, w, b, L.EPI_QKV_SPLIT, q, k, vt)
+    ref = (a.float() @ w.float().t() + b).view(B, 197, 3, 12, 64).permute(2, 0, 3, 1, 4)  # [3,B,12,197,64]
+    assert rel_l2(q.view(B, 12, 197, 64).float(), ref[0] * 0.125) < 4e-3
+    assert rel_l2(k.view(B, 12, 197, 64).float(), ref[1]) < 4e-3
+    v = vt.view(B, 12, 64, L.VT_PITCH)[..., :197].float().transpose(-1, -2)
+    assert rel_l2(v, ref[2]) < 4e-3
+
+
+# --------------------------------------------------------------------------- LayerNorm / attention
+def test_layernorm():
+    _, ops = _mods()
+    x, g, b = _rand(197 * 3 + 1, 768, seed=20, scale=2.0) + 0.3, _rand(768, seed=21) + 1.0, _rand(768, seed=22)
+    out = ops.layernorm(x, g, b, 1e-6)
+    ref = F.layer_norm(x, (768,), g, b, 1e-6)
+    assert rel_l2(out.float(), ref) < 3e-3
+    assert max_abs(out.float(), ref) < 5e-2
+
+
+@pytest.mark.parametrize("B", [1, 3])
+def test_vit_attention(B):
+    L, ops = _mods()
+    q, k, v = (_rand(B, 12, 197, 64, seed=30 + i, dtype=BF16) for i in range(3))
+    qs = (q.float() * 0.125).to(BF16)
+    vt = torch.zeros(B, 12, 64, L.VT_PITCH, device="cuda", dtype=BF16)
+    vt[..., :197] = v.transpose(-1, -2)
+    out = ops.vit_attention(qs.contiguous().view(-1), k.contiguous().view(-1), vt.view(-1), B)
+    att = torch.softmax(qs.float() @ k.float().transpose(-1, -2), dim=-1)
+    ref = (att @ v.float()).transpose(1, 2).reshape(B * 197, 768)
+    assert rel_l2(out.float(), ref) < 1e-2, rel_l2(out.float(), ref)
+    assert max_abs(out.float(), ref) < 3e-2
+
+
+# --------------------------------------------------------------------------- conv / upsample / norm
+CONV_CASES = [
+    # B, h, w, cin, cout, ksize, pad, act
+    (2, 14, 15, 256, 256, 3, "reflect", "elu"),
+    (2, 14, 15, 256, 128, 3, "zero", "elu"),
+    (1, 28, 30, 256, 128, 3, "reflect", "elu"),
+    (2, 28, 30, 128, 64, 3, "reflect", "elu"),
+    (1, 56, 60, 128, 64, 3, "reflect", "elu"),
+    (1, 56, 60, 64, 32, 3, "reflect", "elu"),
+    (1, 112, 120, 64, 32, 3, "reflect", "none"),
+    (1, 112, 120, 32, 16, 3, "reflect", "elu"),
+    (1, 224, 240, 16, 16, 3, "reflect", "elu"),
+    (2, 14, 14, 256, 64, 3, "reflect", "sigmoid"),
+    (1, 14, 15, 320, 256, 3, "zero", "elu"),
+    (2, 14, 15, 128, 16, 1, "zero", "none"),
+]
+
+
+@pytest.mark.parametrize("B,h,w,cin,cout,ks,pad,act", CONV_CASES)
+def test_conv_bf16_out(B, h, w, cin, cout, ks, pad, act):
+    L, ops = _mods()
+    from monodepth_estimation_b200.packing import pack_conv
+
+    x = _rand(B, cin, h, w, seed=40)
+    wt = _rand(cout, cin, ks, ks, seed=41, scale=(cin * ks * ks) ** -0.5)
+    bs = _rand(cout, seed=42, scale=0.1)
+    xp = to_padded_nhwc(x)
+    wp, bp = pack_conv(wt, bs)
+    out = torch.full((B, h + 2, w + 2, cout), float("nan"), device="cuda", dtype=BF16)
+    ops.conv_nhwc(xp, h, w, cin, wp, bp, cout, ks, L.PAD_REFLECT if pad == "reflect" else L.PAD_ZERO,
+                  {"none": L.ACT_NONE, "elu": L.ACT_ELU, "sigmoid": L.ACT_SIGMOID}[act], out_bf16=out)
+    xr, wr = xp.float().permute(0, 3, 1, 2)[:, :, 1:-1, 1:-1], wp[:cout].float().view(cout, ks, ks, cin).permute(0, 3, 1, 2)
+    if ks == 3:
+        xr = F.pad(xr, (1, 1, 1, 1), mode="reflect") if pad == "reflect" else F.pad(xr, (1, 1, 1, 1))
+    ref = F.conv2d(xr, wr, bs)
+    ref = {"none": lambda t: t, "elu": F.elu, "sigmoid": torch.sigmoid}[act](ref)
+    got = from_padded_nhwc(out, with_border=True)
+    assert rel_l2(got[:, :, 1:-1, 1:-1], ref) < 5e-3, rel_l2(got[:, :, 1:-1, 1:-1], ref)
+    # the border must hold the reflection of the interior
+    assert max_abs(got, F.pad(got[:, :, 1:-1, 1:-1], (1, 1, 1, 1), mode="reflect")) == 0.0
+
+
+@pytest.mark.parametrize("B,h,w,cin", [(2, 28, 30, 128), (1, 56, 60, 64), (1, 112, 120, 32), (1, 224, 240, 16), (3, 14, 15, 128)])
+def test_conv_head_f32_out(B, h, w, cin):
+    L, ops = _mods()
+    from monodepth_estimation_b200.packing import pack_conv
+
+    x = _rand(B, cin, h, w, seed=50)
+    wt, bs = _rand(1, cin, 3, 3, seed=51, scale=(cin * 9) ** -0.5), _rand(1, seed=52)
+    xp = to_padded_nhwc(x)
+    wp, bp = pack_conv(wt, bs)
+    out = torch.full((B, h, w), float("nan"), device="cuda")
+    ops.conv_nhwc(xp, h, w, cin, wp, bp, 1, 3, L.PAD_ZERO, L.ACT_SIGMOID, out_f32=out)
+    ref = torch.sigmoid(F.conv2d(xp.float().permute(0, 3, 1, 2)[:, :, 1:-1, 1:-1], wp[:1].float().view(1, 3, 3, cin).permute(0, 3, 1, 2), bs, padding=1))
+    assert max_abs(out, ref[:, 0]) < 2e-5, max_abs(out, ref[:, 0])
+
+
+def test_conv_folded_batchnorm_and_channel_offset():
+    L, ops = _mods()
+    from monodepth_estimation_b200.packing import pack_conv
+
+    B, h, w, cin, cout = 2, 14, 15, 256, 128
+    x, wt, bs = _rand(B, cin, h, w, seed=60), _rand(cout, cin, 3, 3, seed=61, scale=(cin * 9) ** -0.5), _rand(cout, seed=62, scale=0.1)
+    g, beta, mean, var = _rand(cout, seed=63) * 0.2 + 1, _rand(cout, seed=64, scale=0.1), _rand(cout, seed=65, scale=0.1), torch.rand(cout).cuda() + 0.5
+    wp, bp = pack_conv(wt, bs, (g, beta, mean, var))
+    xp = to_padded_nhwc(x)
+    out = torch.zeros(B, h + 2, w + 2, 320, device="cuda", dtype=BF16)
+    ops.conv_nhwc(xp, h, w, cin, wp, bp, cout, 3, L.PAD_REFLECT, L.ACT_ELU, out_bf16=out, out_coff=64)
+    y = F.conv2d(F.pad(xp.float().permute(0, 3, 1, 2)[:, :, 1:-1, 1:-1], (1, 1, 1, 1), mode="reflect"), wt, bs)
+    ref = F.elu(F.batch_norm(y, mean, var, g, beta, False, 0.0, 1e-5))
+    got = from_padded_nhwc(out)
+    assert rel_l2(got[:, 64:192], ref) < 8e-3
+    assert float(got[:, :64].abs().max()) == 0.0 and float(got[:, 192:].abs().max()) == 0.0
+
+
+@pytest.mark.parametrize("B,h,w,ca,cs", [(2, 14, 15, 128, 128), (1, 28, 30, 64, 64), (1, 112, 120, 16, 0), (1, 14, 14, 32, 32)])
+def test_upsample_concat(B, h, w, ca, cs):
+    _, ops = _mods()
+    a = _rand(B, ca, h, w, seed=70)
+    ap = to_padded_nhwc(a)
+    sp, s = None, None
+    if cs:
+        s = _rand(B, cs, 14, 15, seed=71)
+        sp = to_padded_nhwc(s)
+    out = torch.full((B, 2 * h + 2, 2 * w + 2, ca + cs), float("nan"), device="cuda", dtype=BF16)
+    ops.upsample2x_concat(ap, h, w, sp, 14, 15, out)
+    ref = F.interpolate(ap.float().permute(0, 3, 1, 2)[:, :, 1:-1, 1:-1], size=(2 * h, 2 * w), mode="bilinear", align_corners=True)
+    if cs:
+        rs = F.interpolate(sp.float().permute(0, 3, 1, 2)[:, :, 1:-1, 1:-1], size=(2 * h, 2 * w), mode="bilinear", align_corners=True)
+        ref = torch.cat([ref, rs], 1)
+    got = from_padded_nhwc(out, with_border=True)
+    assert rel_l2(got[:, :, 1:-1, 1:-1], ref) < 3e-3
+    assert max_abs(got, F.pad(got[:, :, 1:-1, 1:-1], (1, 1, 1, 1), mode="reflect")) == 0.0
+
+
+@pytest.mark.parametrize("gh,gw", [(14, 15), (14, 14)])
+def test_tokens_to_grid_and_instnorm(gh, gw):
+    _, ops = _mods()
+    B, G = 2, gh * gw
+    strip = G == 196
+    tok = _rand(B, 197, 768, seed=80)
+    grid = ops.tokens_to_grid(tok.view(-1, 768), B, strip, G)
+    ref = tok[:, 1:] if strip else torch.cat([tok, tok.new_zeros(B, G - 197, 768)], 1)
+    assert max_abs(grid.view(B, G, 768).float(), ref.to(BF16).float()) == 0.0
+    x = _rand(B, G, 256, seed=81, scale=3.0) + 1.5
+    outp = torch.zeros(B, gh + 2, gw + 2, 320, device="cuda", dtype=BF16)
+    flat = torch.empty(B * G, 256, device="cuda", dtype=BF16)
+    ops.instnorm_nhwc(x.view(-1, 256), B, gh, gw, 256, 1e-5, outp, 0, flat)
+    refn = F.instance_norm(x.view(B, gh, gw, 256).permute(0, 3, 1, 2))
+    got = from_padded_nhwc(outp, with_border=True)[:, :256]
+    assert rel_l2(got[:, :, 1:-1, 1:-1], refn) < 3e-3
+    assert max_abs(got, F.pad(got[:, :, 1:-1, 1:-1], (1, 1, 1, 1), mode="reflect")) == 0.0
+    assert max_abs(flat.view(B, gh, gw, 256).permute(0, 3, 1, 2).float(), got[:, :, 1:-1, 1:-1]) == 0.0
+
+
+# --------------------------------------------------------------------------- input / output stages
+@pytest.mark.parametrize("kind,H,W", [("unit", 256, 320), ("byte", 224, 224), ("signed", 528, 528), ("unit", 1024, 1024)])
+def test_input_range_and_patchify(kind, H, W):
+    _, ops = _mods()
+    from helpers import synth_images
+    from oracle import depth_oracle as O
+
+    x = synth_images(2, H, W, 5, kind).cuda()
+    sd = {"encoder.normalize.weight": torch.tensor([1.0, 0.9, 1.1]).cuda(), "encoder.normalize.bias": torch.tensor([0.0, 0.01, -0.01]).cuda(),
+          "encoder.normalize.running_mean": torch.tensor([0.0, 0.02, -0.02]).cuda(), "encoder.normalize.running_var": torch.tensor([1.0, 1.1, 0.9]).cuda()}
+    if kind == "unit":  # default BN statistics: the common 2x-1 branch
+        sd = {k: (torch.ones(3) if k.endswith(("weight", "running_var")) else torch.zeros(3)).cuda() for k in sd}
+    bn = torch.cat([sd["encoder.normalize.weight"], sd["encoder.normalize.bias"], sd["encoder.normalize.running_mean"], sd["encoder.normalize.running_var"]])
+    aff = ops.input_range(x, bn, 1e-5)
+    y = O.input_range_map(sd, "encoder.", x)
+    if (H, W) != (224, 224):
+        y = F.interpolate(y, size=(224, 224), mode="bilinear", align_corners=False)
+    ref = y.unfold(2, 16, 16).unfold(3, 16, 16).permute(0, 2, 3, 1, 4, 5).reshape(2 * 196, 768)
+    got = ops.preprocess_patchify(x, aff)
+    assert max_abs(got.float(), ref) < 1.2e-2 * max(1.0, float(ref.abs().max()))
+    assert rel_l2(got.float(), ref) < 4e-3
+
+
+@pytest.mark.parametrize("H,W", [(518, 518), (1024, 1024), (250, 333)])
+def test_resize_maps_and_depth(H, W):
+    _, ops = _mods()
+    B = 2
+    srcs = [torch.rand(B, 28 << i, 30 << i, device="cuda") for i in range(3)]
+    disp = [torch.empty(B, 1, H, W, device="cuda") for _ in srcs]
+    depth = [torch.empty(B, 1, H, W, device="cuda") for _ in srcs]
+    ops.resize_maps([(s, 0.5, d, z) for s, d, z in zip(srcs, disp, depth)], B, H, W, 1 / 100.0, 1 / 0.1)
+    for s, d, z in zip(srcs, disp, depth):
+        ref = F.interpolate((s * 0.5).unsqueeze(1), size=(H, W), mode="bilinear", align_corners=False)
+        assert max_abs(d, ref) < 2e-6
+        assert rel_l2(z, 1 / (0.01 + 9.99 * ref)) < 1e-6
+
+
+def test_resize_bilinear_nchw():
+    _, ops = _mods()
+    x = torch.rand(2, 3, 518, 518, device="cuda")
+    out = ops.resize_bilinear_nchw(x, 528, 528)
+    assert max_abs(out, F.interpolate(x, size=(528, 528), mode="bilinear", align_corners=False)) < 2e-6
+
+
+# --------------------------------------------------------------------------- enhanced-model pieces
+def test_spatial_attention():
+    L, ops = _mods()
+    from oracle import depth_oracle as O
+
+    B, gh, gw = 2, 14, 15
+    G = gh * gw
+    x = _rand(B, 256, gh, gw, seed=90)
+    sd = {"a.query.weight": _rand(32, 256, 1, 1, seed=91, scale=1 / 16), "a.query.bias": _rand(32, seed=92, scale=0.05),
+          "a.key.weight": _rand(32, 256, 1, 1, seed=93, scale=1 / 16), "a.key.bias": _rand(32, seed=94, scale=0.05),
+          "a.value.weight": _rand(256, 256, 1, 1, seed=95, scale=1 / 16), "a.value.bias": _rand(256, seed=96, scale=0.05),
+          "a.gamma": torch.tensor([0.5]).cuda()}
+    xb = x.to(BF16)
+    ref = O.spatial_attention(sd, "a.", xb.float())
+    flat = xb.permute(0, 2, 3, 1).reshape(B * G, 256).contiguous()
+    wq = torch.cat([sd["a.query.weight"], sd["a.key.weight"], sd["a.value.weight"]]).view(320, 256)
+    bq = torch.cat([sd["a.query.bias"], sd["a.key.bias"], sd["a.value.bias"]])
+    from monodepth_estimation_b200.packing import pack_linear
+
+    pw, pb = pack_linear(wq, bq)
+    qkv = torch.empty(B * G, 384, device="cuda")
+    ops.gemm(flat, pw, pb, L.EPI_BIAS_F32, qkv)
+    out = torch.empty(B, gh + 2, gw + 2, 256, device="cuda", dtype=BF16)
+    ops.spatial_attention(flat, qkv, B, gh, gw, sd["a.gamma"], out)
+    got = from_padded_nhwc(out)
+    assert rel_l2(got, ref) < 1e-2, rel_l2(got, ref)
+
+
+def test_enh_fuse():
+    _, ops = _mods()
+    B, gh, gw = 2, 14, 15
+    d = [torch.rand(B, (2 * gh) << i, (2 * gw) << i, device="cuda") for i in range(3)]
+    refn = torch.randn(B, gh, gw, device="cuda") * 0.1
+    fw = torch.tensor([0.3, 0.9, 0.5]).cuda()
+    fused = torch.empty(B, 2 * gh, 2 * gw, device="cuda")
+    ops.enh_fuse(d[0], d[1], d[2], refn, B, 2 * gh, 2 * gw, gh, gw, 0.7, fw, fused)
+    r = F.interpolate(refn.unsqueeze(1), size=(2 * gh, 2 * gw), mode="bilinear", align_corners=False)
+    s = [(d[0].unsqueeze(1) + r) * 0.7, d[1].unsqueeze(1) * 0.7, d[2].unsqueeze(1) * 0.7]
+    wts = torch.softmax(fw, 0)
+    ref = sum(wts[i] * (s[i] if i == 0 else F.interpolate(s[i], size=(2 * gh, 2 * gw), mode="bilinear", align_corners=False)) for i in range(3))
+    assert max_abs(fused.unsqueeze(1), ref) < 2e-6
