@@ -49,17 +49,27 @@ __global__ void __launch_bounds__(256) minmax_kernel(const float4* __restrict__ 
   const long long beg = per * blockIdx.x;
   long long end = beg + per;
   if (end > n4) end = n4;
-  for (long long i = beg + threadIdx.x; i < end; i += blockDim.x) {
-    const float4 v = __ldg(x4 + i);
-    const int c = (int)((i / hw4) % 3);
-    const float lo = fminf(fminf(v.x, v.y), fminf(v.z, v.w));
-    const float hi = fmaxf(fmaxf(v.x, v.y), fmaxf(v.z, v.w));
+  for (long long i0 = beg + threadIdx.x; i0 < end; i0 += 4 * blockDim.x) {
+    float4 v[4];
 #pragma unroll
-    for (int k = 0; k < 3; ++k)
-      if (c == k) {
-        mn[k] = fminf(mn[k], lo);
-        mx[k] = fmaxf(mx[k], hi);
-      }
+    for (int u = 0; u < 4; ++u) {  // 4 independent 16-byte loads in flight per thread
+      const long long i = i0 + u * blockDim.x;
+      v[u] = i < end ? __ldg(x4 + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const long long i = i0 + u * blockDim.x;
+      if (i >= end) break;
+      const int c = (int)((i / hw4) % 3);
+      const float lo = fminf(fminf(v[u].x, v[u].y), fminf(v[u].z, v[u].w));
+      const float hi = fmaxf(fmaxf(v[u].x, v[u].y), fmaxf(v[u].z, v[u].w));
+#pragma unroll
+      for (int k = 0; k < 3; ++k)
+        if (c == k) {
+          mn[k] = fminf(mn[k], lo);
+          mx[k] = fmaxf(mx[k], hi);
+        }
+    }
   }
   __shared__ float red[8][6];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -81,15 +91,17 @@ __global__ void __launch_bounds__(256) minmax_kernel(const float4* __restrict__ 
 
 __global__ void range_finalize_kernel(const float* __restrict__ partials, int nparts, const float* __restrict__ bn, float eps,
                                       float* __restrict__ affine6) {
-  // one warp; lane k<6 reduces statistic k
+  // one warp: lanes stride over the partials, shuffle-reduce each of the 6 statistics
   __shared__ float st[6];
-  if (threadIdx.x < 6) {
-    float r = partials[threadIdx.x];
-    for (int i = 1; i < nparts; ++i) {
-      const float v = partials[i * 6 + threadIdx.x];
-      r = threadIdx.x < 3 ? fminf(r, v) : fmaxf(r, v);
+#pragma unroll
+  for (int k = 0; k < 6; ++k) {
+    float r = k < 3 ? FLT_MAX : -FLT_MAX;
+    for (int i = threadIdx.x; i < nparts; i += 32) {
+      const float v = partials[i * 6 + k];
+      r = k < 3 ? fminf(r, v) : fmaxf(r, v);
     }
-    st[threadIdx.x] = r;
+    r = k < 3 ? warp_min(r) : warp_max(r);
+    if (threadIdx.x == 0) st[k] = r;
   }
   __syncthreads();
   if (threadIdx.x == 0) {
@@ -316,20 +328,19 @@ __global__ void __launch_bounds__(256) upsample_concat_kernel(const bf16* __rest
     const int oy = reflect_idx(Yp - 1, Ho), ox = reflect_idx(Xp - 1, Wo);
     const int c0 = grp * 8;
     const bf16* src;
-    int y0, y1, x0, x1, sw2, shw, cc, cstr;
+    int y0, y1, x0, x1, sw2, cc, cstr;
     float ly, lx;
     if (c0 < ca) {
       src_index_act(sya, oy, h, y0, y1, ly);
       src_index_act(sxa, ox, w, x0, x1, lx);
       src = a + (size_t)b * (h + 2) * (w + 2) * ca;
-      sw2 = w + 2; shw = 0; cc = c0; cstr = ca;
+      sw2 = w + 2; cc = c0; cstr = ca;
     } else {
       src_index_act(sys, oy, hs, y0, y1, ly);
       src_index_act(sxs, ox, ws, x0, x1, lx);
       src = s + (size_t)b * (hs + 2) * (ws + 2) * cs;
-      sw2 = ws + 2; shw = 0; cc = c0 - ca; cstr = cs;
+      sw2 = ws + 2; cc = c0 - ca; cstr = cs;
     }
-    (void)shw;
     const uint4 u00 = __ldg(reinterpret_cast<const uint4*>(src + ((size_t)(y0 + 1) * sw2 + x0 + 1) * cstr + cc));
     const uint4 u01 = __ldg(reinterpret_cast<const uint4*>(src + ((size_t)(y0 + 1) * sw2 + x1 + 1) * cstr + cc));
     const uint4 u10 = __ldg(reinterpret_cast<const uint4*>(src + ((size_t)(y1 + 1) * sw2 + x0 + 1) * cstr + cc));
@@ -377,45 +388,50 @@ struct MapTable {
   int n;
 };
 
+// grid = (ceil(W/PX/256), H, n_maps*B): one block per output row segment.  The two source rows the row
+// interpolates between are staged (pre-multiplied) in shared memory once, so the inner loop is smem reads
+// + FMAs and the stores are full 16-byte streaming stores: the kernel is a pure HBM write stream.
+constexpr int kMaxSrcW = 1024;
 template <bool VEC4>
 __global__ void __launch_bounds__(256) resize_maps_kernel(const __grid_constant__ MapTable tab, int B, int H, int W, float min_disp, float disp_range) {
   constexpr int PX = VEC4 ? 4 : 1;
-  const int wq = W / PX;
-  const long long per_map = (long long)B * H * wq;
-  const long long total = per_map * tab.n;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
-    const int mi = (int)(i / per_map);
-    long long r = i - (long long)mi * per_map;
-    const int xq = (int)(r % wq);
-    r /= wq;
-    const int Y = (int)(r % H), b = (int)(r / H);
-    const mde_map_desc& d = tab.m[mi];
-    const float sh = (float)d.hs / (float)H, sw = (float)d.ws / (float)W;
-    int y0, y1;
-    float ly;
-    src_index_acf(sh, Y, d.hs, y0, y1, ly);
-    const float* r0 = d.src + ((size_t)b * d.hs + y0) * d.ws;
-    const float* r1 = d.src + ((size_t)b * d.hs + y1) * d.ws;
-    float o[PX], dep[PX];
+  __shared__ float s0[kMaxSrcW], s1[kMaxSrcW];
+  const int Y = blockIdx.y;
+  const int mi = blockIdx.z / B, b = blockIdx.z - mi * B;
+  const mde_map_desc& d = tab.m[mi];
+  const int ws = d.ws;
+  int y0, y1;
+  float ly;
+  src_index_acf((float)d.hs / (float)H, Y, d.hs, y0, y1, ly);
+  const float* r0 = d.src + ((size_t)b * d.hs + y0) * ws;
+  const float* r1 = d.src + ((size_t)b * d.hs + y1) * ws;
+  const float mul = d.mul;
+  for (int x = threadIdx.x; x < ws; x += 256) {
+    s0[x] = __ldg(r0 + x) * mul;
+    s1[x] = __ldg(r1 + x) * mul;
+  }
+  __syncthreads();
+  const int xq = blockIdx.x * 256 + threadIdx.x;
+  if (xq * PX >= W) return;
+  const float sw = (float)ws / (float)W;
+  float o[PX], dep[PX];
 #pragma unroll
-    for (int j = 0; j < PX; ++j) {
-      int x0, x1;
-      float lx;
-      src_index_acf(sw, xq * PX + j, d.ws, x0, x1, lx);
-      const float v00 = __ldg(r0 + x0) * d.mul, v01 = __ldg(r0 + x1) * d.mul, v10 = __ldg(r1 + x0) * d.mul, v11 = __ldg(r1 + x1) * d.mul;
-      o[j] = (1.0f - ly) * ((1.0f - lx) * v00 + lx * v01) + ly * ((1.0f - lx) * v10 + lx * v11);
-      dep[j] = 1.0f / (min_disp + disp_range * o[j]);
-    }
-    const size_t off = ((size_t)b * H + Y) * W + (size_t)xq * PX;
-    if constexpr (VEC4) {
-      if (d.dst_disp) __stcs(reinterpret_cast<float4*>(d.dst_disp + off), make_float4(o[0], o[1], o[2], o[3]));
-      if (d.dst_disp2) __stcs(reinterpret_cast<float4*>(d.dst_disp2 + off), make_float4(o[0], o[1], o[2], o[3]));
-      if (d.dst_depth) __stcs(reinterpret_cast<float4*>(d.dst_depth + off), make_float4(dep[0], dep[1], dep[2], dep[3]));
-    } else {
-      if (d.dst_disp) d.dst_disp[off] = o[0];
-      if (d.dst_disp2) d.dst_disp2[off] = o[0];
-      if (d.dst_depth) d.dst_depth[off] = dep[0];
-    }
+  for (int j = 0; j < PX; ++j) {
+    int x0, x1;
+    float lx;
+    src_index_acf(sw, xq * PX + j, ws, x0, x1, lx);
+    o[j] = (1.0f - ly) * ((1.0f - lx) * s0[x0] + lx * s0[x1]) + ly * ((1.0f - lx) * s1[x0] + lx * s1[x1]);
+    dep[j] = 1.0f / (min_disp + disp_range * o[j]);
+  }
+  const size_t off = ((size_t)b * H + Y) * W + (size_t)xq * PX;
+  if constexpr (VEC4) {
+    if (d.dst_disp) __stcs(reinterpret_cast<float4*>(d.dst_disp + off), make_float4(o[0], o[1], o[2], o[3]));
+    if (d.dst_disp2) __stcs(reinterpret_cast<float4*>(d.dst_disp2 + off), make_float4(o[0], o[1], o[2], o[3]));
+    if (d.dst_depth) __stcs(reinterpret_cast<float4*>(d.dst_depth + off), make_float4(dep[0], dep[1], dep[2], dep[3]));
+  } else {
+    if (d.dst_disp) d.dst_disp[off] = o[0];
+    if (d.dst_disp2) d.dst_disp2[off] = o[0];
+    if (d.dst_depth) d.dst_depth[off] = dep[0];
   }
 }
 
@@ -556,17 +572,16 @@ extern "C" int mde_resize_maps(const mde_map_desc* maps, int n_maps, int B, int 
   bool vec = (W % 4 == 0);
   for (int i = 0; i < n_maps; ++i) {
     tab.m[i] = maps[i];
-    MDE_CHECK_ARG(maps[i].src && maps[i].hs > 0 && maps[i].ws > 0, "mde_resize_maps: map %d has no source", i);
+    MDE_CHECK_ARG(maps[i].src && maps[i].hs > 0 && maps[i].ws > 0 && maps[i].ws <= kMaxSrcW, "mde_resize_maps: map %d has no source or is wider than %d", i, kMaxSrcW);
     const uintptr_t al = (uintptr_t)maps[i].dst_disp | (uintptr_t)maps[i].dst_disp2 | (uintptr_t)maps[i].dst_depth;
     if (al % 16 != 0) vec = false;
   }
   const float range = max_disp - min_disp;
+  MDE_CHECK_ARG(H <= 65535 && (long long)n_maps * B <= 65535, "mde_resize_maps: H and n_maps*B must be <= 65535");
   if (vec) {
-    const long long total = (long long)n_maps * B * H * (W / 4);
-    resize_maps_kernel<true><<<grid_for(total, 256), 256, 0, stream>>>(tab, B, H, W, min_disp, range);
+    resize_maps_kernel<true><<<dim3(ceil_div(W / 4, 256), H, n_maps * B), 256, 0, stream>>>(tab, B, H, W, min_disp, range);
   } else {
-    const long long total = (long long)n_maps * B * H * W;
-    resize_maps_kernel<false><<<grid_for(total, 256), 256, 0, stream>>>(tab, B, H, W, min_disp, range);
+    resize_maps_kernel<false><<<dim3(ceil_div(W, 256), H, n_maps * B), 256, 0, stream>>>(tab, B, H, W, min_disp, range);
   }
   MDE_CHECK_LAUNCH();
   return MDE_OK;

@@ -180,8 +180,14 @@ __device__ __forceinline__ void epilogue_chunk(const TcParams& p, float (&v)[NCO
   }
 }
 
+// co-resident CTAs per SM the register budget is compiled for (small tiles hide latency with more CTAs)
+template <int BLOCK_N>
+constexpr int min_ctas() {
+  return BLOCK_N >= 128 ? 1 : (BLOCK_N == 64 ? 2 : (BLOCK_N == 32 ? 3 : 4));
+}
+
 template <int BLOCK_N, int ROWB>
-__global__ void __launch_bounds__(kThreads, 1) tc_gemm_kernel(const __grid_constant__ TcParams p) {
+__global__ void __launch_bounds__(kThreads, min_ctas<BLOCK_N>()) tc_gemm_kernel(const __grid_constant__ TcParams p) {
   constexpr int KCHUNK = ROWB / 2;
   constexpr int A_BYTES = kBlockM * ROWB;
   constexpr int B_BYTES_RAW = BLOCK_N * ROWB;
@@ -349,16 +355,19 @@ static int launch_tc(TcParams& p, cudaStream_t stream) {
   constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   // Large-N tiles own the SM (deep ring); small-N tiles (low-channel convs) leave room for several CTAs per SM
   // because their per-tile MMA time is tiny and latency hiding comes from co-resident CTAs.
-  const int budget = BLOCK_N >= 128 ? 200 * 1024 : (BLOCK_N == 64 ? 96 * 1024 : 48 * 1024);
+  const int budget = BLOCK_N >= 128 ? 200 * 1024 : (220 * 1024) / min_ctas<BLOCK_N>() - 1024;
   int stages = (budget - 2048) / STAGE_BYTES;
   if (stages > kMaxStages) stages = kMaxStages;
   if (stages < 2) stages = 2;
-  const int ctas_per_sm = BLOCK_N >= 128 ? 1 : (BLOCK_N == 64 ? 2 : 4);
   const int smem_bytes = stages * STAGE_BYTES + 1024 /*alignment slack*/ + (2 * kMaxStages + 8) * 8;
-  static bool attr_set = false;  // per instantiation
-  if (!attr_set) {
+  static int ctas_per_sm = 0;  // per instantiation: what the hardware can actually keep resident
+  if (ctas_per_sm == 0) {
     MDE_CHECK_CUDA(cudaFuncSetAttribute(tc_gemm_kernel<BLOCK_N, ROWB>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
-    attr_set = true;
+    int occ = 0;
+    MDE_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, tc_gemm_kernel<BLOCK_N, ROWB>, kThreads, smem_bytes));
+    const int tmem_cols = 2 * BLOCK_N < 32 ? 32 : 2 * BLOCK_N;
+    if (occ > 512 / tmem_cols) occ = 512 / tmem_cols;  // TMEM: 512 columns per SM
+    ctas_per_sm = occ < 1 ? 1 : occ;
   }
   p.stages = stages;
   const int total = p.num_m_tiles * p.num_n_tiles;
