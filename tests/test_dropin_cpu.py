@@ -1,0 +1,69 @@
+"""CPU: the host-side mirror is a drop-in for the reference classes, and libmde.so exports the C-ABI."""
+import os
+import re
+import sys
+
+import pytest
+import torch
+
+import monodepth_estimation_b200 as mde
+from helpers import ROOT
+
+REF = "/root/reference"
+
+
+def test_library_exports_every_declared_symbol():
+    from monodepth_estimation_b200 import _lib
+
+    lib = _lib.load()
+    header = open(os.path.join(ROOT, "include", "mde.h")).read()
+    declared = set(re.findall(r"\b(mde_[a-z0-9_]+)\s*\(", header))
+    assert declared, "no declarations parsed"
+    for name in declared:
+        assert hasattr(lib, name), f"{name} declared in include/mde.h but not exported by libmde.so"
+    assert declared == set(_lib.SIGNATURES), declared ^ set(_lib.SIGNATURES)
+    assert lib.mde_version() >= 100
+
+
+def test_no_cpu_fallback_and_train_mode_raises():
+    m = mde.DepthAnything(pretrained=False)
+    with pytest.raises(RuntimeError):
+        m(torch.rand(1, 3, 224, 224))  # train mode
+    m.eval()
+    with pytest.raises(RuntimeError):
+        m(torch.rand(1, 3, 224, 224))  # CPU: the product path has no fallback
+    with pytest.raises(RuntimeError):
+        mde.DepthAnything(pretrained=True)  # needs the ImageNet checkpoint (network)
+
+
+def test_product_never_imports_oracle():
+    pkg = os.path.join(ROOT, "monodepth-estimation_b200")
+    for f in os.listdir(pkg):
+        if f.endswith(".py"):
+            src = open(os.path.join(pkg, f)).read()
+            assert not re.search(r"^\s*(from|import)\s+oracle", src, re.M), f
+
+
+@pytest.mark.skipif(not os.path.isdir(REF), reason="reference sources only exist in the build container")
+def test_state_dict_and_init_identical_to_reference():
+    sys.path.insert(0, REF)
+    try:
+        from models.enhanced_model import EnhancedDepthAnything as RE
+        from models.model import DepthAnything as RS
+        from models.refinement import MultiScaleDepthFusion as RF
+        from models.refinement import TextureAwareRefinementModule as RT
+    finally:
+        sys.path.remove(REF)
+    pairs = [(lambda: mde.DepthAnything(pretrained=False), lambda: RS(pretrained=False)),
+             (lambda: mde.EnhancedDepthAnything(pretrained=False), lambda: RE(pretrained=False)),
+             (mde.TextureAwareRefinementModule, RT), (mde.MultiScaleDepthFusion, RF)]
+    for mine, ref in pairs:
+        torch.manual_seed(7)
+        a = mine().state_dict()
+        torch.manual_seed(7)
+        b = ref().state_dict()
+        assert list(a) == list(b)
+        for k in a:
+            assert a[k].shape == b[k].shape and torch.equal(a[k], b[k]), k
+    m = mde.EnhancedDepthAnything(pretrained=False)
+    assert sum(p.numel() for p in m.encoder.parameters()) > 8e7 and len(list(m.decoder.parameters())) > 0  # train/mars_adapter.py:49-50
