@@ -46,6 +46,10 @@ int sm_count();  // SMs of the current device (cached per device)
 int encode_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims,
                      const uint64_t* strides_bytes, const uint32_t* box, int swizzle_bytes);
 
+// 2-CTA (cta_group::2) GEMM path of mde_gemm_bf16 (tc_gemm2.cu); same contract, needs N % 256 == 0.
+int launch_gemm_pair(const void* A, int lda, const void* W, int ldw, int M, int N, int K, int epilogue, const float* bias, void* out, int ldo,
+                     const void* aux0, const void* aux1, cudaStream_t stream);
+
 static inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 
 }  // namespace mde

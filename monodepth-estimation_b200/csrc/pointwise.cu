@@ -388,50 +388,54 @@ struct MapTable {
   int n;
 };
 
-// grid = (ceil(W/PX/256), H, n_maps*B): one block per output row segment.  The two source rows the row
-// interpolates between are staged (pre-multiplied) in shared memory once, so the inner loop is smem reads
-// + FMAs and the stores are full 16-byte streaming stores: the kernel is a pure HBM write stream.
+// grid = (ceil(W/PX/256), ceil(H/kRowsPerBlock), n_maps*B).  A thread owns PX consecutive output columns
+// (their x taps/weights are computed once) and walks kRowsPerBlock output rows; the low-resolution source
+// (<= 224x240 floats per image) is read through L1 (__ldg), so DRAM traffic is the output stream only and
+// every thread keeps several independent 16-byte streaming stores in flight.
 constexpr int kMaxSrcW = 1024;
+constexpr int kRowsPerBlock = 8;
 template <bool VEC4>
 __global__ void __launch_bounds__(256) resize_maps_kernel(const __grid_constant__ MapTable tab, int B, int H, int W, float min_disp, float disp_range) {
   constexpr int PX = VEC4 ? 4 : 1;
-  __shared__ float s0[kMaxSrcW], s1[kMaxSrcW];
-  const int Y = blockIdx.y;
   const int mi = blockIdx.z / B, b = blockIdx.z - mi * B;
   const mde_map_desc& d = tab.m[mi];
-  const int ws = d.ws;
-  int y0, y1;
-  float ly;
-  src_index_acf((float)d.hs / (float)H, Y, d.hs, y0, y1, ly);
-  const float* r0 = d.src + ((size_t)b * d.hs + y0) * ws;
-  const float* r1 = d.src + ((size_t)b * d.hs + y1) * ws;
-  const float mul = d.mul;
-  for (int x = threadIdx.x; x < ws; x += 256) {
-    s0[x] = __ldg(r0 + x) * mul;
-    s1[x] = __ldg(r1 + x) * mul;
-  }
-  __syncthreads();
+  const int ws = d.ws, hs = d.hs;
   const int xq = blockIdx.x * 256 + threadIdx.x;
   if (xq * PX >= W) return;
-  const float sw = (float)ws / (float)W;
-  float o[PX], dep[PX];
+  const float sw = (float)ws / (float)W, sh = (float)hs / (float)H;
+  const float mul = d.mul;
+  int x0[PX], x1[PX];
+  float lx[PX];
 #pragma unroll
-  for (int j = 0; j < PX; ++j) {
-    int x0, x1;
-    float lx;
-    src_index_acf(sw, xq * PX + j, ws, x0, x1, lx);
-    o[j] = (1.0f - ly) * ((1.0f - lx) * s0[x0] + lx * s0[x1]) + ly * ((1.0f - lx) * s1[x0] + lx * s1[x1]);
-    dep[j] = 1.0f / (min_disp + disp_range * o[j]);
-  }
-  const size_t off = ((size_t)b * H + Y) * W + (size_t)xq * PX;
-  if constexpr (VEC4) {
-    if (d.dst_disp) __stcs(reinterpret_cast<float4*>(d.dst_disp + off), make_float4(o[0], o[1], o[2], o[3]));
-    if (d.dst_disp2) __stcs(reinterpret_cast<float4*>(d.dst_disp2 + off), make_float4(o[0], o[1], o[2], o[3]));
-    if (d.dst_depth) __stcs(reinterpret_cast<float4*>(d.dst_depth + off), make_float4(dep[0], dep[1], dep[2], dep[3]));
-  } else {
-    if (d.dst_disp) d.dst_disp[off] = o[0];
-    if (d.dst_disp2) d.dst_disp2[off] = o[0];
-    if (d.dst_depth) d.dst_depth[off] = dep[0];
+  for (int j = 0; j < PX; ++j) src_index_acf(sw, xq * PX + j, ws, x0[j], x1[j], lx[j]);
+  const float* src = d.src + (size_t)b * hs * ws;
+  const int Y0 = blockIdx.y * kRowsPerBlock;
+#pragma unroll 2
+  for (int r = 0; r < kRowsPerBlock; ++r) {
+    const int Y = Y0 + r;
+    if (Y >= H) break;
+    int y0, y1;
+    float ly;
+    src_index_acf(sh, Y, hs, y0, y1, ly);
+    const float* r0 = src + (size_t)y0 * ws;
+    const float* r1 = src + (size_t)y1 * ws;
+    float o[PX], dep[PX];
+#pragma unroll
+    for (int j = 0; j < PX; ++j) {
+      const float v00 = __ldg(r0 + x0[j]) * mul, v01 = __ldg(r0 + x1[j]) * mul, v10 = __ldg(r1 + x0[j]) * mul, v11 = __ldg(r1 + x1[j]) * mul;
+      o[j] = (1.0f - ly) * ((1.0f - lx[j]) * v00 + lx[j] * v01) + ly * ((1.0f - lx[j]) * v10 + lx[j] * v11);
+      dep[j] = 1.0f / (min_disp + disp_range * o[j]);
+    }
+    const size_t off = ((size_t)b * H + Y) * W + (size_t)xq * PX;
+    if constexpr (VEC4) {
+      if (d.dst_disp) __stcs(reinterpret_cast<float4*>(d.dst_disp + off), make_float4(o[0], o[1], o[2], o[3]));
+      if (d.dst_disp2) __stcs(reinterpret_cast<float4*>(d.dst_disp2 + off), make_float4(o[0], o[1], o[2], o[3]));
+      if (d.dst_depth) __stcs(reinterpret_cast<float4*>(d.dst_depth + off), make_float4(dep[0], dep[1], dep[2], dep[3]));
+    } else {
+      if (d.dst_disp) d.dst_disp[off] = o[0];
+      if (d.dst_disp2) d.dst_disp2[off] = o[0];
+      if (d.dst_depth) d.dst_depth[off] = dep[0];
+    }
   }
 }
 
@@ -579,9 +583,9 @@ extern "C" int mde_resize_maps(const mde_map_desc* maps, int n_maps, int B, int 
   const float range = max_disp - min_disp;
   MDE_CHECK_ARG(H <= 65535 && (long long)n_maps * B <= 65535, "mde_resize_maps: H and n_maps*B must be <= 65535");
   if (vec) {
-    resize_maps_kernel<true><<<dim3(ceil_div(W / 4, 256), H, n_maps * B), 256, 0, stream>>>(tab, B, H, W, min_disp, range);
+    resize_maps_kernel<true><<<dim3(ceil_div(W / 4, 256), ceil_div(H, kRowsPerBlock), n_maps * B), 256, 0, stream>>>(tab, B, H, W, min_disp, range);
   } else {
-    resize_maps_kernel<false><<<dim3(ceil_div(W, 256), H, n_maps * B), 256, 0, stream>>>(tab, B, H, W, min_disp, range);
+    resize_maps_kernel<false><<<dim3(ceil_div(W, 256), ceil_div(H, kRowsPerBlock), n_maps * B), 256, 0, stream>>>(tab, B, H, W, min_disp, range);
   }
   MDE_CHECK_LAUNCH();
   return MDE_OK;

@@ -1,0 +1,152 @@
+// Fused epilogues shared by the tensor-core kernels (tc_gemm.cu: 1-CTA GEMM + implicit-GEMM conv,
+// tc_gemm2.cu: 2-CTA GEMM).  One thread owns one accumulator row (one TMEM lane) and NCOL consecutive
+// fp32 columns per call; `P` is the kernel's parameter block (fields epi, act, bias, out, ldo, aux0,
+// aux1, cout, h, w, out_cstride, out_coff).
+#pragma once
+#include "common.h"
+#include "ptx.cuh"
+
+namespace mde {
+
+enum { EPI_CONV_BF16 = 16, EPI_CONV_F32 = 17 };
+
+struct RowInfo {
+  bool valid;
+  int m;        // GEMM row
+  int b, y, x;  // conv pixel
+};
+
+template <int NCOL, class P>
+__device__ __forceinline__ void epilogue_chunk(const P& p, float (&v)[NCOL], int n0, const RowInfo& ri) {
+  // bias (same address for every lane: served as an L1 broadcast)
+  const float4* bp = reinterpret_cast<const float4*>(p.bias + n0);
+#pragma unroll
+  for (int j = 0; j < NCOL / 4; ++j) {
+    const float4 b4 = __ldg(bp + j);
+    v[4 * j + 0] += b4.x;
+    v[4 * j + 1] += b4.y;
+    v[4 * j + 2] += b4.z;
+    v[4 * j + 3] += b4.w;
+  }
+  if (!ri.valid) return;
+
+  switch (p.epi) {
+    case MDE_EPI_BIAS_GELU_BF16:
+#pragma unroll
+      for (int j = 0; j < NCOL; ++j) v[j] = gelu_erf(v[j]);
+      // fallthrough
+    case MDE_EPI_BIAS_BF16: {
+      uint4* dst = reinterpret_cast<uint4*>(reinterpret_cast<bf16*>(p.out) + (size_t)ri.m * p.ldo + n0);
+#pragma unroll
+      for (int j = 0; j < NCOL / 8; ++j)
+        dst[j] = make_uint4(pack_bf16x2(v[8 * j], v[8 * j + 1]), pack_bf16x2(v[8 * j + 2], v[8 * j + 3]),
+                            pack_bf16x2(v[8 * j + 4], v[8 * j + 5]), pack_bf16x2(v[8 * j + 6], v[8 * j + 7]));
+      break;
+    }
+    case MDE_EPI_BIAS_RESID_F32: {
+      const float4* rs = reinterpret_cast<const float4*>(reinterpret_cast<const float*>(p.aux0) + (size_t)ri.m * p.ldo + n0);
+      float4* dst = reinterpret_cast<float4*>(reinterpret_cast<float*>(p.out) + (size_t)ri.m * p.ldo + n0);
+#pragma unroll
+      for (int j = 0; j < NCOL / 4; ++j) {
+        const float4 r4 = __ldg(rs + j);
+        dst[j] = make_float4(v[4 * j] + r4.x, v[4 * j + 1] + r4.y, v[4 * j + 2] + r4.z, v[4 * j + 3] + r4.w);
+      }
+      break;
+    }
+    case MDE_EPI_BIAS_F32: {
+      float4* dst = reinterpret_cast<float4*>(reinterpret_cast<float*>(p.out) + (size_t)ri.m * p.ldo + n0);
+#pragma unroll
+      for (int j = 0; j < NCOL / 4; ++j) dst[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+      break;
+    }
+    case MDE_EPI_PATCH_EMBED: {
+      // A row (b, patch) -> token row b*197 + 1 + patch; + pos_embedding (tv:156); CLS row written by patch 0.
+      const int b = ri.m / 196, pp = ri.m - b * 196;
+      const float* pos = reinterpret_cast<const float*>(p.aux0);
+      const float4* ps = reinterpret_cast<const float4*>(pos + (size_t)(1 + pp) * MDE_VIT_DIM + n0);
+      float4* dst = reinterpret_cast<float4*>(reinterpret_cast<float*>(p.out) + ((size_t)b * MDE_VIT_SEQ + 1 + pp) * MDE_VIT_DIM + n0);
+#pragma unroll
+      for (int j = 0; j < NCOL / 4; ++j) {
+        const float4 q4 = __ldg(ps + j);
+        dst[j] = make_float4(v[4 * j] + q4.x, v[4 * j + 1] + q4.y, v[4 * j + 2] + q4.z, v[4 * j + 3] + q4.w);
+      }
+      if (pp == 0) {
+        const float4* cls = reinterpret_cast<const float4*>(reinterpret_cast<const float*>(p.aux1) + n0);
+        const float4* p0 = reinterpret_cast<const float4*>(pos + n0);
+        float4* d0 = reinterpret_cast<float4*>(reinterpret_cast<float*>(p.out) + (size_t)b * MDE_VIT_SEQ * MDE_VIT_DIM + n0);
+#pragma unroll
+        for (int j = 0; j < NCOL / 4; ++j) {
+          const float4 c4 = __ldg(cls + j), q4 = __ldg(p0 + j);
+          d0[j] = make_float4(c4.x + q4.x, c4.y + q4.y, c4.z + q4.z, c4.w + q4.w);
+        }
+      }
+      break;
+    }
+    case MDE_EPI_QKV_SPLIT: {
+      const int b = ri.m / MDE_VIT_SEQ, t = ri.m - b * MDE_VIT_SEQ;
+      const int which = n0 / MDE_VIT_DIM;  // 0 q, 1 k, 2 v (uniform per chunk: 768 % 32 == 0)
+      const int c = n0 - which * MDE_VIT_DIM;
+      const int hd = c >> 6, d0 = c & 63;
+      const size_t slab = (size_t)b * MDE_VIT_HEADS + hd;
+      if (which < 2) {
+        const float sc = which == 0 ? 0.125f : 1.0f;  // 1/sqrt(64) folded into q (exact in bf16)
+        bf16* base = reinterpret_cast<bf16*>(which == 0 ? p.out : const_cast<void*>(p.aux0));
+        uint4* dst = reinterpret_cast<uint4*>(base + (slab * MDE_VIT_SEQ + t) * 64 + d0);
+#pragma unroll
+        for (int j = 0; j < NCOL / 8; ++j)
+          dst[j] = make_uint4(pack_bf16x2(v[8 * j] * sc, v[8 * j + 1] * sc), pack_bf16x2(v[8 * j + 2] * sc, v[8 * j + 3] * sc),
+                              pack_bf16x2(v[8 * j + 4] * sc, v[8 * j + 5] * sc), pack_bf16x2(v[8 * j + 6] * sc, v[8 * j + 7] * sc));
+      } else {
+        // V transposed: vt[slab][d][t]; consecutive lanes hold consecutive tokens -> coalesced 2-byte stores
+        bf16* dst = reinterpret_cast<bf16*>(const_cast<void*>(p.aux1)) + (slab * 64 + d0) * MDE_VT_PITCH + t;
+#pragma unroll
+        for (int j = 0; j < NCOL; ++j) dst[(size_t)j * MDE_VT_PITCH] = __float2bfloat16_rn(v[j]);
+      }
+      break;
+    }
+    case EPI_CONV_BF16:
+    case EPI_CONV_F32: {
+      if (p.act == MDE_ACT_ELU) {
+#pragma unroll
+        for (int j = 0; j < NCOL; ++j) v[j] = elu1(v[j]);
+      } else if (p.act == MDE_ACT_SIGMOID) {
+#pragma unroll
+        for (int j = 0; j < NCOL; ++j) v[j] = sigmoidf_(v[j]);
+      }
+      const int nv = min(NCOL, p.cout - n0);  // valid output channels in this chunk
+      if (nv <= 0) break;
+      if (p.epi == EPI_CONV_F32) {
+        float* dst = reinterpret_cast<float*>(p.out) + (((size_t)ri.b * p.h + ri.y) * p.w + ri.x) * p.cout + n0;
+#pragma unroll
+        for (int j = 0; j < NCOL; ++j)
+          if (j < nv) dst[j] = v[j];
+        break;
+      }
+      uint32_t pk[NCOL / 2];
+#pragma unroll
+      for (int j = 0; j < NCOL / 2; ++j) pk[j] = pack_bf16x2(v[2 * j], v[2 * j + 1]);
+      // interior pixel (y+1, x+1) plus the reflected border copies it owns
+      const int H2 = p.h + 2, W2 = p.w + 2;
+      int ys[3], xs[3], ny = 0, nx = 0;
+      ys[ny++] = ri.y + 1;
+      if (ri.y == 1) ys[ny++] = 0;
+      if (ri.y == p.h - 2) ys[ny++] = p.h + 1;
+      xs[nx++] = ri.x + 1;
+      if (ri.x == 1) xs[nx++] = 0;
+      if (ri.x == p.w - 2) xs[nx++] = p.w + 1;
+      bf16* obase = reinterpret_cast<bf16*>(p.out) + p.out_coff + n0;
+      for (int iy = 0; iy < ny; ++iy)
+        for (int ix = 0; ix < nx; ++ix) {
+          uint4* dst = reinterpret_cast<uint4*>(obase + (((size_t)ri.b * H2 + ys[iy]) * W2 + xs[ix]) * p.out_cstride);
+#pragma unroll
+          for (int j = 0; j < NCOL / 8; ++j)
+            if (8 * j < nv) dst[j] = make_uint4(pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
+        }
+      break;
+    }
+    default:
+      break;
+  }
+}
+
+}  // namespace mde

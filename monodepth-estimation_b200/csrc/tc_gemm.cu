@@ -11,17 +11,19 @@
 // [channels, tw, th, 1] of the padded NHWC activation shifted by the tap, so no im2col buffer exists
 // and zero padding falls out of TMA out-of-bounds fill.
 #include <stdio.h>
+#include <stdlib.h>
+
+#include <algorithm>
 
 #include "common.h"
 #include "ptx.cuh"
+#include "tc_epilogue.cuh"
 
 namespace mde {
 
 constexpr int kBlockM = 128;
 constexpr int kThreads = 192;
 constexpr int kMaxStages = 12;
-
-enum { EPI_CONV_BF16 = 16, EPI_CONV_F32 = 17 };
 
 struct alignas(64) TcParams {
   CUtensorMap tmA;
@@ -40,145 +42,6 @@ struct alignas(64) TcParams {
   const void* aux1;
   int cout, out_cstride, out_coff;
 };
-
-struct RowInfo {
-  bool valid;
-  int m;        // GEMM row
-  int b, y, x;  // conv pixel
-};
-
-template <int NCOL>
-__device__ __forceinline__ void epilogue_chunk(const TcParams& p, float (&v)[NCOL], int n0, const RowInfo& ri) {
-  // bias (same address for every lane: served as an L1 broadcast)
-  const float4* bp = reinterpret_cast<const float4*>(p.bias + n0);
-#pragma unroll
-  for (int j = 0; j < NCOL / 4; ++j) {
-    const float4 b4 = __ldg(bp + j);
-    v[4 * j + 0] += b4.x;
-    v[4 * j + 1] += b4.y;
-    v[4 * j + 2] += b4.z;
-    v[4 * j + 3] += b4.w;
-  }
-  if (!ri.valid) return;
-
-  switch (p.epi) {
-    case MDE_EPI_BIAS_GELU_BF16:
-#pragma unroll
-      for (int j = 0; j < NCOL; ++j) v[j] = gelu_erf(v[j]);
-      // fallthrough
-    case MDE_EPI_BIAS_BF16: {
-      uint4* dst = reinterpret_cast<uint4*>(reinterpret_cast<bf16*>(p.out) + (size_t)ri.m * p.ldo + n0);
-#pragma unroll
-      for (int j = 0; j < NCOL / 8; ++j)
-        dst[j] = make_uint4(pack_bf16x2(v[8 * j], v[8 * j + 1]), pack_bf16x2(v[8 * j + 2], v[8 * j + 3]),
-                            pack_bf16x2(v[8 * j + 4], v[8 * j + 5]), pack_bf16x2(v[8 * j + 6], v[8 * j + 7]));
-      break;
-    }
-    case MDE_EPI_BIAS_RESID_F32: {
-      const float4* rs = reinterpret_cast<const float4*>(reinterpret_cast<const float*>(p.aux0) + (size_t)ri.m * p.ldo + n0);
-      float4* dst = reinterpret_cast<float4*>(reinterpret_cast<float*>(p.out) + (size_t)ri.m * p.ldo + n0);
-#pragma unroll
-      for (int j = 0; j < NCOL / 4; ++j) {
-        const float4 r4 = __ldg(rs + j);
-        dst[j] = make_float4(v[4 * j] + r4.x, v[4 * j + 1] + r4.y, v[4 * j + 2] + r4.z, v[4 * j + 3] + r4.w);
-      }
-      break;
-    }
-    case MDE_EPI_BIAS_F32: {
-      float4* dst = reinterpret_cast<float4*>(reinterpret_cast<float*>(p.out) + (size_t)ri.m * p.ldo + n0);
-#pragma unroll
-      for (int j = 0; j < NCOL / 4; ++j) dst[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
-      break;
-    }
-    case MDE_EPI_PATCH_EMBED: {
-      // A row (b, patch) -> token row b*197 + 1 + patch; + pos_embedding (tv:156); CLS row written by patch 0.
-      const int b = ri.m / 196, pp = ri.m - b * 196;
-      const float* pos = reinterpret_cast<const float*>(p.aux0);
-      const float4* ps = reinterpret_cast<const float4*>(pos + (size_t)(1 + pp) * MDE_VIT_DIM + n0);
-      float4* dst = reinterpret_cast<float4*>(reinterpret_cast<float*>(p.out) + ((size_t)b * MDE_VIT_SEQ + 1 + pp) * MDE_VIT_DIM + n0);
-#pragma unroll
-      for (int j = 0; j < NCOL / 4; ++j) {
-        const float4 q4 = __ldg(ps + j);
-        dst[j] = make_float4(v[4 * j] + q4.x, v[4 * j + 1] + q4.y, v[4 * j + 2] + q4.z, v[4 * j + 3] + q4.w);
-      }
-      if (pp == 0) {
-        const float4* cls = reinterpret_cast<const float4*>(reinterpret_cast<const float*>(p.aux1) + n0);
-        const float4* p0 = reinterpret_cast<const float4*>(pos + n0);
-        float4* d0 = reinterpret_cast<float4*>(reinterpret_cast<float*>(p.out) + (size_t)b * MDE_VIT_SEQ * MDE_VIT_DIM + n0);
-#pragma unroll
-        for (int j = 0; j < NCOL / 4; ++j) {
-          const float4 c4 = __ldg(cls + j), q4 = __ldg(p0 + j);
-          d0[j] = make_float4(c4.x + q4.x, c4.y + q4.y, c4.z + q4.z, c4.w + q4.w);
-        }
-      }
-      break;
-    }
-    case MDE_EPI_QKV_SPLIT: {
-      const int b = ri.m / MDE_VIT_SEQ, t = ri.m - b * MDE_VIT_SEQ;
-      const int which = n0 / MDE_VIT_DIM;  // 0 q, 1 k, 2 v (uniform per chunk: 768 % 32 == 0)
-      const int c = n0 - which * MDE_VIT_DIM;
-      const int hd = c >> 6, d0 = c & 63;
-      const size_t slab = (size_t)b * MDE_VIT_HEADS + hd;
-      if (which < 2) {
-        const float sc = which == 0 ? 0.125f : 1.0f;  // 1/sqrt(64) folded into q (exact in bf16)
-        bf16* base = reinterpret_cast<bf16*>(which == 0 ? p.out : const_cast<void*>(p.aux0));
-        uint4* dst = reinterpret_cast<uint4*>(base + (slab * MDE_VIT_SEQ + t) * 64 + d0);
-#pragma unroll
-        for (int j = 0; j < NCOL / 8; ++j)
-          dst[j] = make_uint4(pack_bf16x2(v[8 * j] * sc, v[8 * j + 1] * sc), pack_bf16x2(v[8 * j + 2] * sc, v[8 * j + 3] * sc),
-                              pack_bf16x2(v[8 * j + 4] * sc, v[8 * j + 5] * sc), pack_bf16x2(v[8 * j + 6] * sc, v[8 * j + 7] * sc));
-      } else {
-        // V transposed: vt[slab][d][t]; consecutive lanes hold consecutive tokens -> coalesced 2-byte stores
-        bf16* dst = reinterpret_cast<bf16*>(const_cast<void*>(p.aux1)) + (slab * 64 + d0) * MDE_VT_PITCH + t;
-#pragma unroll
-        for (int j = 0; j < NCOL; ++j) dst[(size_t)j * MDE_VT_PITCH] = __float2bfloat16_rn(v[j]);
-      }
-      break;
-    }
-    case EPI_CONV_BF16:
-    case EPI_CONV_F32: {
-      if (p.act == MDE_ACT_ELU) {
-#pragma unroll
-        for (int j = 0; j < NCOL; ++j) v[j] = elu1(v[j]);
-      } else if (p.act == MDE_ACT_SIGMOID) {
-#pragma unroll
-        for (int j = 0; j < NCOL; ++j) v[j] = sigmoidf_(v[j]);
-      }
-      const int nv = min(NCOL, p.cout - n0);  // valid output channels in this chunk
-      if (nv <= 0) break;
-      if (p.epi == EPI_CONV_F32) {
-        float* dst = reinterpret_cast<float*>(p.out) + (((size_t)ri.b * p.h + ri.y) * p.w + ri.x) * p.cout + n0;
-#pragma unroll
-        for (int j = 0; j < NCOL; ++j)
-          if (j < nv) dst[j] = v[j];
-        break;
-      }
-      uint32_t pk[NCOL / 2];
-#pragma unroll
-      for (int j = 0; j < NCOL / 2; ++j) pk[j] = pack_bf16x2(v[2 * j], v[2 * j + 1]);
-      // interior pixel (y+1, x+1) plus the reflected border copies it owns
-      const int H2 = p.h + 2, W2 = p.w + 2;
-      int ys[3], xs[3], ny = 0, nx = 0;
-      ys[ny++] = ri.y + 1;
-      if (ri.y == 1) ys[ny++] = 0;
-      if (ri.y == p.h - 2) ys[ny++] = p.h + 1;
-      xs[nx++] = ri.x + 1;
-      if (ri.x == 1) xs[nx++] = 0;
-      if (ri.x == p.w - 2) xs[nx++] = p.w + 1;
-      bf16* obase = reinterpret_cast<bf16*>(p.out) + p.out_coff + n0;
-      for (int iy = 0; iy < ny; ++iy)
-        for (int ix = 0; ix < nx; ++ix) {
-          uint4* dst = reinterpret_cast<uint4*>(obase + (((size_t)ri.b * H2 + ys[iy]) * W2 + xs[ix]) * p.out_cstride);
-#pragma unroll
-          for (int j = 0; j < NCOL / 8; ++j)
-            if (8 * j < nv) dst[j] = make_uint4(pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
-        }
-      break;
-    }
-    default:
-      break;
-  }
-}
 
 // co-resident CTAs per SM the register budget is compiled for (small tiles hide latency with more CTAs)
 template <int BLOCK_N>
@@ -331,7 +194,7 @@ __global__ void __launch_bounds__(kThreads, min_ctas<BLOCK_N>()) tc_gemm_kernel(
         float v[NCOL];
 #pragma unroll
         for (int j = 0; j < NCOL; ++j) v[j] = __uint_as_float(raw[j]);
-        epilogue_chunk<NCOL>(p, v, n_blk * BLOCK_N + c * NCOL, ri);
+        epilogue_chunk<NCOL, TcParams>(p, v, n_blk * BLOCK_N + c * NCOL, ri);
       }
       tc_fence_before();
       __syncwarp();
@@ -363,10 +226,17 @@ static int launch_tc(TcParams& p, cudaStream_t stream) {
   static int ctas_per_sm = 0;  // per instantiation: what the hardware can actually keep resident
   if (ctas_per_sm == 0) {
     MDE_CHECK_CUDA(cudaFuncSetAttribute(tc_gemm_kernel<BLOCK_N, ROWB>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
-    int occ = 0;
-    MDE_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, tc_gemm_kernel<BLOCK_N, ROWB>, kThreads, smem_bytes));
+    MDE_CHECK_CUDA(cudaFuncSetAttribute(tc_gemm_kernel<BLOCK_N, ROWB>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    cudaFuncAttributes fa;
+    MDE_CHECK_CUDA(cudaFuncGetAttributes(&fa, tc_gemm_kernel<BLOCK_N, ROWB>));
+    // resident CTAs per SM from the four per-SM budgets: registers (64 K), shared memory (227 KB usable,
+    // 1 KB reserved per CTA), threads (2048) and TMEM columns (512)
+    const int regs_per_cta = ((fa.numRegs + 7) & ~7) * kThreads;
     const int tmem_cols = 2 * BLOCK_N < 32 ? 32 : 2 * BLOCK_N;
-    if (occ > 512 / tmem_cols) occ = 512 / tmem_cols;  // TMEM: 512 columns per SM
+    int occ = 65536 / regs_per_cta;
+    occ = std::min(occ, (227 * 1024) / (smem_bytes + 1024));
+    occ = std::min(occ, 2048 / kThreads);
+    occ = std::min(occ, 512 / tmem_cols);
     ctas_per_sm = occ < 1 ? 1 : occ;
   }
   p.stages = stages;
@@ -412,6 +282,10 @@ extern "C" int mde_gemm_bf16(const mde_bf16* A, int lda, const mde_bf16* W, int 
     MDE_CHECK_ARG(N == 3 * MDE_VIT_DIM && M % MDE_VIT_SEQ == 0, "mde_gemm_bf16: QKV_SPLIT expects N=2304 and M = B*197");
   }
   if (epilogue <= MDE_EPI_BIAS_F32) MDE_CHECK_ARG(ldo >= N && ldo % 8 == 0, "mde_gemm_bf16: bad ldo=%d", ldo);
+
+  // large problems run on CTA pairs (tc_gemm2.cu); MDE_GEMM_1CTA=1 forces the single-CTA kernel (A/B testing)
+  static const bool force_1cta = getenv("MDE_GEMM_1CTA") != nullptr && getenv("MDE_GEMM_1CTA")[0] == '1';
+  if (!force_1cta && N % 256 == 0 && M >= 1024) return launch_gemm_pair(A, lda, W, ldw, M, N, K, epilogue, bias, out, ldo, aux0, aux1, stream);
 
   TcParams p;
   memset(&p, 0, sizeof(p));

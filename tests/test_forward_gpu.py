@@ -60,6 +60,17 @@ def test_model_vs_reference_golden(name):
             assert rel_l2(g, ref) <= DEPTH_REL_L2, (k, rel_l2(g, ref))
 
 
+@pytest.mark.parametrize("kind", ["standard", "enhanced"])
+def test_model_batch8_vs_oracle(kind):
+    """B=8 -> M = 1576 GEMM rows: the ViT linear layers run on the CTA-pair kernel (tc_gemm2.cu)."""
+    x = synth_images(8, 224, 256, 55)
+    md = {"source": "ingenuity", "altitude": 3.0}
+    with torch.no_grad():
+        ref = (O.standard_forward if kind == "standard" else O.enhanced_forward)(cached_model(kind, 0).state_dict(), x, md)
+    got = cached_model(kind, 0, "cuda")(x.cuda(), md)
+    check_outputs(got, ref, f"{kind}_b8")
+
+
 def test_batch_shard_invariance():
     """Images are independent: forward(B=4) == cat(forward(2), forward(2)) bit for bit."""
     m = cached_model("enhanced", 0, "cuda")

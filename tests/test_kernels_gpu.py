@@ -38,6 +38,46 @@ def test_gemm_bias_f32(M, N, K):
     assert rel_l2(out, ref) < 1e-5, rel_l2(out, ref)
 
 
+# M >= 1024 and N % 256 == 0 route to the CTA-pair kernel (tc_gemm2.cu); the shapes below hit full waves,
+# the four-way split tail items, partial row pairs and the k=3072 pipeline wrap-around.
+@pytest.mark.parametrize("M,N,K,epi", [(1576, 768, 768, "resid"), (1576, 2304, 768, "f32"), (6304, 768, 3072, "resid"), (6304, 3072, 768, "gelu"),
+                                       (1024, 256, 64, "f32"), (6304, 2304, 768, "bf16"), (19000, 768, 768, "resid"), (1100, 256, 768, "f32")])
+def test_gemm_pair_kernel(M, N, K, epi):
+    L, ops = _mods()
+    a, w, b = _rand(M, K, seed=101, dtype=BF16), _rand(N, K, seed=102, scale=K ** -0.5, dtype=BF16), _rand(N, seed=103)
+    ref = a.float() @ w.float().t() + b
+    if epi == "f32":
+        out = torch.full((M, N), float("nan"), device="cuda")
+        ops.gemm(a, w, b, L.EPI_BIAS_F32, out)
+        assert rel_l2(out, ref) < 1e-5, rel_l2(out, ref)
+    elif epi == "resid":
+        r = _rand(M, N, seed=104)
+        out = torch.full((M, N), float("nan"), device="cuda")
+        ops.gemm(a, w, b, L.EPI_BIAS_RESID_F32, out, r)
+        assert rel_l2(out, ref + r) < 1e-5, rel_l2(out, ref + r)
+    else:
+        out = torch.full((M, N), float("nan"), device="cuda", dtype=BF16)
+        ops.gemm(a, w, b, L.EPI_BIAS_GELU_BF16 if epi == "gelu" else L.EPI_BIAS_BF16, out)
+        want = F.gelu(ref) if epi == "gelu" else ref
+        assert torch.isfinite(out.float()).all()
+        assert rel_l2(out.float(), want) < 4e-3, rel_l2(out.float(), want)
+
+
+def test_gemm_pair_kernel_qkv_split():
+    L, ops = _mods()
+    B = 8
+    M = B * 197
+    a, w, b = _rand(M, 768, seed=111, dtype=BF16), _rand(2304, 768, seed=112, scale=768 ** -0.5, dtype=BF16), _rand(2304, seed=113)
+    q = torch.empty(B * 12 * 197 * 64, device="cuda", dtype=BF16)
+    k = torch.empty_like(q)
+    vt = torch.zeros(B * 12 * 64 * L.VT_PITCH, device="cuda", dtype=BF16)
+    ops.gemm(a, w, b, L.EPI_QKV_SPLIT, q, k, vt)
+    ref = (a.float() @ w.float().t() + b).view(B, 197, 3, 12, 64).permute(2, 0, 3, 1, 4)
+    assert rel_l2(q.view(B, 12, 197, 64).float(), ref[0] * 0.125) < 4e-3
+    assert rel_l2(k.view(B, 12, 197, 64).float(), ref[1]) < 4e-3
+    assert rel_l2(vt.view(B, 12, 64, L.VT_PITCH)[..., :197].float().transpose(-1, -2), ref[2]) < 4e-3
+
+
 def test_gemm_bias_bf16_and_gelu():
     L, ops = _mods()
     M, N, K = 500, 3072, 768
