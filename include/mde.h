@@ -29,6 +29,7 @@ extern "C" {
 
 typedef struct CUstream_st* mde_stream_t; /* == cudaStream_t */
 typedef uint16_t mde_bf16;
+typedef uint16_t mde_f16; /* IEEE binary16 bit pattern */
 
 enum mde_status {
   MDE_OK = 0,
@@ -76,6 +77,11 @@ int mde_input_range(const float* x, int B, int H, int W, const float* bn4x3, flo
  * model.py:51-54 (pad-to-/16 resize), enhanced_model.py:95-96 (rgb -> 14x15). */
 int mde_resize_bilinear_nchw(const float* src, int B, int C, int Hs, int Ws, float* dst, int Hd, int Wd,
                              mde_stream_t stream);
+
+/* ---- run_mars_depth.py:97-104 (caller side): uint8 HWC image batch [B][H][W][3] -> float32 CHW [B][3][H][W] / 255,
+ * i.e. `torch.from_numpy(np.array(img)).float().permute(2,0,1) / 255.0` evaluated on the device (IEEE fp32 division,
+ * bit-identical to the host expression) so the host->device copy moves 1 byte per sample instead of 4. H*W % 4 == 0. */
+int mde_u8hwc_to_f32chw(const uint8_t* src, int B, int H, int W, float* dst, mde_stream_t stream);
 
 /* ---- encoder.py:139-144 + tv:_process_input: resize to 224^2 (bilinear, align_corners=False),
  * apply affine6, and lay the result out as the patch-embedding GEMM's A operand:
@@ -132,6 +138,13 @@ int mde_conv_nhwc(const mde_bf16* in, int B, int h, int w, int cin, int in_cstri
                   int cout, int ksize, int padding, int activation, mde_bf16* out_bf16, int out_cstride,
                   int out_coff, float* out_f32, mde_stream_t stream);
 
+/* Same kernel with IEEE fp16 operands and fp16 padded-NHWC output (10 mantissa bits instead of 8, fp32 accumulate;
+ * values saturate at +-65504).  Used by the refinement.py conv chain, whose output is a small difference of larger
+ * terms and needs the extra bits to stay inside the 1e-2 bar. */
+int mde_conv_nhwc_f16(const mde_f16* in, int B, int h, int w, int cin, int in_cstride, const mde_f16* wpacked, const float* bias,
+                      int cout, int ksize, int padding, int activation, mde_f16* out_f16, int out_cstride,
+                      int out_coff, float* out_f32, mde_stream_t stream);
+
 /* ---- decoder.py:118-145: x2 bilinear upsample (align_corners=True) of `a`, optional bilinear
  * resize (align_corners=True) of the skip branch `s` to the same size, channel concat.
  * a: padded NHWC [B][h+2][w+2][ca]; s: padded NHWC [B][hs+2][ws+2][cs] or NULL (cs=0);
@@ -176,6 +189,29 @@ int mde_spatial_attention(const mde_bf16* x, const float* qkv, int B, int gh, in
  * Outputs (f32 [B][h0][w0]): fused. */
 int mde_enh_fuse(const float* d0, const float* d1, const float* d2, const float* refinement, int B, int h0,
                  int w0, int gh, int gw, float mul, const float* fusion_w3, float* fused, mde_stream_t stream);
+
+/* ---- models/refinement.py:131-183 MultiScaleDepthFusion.forward, one fused stencil kernel ---------
+ * maps[i]: f32 [B][hs[i]][ws[i]] device pointers (host array of n_maps pointers, scale order); every map
+ * is resampled to H x W (bilinear, align_corners=False; identity when already H x W), then
+ *   conf_i = sigmoid(conv3x3_i(f_i) + conf_b[i])  (zero padding),  w_i = conf_i / (sum_j conf_j + 1e-8),
+ *   out    = sum_i fuse_w[i] * f_i * w_i + fuse_b[0].
+ * conf_w f32 [n_maps][9], conf_b f32 [n_maps], fuse_w f32 [n_maps], fuse_b f32 [1] (device); out f32 [B][H][W]. */
+#define MDE_MAX_FUSION_SCALES 4
+int mde_depth_fusion(const float* const* maps, const int* hs, const int* ws, int n_maps, int B, int H, int W,
+                     const float* conf_w, const float* conf_b, const float* fuse_w, const float* fuse_b, float* out,
+                     mde_stream_t stream);
+
+/* ---- models/refinement.py:57-107 TextureAwareRefinementModule.forward (live lines :68-85,:92-107) ----
+ * The module runs as  mde_refine_pack_inputs -> 5 x mde_conv_nhwc_f16 (zero pad, ELU) -> mde_refine_output:
+ *   pack  : rgb f32 [B,3,H,W] + depth f32 [B,1,H,W] -> in16 fp16 padded NHWC [B][H+2][W+2][16] with channels
+ *           {r,g,b,depth,0...}  (operand of the merged rgb_conv1|depth_conv1 implicit GEMM, 16 -> 128) and
+ *           gate f32 [B][H][W] = sigmoid(5*sqrt(ex^2+ey^2)), ex/ey the frozen Sobel/3 convs of :41-49,:83-85;
+ *   output: out f32 [B][H][W] = depth + (w32 . feat[...,0:32] + bias1[0]) * gate  (:98-105),
+ *           feat = combined_conv2 output, padded NHWC fp16 [B][H+2][W+2][cstride]. */
+int mde_refine_pack_inputs(const float* rgb, const float* depth, int B, int H, int W, mde_f16* in16_padded, float* gate,
+                           mde_stream_t stream);
+int mde_refine_output(const mde_f16* feat_padded, int cstride, const float* w32, const float* bias1, const float* depth,
+                      const float* gate, int B, int H, int W, float* out, mde_stream_t stream);
 
 #ifdef __cplusplus
 }

@@ -4,5 +4,6 @@ from .model import DepthAnything, source_scale  # noqa: F401
 from .enhanced_model import EnhancedDepthAnything  # noqa: F401
 from .refinement import MultiScaleDepthFusion, TextureAwareRefinementModule  # noqa: F401
 from .layers import disp_to_depth  # noqa: F401
+from .pipeline import BatchPipeline  # noqa: F401
 
 __version__ = "0.1.0"

@@ -20,6 +20,7 @@ PAD_REFLECT, PAD_ZERO = range(2)
 VIT_SEQ, VIT_DIM, VIT_HEADS, VT_PITCH = 197, 768, 12, 208
 RANGE_SCRATCH_FLOATS = 6 * 1024
 MAX_MAPS = 8
+MAX_FUSION_SCALES = 4
 
 _p, _i, _f = C.c_void_p, C.c_int, C.c_float
 
@@ -36,6 +37,7 @@ SIGNATURES = {
     "mde_sm_count": [],
     "mde_input_range": [_p, _i, _i, _i, _p, _f, _p, _p, _p],
     "mde_resize_bilinear_nchw": [_p, _i, _i, _i, _i, _p, _i, _i, _p],
+    "mde_u8hwc_to_f32chw": [_p, _i, _i, _i, _p, _p],
     "mde_preprocess_patchify": [_p, _i, _i, _i, _p, _p, _p],
     "mde_gemm_bf16": [_p, _i, _p, _i, _i, _i, _i, _i, _p, _p, _i, _p, _p, _p],
     "mde_layernorm_bf16": [_p, _i, _i, _p, _p, _f, _p, _p],
@@ -43,11 +45,15 @@ SIGNATURES = {
     "mde_tokens_to_grid_bf16": [_p, _i, _i, _i, _p, _p],
     "mde_instnorm_nhwc": [_p, _i, _i, _i, _i, _f, _p, _i, _i, _p, _p],
     "mde_conv_nhwc": [_p, _i, _i, _i, _i, _i, _p, _p, _i, _i, _i, _i, _p, _i, _i, _p, _p],
+    "mde_conv_nhwc_f16": [_p, _i, _i, _i, _i, _i, _p, _p, _i, _i, _i, _i, _p, _i, _i, _p, _p],
     "mde_upsample2x_concat_nhwc": [_p, _i, _i, _i, _i, _p, _i, _i, _i, _p, _p],
     "mde_rgb_to_grid_nhwc": [_p, _i, _i, _i, _i, _i, _p, _i, _i, _i, _p],
     "mde_resize_maps": [C.POINTER(MapDesc), _i, _i, _i, _i, _f, _f, _p],
     "mde_spatial_attention": [_p, _p, _i, _i, _i, _p, _p, _p],
     "mde_enh_fuse": [_p, _p, _p, _p, _i, _i, _i, _i, _i, _f, _p, _p, _p],
+    "mde_depth_fusion": [C.POINTER(_p), C.POINTER(_i), C.POINTER(_i), _i, _i, _i, _i, _p, _p, _p, _p, _p, _p],
+    "mde_refine_pack_inputs": [_p, _p, _i, _i, _i, _p, _p, _p],
+    "mde_refine_output": [_p, _i, _p, _p, _p, _p, _i, _i, _i, _p, _p],
 }
 _RESTYPES = {"mde_last_error": C.c_char_p}
 

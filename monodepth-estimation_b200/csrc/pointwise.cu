@@ -471,6 +471,25 @@ __global__ void __launch_bounds__(256) enh_fuse_kernel(const float* __restrict__
   }
 }
 
+// ------------------------------------------------------------------ caller-side input conversion (run_mars_depth.py:97-104)
+// uint8 HWC (decoder output) -> float32 CHW / 255: `torch.from_numpy(arr).float().permute(2,0,1) / 255.0` on the device.
+// One thread converts 4 pixels: three aligned 4-byte loads, three 16-byte streaming-friendly stores.
+__global__ void __launch_bounds__(256) u8hwc_to_f32chw_kernel(const uint32_t* __restrict__ src, long long quads, int HW4, float4* __restrict__ dst) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < quads; i += (long long)gridDim.x * blockDim.x) {
+    const long long b = i / HW4;
+    const int q = (int)(i - b * HW4);
+    const uint32_t w0 = __ldg(src + 3 * i), w1 = __ldg(src + 3 * i + 1), w2 = __ldg(src + 3 * i + 2);
+    // bytes: r0 g0 b0 r1 | g1 b1 r2 g2 | b2 r3 g3 b3
+    const float r[4] = {(float)(w0 & 255u), (float)(w0 >> 24), (float)((w1 >> 16) & 255u), (float)((w2 >> 8) & 255u)};
+    const float g[4] = {(float)((w0 >> 8) & 255u), (float)(w1 & 255u), (float)(w1 >> 24), (float)((w2 >> 16) & 255u)};
+    const float bl[4] = {(float)((w0 >> 16) & 255u), (float)((w1 >> 8) & 255u), (float)(w2 & 255u), (float)(w2 >> 24)};
+    float4* o = dst + b * 3 * HW4 + q;
+    o[0] = make_float4(__fdiv_rn(r[0], 255.0f), __fdiv_rn(r[1], 255.0f), __fdiv_rn(r[2], 255.0f), __fdiv_rn(r[3], 255.0f));
+    o[HW4] = make_float4(__fdiv_rn(g[0], 255.0f), __fdiv_rn(g[1], 255.0f), __fdiv_rn(g[2], 255.0f), __fdiv_rn(g[3], 255.0f));
+    o[2 * (size_t)HW4] = make_float4(__fdiv_rn(bl[0], 255.0f), __fdiv_rn(bl[1], 255.0f), __fdiv_rn(bl[2], 255.0f), __fdiv_rn(bl[3], 255.0f));
+  }
+}
+
 static inline int grid_for(long long work_items, int threads) {
   long long blocks = (work_items + threads - 1) / threads;
   const long long cap = (long long)sm_count() * 16;
@@ -595,6 +614,17 @@ extern "C" int mde_enh_fuse(const float* d0, const float* d1, const float* d2, c
                             float mul, const float* fusion_w3, float* fused, mde_stream_t stream) {
   MDE_CHECK_ARG(d0 && d1 && d2 && refinement && fusion_w3 && fused && B > 0 && h0 > 0 && w0 > 0, "mde_enh_fuse: bad arguments");
   enh_fuse_kernel<<<grid_for((long long)B * h0 * w0, 256), 256, 0, stream>>>(d0, d1, d2, refinement, B, h0, w0, gh, gw, mul, fusion_w3, fused);
+  MDE_CHECK_LAUNCH();
+  return MDE_OK;
+}
+
+extern "C" int mde_u8hwc_to_f32chw(const uint8_t* src, int B, int H, int W, float* dst, mde_stream_t stream) {
+  MDE_CHECK_ARG(src && dst && B > 0 && H > 0 && W > 0, "mde_u8hwc_to_f32chw: bad arguments");
+  MDE_CHECK_ARG(((long long)H * W) % 4 == 0 && (uintptr_t)src % 4 == 0 && (uintptr_t)dst % 16 == 0,
+                "mde_u8hwc_to_f32chw: H*W must be a multiple of 4, src 4-byte and dst 16-byte aligned");
+  const int hw4 = (int)(((long long)H * W) / 4);
+  const long long quads = (long long)B * hw4;
+  u8hwc_to_f32chw_kernel<<<grid_for(quads, 256), 256, 0, stream>>>(reinterpret_cast<const uint32_t*>(src), quads, hw4, reinterpret_cast<float4*>(dst));
   MDE_CHECK_LAUNCH();
   return MDE_OK;
 }

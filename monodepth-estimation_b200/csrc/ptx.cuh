@@ -212,6 +212,11 @@ __host__ __device__ constexpr uint32_t umma_idesc_bf16(int m, int n) {
   return (1u << 4) | (1u << 7) | (1u << 10) | (static_cast<uint32_t>(n >> 3) << 17) | (static_cast<uint32_t>(m >> 4) << 24);
 }
 
+// Same, A/B = fp16 (a_format = b_format = 0): used where 10 mantissa bits are needed (refinement.py conv chain).
+__host__ __device__ constexpr uint32_t umma_idesc_f16(int m, int n) {
+  return (1u << 4) | (static_cast<uint32_t>(n >> 3) << 17) | (static_cast<uint32_t>(m >> 4) << 24);
+}
+
 // ------------------------------------------------------------------ small math helpers
 __device__ __forceinline__ float fast_rcp(float x) {
   float y;
@@ -237,12 +242,29 @@ __device__ __forceinline__ float erf_as(float x) {
   return copysignf(fmaf(-p, e, 1.0f), x);
 }
 __device__ __forceinline__ float gelu_erf(float x) { return 0.5f * x * (1.0f + erf_as(x * 0.70710678118654752f)); }
+// Exact-erf GELU for a bf16 destination:  gelu(x) = x * Phi(x),  Phi(x) ~= sigmoid(x * (c0 + c1 x^2 + c2 x^4)), minimax fit of
+// x*Phi(x) on [-9, 9]: max |error| 2.5e-5 (bf16 half-ulp is 2e-3 relative), well conditioned for negative x (no 1+erf
+// cancellation).  9 instructions, 2 of them SFU (ex2, rcp) against ~20 for gelu_erf: the fc1 epilogue is ALU-bound.
+// The coefficients carry the factor -log2(e); x^2 is clamped where the sigmoid has saturated (keeps the quartic monotone).
+__device__ __forceinline__ float gelu_fast(float x) {
+  const float x2 = fminf(x * x, 50.0f);
+  float q = fmaf(x2, 1.0142630e-3f, -1.0677571e-1f);  // -log2e * (c2 x^2 + c1)
+  q = fmaf(q, x2, -2.3011213f);                        // -log2e * c0
+  return x * fast_rcp(1.0f + fast_ex2(x * q));
+}
 __device__ __forceinline__ float elu1(float x) { return x > 0.0f ? x : (__expf(x) - 1.0f); }
 __device__ __forceinline__ float sigmoidf_(float x) { return 1.0f / (1.0f + __expf(-x)); }
 
 __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
   __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
   return *reinterpret_cast<uint32_t*>(&v);
+}
+
+// two floats -> packed fp16x2 (lo in the low half), round-to-nearest, saturating to +-65504 instead of inf
+__device__ __forceinline__ uint32_t pack_f16x2(float lo, float hi) {
+  uint32_t r;
+  asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  return r;
 }
 
 }  // namespace mde

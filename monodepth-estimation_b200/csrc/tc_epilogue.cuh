@@ -1,7 +1,7 @@
 // Fused epilogues shared by the tensor-core kernels (tc_gemm.cu: 1-CTA GEMM + implicit-GEMM conv,
 // tc_gemm2.cu: 2-CTA GEMM).  One thread owns one accumulator row (one TMEM lane) and NCOL consecutive
 // fp32 columns per call; `P` is the kernel's parameter block (fields epi, act, bias, out, ldo, aux0,
-// aux1, cout, h, w, out_cstride, out_coff).
+// aux1, cout, h, w, out_cstride, out_coff, f16).
 #pragma once
 #include "common.h"
 #include "ptx.cuh"
@@ -33,7 +33,7 @@ __device__ __forceinline__ void epilogue_chunk(const P& p, float (&v)[NCOL], int
   switch (p.epi) {
     case MDE_EPI_BIAS_GELU_BF16:
 #pragma unroll
-      for (int j = 0; j < NCOL; ++j) v[j] = gelu_erf(v[j]);
+      for (int j = 0; j < NCOL; ++j) v[j] = gelu_fast(v[j]);
       // fallthrough
     case MDE_EPI_BIAS_BF16: {
       uint4* dst = reinterpret_cast<uint4*>(reinterpret_cast<bf16*>(p.out) + (size_t)ri.m * p.ldo + n0);
@@ -124,7 +124,7 @@ __device__ __forceinline__ void epilogue_chunk(const P& p, float (&v)[NCOL], int
       }
       uint32_t pk[NCOL / 2];
 #pragma unroll
-      for (int j = 0; j < NCOL / 2; ++j) pk[j] = pack_bf16x2(v[2 * j], v[2 * j + 1]);
+      for (int j = 0; j < NCOL / 2; ++j) pk[j] = p.f16 ? pack_f16x2(v[2 * j], v[2 * j + 1]) : pack_bf16x2(v[2 * j], v[2 * j + 1]);
       // interior pixel (y+1, x+1) plus the reflected border copies it owns
       const int H2 = p.h + 2, W2 = p.w + 2;
       int ys[3], xs[3], ny = 0, nx = 0;

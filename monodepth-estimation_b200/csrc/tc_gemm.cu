@@ -41,6 +41,7 @@ struct alignas(64) TcParams {
   const void* aux0;
   const void* aux1;
   int cout, out_cstride, out_coff;
+  int f16;  // operands (and bf16-slot outputs) are fp16 instead of bf16
 };
 
 // co-resident CTAs per SM the register budget is compiled for (small tiles hide latency with more CTAs)
@@ -134,7 +135,7 @@ __global__ void __launch_bounds__(kThreads, min_ctas<BLOCK_N>()) tc_gemm_kernel(
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer
     if (elect_one()) {
-      constexpr uint32_t idesc = umma_idesc_bf16(kBlockM, BLOCK_N);
+      const uint32_t idesc = p.f16 ? umma_idesc_f16(kBlockM, BLOCK_N) : umma_idesc_bf16(kBlockM, BLOCK_N);
       int stage = 0, acc = 0;
       uint32_t phase = 0, acc_phase = 0;
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
@@ -322,7 +323,7 @@ extern "C" int mde_gemm_bf16(const mde_bf16* A, int lda, const mde_bf16* W, int 
   return dispatch_tc(p, block_n, 128, stream);
 }
 
-extern "C" int mde_conv_nhwc(const mde_bf16* in, int B, int h, int w, int cin, int in_cstride, const mde_bf16* wpacked, const float* bias,
+static int conv_nhwc_impl(int f16, const mde_bf16* in, int B, int h, int w, int cin, int in_cstride, const mde_bf16* wpacked, const float* bias,
                              int cout, int ksize, int padding, int activation, mde_bf16* out_bf16, int out_cstride,
                              int out_coff, float* out_f32, mde_stream_t stream) {
   MDE_CHECK_ARG(in && wpacked && bias, "mde_conv_nhwc: null pointer");
@@ -373,7 +374,7 @@ extern "C" int mde_conv_nhwc(const mde_bf16* in, int B, int h, int w, int cin, i
   }
   // block_n: largest tile that divides cout_pad, shrunk while the grid would leave SMs idle
   int block_n = 16;
-  for (int bn = 256; bn >= 16; bn >>= 1)
+  for (int bn = (rowb == 128 ? 256 : 64); bn >= 16; bn >>= 1)  // narrow-K tiles (16/32 input channels) are built for N <= 64
     if (cout_pad % bn == 0) {
       block_n = bn;
       break;
@@ -411,5 +412,18 @@ extern "C" int mde_conv_nhwc(const mde_bf16* in, int B, int h, int w, int cin, i
   p.cout = cout;
   p.out_cstride = out_cstride;
   p.out_coff = out_coff;
+  p.f16 = f16;
   return dispatch_tc(p, block_n, rowb, stream);
+}
+
+extern "C" int mde_conv_nhwc(const mde_bf16* in, int B, int h, int w, int cin, int in_cstride, const mde_bf16* wpacked, const float* bias,
+                             int cout, int ksize, int padding, int activation, mde_bf16* out_bf16, int out_cstride,
+                             int out_coff, float* out_f32, mde_stream_t stream) {
+  return conv_nhwc_impl(0, in, B, h, w, cin, in_cstride, wpacked, bias, cout, ksize, padding, activation, out_bf16, out_cstride, out_coff, out_f32, stream);
+}
+
+extern "C" int mde_conv_nhwc_f16(const mde_f16* in, int B, int h, int w, int cin, int in_cstride, const mde_f16* wpacked, const float* bias,
+                                 int cout, int ksize, int padding, int activation, mde_f16* out_f16, int out_cstride,
+                                 int out_coff, float* out_f32, mde_stream_t stream) {
+  return conv_nhwc_impl(1, in, B, h, w, cin, in_cstride, wpacked, bias, cout, ksize, padding, activation, out_f16, out_cstride, out_coff, out_f32, stream);
 }

@@ -46,7 +46,7 @@ struct alignas(64) Tc2Params {
   int ldo;
   const void* aux0;
   const void* aux1;
-  int cout, h, w, out_cstride, out_coff;
+  int cout, h, w, out_cstride, out_coff, f16;
 };
 
 struct Item {

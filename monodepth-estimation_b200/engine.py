@@ -19,7 +19,7 @@ from . import _lib as L
 from . import ops
 from .packing import pack_conv, pack_decoder, pack_encoder, pack_enhanced
 
-BF16, F32 = torch.bfloat16, torch.float32
+BF16, F16, F32 = torch.bfloat16, torch.float16, torch.float32
 HOOKS = (2, 5, 8, 11)
 DEC_CH = (256, 128, 64, 32, 16)
 
@@ -313,9 +313,106 @@ class DepthEngine:
 
 
 # ---------------------------------------------------------------------- refinement.py modules
+class _ModuleCache:
+    """Packed weights (re-derived when a parameter changes or moves) + per-geometry buffers of a refinement.py module."""
+
+    def __init__(self, module, pack):
+        self.module, self.pack = module, pack
+        self._fp, self._w, self.bufs = None, None, {}
+
+    def weights(self):
+        fp = _fingerprint(self.module)
+        if fp != self._fp:
+            dev = next(self.module.parameters()).device
+            if dev.type != "cuda":
+                raise RuntimeError("the module must live on a CUDA (sm_100) device: there is no CPU path — call module.to('cuda')")
+            with torch.cuda.device(dev):
+                ops.device_check()
+                self._w = self.pack(self.module.state_dict())
+            self._fp = fp
+        return self._w
+
+    def buffers(self, key, make):
+        b = self.bufs.get(key)
+        if b is None:
+            if len(self.bufs) >= 2:
+                self.bufs.pop(next(iter(self.bufs)))
+            b = self.bufs[key] = make()
+        return b
+
+
+def _cache(module, pack):
+    c = module.__dict__.get("_mde_cache")
+    if c is None:
+        c = module.__dict__["_mde_cache"] = _ModuleCache(module, pack)
+    return c
+
+
+def _as_f32(t, dev):
+    if not t.is_cuda or t.device != dev:
+        raise RuntimeError(f"input is on {t.device} but the module is on {dev}")
+    return t if (t.dtype == F32 and t.is_contiguous()) else t.to(F32).contiguous()
+
+
 def texture_refine_forward(module, depth_map, rgb_image):
-    raise NotImplementedError("TextureAwareRefinementModule (refinement.py:57-107) is not built yet (SURVEY.md §8 a18)")
+    """refinement.py:57-107 (live lines :68-85,:92-107): pack -> merged 16->128 conv -> rgb_conv2 | depth_conv2 (written side by
+    side = the channel concat of :93) -> combined_conv1 -> combined_conv2 -> output kernel (1x1 conv, edge gate, residual add)."""
+    from .packing import pack_texture_refine
+
+    c = _cache(module, pack_texture_refine)
+    w = c.weights()
+    dev = next(module.parameters()).device
+    depth_map, rgb_image = _as_f32(depth_map, dev), _as_f32(rgb_image, dev)
+    B, cd, H, W = depth_map.shape
+    if cd != 1 or rgb_image.shape[0] != B or rgb_image.shape[1] != 3:
+        raise ValueError("expected depth_map [B,1,H,W] and rgb_image [B,3,h,w]")
+    with torch.cuda.device(dev):
+        def make():
+            e = lambda ch: torch.empty(B, H + 2, W + 2, ch, device=dev, dtype=F16)
+            return {"in16": e(16), "f128": e(128), "cat": e(128), "gate": torch.empty(B, H, W, device=dev, dtype=F32),
+                    "rgb": torch.empty(B, 3, H, W, device=dev, dtype=F32)}
+
+        bf = c.buffers((B, H, W), make)
+        if rgb_image.shape[2:] != depth_map.shape[2:]:  # refinement.py:71-72
+            rgb_image = ops.resize_bilinear_nchw(rgb_image, H, W, out=bf["rgb"])
+        ops.refine_pack_inputs(rgb_image, depth_map, bf["in16"], bf["gate"])
+        conv = lambda inp, cin, wb, cout, out, in_coff=0, out_coff=0: ops.conv_nhwc(
+            inp, H, W, cin, wb[0], wb[1], cout, 3, L.PAD_ZERO, L.ACT_ELU, out_bf16=out, out_coff=out_coff, in_coff=in_coff)
+        conv(bf["in16"], 16, w["l1"], 128, bf["f128"])
+        conv(bf["f128"], 64, w["rgb_conv2"], 64, bf["cat"], in_coff=0, out_coff=0)
+        conv(bf["f128"], 64, w["depth_conv2"], 64, bf["cat"], in_coff=64, out_coff=64)
+        conv(bf["cat"], 128, w["combined_conv1"], 64, bf["f128"], out_coff=0)      # f128[..., 0:64]  <- combined_conv1
+        conv(bf["f128"], 64, w["combined_conv2"], 32, bf["f128"], in_coff=0, out_coff=64)  # f128[..., 64:96] <- combined_conv2
+        out = torch.empty(B, 1, H, W, device=dev, dtype=F32)
+        feat = bf["f128"]
+        L.call("mde_refine_output", ops.C.c_void_p(feat.data_ptr() + 2 * 64), feat.shape[-1], ops._ptr(w["out_w"], F32), ops._ptr(w["out_b"], F32),
+               ops._ptr(depth_map, F32), ops._ptr(bf["gate"], F32), B, H, W, ops._ptr(out, F32), ops._stream())
+    return out
 
 
 def depth_fusion_forward(module, depth_scales):
-    raise NotImplementedError("MultiScaleDepthFusion (refinement.py:131-183) is not built yet (SURVEY.md §8 a19)")
+    """refinement.py:131-183: key lookup and target size as the reference, then one fused kernel."""
+    from .packing import pack_depth_fusion
+
+    scales = list(module.scales)
+    key = lambda s: ("disp", s) if ("disp", s) in depth_scales else ("depth", s)
+    maps = []
+    for s in scales:
+        if key(s) not in depth_scales:
+            # the reference `continue`s and then fails in fusion_conv (channel mismatch, refinement.py:152-153,179)
+            raise RuntimeError(f"MultiScaleDepthFusion: scale {s} missing from depth_scales (the reference fails in fusion_conv)")
+        maps.append(depth_scales[key(s)])
+    n = len(scales)
+    if n > L.MAX_FUSION_SCALES:
+        raise ValueError(f"at most {L.MAX_FUSION_SCALES} scales are built")
+    c = _cache(module, lambda sd: pack_depth_fusion(sd, n))
+    w = c.weights()
+    dev = next(module.parameters()).device
+    maps = [_as_f32(m, dev) for m in maps]
+    tgt = depth_scales[key(min(scales))]
+    H, W = tgt.shape[2:]
+    for m in maps:
+        if m.shape[0] != tgt.shape[0] or m.shape[1] != 1:
+            raise ValueError("expected [B,1,h,w] maps of one batch size")
+    with torch.cuda.device(dev):
+        return ops.depth_fusion(maps, H, W, w["conf_w"], w["conf_b"], w["fuse_w"], w["fuse_b"])

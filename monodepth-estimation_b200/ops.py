@@ -13,7 +13,7 @@ import torch
 
 from . import _lib as L
 
-BF16, F32 = torch.bfloat16, torch.float32
+BF16, F16, F32 = torch.bfloat16, torch.float16, torch.float32
 
 
 def _stream():
@@ -98,10 +98,18 @@ def instnorm_nhwc(x, B, gh, gw, Cc, eps, out_padded, out_coff=0, out_flat=None):
     return out_padded
 
 
-def conv_nhwc(inp, h, w, cin, wpacked, bias, cout, ksize, padding, act, out_bf16=None, out_coff=0, out_f32=None):
+def conv_nhwc(inp, h, w, cin, wpacked, bias, cout, ksize, padding, act, out_bf16=None, out_coff=0, out_f32=None, in_coff=0):
+    """``in_coff``: first input channel read (a multiple of 8), so a conv can consume a channel slice of a wider tensor.
+    The operand dtype (bf16, or fp16 -> ``mde_conv_nhwc_f16``) is taken from ``inp``; weights and output must match."""
     B = inp.shape[0]
-    L.call("mde_conv_nhwc", _ptr(inp, BF16), B, h, w, cin, inp.shape[-1], _ptr(wpacked, BF16), _ptr(bias, F32), cout, ksize, padding, act,
-           _ptr(out_bf16, BF16), 0 if out_bf16 is None else out_bf16.shape[-1], out_coff, _ptr(out_f32, F32), _stream())
+    dt = inp.dtype
+    if dt not in (BF16, F16):
+        raise ValueError("conv operands must be bf16 or fp16")
+    if in_coff % 8 or in_coff + cin > inp.shape[-1]:
+        raise ValueError("in_coff must be a multiple of 8 and in_coff + cin <= channels")
+    src = C.c_void_p(_ptr(inp, dt).value + 2 * in_coff)
+    L.call("mde_conv_nhwc" if dt == BF16 else "mde_conv_nhwc_f16", src, B, h, w, cin, inp.shape[-1], _ptr(wpacked, dt), _ptr(bias, F32), cout, ksize,
+           padding, act, _ptr(out_bf16, dt), 0 if out_bf16 is None else out_bf16.shape[-1], out_coff, _ptr(out_f32, F32), _stream())
     return out_bf16 if out_bf16 is not None else out_f32
 
 
@@ -140,3 +148,35 @@ def enh_fuse(d0, d1, d2, refinement, B, h0, w0, gh, gw, mul, fusion_w, fused):
     L.call("mde_enh_fuse", _ptr(d0, F32), _ptr(d1, F32), _ptr(d2, F32), _ptr(refinement, F32), B, h0, w0, gh, gw, float(mul),
            _ptr(fusion_w, F32), _ptr(fused, F32), _stream())
     return fused
+
+
+def depth_fusion(maps, H, W, conf_w, conf_b, fuse_w, fuse_b, out=None):
+    """maps: list of f32 [B,1,h,w] (or [B,h,w]) tensors in scale order; out f32 [B,1,H,W]."""
+    n, B = len(maps), maps[0].shape[0]
+    ptrs = (C.c_void_p * n)(*[_ptr(m, F32).value for m in maps])
+    hs = (C.c_int * n)(*[m.shape[-2] for m in maps])
+    ws = (C.c_int * n)(*[m.shape[-1] for m in maps])
+    out = out if out is not None else torch.empty(B, 1, H, W, device=maps[0].device, dtype=F32)
+    L.call("mde_depth_fusion", ptrs, hs, ws, n, B, H, W, _ptr(conf_w, F32), _ptr(conf_b, F32), _ptr(fuse_w, F32), _ptr(fuse_b, F32),
+           _ptr(out, F32), _stream())
+    return out
+
+
+def refine_pack_inputs(rgb, depth, in16_padded, gate):
+    B, _, H, W = rgb.shape
+    L.call("mde_refine_pack_inputs", _ptr(rgb, F32), _ptr(depth, F32), B, H, W, _ptr(in16_padded, F16), _ptr(gate, F32), _stream())
+
+
+def refine_output(feat_padded, w32, bias1, depth, gate, out):
+    B, H, W = gate.shape
+    L.call("mde_refine_output", _ptr(feat_padded, F16), feat_padded.shape[-1], _ptr(w32, F32), _ptr(bias1, F32), _ptr(depth, F32),
+           _ptr(gate, F32), B, H, W, _ptr(out, F32), _stream())
+    return out
+
+
+def u8hwc_to_f32chw(src, out=None):
+    """uint8 [B,H,W,3] -> float32 [B,3,H,W] / 255 (run_mars_depth.py:100-103 on the device)."""
+    B, H, W, _ = src.shape
+    out = out if out is not None else torch.empty(B, 3, H, W, device=src.device, dtype=F32)
+    L.call("mde_u8hwc_to_f32chw", _ptr(src, torch.uint8), B, H, W, _ptr(out, F32), _stream())
+    return out

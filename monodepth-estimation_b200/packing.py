@@ -11,7 +11,7 @@ from __future__ import annotations
 
 import torch
 
-BF16, F32 = torch.bfloat16, torch.float32
+BF16, F16, F32 = torch.bfloat16, torch.float16, torch.float32
 
 
 def _pad_rows(w2d: torch.Tensor, mult: int) -> torch.Tensor:
@@ -24,7 +24,7 @@ def _pad_rows(w2d: torch.Tensor, mult: int) -> torch.Tensor:
     return out
 
 
-def pack_conv(weight, bias, bn=None, cin_pad=None, eps=1e-5):
+def pack_conv(weight, bias, bn=None, cin_pad=None, eps=1e-5, dtype=BF16):
     """[cout,cin,k,k] conv (+ optional eval BN) -> (bf16 [cout_pad, k*k*cin_pad], f32 bias [cout_pad])."""
     w = weight.detach().to(F32)
     cout, cin, kh, kw = w.shape
@@ -39,7 +39,7 @@ def pack_conv(weight, bias, bn=None, cin_pad=None, eps=1e-5):
         wp = w.new_zeros(cout, kh, kw, cin_pad)
         wp[..., :cin] = w
         w = wp
-    w2 = _pad_rows(w.reshape(cout, -1), 16).to(BF16).contiguous()
+    w2 = _pad_rows(w.reshape(cout, -1), 16).to(dtype).contiguous()
     b2 = _pad_rows(b.view(-1, 1), 16).view(-1).contiguous()
     return w2, b2
 
@@ -104,3 +104,28 @@ def pack_enhanced(sd):
     out["ref3"] = pack_conv(sd[r + "conv3.weight"], sd[r + "conv3.bias"])
     out["fusion_w"] = sd["feature_fusion.weights"].detach().to(F32).contiguous()
     return out
+
+
+def pack_texture_refine(sd, p=""):
+    """refinement.py:19-36 TextureAwareRefinementModule: rgb_conv1 (3->64) and depth_conv1 (1->64) are merged into ONE
+    16->128 conv over the packed input {r,g,b,depth,0..} (block-structured weights: rows 0..63 see r,g,b, rows 64..127 see
+    depth), so the first layer is a single implicit GEMM; operands are fp16 (see mde_conv_nhwc_f16); the 1x1 output conv stays fp32 for the output kernel."""
+    f = lambda k: sd[p + k].detach().to(F32)
+    w1 = f("rgb_conv1.weight").new_zeros(128, 16, 3, 3)
+    w1[:64, 0:3] = f("rgb_conv1.weight")
+    w1[64:, 3:4] = f("depth_conv1.weight")
+    b1 = torch.cat([f("rgb_conv1.bias"), f("depth_conv1.bias")])
+    out = {"l1": pack_conv(w1, b1, dtype=F16)}
+    for n in ("rgb_conv2", "depth_conv2", "combined_conv1", "combined_conv2"):
+        out[n] = pack_conv(sd[p + n + ".weight"], sd[p + n + ".bias"], dtype=F16)
+    out["out_w"] = f("output_conv.weight").reshape(32).contiguous()
+    out["out_b"] = f("output_conv.bias").reshape(1).contiguous()
+    return out
+
+
+def pack_depth_fusion(sd, n, p=""):
+    """refinement.py:122-129 MultiScaleDepthFusion: the n 3x3 1->1 confidence convs and the 1x1 n->1 fusion conv as flat fp32."""
+    f = lambda k: sd[p + k].detach().to(F32)
+    return {"conf_w": torch.stack([f(f"confidence_conv.{i}.weight").reshape(9) for i in range(n)]).contiguous(),
+            "conf_b": torch.cat([f(f"confidence_conv.{i}.bias").reshape(1) for i in range(n)]).contiguous(),
+            "fuse_w": f("fusion_conv.weight").reshape(n).contiguous(), "fuse_b": f("fusion_conv.bias").reshape(1).contiguous()}

@@ -1,0 +1,109 @@
+"""Caller-side batching: a pinned-memory, multi-stream host <-> device pipeline around ``model(x, metadata)``.
+
+The reference's callers run strictly one image at a time with a blocking ``.to(device)`` before and a blocking
+``.cpu()`` after every forward (``run_mars_depth.py:90-147``; ``--batch_size`` is parsed and never used, ``:47-50``).
+Once the forward itself costs ~0.1 ms/image the PCIe copies are the whole cost, so this module overlaps them:
+
+    copy-in stream :  H2D(i+1) ───────────────►
+    compute stream :        forward(i) ──►
+    copy-out stream:   D2H(i-1) ──►
+
+``depth`` device input buffers and pinned host output buffers form a ring; CUDA events order the three streams, the
+host never blocks inside the loop except to hand a finished result back.  PCIe is full duplex, so the steady state is
+``max(H2D, forward, D2H)`` per batch instead of their sum.
+
+Two host formats are accepted:
+  * ``float32 [B,3,H,W]`` — exactly what the reference callers build on the host (``run_mars_depth.py:100-104``);
+  * ``uint8 [B,H,W,3]``   — what the image decoder produces (``np.array(PIL image)``, ``:97-100``); the
+    ``float()/255`` + HWC->CHW step then runs on the device (``mde_u8hwc_to_f32chw``: same IEEE fp32 division,
+    bit-identical to the host expression) and the H2D copy is 4x smaller.
+"""
+from __future__ import annotations
+
+import torch
+
+from . import ops
+
+F32 = torch.float32
+
+
+class BatchPipeline:
+    def __init__(self, model, keys=(("disp", 0),), depth: int = 2):
+        if depth < 2:
+            raise ValueError("depth must be >= 2 (double buffering)")
+        self.model = model
+        self.keys = tuple(keys)
+        self.depth = depth
+        self.dev = next(model.parameters()).device
+        if self.dev.type != "cuda":
+            raise RuntimeError("the model must live on a CUDA device")
+        with torch.cuda.device(self.dev):
+            self.s_in, self.s_out = torch.cuda.Stream(), torch.cuda.Stream()
+        self._slots = None
+        self._sig = None
+
+    def _prepare(self, batch):
+        sig = (tuple(batch.shape), batch.dtype)
+        if sig == self._sig:
+            return
+        if batch.dtype == torch.uint8:
+            B, H, W, C = batch.shape
+            if C != 3:
+                raise ValueError("uint8 batches must be [B,H,W,3]")
+        elif batch.dtype == F32:
+            B, C, H, W = batch.shape
+            if C != 3:
+                raise ValueError("float32 batches must be [B,3,H,W]")
+        else:
+            raise ValueError("host batches must be float32 [B,3,H,W] or uint8 [B,H,W,3]")
+        ev = lambda: torch.cuda.Event()
+        self._slots = []
+        for _ in range(self.depth):
+            s = {"raw": torch.empty(batch.shape, device=self.dev, dtype=batch.dtype), "in_ready": ev(), "in_free": ev(), "done": ev(), "copied": ev(),
+                 "host": {k: torch.empty(B, 1, H, W, dtype=F32).pin_memory() for k in self.keys}, "busy": False}
+            s["x"] = s["raw"] if batch.dtype == F32 else torch.empty(B, 3, H, W, device=self.dev, dtype=F32)
+            self._slots.append(s)
+        self._sig = sig
+
+    def run(self, host_batches, metadata=None, consume=None):
+        """Feeds every batch of ``host_batches`` (an iterable of pinned host tensors, all the same shape/dtype) through
+        the model.  ``consume(index, {key: pinned host tensor})`` is called as each result lands (the tensors are reused
+        ``depth`` batches later, so copy out what must outlive that).  Returns the number of batches processed."""
+        n = 0
+        pending = []  # (index, slot) in submission order
+        with torch.cuda.device(self.dev):
+            compute = torch.cuda.current_stream()
+            for i, hb in enumerate(host_batches):
+                self._prepare(hb)
+                s = self._slots[i % self.depth]
+                if s["busy"]:  # this slot's previous result must have been handed back before its buffers are reused
+                    j, sj = pending.pop(0)
+                    sj["copied"].synchronize()
+                    if consume is not None:
+                        consume(j, sj["host"])
+                    sj["busy"] = False
+                with torch.cuda.stream(self.s_in):
+                    self.s_in.wait_event(s["in_free"])
+                    s["raw"].copy_(hb, non_blocking=True)
+                    s["in_ready"].record(self.s_in)
+                compute.wait_event(s["in_ready"])
+                if s["raw"].dtype == torch.uint8:
+                    ops.u8hwc_to_f32chw(s["raw"], s["x"])
+                out = self.model(s["x"], metadata)
+                s["in_free"].record(compute)
+                s["done"].record(compute)
+                with torch.cuda.stream(self.s_out):
+                    self.s_out.wait_event(s["done"])
+                    for k in self.keys:
+                        s["host"][k].copy_(out[k], non_blocking=True)
+                        out[k].record_stream(self.s_out)
+                    s["copied"].record(self.s_out)
+                s["busy"] = True
+                pending.append((i, s))
+                n += 1
+            for j, sj in pending:
+                sj["copied"].synchronize()
+                if consume is not None:
+                    consume(j, sj["host"])
+                sj["busy"] = False
+        return n

@@ -1,5 +1,7 @@
 """Summarise an `ncu --metrics gpu__time_duration.sum --csv` launch list: per kernel/grid class,
-launches per step, average and total device time.  usage: launch_summary.py file.csv steps [skip_steps]"""
+launches per step, average and total device time.
+usage: launch_summary.py file.csv steps [skip_steps]      (equal-length steps)
+       launch_summary.py file.csv --from <kernel substring>   (the LAST forward: from the last launch of that kernel to the end)"""
 import collections
 import csv
 import re
@@ -7,8 +9,10 @@ import sys
 
 
 def main():
-    path, steps = sys.argv[1], int(sys.argv[2])
-    skip = int(sys.argv[3]) if len(sys.argv) > 3 else 0
+    path = sys.argv[1]
+    start_name = sys.argv[3] if sys.argv[2] == "--from" else None
+    steps = 1 if start_name else int(sys.argv[2])
+    skip = int(sys.argv[3]) if len(sys.argv) > 3 and not start_name else 0
     lines = [l for l in open(path) if not l.startswith("==")]
     seq = []
     for row in csv.DictReader(lines):
@@ -18,8 +22,13 @@ def main():
         v = float(row["Metric Value"].replace(",", ""))
         v = v / 1000 if row["Metric Unit"] == "ns" else (v * 1000 if row["Metric Unit"] == "ms" else v)
         seq.append((name, row["Grid Size"], v))
-    per = len(seq) // (steps + skip)
-    seq = seq[per * skip:per * (skip + steps)]
+    if start_name:
+        first = max(i for i, (n, _, _) in enumerate(seq) if start_name in n)
+        seq = seq[first:]
+        per = len(seq)
+    else:
+        per = len(seq) // (steps + skip)
+        seq = seq[per * skip:per * (skip + steps)]
     agg = collections.OrderedDict()
     for n, g, v in seq:
         a = agg.setdefault((n, g), [0, 0.0])
