@@ -327,7 +327,9 @@ def roofline_leg(model, x_dev, md, ops, pk):
             "achieved": round(ach, 1), "peak": pk["bf16_tflops_sustained"], "unit": "TFLOP/s", "frac": round(ach / pk["bf16_tflops_sustained"], 4),
             "peak_source": f"{pk['source']} (sustained cuBLAS bf16: kernel timed inside a long step)", "traffic": None,
             "launches_per_step": len(ts), "avg_us": round(avg * 1e6, 2), "share_of_gemm_time": round(sum(ts) / total_all, 4),
-            "all_gemms_tflops": round(allf / total_all / 1e12, 1), "all_gemms_ms_per_step": round(total_all * 1e3, 4)}
+            "all_gemms_tflops": round(allf / total_all / 1e12, 1), "all_gemms_ms_per_step": round(total_all * 1e3, 4),
+            "gemm_classes": [{"M": k[0], "N": k[1], "K": k[2], "epi": k[3], "n": len(v), "avg_us": round(sum(v) / len(v) * 1e6, 2),
+                              "tflops": round(2.0 * k[0] * k[1] * k[2] * len(v) / sum(v) / 1e12, 1)} for k, v in sorted(agg.items(), key=lambda kv: -sum(kv[1]))]}
 
 
 if __name__ == "__main__":

@@ -45,6 +45,11 @@ static PFN_cuTensorMapEncodeTiled_v12000 get_encode_fn() {
 
 int encode_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
                      const uint32_t* box, int swizzle_bytes) {
+  return encode_tmap(out, 2, base, rank, dims, strides_bytes, box, swizzle_bytes);
+}
+
+int encode_tmap(CUtensorMap* out, int elt_bytes, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+                const uint32_t* box, int swizzle_bytes) {
   PFN_cuTensorMapEncodeTiled_v12000 fn = get_encode_fn();
   if (!fn) {
     set_error("cuTensorMapEncodeTiled entry point unavailable (driver too old?)");
@@ -62,7 +67,7 @@ int encode_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_
     estr[i] = 1;
   }
   for (int i = 0; i + 1 < rank; ++i) gstrides[i] = strides_bytes[i];
-  CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(base), gdims, gstrides, gbox, estr,
+  CUresult r = fn(out, elt_bytes == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(base), gdims, gstrides, gbox, estr,
                   CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
     set_error("cuTensorMapEncodeTiled failed with CUresult %d (rank %d, dims %llu %llu, box %u %u, swizzle %d)", (int)r, rank,

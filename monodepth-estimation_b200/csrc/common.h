@@ -45,10 +45,18 @@ int sm_count();  // SMs of the current device (cached per device)
 // entries (strides of dims 1..rank-1).  swizzle_bytes in {32, 64, 128}.  Returns MDE_OK or error.
 int encode_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims,
                      const uint64_t* strides_bytes, const uint32_t* box, int swizzle_bytes);
+// Same for 4-byte (fp32) elements when elt_bytes == 4 (2 -> bf16).
+int encode_tmap(CUtensorMap* out, int elt_bytes, const void* base, int rank, const uint64_t* dims,
+                const uint64_t* strides_bytes, const uint32_t* box, int swizzle_bytes);
 
 // 2-CTA (cta_group::2) GEMM path of mde_gemm_bf16 (tc_gemm2.cu); same contract, needs N % 256 == 0.
 int launch_gemm_pair(const void* A, int lda, const void* W, int ldw, int M, int N, int K, int epilogue, const float* bias, void* out, int ldo,
                      const void* aux0, const void* aux1, cudaStream_t stream);
+
+// Halo-resident 3x3 conv path of mde_conv_nhwc (conv_halo.cu).  MDE_OK = launched; MDE_ERR_UNSUPPORTED (no error text) =
+// geometry not served there, the caller uses the tap-shifted kernel.
+int launch_conv_halo(int f16, const void* in, int B, int h, int w, int cin, int in_cstride, const void* wpacked, const float* bias, int cout,
+                     int padding, int activation, void* out_bf16, int out_cstride, int out_coff, float* out_f32, cudaStream_t stream);
 
 static inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 

@@ -350,6 +350,12 @@ static int conv_nhwc_impl(int f16, const mde_bf16* in, int B, int h, int w, int 
   }
   MDE_CHECK_ARG(((uintptr_t)in | (uintptr_t)wpacked | (uintptr_t)bias) % 16 == 0, "mde_conv_nhwc: pointers must be 16-byte aligned");
 
+  if (ksize == 3) {  // wide maps: halo-resident kernel (conv_halo.cu); it declines geometries it does not serve
+    const int rc = launch_conv_halo(f16, in, B, h, w, cin, in_cstride, wpacked, bias, cout, padding, activation, out_bf16, out_cstride, out_coff,
+                                    out_f32, stream);
+    if (rc != MDE_ERR_UNSUPPORTED) return rc;
+  }
+
   // spatial tile: 128 output pixels = th rows x tw columns
   int tw = 16;
   while (tw < w && tw < 128) tw <<= 1;

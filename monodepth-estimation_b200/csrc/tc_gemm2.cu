@@ -12,7 +12,14 @@
 //
 // Warp roles per CTA (320 threads): warp 0 TMA producer (loads its CTA's A rows and B half, credits the
 // leader's full barrier), warp 1 TMEM allocator + (leader only) MMA issuer, warps 2..9 epilogue: two warps
-// per TMEM lane quarter, each taking every other 32-column chunk, residual loads software-pipelined.
+// per TMEM lane quarter, each taking every other 128-byte output chunk.
+//
+// Epilogue data path (bias | bias+GELU | bias+residual, i.e. every ViT linear layer except QKV / patch embed): a thread owns
+// one accumulator row, so direct global stores would touch 32 different cache lines per warp instruction — measured at
+// ~20 us per 256x256 tile against 3 us of MMA time (r01e).  Instead each epilogue warp stages its 32-row x 128-byte
+// sub-tile in a private, 128B-swizzled shared-memory buffer and moves it with TMA: the residual arrives by TMA LOAD
+// one chunk ahead, bias/activation/residual are applied in place, and a TMA STORE (bulk group) writes it out while
+// the warp is already on its next chunk.  No LSU global traffic, full-line writes, rows >= M clipped by the tensor map.
 #include <stdio.h>
 
 #include <algorithm>
@@ -29,11 +36,19 @@ constexpr int k2ABytes = 128 * 128;       // 128 rows x 64 bf16
 constexpr int k2BBytes = 128 * 128;       // B half of a wide item (128 rows); narrow items use the first 4 KB
 constexpr int k2StageBytes = k2ABytes + k2BBytes;
 constexpr uint32_t k2TmemCols = 512;      // 2 accumulator buffers x 256 columns
+constexpr int k2EpiWarps = 8;
+constexpr int k2EpiBufBytes = 32 * 128;   // one epilogue warp's staging buffer: 32 rows x 128 bytes (SWIZZLE_128B)
+constexpr int k2StagingBytes = k2EpiWarps * 2 * k2EpiBufBytes;
+constexpr int k2BarrierBytes = 512;
 
 struct alignas(64) Tc2Params {
   CUtensorMap tmA;   // box [64, 128]
   CUtensorMap tmB;   // box [64, 128]: wide items (pair N = 256)
   CUtensorMap tmBn;  // box [64, 32] : narrow items (pair N = 64)
+  CUtensorMap tmOut; // box [128 bytes of columns, 32 rows] over the output (TMA-store epilogue)
+  CUtensorMap tmRes; // same geometry over the residual input
+  int tma_epi;       // 1: TMA-store epilogue (out_elt = 4: fp32, 2: bf16); 0: direct-store epilogue (QKV split, patch embed)
+  int out_elt;
   int M, N;
   int k_blocks, stages;
   int n_wide;        // N / 256
@@ -73,11 +88,13 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(k2Threads, 1) tc_gem
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
   const int stages = p.stages;
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + (size_t)stages * k2StageBytes);
+  uint8_t* staging = smem + (size_t)stages * k2StageBytes;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(staging + k2StagingBytes);
   uint64_t* empty_bar = full_bar + stages;
   uint64_t* tfull_bar = empty_bar + stages;
   uint64_t* tempty_bar = tfull_bar + 2;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+  uint64_t* res_bar = tempty_bar + 2;  // [k2EpiWarps][2] residual-chunk arrival barriers
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(res_bar + 2 * k2EpiWarps);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t rank = cluster_ctarank();
@@ -88,6 +105,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(k2Threads, 1) tc_gem
     tma_prefetch_desc(&p.tmA);
     tma_prefetch_desc(&p.tmB);
     tma_prefetch_desc(&p.tmBn);
+    if (p.tma_epi) {
+      tma_prefetch_desc(&p.tmOut);
+      tma_prefetch_desc(&p.tmRes);
+    }
   }
   if (warp == 1) {
     if (elect_one()) {
@@ -99,6 +120,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(k2Threads, 1) tc_gem
         mbar_init(&tfull_bar[a], 1);    // pair commit (multicast)
         mbar_init(&tempty_bar[a], 16);  // 8 epilogue warps x 2 CTAs (only the leader's copy is waited on)
       }
+      for (int a = 0; a < 2 * k2EpiWarps; ++a) mbar_init(&res_bar[a], 1);
       fence_barrier_init();
     }
     __syncwarp();
@@ -165,54 +187,129 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(k2Threads, 1) tc_gem
   } else {
     // ------------------------------------------------------------------ epilogue warps (both CTAs)
     const int q = warp & 3;          // TMEM lane quarter
-    const int par = (warp - 2) >> 2; // which half of the 32-column chunks this warp takes
+    const int par = (warp - 2) >> 2; // which half of the output chunks this warp takes
     const int r = q * 32 + lane;
     int acc = 0;
     uint32_t acc_phase = 0;
-    for (int i = cluster_id; i < p.total_items; i += num_clusters) {
-      const Item it = decode_item(p, i);
-      RowInfo ri;
-      ri.m = it.m0 + (int)rank * 128 + r;
-      ri.b = ri.y = ri.x = 0;
-      ri.valid = ri.m < p.M;
-      mbar_wait(&tfull_bar[acc], acc_phase);
-      tc_fence_after();
-      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * 256;
-      const int nchunks = it.bn >> 5;
-      if (p.epi == MDE_EPI_BIAS_RESID_F32) {
-        // residual rows are read one chunk ahead of the accumulator they are added to
-        const float* rs_row = reinterpret_cast<const float*>(p.aux0) + (size_t)ri.m * p.ldo + it.n0;
-        float* out_row = reinterpret_cast<float*>(p.out) + (size_t)ri.m * p.ldo + it.n0;
-        float4 nxt[8];
-        int c = par;
-        if (ri.valid && c < nchunks) {
-#pragma unroll
-          for (int j = 0; j < 8; ++j) nxt[j] = __ldg(reinterpret_cast<const float4*>(rs_row + c * 32) + j);
-        }
+    if (p.tma_epi) {
+      const int ew = warp - 2;
+      uint8_t* stg = staging + ew * 2 * k2EpiBufBytes;
+      uint64_t* rbar = res_bar + ew * 2;
+      const bool resid = p.epi == MDE_EPI_BIAS_RESID_F32;
+      const bool f32out = p.out_elt == 4;
+      const int cw = f32out ? 32 : 64;  // columns per 128-byte chunk
+      const uint32_t sw = static_cast<uint32_t>(lane & 7);
+      uint32_t g = 0;  // chunks this warp has processed: staging buffer = g & 1, residual barrier parity = (g >> 1) & 1
+      // lane 0: TMA-load the residual sub-tile of (item, chunk) into the buffer chunk number `gg` will use
+      auto load_resid = [&](const Item& it2, int c2, uint32_t gg) {
+        uint64_t* b = &rbar[gg & 1];
+        mbar_expect_tx(b, k2EpiBufBytes);
+        tma_load_2d(stg + (gg & 1) * k2EpiBufBytes, &p.tmRes, b, it2.n0 + c2 * cw, it2.m0 + (int)rank * 128 + q * 32);
+      };
+      int i = cluster_id;
+      Item it = decode_item(p, i < p.total_items ? i : 0);
+      if (resid && i < p.total_items && par < it.bn / cw && lane == 0) load_resid(it, par, g);
+      while (i < p.total_items) {
+        const int inext = i + num_clusters;
+        const bool has_next = inext < p.total_items;
+        const Item itn = decode_item(p, has_next ? inext : i);
+        const int nch = it.bn / cw;
+        const int row0 = it.m0 + (int)rank * 128 + q * 32;
+        mbar_wait(&tfull_bar[acc], acc_phase);
+        tc_fence_after();
+        const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * 256;
 #pragma unroll 1
-        for (; c < nchunks; c += 2) {
-          float4 cur[8];
-#pragma unroll
-          for (int j = 0; j < 8; ++j) cur[j] = nxt[j];
-          if (ri.valid && c + 2 < nchunks) {
-#pragma unroll
-            for (int j = 0; j < 8; ++j) nxt[j] = __ldg(reinterpret_cast<const float4*>(rs_row + (c + 2) * 32) + j);
-          }
-          uint32_t raw[32];
-          tmem_ld_32x32b_x32(taddr + c * 32, raw);
-          tmem_ld_wait();
-          if (ri.valid) {
-            const float4* bp = reinterpret_cast<const float4*>(p.bias + it.n0 + c * 32);
-            float4* dst = reinterpret_cast<float4*>(out_row + c * 32);
+        for (int c = par; c < nch; c += 2, ++g) {
+          uint8_t* buf = stg + (g & 1) * k2EpiBufBytes;
+          uint8_t* row = buf + lane * 128;
+          const int n0 = it.n0 + c * cw;
+          if (f32out) {
+            uint32_t raw[32];
+            tmem_ld_32x32b_x32(taddr + c * 32, raw);
+            if (lane == 0) {
+              if (resid) {
+                // the other buffer (chunk g+1's) was last read by the store of chunk g-1: wait for it, then prefetch into it
+                if (c + 2 < nch) {
+                  bulk_wait_read<0>();
+                  load_resid(it, c + 2, g + 1);
+                } else if (has_next && par < itn.bn / cw) {
+                  bulk_wait_read<0>();
+                  load_resid(itn, par, g + 1);
+                }
+              } else {
+                bulk_wait_read<1>();  // this buffer's previous store (chunk g-2) has finished reading it
+              }
+            }
+            __syncwarp();
+            tmem_ld_wait();
+            if (resid) mbar_wait(&rbar[g & 1], (g >> 1) & 1);
+            const float4* bp = reinterpret_cast<const float4*>(p.bias + n0);
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
+              float4* sp = reinterpret_cast<float4*>(row + ((static_cast<uint32_t>(j) ^ sw) << 4));
               const float4 b4 = __ldg(bp + j);
-              dst[j] = make_float4(__uint_as_float(raw[4 * j]) + b4.x + cur[j].x, __uint_as_float(raw[4 * j + 1]) + b4.y + cur[j].y,
-                                   __uint_as_float(raw[4 * j + 2]) + b4.z + cur[j].z, __uint_as_float(raw[4 * j + 3]) + b4.w + cur[j].w);
+              float4 o = make_float4(__uint_as_float(raw[4 * j]) + b4.x, __uint_as_float(raw[4 * j + 1]) + b4.y,
+                                     __uint_as_float(raw[4 * j + 2]) + b4.z, __uint_as_float(raw[4 * j + 3]) + b4.w);
+              if (resid) {
+                const float4 r4 = *sp;
+                o.x += r4.x;
+                o.y += r4.y;
+                o.z += r4.z;
+                o.w += r4.w;
+              }
+              *sp = o;
+            }
+          } else {
+            uint32_t raw[64];
+            tmem_ld_32x32b_x32(taddr + c * 64, *reinterpret_cast<uint32_t(*)[32]>(&raw[0]));
+            tmem_ld_32x32b_x32(taddr + c * 64 + 32, *reinterpret_cast<uint32_t(*)[32]>(&raw[32]));
+            if (lane == 0) bulk_wait_read<1>();
+            __syncwarp();
+            tmem_ld_wait();
+            const float4* bp = reinterpret_cast<const float4*>(p.bias + n0);
+            const bool gelu = p.epi == MDE_EPI_BIAS_GELU_BF16;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const float4 b0 = __ldg(bp + 2 * j), b1 = __ldg(bp + 2 * j + 1);
+              float v[8] = {__uint_as_float(raw[8 * j]) + b0.x,     __uint_as_float(raw[8 * j + 1]) + b0.y, __uint_as_float(raw[8 * j + 2]) + b0.z,
+                            __uint_as_float(raw[8 * j + 3]) + b0.w, __uint_as_float(raw[8 * j + 4]) + b1.x, __uint_as_float(raw[8 * j + 5]) + b1.y,
+                            __uint_as_float(raw[8 * j + 6]) + b1.z, __uint_as_float(raw[8 * j + 7]) + b1.w};
+              if (gelu) {
+#pragma unroll
+                for (int t = 0; t < 8; ++t) v[t] = gelu_fast(v[t]);
+              }
+              *reinterpret_cast<uint4*>(row + ((static_cast<uint32_t>(j) ^ sw) << 4)) =
+                  make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
             }
           }
+          fence_proxy_async_smem();  // generic-proxy writes -> visible to the TMA engine
+          __syncwarp();
+          if (lane == 0) {
+            tma_store_2d(&p.tmOut, buf, n0, row0);
+            bulk_commit();
+          }
         }
-      } else {
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive_cluster(&tempty_bar[acc], 0);  // the leader's MMA thread owns the accumulator ring
+        acc ^= 1;
+        if (acc == 0) acc_phase ^= 1;
+        i = inext;
+        it = itn;
+      }
+      if (lane == 0) bulk_wait_all<0>();  // every store has left shared memory and is globally performed
+      __syncwarp();
+    } else {
+      for (int i = cluster_id; i < p.total_items; i += num_clusters) {
+        const Item it = decode_item(p, i);
+        RowInfo ri;
+        ri.m = it.m0 + (int)rank * 128 + r;
+        ri.b = ri.y = ri.x = 0;
+        ri.valid = ri.m < p.M;
+        mbar_wait(&tfull_bar[acc], acc_phase);
+        tc_fence_after();
+        const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * 256;
+        const int nchunks = it.bn >> 5;
 #pragma unroll 1
         for (int c = par; c < nchunks; c += 2) {
           uint32_t raw[32];
@@ -223,12 +320,12 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(k2Threads, 1) tc_gem
           for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(raw[j]);
           epilogue_chunk<32, Tc2Params>(p, v, it.n0 + c * 32, ri);
         }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive_cluster(&tempty_bar[acc], 0);
+        acc ^= 1;
+        if (acc == 0) acc_phase ^= 1;
       }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive_cluster(&tempty_bar[acc], 0);  // the leader's MMA thread owns the accumulator ring
-      acc ^= 1;
-      if (acc == 0) acc_phase ^= 1;
     }
   }
 
@@ -274,10 +371,26 @@ int launch_gemm_pair(const void* A, int lda, const void* W, int ldw, int M, int 
   p.ldo = ldo;
   p.aux0 = aux0;
   p.aux1 = aux1;
-  int stages = (220 * 1024 - 2048) / k2StageBytes;
+  p.tma_epi = epilogue <= MDE_EPI_BIAS_F32;
+  p.out_elt = (epilogue == MDE_EPI_BIAS_RESID_F32 || epilogue == MDE_EPI_BIAS_F32) ? 4 : 2;
+  if (p.tma_epi) {
+    if (((uintptr_t)out % 16) || (ldo * p.out_elt) % 16 || (aux0 && epilogue == MDE_EPI_BIAS_RESID_F32 && ((uintptr_t)aux0 % 16))) {
+      set_error("mde_gemm_bf16: output/residual must be 16-byte aligned with a 16-byte multiple row pitch");
+      return MDE_ERR_BAD_ARGUMENT;
+    }
+    const uint64_t dims[2] = {(uint64_t)N, (uint64_t)M};
+    const uint64_t strides[1] = {(uint64_t)ldo * p.out_elt};
+    const uint32_t box[2] = {(uint32_t)(128 / p.out_elt), 32};
+    int rc = encode_tmap(&p.tmOut, p.out_elt, out, 2, dims, strides, box, 128);
+    if (rc != MDE_OK) return rc;
+    rc = encode_tmap(&p.tmRes, p.out_elt, epilogue == MDE_EPI_BIAS_RESID_F32 ? aux0 : out, 2, dims, strides, box, 128);
+    if (rc != MDE_OK) return rc;
+  }
+  const int smem_max = 227 * 1024;
+  int stages = (smem_max - 1024 - k2StagingBytes - k2BarrierBytes) / k2StageBytes;
   if (stages > k2MaxStages) stages = k2MaxStages;
   p.stages = stages;
-  const int smem_bytes = stages * k2StageBytes + 1024 + (2 * k2MaxStages + 8) * 8;
+  const int smem_bytes = stages * k2StageBytes + k2StagingBytes + 1024 + k2BarrierBytes;
   static bool attr_set = false;
   if (!attr_set) {
     MDE_CHECK_CUDA(cudaFuncSetAttribute(tc_gemm2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
