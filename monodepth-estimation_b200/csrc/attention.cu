@@ -23,10 +23,10 @@ constexpr int kPBytes = 128 * 128;            // one k-block of P: 128 rows x 64
 constexpr int kOffK = 2 * kQBytes;
 constexpr int kOffV = kOffK + kKBytesPad;
 constexpr int kOffP = kOffV + 4 * kVBytes;
-constexpr int kOffBar = kOffP + 4 * kPBytes;
+constexpr int kOffBar = kOffP + 2 * 4 * kPBytes;  // one P tile (4 k-blocks) per query tile
 constexpr int kAttnSmem = kOffBar + 64 + 1024;
 constexpr uint32_t kTmemCols = 512;
-constexpr uint32_t kTmemO = 256;  // O accumulator column offset (S occupies [0,208))
+constexpr uint32_t kTmemTile = 256;  // column stride between the two query tiles; O reuses the first 64 columns of its tile's S
 
 struct alignas(64) AttnParams {
   CUtensorMap tmQ, tmK, tmV;
@@ -34,21 +34,24 @@ struct alignas(64) AttnParams {
   int B;
 };
 
-__global__ void __launch_bounds__(128, 1) vit_attn_kernel(const __grid_constant__ AttnParams p) {
+// 256 threads = two warpgroups; warpgroup g owns query tile g (rows 128g .. 128g+127) end to end, so the two tiles'
+// S = Q K^T MMAs are issued back to back and the softmax of one tile overlaps the MMAs / TMEM traffic of the other.
+__global__ void __launch_bounds__(256, 1) vit_attn_kernel(const __grid_constant__ AttnParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
   uint8_t* sQ = smem;
   uint8_t* sK = smem + kOffK;
   uint8_t* sV = smem + kOffV;
-  uint8_t* sP = smem + kOffP;
   uint64_t* bar_load = reinterpret_cast<uint64_t*>(smem + kOffBar);
-  uint64_t* bar_s = bar_load + 1;
-  uint64_t* bar_o = bar_load + 2;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_load + 3);
+  uint64_t* bar_s = bar_load + 1;  // [2]
+  uint64_t* bar_o = bar_load + 3;  // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_load + 5);
 
   const int tid = threadIdx.x, warp = tid >> 5;
-  const int slab = blockIdx.x;  // b * 12 + head
+  const int wg = tid >> 7, wt = tid & 127;  // warpgroup = query tile, row within the tile
+  const int slab = blockIdx.x;              // b * 12 + head
   const int b = slab / MDE_VIT_HEADS, hd = slab - b * MDE_VIT_HEADS;
+  uint8_t* sP = smem + kOffP + wg * 4 * kPBytes;
 
   if (warp == 0) {
     if (elect_one()) {
@@ -56,8 +59,10 @@ __global__ void __launch_bounds__(128, 1) vit_attn_kernel(const __grid_constant_
       tma_prefetch_desc(&p.tmK);
       tma_prefetch_desc(&p.tmV);
       mbar_init(bar_load, 1);
-      mbar_init(bar_s, 1);
-      mbar_init(bar_o, 1);
+      for (int i = 0; i < 2; ++i) {
+        mbar_init(&bar_s[i], 1);
+        mbar_init(&bar_o[i], 1);
+      }
       fence_barrier_init();
     }
     __syncwarp();
@@ -78,122 +83,120 @@ __global__ void __launch_bounds__(128, 1) vit_attn_kernel(const __grid_constant_
   }
   mbar_wait(bar_load, 0);
 
-  const uint32_t t_row = tmem_base + (static_cast<uint32_t>(warp * 32) << 16);  // this thread's TMEM lane
-  const uint32_t sw = static_cast<uint32_t>(tid & 7);                            // swizzle phase of row tid
-  uint8_t* p_row = sP + tid * 128;
+  const uint32_t t_tile = tmem_base + wg * kTmemTile;                                   // this tile's S (and later O) columns
+  const uint32_t t_row = t_tile + (static_cast<uint32_t>((warp & 3) * 32) << 16);       // this thread's TMEM lane
+  const uint32_t sw = static_cast<uint32_t>(wt & 7);                                    // swizzle phase of row wt
+  uint8_t* p_row = sP + wt * 128;
   constexpr float kLog2e = 1.4426950408889634f;
 
-#pragma unroll 1
-  for (int mt = 0; mt < 2; ++mt) {
-    // ---- S = Q_mt K^T  (128 x 208, K = 64)
-    if (tid == 0) {
-      tc_fence_after();
-      constexpr uint32_t idesc_s = umma_idesc_bf16(128, kKeys);
-      const uint64_t da = umma_smem_desc_kmajor<128>(smem_u32(sQ + mt * kQBytes));
-      const uint64_t db = umma_smem_desc_kmajor<128>(smem_u32(sK));
-#pragma unroll
-      for (int k = 0; k < 4; ++k) umma_bf16_ss(tmem_base, da + 2 * k, db + 2 * k, idesc_s, k != 0);
-      umma_commit(bar_s);
-    }
-    mbar_wait(bar_s, mt & 1);
+  // ---- S = Q_g K^T  (128 x 208, K = 64)
+  if (wt == 0) {
     tc_fence_after();
-
-    // ---- row softmax over the 197 real keys (columns >= 197 are zero-filled K rows: masked)
-    float mx = -INFINITY;
-#pragma unroll 1
-    for (int c = 0; c < 6; ++c) {
-      uint32_t r[32];
-      tmem_ld_32x32b_x32(t_row + c * 32, r);
-      tmem_ld_wait();
+    constexpr uint32_t idesc_s = umma_idesc_bf16(128, kKeys);
+    const uint64_t da = umma_smem_desc_kmajor<128>(smem_u32(sQ + wg * kQBytes));
+    const uint64_t db = umma_smem_desc_kmajor<128>(smem_u32(sK));
 #pragma unroll
-      for (int j = 0; j < 32; ++j) mx = fmaxf(mx, __uint_as_float(r[j]));
-    }
-    {
-      uint32_t r[16];
-      tmem_ld_32x32b_x16(t_row + 192, r);
-      tmem_ld_wait();
-#pragma unroll
-      for (int j = 0; j < kS - 192; ++j) mx = fmaxf(mx, __uint_as_float(r[j]));
-    }
-    const float mxs = mx * kLog2e;
-    float sum = 0.0f;
-#pragma unroll 1
-    for (int c = 0; c < 6; ++c) {
-      uint32_t r[32];
-      tmem_ld_32x32b_x32(t_row + c * 32, r);
-      tmem_ld_wait();
-      float e[32];
-#pragma unroll
-      for (int j = 0; j < 32; ++j) {
-        e[j] = fast_ex2(fmaf(__uint_as_float(r[j]), kLog2e, -mxs));
-        sum += e[j];
-      }
-      uint8_t* blk = p_row + (c >> 1) * kPBytes;
-#pragma unroll
-      for (int g = 0; g < 4; ++g) {
-        const uint32_t chunk = static_cast<uint32_t>((c & 1) * 4 + g);
-        *reinterpret_cast<uint4*>(blk + ((chunk ^ sw) << 4)) =
-            make_uint4(pack_bf16x2(e[8 * g], e[8 * g + 1]), pack_bf16x2(e[8 * g + 2], e[8 * g + 3]),
-                       pack_bf16x2(e[8 * g + 4], e[8 * g + 5]), pack_bf16x2(e[8 * g + 6], e[8 * g + 7]));
-      }
-    }
-    {
-      uint32_t r[16];
-      tmem_ld_32x32b_x16(t_row + 192, r);
-      tmem_ld_wait();
-      float e[16];
-#pragma unroll
-      for (int j = 0; j < 16; ++j) {
-        e[j] = (j < kS - 192) ? fast_ex2(fmaf(__uint_as_float(r[j]), kLog2e, -mxs)) : 0.0f;
-        sum += e[j];
-      }
-      uint8_t* blk = p_row + 3 * kPBytes;
-#pragma unroll
-      for (int g = 0; g < 2; ++g)
-        *reinterpret_cast<uint4*>(blk + ((static_cast<uint32_t>(g) ^ sw) << 4)) =
-            make_uint4(pack_bf16x2(e[8 * g], e[8 * g + 1]), pack_bf16x2(e[8 * g + 2], e[8 * g + 3]),
-                       pack_bf16x2(e[8 * g + 4], e[8 * g + 5]), pack_bf16x2(e[8 * g + 6], e[8 * g + 7]));
-    }
-    const float inv = 1.0f / sum;
-    fence_proxy_async_smem();  // generic-proxy smem writes -> visible to the tensor core (async proxy)
-    tc_fence_before();
-    __syncthreads();
-
-    // ---- O = P V  (128 x 64, K = 208 = 3 x 64 + 16)
-    if (tid == 0) {
-      tc_fence_after();
-      constexpr uint32_t idesc_o = umma_idesc_bf16(128, 64);
-#pragma unroll
-      for (int kb = 0; kb < 4; ++kb) {
-        const uint64_t da = umma_smem_desc_kmajor<128>(smem_u32(sP + kb * kPBytes));
-        const uint64_t db = umma_smem_desc_kmajor<128>(smem_u32(sV + kb * kVBytes));
-        const int nk = kb < 3 ? 4 : 1;
-        for (int k = 0; k < nk; ++k) umma_bf16_ss(tmem_base + kTmemO, da + 2 * k, db + 2 * k, idesc_o, (kb | k) != 0);
-      }
-      umma_commit(bar_o);
-    }
-    mbar_wait(bar_o, mt & 1);
-    tc_fence_after();
-
-    const int t = mt * 128 + tid;
-#pragma unroll 1
-    for (int c = 0; c < 2; ++c) {
-      uint32_t r[32];
-      tmem_ld_32x32b_x32(t_row + kTmemO + c * 32, r);
-      tmem_ld_wait();
-      if (t < kS) {
-        uint4* dst = reinterpret_cast<uint4*>(p.out + ((size_t)b * kS + t) * MDE_VIT_DIM + hd * 64 + c * 32);
-#pragma unroll
-        for (int g = 0; g < 4; ++g)
-          dst[g] = make_uint4(pack_bf16x2(__uint_as_float(r[8 * g]) * inv, __uint_as_float(r[8 * g + 1]) * inv),
-                              pack_bf16x2(__uint_as_float(r[8 * g + 2]) * inv, __uint_as_float(r[8 * g + 3]) * inv),
-                              pack_bf16x2(__uint_as_float(r[8 * g + 4]) * inv, __uint_as_float(r[8 * g + 5]) * inv),
-                              pack_bf16x2(__uint_as_float(r[8 * g + 6]) * inv, __uint_as_float(r[8 * g + 7]) * inv));
-      }
-    }
-    tc_fence_before();
-    __syncthreads();  // S columns and the P tile are free for the next query tile
+    for (int k = 0; k < 4; ++k) umma_bf16_ss(t_tile, da + 2 * k, db + 2 * k, idesc_s, k != 0);
+    umma_commit(&bar_s[wg]);
   }
+  mbar_wait(&bar_s[wg], 0);
+  tc_fence_after();
+
+  // ---- row softmax over the 197 real keys (columns >= 197 are zero-filled K rows: masked)
+  float mx = -INFINITY;
+#pragma unroll 1
+  for (int c = 0; c < 6; ++c) {
+    uint32_t r[32];
+    tmem_ld_32x32b_x32(t_row + c * 32, r);
+    tmem_ld_wait();
+#pragma unroll
+    for (int j = 0; j < 32; ++j) mx = fmaxf(mx, __uint_as_float(r[j]));
+  }
+  {
+    uint32_t r[16];
+    tmem_ld_32x32b_x16(t_row + 192, r);
+    tmem_ld_wait();
+#pragma unroll
+    for (int j = 0; j < kS - 192; ++j) mx = fmaxf(mx, __uint_as_float(r[j]));
+  }
+  const float mxs = mx * kLog2e;
+  float sum = 0.0f;
+#pragma unroll 1
+  for (int c = 0; c < 6; ++c) {
+    uint32_t r[32];
+    tmem_ld_32x32b_x32(t_row + c * 32, r);
+    tmem_ld_wait();
+    float e[32];
+#pragma unroll
+    for (int j = 0; j < 32; ++j) {
+      e[j] = fast_ex2(fmaf(__uint_as_float(r[j]), kLog2e, -mxs));
+      sum += e[j];
+    }
+    uint8_t* blk = p_row + (c >> 1) * kPBytes;
+#pragma unroll
+    for (int g = 0; g < 4; ++g) {
+      const uint32_t chunk = static_cast<uint32_t>((c & 1) * 4 + g);
+      *reinterpret_cast<uint4*>(blk + ((chunk ^ sw) << 4)) =
+          make_uint4(pack_bf16x2(e[8 * g], e[8 * g + 1]), pack_bf16x2(e[8 * g + 2], e[8 * g + 3]),
+                     pack_bf16x2(e[8 * g + 4], e[8 * g + 5]), pack_bf16x2(e[8 * g + 6], e[8 * g + 7]));
+    }
+  }
+  {
+    uint32_t r[16];
+    tmem_ld_32x32b_x16(t_row + 192, r);
+    tmem_ld_wait();
+    float e[16];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+      e[j] = (j < kS - 192) ? fast_ex2(fmaf(__uint_as_float(r[j]), kLog2e, -mxs)) : 0.0f;
+      sum += e[j];
+    }
+    uint8_t* blk = p_row + 3 * kPBytes;
+#pragma unroll
+    for (int g = 0; g < 2; ++g)
+      *reinterpret_cast<uint4*>(blk + ((static_cast<uint32_t>(g) ^ sw) << 4)) =
+          make_uint4(pack_bf16x2(e[8 * g], e[8 * g + 1]), pack_bf16x2(e[8 * g + 2], e[8 * g + 3]),
+                     pack_bf16x2(e[8 * g + 4], e[8 * g + 5]), pack_bf16x2(e[8 * g + 6], e[8 * g + 7]));
+  }
+  const float inv = 1.0f / sum;
+  fence_proxy_async_smem();  // generic-proxy smem writes -> visible to the tensor core (async proxy)
+  tc_fence_before();
+  asm volatile("bar.sync %0, 128;" ::"r"(1 + wg) : "memory");  // this warpgroup only: P complete, S columns dead
+
+  // ---- O = P V  (128 x 64, K = 208 = 3 x 64 + 16), accumulated over the first 64 columns of this tile's S
+  if (wt == 0) {
+    tc_fence_after();
+    constexpr uint32_t idesc_o = umma_idesc_bf16(128, 64);
+#pragma unroll
+    for (int kb = 0; kb < 4; ++kb) {
+      const uint64_t da = umma_smem_desc_kmajor<128>(smem_u32(sP + kb * kPBytes));
+      const uint64_t db = umma_smem_desc_kmajor<128>(smem_u32(sV + kb * kVBytes));
+      const int nk = kb < 3 ? 4 : 1;
+      for (int k = 0; k < nk; ++k) umma_bf16_ss(t_tile, da + 2 * k, db + 2 * k, idesc_o, (kb | k) != 0);
+    }
+    umma_commit(&bar_o[wg]);
+  }
+  mbar_wait(&bar_o[wg], 0);
+  tc_fence_after();
+
+  const int t = wg * 128 + wt;
+#pragma unroll 1
+  for (int c = 0; c < 2; ++c) {
+    uint32_t r[32];
+    tmem_ld_32x32b_x32(t_row + c * 32, r);
+    tmem_ld_wait();
+    if (t < kS) {
+      uint4* dst = reinterpret_cast<uint4*>(p.out + ((size_t)b * kS + t) * MDE_VIT_DIM + hd * 64 + c * 32);
+#pragma unroll
+      for (int g = 0; g < 4; ++g)
+        dst[g] = make_uint4(pack_bf16x2(__uint_as_float(r[8 * g]) * inv, __uint_as_float(r[8 * g + 1]) * inv),
+                            pack_bf16x2(__uint_as_float(r[8 * g + 2]) * inv, __uint_as_float(r[8 * g + 3]) * inv),
+                            pack_bf16x2(__uint_as_float(r[8 * g + 4]) * inv, __uint_as_float(r[8 * g + 5]) * inv),
+                            pack_bf16x2(__uint_as_float(r[8 * g + 6]) * inv, __uint_as_float(r[8 * g + 7]) * inv));
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
   tc_fence_after();
   if (warp == 0) tmem_dealloc(tmem_base, kTmemCols);
 }
@@ -308,7 +311,7 @@ extern "C" int mde_vit_attention(const mde_bf16* q, const mde_bf16* k, const mde
     MDE_CHECK_CUDA(cudaFuncSetAttribute(vit_attn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kAttnSmem));
     attr_set = true;
   }
-  vit_attn_kernel<<<(unsigned)slabs, 128, kAttnSmem, stream>>>(p);
+  vit_attn_kernel<<<(unsigned)slabs, 256, kAttnSmem, stream>>>(p);
   MDE_CHECK_LAUNCH();
   return MDE_OK;
 }

@@ -10,8 +10,10 @@
 // addresses, no data movement.  The hardware swizzle is a function of the shared-memory address bits, so a view that
 // starts at any 16-byte-aligned row of a TMA-written tile stays consistent with how TMA laid the tile out.
 //
-// Warp roles (192 threads): warp 0 TMA producer (weights once, then one halo box per tile and channel chunk), warp 1
-// TMEM allocator + MMA issuer, warps 2..5 epilogue (shared with tc_gemm.cu: bias, folded BN, ELU/sigmoid, bf16/fp16
+// Warp roles (320 threads): warp 0 TMA producer (weights once, then one halo box per tile and channel chunk), warp 1
+// TMEM allocator + MMA issuer, warps 2..9 epilogue — two warps per TMEM lane quarter taking alternate MMA blocks, and for
+// the low-channel layers (small shared-memory footprint) several CTAs per SM: with one warp per scheduler the
+// dependent-issue latency of the ELU/pack/store chain, not HBM, bounded the 16-channel layers (r01g: 113 us for 17 us of traffic) (shared with tc_gemm.cu: bias, folded BN, ELU/sigmoid, bf16/fp16
 // padded-NHWC store with reflected border, or fp32 head).  Two accumulator sets in TMEM overlap the epilogue of tile
 // i with the MMAs of tile i+1.
 #include <stdlib.h>
@@ -26,7 +28,8 @@ namespace mde {
 
 constexpr int kHaloPitch = 64;  // halo tile width in pixels
 constexpr int kHaloTW = 62;     // real outputs per tile row
-constexpr int kHaloThreads = 192;
+constexpr int kHaloThreads = 320;
+constexpr int kHaloEpiWarps = 8;
 constexpr int kHaloMaxStages = 4;
 
 struct alignas(64) HaloParams {
@@ -45,7 +48,7 @@ struct alignas(64) HaloParams {
 };
 
 template <int BLOCK_N, int ROWB>
-__global__ void __launch_bounds__(kHaloThreads, 1) conv_halo_kernel(const __grid_constant__ HaloParams p) {
+__global__ void __launch_bounds__(kHaloThreads, BLOCK_N <= 32 ? 2 : 1) conv_halo_kernel(const __grid_constant__ HaloParams p) {
   constexpr int KC = ROWB / 2;
   constexpr int WB_RAW = BLOCK_N * ROWB;
   constexpr int WB = (WB_RAW + 1023) & ~1023;
@@ -81,7 +84,7 @@ __global__ void __launch_bounds__(kHaloThreads, 1) conv_halo_kernel(const __grid
       }
       for (int a = 0; a < 2; ++a) {
         mbar_init(&tfull_bar[a], 1);
-        mbar_init(&tempty_bar[a], 4);
+        mbar_init(&tempty_bar[a], kHaloEpiWarps);
       }
       mbar_init(w_bar, 1);
       fence_barrier_init();
@@ -155,6 +158,7 @@ __global__ void __launch_bounds__(kHaloThreads, 1) conv_halo_kernel(const __grid
   } else {
     // ------------------------------------------------------------------ epilogue warps
     const int q = warp & 3;
+    const int half = (warp - 2) >> 2;  // the two warps of a lane quarter take alternate MMA blocks
     int acc = 0;
     uint32_t acc_phase = 0;
     for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
@@ -162,7 +166,7 @@ __global__ void __launch_bounds__(kHaloThreads, 1) conv_halo_kernel(const __grid
       const int y0 = (r / p.tiles_x) * p.th, x0 = (r % p.tiles_x) * kHaloTW;
       mbar_wait(&tfull_bar[acc], acc_phase);
       tc_fence_after();
-      for (int j = 0; j < p.nblk; ++j) {
+      for (int j = half; j < p.nblk; j += 2) {
         const int o = 128 * j + q * 32 + lane;
         const int yy = o >> 6, xx = o & 63;
         RowInfo ri;
@@ -201,15 +205,19 @@ __global__ void __launch_bounds__(kHaloThreads, 1) conv_halo_kernel(const __grid
 // ------------------------------------------------------------------------------------ host side
 template <int BLOCK_N, int ROWB>
 static int launch_halo(HaloParams& p, int smem_bytes, cudaStream_t stream) {
-  static int ctas_per_sm = 0;
   static int smem_attr = 0;
-  if (smem_attr < smem_bytes) {
+  if (smem_attr == 0) {
     MDE_CHECK_CUDA(cudaFuncSetAttribute(conv_halo_kernel<BLOCK_N, ROWB>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     MDE_CHECK_CUDA(cudaFuncSetAttribute(conv_halo_kernel<BLOCK_N, ROWB>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
-    smem_attr = 227 * 1024;
+    smem_attr = 1;
   }
-  (void)ctas_per_sm;
-  int grid = sm_count();  // one persistent CTA per SM: the tile loop, the smem ring and the TMEM ring hide latency
+  // persistent CTAs: as many per SM as registers / shared memory / TMEM columns allow (1 for the 64-channel layers)
+  int occ = 1;
+  MDE_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, conv_halo_kernel<BLOCK_N, ROWB>, kHaloThreads, smem_bytes));
+  int tmem_cols = 32;
+  while (tmem_cols < 2 * p.nblk * BLOCK_N) tmem_cols <<= 1;
+  occ = std::max(1, std::min(occ, 512 / tmem_cols));
+  int grid = sm_count() * occ;
   if (grid > p.total_tiles) grid = p.total_tiles;
   conv_halo_kernel<BLOCK_N, ROWB><<<grid, kHaloThreads, smem_bytes, stream>>>(p);
   MDE_CHECK_LAUNCH();

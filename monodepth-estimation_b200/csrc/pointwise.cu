@@ -259,32 +259,51 @@ __global__ void __launch_bounds__(256) tokens_to_grid_kernel(const float* __rest
 
 // ------------------------------------------------------------------ instance norm (encoder.py:167) -> padded NHWC bf16
 // grid (C/64, B), block 256 = 64 channels x 4 row lanes
+// block = 16 channels x 16 position groups: every thread keeps its <= 14 positions in registers (one pass over the data),
+// grid = (C/16, B) blocks so the 4 x 32-image launch fills the machine (the first version ran 128 blocks of 53-step loops).
+constexpr int kInMaxPer = 14;  // ceil(224 / 16)
 __global__ void __launch_bounds__(256) instnorm_kernel(const float* __restrict__ x, int gh, int gw, int C, float eps, bf16* __restrict__ outp,
                                                        int cstride, int coff, bf16* __restrict__ outf) {
   const int G = gh * gw;
-  const int cl = threadIdx.x & 63, rl = threadIdx.x >> 6;
-  const int c = blockIdx.x * 64 + cl, b = blockIdx.y;
+  const int cl = threadIdx.x & 15, rl = threadIdx.x >> 4;
+  const int c = blockIdx.x * 16 + cl, b = blockIdx.y;
   const float* xb = x + (size_t)b * G * C + c;
-  __shared__ float red[4][64];
+  __shared__ float red[16][17];
+  float v[kInMaxPer];
   float s = 0.0f;
-  for (int g = rl; g < G; g += 4) s += xb[(size_t)g * C];
+#pragma unroll
+  for (int i = 0; i < kInMaxPer; ++i) {
+    const int g = rl + 16 * i;
+    v[i] = g < G ? __ldg(xb + (size_t)g * C) : 0.0f;
+    s += v[i];
+  }
   red[rl][cl] = s;
   __syncthreads();
-  const float mean = (red[0][cl] + red[1][cl] + red[2][cl] + red[3][cl]) / (float)G;
+  float mean = 0.0f;
+#pragma unroll
+  for (int i = 0; i < 16; ++i) mean += red[i][cl];
+  mean /= (float)G;
   __syncthreads();
   float q = 0.0f;
-  for (int g = rl; g < G; g += 4) {
-    const float d = xb[(size_t)g * C] - mean;
+#pragma unroll
+  for (int i = 0; i < kInMaxPer; ++i) {
+    const float d = (rl + 16 * i < G) ? v[i] - mean : 0.0f;
     q = fmaf(d, d, q);
   }
   red[rl][cl] = q;
   __syncthreads();
-  const float var = (red[0][cl] + red[1][cl] + red[2][cl] + red[3][cl]) / (float)G;  // biased, like F.instance_norm
+  float var = 0.0f;
+#pragma unroll
+  for (int i = 0; i < 16; ++i) var += red[i][cl];
+  var /= (float)G;  // biased, like F.instance_norm
   const float rstd = 1.0f / sqrtf(var + eps);
   const int H2 = gh + 2, W2 = gw + 2;
-  for (int g = rl; g < G; g += 4) {
-    const bf16 v = __float2bfloat16_rn((xb[(size_t)g * C] - mean) * rstd);
-    if (outf) outf[((size_t)b * G + g) * C + c] = v;
+#pragma unroll
+  for (int i = 0; i < kInMaxPer; ++i) {
+    const int g = rl + 16 * i;
+    if (g >= G) break;
+    const bf16 o = __float2bfloat16_rn((v[i] - mean) * rstd);
+    if (outf) outf[((size_t)b * G + g) * C + c] = o;
     const int y = g / gw, xx = g - y * gw;
     int ys[3], xs[3], ny = 0, nx = 0;
     ys[ny++] = y + 1;
@@ -294,11 +313,10 @@ __global__ void __launch_bounds__(256) instnorm_kernel(const float* __restrict__
     if (xx == 1) xs[nx++] = 0;
     if (xx == gw - 2) xs[nx++] = gw + 1;
     for (int iy = 0; iy < ny; ++iy)
-      for (int ix = 0; ix < nx; ++ix) outp[(((size_t)b * H2 + ys[iy]) * W2 + xs[ix]) * cstride + coff + c] = v;
+      for (int ix = 0; ix < nx; ++ix) outp[(((size_t)b * H2 + ys[iy]) * W2 + xs[ix]) * cstride + coff + c] = o;
   }
 }
 
-// ------------------------------------------------------------------ x2 upsample (align_corners=True) + skip resize + concat
 __device__ __forceinline__ void bf16x8_to_float(const uint4& u, float (&f)[8]) {
   const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
 #pragma unroll
@@ -312,39 +330,42 @@ __device__ __forceinline__ int reflect_idx(int i, int n) {  // ReflectionPad2d(1
   return i < 0 ? -i : (i >= n ? 2 * n - 2 - i : i);
 }
 
+// One block per padded output row (b, Yp): the vertical taps/weights of both sources are block constants, the item loop is
+// 32-bit (the first version spent its time in 64-bit index divisions: issue-bound at 4x the HBM time, r01b profile).
 __global__ void __launch_bounds__(256) upsample_concat_kernel(const bf16* __restrict__ a, int B, int h, int w, int ca, const bf16* __restrict__ s,
                                                               int hs, int ws, int cs, bf16* __restrict__ out) {
-  const int Ho = 2 * h, Wo = 2 * w, ct = ca + cs, groups = ct / 8;
-  const float sya = (float)(h - 1) / (float)(Ho - 1), sxa = (float)(w - 1) / (float)(Wo - 1);
-  const float sys = cs ? (float)(hs - 1) / (float)(Ho - 1) : 0.0f, sxs = cs ? (float)(ws - 1) / (float)(Wo - 1) : 0.0f;
-  const long long total = (long long)B * (Ho + 2) * (Wo + 2) * groups;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
-    const int grp = (int)(i % groups);
-    long long px = i / groups;
-    const int Xp = (int)(px % (Wo + 2));
-    px /= (Wo + 2);
-    const int Yp = (int)(px % (Ho + 2));
-    const int b = (int)(px / (Ho + 2));
-    const int oy = reflect_idx(Yp - 1, Ho), ox = reflect_idx(Xp - 1, Wo);
-    const int c0 = grp * 8;
-    const bf16* src;
-    int y0, y1, x0, x1, sw2, cc, cstr;
+  const int Ho = 2 * h, Wo = 2 * w, ct = ca + cs, groups = ct >> 3, ga = ca >> 3;
+  const int b = blockIdx.x / (Ho + 2), Yp = blockIdx.x - b * (Ho + 2);
+  const int oy = reflect_idx(Yp - 1, Ho);
+  const float sxa = (float)(w - 1) / (float)(Wo - 1);
+  const float sxs = cs ? (float)(ws - 1) / (float)(Wo - 1) : 0.0f;
+  int ya0, ya1, ys0 = 0, ys1 = 0;
+  float lya, lys = 0.0f;
+  src_index_act((float)(h - 1) / (float)(Ho - 1), oy, h, ya0, ya1, lya);
+  if (cs) src_index_act((float)(hs - 1) / (float)(Ho - 1), oy, hs, ys0, ys1, lys);
+  const bf16* a0 = a + ((size_t)b * (h + 2) + ya0 + 1) * (w + 2) * ca;
+  const bf16* a1 = a + ((size_t)b * (h + 2) + ya1 + 1) * (w + 2) * ca;
+  const bf16* s0 = cs ? s + ((size_t)b * (hs + 2) + ys0 + 1) * (ws + 2) * cs : nullptr;
+  const bf16* s1 = cs ? s + ((size_t)b * (hs + 2) + ys1 + 1) * (ws + 2) * cs : nullptr;
+  bf16* orow = out + ((size_t)b * (Ho + 2) + Yp) * (Wo + 2) * ct;
+  const int items = (Wo + 2) * groups;
+  for (int i = threadIdx.x; i < items; i += 256) {
+    const int Xp = i / groups, grp = i - Xp * groups;
+    const int ox = reflect_idx(Xp - 1, Wo);
+    const bf16 *r0, *r1;
+    int x0, x1, cc, cstr;
     float ly, lx;
-    if (c0 < ca) {
-      src_index_act(sya, oy, h, y0, y1, ly);
+    if (grp < ga) {
       src_index_act(sxa, ox, w, x0, x1, lx);
-      src = a + (size_t)b * (h + 2) * (w + 2) * ca;
-      sw2 = w + 2; cc = c0; cstr = ca;
+      r0 = a0; r1 = a1; ly = lya; cc = grp << 3; cstr = ca;
     } else {
-      src_index_act(sys, oy, hs, y0, y1, ly);
       src_index_act(sxs, ox, ws, x0, x1, lx);
-      src = s + (size_t)b * (hs + 2) * (ws + 2) * cs;
-      sw2 = ws + 2; cc = c0 - ca; cstr = cs;
+      r0 = s0; r1 = s1; ly = lys; cc = (grp - ga) << 3; cstr = cs;
     }
-    const uint4 u00 = __ldg(reinterpret_cast<const uint4*>(src + ((size_t)(y0 + 1) * sw2 + x0 + 1) * cstr + cc));
-    const uint4 u01 = __ldg(reinterpret_cast<const uint4*>(src + ((size_t)(y0 + 1) * sw2 + x1 + 1) * cstr + cc));
-    const uint4 u10 = __ldg(reinterpret_cast<const uint4*>(src + ((size_t)(y1 + 1) * sw2 + x0 + 1) * cstr + cc));
-    const uint4 u11 = __ldg(reinterpret_cast<const uint4*>(src + ((size_t)(y1 + 1) * sw2 + x1 + 1) * cstr + cc));
+    const uint4 u00 = __ldg(reinterpret_cast<const uint4*>(r0 + (x0 + 1) * cstr + cc));
+    const uint4 u01 = __ldg(reinterpret_cast<const uint4*>(r0 + (x1 + 1) * cstr + cc));
+    const uint4 u10 = __ldg(reinterpret_cast<const uint4*>(r1 + (x0 + 1) * cstr + cc));
+    const uint4 u11 = __ldg(reinterpret_cast<const uint4*>(r1 + (x1 + 1) * cstr + cc));
     float f00[8], f01[8], f10[8], f11[8], r[8];
     bf16x8_to_float(u00, f00);
     bf16x8_to_float(u01, f01);
@@ -353,7 +374,7 @@ __global__ void __launch_bounds__(256) upsample_concat_kernel(const bf16* __rest
 #pragma unroll
     for (int k = 0; k < 8; ++k)
       r[k] = (1.0f - ly) * ((1.0f - lx) * f00[k] + lx * f01[k]) + ly * ((1.0f - lx) * f10[k] + lx * f11[k]);
-    *reinterpret_cast<uint4*>(out + (((size_t)b * (Ho + 2) + Yp) * (Wo + 2) + Xp) * ct + c0) =
+    *reinterpret_cast<uint4*>(orow + (size_t)i * 8) =
         make_uint4(pack_bf16x2(r[0], r[1]), pack_bf16x2(r[2], r[3]), pack_bf16x2(r[4], r[5]), pack_bf16x2(r[6], r[7]));
   }
 }
@@ -388,45 +409,58 @@ struct MapTable {
   int n;
 };
 
-// grid = (ceil(W/PX/256), ceil(H/kRowsPerBlock), n_maps*B).  A thread owns PX consecutive output columns
-// (their x taps/weights are computed once) and walks kRowsPerBlock output rows; the low-resolution source
-// (<= 224x240 floats per image) is read through L1 (__ldg), so DRAM traffic is the output stream only and
-// every thread keeps several independent 16-byte streaming stores in flight.
+// grid = (ceil(W/PX/256), ceil(H/kRowsPerBlock), n_maps*B).  The block first blends its kRowsPerBlock output rows VERTICALLY
+// at source resolution into shared memory (<= 1024 floats per row, `mul` folded in, one duplicated element at the end so
+// the right tap is always x0+1), then every thread produces PX consecutive pixels per row with two shared-memory reads
+// and one lerp each: ~25 instructions per 16-byte store instead of ~190 (r01b: the 4-tap-per-pixel version was issue-
+// bound at 2.4 TB/s).  DRAM traffic is the output stream only.
 constexpr int kMaxSrcW = 1024;
 constexpr int kRowsPerBlock = 8;
 template <bool VEC4>
 __global__ void __launch_bounds__(256) resize_maps_kernel(const __grid_constant__ MapTable tab, int B, int H, int W, float min_disp, float disp_range) {
   constexpr int PX = VEC4 ? 4 : 1;
+  __shared__ float srow[kRowsPerBlock][kMaxSrcW + 1];
   const int mi = blockIdx.z / B, b = blockIdx.z - mi * B;
   const mde_map_desc& d = tab.m[mi];
   const int ws = d.ws, hs = d.hs;
-  const int xq = blockIdx.x * 256 + threadIdx.x;
-  if (xq * PX >= W) return;
-  const float sw = (float)ws / (float)W, sh = (float)hs / (float)H;
+  const float sh = (float)hs / (float)H;
   const float mul = d.mul;
-  int x0[PX], x1[PX];
-  float lx[PX];
-#pragma unroll
-  for (int j = 0; j < PX; ++j) src_index_acf(sw, xq * PX + j, ws, x0[j], x1[j], lx[j]);
   const float* src = d.src + (size_t)b * hs * ws;
   const int Y0 = blockIdx.y * kRowsPerBlock;
-#pragma unroll 2
-  for (int r = 0; r < kRowsPerBlock; ++r) {
-    const int Y = Y0 + r;
-    if (Y >= H) break;
+  const int nrows = min(kRowsPerBlock, H - Y0);
+  for (int r = 0; r < nrows; ++r) {
     int y0, y1;
     float ly;
-    src_index_acf(sh, Y, hs, y0, y1, ly);
+    src_index_acf(sh, Y0 + r, hs, y0, y1, ly);
     const float* r0 = src + (size_t)y0 * ws;
     const float* r1 = src + (size_t)y1 * ws;
+    const float w0 = (1.0f - ly) * mul, w1 = ly * mul;
+    for (int x = threadIdx.x; x <= ws; x += 256) {
+      const int xc = min(x, ws - 1);
+      srow[r][x] = w0 * __ldg(r0 + xc) + w1 * __ldg(r1 + xc);
+    }
+  }
+  __syncthreads();
+  const int xq = blockIdx.x * 256 + threadIdx.x;
+  if (xq * PX >= W) return;
+  const float sw = (float)ws / (float)W;
+  int x0[PX];
+  float lx[PX];
+#pragma unroll
+  for (int j = 0; j < PX; ++j) {
+    int x1;
+    src_index_acf(sw, xq * PX + j, ws, x0[j], x1, lx[j]);  // x1 == x0 only at the clamped right edge, where srow[x0+1] == srow[x0]
+  }
+  size_t off = ((size_t)b * H + Y0) * W + (size_t)xq * PX;
+#pragma unroll 2
+  for (int r = 0; r < nrows; ++r, off += W) {
     float o[PX], dep[PX];
 #pragma unroll
     for (int j = 0; j < PX; ++j) {
-      const float v00 = __ldg(r0 + x0[j]) * mul, v01 = __ldg(r0 + x1[j]) * mul, v10 = __ldg(r1 + x0[j]) * mul, v11 = __ldg(r1 + x1[j]) * mul;
-      o[j] = (1.0f - ly) * ((1.0f - lx[j]) * v00 + lx[j] * v01) + ly * ((1.0f - lx[j]) * v10 + lx[j] * v11);
-      dep[j] = 1.0f / (min_disp + disp_range * o[j]);
+      const float a = srow[r][x0[j]], c = srow[r][x0[j] + 1];
+      o[j] = fmaf(lx[j], c - a, a);
+      dep[j] = fast_rcp(fmaf(disp_range, o[j], min_disp));
     }
-    const size_t off = ((size_t)b * H + Y) * W + (size_t)xq * PX;
     if constexpr (VEC4) {
       if (d.dst_disp) __stcs(reinterpret_cast<float4*>(d.dst_disp + off), make_float4(o[0], o[1], o[2], o[3]));
       if (d.dst_disp2) __stcs(reinterpret_cast<float4*>(d.dst_disp2 + off), make_float4(o[0], o[1], o[2], o[3]));
@@ -560,8 +594,9 @@ extern "C" int mde_tokens_to_grid_bf16(const float* tokens, int B, int strip_cls
 extern "C" int mde_instnorm_nhwc(const float* x, int B, int gh, int gw, int C, float eps, mde_bf16* out_padded, int out_cstride, int out_coff,
                                  mde_bf16* out_flat, mde_stream_t stream) {
   MDE_CHECK_ARG(x && out_padded && B > 0 && gh >= 3 && gw >= 3, "mde_instnorm_nhwc: bad arguments");
-  MDE_CHECK_ARG(C % 64 == 0 && out_coff + C <= out_cstride, "mde_instnorm_nhwc: C must be a multiple of 64 and fit the output stride");
-  instnorm_kernel<<<dim3(C / 64, B), 256, 0, stream>>>(x, gh, gw, C, eps, reinterpret_cast<bf16*>(out_padded), out_cstride, out_coff,
+  MDE_CHECK_ARG(C % 16 == 0 && out_coff + C <= out_cstride, "mde_instnorm_nhwc: C must be a multiple of 16 and fit the output stride");
+  MDE_CHECK_ARG(gh * gw <= 16 * kInMaxPer, "mde_instnorm_nhwc: grid %dx%d exceeds %d positions", gh, gw, 16 * kInMaxPer);
+  instnorm_kernel<<<dim3(C / 16, B), 256, 0, stream>>>(x, gh, gw, C, eps, reinterpret_cast<bf16*>(out_padded), out_cstride, out_coff,
                                                        reinterpret_cast<bf16*>(out_flat));
   MDE_CHECK_LAUNCH();
   return MDE_OK;
@@ -572,8 +607,8 @@ extern "C" int mde_upsample2x_concat_nhwc(const mde_bf16* a, int B, int h, int w
   MDE_CHECK_ARG(a && out && B > 0 && h >= 2 && w >= 2 && ca > 0 && ca % 8 == 0, "mde_upsample2x_concat_nhwc: bad arguments");
   MDE_CHECK_ARG((s == nullptr) == (cs == 0) && cs % 8 == 0, "mde_upsample2x_concat_nhwc: skip tensor / cs mismatch");
   if (s) MDE_CHECK_ARG(hs >= 2 && ws >= 2, "mde_upsample2x_concat_nhwc: bad skip size");
-  const long long total = (long long)B * (2 * h + 2) * (2 * w + 2) * ((ca + cs) / 8);
-  upsample_concat_kernel<<<grid_for(total, 256), 256, 0, stream>>>(reinterpret_cast<const bf16*>(a), B, h, w, ca, reinterpret_cast<const bf16*>(s),
+  MDE_CHECK_ARG((long long)B * (2 * h + 2) < (1ll << 31), "mde_upsample2x_concat_nhwc: too many rows");
+  upsample_concat_kernel<<<B * (2 * h + 2), 256, 0, stream>>>(reinterpret_cast<const bf16*>(a), B, h, w, ca, reinterpret_cast<const bf16*>(s),
                                                                    hs, ws, cs, reinterpret_cast<bf16*>(out));
   MDE_CHECK_LAUNCH();
   return MDE_OK;

@@ -65,8 +65,8 @@ class Workspace:
         self.vt = z(B * 12 * 64 * L.VT_PITCH)
         self.attn = e(M, 768)
         self.mlp = e(M, 3072)
-        self.grid_a = e(B * G, 768)
-        self.reduced = e(B * G, 256, dt=F32)
+        self.grid_a = [e(B * G, 768) for _ in range(4)]  # per tap: the side stream works on tap i while the ViT runs on
+        self.reduced = [e(B * G, 256, dt=F32) for _ in range(4)]
         c0 = 320 if enhanced else 256  # feature 0 carries the 3 rgb + 61 zero channels of the refinement conv
         self.feats = [z(B, gh + 2, gw + 2, c0)] + [e(B, gh + 2, gw + 2, 256) for _ in range(3)]
         # decoder
@@ -84,7 +84,7 @@ class Workspace:
         self.d_x3b = e(B, h + 2, w + 2, 16)  # mars_adapt output
         if enhanced:
             self.flat = [None, e(B * G, 256), e(B * G, 256), None]
-            self.qkv = e(B * G, 384, dt=F32)
+            self.qkv = [None, e(B * G, 384, dt=F32), e(B * G, 384, dt=F32), None]
             self.enh = [None, e(B, gh + 2, gw + 2, 256), e(B, gh + 2, gw + 2, 256), None]
             self.u1, self.u2 = e(B, gh + 2, gw + 2, 128), e(B, gh + 2, gw + 2, 128)
             self.r1, self.r2 = e(B, gh + 2, gw + 2, 256), e(B, gh + 2, gw + 2, 128)
@@ -106,6 +106,9 @@ class DepthEngine:
         # CUDA graphs remove ~150 launch latencies per forward; MDE_NO_GRAPH=1 runs eagerly (debugging)
         self.use_graph = os.environ.get("MDE_NO_GRAPH", "0") != "1"
         self.launches_per_forward = 0
+        # MDE_NO_OVERLAP=1 keeps every launch on one stream (A/B testing)
+        self.overlap = os.environ.get("MDE_NO_OVERLAP", "0") != "1"
+        self.side = None
 
     # ------------------------------------------------------------------ weights
     def weights(self):
@@ -148,7 +151,7 @@ class DepthEngine:
             n += 1
         return n
 
-    def _vit(self, ws, w, want=None):
+    def _vit(self, ws, w, want=None, on_tap=None):
         enc, B = w["enc"], ws.B
         n = 0
         ops.gemm(ws.patches, enc["patch_w"], enc["patch_b"], L.EPI_PATCH_EMBED, ws.xa, enc["pos"], enc["cls"])
@@ -173,34 +176,47 @@ class DepthEngine:
                 want["block0_q"] = ws.q.clone()
                 want["block0_attn"] = ws.attn.clone()
                 want["block0_out"] = x_out.clone()
+            if on_tap is not None and i in HOOKS:
+                n += on_tap(HOOKS.index(i))
             x_in = x_out
         return n
 
-    def _features(self, ws, w):
+    def _feature(self, ws, w, i):
+        """encoder.py:147-168 for tap i: token->grid rows, 1x1 reduce, instance norm; enhanced: + the per-feature extras
+        (attention block on features 1/2, uncertainty + refinement heads on feature 0) and the decoder skip conv that
+        consumes this feature (decoder.py:126-137) — everything that depends on this tap only."""
         enc, B, gh, gw = w["enc"], ws.B, ws.gh, ws.gw
         G = gh * gw
-        n = 0
-        for i in range(4):
-            ops.tokens_to_grid(ws.taps[i], B, ws.strip, G, ws.grid_a)
-            rw, rb = enc["reduce"][i]
-            ops.gemm(ws.grid_a, rw, rb, L.EPI_BIAS_F32, ws.reduced)
-            flat = ws.flat[i] if self.enhanced else None
-            ops.instnorm_nhwc(ws.reduced, B, gh, gw, 256, 1e-5, ws.feats[i], 0, flat)
-            n += 3
+        ops.tokens_to_grid(ws.taps[i], B, ws.strip, G, ws.grid_a[i])
+        rw, rb = enc["reduce"][i]
+        ops.gemm(ws.grid_a[i], rw, rb, L.EPI_BIAS_F32, ws.reduced[i])
+        flat = ws.flat[i] if self.enhanced else None
+        ops.instnorm_nhwc(ws.reduced[i], B, gh, gw, 256, 1e-5, ws.feats[i], 0, flat)
+        n = 3
+        feat = ws.feats[i]
+        if self.enhanced:
+            n += self._enhanced_feature(ws, w, i)
+            if i in (1, 2):
+                feat = ws.enh[i]
+        if i < 3:
+            lvl = 2 - i  # decoder level whose skip branch reads feature i
+            self._conv(feat, gh, gw, 256, w["dec"][f"skip_{lvl}"], DEC_CH[lvl + 1], L.ACT_ELU, out=ws.d_s[lvl])
+            n += 1
         return n
 
     def _conv(self, inp, h, w_, cin, wb, cout, act, out=None, out_f32=None, ksize=3, pad=L.PAD_REFLECT):
         ops.conv_nhwc(inp, h, w_, cin, wb[0], wb[1], cout, ksize, pad, act, out_bf16=out, out_f32=out_f32)
 
-    def _enhanced_pre_decoder(self, ws, w):
+    def _enhanced_feature(self, ws, w, i):
         """enhanced_model.py:183-196: attention on features 1,2; uncertainty + refinement heads on feature 0."""
         enh, B, gh, gw = w["enh"], ws.B, ws.gh, ws.gw
-        n = 0
-        for i in (1, 2):
+        if i in (1, 2):
             pw, pb, gamma = enh["attn"][str(i)]
-            ops.gemm(ws.flat[i], pw, pb, L.EPI_BIAS_F32, ws.qkv)
-            ops.spatial_attention(ws.flat[i], ws.qkv, B, gh, gw, gamma, ws.enh[i])
-            n += 2
+            ops.gemm(ws.flat[i], pw, pb, L.EPI_BIAS_F32, ws.qkv[i])
+            ops.spatial_attention(ws.flat[i], ws.qkv[i], B, gh, gw, gamma, ws.enh[i])
+            return 2
+        if i != 0:
+            return 0
         f0 = ws.feats[0]
         self._conv(f0, gh, gw, 256, enh["unc1"], 128, L.ACT_ELU, out=ws.u1, pad=L.PAD_ZERO)
         self._conv(ws.u1, gh, gw, 128, enh["unc2"], 128, L.ACT_ELU, out=ws.u2, pad=L.PAD_ZERO)
@@ -208,7 +224,7 @@ class DepthEngine:
         self._conv(f0, gh, gw, 320, enh["ref1"], 256, L.ACT_ELU, out=ws.r1, pad=L.PAD_ZERO)
         self._conv(ws.r1, gh, gw, 256, enh["ref2"], 128, L.ACT_ELU, out=ws.r2, pad=L.PAD_ZERO)
         self._conv(ws.r2, gh, gw, 128, enh["ref3"], 1, L.ACT_NONE, out_f32=ws.refn, ksize=1)
-        return n + 6
+        return 6
 
     def _decoder(self, ws, w, feats):
         """decoder.py:90-173."""
@@ -220,11 +236,7 @@ class DepthEngine:
         for i in range(4):
             ci, co = DEC_CH[i], DEC_CH[i + 1]
             self._conv(x, h, w_, ci, dec[f"upconv_{i}_0"], co, L.ACT_ELU, out=ws.d_a[i])
-            s = None
-            if i < 3:
-                s = ws.d_s[i]
-                self._conv(feats[2 - i], gh, gw, 256, dec[f"skip_{i}"], co, L.ACT_ELU, out=s)
-                n += 1
+            s = ws.d_s[i] if i < 3 else None  # skip branch: computed with its feature (_feature)
             ops.upsample2x_concat(ws.d_a[i], h, w_, s, gh, gw, ws.d_cat[i])
             h, w_ = 2 * h, 2 * w_
             self._conv(ws.d_cat[i], h, w_, ws.d_cat[i].shape[-1], dec[f"upconv_{i}_1"], co, L.ACT_ELU, out=ws.d_x[i])
@@ -239,12 +251,26 @@ class DepthEngine:
         return n
 
     def _body(self, ws, w, scale, want=None):
-        """Everything between the input kernels and the output kernel (graph-captured)."""
-        n = self._vit(ws, w, want)
-        n += self._features(ws, w)
+        """Everything between the input kernels and the output kernel (graph-captured).  The work that depends on one tap
+        only (features 0..2 and their consumers) runs on a side stream, forked after the hooked ViT layer and joined before
+        the decoder: those launches are small (210 positions per image) and fill the tail of the persistent GEMMs."""
+        main = torch.cuda.current_stream()
+        counts = []
+
+        def on_tap(i):
+            if i == 3 or self.side is None:
+                return self._feature(ws, w, i)
+            self.side.wait_stream(main)  # fork (first use) / order after the layer that produced tap i
+            with torch.cuda.stream(self.side):
+                counts.append(self._feature(ws, w, i))
+            return 0
+
+        n = self._vit(ws, w, want, on_tap)
+        if self.side is not None:
+            main.wait_stream(self.side)  # join
+        n += sum(counts)
         feats = ws.feats
         if self.enhanced:
-            n += self._enhanced_pre_decoder(ws, w)
             feats = [ws.feats[0], ws.enh[1], ws.enh[2], ws.feats[3]]
         n += self._decoder(ws, w, feats)
         if self.enhanced:
@@ -292,6 +318,8 @@ class DepthEngine:
         B, _, H0, W0 = x.shape
         with torch.cuda.device(dev):
             ws = self.workspace(dev, B, H0, W0)
+            if self.overlap and (self.side is None or self.side.device != dev):
+                self.side = torch.cuda.Stream(device=dev)
             n = self._pre(ws, w, x)
             if want is not None or not self.use_graph:
                 n += self._body(ws, w, scale, want)
