@@ -13,8 +13,8 @@
 // Warp roles (320 threads): warp 0 TMA producer (weights once, then one halo box per tile and channel chunk), warp 1
 // TMEM allocator + MMA issuer, warps 2..9 epilogue — two warps per TMEM lane quarter taking alternate MMA blocks, and for
 // the low-channel layers (small shared-memory footprint) several CTAs per SM: with one warp per scheduler the
-// dependent-issue latency of the ELU/pack/store chain, not HBM, bounded the 16-channel layers (r01g: 113 us for 17 us of traffic) (shared with tc_gemm.cu: bias, folded BN, ELU/sigmoid, bf16/fp16
-// padded-NHWC store with reflected border, or fp32 head).  Two accumulator sets in TMEM overlap the epilogue of tile
+// dependent-issue latency of the ELU/pack/store chain, not HBM, bounded the 16-channel layers (r01g: 113 us for 17 us of traffic).  The epilogue itself is shared with tc_gemm.cu: bias,
+// folded BN, ELU/sigmoid, bf16/fp16 padded-NHWC store with reflected border, or fp32 head.  Two accumulator sets in TMEM overlap the epilogue of tile
 // i with the MMAs of tile i+1.
 #include <stdlib.h>
 
@@ -44,7 +44,7 @@ struct alignas(64) HaloParams {
   int ldo;
   const void* aux0;
   const void* aux1;
-  int cout, out_cstride, out_coff, f16;
+  int cout, out_cstride, out_coff, f16, st32;
 };
 
 template <int BLOCK_N, int ROWB>
@@ -304,6 +304,7 @@ int launch_conv_halo(int f16, const void* in, int B, int h, int w, int cin, int 
   p.out_cstride = out_cstride;
   p.out_coff = out_coff;
   p.f16 = f16;
+  p.st32 = out_bf16 && cout % 16 == 0 && ((uintptr_t)out_bf16 % 32 == 0) && (out_cstride * 2) % 32 == 0 && (out_coff * 2) % 32 == 0;
   const int smem_bytes = 1024 + weights_bytes + stages * stage_bytes + 1024 + 256;
 #define MDE_HALO_CASE(BN, RB) \
   if (block_n == BN && rowb == RB) return launch_halo<BN, RB>(p, smem_bytes, stream);

@@ -278,6 +278,14 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
   return *reinterpret_cast<uint32_t*>(&v);
 }
 
+// 32-byte global store (sm_100: 256-bit LSU path).  One instruction per 32 contiguous bytes halves the number of
+// cache-line requests of a row-per-thread epilogue, which is what bounds it.  `p` must be 32-byte aligned.
+__device__ __forceinline__ void st_global_v8(void* p, const uint4& a, const uint4& b) {
+  asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(p), "r"(a.x), "r"(a.y), "r"(a.z), "r"(a.w), "r"(b.x), "r"(b.y),
+               "r"(b.z), "r"(b.w)
+               : "memory");
+}
+
 // two floats -> packed fp16x2 (lo in the low half), round-to-nearest, saturating to +-65504 instead of inf
 __device__ __forceinline__ uint32_t pack_f16x2(float lo, float hi) {
   uint32_t r;

@@ -1,7 +1,7 @@
 // Fused epilogues shared by the tensor-core kernels (tc_gemm.cu: 1-CTA GEMM + implicit-GEMM conv,
 // tc_gemm2.cu: 2-CTA GEMM).  One thread owns one accumulator row (one TMEM lane) and NCOL consecutive
 // fp32 columns per call; `P` is the kernel's parameter block (fields epi, act, bias, out, ldo, aux0,
-// aux1, cout, h, w, out_cstride, out_coff, f16).
+// aux1, cout, h, w, out_cstride, out_coff, f16, st32).
 #pragma once
 #include "common.h"
 #include "ptx.cuh"
@@ -138,9 +138,17 @@ __device__ __forceinline__ void epilogue_chunk(const P& p, float (&v)[NCOL], int
       for (int iy = 0; iy < ny; ++iy)
         for (int ix = 0; ix < nx; ++ix) {
           uint4* dst = reinterpret_cast<uint4*>(obase + (((size_t)ri.b * H2 + ys[iy]) * W2 + xs[ix]) * p.out_cstride);
+          if (p.st32) {  // 32-byte stores (host checked alignment and cout % 16 == 0)
 #pragma unroll
-          for (int j = 0; j < NCOL / 8; ++j)
-            if (8 * j < nv) dst[j] = make_uint4(pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
+            for (int j = 0; j < NCOL / 16; ++j)
+              if (16 * j < nv)
+                st_global_v8(dst + 2 * j, make_uint4(pk[8 * j], pk[8 * j + 1], pk[8 * j + 2], pk[8 * j + 3]),
+                             make_uint4(pk[8 * j + 4], pk[8 * j + 5], pk[8 * j + 6], pk[8 * j + 7]));
+          } else {
+#pragma unroll
+            for (int j = 0; j < NCOL / 8; ++j)
+              if (8 * j < nv) dst[j] = make_uint4(pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
+          }
         }
       break;
     }

@@ -41,7 +41,8 @@ struct alignas(64) TcParams {
   const void* aux0;
   const void* aux1;
   int cout, out_cstride, out_coff;
-  int f16;  // operands (and bf16-slot outputs) are fp16 instead of bf16
+  int f16;   // operands (and bf16-slot outputs) are fp16 instead of bf16
+  int st32;  // conv bf16/fp16 output: 32-byte stores are legal (alignment, cout % 16 == 0)
 };
 
 // co-resident CTAs per SM the register budget is compiled for (small tiles hide latency with more CTAs)
@@ -419,6 +420,7 @@ static int conv_nhwc_impl(int f16, const mde_bf16* in, int B, int h, int w, int 
   p.out_cstride = out_cstride;
   p.out_coff = out_coff;
   p.f16 = f16;
+  p.st32 = out_bf16 && cout % 16 == 0 && ((uintptr_t)out_bf16 % 32 == 0) && (out_cstride * 2) % 32 == 0 && (out_coff * 2) % 32 == 0;
   return dispatch_tc(p, block_n, rowb, stream);
 }
 

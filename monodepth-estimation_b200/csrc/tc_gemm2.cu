@@ -61,7 +61,7 @@ struct alignas(64) Tc2Params {
   int ldo;
   const void* aux0;
   const void* aux1;
-  int cout, h, w, out_cstride, out_coff, f16;
+  int cout, h, w, out_cstride, out_coff, f16, st32;
 };
 
 struct Item {
