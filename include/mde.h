@@ -46,7 +46,7 @@ enum mde_gemm_epilogue {
   MDE_EPI_BIAS_RESID_F32 = 2, /* out f32[M,ldo]   = acc + bias + resid[M,ldo] (tv:115,120)  */
   MDE_EPI_BIAS_F32 = 3,       /* out f32[M,ldo]   = acc + bias                              */
   MDE_EPI_PATCH_EMBED = 4,    /* rows (b,p) -> token row b*197+1+p, + bias + pos_emb; also writes the CLS rows */
-  MDE_EPI_QKV_SPLIT = 5       /* q*(1/8), k -> [B*12][197][64]; v -> transposed [B*12][64][MDE_VT_PITCH] */
+  MDE_EPI_QKV_SPLIT = 5       /* q*(1/8), k -> token-major [B*197][768]; v -> transposed [B*12][64][MDE_VT_PITCH] */
 };
 
 enum mde_activation { MDE_ACT_NONE = 0, MDE_ACT_ELU = 1, MDE_ACT_SIGMOID = 2 };
@@ -107,7 +107,7 @@ int mde_layernorm_bf16(const float* x, int rows, int dim, const float* gamma, co
 
 /* ---- ViT self-attention core (tv:113, nn.MultiheadAttention, 12 heads x 64, S=197) -----
  * softmax(q k^T) v per (image, head) with q pre-scaled by 1/8; tcgen05 for both products,
- * softmax fused in between.  q,k: [B*12][197][64]; vt: [B*12][64][MDE_VT_PITCH];
+ * softmax fused in between.  q,k: token-major [B*197][768] (head h in columns 64h..64h+63); vt: [B*12][64][MDE_VT_PITCH];
  * out bf16 [B*197][768] (token-major, head h in columns 64h..64h+63). */
 int mde_vit_attention(const mde_bf16* q, const mde_bf16* k, const mde_bf16* vt, int B, mde_bf16* out,
                       mde_stream_t stream);

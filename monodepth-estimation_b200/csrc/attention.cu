@@ -1,6 +1,6 @@
 // Attention kernels.
 //  * vit_attn_kernel   — tv:113 nn.MultiheadAttention core for ViT-B/16 (S=197, 12 heads x 64):
-//    one CTA per (image, head); Q/K/V^T tiles arrive by TMA (out-of-bounds rows zero-filled, so
+//    one CTA per (image, head); Q/K (token-major, 4-D box) and V^T tiles arrive by TMA (out-of-bounds rows zero-filled, so
 //    the 197-token sequence needs no padded copy), S = Q K^T and O = P V run on tcgen05 with
 //    the accumulators in TMEM, and the softmax is fused in between: each of the 128 threads owns
 //    one query row (one TMEM lane), reads its scores with tcgen05.ld, and writes the
@@ -75,9 +75,9 @@ __global__ void __launch_bounds__(256, 1) vit_attn_kernel(const __grid_constant_
 
   if (tid == 0) {
     mbar_expect_tx(bar_load, 2 * kQBytes + kKBytes + 4 * kVBytes);
-    tma_load_3d(sQ, &p.tmQ, bar_load, 0, 0, slab);
-    tma_load_3d(sQ + kQBytes, &p.tmQ, bar_load, 0, 128, slab);
-    tma_load_3d(sK, &p.tmK, bar_load, 0, 0, slab);
+    tma_load_4d(sQ, &p.tmQ, bar_load, 0, hd, 0, b);  // q, k are token-major [B][197][12][64]: box = {64 d, 1 head, rows, 1 image}
+    tma_load_4d(sQ + kQBytes, &p.tmQ, bar_load, 0, hd, 128, b);
+    tma_load_4d(sK, &p.tmK, bar_load, 0, hd, 0, b);
 #pragma unroll
     for (int j = 0; j < 4; ++j) tma_load_3d(sV + j * kVBytes, &p.tmV, bar_load, 64 * j, 0, slab);
   }
@@ -288,13 +288,14 @@ extern "C" int mde_vit_attention(const mde_bf16* q, const mde_bf16* k, const mde
   memset(&p, 0, sizeof(p));
   const uint64_t slabs = (uint64_t)B * MDE_VIT_HEADS;
   {
-    const uint64_t dims[3] = {64, (uint64_t)kS, slabs};
-    const uint64_t strides[2] = {128, (uint64_t)kS * 128};
-    const uint32_t boxq[3] = {64, 128, 1};
-    const uint32_t boxk[3] = {64, (uint32_t)kKeys, 1};
-    int rc = encode_tmap_bf16(&p.tmQ, q, 3, dims, strides, boxq, 128);
+    // token-major q / k: element (d, head, t, b) at ((b*197 + t)*768 + head*64 + d); rows t >= 197 of the box are zero-filled
+    const uint64_t dims[4] = {64, MDE_VIT_HEADS, (uint64_t)kS, (uint64_t)B};
+    const uint64_t strides[3] = {128, (uint64_t)MDE_VIT_DIM * 2, (uint64_t)kS * MDE_VIT_DIM * 2};
+    const uint32_t boxq[4] = {64, 1, 128, 1};
+    const uint32_t boxk[4] = {64, 1, (uint32_t)kKeys, 1};
+    int rc = encode_tmap_bf16(&p.tmQ, q, 4, dims, strides, boxq, 128);
     if (rc != MDE_OK) return rc;
-    rc = encode_tmap_bf16(&p.tmK, k, 3, dims, strides, boxk, 128);
+    rc = encode_tmap_bf16(&p.tmK, k, 4, dims, strides, boxk, 128);
     if (rc != MDE_OK) return rc;
   }
   {

@@ -459,7 +459,7 @@ __global__ void __launch_bounds__(256) resize_maps_kernel(const __grid_constant_
     for (int j = 0; j < PX; ++j) {
       const float a = srow[r][x0[j]], c = srow[r][x0[j] + 1];
       o[j] = fmaf(lx[j], c - a, a);
-      dep[j] = fast_rcp(fmaf(disp_range, o[j], min_disp));
+      dep[j] = d.dst_depth ? fast_rcp(fmaf(disp_range, o[j], min_disp)) : 0.0f;
     }
     if constexpr (VEC4) {
       if (d.dst_disp) __stcs(reinterpret_cast<float4*>(d.dst_disp + off), make_float4(o[0], o[1], o[2], o[3]));
@@ -469,6 +469,72 @@ __global__ void __launch_bounds__(256) resize_maps_kernel(const __grid_constant_
       if (d.dst_disp) d.dst_disp[off] = o[0];
       if (d.dst_disp2) d.dst_disp2[off] = o[0];
       if (d.dst_depth) d.dst_depth[off] = dep[0];
+    }
+  }
+}
+
+// Fast variant for >= 3x horizontal upscaling with W % 4 == 0 (every 1024-px configuration: sources are <= 240 wide).
+// The four consecutive pixels of a thread then fall into at most two adjacent source intervals, so each pixel is
+// wa*s[i] + wb*s[i+1] + wc*s[i+2] with per-thread constant weights (one of wa, wc is zero): 3 shared-memory reads and 12
+// FP instructions per 16-byte store, rows fully unrolled so every address is base + immediate.
+__global__ void __launch_bounds__(256) resize_maps_up3_kernel(const __grid_constant__ MapTable tab, int B, int H, int W, float min_disp, float disp_range) {
+  __shared__ float srow[kRowsPerBlock][kMaxSrcW + 2];
+  const int mi = blockIdx.z / B, b = blockIdx.z - mi * B;
+  const mde_map_desc& d = tab.m[mi];
+  const int ws = d.ws, hs = d.hs;
+  const float sh = (float)hs / (float)H;
+  const float mul = d.mul;
+  const float* src = d.src + (size_t)b * hs * ws;
+  const int Y0 = blockIdx.y * kRowsPerBlock;
+  const int nrows = min(kRowsPerBlock, H - Y0);
+  for (int r = 0; r < nrows; ++r) {
+    int y0, y1;
+    float ly;
+    src_index_acf(sh, Y0 + r, hs, y0, y1, ly);
+    const float* r0 = src + (size_t)y0 * ws;
+    const float* r1 = src + (size_t)y1 * ws;
+    const float w0 = (1.0f - ly) * mul, w1 = ly * mul;
+    for (int x = threadIdx.x; x < ws + 2; x += 256) {
+      const int xc = min(x, ws - 1);
+      srow[r][x] = w0 * __ldg(r0 + xc) + w1 * __ldg(r1 + xc);
+    }
+  }
+  __syncthreads();
+  const int xq = blockIdx.x * 256 + threadIdx.x;
+  if (xq * 4 >= W) return;
+  const float sw = (float)ws / (float)W;
+  int xb, x1;
+  float l0;
+  src_index_acf(sw, xq * 4, ws, xb, x1, l0);
+  float wa[4], wb[4], wc[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    int xj;
+    float lj;
+    src_index_acf(sw, xq * 4 + j, ws, xj, x1, lj);
+    const bool same = xj == xb;  // else xj == xb + 1 (3 * sw < 1)
+    wa[j] = same ? 1.0f - lj : 0.0f;
+    wb[j] = same ? lj : 1.0f - lj;
+    wc[j] = same ? 0.0f : lj;
+  }
+  const float* sp = &srow[0][xb];
+  const size_t off0 = ((size_t)b * H + Y0) * W + (size_t)xq * 4;
+  float* dd = d.dst_disp ? d.dst_disp + off0 : nullptr;
+  float* d2 = d.dst_disp2 ? d.dst_disp2 + off0 : nullptr;
+  float* dz = d.dst_depth ? d.dst_depth + off0 : nullptr;
+#pragma unroll
+  for (int r = 0; r < kRowsPerBlock; ++r) {
+    if (r < nrows) {
+      const float a = sp[r * (kMaxSrcW + 2)], bb = sp[r * (kMaxSrcW + 2) + 1], c = sp[r * (kMaxSrcW + 2) + 2];
+      float o[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) o[j] = fmaf(wc[j], c, fmaf(wb[j], bb, wa[j] * a));
+      if (dd) __stcs(reinterpret_cast<float4*>(dd + (size_t)r * W), make_float4(o[0], o[1], o[2], o[3]));
+      if (d2) __stcs(reinterpret_cast<float4*>(d2 + (size_t)r * W), make_float4(o[0], o[1], o[2], o[3]));
+      if (dz)
+        __stcs(reinterpret_cast<float4*>(dz + (size_t)r * W),
+               make_float4(fast_rcp(fmaf(disp_range, o[0], min_disp)), fast_rcp(fmaf(disp_range, o[1], min_disp)),
+                           fast_rcp(fmaf(disp_range, o[2], min_disp)), fast_rcp(fmaf(disp_range, o[3], min_disp))));
     }
   }
 }
@@ -636,7 +702,11 @@ extern "C" int mde_resize_maps(const mde_map_desc* maps, int n_maps, int B, int 
   }
   const float range = max_disp - min_disp;
   MDE_CHECK_ARG(H <= 65535 && (long long)n_maps * B <= 65535, "mde_resize_maps: H and n_maps*B must be <= 65535");
-  if (vec) {
+  bool up3 = vec;
+  for (int i = 0; i < n_maps; ++i) up3 = up3 && 3 * maps[i].ws < W;
+  if (up3) {
+    resize_maps_up3_kernel<<<dim3(ceil_div(W / 4, 256), ceil_div(H, kRowsPerBlock), n_maps * B), 256, 0, stream>>>(tab, B, H, W, min_disp, range);
+  } else if (vec) {
     resize_maps_kernel<true><<<dim3(ceil_div(W / 4, 256), ceil_div(H, kRowsPerBlock), n_maps * B), 256, 0, stream>>>(tab, B, H, W, min_disp, range);
   } else {
     resize_maps_kernel<false><<<dim3(ceil_div(W, 256), ceil_div(H, kRowsPerBlock), n_maps * B), 256, 0, stream>>>(tab, B, H, W, min_disp, range);

@@ -91,7 +91,7 @@ __device__ __forceinline__ void epilogue_chunk(const P& p, float (&v)[NCOL], int
       if (which < 2) {
         const float sc = which == 0 ? 0.125f : 1.0f;  // 1/sqrt(64) folded into q (exact in bf16)
         bf16* base = reinterpret_cast<bf16*>(which == 0 ? p.out : const_cast<void*>(p.aux0));
-        uint4* dst = reinterpret_cast<uint4*>(base + (slab * MDE_VIT_SEQ + t) * 64 + d0);
+        uint4* dst = reinterpret_cast<uint4*>(base + (size_t)ri.m * MDE_VIT_DIM + c);  // token-major [B*197][768]
 #pragma unroll
         for (int j = 0; j < NCOL / 8; ++j)
           dst[j] = make_uint4(pack_bf16x2(v[8 * j] * sc, v[8 * j + 1] * sc), pack_bf16x2(v[8 * j + 2] * sc, v[8 * j + 3] * sc),

@@ -268,6 +268,26 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(k2Threads, 1) tc_gem
             tmem_ld_wait();
             const float4* bp = reinterpret_cast<const float4*>(p.bias + n0);
             const bool gelu = p.epi == MDE_EPI_BIAS_GELU_BF16;
+            const int which = p.epi == MDE_EPI_QKV_SPLIT ? n0 / MDE_VIT_DIM : 0;  // 0 q, 1 k, 2 v (uniform per 64-column chunk)
+            if (which == 2) {
+              // V goes out transposed, vt[b*12+head][d][token]: consecutive lanes hold consecutive tokens -> coalesced 2-byte stores
+              const int m = row0 + lane;
+              if (m < p.M) {
+                const int bb = m / MDE_VIT_SEQ, t = m - bb * MDE_VIT_SEQ;
+                const int cc = n0 - 2 * MDE_VIT_DIM;  // = head * 64
+                bf16* dst = reinterpret_cast<bf16*>(const_cast<void*>(p.aux1)) + ((size_t)bb * MDE_VIT_DIM + cc) * MDE_VT_PITCH + t;
+#pragma unroll
+                for (int j = 0; j < 16; ++j) {
+                  const float4 b4 = __ldg(bp + j);
+                  dst[(size_t)(4 * j) * MDE_VT_PITCH] = __float2bfloat16_rn(__uint_as_float(raw[4 * j]) + b4.x);
+                  dst[(size_t)(4 * j + 1) * MDE_VT_PITCH] = __float2bfloat16_rn(__uint_as_float(raw[4 * j + 1]) + b4.y);
+                  dst[(size_t)(4 * j + 2) * MDE_VT_PITCH] = __float2bfloat16_rn(__uint_as_float(raw[4 * j + 2]) + b4.z);
+                  dst[(size_t)(4 * j + 3) * MDE_VT_PITCH] = __float2bfloat16_rn(__uint_as_float(raw[4 * j + 3]) + b4.w);
+                }
+              }
+              continue;  // nothing staged, no TMA store for this chunk (g is advanced by the loop header)
+            }
+            const float qs = (p.epi == MDE_EPI_QKV_SPLIT && which == 0) ? 0.125f : 1.0f;  // 1/sqrt(64) folded into q
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
               const float4 b0 = __ldg(bp + 2 * j), b1 = __ldg(bp + 2 * j + 1);
@@ -278,6 +298,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(k2Threads, 1) tc_gem
 #pragma unroll
                 for (int t = 0; t < 8; ++t) v[t] = gelu_fast(v[t]);
               }
+#pragma unroll
+              for (int t = 0; t < 8; ++t) v[t] *= qs;
               *reinterpret_cast<uint4*>(row + ((static_cast<uint32_t>(j) ^ sw) << 4)) =
                   make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
             }
@@ -285,7 +307,12 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(k2Threads, 1) tc_gem
           fence_proxy_async_smem();  // generic-proxy writes -> visible to the TMA engine
           __syncwarp();
           if (lane == 0) {
-            tma_store_2d(&p.tmOut, buf, n0, row0);
+            if (p.epi == MDE_EPI_QKV_SPLIT) {  // q -> tmOut, k -> tmRes, both token-major [B*197][768]
+              const int which = n0 / MDE_VIT_DIM;
+              tma_store_2d(which == 0 ? &p.tmOut : &p.tmRes, buf, n0 - which * MDE_VIT_DIM, row0);
+            } else {
+              tma_store_2d(&p.tmOut, buf, n0, row0);
+            }
             bulk_commit();
           }
         }
@@ -371,19 +398,22 @@ int launch_gemm_pair(const void* A, int lda, const void* W, int ldw, int M, int 
   p.ldo = ldo;
   p.aux0 = aux0;
   p.aux1 = aux1;
-  p.tma_epi = epilogue <= MDE_EPI_BIAS_F32;
+  p.tma_epi = epilogue <= MDE_EPI_BIAS_F32 || epilogue == MDE_EPI_QKV_SPLIT;
   p.out_elt = (epilogue == MDE_EPI_BIAS_RESID_F32 || epilogue == MDE_EPI_BIAS_F32) ? 4 : 2;
   if (p.tma_epi) {
-    if (((uintptr_t)out % 16) || (ldo * p.out_elt) % 16 || (aux0 && epilogue == MDE_EPI_BIAS_RESID_F32 && ((uintptr_t)aux0 % 16))) {
+    const bool qkv = epilogue == MDE_EPI_QKV_SPLIT;
+    const int out_cols = qkv ? MDE_VIT_DIM : N, out_ld = qkv ? MDE_VIT_DIM : ldo;
+    const void* second = epilogue == MDE_EPI_BIAS_RESID_F32 ? aux0 : (qkv ? aux0 : out);  // residual in / k out / unused
+    if (((uintptr_t)out % 16) || ((uintptr_t)second % 16) || (out_ld * p.out_elt) % 16) {
       set_error("mde_gemm_bf16: output/residual must be 16-byte aligned with a 16-byte multiple row pitch");
       return MDE_ERR_BAD_ARGUMENT;
     }
-    const uint64_t dims[2] = {(uint64_t)N, (uint64_t)M};
-    const uint64_t strides[1] = {(uint64_t)ldo * p.out_elt};
+    const uint64_t dims[2] = {(uint64_t)out_cols, (uint64_t)M};
+    const uint64_t strides[1] = {(uint64_t)out_ld * p.out_elt};
     const uint32_t box[2] = {(uint32_t)(128 / p.out_elt), 32};
     int rc = encode_tmap(&p.tmOut, p.out_elt, out, 2, dims, strides, box, 128);
     if (rc != MDE_OK) return rc;
-    rc = encode_tmap(&p.tmRes, p.out_elt, epilogue == MDE_EPI_BIAS_RESID_F32 ? aux0 : out, 2, dims, strides, box, 128);
+    rc = encode_tmap(&p.tmRes, p.out_elt, second, 2, dims, strides, box, 128);
     if (rc != MDE_OK) return rc;
   }
   const int smem_max = 227 * 1024;

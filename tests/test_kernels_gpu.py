@@ -73,8 +73,8 @@ def test_gemm_pair_kernel_qkv_split():
     vt = torch.zeros(B * 12 * 64 * L.VT_PITCH, device="cuda", dtype=BF16)
     ops.gemm(a, w, b, L.EPI_QKV_SPLIT, q, k, vt)
     ref = (a.float() @ w.float().t() + b).view(B, 197, 3, 12, 64).permute(2, 0, 3, 1, 4)
-    assert rel_l2(q.view(B, 12, 197, 64).float(), ref[0] * 0.125) < 4e-3
-    assert rel_l2(k.view(B, 12, 197, 64).float(), ref[1]) < 4e-3
+    assert rel_l2(q.view(B, 197, 12, 64).permute(0, 2, 1, 3).float(), ref[0] * 0.125) < 4e-3  # q, k are token-major
+    assert rel_l2(k.view(B, 197, 12, 64).permute(0, 2, 1, 3).float(), ref[1]) < 4e-3
     assert rel_l2(vt.view(B, 12, 64, L.VT_PITCH)[..., :197].float().transpose(-1, -2), ref[2]) < 4e-3
 
 
@@ -125,8 +125,8 @@ def test_gemm_qkv_split_epilogue():
     vt = torch.zeros(B * 12 * 64 * L.VT_PITCH, device="cuda", dtype=BF16)
     ops.gemm(a, w, b, L.EPI_QKV_SPLIT, q, k, vt)
     ref = (a.float() @ w.float().t() + b).view(B, 197, 3, 12, 64).permute(2, 0, 3, 1, 4)  # [3,B,12,197,64]
-    assert rel_l2(q.view(B, 12, 197, 64).float(), ref[0] * 0.125) < 4e-3
-    assert rel_l2(k.view(B, 12, 197, 64).float(), ref[1]) < 4e-3
+    assert rel_l2(q.view(B, 197, 12, 64).permute(0, 2, 1, 3).float(), ref[0] * 0.125) < 4e-3  # q, k are token-major
+    assert rel_l2(k.view(B, 197, 12, 64).permute(0, 2, 1, 3).float(), ref[1]) < 4e-3
     v = vt.view(B, 12, 64, L.VT_PITCH)[..., :197].float().transpose(-1, -2)
     assert rel_l2(v, ref[2]) < 4e-3
 
@@ -148,7 +148,8 @@ def test_vit_attention(B):
     qs = (q.float() * 0.125).to(BF16)
     vt = torch.zeros(B, 12, 64, L.VT_PITCH, device="cuda", dtype=BF16)
     vt[..., :197] = v.transpose(-1, -2)
-    out = ops.vit_attention(qs.contiguous().view(-1), k.contiguous().view(-1), vt.view(-1), B)
+    tm = lambda t: t.permute(0, 2, 1, 3).contiguous().view(-1)  # [B,12,197,64] -> token-major [B*197][768]
+    out = ops.vit_attention(tm(qs), tm(k), vt.view(-1), B)
     att = torch.softmax(qs.float() @ k.float().transpose(-1, -2), dim=-1)
     ref = (att @ v.float()).transpose(1, 2).reshape(B * 197, 768)
     assert rel_l2(out.float(), ref) < 1e-2, rel_l2(out.float(), ref)

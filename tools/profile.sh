@@ -18,7 +18,7 @@ echo "launch list rc=$?"
 ncu --set full --clock-control none --import-source on -k 'regex:tc_gemm2_kernel|vit_attn_kernel|layernorm_kernel' -s 91 -c 7 \
     -o $OUT/${TAG}_vit -f $CMD > $OUT/${TAG}_ncu2.log 2>&1
 echo "vit capture rc=$?"
-ncu --set full --clock-control none --import-source on -k 'regex:resize_maps_kernel|minmax_kernel|patchify_kernel|upsample_concat_kernel|tc_gemm_kernel' -s 0 -c 40 \
+ncu --set full --clock-control none --import-source on -k 'regex:resize_maps_kernel|minmax_kernel|patchify_kernel|upsample_concat_kernel|conv_halo_kernel|instnorm_kernel' -s 0 -c 24 \
     -o $OUT/${TAG}_hbm -f $CMD > $OUT/${TAG}_ncu3.log 2>&1
 echo "hbm/conv capture rc=$?"
 ls -la $OUT
