@@ -153,6 +153,7 @@ def main():
     pkgload.load()
     import monodepth_estimation_b200 as mde
     from monodepth_estimation_b200 import ops
+    from monodepth_estimation_b200.sharding import whole_job_rate
     from monodepth_estimation_b200.synth import synth_images, synth_state_dict
 
     rank, world, local = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("LOCAL_RANK", "0"))
@@ -206,10 +207,7 @@ def main():
             step()
         e1.record(stream)
         barrier()
-        t = torch.tensor([e0.elapsed_time(e1) / 1e3], device=dev)
-        if dist is not None:
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
+        return whole_job_rate(B * steps, e0.elapsed_time(e1) / 1e3, dist, dev)[1]  # max seconds over ranks
 
     model = make(a.model)
     sampler = ClockSampler(local) if rank == 0 else None
@@ -241,10 +239,7 @@ def main():
             pipe.run([host_batch] * steps, md)  # returns once the last result is in host memory
             e1.record(torch.cuda.current_stream())
             barrier()
-            tt = torch.tensor([e0.elapsed_time(e1) / 1e3], device=dev)
-            if dist is not None:
-                dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-            return float(tt.item())
+            return whole_job_rate(B * steps, e0.elapsed_time(e1) / 1e3, dist, dev)[1]
 
         te = timed_pipeline(x_host, a.steps, a.warmup)
         line["e2e"] = {"value": round(world * B * a.steps / te, 1), "unit": "images/s", "h2d_bytes_per_step": x_host.numel() * 4,

@@ -1,0 +1,56 @@
+"""CPU, world_size 2, gloo: the host-side multi-rank logic (batch sharding and the whole-job throughput reduction that
+bench.py uses under torchrun).  The data path itself has no collective."""
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import pkgload  # noqa: E402  (spawned workers re-import this module without conftest.py)
+
+pkgload.load()
+
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from monodepth_estimation_b200.sharding import shard_bounds, whole_job_rate
+
+
+def test_shard_bounds_partition_every_batch():
+    for B in (0, 1, 7, 16, 32, 33):
+        for world in (1, 2, 3, 8):
+            cuts = [shard_bounds(B, world, r) for r in range(world)]
+            assert cuts[0][0] == 0 and cuts[-1][1] == B
+            assert all(a[1] == b[0] for a, b in zip(cuts, cuts[1:]))
+            sizes = [hi - lo for lo, hi in cuts]
+            assert max(sizes) - min(sizes) <= 1
+
+
+def _worker(rank, world, port, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    lo, hi = shard_bounds(33, world, rank)
+    x = torch.arange(33 * 4, dtype=torch.float32).view(33, 4)[lo:hi]          # this rank's slice of the global batch
+    secs = 0.5 + 0.25 * rank                                                    # rank 1 is the slow one
+    rate, tmax, total = whole_job_rate(x.shape[0], secs, dist)
+    got = [None] * world
+    dist.all_gather_object(got, (lo, hi, float(x.sum())))
+    if rank == 0:
+        out.put((rate, tmax, total, got))
+    dist.destroy_process_group()
+
+
+def test_world2_gloo_rate_is_total_images_over_slowest_rank():
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 29600 + os.getpid() % 300
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    rate, tmax, total, got = q.get(timeout=120)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert total == 33 and tmax == 0.75 and abs(rate - 33 / 0.75) < 1e-9
+    assert [g[:2] for g in got] == [(0, 17), (17, 33)]
+    full = torch.arange(33 * 4, dtype=torch.float32).view(33, 4)
+    assert abs(sum(g[2] for g in got) - float(full.sum())) < 1e-3  # the two slices cover the batch exactly once
