@@ -8,6 +8,8 @@
 //    second MMA consumes.  1/rowsum is applied in the output epilogue.
 //  * spatial_attn_kernel — enhanced_model.py:20-39 on the 14x15 grid (G<=224 positions,
 //    32-dim q/k, 256-dim v): tiny (25 MFLOP/image), fp32 CUDA-core kernel.
+#include <stdlib.h>
+
 #include "common.h"
 #include "ptx.cuh"
 
@@ -201,6 +203,162 @@ __global__ void __launch_bounds__(256, 1) vit_attn_kernel(const __grid_constant_
   if (warp == 0) tmem_dealloc(tmem_base, kTmemCols);
 }
 
+// ------------------------------------------------------------------ ViT attention, probabilities kept in TMEM
+// One CTA per (image, head, 128-row query tile), 128 threads, 75 KB of shared memory and 256 TMEM columns, so TWO CTAs
+// share an SM and one's softmax overlaps the other's loads and MMAs (the shared-memory-P kernel above needs 225 KB and
+// runs alone).  S = Q K^T lands in TMEM columns [0,208); each thread (= query row = TMEM lane) reads its row twice (max,
+// then exp), and writes the un-normalised bf16 probabilities back into TMEM columns [104,208) — two per 32-bit column,
+// processed from the last chunk to the first so a chunk's probabilities only ever overwrite scores that are already in
+// registers.  O = P V then runs with the A operand read from TMEM (tcgen05.mma [d], [a], b-desc) and accumulates into
+// columns [0,64), which the scores no longer need.  No P tile in shared memory, no proxy fence.
+constexpr int kTpOffK = kQBytes;
+constexpr int kTpOffV = kTpOffK + kKBytesPad;
+constexpr int kTpOffBar = kTpOffV + 4 * kVBytes;
+constexpr int kTpSmem = kTpOffBar + 64 + 1024;
+constexpr uint32_t kTpTmemCols = 256;
+constexpr uint32_t kTpP = 104;  // first TMEM column of P (208 keys x bf16 = 104 columns)
+
+__global__ void __launch_bounds__(128, 2) vit_attn_tp_kernel(const __grid_constant__ AttnParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
+  uint8_t* sQ = smem;
+  uint8_t* sK = smem + kTpOffK;
+  uint8_t* sV = smem + kTpOffV;
+  uint64_t* bar_load = reinterpret_cast<uint64_t*>(smem + kTpOffBar);
+  uint64_t* bar_s = bar_load + 1;
+  uint64_t* bar_o = bar_load + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_load + 3);
+
+  const int tid = threadIdx.x, warp = tid >> 5;
+  const int slab = blockIdx.x >> 1, mt = blockIdx.x & 1;  // (image, head), query tile
+  const int b = slab / MDE_VIT_HEADS, hd = slab - b * MDE_VIT_HEADS;
+
+  if (warp == 0) {
+    if (elect_one()) {
+      tma_prefetch_desc(&p.tmQ);
+      tma_prefetch_desc(&p.tmK);
+      tma_prefetch_desc(&p.tmV);
+      mbar_init(bar_load, 1);
+      mbar_init(bar_s, 1);
+      mbar_init(bar_o, 1);
+      fence_barrier_init();
+    }
+    __syncwarp();
+    tmem_alloc(tmem_slot, kTpTmemCols);
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (tid == 0) {
+    mbar_expect_tx(bar_load, kQBytes + kKBytes + 4 * kVBytes);
+    tma_load_4d(sQ, &p.tmQ, bar_load, 0, hd, mt * 128, b);
+    tma_load_4d(sK, &p.tmK, bar_load, 0, hd, 0, b);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) tma_load_3d(sV + j * kVBytes, &p.tmV, bar_load, 64 * j, 0, slab);
+    mbar_wait(bar_load, 0);
+    tc_fence_after();
+    // ---- S = Q K^T  (128 x 208, K = 64)
+    constexpr uint32_t idesc_s = umma_idesc_bf16(128, kKeys);
+    const uint64_t da = umma_smem_desc_kmajor<128>(smem_u32(sQ));
+    const uint64_t db = umma_smem_desc_kmajor<128>(smem_u32(sK));
+#pragma unroll
+    for (int k = 0; k < 4; ++k) umma_bf16_ss(tmem_base, da + 2 * k, db + 2 * k, idesc_s, k != 0);
+    umma_commit(bar_s);
+  }
+  mbar_wait(bar_s, 0);
+  tc_fence_after();
+
+  const uint32_t t_row = tmem_base + (static_cast<uint32_t>(warp * 32) << 16);  // this thread's TMEM lane
+  constexpr float kLog2e = 1.4426950408889634f;
+
+  // ---- pass 1: row maximum over the 197 real keys
+  float mx = -INFINITY;
+#pragma unroll 1
+  for (int c = 0; c < 6; ++c) {
+    uint32_t r[32];
+    tmem_ld_32x32b_x32(t_row + c * 32, r);
+    tmem_ld_wait();
+#pragma unroll
+    for (int j = 0; j < 32; ++j) mx = fmaxf(mx, __uint_as_float(r[j]));
+  }
+  uint32_t tail[16];
+  tmem_ld_32x32b_x16(t_row + 192, tail);
+  tmem_ld_wait();
+#pragma unroll
+  for (int j = 0; j < kS - 192; ++j) mx = fmaxf(mx, __uint_as_float(tail[j]));
+  const float mxs = mx * kLog2e;
+
+  // ---- pass 2, last chunk first: exp, row sum, bf16 probabilities back into TMEM
+  float sum = 0.0f;
+  {
+    uint32_t pk[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float e0 = (2 * j < kS - 192) ? fast_ex2(fmaf(__uint_as_float(tail[2 * j]), kLog2e, -mxs)) : 0.0f;
+      const float e1 = (2 * j + 1 < kS - 192) ? fast_ex2(fmaf(__uint_as_float(tail[2 * j + 1]), kLog2e, -mxs)) : 0.0f;
+      sum += e0 + e1;
+      pk[j] = pack_bf16x2(e0, e1);
+    }
+    tmem_st_32x32b_x8(t_row + kTpP + 96, pk);
+  }
+#pragma unroll 1
+  for (int c = 5; c >= 0; --c) {
+    uint32_t r[32];
+    tmem_ld_32x32b_x32(t_row + c * 32, r);
+    tmem_ld_wait();
+    uint32_t pk[16];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+      const float e0 = fast_ex2(fmaf(__uint_as_float(r[2 * j]), kLog2e, -mxs));
+      const float e1 = fast_ex2(fmaf(__uint_as_float(r[2 * j + 1]), kLog2e, -mxs));
+      sum += e0 + e1;
+      pk[j] = pack_bf16x2(e0, e1);
+    }
+    tmem_st_32x32b_x16(t_row + kTpP + 16 * c, pk);  // columns >= 104 + 16c: scores there (>= 32c) are already consumed
+  }
+  tmem_st_wait();
+  const float inv = 1.0f / sum;
+  tc_fence_before();
+  __syncthreads();
+
+  // ---- O = P V  (128 x 64, K = 208 = 13 x 16): A from TMEM, B = V^T tiles in shared memory
+  if (tid == 0) {
+    tc_fence_after();
+    constexpr uint32_t idesc_o = umma_idesc_bf16(128, 64);
+#pragma unroll
+    for (int kk = 0; kk < 13; ++kk) {
+      const uint64_t db = umma_smem_desc_kmajor<128>(smem_u32(sV + (kk >> 2) * kVBytes)) + 2 * (kk & 3);
+      umma_bf16_ts(tmem_base, tmem_base + kTpP + 8 * kk, db, idesc_o, kk != 0);
+    }
+    umma_commit(bar_o);
+  }
+  mbar_wait(bar_o, 0);
+  tc_fence_after();
+
+  const int t = mt * 128 + tid;
+#pragma unroll 1
+  for (int c = 0; c < 2; ++c) {
+    uint32_t r[32];
+    tmem_ld_32x32b_x32(t_row + c * 32, r);
+    tmem_ld_wait();
+    if (t < kS) {
+      uint4* dst = reinterpret_cast<uint4*>(p.out + ((size_t)b * kS + t) * MDE_VIT_DIM + hd * 64 + c * 32);
+#pragma unroll
+      for (int g = 0; g < 4; ++g)
+        dst[g] = make_uint4(pack_bf16x2(__uint_as_float(r[8 * g]) * inv, __uint_as_float(r[8 * g + 1]) * inv),
+                            pack_bf16x2(__uint_as_float(r[8 * g + 2]) * inv, __uint_as_float(r[8 * g + 3]) * inv),
+                            pack_bf16x2(__uint_as_float(r[8 * g + 4]) * inv, __uint_as_float(r[8 * g + 5]) * inv),
+                            pack_bf16x2(__uint_as_float(r[8 * g + 6]) * inv, __uint_as_float(r[8 * g + 7]) * inv));
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  if (warp == 0) tmem_dealloc(tmem_base, kTpTmemCols);
+}
+
 // ------------------------------------------------------------------ spatial self-attention (enhanced_model.py:20-39)
 constexpr int kSaQ = 8;        // queries per block
 constexpr int kSaMaxG = 224;   // grid positions supported (14x15 = 210, 14x14 = 196)
@@ -310,9 +468,14 @@ extern "C" int mde_vit_attention(const mde_bf16* q, const mde_bf16* k, const mde
   static bool attr_set = false;
   if (!attr_set) {
     MDE_CHECK_CUDA(cudaFuncSetAttribute(vit_attn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kAttnSmem));
+    MDE_CHECK_CUDA(cudaFuncSetAttribute(vit_attn_tp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kTpSmem));
+    MDE_CHECK_CUDA(cudaFuncSetAttribute(vit_attn_tp_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
     attr_set = true;
   }
-  vit_attn_kernel<<<(unsigned)slabs, 256, kAttnSmem, stream>>>(p);
+  // MDE_ATTN_SMEM_P=1 selects the shared-memory-P kernel (A/B testing); default: probabilities in TMEM, 2 CTAs per SM
+  static const bool smem_p = getenv("MDE_ATTN_SMEM_P") != nullptr && getenv("MDE_ATTN_SMEM_P")[0] == '1';
+  if (smem_p) vit_attn_kernel<<<(unsigned)slabs, 256, kAttnSmem, stream>>>(p);
+  else vit_attn_tp_kernel<<<(unsigned)(2 * slabs), 128, kTpSmem, stream>>>(p);
   MDE_CHECK_LAUNCH();
   return MDE_OK;
 }
