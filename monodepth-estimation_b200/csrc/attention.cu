@@ -39,6 +39,8 @@ struct alignas(64) AttnParams {
 // 256 threads = two warpgroups; warpgroup g owns query tile g (rows 128g .. 128g+127) end to end, so the two tiles'
 // S = Q K^T MMAs are issued back to back and the softmax of one tile overlaps the MMAs / TMEM traffic of the other.
 __global__ void __launch_bounds__(256, 1) vit_attn_kernel(const __grid_constant__ AttnParams p) {
+  pdl_launch_dependents();
+  pdl_grid_wait();
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
   uint8_t* sQ = smem;
@@ -219,6 +221,8 @@ constexpr uint32_t kTpTmemCols = 256;
 constexpr uint32_t kTpP = 104;  // first TMEM column of P (208 keys x bf16 = 104 columns)
 
 __global__ void __launch_bounds__(128, 2) vit_attn_tp_kernel(const __grid_constant__ AttnParams p) {
+  pdl_launch_dependents();
+  pdl_grid_wait();
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
   uint8_t* sQ = smem;
@@ -366,6 +370,8 @@ constexpr int kSaLd = 384;     // row pitch of the fp32 q|k|v projection buffer
 
 __global__ void __launch_bounds__(256) spatial_attn_kernel(const bf16* __restrict__ x, const float* __restrict__ qkv, int gh, int gw,
                                                            const float* __restrict__ gamma_p, bf16* __restrict__ out) {
+  pdl_launch_dependents();
+  pdl_grid_wait();
   __shared__ float sK[kSaMaxG][33];
   __shared__ float sQ[kSaQ][32];
   __shared__ float sA[kSaQ][kSaMaxG];
@@ -474,8 +480,8 @@ extern "C" int mde_vit_attention(const mde_bf16* q, const mde_bf16* k, const mde
   }
   // MDE_ATTN_SMEM_P=1 selects the shared-memory-P kernel (A/B testing); default: probabilities in TMEM, 2 CTAs per SM
   static const bool smem_p = getenv("MDE_ATTN_SMEM_P") != nullptr && getenv("MDE_ATTN_SMEM_P")[0] == '1';
-  if (smem_p) vit_attn_kernel<<<(unsigned)slabs, 256, kAttnSmem, stream>>>(p);
-  else vit_attn_tp_kernel<<<(unsigned)(2 * slabs), 128, kTpSmem, stream>>>(p);
+  if (smem_p) launch_k(vit_attn_kernel, dim3((unsigned)slabs), dim3(256), kAttnSmem, stream, p);
+  else launch_k(vit_attn_tp_kernel, dim3((unsigned)(2 * slabs)), dim3(128), kTpSmem, stream, p);
   MDE_CHECK_LAUNCH();
   return MDE_OK;
 }
@@ -484,7 +490,7 @@ extern "C" int mde_spatial_attention(const mde_bf16* x, const float* qkv, int B,
                                      mde_stream_t stream) {
   MDE_CHECK_ARG(x && qkv && gamma && out_padded && B > 0 && gh >= 3 && gw >= 3, "mde_spatial_attention: bad arguments");
   MDE_CHECK_ARG(gh * gw <= kSaMaxG, "mde_spatial_attention: grid %dx%d exceeds %d positions", gh, gw, kSaMaxG);
-  spatial_attn_kernel<<<dim3(ceil_div(gh * gw, kSaQ), B), 256, 0, stream>>>(reinterpret_cast<const bf16*>(x), qkv, gh, gw, gamma,
+  launch_k(spatial_attn_kernel, dim3(ceil_div(gh * gw, kSaQ), B), dim3(256), 0, stream, reinterpret_cast<const bf16*>(x), qkv, gh, gw, gamma,
                                                                             reinterpret_cast<bf16*>(out_padded));
   MDE_CHECK_LAUNCH();
   return MDE_OK;

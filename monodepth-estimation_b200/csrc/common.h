@@ -4,6 +4,7 @@
 #include <cuda.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <string.h>
 
 #include "../../include/mde.h"
 
@@ -57,6 +58,26 @@ int launch_gemm_pair(const void* A, int lda, const void* W, int ldw, int M, int 
 // geometry not served there, the caller uses the tap-shifted kernel.
 int launch_conv_halo(int f16, const void* in, int B, int h, int w, int cin, int in_cstride, const void* wpacked, const float* bias, int cout,
                      int padding, int activation, void* out_bf16, int out_cstride, int out_coff, float* out_f32, cudaStream_t stream);
+
+// Kernel launch, optionally with programmatic dependent launch (MDE_PDL=1; off by default, see pdl_enabled()).  Errors are picked up
+// by MDE_CHECK_LAUNCH() at the call site.
+bool pdl_enabled();
+template <class... KArgs, class... Args>
+static inline void launch_k(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream, Args... args) {
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute at;
+  memset(&at, 0, sizeof(at));
+  at.id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at.val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = &at;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  (void)cudaLaunchKernelEx(&cfg, kernel, args...);
+}
 
 static inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 

@@ -49,6 +49,8 @@ struct alignas(64) HaloParams {
 
 template <int BLOCK_N, int ROWB>
 __global__ void __launch_bounds__(kHaloThreads, BLOCK_N <= 32 ? 2 : 1) conv_halo_kernel(const __grid_constant__ HaloParams p) {
+  pdl_launch_dependents();
+  pdl_grid_wait();
   constexpr int KC = ROWB / 2;
   constexpr int WB_RAW = BLOCK_N * ROWB;
   constexpr int WB = (WB_RAW + 1023) & ~1023;
@@ -219,7 +221,7 @@ static int launch_halo(HaloParams& p, int smem_bytes, cudaStream_t stream) {
   occ = std::max(1, std::min(occ, 512 / tmem_cols));
   int grid = sm_count() * occ;
   if (grid > p.total_tiles) grid = p.total_tiles;
-  conv_halo_kernel<BLOCK_N, ROWB><<<grid, kHaloThreads, smem_bytes, stream>>>(p);
+  launch_k(conv_halo_kernel<BLOCK_N, ROWB>, dim3(grid), dim3(kHaloThreads), smem_bytes, stream, p);
   MDE_CHECK_LAUNCH();
   return MDE_OK;
 }

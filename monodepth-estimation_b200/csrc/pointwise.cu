@@ -44,6 +44,8 @@ __device__ __forceinline__ void src_index_act(float scale, int dst, int in_size,
 
 // ------------------------------------------------------------------ input range (encoder.py:129-135)
 __global__ void __launch_bounds__(256) minmax_kernel(const float4* __restrict__ x4, long long n4, int hw4, float* __restrict__ partials) {
+  pdl_launch_dependents();
+  pdl_grid_wait();
   float mn[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, mx[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
   const long long per = (n4 + gridDim.x - 1) / gridDim.x;
   const long long beg = per * blockIdx.x;
@@ -91,6 +93,8 @@ __global__ void __launch_bounds__(256) minmax_kernel(const float4* __restrict__ 
 
 __global__ void range_finalize_kernel(const float* __restrict__ partials, int nparts, const float* __restrict__ bn, float eps,
                                       float* __restrict__ affine6) {
+  pdl_launch_dependents();
+  pdl_grid_wait();
   // one warp: lanes stride over the partials, shuffle-reduce each of the 6 statistics
   __shared__ float st[6];
 #pragma unroll
@@ -139,6 +143,8 @@ __global__ void range_finalize_kernel(const float* __restrict__ partials, int np
 // ------------------------------------------------------------------ generic fp32 NCHW bilinear (align_corners=False)
 __global__ void __launch_bounds__(256) resize_nchw_kernel(const float* __restrict__ src, int planes, int Hs, int Ws, float* __restrict__ dst,
                                                           int Hd, int Wd) {
+  pdl_launch_dependents();
+  pdl_grid_wait();
   const float sh = (float)Hs / (float)Hd, sw = (float)Ws / (float)Wd;
   const long long total = (long long)planes * Hd * Wd;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
@@ -160,6 +166,8 @@ __global__ void __launch_bounds__(256) resize_nchw_kernel(const float* __restric
 // one thread = 8 consecutive kx of one (b, patch, c, ky): one 16-byte store of the GEMM A operand
 __global__ void __launch_bounds__(256) patchify_kernel(const float* __restrict__ x, int B, int H, int W, const float* __restrict__ affine6,
                                                        bf16* __restrict__ patches) {
+  pdl_launch_dependents();
+  pdl_grid_wait();
   const float sh = (float)H / 224.0f, sw = (float)W / 224.0f;
   const bool identity = (H == 224 && W == 224);
   const long long total = (long long)B * 196 * 96;  // 768 / 8 groups per patch row
@@ -201,6 +209,8 @@ __global__ void __launch_bounds__(256) patchify_kernel(const float* __restrict__
 template <int DIM>
 __global__ void __launch_bounds__(256) layernorm_kernel(const float* __restrict__ x, int rows, const float* __restrict__ gamma,
                                                         const float* __restrict__ beta, float eps, bf16* __restrict__ out) {
+  pdl_launch_dependents();
+  pdl_grid_wait();
   constexpr int PER = DIM / 256;  // 8-element groups per lane
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int row = blockIdx.x * 8 + warp;
@@ -241,6 +251,8 @@ __global__ void __launch_bounds__(256) layernorm_kernel(const float* __restrict_
 
 // ------------------------------------------------------------------ tokens -> grid rows (encoder.py:69-110), fp32 -> bf16
 __global__ void __launch_bounds__(256) tokens_to_grid_kernel(const float* __restrict__ tok, int B, int strip, int G, bf16* __restrict__ out) {
+  pdl_launch_dependents();
+  pdl_grid_wait();
   const int T = MDE_VIT_SEQ - strip;  // tokens copied per image
   const long long total = (long long)B * G * 96;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
@@ -264,6 +276,8 @@ __global__ void __launch_bounds__(256) tokens_to_grid_kernel(const float* __rest
 constexpr int kInMaxPer = 14;  // ceil(224 / 16)
 __global__ void __launch_bounds__(256) instnorm_kernel(const float* __restrict__ x, int gh, int gw, int C, float eps, bf16* __restrict__ outp,
                                                        int cstride, int coff, bf16* __restrict__ outf) {
+  pdl_launch_dependents();
+  pdl_grid_wait();
   const int G = gh * gw;
   const int cl = threadIdx.x & 15, rl = threadIdx.x >> 4;
   const int c = blockIdx.x * 16 + cl, b = blockIdx.y;
@@ -334,6 +348,8 @@ __device__ __forceinline__ int reflect_idx(int i, int n) {  // ReflectionPad2d(1
 // 32-bit (the first version spent its time in 64-bit index divisions: issue-bound at 4x the HBM time, r01b profile).
 __global__ void __launch_bounds__(256) upsample_concat_kernel(const bf16* __restrict__ a, int B, int h, int w, int ca, const bf16* __restrict__ s,
                                                               int hs, int ws, int cs, bf16* __restrict__ out) {
+  pdl_launch_dependents();
+  pdl_grid_wait();
   const int Ho = 2 * h, Wo = 2 * w, ct = ca + cs, groups = ct >> 3, ga = ca >> 3;
   const int b = blockIdx.x / (Ho + 2), Yp = blockIdx.x - b * (Ho + 2);
   const int oy = reflect_idx(Yp - 1, Ho);
@@ -382,6 +398,8 @@ __global__ void __launch_bounds__(256) upsample_concat_kernel(const bf16* __rest
 // ------------------------------------------------------------------ rgb -> grid channels of a padded NHWC buffer (enhanced_model.py:95-98)
 __global__ void __launch_bounds__(256) rgb_to_grid_kernel(const float* __restrict__ x, int B, int H, int W, int gh, int gw, bf16* __restrict__ out,
                                                           int cstride, int coff, int cfill) {
+  pdl_launch_dependents();
+  pdl_grid_wait();
   const float sh = (float)H / (float)gh, sw = (float)W / (float)gw;
   const int total = B * gh * gw;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
@@ -418,6 +436,8 @@ constexpr int kMaxSrcW = 1024;
 constexpr int kRowsPerBlock = 8;
 template <bool VEC4>
 __global__ void __launch_bounds__(256) resize_maps_kernel(const __grid_constant__ MapTable tab, int B, int H, int W, float min_disp, float disp_range) {
+  pdl_launch_dependents();
+  pdl_grid_wait();
   constexpr int PX = VEC4 ? 4 : 1;
   __shared__ float srow[kRowsPerBlock][kMaxSrcW + 1];
   const int mi = blockIdx.z / B, b = blockIdx.z - mi * B;
@@ -478,6 +498,8 @@ __global__ void __launch_bounds__(256) resize_maps_kernel(const __grid_constant_
 // wa*s[i] + wb*s[i+1] + wc*s[i+2] with per-thread constant weights (one of wa, wc is zero): 3 shared-memory reads and 12
 // FP instructions per 16-byte store, rows fully unrolled so every address is base + immediate.
 __global__ void __launch_bounds__(256) resize_maps_up3_kernel(const __grid_constant__ MapTable tab, int B, int H, int W, float min_disp, float disp_range) {
+  pdl_launch_dependents();
+  pdl_grid_wait();
   __shared__ float srow[kRowsPerBlock][kMaxSrcW + 2];
   const int mi = blockIdx.z / B, b = blockIdx.z - mi * B;
   const mde_map_desc& d = tab.m[mi];
@@ -553,6 +575,8 @@ __device__ __forceinline__ float bilinear_acf(const float* p, int hs, int ws, in
 __global__ void __launch_bounds__(256) enh_fuse_kernel(const float* __restrict__ d0, const float* __restrict__ d1, const float* __restrict__ d2,
                                                        const float* __restrict__ refn, int B, int h0, int w0, int gh, int gw, float mul,
                                                        const float* __restrict__ fw, float* __restrict__ fused) {
+  pdl_launch_dependents();
+  pdl_grid_wait();
   // softmax over the three fusion weights (enhanced_model.py:70)
   const float a0 = fw[0], a1 = fw[1], a2 = fw[2];
   const float m = fmaxf(a0, fmaxf(a1, a2));
@@ -575,6 +599,8 @@ __global__ void __launch_bounds__(256) enh_fuse_kernel(const float* __restrict__
 // uint8 HWC (decoder output) -> float32 CHW / 255: `torch.from_numpy(arr).float().permute(2,0,1) / 255.0` on the device.
 // One thread converts 4 pixels: three aligned 4-byte loads, three 16-byte streaming-friendly stores.
 __global__ void __launch_bounds__(256) u8hwc_to_f32chw_kernel(const uint32_t* __restrict__ src, long long quads, int HW4, float4* __restrict__ dst) {
+  pdl_launch_dependents();
+  pdl_grid_wait();
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < quads; i += (long long)gridDim.x * blockDim.x) {
     const long long b = i / HW4;
     const int q = (int)(i - b * HW4);
@@ -611,9 +637,9 @@ extern "C" int mde_input_range(const float* x, int B, int H, int W, const float*
   int parts = sm_count() * 4;
   if (parts > 1024) parts = 1024;
   if (parts > n4) parts = (int)n4;
-  minmax_kernel<<<parts, 256, 0, stream>>>(reinterpret_cast<const float4*>(x), n4, H * W / 4, scratch);
+  launch_k(minmax_kernel, dim3(parts), dim3(256), 0, stream, reinterpret_cast<const float4*>(x), n4, H * W / 4, scratch);
   MDE_CHECK_LAUNCH();
-  range_finalize_kernel<<<1, 32, 0, stream>>>(scratch, parts, bn4x3, eps, affine6);
+  launch_k(range_finalize_kernel, dim3(1), dim3(32), 0, stream, scratch, parts, bn4x3, eps, affine6);
   MDE_CHECK_LAUNCH();
   return MDE_OK;
 }
@@ -621,7 +647,7 @@ extern "C" int mde_input_range(const float* x, int B, int H, int W, const float*
 extern "C" int mde_resize_bilinear_nchw(const float* src, int B, int C, int Hs, int Ws, float* dst, int Hd, int Wd, mde_stream_t stream) {
   MDE_CHECK_ARG(src && dst && B > 0 && C > 0 && Hs > 0 && Ws > 0 && Hd > 0 && Wd > 0, "mde_resize_bilinear_nchw: bad arguments");
   const long long total = (long long)B * C * Hd * Wd;
-  resize_nchw_kernel<<<grid_for(total, 256), 256, 0, stream>>>(src, B * C, Hs, Ws, dst, Hd, Wd);
+  launch_k(resize_nchw_kernel, dim3(grid_for(total, 256)), dim3(256), 0, stream, src, B * C, Hs, Ws, dst, Hd, Wd);
   MDE_CHECK_LAUNCH();
   return MDE_OK;
 }
@@ -630,7 +656,7 @@ extern "C" int mde_preprocess_patchify(const float* x, int B, int H, int W, cons
   MDE_CHECK_ARG(x && affine6 && patches && B > 0 && H > 0 && W > 0, "mde_preprocess_patchify: bad arguments");
   MDE_CHECK_ARG((uintptr_t)patches % 16 == 0, "mde_preprocess_patchify: patches must be 16-byte aligned");
   const long long total = (long long)B * 196 * 96;
-  patchify_kernel<<<grid_for(total, 256), 256, 0, stream>>>(x, B, H, W, affine6, reinterpret_cast<bf16*>(patches));
+  launch_k(patchify_kernel, dim3(grid_for(total, 256)), dim3(256), 0, stream, x, B, H, W, affine6, reinterpret_cast<bf16*>(patches));
   MDE_CHECK_LAUNCH();
   return MDE_OK;
 }
@@ -643,7 +669,7 @@ extern "C" int mde_layernorm_bf16(const float* x, int rows, int dim, const float
     set_error("mde_layernorm_bf16: dim=%d not built (768 only)", dim);
     return MDE_ERR_UNSUPPORTED;
   }
-  layernorm_kernel<768><<<ceil_div(rows, 8), 256, 0, stream>>>(x, rows, gamma, beta, eps, reinterpret_cast<bf16*>(out));
+  launch_k(layernorm_kernel<768>, dim3(ceil_div(rows, 8)), dim3(256), 0, stream, x, rows, gamma, beta, eps, reinterpret_cast<bf16*>(out));
   MDE_CHECK_LAUNCH();
   return MDE_OK;
 }
@@ -652,7 +678,7 @@ extern "C" int mde_tokens_to_grid_bf16(const float* tokens, int B, int strip_cls
   MDE_CHECK_ARG(tokens && out && B > 0, "mde_tokens_to_grid_bf16: bad arguments");
   MDE_CHECK_ARG((strip_cls == 0 || strip_cls == 1) && G >= MDE_VIT_SEQ - strip_cls, "mde_tokens_to_grid_bf16: G=%d too small", G);
   const long long total = (long long)B * G * 96;
-  tokens_to_grid_kernel<<<grid_for(total, 256), 256, 0, stream>>>(tokens, B, strip_cls, G, reinterpret_cast<bf16*>(out));
+  launch_k(tokens_to_grid_kernel, dim3(grid_for(total, 256)), dim3(256), 0, stream, tokens, B, strip_cls, G, reinterpret_cast<bf16*>(out));
   MDE_CHECK_LAUNCH();
   return MDE_OK;
 }
@@ -662,7 +688,7 @@ extern "C" int mde_instnorm_nhwc(const float* x, int B, int gh, int gw, int C, f
   MDE_CHECK_ARG(x && out_padded && B > 0 && gh >= 3 && gw >= 3, "mde_instnorm_nhwc: bad arguments");
   MDE_CHECK_ARG(C % 16 == 0 && out_coff + C <= out_cstride, "mde_instnorm_nhwc: C must be a multiple of 16 and fit the output stride");
   MDE_CHECK_ARG(gh * gw <= 16 * kInMaxPer, "mde_instnorm_nhwc: grid %dx%d exceeds %d positions", gh, gw, 16 * kInMaxPer);
-  instnorm_kernel<<<dim3(C / 16, B), 256, 0, stream>>>(x, gh, gw, C, eps, reinterpret_cast<bf16*>(out_padded), out_cstride, out_coff,
+  launch_k(instnorm_kernel, dim3(C / 16, B), dim3(256), 0, stream, x, gh, gw, C, eps, reinterpret_cast<bf16*>(out_padded), out_cstride, out_coff,
                                                        reinterpret_cast<bf16*>(out_flat));
   MDE_CHECK_LAUNCH();
   return MDE_OK;
@@ -674,7 +700,7 @@ extern "C" int mde_upsample2x_concat_nhwc(const mde_bf16* a, int B, int h, int w
   MDE_CHECK_ARG((s == nullptr) == (cs == 0) && cs % 8 == 0, "mde_upsample2x_concat_nhwc: skip tensor / cs mismatch");
   if (s) MDE_CHECK_ARG(hs >= 2 && ws >= 2, "mde_upsample2x_concat_nhwc: bad skip size");
   MDE_CHECK_ARG((long long)B * (2 * h + 2) < (1ll << 31), "mde_upsample2x_concat_nhwc: too many rows");
-  upsample_concat_kernel<<<B * (2 * h + 2), 256, 0, stream>>>(reinterpret_cast<const bf16*>(a), B, h, w, ca, reinterpret_cast<const bf16*>(s),
+  launch_k(upsample_concat_kernel, dim3(B * (2 * h + 2)), dim3(256), 0, stream, reinterpret_cast<const bf16*>(a), B, h, w, ca, reinterpret_cast<const bf16*>(s),
                                                                    hs, ws, cs, reinterpret_cast<bf16*>(out));
   MDE_CHECK_LAUNCH();
   return MDE_OK;
@@ -683,7 +709,7 @@ extern "C" int mde_upsample2x_concat_nhwc(const mde_bf16* a, int B, int h, int w
 extern "C" int mde_rgb_to_grid_nhwc(const float* x, int B, int H, int W, int gh, int gw, mde_bf16* out_padded, int out_cstride, int out_coff,
                                     int cfill, mde_stream_t stream) {
   MDE_CHECK_ARG(x && out_padded && B > 0 && cfill >= 3 && out_coff + cfill <= out_cstride, "mde_rgb_to_grid_nhwc: bad arguments");
-  rgb_to_grid_kernel<<<grid_for((long long)B * gh * gw, 256), 256, 0, stream>>>(x, B, H, W, gh, gw, reinterpret_cast<bf16*>(out_padded),
+  launch_k(rgb_to_grid_kernel, dim3(grid_for((long long)B * gh * gw, 256)), dim3(256), 0, stream, x, B, H, W, gh, gw, reinterpret_cast<bf16*>(out_padded),
                                                                                out_cstride, out_coff, cfill);
   MDE_CHECK_LAUNCH();
   return MDE_OK;
@@ -705,11 +731,11 @@ extern "C" int mde_resize_maps(const mde_map_desc* maps, int n_maps, int B, int 
   bool up3 = vec;
   for (int i = 0; i < n_maps; ++i) up3 = up3 && 3 * maps[i].ws < W;
   if (up3) {
-    resize_maps_up3_kernel<<<dim3(ceil_div(W / 4, 256), ceil_div(H, kRowsPerBlock), n_maps * B), 256, 0, stream>>>(tab, B, H, W, min_disp, range);
+    launch_k(resize_maps_up3_kernel, dim3(ceil_div(W / 4, 256), ceil_div(H, kRowsPerBlock), n_maps * B), dim3(256), 0, stream, tab, B, H, W, min_disp, range);
   } else if (vec) {
-    resize_maps_kernel<true><<<dim3(ceil_div(W / 4, 256), ceil_div(H, kRowsPerBlock), n_maps * B), 256, 0, stream>>>(tab, B, H, W, min_disp, range);
+    launch_k(resize_maps_kernel<true>, dim3(ceil_div(W / 4, 256), ceil_div(H, kRowsPerBlock), n_maps * B), dim3(256), 0, stream, tab, B, H, W, min_disp, range);
   } else {
-    resize_maps_kernel<false><<<dim3(ceil_div(W, 256), ceil_div(H, kRowsPerBlock), n_maps * B), 256, 0, stream>>>(tab, B, H, W, min_disp, range);
+    launch_k(resize_maps_kernel<false>, dim3(ceil_div(W, 256), ceil_div(H, kRowsPerBlock), n_maps * B), dim3(256), 0, stream, tab, B, H, W, min_disp, range);
   }
   MDE_CHECK_LAUNCH();
   return MDE_OK;
@@ -718,7 +744,7 @@ extern "C" int mde_resize_maps(const mde_map_desc* maps, int n_maps, int B, int 
 extern "C" int mde_enh_fuse(const float* d0, const float* d1, const float* d2, const float* refinement, int B, int h0, int w0, int gh, int gw,
                             float mul, const float* fusion_w3, float* fused, mde_stream_t stream) {
   MDE_CHECK_ARG(d0 && d1 && d2 && refinement && fusion_w3 && fused && B > 0 && h0 > 0 && w0 > 0, "mde_enh_fuse: bad arguments");
-  enh_fuse_kernel<<<grid_for((long long)B * h0 * w0, 256), 256, 0, stream>>>(d0, d1, d2, refinement, B, h0, w0, gh, gw, mul, fusion_w3, fused);
+  launch_k(enh_fuse_kernel, dim3(grid_for((long long)B * h0 * w0, 256)), dim3(256), 0, stream, d0, d1, d2, refinement, B, h0, w0, gh, gw, mul, fusion_w3, fused);
   MDE_CHECK_LAUNCH();
   return MDE_OK;
 }
@@ -729,7 +755,7 @@ extern "C" int mde_u8hwc_to_f32chw(const uint8_t* src, int B, int H, int W, floa
                 "mde_u8hwc_to_f32chw: H*W must be a multiple of 4, src 4-byte and dst 16-byte aligned");
   const int hw4 = (int)(((long long)H * W) / 4);
   const long long quads = (long long)B * hw4;
-  u8hwc_to_f32chw_kernel<<<grid_for(quads, 256), 256, 0, stream>>>(reinterpret_cast<const uint32_t*>(src), quads, hw4, reinterpret_cast<float4*>(dst));
+  launch_k(u8hwc_to_f32chw_kernel, dim3(grid_for(quads, 256)), dim3(256), 0, stream, reinterpret_cast<const uint32_t*>(src), quads, hw4, reinterpret_cast<float4*>(dst));
   MDE_CHECK_LAUNCH();
   return MDE_OK;
 }

@@ -66,6 +66,15 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   }
 }
 
+// ----------------------------------------------------------------------------- programmatic dependent launch
+// Every kernel of the path CAN be launched with the programmatic-stream-serialization attribute (common.h: launch_k,
+// MDE_PDL=1): it may
+// start while its predecessor in the stream is still draining, run its private prologue (barrier init, TMEM allocation,
+// descriptor prefetch, weight prefetch), and must call pdl_grid_wait() before it touches anything the predecessor wrote
+// or still reads.  pdl_launch_dependents() lets the NEXT kernel do the same; both are no-ops without the attribute.
+__device__ __forceinline__ void pdl_grid_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 // ----------------------------------------------------------------------------- TMA
 __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* m) {
   asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(m)) : "memory");

@@ -48,6 +48,8 @@ struct FusionParams {
 };
 
 __global__ void __launch_bounds__(256) depth_fusion_kernel(const __grid_constant__ FusionParams p) {
+  pdl_launch_dependents();
+  pdl_grid_wait();
   __shared__ float tile[MDE_MAX_FUSION_SCALES][kFuTH + 2][kFuTW + 2];
   __shared__ float sw[MDE_MAX_FUSION_SCALES][12];
   const int b = blockIdx.z, X0 = blockIdx.x * kFuTW, Y0 = blockIdx.y * kFuTH;
@@ -109,6 +111,8 @@ __global__ void __launch_bounds__(256) depth_fusion_kernel(const __grid_constant
 //   gate  f32 [B][H][W] = sigmoid(5 * sqrt(ex^2 + ey^2)), ex/ey = Sobel/3 summed over the 3 channels, zero padded
 __global__ void __launch_bounds__(256) refine_pack_kernel(const float* __restrict__ rgb, const float* __restrict__ depth, int B, int H, int W,
                                                           __half* __restrict__ in16, float* __restrict__ gate) {
+  pdl_launch_dependents();
+  pdl_grid_wait();
   const long long total = (long long)B * H * W;
   const size_t plane = (size_t)H * W;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
@@ -145,6 +149,8 @@ __global__ void __launch_bounds__(256) refine_pack_kernel(const float* __restric
 __global__ void __launch_bounds__(256) refine_output_kernel(const __half* __restrict__ feat, int cstride, const float* __restrict__ w32,
                                                             const float* __restrict__ bias1, const float* __restrict__ depth,
                                                             const float* __restrict__ gate, int B, int H, int W, float* __restrict__ out) {
+  pdl_launch_dependents();
+  pdl_grid_wait();
   __shared__ float sw[32];
   if (threadIdx.x < 32) sw[threadIdx.x] = w32[threadIdx.x];
   __syncthreads();
@@ -206,7 +212,7 @@ extern "C" int mde_depth_fusion(const float* const* maps, const int* hs, const i
   p.fuse_b = fuse_b;
   p.out = out;
   MDE_CHECK_ARG(ceil_div(H, kFuTH) <= 65535, "mde_depth_fusion: H too large");
-  depth_fusion_kernel<<<dim3(ceil_div(W, kFuTW), ceil_div(H, kFuTH), B), 256, 0, stream>>>(p);
+  launch_k(depth_fusion_kernel, dim3(ceil_div(W, kFuTW), ceil_div(H, kFuTH), B), dim3(256), 0, stream, p);
   MDE_CHECK_LAUNCH();
   return MDE_OK;
 }
@@ -215,7 +221,7 @@ extern "C" int mde_refine_pack_inputs(const float* rgb, const float* depth, int 
                                       mde_stream_t stream) {
   MDE_CHECK_ARG(rgb && depth && in16_padded && gate && B > 0 && H >= 3 && W >= 3, "mde_refine_pack_inputs: bad arguments");
   MDE_CHECK_ARG((uintptr_t)in16_padded % 16 == 0, "mde_refine_pack_inputs: in16_padded must be 16-byte aligned");
-  refine_pack_kernel<<<grid_cap((long long)B * H * W, 256, 16), 256, 0, stream>>>(rgb, depth, B, H, W, reinterpret_cast<__half*>(in16_padded), gate);
+  launch_k(refine_pack_kernel, dim3(grid_cap((long long)B * H * W, 256, 16)), dim3(256), 0, stream, rgb, depth, B, H, W, reinterpret_cast<__half*>(in16_padded), gate);
   MDE_CHECK_LAUNCH();
   return MDE_OK;
 }
@@ -224,7 +230,7 @@ extern "C" int mde_refine_output(const mde_f16* feat_padded, int cstride, const 
                                  const float* gate, int B, int H, int W, float* out, mde_stream_t stream) {
   MDE_CHECK_ARG(feat_padded && w32 && bias1 && depth && gate && out && B > 0 && H >= 3 && W >= 3, "mde_refine_output: bad arguments");
   MDE_CHECK_ARG(cstride >= 32 && cstride % 8 == 0 && (uintptr_t)feat_padded % 16 == 0, "mde_refine_output: feat must have >= 32 channels, 16-byte aligned");
-  refine_output_kernel<<<grid_cap((long long)B * H * W, 256, 16), 256, 0, stream>>>(reinterpret_cast<const __half*>(feat_padded), cstride, w32, bias1, depth,
+  launch_k(refine_output_kernel, dim3(grid_cap((long long)B * H * W, 256, 16)), dim3(256), 0, stream, reinterpret_cast<const __half*>(feat_padded), cstride, w32, bias1, depth,
                                                                                     gate, B, H, W, out);
   MDE_CHECK_LAUNCH();
   return MDE_OK;

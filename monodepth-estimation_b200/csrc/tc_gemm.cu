@@ -53,6 +53,8 @@ constexpr int min_ctas() {
 
 template <int BLOCK_N, int ROWB>
 __global__ void __launch_bounds__(kThreads, min_ctas<BLOCK_N>()) tc_gemm_kernel(const __grid_constant__ TcParams p) {
+  pdl_launch_dependents();
+  pdl_grid_wait();
   constexpr int KCHUNK = ROWB / 2;
   constexpr int A_BYTES = kBlockM * ROWB;
   constexpr int B_BYTES_RAW = BLOCK_N * ROWB;
@@ -245,7 +247,7 @@ static int launch_tc(TcParams& p, cudaStream_t stream) {
   const int total = p.num_m_tiles * p.num_n_tiles;
   int grid = sm_count() * ctas_per_sm;
   if (grid > total) grid = total;
-  tc_gemm_kernel<BLOCK_N, ROWB><<<grid, kThreads, smem_bytes, stream>>>(p);
+  launch_k(tc_gemm_kernel<BLOCK_N, ROWB>, dim3(grid), dim3(kThreads), smem_bytes, stream, p);
   MDE_CHECK_LAUNCH();
   return MDE_OK;
 }
@@ -387,7 +389,7 @@ static int conv_nhwc_impl(int f16, const mde_bf16* in, int B, int h, int w, int 
       break;
     }
   const int m_tiles = B * ceil_div(h, th) * ceil_div(w, tw);
-  while (block_n > 64 && m_tiles * (cout_pad / block_n) < sm_count()) block_n >>= 1;
+  while (block_n > 64 && m_tiles * (cout_pad / block_n) < sm_count()) block_n >>= 1;  // (N = 32 tiles measured slower: r01r)
   const int ktot = ksize * ksize * cin;
   {
     const uint64_t dims[2] = {(uint64_t)ktot, (uint64_t)cout_pad};

@@ -85,6 +85,8 @@ __device__ __forceinline__ Item decode_item(const Tc2Params& p, int i) {
 }
 
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(k2Threads, 1) tc_gemm2_kernel(const __grid_constant__ Tc2Params p) {
+  pdl_launch_dependents();
+  pdl_grid_wait();
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
   const int stages = p.stages;
@@ -427,7 +429,7 @@ int launch_gemm_pair(const void* A, int lda, const void* W, int ldw, int M, int 
     attr_set = true;
   }
   const int grid = 2 * std::min(clusters, p.total_items);
-  tc_gemm2_kernel<<<grid, k2Threads, smem_bytes, stream>>>(p);
+  launch_k(tc_gemm2_kernel, dim3(grid), dim3(k2Threads), smem_bytes, stream, p);
   MDE_CHECK_LAUNCH();
   return MDE_OK;
 }
