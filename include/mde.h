@@ -56,7 +56,7 @@ enum mde_padding { MDE_PAD_REFLECT = 0, MDE_PAD_ZERO = 1 };
 #define MDE_VIT_DIM 768
 #define MDE_VIT_HEADS 12
 #define MDE_VT_PITCH 208       /* row pitch (elements) of the transposed V buffer            */
-#define MDE_RANGE_SCRATCH_FLOATS (6 * 1024)
+#define MDE_RANGE_SCRATCH_FLOATS (6 * 8192)
 
 int mde_version(void);
 const char* mde_last_error(void);
@@ -88,6 +88,14 @@ int mde_u8hwc_to_f32chw(const uint8_t* src, int B, int H, int W, float* dst, mde
  * patches bf16 [B*196][768], column = c*256 + ky*16 + kx. */
 int mde_preprocess_patchify(const float* x, int B, int H, int W, const float* affine6, mde_bf16* patches,
                             mde_stream_t stream);
+
+/* ---- encoder.py:129-144 in ONE pass over x (the fused form of mde_input_range + mde_preprocess_patchify) -------------
+ * resize(a*x + b) == a*resize(x) + b for the per-channel affine map of BN + range heuristic, so the input is read once:
+ * the scan kernel takes per-channel min/max AND resamples the raw image to raw224 f32 [B][3][224][224]; the finalize
+ * kernel evaluates the heuristic on device (affine6 as above); the patchify kernel applies it and writes
+ * patches bf16 [B*196][768].  W % 4 == 0.  scratch: MDE_RANGE_SCRATCH_FLOATS floats. */
+int mde_input_stage(const float* x, int B, int H, int W, const float* bn4x3, float eps, float* scratch, float* affine6,
+                    float* raw224, mde_bf16* patches, mde_stream_t stream);
 
 /* ---- tcgen05 GEMM: D[M,N] = epilogue(A[M,K] * W[N,K]^T), bf16 in, fp32 accumulate --------
  * Replaces conv_proj (tv:277), in_proj / out_proj (tv:113), mlp.0 / mlp.3 (tv:118) and

@@ -18,7 +18,7 @@ EPI_BIAS_BF16, EPI_BIAS_GELU_BF16, EPI_BIAS_RESID_F32, EPI_BIAS_F32, EPI_PATCH_E
 ACT_NONE, ACT_ELU, ACT_SIGMOID = range(3)
 PAD_REFLECT, PAD_ZERO = range(2)
 VIT_SEQ, VIT_DIM, VIT_HEADS, VT_PITCH = 197, 768, 12, 208
-RANGE_SCRATCH_FLOATS = 6 * 1024
+RANGE_SCRATCH_FLOATS = 6 * 8192
 MAX_MAPS = 8
 MAX_FUSION_SCALES = 4
 
@@ -39,6 +39,7 @@ SIGNATURES = {
     "mde_resize_bilinear_nchw": [_p, _i, _i, _i, _i, _p, _i, _i, _p],
     "mde_u8hwc_to_f32chw": [_p, _i, _i, _i, _p, _p],
     "mde_preprocess_patchify": [_p, _i, _i, _i, _p, _p, _p],
+    "mde_input_stage": [_p, _i, _i, _i, _p, _f, _p, _p, _p, _p, _p],
     "mde_gemm_bf16": [_p, _i, _p, _i, _i, _i, _i, _i, _p, _p, _i, _p, _p, _p],
     "mde_layernorm_bf16": [_p, _i, _i, _p, _p, _f, _p, _p],
     "mde_vit_attention": [_p, _p, _p, _i, _p, _p],

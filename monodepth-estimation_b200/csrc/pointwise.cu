@@ -91,21 +91,28 @@ __global__ void __launch_bounds__(256) minmax_kernel(const float4* __restrict__ 
   }
 }
 
-__global__ void range_finalize_kernel(const float* __restrict__ partials, int nparts, const float* __restrict__ bn, float eps,
+__global__ void __launch_bounds__(768) range_finalize_kernel(const float* __restrict__ partials, int nparts, const float* __restrict__ bn, float eps,
                                       float* __restrict__ affine6) {
   pdl_launch_dependents();
   pdl_grid_wait();
-  // one warp: lanes stride over the partials, shuffle-reduce each of the 6 statistics
-  __shared__ float st[6];
-#pragma unroll
-  for (int k = 0; k < 6; ++k) {
+  // 768 threads (a multiple of 6): thread t reads floats t, t+768, ... (coalesced, all of statistic t % 6), then a
+  // shared-memory tree whose strides stay multiples of 6
+  __shared__ float st[768];
+  {
+    const int k = threadIdx.x % 6;
     float r = k < 3 ? FLT_MAX : -FLT_MAX;
-    for (int i = threadIdx.x; i < nparts; i += 32) {
-      const float v = partials[i * 6 + k];
+    for (int i = threadIdx.x; i < nparts * 6; i += 768) {
+      const float v = partials[i];
       r = k < 3 ? fminf(r, v) : fmaxf(r, v);
     }
-    r = k < 3 ? warp_min(r) : warp_max(r);
-    if (threadIdx.x == 0) st[k] = r;
+    st[threadIdx.x] = r;
+    for (int s = 384; s >= 6; s >>= 1) {
+      __syncthreads();
+      if ((int)threadIdx.x < s) {
+        const float u = st[threadIdx.x], v = st[threadIdx.x + s];
+        st[threadIdx.x] = k < 3 ? fminf(u, v) : fmaxf(u, v);
+      }
+    }
   }
   __syncthreads();
   if (threadIdx.x == 0) {
@@ -202,6 +209,103 @@ __global__ void __launch_bounds__(256) patchify_kernel(const float* __restrict__
     for (int j = 0; j < 8; ++j) v[j] = fmaf(a, v[j], bb);
     *reinterpret_cast<uint4*>(patches + row * 768 + grp * 8) =
         make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
+  }
+}
+
+// ------------------------------------------------------------------ fused input stage (encoder.py:129-144), one pass over x
+// Bilinear resampling is linear with weights summing to 1 and BN + the range heuristic are one per-channel affine map, so
+//   resize(a*x + b) == a*resize(x) + b
+// and the 224x224 image can be resampled from the RAW input in the same pass that scans it for min/max; the affine map is
+// applied afterwards to the 0.6 MB/image result.  A block owns `rpb` consecutive output rows of one (image, channel)
+// plane: it scans the source rows [y0(first), y0(last+1)) — a contiguous range; the ranges of all blocks tile the plane
+// exactly once — with four independent 16-byte loads in flight per thread, writes its min/max partial, then produces its
+// output rows from taps that are now in L1/L2.  The separate patchify pass read 44 % of the input a second time from DRAM.
+__device__ __forceinline__ int scan_row_start(float sh, int oy, int H) {  // first source row owned by output row oy
+  if (oy <= 0) return 0;
+  if (oy >= 224) return H;
+  int y0, y1;
+  float l;
+  src_index_acf(sh, oy, H, y0, y1, l);
+  return y0;
+}
+__global__ void __launch_bounds__(256) input_scan_resample_kernel(const float* __restrict__ x, int H, int W, int rpb, int groups,
+                                                                  float* __restrict__ partials, float* __restrict__ raw224) {
+  pdl_launch_dependents();
+  pdl_grid_wait();
+  const int grp = blockIdx.x % groups, plane = blockIdx.x / groups;  // plane = b*3 + c
+  const int c = plane % 3;
+  const int oy0 = grp * rpb, oy1 = min(224, oy0 + rpb);
+  const float sh = (float)H / 224.0f, sw = (float)W / 224.0f;
+  const float* pl = x + (size_t)plane * H * W;
+  const int lo = scan_row_start(sh, oy0, H), hi = scan_row_start(sh, oy1, H);
+  float mn = FLT_MAX, mx = -FLT_MAX;
+  {
+    const float4* p4 = reinterpret_cast<const float4*>(pl + (size_t)lo * W);  // host checked W % 4 == 0 and 16-byte alignment
+    const int n4 = (hi - lo) * (W >> 2);
+    for (int i0 = threadIdx.x; i0 < n4; i0 += 4 * 256) {
+      float4 v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int i = i0 + u * 256;
+        v[u] = __ldg(p4 + min(i, n4 - 1));  // past the end: re-read the last vector (neutral for min and max)
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        mn = fminf(mn, fminf(fminf(v[u].x, v[u].y), fminf(v[u].z, v[u].w)));
+        mx = fmaxf(mx, fmaxf(fmaxf(v[u].x, v[u].y), fmaxf(v[u].z, v[u].w)));
+      }
+    }
+  }
+  __shared__ float red[8][2];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  mn = warp_min(mn);
+  mx = warp_max(mx);
+  if (lane == 0) {
+    red[warp][0] = mn;
+    red[warp][1] = mx;
+  }
+  __syncthreads();
+  if (threadIdx.x < 6) {
+    const int k = threadIdx.x;
+    float r = k < 3 ? FLT_MAX : -FLT_MAX;
+    if (k == c || k == 3 + c)
+      for (int w = 0; w < 8; ++w) r = k < 3 ? fminf(r, red[w][0]) : fmaxf(r, red[w][1]);
+    partials[(size_t)blockIdx.x * 6 + k] = r;
+  }
+  // resample this block's output rows (torch bilinear, align_corners=False)
+  const int ox = threadIdx.x;
+  if (ox >= 224) return;
+  int x0, x1;
+  float lx;
+  src_index_acf(sw, ox, W, x0, x1, lx);
+  float* dst = raw224 + ((size_t)plane * 224 + oy0) * 224 + ox;
+  for (int oy = oy0; oy < oy1; ++oy, dst += 224) {
+    int y0, y1;
+    float ly;
+    src_index_acf(sh, oy, H, y0, y1, ly);
+    const float* r0 = pl + (size_t)y0 * W;
+    const float* r1 = pl + (size_t)y1 * W;
+    *dst = (1.0f - ly) * ((1.0f - lx) * __ldg(r0 + x0) + lx * __ldg(r0 + x1)) + ly * ((1.0f - lx) * __ldg(r1 + x0) + lx * __ldg(r1 + x1));
+  }
+}
+
+// raw224 f32 [B][3][224][224] -> affine -> patch-embedding A operand bf16 [B*196][768], column = c*256 + ky*16 + kx
+__global__ void __launch_bounds__(256) patchify224_kernel(const float* __restrict__ raw, int B, const float* __restrict__ affine6,
+                                                          bf16* __restrict__ patches) {
+  pdl_launch_dependents();
+  pdl_grid_wait();
+  const int total = B * 196 * 96;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int grp = i % 96, row = i / 96;  // row = b*196 + patch
+    const int patch = row % 196, b = row / 196;
+    const int c = grp >> 5, ky = (grp >> 1) & 15, kx0 = (grp & 1) * 8;
+    const int Y = (patch / 14) * 16 + ky, X0 = (patch % 14) * 16 + kx0;
+    const float a = __ldg(affine6 + c), bb = __ldg(affine6 + 3 + c);
+    const float4* src = reinterpret_cast<const float4*>(raw + (((size_t)b * 3 + c) * 224 + Y) * 224 + X0);
+    const float4 u = __ldg(src), w = __ldg(src + 1);
+    *reinterpret_cast<uint4*>(patches + (size_t)row * 768 + grp * 8) =
+        make_uint4(pack_bf16x2(fmaf(a, u.x, bb), fmaf(a, u.y, bb)), pack_bf16x2(fmaf(a, u.z, bb), fmaf(a, u.w, bb)),
+                   pack_bf16x2(fmaf(a, w.x, bb), fmaf(a, w.y, bb)), pack_bf16x2(fmaf(a, w.z, bb), fmaf(a, w.w, bb)));
   }
 }
 
@@ -639,7 +743,7 @@ extern "C" int mde_input_range(const float* x, int B, int H, int W, const float*
   if (parts > n4) parts = (int)n4;
   launch_k(minmax_kernel, dim3(parts), dim3(256), 0, stream, reinterpret_cast<const float4*>(x), n4, H * W / 4, scratch);
   MDE_CHECK_LAUNCH();
-  launch_k(range_finalize_kernel, dim3(1), dim3(32), 0, stream, scratch, parts, bn4x3, eps, affine6);
+  launch_k(range_finalize_kernel, dim3(1), dim3(768), 0, stream, scratch, parts, bn4x3, eps, affine6);
   MDE_CHECK_LAUNCH();
   return MDE_OK;
 }
@@ -756,6 +860,27 @@ extern "C" int mde_u8hwc_to_f32chw(const uint8_t* src, int B, int H, int W, floa
   const int hw4 = (int)(((long long)H * W) / 4);
   const long long quads = (long long)B * hw4;
   launch_k(u8hwc_to_f32chw_kernel, dim3(grid_for(quads, 256)), dim3(256), 0, stream, reinterpret_cast<const uint32_t*>(src), quads, hw4, reinterpret_cast<float4*>(dst));
+  MDE_CHECK_LAUNCH();
+  return MDE_OK;
+}
+
+extern "C" int mde_input_stage(const float* x, int B, int H, int W, const float* bn4x3, float eps, float* scratch, float* affine6,
+                               float* raw224, mde_bf16* patches, mde_stream_t stream) {
+  MDE_CHECK_ARG(x && bn4x3 && scratch && affine6 && raw224 && patches, "mde_input_stage: null pointer");
+  MDE_CHECK_ARG(B > 0 && H > 0 && W > 0 && W % 4 == 0 && (uintptr_t)x % 16 == 0, "mde_input_stage: W must be a multiple of 4 and x 16-byte aligned (H=%d W=%d)", H, W);
+  MDE_CHECK_ARG((uintptr_t)raw224 % 16 == 0 && (uintptr_t)patches % 16 == 0, "mde_input_stage: raw224 / patches must be 16-byte aligned");
+  const int max_parts = MDE_RANGE_SCRATCH_FLOATS / 6;
+  int rpb = ceil_div(224 * 3 * B, max_parts);  // output rows per block: as few as the partials buffer allows, at least kMinRows
+  static const int kMinRows = getenv("MDE_SCAN_ROWS") ? atoi(getenv("MDE_SCAN_ROWS")) : 8;
+  if (rpb < kMinRows) rpb = kMinRows;
+  MDE_CHECK_ARG(rpb <= 224, "mde_input_stage: batch %d too large for the partials buffer", B);
+  const int groups = ceil_div(224, rpb);
+  const int parts = groups * 3 * B;
+  launch_k(input_scan_resample_kernel, dim3(parts), dim3(256), 0, stream, x, H, W, rpb, groups, scratch, raw224);
+  MDE_CHECK_LAUNCH();
+  launch_k(range_finalize_kernel, dim3(1), dim3(768), 0, stream, scratch, parts, bn4x3, eps, affine6);
+  MDE_CHECK_LAUNCH();
+  launch_k(patchify224_kernel, dim3(grid_for((long long)B * 196 * 96, 256)), dim3(256), 0, stream, raw224, B, affine6, reinterpret_cast<bf16*>(patches));
   MDE_CHECK_LAUNCH();
   return MDE_OK;
 }

@@ -58,6 +58,7 @@ class Workspace:
         self.scratch = e(L.RANGE_SCRATCH_FLOATS, dt=F32)
         self.affine = e(6, dt=F32)
         self.patches = e(B * 196, 768)
+        self.raw224 = e(B, 3, 224, 224, dt=F32)
         self.xa, self.xb = e(M, 768, dt=F32), e(M, 768, dt=F32)
         self.taps = [e(M, 768, dt=F32) for _ in range(4)]
         self.h = e(M, 768)
@@ -143,8 +144,11 @@ class DepthEngine:
         xin = x
         if ws.xp is not None:
             xin = ops.resize_bilinear_nchw(x, ws.Hp, ws.Wp, out=ws.xp)
-        ops.input_range(xin, w["enc"]["bn4x3"], 1e-5, ws.scratch, ws.affine)
-        ops.preprocess_patchify(xin, ws.affine, ws.patches)
+        if ws.Wp % 4 == 0:  # one pass over the input (scan + raw resample), then finalize + patchify on 0.6 MB/image
+            ops.input_stage(xin, w["enc"]["bn4x3"], 1e-5, ws.scratch, ws.affine, ws.raw224, ws.patches)
+        else:
+            ops.input_range(xin, w["enc"]["bn4x3"], 1e-5, ws.scratch, ws.affine)
+            ops.preprocess_patchify(xin, ws.affine, ws.patches)
         n = 3 + (ws.xp is not None)
         if self.enhanced:
             ops.rgb_to_grid(xin, ws.gh, ws.gw, ws.feats[0], 256, 64)  # enhanced_model.py:95-98

@@ -180,3 +180,11 @@ def u8hwc_to_f32chw(src, out=None):
     out = out if out is not None else torch.empty(B, 3, H, W, device=src.device, dtype=F32)
     L.call("mde_u8hwc_to_f32chw", _ptr(src, torch.uint8), B, H, W, _ptr(out, F32), _stream())
     return out
+
+
+def input_stage(x, bn4x3, eps, scratch, affine, raw224, patches):
+    """encoder.py:129-144 in one pass: min/max scan + raw 224x224 resample, device-side range heuristic, affine + patchify."""
+    B, _, H, W = x.shape
+    L.call("mde_input_stage", _ptr(x, F32), B, H, W, _ptr(bn4x3, F32), float(eps), _ptr(scratch, F32), _ptr(affine, F32), _ptr(raw224, F32),
+           _ptr(patches, BF16), _stream())
+    return patches

@@ -294,6 +294,30 @@ def test_input_range_and_patchify(kind, H, W):
     assert rel_l2(got.float(), ref) < 4e-3
 
 
+@pytest.mark.parametrize("kind,H,W,B", [("unit", 256, 320, 2), ("byte", 224, 224, 2), ("signed", 528, 528, 3), ("unit", 1024, 1024, 2), ("byte", 100, 148, 1),
+                                        ("unit", 1024, 1024, 33)])
+def test_input_stage_fused(kind, H, W, B):
+    """The one-pass input stage (scan + raw resample, finalize, patchify) against the two-pass kernels and the oracle."""
+    L, ops = _mods()
+    from helpers import synth_images
+
+    x = synth_images(min(B, 3), H, W, 7, kind).repeat((B + 2) // 3, 1, 1, 1)[:B].contiguous().cuda()
+    x[B - 1, 2, H - 1, W - 4:] = x.max() + 0.25  # extremes in the last rows / first row: every source row must be scanned once
+    x[0, 0, 0, :4] = x.min() - 0.25
+    bn = torch.tensor([1.0, 0.9, 1.1, 0.0, 0.01, -0.01, 0.0, 0.02, -0.02, 1.0, 1.1, 0.9], device="cuda")
+    aff_ref = ops.input_range(x, bn, 1e-5)
+    ref = ops.preprocess_patchify(x, aff_ref).float()
+    scratch = torch.empty(L.RANGE_SCRATCH_FLOATS, device="cuda")
+    aff = torch.empty(6, device="cuda")
+    raw = torch.empty(B, 3, 224, 224, device="cuda")
+    got = ops.input_stage(x, bn, 1e-5, scratch, aff, raw, torch.empty(B * 196, 768, device="cuda", dtype=BF16)).float()
+    assert torch.equal(aff, aff_ref)
+    want_raw = x if (H, W) == (224, 224) else F.interpolate(x, size=(224, 224), mode="bilinear", align_corners=False)
+    assert max_abs(raw, want_raw) < 2e-5 * max(1.0, float(x.abs().max()))
+    assert max_abs(got, ref) <= 1.6e-2 * max(1.0, float(ref.abs().max()))  # one bf16 ulp where the fp32 values straddle a rounding boundary
+    assert rel_l2(got, ref) < 1e-3
+
+
 @pytest.mark.parametrize("H,W", [(518, 518), (1024, 1024), (250, 333)])
 def test_resize_maps_and_depth(H, W):
     _, ops = _mods()
