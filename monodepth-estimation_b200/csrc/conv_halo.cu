@@ -187,7 +187,8 @@ __global__ void __launch_bounds__(kHaloThreads, BLOCK_N <= 32 ? 2 : 1) conv_halo
           float v[NCOL];
 #pragma unroll
           for (int jj = 0; jj < NCOL; ++jj) v[jj] = __uint_as_float(raw[jj]);
-          epilogue_chunk<NCOL, HaloParams>(p, v, c * NCOL, ri);
+          add_bias<NCOL, HaloParams>(p, v, c * NCOL);
+          if (ri.valid) epilogue_conv<NCOL, HaloParams>(p, v, c * NCOL, ri);
         }
       }
       tc_fence_before();

@@ -871,7 +871,7 @@ extern "C" int mde_input_stage(const float* x, int B, int H, int W, const float*
   MDE_CHECK_ARG((uintptr_t)raw224 % 16 == 0 && (uintptr_t)patches % 16 == 0, "mde_input_stage: raw224 / patches must be 16-byte aligned");
   const int max_parts = MDE_RANGE_SCRATCH_FLOATS / 6;
   int rpb = ceil_div(224 * 3 * B, max_parts);  // output rows per block: as few as the partials buffer allows, at least kMinRows
-  static const int kMinRows = getenv("MDE_SCAN_ROWS") ? atoi(getenv("MDE_SCAN_ROWS")) : 8;
+  static const int kMinRows = getenv("MDE_SCAN_ROWS") ? atoi(getenv("MDE_SCAN_ROWS")) : 4;
   if (rpb < kMinRows) rpb = kMinRows;
   MDE_CHECK_ARG(rpb <= 224, "mde_input_stage: batch %d too large for the partials buffer", B);
   const int groups = ceil_div(224, rpb);

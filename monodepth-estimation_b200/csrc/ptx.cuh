@@ -304,8 +304,9 @@ __device__ __forceinline__ float gelu_fast(float x) {
   q = fmaf(q, x2, -2.3011213f);                        // -log2e * c0
   return x * fast_rcp(1.0f + fast_ex2(x * q));
 }
-__device__ __forceinline__ float elu1(float x) { return x > 0.0f ? x : (__expf(x) - 1.0f); }
-__device__ __forceinline__ float sigmoidf_(float x) { return 1.0f / (1.0f + __expf(-x)); }
+// one MUFU each (ex2.approx.ftz / rcp.approx.ftz), no denormal-scaling branches: the conv epilogues are issue-bound (r01v)
+__device__ __forceinline__ float elu1(float x) { return x > 0.0f ? x : fast_ex2(x * 1.4426950408889634f) - 1.0f; }
+__device__ __forceinline__ float sigmoidf_(float x) { return fast_rcp(1.0f + fast_ex2(x * -1.4426950408889634f)); }
 
 __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
   __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);

@@ -16,9 +16,72 @@ struct RowInfo {
   int b, y, x;  // conv pixel
 };
 
+// conv epilogue proper (after the bias add): activation, then a bf16/fp16 padded-NHWC store with the reflected border copies
+// the pixel owns, or an fp32 NHWC head.  conv_halo.cu calls it directly (no GEMM cases in its instruction stream).
 template <int NCOL, class P>
-__device__ __forceinline__ void epilogue_chunk(const P& p, float (&v)[NCOL], int n0, const RowInfo& ri) {
-  // bias (same address for every lane: served as an L1 broadcast)
+__device__ __forceinline__ void epilogue_conv(const P& p, float (&v)[NCOL], int n0, const RowInfo& ri) {
+  const int nv = min(NCOL, p.cout - n0);  // valid output channels in this chunk
+  if (nv <= 0) return;
+  if (p.epi == EPI_CONV_F32 && nv == 1) {  // the 1-channel heads (dispconv, uncertainty): one activation, one store
+    float r = v[0];
+    r = p.act == MDE_ACT_ELU ? elu1(r) : p.act == MDE_ACT_SIGMOID ? sigmoidf_(r) : r;
+    reinterpret_cast<float*>(p.out)[(((size_t)ri.b * p.h + ri.y) * p.w + ri.x) * p.cout + n0] = r;
+    return;
+  }
+  if (p.act == MDE_ACT_ELU) {
+#pragma unroll
+    for (int j = 0; j < NCOL; ++j) v[j] = elu1(v[j]);
+  } else if (p.act == MDE_ACT_SIGMOID) {
+#pragma unroll
+    for (int j = 0; j < NCOL; ++j) v[j] = sigmoidf_(v[j]);
+  }
+  if (p.epi == EPI_CONV_F32) {
+    float* dst = reinterpret_cast<float*>(p.out) + (((size_t)ri.b * p.h + ri.y) * p.w + ri.x) * p.cout + n0;
+#pragma unroll
+    for (int j = 0; j < NCOL; ++j)
+      if (j < nv) dst[j] = v[j];
+    return;
+  }
+  uint32_t pk[NCOL / 2];
+#pragma unroll
+  for (int j = 0; j < NCOL / 2; ++j) pk[j] = p.f16 ? pack_f16x2(v[2 * j], v[2 * j + 1]) : pack_bf16x2(v[2 * j], v[2 * j + 1]);
+  const int H2 = p.h + 2, W2 = p.w + 2;
+  bf16* obase = reinterpret_cast<bf16*>(p.out) + p.out_coff + n0;
+  auto store_px = [&](int Y, int X) {  // padded coordinates
+    uint4* dst = reinterpret_cast<uint4*>(obase + (((size_t)ri.b * H2 + Y) * W2 + X) * p.out_cstride);
+    if (p.st32) {  // 32-byte stores (host checked alignment and cout % 16 == 0)
+#pragma unroll
+      for (int j = 0; j < NCOL / 16; ++j)
+        if (16 * j < nv)
+          st_global_v8(dst + 2 * j, make_uint4(pk[8 * j], pk[8 * j + 1], pk[8 * j + 2], pk[8 * j + 3]),
+                       make_uint4(pk[8 * j + 4], pk[8 * j + 5], pk[8 * j + 6], pk[8 * j + 7]));
+    } else {
+#pragma unroll
+      for (int j = 0; j < NCOL / 8; ++j)
+        if (8 * j < nv) dst[j] = make_uint4(pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
+    }
+  };
+  store_px(ri.y + 1, ri.x + 1);  // interior pixel
+  // the reflected border copies this pixel owns (rows 1 / h-2 -> padded rows 0 / h+1, same for columns): rare path
+  const bool by = ri.y == 1 || ri.y == p.h - 2, bx = ri.x == 1 || ri.x == p.w - 2;
+  if (by || bx) {
+#pragma unroll 1
+    for (int iy = 0; iy < 3; ++iy) {
+      const int Y = iy == 0 ? ri.y + 1 : iy == 1 ? (ri.y == 1 ? 0 : -1) : (ri.y == p.h - 2 ? p.h + 1 : -1);
+      if (Y < 0) continue;
+#pragma unroll 1
+      for (int ix = 0; ix < 3; ++ix) {
+        const int X = ix == 0 ? ri.x + 1 : ix == 1 ? (ri.x == 1 ? 0 : -1) : (ri.x == p.w - 2 ? p.w + 1 : -1);
+        if (X < 0 || (iy == 0 && ix == 0)) continue;
+        store_px(Y, X);
+      }
+    }
+  }
+}
+
+template <int NCOL, class P>
+__device__ __forceinline__ void add_bias(const P& p, float (&v)[NCOL], int n0) {
+  // same address for every lane: served as an L1 broadcast
   const float4* bp = reinterpret_cast<const float4*>(p.bias + n0);
 #pragma unroll
   for (int j = 0; j < NCOL / 4; ++j) {
@@ -28,6 +91,11 @@ __device__ __forceinline__ void epilogue_chunk(const P& p, float (&v)[NCOL], int
     v[4 * j + 2] += b4.z;
     v[4 * j + 3] += b4.w;
   }
+}
+
+template <int NCOL, class P>
+__device__ __forceinline__ void epilogue_chunk(const P& p, float (&v)[NCOL], int n0, const RowInfo& ri) {
+  add_bias<NCOL, P>(p, v, n0);
   if (!ri.valid) return;
 
   switch (p.epi) {
@@ -105,53 +173,9 @@ __device__ __forceinline__ void epilogue_chunk(const P& p, float (&v)[NCOL], int
       break;
     }
     case EPI_CONV_BF16:
-    case EPI_CONV_F32: {
-      if (p.act == MDE_ACT_ELU) {
-#pragma unroll
-        for (int j = 0; j < NCOL; ++j) v[j] = elu1(v[j]);
-      } else if (p.act == MDE_ACT_SIGMOID) {
-#pragma unroll
-        for (int j = 0; j < NCOL; ++j) v[j] = sigmoidf_(v[j]);
-      }
-      const int nv = min(NCOL, p.cout - n0);  // valid output channels in this chunk
-      if (nv <= 0) break;
-      if (p.epi == EPI_CONV_F32) {
-        float* dst = reinterpret_cast<float*>(p.out) + (((size_t)ri.b * p.h + ri.y) * p.w + ri.x) * p.cout + n0;
-#pragma unroll
-        for (int j = 0; j < NCOL; ++j)
-          if (j < nv) dst[j] = v[j];
-        break;
-      }
-      uint32_t pk[NCOL / 2];
-#pragma unroll
-      for (int j = 0; j < NCOL / 2; ++j) pk[j] = p.f16 ? pack_f16x2(v[2 * j], v[2 * j + 1]) : pack_bf16x2(v[2 * j], v[2 * j + 1]);
-      // interior pixel (y+1, x+1) plus the reflected border copies it owns
-      const int H2 = p.h + 2, W2 = p.w + 2;
-      int ys[3], xs[3], ny = 0, nx = 0;
-      ys[ny++] = ri.y + 1;
-      if (ri.y == 1) ys[ny++] = 0;
-      if (ri.y == p.h - 2) ys[ny++] = p.h + 1;
-      xs[nx++] = ri.x + 1;
-      if (ri.x == 1) xs[nx++] = 0;
-      if (ri.x == p.w - 2) xs[nx++] = p.w + 1;
-      bf16* obase = reinterpret_cast<bf16*>(p.out) + p.out_coff + n0;
-      for (int iy = 0; iy < ny; ++iy)
-        for (int ix = 0; ix < nx; ++ix) {
-          uint4* dst = reinterpret_cast<uint4*>(obase + (((size_t)ri.b * H2 + ys[iy]) * W2 + xs[ix]) * p.out_cstride);
-          if (p.st32) {  // 32-byte stores (host checked alignment and cout % 16 == 0)
-#pragma unroll
-            for (int j = 0; j < NCOL / 16; ++j)
-              if (16 * j < nv)
-                st_global_v8(dst + 2 * j, make_uint4(pk[8 * j], pk[8 * j + 1], pk[8 * j + 2], pk[8 * j + 3]),
-                             make_uint4(pk[8 * j + 4], pk[8 * j + 5], pk[8 * j + 6], pk[8 * j + 7]));
-          } else {
-#pragma unroll
-            for (int j = 0; j < NCOL / 8; ++j)
-              if (8 * j < nv) dst[j] = make_uint4(pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
-          }
-        }
+    case EPI_CONV_F32:
+      epilogue_conv<NCOL, P>(p, v, n0, ri);
       break;
-    }
     default:
       break;
   }
