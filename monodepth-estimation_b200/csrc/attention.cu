@@ -40,7 +40,6 @@ struct alignas(64) AttnParams {
 // S = Q K^T MMAs are issued back to back and the softmax of one tile overlaps the MMAs / TMEM traffic of the other.
 __global__ void __launch_bounds__(256, 1) vit_attn_kernel(const __grid_constant__ AttnParams p) {
   pdl_launch_dependents();
-  pdl_grid_wait();
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
   uint8_t* sQ = smem;
@@ -76,6 +75,7 @@ __global__ void __launch_bounds__(256, 1) vit_attn_kernel(const __grid_constant_
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_grid_wait();  // the set-up above overlaps the previous kernel's tail
 
   if (tid == 0) {
     mbar_expect_tx(bar_load, 2 * kQBytes + kKBytes + 4 * kVBytes);
@@ -222,7 +222,6 @@ constexpr uint32_t kTpP = 104;  // first TMEM column of P (208 keys x bf16 = 104
 
 __global__ void __launch_bounds__(128, 2) vit_attn_tp_kernel(const __grid_constant__ AttnParams p) {
   pdl_launch_dependents();
-  pdl_grid_wait();
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
   uint8_t* sQ = smem;
@@ -254,6 +253,7 @@ __global__ void __launch_bounds__(128, 2) vit_attn_tp_kernel(const __grid_consta
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_grid_wait();  // the set-up above overlaps the previous kernel's tail
 
   if (tid == 0) {
     mbar_expect_tx(bar_load, kQBytes + kKBytes + 4 * kVBytes);

@@ -59,7 +59,7 @@ int launch_gemm_pair(const void* A, int lda, const void* W, int ldw, int M, int 
 int launch_conv_halo(int f16, const void* in, int B, int h, int w, int cin, int in_cstride, const void* wpacked, const float* bias, int cout,
                      int padding, int activation, void* out_bf16, int out_cstride, int out_coff, float* out_f32, cudaStream_t stream);
 
-// Kernel launch, optionally with programmatic dependent launch (MDE_PDL=1; off by default, see pdl_enabled()).  Errors are picked up
+// Kernel launch, with programmatic dependent launch unless MDE_PDL=0 (see pdl_enabled()).  Errors are picked up
 // by MDE_CHECK_LAUNCH() at the call site.
 bool pdl_enabled();
 template <class... KArgs, class... Args>

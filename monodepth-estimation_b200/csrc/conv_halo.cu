@@ -45,12 +45,12 @@ struct alignas(64) HaloParams {
   const void* aux0;
   const void* aux1;
   int cout, out_cstride, out_coff, f16, st32;
+  int dbg;  // MDE_HALO_DBG bit mask, tools/conv_bench.py only: 1 no epilogue, 2 no MMAs, 4 no activation/stores, 8 no halo loads, 16 stores to one pixel
 };
 
 template <int BLOCK_N, int ROWB>
 __global__ void __launch_bounds__(kHaloThreads, BLOCK_N <= 32 ? 2 : 1) conv_halo_kernel(const __grid_constant__ HaloParams p) {
   pdl_launch_dependents();
-  pdl_grid_wait();
   constexpr int KC = ROWB / 2;
   constexpr int WB_RAW = BLOCK_N * ROWB;
   constexpr int WB = (WB_RAW + 1023) & ~1023;
@@ -98,6 +98,7 @@ __global__ void __launch_bounds__(kHaloThreads, BLOCK_N <= 32 ? 2 : 1) conv_halo
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_grid_wait();  // the set-up above overlaps the previous kernel's tail
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
@@ -111,8 +112,12 @@ __global__ void __launch_bounds__(kHaloThreads, BLOCK_N <= 32 ? 2 : 1) conv_halo
         const int y0 = (r / p.tiles_x) * p.th, x0 = (r % p.tiles_x) * kHaloTW;
         for (int c = 0; c < p.chunks; ++c) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
-          mbar_expect_tx(&full_bar[stage], (uint32_t)p.halo_bytes);
-          tma_load_4d(sH + (size_t)stage * p.stage_bytes, &p.tmA, &full_bar[stage], c * KC, x0 + p.coord_off, y0 + p.coord_off, b);
+          if (p.dbg & 8) {
+            mbar_arrive(&full_bar[stage]);
+          } else {
+            mbar_expect_tx(&full_bar[stage], (uint32_t)p.halo_bytes);
+            tma_load_4d(sH + (size_t)stage * p.stage_bytes, &p.tmA, &full_bar[stage], c * KC, x0 + p.coord_off, y0 + p.coord_off, b);
+          }
           if (++stage == stages) {
             stage = 0;
             phase ^= 1;
@@ -135,7 +140,7 @@ __global__ void __launch_bounds__(kHaloThreads, BLOCK_N <= 32 ? 2 : 1) conv_halo
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after();
           const uint32_t a_base = smem_u32(sH + (size_t)stage * p.stage_bytes);
-          for (int j = 0; j < p.nblk; ++j) {
+          for (int j = 0; j < ((p.dbg & 2) ? 0 : p.nblk); ++j) {
             const uint32_t d_tmem = tmem_base + (uint32_t)((acc * p.nblk + j) * BLOCK_N);
 #pragma unroll
             for (int t = 0; t < 9; ++t) {
@@ -168,7 +173,7 @@ __global__ void __launch_bounds__(kHaloThreads, BLOCK_N <= 32 ? 2 : 1) conv_halo
       const int y0 = (r / p.tiles_x) * p.th, x0 = (r % p.tiles_x) * kHaloTW;
       mbar_wait(&tfull_bar[acc], acc_phase);
       tc_fence_after();
-      for (int j = half; j < p.nblk; j += 2) {
+      for (int j = half; j < ((p.dbg & 1) ? 0 : p.nblk); j += 2) {
         const int o = 128 * j + q * 32 + lane;
         const int yy = o >> 6, xx = o & 63;
         RowInfo ri;
@@ -176,7 +181,8 @@ __global__ void __launch_bounds__(kHaloThreads, BLOCK_N <= 32 ? 2 : 1) conv_halo
         ri.b = b;
         ri.y = y0 + yy;
         ri.x = x0 + xx;
-        ri.valid = xx < kHaloTW && ri.y < p.h && ri.x < p.w;
+        ri.valid = xx < kHaloTW && ri.y < p.h && ri.x < p.w && !(p.dbg & 4);
+        if (p.dbg & 16) ri.b = 0, ri.y = 2, ri.x = 2;  // every lane stores to one pixel: same instructions, no store traffic
         const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + (uint32_t)((acc * p.nblk + j) * BLOCK_N);
 #pragma unroll 1
         for (int c = 0; c < BLOCK_N / NCOL; ++c) {
@@ -307,6 +313,8 @@ int launch_conv_halo(int f16, const void* in, int B, int h, int w, int cin, int 
   p.out_cstride = out_cstride;
   p.out_coff = out_coff;
   p.f16 = f16;
+  static const int dbg = getenv("MDE_HALO_DBG") ? atoi(getenv("MDE_HALO_DBG")) : 0;
+  p.dbg = dbg;
   p.st32 = out_bf16 && cout % 16 == 0 && ((uintptr_t)out_bf16 % 32 == 0) && (out_cstride * 2) % 32 == 0 && (out_coff * 2) % 32 == 0;
   const int smem_bytes = 1024 + weights_bytes + stages * stage_bytes + 1024 + 256;
 #define MDE_HALO_CASE(BN, RB) \

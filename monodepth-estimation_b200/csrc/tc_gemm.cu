@@ -54,7 +54,6 @@ constexpr int min_ctas() {
 template <int BLOCK_N, int ROWB>
 __global__ void __launch_bounds__(kThreads, min_ctas<BLOCK_N>()) tc_gemm_kernel(const __grid_constant__ TcParams p) {
   pdl_launch_dependents();
-  pdl_grid_wait();
   constexpr int KCHUNK = ROWB / 2;
   constexpr int A_BYTES = kBlockM * ROWB;
   constexpr int B_BYTES_RAW = BLOCK_N * ROWB;
@@ -99,6 +98,7 @@ __global__ void __launch_bounds__(kThreads, min_ctas<BLOCK_N>()) tc_gemm_kernel(
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_grid_wait();  // the set-up above overlaps the previous kernel's tail
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer

@@ -86,7 +86,6 @@ __device__ __forceinline__ Item decode_item(const Tc2Params& p, int i) {
 
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(k2Threads, 1) tc_gemm2_kernel(const __grid_constant__ Tc2Params p) {
   pdl_launch_dependents();
-  pdl_grid_wait();
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
   const int stages = p.stages;
@@ -132,6 +131,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(k2Threads, 1) tc_gem
   cluster_sync_all();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_grid_wait();  // everything above (barriers, TMEM, descriptor prefetch) overlaps the previous kernel's tail
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer (both CTAs)
