@@ -109,6 +109,28 @@ int mde_gemm_bf16(const mde_bf16* A, int lda, const mde_bf16* W, int ldw, int M,
                   const float* bias, void* out, int ldo, const void* aux0, const void* aux1,
                   mde_stream_t stream);
 
+/* ---- the same GEMM with the LayerNorm between two linear layers folded into their epilogues (tv:112-113, 117-118) -----
+ * y = LN(x) W^T + b  ==  rstd * (bf16(x) (gamma.W)^T - mean * colsum) + (b + W beta)   with colsum[n] = sum_k (gamma.W)[n][k].
+ * PRODUCER side (the GEMM that writes the fp32 residual stream x: RESID_F32, BIAS_F32 or PATCH_EMBED epilogue):
+ *   xb_out bf16 [rows][N] receives bf16(x), ln_stats_out f32 [N/32][rows][2] (chunk-major, so warps access it coalesced) the (sum, sum of squares) of every
+ *   32-column chunk of every row (fp32 values, before rounding).  For PATCH_EMBED rows = B*197.
+ * CONSUMER side (the GEMM that follows the LayerNorm: BIAS_BF16, BIAS_GELU_BF16 or QKV_SPLIT epilogue): A = xb,
+ *   W = bf16(gamma . W), bias = b + W beta, ln_stats_in = the producer's buffer (K/32 chunks per row, summed in a fixed
+ *   order: deterministic), ln_colsum f32 [N] (computed from the ROUNDED folded weight), ln_eps.
+ * Either side may be used alone (pass NULL for the other side's pointers).  Only the CTA-pair kernel has these epilogues:
+ * M >= MDE_GEMM_LN_MIN_ROWS and N % 256 == 0, otherwise MDE_ERR_UNSUPPORTED (use mde_layernorm_bf16 + mde_gemm_bf16). */
+#define MDE_GEMM_LN_MIN_ROWS 1024
+int mde_gemm_ln_bf16(const mde_bf16* A, int lda, const mde_bf16* W, int ldw, int M, int N, int K, int epilogue,
+                     const float* bias, void* out, int ldo, const void* aux0, const void* aux1,
+                     const float* ln_stats_in, const float* ln_colsum, float ln_eps, mde_bf16* xb_out, float* ln_stats_out,
+                     mde_stream_t stream);
+
+/* Development hook (tools/gemm_prof.py): while `counters` (device, 8 x int64 per CTA, zeroed by the caller) is set, the
+ * CTA-pair GEMM adds clock64 deltas per CTA: [0] MMA thread waiting for a free accumulator, [1] MMA thread waiting for
+ * operands, [2] epilogue warp waiting for an accumulator, [3] epilogue warp working, [4] tiles, [5] CTA lifetime.
+ * Pass NULL to switch it off. */
+int mde_debug_gemm_prof(long long* counters);
+
 /* ---- LayerNorm over the last dim (tv:112,117; eps 1e-6), fp32 in, bf16 out ------------- */
 int mde_layernorm_bf16(const float* x, int rows, int dim, const float* gamma, const float* beta, float eps,
                        mde_bf16* out, mde_stream_t stream);

@@ -11,7 +11,7 @@ import os
 import threading
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-SO_PATH = os.path.join(HERE, "libmde.so")
+SO_PATH = os.environ.get("MDE_LIB_PATH") or os.path.join(HERE, "libmde.so")  # MDE_LIB_PATH: A/B builds during kernel work
 
 MDE_OK = 0
 EPI_BIAS_BF16, EPI_BIAS_GELU_BF16, EPI_BIAS_RESID_F32, EPI_BIAS_F32, EPI_PATCH_EMBED, EPI_QKV_SPLIT = range(6)
@@ -19,6 +19,7 @@ ACT_NONE, ACT_ELU, ACT_SIGMOID = range(3)
 PAD_REFLECT, PAD_ZERO = range(2)
 VIT_SEQ, VIT_DIM, VIT_HEADS, VT_PITCH = 197, 768, 12, 208
 RANGE_SCRATCH_FLOATS = 6 * 8192
+GEMM_LN_MIN_ROWS = 1024  # MDE_GEMM_LN_MIN_ROWS
 MAX_MAPS = 8
 MAX_FUSION_SCALES = 4
 
@@ -41,6 +42,8 @@ SIGNATURES = {
     "mde_preprocess_patchify": [_p, _i, _i, _i, _p, _p, _p],
     "mde_input_stage": [_p, _i, _i, _i, _p, _f, _p, _p, _p, _p, _p],
     "mde_gemm_bf16": [_p, _i, _p, _i, _i, _i, _i, _i, _p, _p, _i, _p, _p, _p],
+    "mde_debug_gemm_prof": [_p],
+    "mde_gemm_ln_bf16": [_p, _i, _p, _i, _i, _i, _i, _i, _p, _p, _i, _p, _p, _p, _p, _f, _p, _p, _p],
     "mde_layernorm_bf16": [_p, _i, _i, _p, _p, _f, _p, _p],
     "mde_vit_attention": [_p, _p, _p, _i, _p, _p],
     "mde_tokens_to_grid_bf16": [_p, _i, _i, _i, _p, _p],

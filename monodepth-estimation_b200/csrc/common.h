@@ -51,8 +51,18 @@ int encode_tmap(CUtensorMap* out, int elt_bytes, const void* base, int rank, con
                 const uint64_t* strides_bytes, const uint32_t* box, int swizzle_bytes);
 
 // 2-CTA (cta_group::2) GEMM path of mde_gemm_bf16 (tc_gemm2.cu); same contract, needs N % 256 == 0.
+// LayerNorm folded into the GEMMs on either side of it (mde_gemm_ln_bf16): a producer (residual / patch-embed epilogue)
+// also writes a bf16 copy of its fp32 output and per-row partial sums; a consumer (QKV / fc1) reads A = that bf16 copy
+// and applies (acc - mean*colsum) * rstd + bias in its epilogue.  All pointers optional (null = not used).
+struct LnFuse {
+  const float* stats_in;  // consumer: [K/32][M][2] (slot-major) partial (sum, sum of squares) per 32-column chunk of the normalised row
+  const float* colsum;    // consumer: [N] sum over k of the (gamma-folded, bf16-rounded) weight row
+  float eps;
+  void* xb_out;           // producer: bf16 [M][N] copy of the fp32 output
+  float* stats_out;       // producer: [N/32][M][2]
+};
 int launch_gemm_pair(const void* A, int lda, const void* W, int ldw, int M, int N, int K, int epilogue, const float* bias, void* out, int ldo,
-                     const void* aux0, const void* aux1, cudaStream_t stream);
+                     const void* aux0, const void* aux1, const LnFuse* ln, cudaStream_t stream);
 
 // Halo-resident 3x3 conv path of mde_conv_nhwc (conv_halo.cu).  MDE_OK = launched; MDE_ERR_UNSUPPORTED (no error text) =
 // geometry not served there, the caller uses the tap-shifted kernel.

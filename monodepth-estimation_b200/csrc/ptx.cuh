@@ -294,15 +294,23 @@ __device__ __forceinline__ float erf_as(float x) {
   return copysignf(fmaf(-p, e, 1.0f), x);
 }
 __device__ __forceinline__ float gelu_erf(float x) { return 0.5f * x * (1.0f + erf_as(x * 0.70710678118654752f)); }
-// Exact-erf GELU for a bf16 destination:  gelu(x) = x * Phi(x),  Phi(x) ~= sigmoid(x * (c0 + c1 x^2 + c2 x^4)), minimax fit of
-// x*Phi(x) on [-9, 9]: max |error| 2.5e-5 (bf16 half-ulp is 2e-3 relative), well conditioned for negative x (no 1+erf
-// cancellation).  9 instructions, 2 of them SFU (ex2, rcp) against ~20 for gelu_erf: the fc1 epilogue is ALU-bound.
-// The coefficients carry the factor -log2(e); x^2 is clamped where the sigmoid has saturated (keeps the quartic monotone).
+// Exact-erf GELU for a bf16 destination:  gelu(x) = x * Phi(x),  Phi(x) ~= sigmoid(x * (c0 + c1 x^2 + c2 x^4)) = 0.5 + 0.5 tanh(x/2 * (...)),
+// minimax fit of x*Phi(x) on [-9, 9]: max |error| 2.5e-5 in exact arithmetic.  tanh.approx.f32 (relative error 2^-11) adds at
+// most |x| * 2.4e-4 in the negative tail, where bf16 outputs of neighbouring magnitude already carry more rounding noise (half-ulp
+// is 2e-3 relative).  8 instructions with ONE SFU op: the fc1 epilogue (128 values per thread and tile) is bound by the
+// 16-lane SFU pipe — ex2 + rcp (r01f) took 5.0 us per 128x256 tile against 4.2 us of MMAs (in-kernel clock counters, tools/gemm_bench.py).
+// The coefficients carry the factor 1/2; x^2 is clamped where Phi has saturated (keeps the quartic monotone).
+__device__ __forceinline__ float fast_tanh(float x) {
+  float y;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
 __device__ __forceinline__ float gelu_fast(float x) {
   const float x2 = fminf(x * x, 50.0f);
-  float q = fmaf(x2, 1.0142630e-3f, -1.0677571e-1f);  // -log2e * (c2 x^2 + c1)
-  q = fmaf(q, x2, -2.3011213f);                        // -log2e * c0
-  return x * fast_rcp(1.0f + fast_ex2(x * q));
+  float q = fmaf(x2, -3.5151677e-4f, 3.7005641e-2f);  // (c2 x^2 + c1) / 2
+  q = fmaf(q, x2, 7.9750787e-1f);                      // c0 / 2 (= sqrt(2/pi) up to the fit)
+  const float h = 0.5f * x;
+  return fmaf(h, fast_tanh(x * q), h);
 }
 // one MUFU each (ex2.approx.ftz / rcp.approx.ftz), no denormal-scaling branches: the conv epilogues are issue-bound (r01v)
 __device__ __forceinline__ float elu1(float x) { return x > 0.0f ? x : fast_ex2(x * 1.4426950408889634f) - 1.0f; }

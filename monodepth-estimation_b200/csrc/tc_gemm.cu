@@ -43,6 +43,10 @@ struct alignas(64) TcParams {
   int cout, out_cstride, out_coff;
   int f16;   // operands (and bf16-slot outputs) are fp16 instead of bf16
   int st32;  // conv bf16/fp16 output: 32-byte stores are legal (alignment, cout % 16 == 0)
+  // LayerNorm fusion (pair kernel only; always null here, the shared patch-embed epilogue refers to them)
+  void* xb;
+  float* ln_out;
+  int ln_rows;
 };
 
 // co-resident CTAs per SM the register budget is compiled for (small tiles hide latency with more CTAs)
@@ -267,9 +271,8 @@ static int dispatch_tc(TcParams& p, int block_n, int rowb, cudaStream_t stream) 
 
 using namespace mde;
 
-extern "C" int mde_gemm_bf16(const mde_bf16* A, int lda, const mde_bf16* W, int ldw, int M, int N, int K, int epilogue,
-                             const float* bias, void* out, int ldo, const void* aux0, const void* aux1,
-                             mde_stream_t stream) {
+static int gemm_impl(const mde_bf16* A, int lda, const mde_bf16* W, int ldw, int M, int N, int K, int epilogue, const float* bias, void* out, int ldo,
+                     const void* aux0, const void* aux1, const LnFuse* ln, mde_stream_t stream) {
   MDE_CHECK_ARG(A && W && bias && out, "mde_gemm_bf16: null pointer");
   MDE_CHECK_ARG(M > 0 && N > 0 && K > 0, "mde_gemm_bf16: empty problem M=%d N=%d K=%d", M, N, K);
   MDE_CHECK_ARG(K % 64 == 0 && N % 128 == 0, "mde_gemm_bf16: need K %% 64 == 0 and N %% 128 == 0 (K=%d N=%d)", K, N);
@@ -289,7 +292,11 @@ extern "C" int mde_gemm_bf16(const mde_bf16* A, int lda, const mde_bf16* W, int 
 
   // large problems run on CTA pairs (tc_gemm2.cu); MDE_GEMM_1CTA=1 forces the single-CTA kernel (A/B testing)
   static const bool force_1cta = getenv("MDE_GEMM_1CTA") != nullptr && getenv("MDE_GEMM_1CTA")[0] == '1';
-  if (!force_1cta && N % 256 == 0 && M >= 1024) return launch_gemm_pair(A, lda, W, ldw, M, N, K, epilogue, bias, out, ldo, aux0, aux1, stream);
+  if (!force_1cta && N % 256 == 0 && M >= MDE_GEMM_LN_MIN_ROWS) return launch_gemm_pair(A, lda, W, ldw, M, N, K, epilogue, bias, out, ldo, aux0, aux1, ln, stream);
+  if (ln) {
+    set_error("mde_gemm_ln_bf16: the LayerNorm-fused epilogues exist in the CTA-pair kernel only (M >= %d, N %% 256 == 0; M=%d N=%d)", MDE_GEMM_LN_MIN_ROWS, M, N);
+    return MDE_ERR_UNSUPPORTED;
+  }
 
   TcParams p;
   memset(&p, 0, sizeof(p));
@@ -324,6 +331,25 @@ extern "C" int mde_gemm_bf16(const mde_bf16* A, int lda, const mde_bf16* W, int 
   p.aux0 = aux0;
   p.aux1 = aux1;
   return dispatch_tc(p, block_n, 128, stream);
+}
+
+extern "C" int mde_gemm_bf16(const mde_bf16* A, int lda, const mde_bf16* W, int ldw, int M, int N, int K, int epilogue,
+                             const float* bias, void* out, int ldo, const void* aux0, const void* aux1,
+                             mde_stream_t stream) {
+  return gemm_impl(A, lda, W, ldw, M, N, K, epilogue, bias, out, ldo, aux0, aux1, nullptr, stream);
+}
+
+extern "C" int mde_gemm_ln_bf16(const mde_bf16* A, int lda, const mde_bf16* W, int ldw, int M, int N, int K, int epilogue,
+                                const float* bias, void* out, int ldo, const void* aux0, const void* aux1, const float* ln_stats_in,
+                                const float* ln_colsum, float ln_eps, mde_bf16* xb_out, float* ln_stats_out, mde_stream_t stream) {
+  LnFuse ln;
+  ln.stats_in = ln_stats_in;
+  ln.colsum = ln_colsum;
+  ln.eps = ln_eps;
+  ln.xb_out = xb_out;
+  ln.stats_out = ln_stats_out;
+  const bool any = ln_stats_in || ln_colsum || xb_out || ln_stats_out;
+  return gemm_impl(A, lda, W, ldw, M, N, K, epilogue, bias, out, ldo, aux0, aux1, any ? &ln : nullptr, stream);
 }
 
 static int conv_nhwc_impl(int f16, const mde_bf16* in, int B, int h, int w, int cin, int in_cstride, const mde_bf16* wpacked, const float* bias,

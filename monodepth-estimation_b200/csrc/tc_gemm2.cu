@@ -21,6 +21,7 @@
 // one chunk ahead, bias/activation/residual are applied in place, and a TMA STORE (bulk group) writes it out while
 // the warp is already on its next chunk.  No LSU global traffic, full-line writes, rows >= M clipped by the tensor map.
 #include <stdio.h>
+#include <stdlib.h>
 
 #include <algorithm>
 
@@ -62,7 +63,18 @@ struct alignas(64) Tc2Params {
   const void* aux0;
   const void* aux1;
   int cout, h, w, out_cstride, out_coff, f16, st32;
+  // LayerNorm fusion (see LnFuse in common.h)
+  void* xb;             // producer: bf16 copy of the fp32 output, row pitch xb_ld
+  float* ln_out;        // producer: [N/32][ln_rows][2] partial (sum, sum of squares) per 32-column chunk (slot-major: coalesced)
+  int ln_rows, xb_ld;
+  const float* ln_in;   // consumer: [ln_slots = K/32][M][2]
+  const float* ln_cs;   // consumer: [N] column sums of the folded weight
+  int ln_slots;
+  float ln_eps, ln_invk;
+  long long* prof;      // debug (mde_debug_gemm_prof): per CTA 8 counters of cycles spent waiting / working, or null
 };
+
+__device__ __forceinline__ long long clk() { return clock64(); }
 
 struct Item {
   int m0, n0, bn;
@@ -132,6 +144,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(k2Threads, 1) tc_gem
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   pdl_grid_wait();  // everything above (barriers, TMEM, descriptor prefetch) overlaps the previous kernel's tail
+  long long t_start = 0;
+  if (p.prof && threadIdx.x == 0) t_start = clk();
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer (both CTAs)
@@ -164,11 +178,16 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(k2Threads, 1) tc_gem
       for (int i = cluster_id; i < p.total_items; i += num_clusters) {
         const Item it = decode_item(p, i);
         const uint32_t idesc = umma_idesc_bf16(256, it.bn);
+        long long t0 = 0;
+        if (p.prof) t0 = clk();
         mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
+        if (p.prof) p.prof[blockIdx.x * 8 + 0] += clk() - t0;  // MMA thread waiting for a free accumulator (epilogue behind)
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * 256;
         for (int kb = 0; kb < p.k_blocks; ++kb) {
+          if (p.prof) t0 = clk();
           mbar_wait(&full_bar[stage], phase);
+          if (p.prof) p.prof[blockIdx.x * 8 + 1] += clk() - t0;  // MMA thread waiting for operands (TMA behind)
           tc_fence_after();
           const uint32_t sa = smem_u32(smem + (size_t)stage * k2StageBytes);
           const uint64_t da = umma_smem_desc_kmajor<128>(sa);
@@ -217,7 +236,33 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(k2Threads, 1) tc_gem
         const Item itn = decode_item(p, has_next ? inext : i);
         const int nch = it.bn / cw;
         const int row0 = it.m0 + (int)rank * 128 + q * 32;
+        float mu = 0.0f, rstd = 1.0f;  // LayerNorm of this thread's A row, from the producer's partial sums (fixed order: deterministic)
+        if (p.ln_in && row0 + lane < p.M) {
+          // slot-major [K/32][M][2]: a warp reads 32 consecutive rows of one slot = 256 contiguous bytes per instruction
+          const float2* st = reinterpret_cast<const float2*>(p.ln_in) + (row0 + lane);
+          float s1 = 0.0f, s2 = 0.0f;
+          for (int t0 = 0; t0 < p.ln_slots; t0 += 8) {  // eight independent loads in flight (host checked ln_slots % 8 == 0), summed in slot order
+            float2 a[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) a[u] = __ldg(st + (size_t)(t0 + u) * p.M);
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+              s1 += a[u].x;
+              s2 += a[u].y;
+            }
+          }
+          mu = s1 * p.ln_invk;
+          rstd = rsqrtf(fmaxf(fmaf(-mu, mu, s2 * p.ln_invk), 0.0f) + p.ln_eps);
+        }
+        long long t0 = 0;
+        const bool prof = p.prof && warp == 2 && lane == 0;
+        if (prof) t0 = clk();
         mbar_wait(&tfull_bar[acc], acc_phase);
+        if (prof) {
+          const long long t1 = clk();
+          p.prof[blockIdx.x * 8 + 2] += t1 - t0;  // epilogue warp 2 waiting for the accumulator (MMA behind)
+          t0 = t1;
+        }
         tc_fence_after();
         const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * 256;
 #pragma unroll 1
@@ -269,6 +314,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(k2Threads, 1) tc_gem
             __syncwarp();
             tmem_ld_wait();
             const float4* bp = reinterpret_cast<const float4*>(p.bias + n0);
+            const bool lnc = p.ln_in != nullptr;  // LayerNorm consumer: (acc - mean * colsum) * rstd + bias
+            const float4* csp = reinterpret_cast<const float4*>(p.ln_cs + n0);
             const bool gelu = p.epi == MDE_EPI_BIAS_GELU_BF16;
             const int which = p.epi == MDE_EPI_QKV_SPLIT ? n0 / MDE_VIT_DIM : 0;  // 0 q, 1 k, 2 v (uniform per 64-column chunk)
             if (which == 2) {
@@ -281,10 +328,15 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(k2Threads, 1) tc_gem
 #pragma unroll
                 for (int j = 0; j < 16; ++j) {
                   const float4 b4 = __ldg(bp + j);
-                  dst[(size_t)(4 * j) * MDE_VT_PITCH] = __float2bfloat16_rn(__uint_as_float(raw[4 * j]) + b4.x);
-                  dst[(size_t)(4 * j + 1) * MDE_VT_PITCH] = __float2bfloat16_rn(__uint_as_float(raw[4 * j + 1]) + b4.y);
-                  dst[(size_t)(4 * j + 2) * MDE_VT_PITCH] = __float2bfloat16_rn(__uint_as_float(raw[4 * j + 2]) + b4.z);
-                  dst[(size_t)(4 * j + 3) * MDE_VT_PITCH] = __float2bfloat16_rn(__uint_as_float(raw[4 * j + 3]) + b4.w);
+                  float4 a4 = make_float4(__uint_as_float(raw[4 * j]), __uint_as_float(raw[4 * j + 1]), __uint_as_float(raw[4 * j + 2]), __uint_as_float(raw[4 * j + 3]));
+                  if (lnc) {
+                    const float4 c4 = __ldg(csp + j);
+                    a4 = make_float4(fmaf(-mu, c4.x, a4.x) * rstd, fmaf(-mu, c4.y, a4.y) * rstd, fmaf(-mu, c4.z, a4.z) * rstd, fmaf(-mu, c4.w, a4.w) * rstd);
+                  }
+                  dst[(size_t)(4 * j) * MDE_VT_PITCH] = __float2bfloat16_rn(a4.x + b4.x);
+                  dst[(size_t)(4 * j + 1) * MDE_VT_PITCH] = __float2bfloat16_rn(a4.y + b4.y);
+                  dst[(size_t)(4 * j + 2) * MDE_VT_PITCH] = __float2bfloat16_rn(a4.z + b4.z);
+                  dst[(size_t)(4 * j + 3) * MDE_VT_PITCH] = __float2bfloat16_rn(a4.w + b4.w);
                 }
               }
               continue;  // nothing staged, no TMA store for this chunk (g is advanced by the loop header)
@@ -293,15 +345,28 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(k2Threads, 1) tc_gem
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
               const float4 b0 = __ldg(bp + 2 * j), b1 = __ldg(bp + 2 * j + 1);
-              float v[8] = {__uint_as_float(raw[8 * j]) + b0.x,     __uint_as_float(raw[8 * j + 1]) + b0.y, __uint_as_float(raw[8 * j + 2]) + b0.z,
-                            __uint_as_float(raw[8 * j + 3]) + b0.w, __uint_as_float(raw[8 * j + 4]) + b1.x, __uint_as_float(raw[8 * j + 5]) + b1.y,
-                            __uint_as_float(raw[8 * j + 6]) + b1.z, __uint_as_float(raw[8 * j + 7]) + b1.w};
+              float v[8];
+#pragma unroll
+              for (int t = 0; t < 8; ++t) v[t] = __uint_as_float(raw[8 * j + t]);
+              if (lnc) {
+                const float4 c0 = __ldg(csp + 2 * j), c1 = __ldg(csp + 2 * j + 1);
+                const float cs[8] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w};
+#pragma unroll
+                for (int t = 0; t < 8; ++t) v[t] = fmaf(-mu, cs[t], v[t]) * rstd;
+              }
+              {
+                const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+#pragma unroll
+                for (int t = 0; t < 8; ++t) v[t] += bb[t];
+              }
               if (gelu) {
 #pragma unroll
                 for (int t = 0; t < 8; ++t) v[t] = gelu_fast(v[t]);
               }
+              if (qs != 1.0f) {
 #pragma unroll
-              for (int t = 0; t < 8; ++t) v[t] *= qs;
+                for (int t = 0; t < 8; ++t) v[t] *= qs;
+              }
               *reinterpret_cast<uint4*>(row + ((static_cast<uint32_t>(j) ^ sw) << 4)) =
                   make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
             }
@@ -317,10 +382,39 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(k2Threads, 1) tc_gem
             }
             bulk_commit();
           }
+          if (p.xb) {
+            // LayerNorm producer: bf16 copy of the staged fp32 chunk, read back with lane = four columns so that a warp store
+            // covers four 64-byte row segments (a row-per-thread store would touch 32 lines per instruction), plus the
+            // row's partial sums.  The staged tile is only read here and by the TMA store.
+            bf16* xb = reinterpret_cast<bf16*>(p.xb);
+            const int cc = (lane & 7) * 4;  // lane = four columns: a warp store covers four 64-byte row segments
+#pragma unroll
+            for (int t = 0; t < 8; ++t) {
+              const int rr = 4 * t + (lane >> 3);
+              const float4 f = *reinterpret_cast<const float4*>(buf + rr * 128 + ((static_cast<uint32_t>(lane & 7) ^ (rr & 7)) << 4));
+              if (row0 + rr < p.M)
+                *reinterpret_cast<uint2*>(xb + (size_t)(row0 + rr) * p.xb_ld + n0 + cc) = make_uint2(pack_bf16x2(f.x, f.y), pack_bf16x2(f.z, f.w));
+            }
+            if (row0 + lane < p.M) {  // this thread's own row, re-read from the staged tile (keeps the common path free of the sums)
+              float ls1 = 0.0f, ls2 = 0.0f;
+#pragma unroll
+              for (int j = 0; j < 8; ++j) {
+                const float4 o = *reinterpret_cast<const float4*>(row + ((static_cast<uint32_t>(j) ^ sw) << 4));  // logical column order: the sums do not depend on the lane
+                ls1 += (o.x + o.y) + (o.z + o.w);
+                ls2 = fmaf(o.x, o.x, fmaf(o.y, o.y, fmaf(o.z, o.z, fmaf(o.w, o.w, ls2))));
+              }
+              *reinterpret_cast<float2*>(p.ln_out + ((size_t)(n0 >> 5) * p.M + (row0 + lane)) * 2) = make_float2(ls1, ls2);
+            }
+            __syncwarp();  // every lane has read the tile before lane 0 may recycle the buffer
+          }
         }
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive_cluster(&tempty_bar[acc], 0);  // the leader's MMA thread owns the accumulator ring
+        if (prof) {
+          p.prof[blockIdx.x * 8 + 3] += clk() - t0;  // epilogue warp 2 working on the tile
+          p.prof[blockIdx.x * 8 + 4] += 1;           // tiles
+        }
         acc ^= 1;
         if (acc == 0) acc_phase ^= 1;
         i = inext;
@@ -358,6 +452,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(k2Threads, 1) tc_gem
     }
   }
 
+  if (p.prof && threadIdx.x == 0) p.prof[blockIdx.x * 8 + 5] += clk() - t_start;  // CTA lifetime after the dependency wait
   tc_fence_before();
   cluster_sync_all();  // both CTAs are done with each other's shared memory / TMEM
   tc_fence_after();
@@ -365,10 +460,37 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(k2Threads, 1) tc_gem
 }
 
 // ------------------------------------------------------------------------------------ host side
+long long* g_gemm_prof = nullptr;  // set by mde_debug_gemm_prof (tools/gemm_prof.py)
+
 int launch_gemm_pair(const void* A, int lda, const void* W, int ldw, int M, int N, int K, int epilogue, const float* bias, void* out, int ldo,
-                     const void* aux0, const void* aux1, cudaStream_t stream) {
+                     const void* aux0, const void* aux1, const LnFuse* ln, cudaStream_t stream) {
   Tc2Params p;
   memset(&p, 0, sizeof(p));
+  if (ln) {
+    const bool f32res = epilogue == MDE_EPI_BIAS_RESID_F32 || epilogue == MDE_EPI_BIAS_F32 || epilogue == MDE_EPI_PATCH_EMBED;
+    if (ln->xb_out || ln->stats_out) {  // producer
+      if (!(ln->xb_out && ln->stats_out) || !f32res || N % 64 != 0 || (uintptr_t)ln->xb_out % 16 || (uintptr_t)ln->stats_out % 16) {
+        set_error("mde_gemm_ln_bf16: xb_out + stats_out need an fp32 epilogue (RESID_F32 / BIAS_F32 / PATCH_EMBED), N %% 64 == 0, 16-byte alignment");
+        return MDE_ERR_BAD_ARGUMENT;
+      }
+      p.xb = ln->xb_out;
+      p.ln_out = ln->stats_out;
+      p.ln_rows = epilogue == MDE_EPI_PATCH_EMBED ? M / 196 * MDE_VIT_SEQ : M;
+      p.xb_ld = N;
+    }
+    if (ln->stats_in || ln->colsum) {  // consumer
+      const bool b16 = epilogue == MDE_EPI_BIAS_BF16 || epilogue == MDE_EPI_BIAS_GELU_BF16 || epilogue == MDE_EPI_QKV_SPLIT;
+      if (!(ln->stats_in && ln->colsum) || !b16 || K % 256 != 0 || (uintptr_t)ln->stats_in % 16 || (uintptr_t)ln->colsum % 16) {
+        set_error("mde_gemm_ln_bf16: stats_in + colsum need a bf16 epilogue (BIAS_BF16 / BIAS_GELU_BF16 / QKV_SPLIT), K %% 256 == 0, 16-byte alignment");
+        return MDE_ERR_BAD_ARGUMENT;
+      }
+      p.ln_in = ln->stats_in;
+      p.ln_cs = ln->colsum;
+      p.ln_slots = K / 32;
+      p.ln_eps = ln->eps;
+      p.ln_invk = 1.0f / (float)K;
+    }
+  }
   {
     const uint64_t dims[2] = {(uint64_t)K, (uint64_t)M};
     const uint64_t strides[1] = {(uint64_t)lda * 2};
@@ -418,9 +540,12 @@ int launch_gemm_pair(const void* A, int lda, const void* W, int ldw, int M, int 
     rc = encode_tmap(&p.tmRes, p.out_elt, second, 2, dims, strides, box, 128);
     if (rc != MDE_OK) return rc;
   }
+  p.prof = g_gemm_prof;
   const int smem_max = 227 * 1024;
   int stages = (smem_max - 1024 - k2StagingBytes - k2BarrierBytes) / k2StageBytes;
   if (stages > k2MaxStages) stages = k2MaxStages;
+  static const int stages_env = getenv("MDE_GEMM_STAGES") ? atoi(getenv("MDE_GEMM_STAGES")) : 0;  // experiments: fewer pipeline stages
+  if (stages_env > 0 && stages_env < stages) stages = stages_env;
   p.stages = stages;
   const int smem_bytes = stages * k2StageBytes + k2StagingBytes + 1024 + k2BarrierBytes;
   static bool attr_set = false;
@@ -435,3 +560,8 @@ int launch_gemm_pair(const void* A, int lda, const void* W, int ldw, int M, int 
 }
 
 }  // namespace mde
+
+extern "C" int mde_debug_gemm_prof(long long* counters) {
+  mde::g_gemm_prof = counters;  // device buffer of 8 counters per CTA (zeroed by the caller), or null to switch the counters off
+  return MDE_OK;
+}

@@ -38,6 +38,8 @@ def _fingerprint(module):
     return tuple((t.data_ptr(), t._version, t.device.index) for t in list(module.parameters()) + list(module.buffers()))
 
 
+_LN_FUSION = os.environ.get("MDE_LN_FUSION") == "1"  # opt-in, see DepthEngine._vit
+
 class Workspace:
     """All intermediates of one forward for a fixed (B, Hp, Wp); allocated once."""
 
@@ -62,6 +64,7 @@ class Workspace:
         self.xa, self.xb = e(M, 768, dt=F32), e(M, 768, dt=F32)
         self.taps = [e(M, 768, dt=F32) for _ in range(4)]
         self.h = e(M, 768)
+        self.lnstats = e(24, M, 2, dt=F32)  # per-row (sum, sum of squares) partials of the residual stream (LayerNorm fused into the GEMMs)
         self.q, self.k = e(B * 12 * L.VIT_SEQ * 64), e(B * 12 * L.VIT_SEQ * 64)
         self.vt = z(B * 12 * 64 * L.VT_PITCH)
         self.attn = e(M, 768)
@@ -158,7 +161,16 @@ class DepthEngine:
     def _vit(self, ws, w, want=None, on_tap=None):
         enc, B = w["enc"], ws.B
         n = 0
-        ops.gemm(ws.patches, enc["patch_w"], enc["patch_b"], L.EPI_PATCH_EMBED, ws.xa, enc["pos"], enc["cls"])
+        # Optional (MDE_LN_FUSION=1): LayerNorm folded into the GEMMs around it when the CTA-pair kernel runs (M >= 1024) — the
+        # producer of the residual stream also writes bf16(x) into ws.h and per-row partial sums, the QKV / fc1 epilogues
+        # normalise.  24 launches fewer, parity-tested, but measured a wash at B=32 (2.456 vs 2.447 ms): the producers are
+        # single-wave GEMMs whose epilogue is exposed (+3.3 us each), the consumers reload row statistics per tile (+5.5 us).
+        fused = ws.B * 197 >= L.GEMM_LN_MIN_ROWS and _LN_FUSION
+        prod = dict(xb_out=ws.h, stats_out=ws.lnstats) if fused else {}
+        if fused:
+            ops.gemm_ln(ws.patches, enc["patch_w"], enc["patch_b"], L.EPI_PATCH_EMBED, ws.xa, enc["pos"], enc["cls"], **prod)
+        else:
+            ops.gemm(ws.patches, enc["patch_w"], enc["patch_b"], L.EPI_PATCH_EMBED, ws.xa, enc["pos"], enc["cls"])
         n += 1
         # residual stream: x_in --(attention)--> x_mid --(MLP)--> x_out.  x_in is dead once the out-proj
         # epilogue has read it, so two working buffers suffice; hooked layers (encoder.py:44-50) write
@@ -168,14 +180,24 @@ class DepthEngine:
         for i, ly in enumerate(enc["layers"]):
             x_mid = work[1] if x_in is work[0] else work[0]
             x_out = ws.taps[HOOKS.index(i)] if i in HOOKS else (work[0] if x_mid is work[1] else work[1])
-            ops.layernorm(x_in, ly["ln1_w"], ly["ln1_b"], 1e-6, ws.h)
-            ops.gemm(ws.h, ly["qkv_w"], ly["qkv_b"], L.EPI_QKV_SPLIT, ws.q, ws.k, ws.vt)
-            ops.vit_attention(ws.q, ws.k, ws.vt, B, ws.attn)
-            ops.gemm(ws.attn, ly["proj_w"], ly["proj_b"], L.EPI_BIAS_RESID_F32, x_mid, x_in)
-            ops.layernorm(x_mid, ly["ln2_w"], ly["ln2_b"], 1e-6, ws.h)
-            ops.gemm(ws.h, ly["fc1_w"], ly["fc1_b"], L.EPI_BIAS_GELU_BF16, ws.mlp)
-            ops.gemm(ws.mlp, ly["fc2_w"], ly["fc2_b"], L.EPI_BIAS_RESID_F32, x_out, x_mid)
-            n += 7
+            if fused:
+                qw, qb, qcs = ly["qkv_ln"]
+                fw, fb, fcs = ly["fc1_ln"]
+                ops.gemm_ln(ws.h, qw, qb, L.EPI_QKV_SPLIT, ws.q, ws.k, ws.vt, stats_in=ws.lnstats, colsum=qcs)
+                ops.vit_attention(ws.q, ws.k, ws.vt, B, ws.attn)
+                ops.gemm_ln(ws.attn, ly["proj_w"], ly["proj_b"], L.EPI_BIAS_RESID_F32, x_mid, x_in, **prod)
+                ops.gemm_ln(ws.h, fw, fb, L.EPI_BIAS_GELU_BF16, ws.mlp, stats_in=ws.lnstats, colsum=fcs)
+                ops.gemm_ln(ws.mlp, ly["fc2_w"], ly["fc2_b"], L.EPI_BIAS_RESID_F32, x_out, x_mid, **prod)
+                n += 5
+            else:
+                ops.layernorm(x_in, ly["ln1_w"], ly["ln1_b"], 1e-6, ws.h)
+                ops.gemm(ws.h, ly["qkv_w"], ly["qkv_b"], L.EPI_QKV_SPLIT, ws.q, ws.k, ws.vt)
+                ops.vit_attention(ws.q, ws.k, ws.vt, B, ws.attn)
+                ops.gemm(ws.attn, ly["proj_w"], ly["proj_b"], L.EPI_BIAS_RESID_F32, x_mid, x_in)
+                ops.layernorm(x_mid, ly["ln2_w"], ly["ln2_b"], 1e-6, ws.h)
+                ops.gemm(ws.h, ly["fc1_w"], ly["fc1_b"], L.EPI_BIAS_GELU_BF16, ws.mlp)
+                ops.gemm(ws.mlp, ly["fc2_w"], ly["fc2_b"], L.EPI_BIAS_RESID_F32, x_out, x_mid)
+                n += 7
             if want is not None and i == 0:
                 want["block0_q"] = ws.q.clone()
                 want["block0_attn"] = ws.attn.clone()

@@ -73,6 +73,17 @@ def gemm(a, w, bias, epilogue, out, aux0=None, aux1=None, M=None):
     return out
 
 
+def gemm_ln(a, w, bias, epilogue, out, aux0=None, aux1=None, stats_in=None, colsum=None, eps=1e-6, xb_out=None, stats_out=None):
+    """``gemm`` with the neighbouring LayerNorm folded in (``mde_gemm_ln_bf16``): a producer passes ``xb_out`` + ``stats_out``,
+    a consumer ``stats_in`` + ``colsum`` (and ``a`` = the producer's ``xb_out``, ``w``/``bias`` folded by ``packing.fold_layernorm``)."""
+    M, K = a.shape
+    N = w.shape[0]
+    ldo = out.shape[-1] if epilogue <= L.EPI_BIAS_F32 else 0
+    L.call("mde_gemm_ln_bf16", _ptr(a, BF16), a.stride(0), _ptr(w, BF16), w.stride(0), M, N, K, epilogue, _ptr(bias, F32), _ptr(out), ldo,
+           _ptr(aux0), _ptr(aux1), _ptr(stats_in, F32), _ptr(colsum, F32), float(eps), _ptr(xb_out, BF16), _ptr(stats_out, F32), _stream())
+    return out
+
+
 def layernorm(x, gamma, beta, eps, out=None):
     rows, dim = x.shape
     out = out if out is not None else torch.empty(rows, dim, device=x.device, dtype=BF16)

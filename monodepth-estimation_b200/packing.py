@@ -50,6 +50,19 @@ def pack_linear(weight, bias, n_mult=128):
     return w, b
 
 
+def fold_layernorm(weight, bias, gamma, beta, n_mult=128):
+    """LayerNorm folded into the linear layer that follows it (``mde_gemm_ln_bf16`` consumer side):
+    LN(x) W^T + b = rstd * (x (gamma.W)^T - mean * colsum) + (b + W beta).
+    Returns (bf16 gamma.W [N,K], f32 b + W beta [N], f32 colsum [N]); colsum is taken over the ROUNDED weight so that the
+    mean term cancels exactly what the tensor cores accumulate."""
+    w = weight.detach().to(F32).reshape(weight.shape[0], -1)
+    g, be = gamma.detach().to(F32), beta.detach().to(F32)
+    wf = _pad_rows(w * g.view(1, -1), n_mult).to(BF16).contiguous()
+    b = _pad_rows((bias.detach().to(F32) + w @ be).view(-1, 1), n_mult).view(-1).contiguous()
+    cs = wf.to(torch.float64).sum(1).to(F32).contiguous()
+    return wf, b, cs
+
+
 def pack_encoder(sd, p="encoder."):
     """ViT-B/16 + channel_reduce + input BN (encoder.py:16-58)."""
     f = lambda k: sd[p + k].detach().to(F32).contiguous()
@@ -66,6 +79,9 @@ def pack_encoder(sd, p="encoder."):
         ly["proj_w"], ly["proj_b"] = pack_linear(sd[p + q + "self_attention.out_proj.weight"], sd[p + q + "self_attention.out_proj.bias"])
         ly["fc1_w"], ly["fc1_b"] = pack_linear(sd[p + q + "mlp.0.weight"], sd[p + q + "mlp.0.bias"])
         ly["fc2_w"], ly["fc2_b"] = pack_linear(sd[p + q + "mlp.3.weight"], sd[p + q + "mlp.3.bias"])
+        # the same two layers with ln_1 / ln_2 folded in (used when the batch is large enough for the CTA-pair GEMM)
+        ly["qkv_ln"] = fold_layernorm(sd[p + q + "self_attention.in_proj_weight"], sd[p + q + "self_attention.in_proj_bias"], ly["ln1_w"], ly["ln1_b"])
+        ly["fc1_ln"] = fold_layernorm(sd[p + q + "mlp.0.weight"], sd[p + q + "mlp.0.bias"], ly["ln2_w"], ly["ln2_b"])
         layers.append(ly)
     out["layers"] = layers
     out["reduce"] = [pack_linear(sd[f"{p}channel_reduce.{i}.weight"], sd[f"{p}channel_reduce.{i}.bias"]) for i in range(4)]

@@ -82,6 +82,32 @@ def test_batch_shard_invariance():
         assert torch.equal(full[k], torch.cat([a[k], b[k]])), k
 
 
+def test_layernorm_fusion_matches_separate_kernels(monkeypatch):
+    """MDE_LN_FUSION=1 (LayerNorm folded into the neighbouring GEMM epilogues, CTA-pair kernel, B >= 6) against the default path
+    and the fp32 oracle; 12 + 8 images also covers the bit-exact shard invariance of the fused statistics."""
+    import monodepth_estimation_b200.engine as E
+
+    m = cached_model("standard", 0, "cuda")
+    x = synth_images(12, 224, 224, 79)
+    md = {"source": "rover"}
+    eng = m._get_engine()
+    base = {k: v.clone() for k, v in m(x.cuda(), md).items()}
+    monkeypatch.setattr(E, "_LN_FUSION", True)
+    eng._ws.clear()  # captured graphs hold the unfused launch sequence
+    try:
+        fused = {k: v.clone() for k, v in m(x.cuda(), md).items()}
+        part = m(x[:8].contiguous().cuda(), md)
+    finally:
+        monkeypatch.setattr(E, "_LN_FUSION", False)
+        eng._ws.clear()
+    with torch.no_grad():
+        ref = O.standard_forward(cached_model("standard", 0).state_dict(), x, md)
+    for k in base:
+        assert rel_l2(fused[k].float().cpu(), base[k].float().cpu()) < 8e-3, k  # two bf16 paths, each within 1e-2 of the oracle
+        assert torch.equal(fused[k][:8], part[k]), k
+    check_outputs(fused, ref, "ln_fusion")
+
+
 def test_graph_and_eager_agree_and_repeat():
     import monodepth_estimation_b200.engine as E
 

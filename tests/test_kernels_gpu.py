@@ -78,6 +78,85 @@ def test_gemm_pair_kernel_qkv_split():
     assert rel_l2(vt.view(B, 12, 64, L.VT_PITCH)[..., :197].float().transpose(-1, -2), ref[2]) < 4e-3
 
 
+# --------------------------------------------------------------------------- LayerNorm folded into the neighbouring GEMMs
+@pytest.mark.parametrize("M,K,epi", [(6304, 768, "resid"), (1576, 3072, "resid"), (1100, 768, "f32"), (8 * 196, 768, "patch")])
+def test_gemm_ln_producer(M, K, epi):
+    """The producer epilogues also emit bf16(x) and per-row (sum, sum of squares) partials of the fp32 output."""
+    L, ops = _mods()
+    N = 768
+    a, w, b = _rand(M, K, seed=201, dtype=BF16), _rand(N, K, seed=202, scale=K ** -0.5, dtype=BF16), _rand(N, seed=203)
+    rows = M // 196 * 197 if epi == "patch" else M
+    out = torch.full((rows, N), float("nan"), device="cuda")
+    xb = torch.full((rows + 2, N), 5.0, device="cuda", dtype=BF16)
+    st = torch.full((N // 32, rows, 2), float("nan"), device="cuda")  # chunk-major
+    if epi == "patch":
+        pos, cls = _rand(197, 768, seed=204, scale=0.5), _rand(768, seed=205, scale=0.5)
+        ops.gemm_ln(a, w, b, L.EPI_PATCH_EMBED, out, pos, cls, xb_out=xb, stats_out=st)
+        ref = torch.empty_like(out)
+        ops.gemm(a, w, b, L.EPI_PATCH_EMBED, ref, pos, cls)
+    elif epi == "resid":
+        r = _rand(M, N, seed=206)
+        ops.gemm_ln(a, w, b, L.EPI_BIAS_RESID_F32, out, r, xb_out=xb, stats_out=st)
+        ref = torch.empty_like(out)
+        ops.gemm(a, w, b, L.EPI_BIAS_RESID_F32, ref, r)
+    else:
+        ops.gemm_ln(a, w, b, L.EPI_BIAS_F32, out, xb_out=xb, stats_out=st)
+        ref = torch.empty_like(out)
+        ops.gemm(a, w, b, L.EPI_BIAS_F32, ref)
+    assert torch.equal(out, ref)  # the fp32 output itself is unchanged
+    assert torch.equal(xb[:rows], ref.to(BF16))
+    assert float((xb[rows:].float() - 5.0).abs().max()) == 0.0  # rows beyond M untouched
+    chunks = ref.view(rows, N // 32, 32).double()
+    assert max_abs(st[..., 0].t().double(), chunks.sum(-1)) < 1e-4
+    assert rel_l2(st[..., 1].t().double(), (chunks * chunks).sum(-1)) < 1e-6
+
+
+@pytest.mark.parametrize("M,N,epi", [(6304, 3072, "gelu"), (1576, 2304, "qkv"), (1100, 768, "bf16")])
+def test_gemm_ln_consumer(M, N, epi):
+    """rstd * (bf16(x) (gamma.W)^T - mean * colsum) + (b + W beta)  ==  LN(x) W^T + b, with x carrying a per-row offset."""
+    L, ops = _mods()
+    from monodepth_estimation_b200.packing import fold_layernorm
+
+    K = 768
+    x = _rand(M, K, seed=211) * (0.5 + torch.rand(M, 1, device="cuda")) + 0.3 * _rand(M, 1, seed=212)
+    w, b = _rand(N, K, seed=213, scale=K ** -0.5), _rand(N, seed=214)
+    gamma, beta = 1.0 + 0.2 * _rand(K, seed=215), 0.1 * _rand(K, seed=216)
+    wf, bf, cs = fold_layernorm(w, b, gamma, beta)
+    ch = x.view(M, K // 32, 32)
+    st = torch.stack([ch.sum(-1), (ch * ch).sum(-1)], -1).transpose(0, 1).contiguous()  # [K/32][M][2]
+    ref = F.layer_norm(x, (K,), gamma, beta, 1e-6) @ w.t() + b
+    xb = x.to(BF16)
+    if epi == "qkv":
+        B = M // 197
+        q = torch.empty(B * 12 * 197 * 64, device="cuda", dtype=BF16)
+        k = torch.empty_like(q)
+        vt = torch.zeros(B * 12 * 64 * L.VT_PITCH, device="cuda", dtype=BF16)
+        ops.gemm_ln(xb, wf, bf, L.EPI_QKV_SPLIT, q, k, vt, stats_in=st, colsum=cs)
+        r = ref.view(B, 197, 3, 12, 64).permute(2, 0, 3, 1, 4)
+        assert rel_l2(q.view(B, 197, 12, 64).permute(0, 2, 1, 3).float(), r[0] * 0.125) < 5e-3
+        assert rel_l2(k.view(B, 197, 12, 64).permute(0, 2, 1, 3).float(), r[1]) < 5e-3
+        assert rel_l2(vt.view(B, 12, 64, L.VT_PITCH)[..., :197].float().transpose(-1, -2), r[2]) < 5e-3
+        return
+    out = torch.full((M, N), float("nan"), device="cuda", dtype=BF16)
+    ops.gemm_ln(xb, wf, bf, L.EPI_BIAS_GELU_BF16 if epi == "gelu" else L.EPI_BIAS_BF16, out, stats_in=st, colsum=cs)
+    want = F.gelu(ref) if epi == "gelu" else ref
+    assert torch.isfinite(out.float()).all()
+    assert rel_l2(out.float(), want) < 5e-3, rel_l2(out.float(), want)
+    # against the unfused pair of kernels: same error level as the separate LayerNorm
+    h = ops.layernorm(x, gamma, beta, 1e-6)
+    out2 = torch.empty_like(out)
+    ops.gemm(h, w.to(BF16).contiguous(), b, L.EPI_BIAS_GELU_BF16 if epi == "gelu" else L.EPI_BIAS_BF16, out2)
+    assert rel_l2(out.float(), want) < 1.5 * rel_l2(out2.float(), want) + 1e-4
+
+
+def test_gemm_ln_small_m_is_an_error():
+    L, ops = _mods()
+    a, w, b = _rand(512, 768, seed=1, dtype=BF16), _rand(768, 768, seed=2, dtype=BF16), _rand(768, seed=3)
+    out = torch.empty(512, 768, device="cuda")
+    with pytest.raises(RuntimeError, match="CTA-pair"):
+        ops.gemm_ln(a, w, b, L.EPI_BIAS_F32, out, xb_out=torch.empty(512, 768, device="cuda", dtype=BF16), stats_out=torch.empty(24, 512, 2, device="cuda"))
+
+
 def test_gemm_bias_bf16_and_gelu():
     L, ops = _mods()
     M, N, K = 500, 3072, 768

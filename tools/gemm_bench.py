@@ -48,6 +48,17 @@ def main():
         us = e0.elapsed_time(e1) * 1e3 / reps
         total += us
         print(f"{name:5s} M={M} N={N} K={K}: {us:7.2f} us  {2.0 * M * N * K / us / 1e6:7.1f} TFLOP/s")
+        if os.environ.get("MDE_GEMM_PROF") == "1":  # in-kernel clock64 counters of ONE launch (mde_debug_gemm_prof)
+            prof = torch.zeros(148, 8, device=dev, dtype=torch.int64)
+            L.call("mde_debug_gemm_prof", prof.data_ptr())
+            ops.gemm(a, w, bias, epi, *args)
+            torch.cuda.synchronize()
+            L.call("mde_debug_gemm_prof", None)
+            pr = prof.double().cpu() / 1.9e3  # us at ~1.9 GHz
+            lead, both = pr[0::2], pr
+            print(f"      per CTA (us, mean/max): MMA waits accumulator {lead[:, 0].mean():.2f}/{lead[:, 0].max():.2f}, MMA waits operands "
+                  f"{lead[:, 1].mean():.2f}/{lead[:, 1].max():.2f}, epilogue waits MMA {both[:, 2].mean():.2f}/{both[:, 2].max():.2f}, epilogue works "
+                  f"{both[:, 3].mean():.2f}/{both[:, 3].max():.2f} over {both[:, 4].mean():.2f} tiles, CTA lifetime {both[:, 5].mean():.2f}/{both[:, 5].max():.2f}")
     print(f"per ViT layer (4 GEMMs): {total:.1f} us; x12 = {total * 12 / 1e3:.3f} ms")
 
 
