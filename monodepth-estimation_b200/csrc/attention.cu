@@ -277,32 +277,34 @@ __global__ void __launch_bounds__(128, 2) vit_attn_tp_kernel(const __grid_consta
   const uint32_t t_row = tmem_base + (static_cast<uint32_t>(warp * 32) << 16);  // this thread's TMEM lane
   constexpr float kLog2e = 1.4426950408889634f;
 
-  // ---- pass 1: row maximum over the 197 real keys
-  float mx = -INFINITY;
+  // ---- pass 1: row maximum over the 197 real keys (four independent chains: a thread is alone with its row, so the
+  // dependent-issue latency of one 197-long fmax chain was ~0.4 us of every CTA)
+  float m4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
 #pragma unroll 1
   for (int c = 0; c < 6; ++c) {
     uint32_t r[32];
     tmem_ld_32x32b_x32(t_row + c * 32, r);
     tmem_ld_wait();
 #pragma unroll
-    for (int j = 0; j < 32; ++j) mx = fmaxf(mx, __uint_as_float(r[j]));
+    for (int j = 0; j < 32; ++j) m4[j & 3] = fmaxf(m4[j & 3], __uint_as_float(r[j]));
   }
   uint32_t tail[16];
   tmem_ld_32x32b_x16(t_row + 192, tail);
   tmem_ld_wait();
 #pragma unroll
-  for (int j = 0; j < kS - 192; ++j) mx = fmaxf(mx, __uint_as_float(tail[j]));
+  for (int j = 0; j < kS - 192; ++j) m4[j & 3] = fmaxf(m4[j & 3], __uint_as_float(tail[j]));
+  const float mx = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3]));
   const float mxs = mx * kLog2e;
 
   // ---- pass 2, last chunk first: exp, row sum, bf16 probabilities back into TMEM
-  float sum = 0.0f;
+  float s4[4] = {0.0f, 0.0f, 0.0f, 0.0f};  // partial row sums (fixed assignment of columns to partials: deterministic)
   {
     uint32_t pk[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
       const float e0 = (2 * j < kS - 192) ? fast_ex2(fmaf(__uint_as_float(tail[2 * j]), kLog2e, -mxs)) : 0.0f;
       const float e1 = (2 * j + 1 < kS - 192) ? fast_ex2(fmaf(__uint_as_float(tail[2 * j + 1]), kLog2e, -mxs)) : 0.0f;
-      sum += e0 + e1;
+      s4[j & 3] += e0 + e1;
       pk[j] = pack_bf16x2(e0, e1);
     }
     tmem_st_32x32b_x8(t_row + kTpP + 96, pk);
@@ -317,13 +319,13 @@ __global__ void __launch_bounds__(128, 2) vit_attn_tp_kernel(const __grid_consta
     for (int j = 0; j < 16; ++j) {
       const float e0 = fast_ex2(fmaf(__uint_as_float(r[2 * j]), kLog2e, -mxs));
       const float e1 = fast_ex2(fmaf(__uint_as_float(r[2 * j + 1]), kLog2e, -mxs));
-      sum += e0 + e1;
+      s4[j & 3] += e0 + e1;
       pk[j] = pack_bf16x2(e0, e1);
     }
     tmem_st_32x32b_x16(t_row + kTpP + 16 * c, pk);  // columns >= 104 + 16c: scores there (>= 32c) are already consumed
   }
   tmem_st_wait();
-  const float inv = 1.0f / sum;
+  const float inv = 1.0f / ((s4[0] + s4[1]) + (s4[2] + s4[3]));
   tc_fence_before();
   __syncthreads();
 

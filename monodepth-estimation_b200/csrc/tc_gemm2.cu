@@ -74,6 +74,13 @@ struct alignas(64) Tc2Params {
   long long* prof;      // debug (mde_debug_gemm_prof): per CTA 8 counters of cycles spent waiting / working, or null
 };
 
+// In-kernel counters (mde_debug_gemm_prof) exist only in builds with -DMDE_GEMM_PROF (MDE_BUILD_PROF=1 python build.py):
+// even a never-taken branch per k-block in the MMA-issuing thread costs ~0.7 us per launch.
+#ifdef MDE_GEMM_PROF
+#define MDE_PROF(...) __VA_ARGS__
+#else
+#define MDE_PROF(...)
+#endif
 __device__ __forceinline__ long long clk() { return clock64(); }
 
 struct Item {
@@ -96,6 +103,9 @@ __device__ __forceinline__ Item decode_item(const Tc2Params& p, int i) {
   return it;
 }
 
+// LNF = 1 adds the LayerNorm-fusion code (producer: bf16 copy + row sums, consumer: normalising epilogue); the default
+// instantiation carries none of it (the extra registers / instructions cost ~0.6 us per launch even when never executed).
+template <int LNF>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(k2Threads, 1) tc_gemm2_kernel(const __grid_constant__ Tc2Params p) {
   pdl_launch_dependents();
   extern __shared__ uint8_t smem_raw[];
@@ -144,8 +154,6 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(k2Threads, 1) tc_gem
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   pdl_grid_wait();  // everything above (barriers, TMEM, descriptor prefetch) overlaps the previous kernel's tail
-  long long t_start = 0;
-  if (p.prof && threadIdx.x == 0) t_start = clk();
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer (both CTAs)
@@ -178,16 +186,15 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(k2Threads, 1) tc_gem
       for (int i = cluster_id; i < p.total_items; i += num_clusters) {
         const Item it = decode_item(p, i);
         const uint32_t idesc = umma_idesc_bf16(256, it.bn);
-        long long t0 = 0;
-        if (p.prof) t0 = clk();
+        MDE_PROF(long long t0 = 0; if (p.prof) t0 = clk();)
         mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
-        if (p.prof) p.prof[blockIdx.x * 8 + 0] += clk() - t0;  // MMA thread waiting for a free accumulator (epilogue behind)
+        MDE_PROF(if (p.prof) p.prof[blockIdx.x * 8 + 0] += clk() - t0;)  // MMA thread waiting for a free accumulator (epilogue behind)
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * 256;
         for (int kb = 0; kb < p.k_blocks; ++kb) {
-          if (p.prof) t0 = clk();
+          MDE_PROF(if (p.prof) t0 = clk();)
           mbar_wait(&full_bar[stage], phase);
-          if (p.prof) p.prof[blockIdx.x * 8 + 1] += clk() - t0;  // MMA thread waiting for operands (TMA behind)
+          MDE_PROF(if (p.prof) p.prof[blockIdx.x * 8 + 1] += clk() - t0;)  // MMA thread waiting for operands (TMA behind)
           tc_fence_after();
           const uint32_t sa = smem_u32(smem + (size_t)stage * k2StageBytes);
           const uint64_t da = umma_smem_desc_kmajor<128>(sa);
@@ -237,7 +244,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(k2Threads, 1) tc_gem
         const int nch = it.bn / cw;
         const int row0 = it.m0 + (int)rank * 128 + q * 32;
         float mu = 0.0f, rstd = 1.0f;  // LayerNorm of this thread's A row, from the producer's partial sums (fixed order: deterministic)
-        if (p.ln_in && row0 + lane < p.M) {
+        if (LNF && p.ln_in && row0 + lane < p.M) {
           // slot-major [K/32][M][2]: a warp reads 32 consecutive rows of one slot = 256 contiguous bytes per instruction
           const float2* st = reinterpret_cast<const float2*>(p.ln_in) + (row0 + lane);
           float s1 = 0.0f, s2 = 0.0f;
@@ -254,15 +261,13 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(k2Threads, 1) tc_gem
           mu = s1 * p.ln_invk;
           rstd = rsqrtf(fmaxf(fmaf(-mu, mu, s2 * p.ln_invk), 0.0f) + p.ln_eps);
         }
-        long long t0 = 0;
-        const bool prof = p.prof && warp == 2 && lane == 0;
-        if (prof) t0 = clk();
+        MDE_PROF(long long t0 = 0; const bool prof = p.prof && warp == 2 && lane == 0; if (prof) t0 = clk();)
         mbar_wait(&tfull_bar[acc], acc_phase);
-        if (prof) {
+        MDE_PROF(if (prof) {
           const long long t1 = clk();
           p.prof[blockIdx.x * 8 + 2] += t1 - t0;  // epilogue warp 2 waiting for the accumulator (MMA behind)
           t0 = t1;
-        }
+        })
         tc_fence_after();
         const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * 256;
 #pragma unroll 1
@@ -314,7 +319,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(k2Threads, 1) tc_gem
             __syncwarp();
             tmem_ld_wait();
             const float4* bp = reinterpret_cast<const float4*>(p.bias + n0);
-            const bool lnc = p.ln_in != nullptr;  // LayerNorm consumer: (acc - mean * colsum) * rstd + bias
+            const bool lnc = LNF && p.ln_in != nullptr;  // LayerNorm consumer: (acc - mean * colsum) * rstd + bias
             const float4* csp = reinterpret_cast<const float4*>(p.ln_cs + n0);
             const bool gelu = p.epi == MDE_EPI_BIAS_GELU_BF16;
             const int which = p.epi == MDE_EPI_QKV_SPLIT ? n0 / MDE_VIT_DIM : 0;  // 0 q, 1 k, 2 v (uniform per 64-column chunk)
@@ -382,7 +387,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(k2Threads, 1) tc_gem
             }
             bulk_commit();
           }
-          if (p.xb) {
+          if (LNF && p.xb) {
             // LayerNorm producer: bf16 copy of the staged fp32 chunk, read back with lane = four columns so that a warp store
             // covers four 64-byte row segments (a row-per-thread store would touch 32 lines per instruction), plus the
             // row's partial sums.  The staged tile is only read here and by the TMA store.
@@ -411,10 +416,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(k2Threads, 1) tc_gem
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive_cluster(&tempty_bar[acc], 0);  // the leader's MMA thread owns the accumulator ring
-        if (prof) {
+        MDE_PROF(if (prof) {
           p.prof[blockIdx.x * 8 + 3] += clk() - t0;  // epilogue warp 2 working on the tile
           p.prof[blockIdx.x * 8 + 4] += 1;           // tiles
-        }
+        })
         acc ^= 1;
         if (acc == 0) acc_phase ^= 1;
         i = inext;
@@ -452,7 +457,6 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(k2Threads, 1) tc_gem
     }
   }
 
-  if (p.prof && threadIdx.x == 0) p.prof[blockIdx.x * 8 + 5] += clk() - t_start;  // CTA lifetime after the dependency wait
   tc_fence_before();
   cluster_sync_all();  // both CTAs are done with each other's shared memory / TMEM
   tc_fence_after();
@@ -550,11 +554,15 @@ int launch_gemm_pair(const void* A, int lda, const void* W, int ldw, int M, int 
   const int smem_bytes = stages * k2StageBytes + k2StagingBytes + 1024 + k2BarrierBytes;
   static bool attr_set = false;
   if (!attr_set) {
-    MDE_CHECK_CUDA(cudaFuncSetAttribute(tc_gemm2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
+    MDE_CHECK_CUDA(cudaFuncSetAttribute(tc_gemm2_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
+    MDE_CHECK_CUDA(cudaFuncSetAttribute(tc_gemm2_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
     attr_set = true;
   }
   const int grid = 2 * std::min(clusters, p.total_items);
-  launch_k(tc_gemm2_kernel, dim3(grid), dim3(k2Threads), smem_bytes, stream, p);
+  if (p.xb || p.ln_in)
+    launch_k(tc_gemm2_kernel<1>, dim3(grid), dim3(k2Threads), smem_bytes, stream, p);
+  else
+    launch_k(tc_gemm2_kernel<0>, dim3(grid), dim3(k2Threads), smem_bytes, stream, p);
   MDE_CHECK_LAUNCH();
   return MDE_OK;
 }
@@ -562,6 +570,12 @@ int launch_gemm_pair(const void* A, int lda, const void* W, int ldw, int M, int 
 }  // namespace mde
 
 extern "C" int mde_debug_gemm_prof(long long* counters) {
+#ifdef MDE_GEMM_PROF
   mde::g_gemm_prof = counters;  // device buffer of 8 counters per CTA (zeroed by the caller), or null to switch the counters off
   return MDE_OK;
+#else
+  (void)counters;
+  mde::set_error("mde_debug_gemm_prof: this build has no counters (rebuild with MDE_BUILD_PROF=1 python monodepth-estimation_b200/build.py)");
+  return MDE_ERR_UNSUPPORTED;
+#endif
 }
