@@ -105,7 +105,9 @@ __device__ __forceinline__ Item decode_item(const Tc2Params& p, int i) {
 
 // LNF = 1 adds the LayerNorm-fusion code (producer: bf16 copy + row sums, consumer: normalising epilogue); the default
 // instantiation carries none of it (the extra registers / instructions cost ~0.6 us per launch even when never executed).
-template <int LNF>
+// EC = epilogue class: 0 fp32 through TMA (bias / bias + residual), 1 bf16 through TMA (bias / GELU / QKV split), 2 direct stores
+// (patch embed): each instantiation carries only its own epilogue code.
+template <int LNF, int EC>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(k2Threads, 1) tc_gemm2_kernel(const __grid_constant__ Tc2Params p) {
   pdl_launch_dependents();
   extern __shared__ uint8_t smem_raw[];
@@ -128,7 +130,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(k2Threads, 1) tc_gem
     tma_prefetch_desc(&p.tmA);
     tma_prefetch_desc(&p.tmB);
     tma_prefetch_desc(&p.tmBn);
-    if (p.tma_epi) {
+    if (EC != 2) {
       tma_prefetch_desc(&p.tmOut);
       tma_prefetch_desc(&p.tmRes);
     }
@@ -219,12 +221,12 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(k2Threads, 1) tc_gem
     const int r = q * 32 + lane;
     int acc = 0;
     uint32_t acc_phase = 0;
-    if (p.tma_epi) {
+    if constexpr (EC != 2) {
       const int ew = warp - 2;
       uint8_t* stg = staging + ew * 2 * k2EpiBufBytes;
       uint64_t* rbar = res_bar + ew * 2;
-      const bool resid = p.epi == MDE_EPI_BIAS_RESID_F32;
-      const bool f32out = p.out_elt == 4;
+      const bool resid = EC == 0 && p.epi == MDE_EPI_BIAS_RESID_F32;
+      constexpr bool f32out = EC == 0;
       const int cw = f32out ? 32 : 64;  // columns per 128-byte chunk
       const uint32_t sw = static_cast<uint32_t>(lane & 7);
       uint32_t g = 0;  // chunks this warp has processed: staging buffer = g & 1, residual barrier parity = (g >> 1) & 1
@@ -244,7 +246,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(k2Threads, 1) tc_gem
         const int nch = it.bn / cw;
         const int row0 = it.m0 + (int)rank * 128 + q * 32;
         float mu = 0.0f, rstd = 1.0f;  // LayerNorm of this thread's A row, from the producer's partial sums (fixed order: deterministic)
-        if (LNF && p.ln_in && row0 + lane < p.M) {
+        if (LNF && EC == 1 && p.ln_in && row0 + lane < p.M) {
           // slot-major [K/32][M][2]: a warp reads 32 consecutive rows of one slot = 256 contiguous bytes per instruction
           const float2* st = reinterpret_cast<const float2*>(p.ln_in) + (row0 + lane);
           float s1 = 0.0f, s2 = 0.0f;
@@ -275,7 +277,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(k2Threads, 1) tc_gem
           uint8_t* buf = stg + (g & 1) * k2EpiBufBytes;
           uint8_t* row = buf + lane * 128;
           const int n0 = it.n0 + c * cw;
-          if (f32out) {
+          if constexpr (f32out) {
             uint32_t raw[32];
             tmem_ld_32x32b_x32(taddr + c * 32, raw);
             if (lane == 0) {
@@ -387,7 +389,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(k2Threads, 1) tc_gem
             }
             bulk_commit();
           }
-          if (LNF && p.xb) {
+          if (LNF && EC == 0 && p.xb) {
             // LayerNorm producer: bf16 copy of the staged fp32 chunk, read back with lane = four columns so that a warp store
             // covers four 64-byte row segments (a row-per-thread store would touch 32 lines per instruction), plus the
             // row's partial sums.  The staged tile is only read here and by the TMA store.
@@ -554,15 +556,18 @@ int launch_gemm_pair(const void* A, int lda, const void* W, int ldw, int M, int 
   const int smem_bytes = stages * k2StageBytes + k2StagingBytes + 1024 + k2BarrierBytes;
   static bool attr_set = false;
   if (!attr_set) {
-    MDE_CHECK_CUDA(cudaFuncSetAttribute(tc_gemm2_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
-    MDE_CHECK_CUDA(cudaFuncSetAttribute(tc_gemm2_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
+#define MDE_G2_ATTR(L_, E_) MDE_CHECK_CUDA(cudaFuncSetAttribute(tc_gemm2_kernel<L_, E_>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
+    MDE_G2_ATTR(0, 0) MDE_G2_ATTR(0, 1) MDE_G2_ATTR(0, 2) MDE_G2_ATTR(1, 0) MDE_G2_ATTR(1, 1) MDE_G2_ATTR(1, 2)
+#undef MDE_G2_ATTR
     attr_set = true;
   }
   const int grid = 2 * std::min(clusters, p.total_items);
-  if (p.xb || p.ln_in)
-    launch_k(tc_gemm2_kernel<1>, dim3(grid), dim3(k2Threads), smem_bytes, stream, p);
-  else
-    launch_k(tc_gemm2_kernel<0>, dim3(grid), dim3(k2Threads), smem_bytes, stream, p);
+  const int ec = !p.tma_epi ? 2 : (p.out_elt == 4 ? 0 : 1);
+  const int lnf = (p.xb || p.ln_in) ? 1 : 0;
+#define MDE_G2_CASE(L_, E_) \
+  if (lnf == L_ && ec == E_) launch_k(tc_gemm2_kernel<L_, E_>, dim3(grid), dim3(k2Threads), smem_bytes, stream, p);
+  MDE_G2_CASE(0, 0) MDE_G2_CASE(0, 1) MDE_G2_CASE(0, 2) MDE_G2_CASE(1, 0) MDE_G2_CASE(1, 1) MDE_G2_CASE(1, 2)
+#undef MDE_G2_CASE
   MDE_CHECK_LAUNCH();
   return MDE_OK;
 }
