@@ -15,10 +15,10 @@ CMD="python bench.py --no-extras --steps 1 --warmup 1 --model $MODEL"
 $CMD > $OUT/${TAG}_plain.log 2>&1 || { echo "plain run failed"; tail -20 $OUT/${TAG}_plain.log; exit 1; }
 ncu --metrics gpu__time_duration.sum --clock-control none -c 1200 --csv --log-file $OUT/${TAG}_launches.csv $CMD > $OUT/${TAG}_ncu1.log 2>&1
 echo "launch list rc=$?"
-ncu --set full --clock-control none --import-source on -k 'regex:tc_gemm2_kernel|vit_attn_kernel|layernorm_kernel' -s 91 -c 7 \
+ncu --set full --clock-control none --import-source on -k 'regex:tc_gemm2_kernel|vit_attn|layernorm_kernel' -s 91 -c 7 \
     -o $OUT/${TAG}_vit -f $CMD > $OUT/${TAG}_ncu2.log 2>&1
 echo "vit capture rc=$?"
-ncu --set full --clock-control none --import-source on -k 'regex:resize_maps_kernel|minmax_kernel|patchify_kernel|upsample_concat_kernel|conv_halo_kernel|instnorm_kernel' -s 0 -c 24 \
+ncu --set full --clock-control none --import-source on -k 'regex:resize_maps|input_scan_resample_kernel|patchify224_kernel|upsample_concat_kernel|conv_halo_kernel|instnorm_kernel|tc_gemm_kernel' -s 0 -c 30 \
     -o $OUT/${TAG}_hbm -f $CMD > $OUT/${TAG}_ncu3.log 2>&1
 echo "hbm/conv capture rc=$?"
 ls -la $OUT
