@@ -52,6 +52,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
             cmd = [nvcc, *NVCC_FLAGS, "-c", src, "-o", obj]
             if os.environ.get("MDE_BUILD_PROF") == "1":  # in-kernel GEMM counters (tools/gemm_bench.py, MDE_GEMM_PROF=1)
                 cmd.insert(1, "-DMDE_GEMM_PROF")
+                cmd.insert(1, "-DMDE_ATTN_PROF")
             if verbose:
                 cmd.insert(1, "-Xptxas=-v")
             r = subprocess.run(cmd, capture_output=True, text=True)

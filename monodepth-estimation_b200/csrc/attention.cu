@@ -365,6 +365,279 @@ __global__ void __launch_bounds__(128, 2) vit_attn_tp_kernel(const __grid_consta
   if (warp == 0) tmem_dealloc(tmem_base, kTpTmemCols);
 }
 
+// ------------------------------------------------------------------ ViT attention, persistent and pipelined
+// One CTA per SM loops over (image, head) pairs.  320 threads: warpgroup t (warps 4t..4t+3) owns query tile t (rows 128t..)
+// and TMEM columns [256t, 256t+208); warp 8 is the TMA producer (Q tiles, K and V^T of the NEXT pair land in the other
+// shared-memory stage while this one is being used: K and V are loaded once for both query tiles); one thread of warp 9
+// issues every MMA.  Each tile runs the vit_attn_tp_kernel scheme (S in TMEM, un-normalised bf16 P written back into TMEM
+// columns [104,208) of the tile, O = P V as a TS-mode MMA into columns [0,64)).  The MMA thread is event-driven: it polls
+// the two tiles' barriers and issues whichever step (S of the tile's next pair, or P V) has become possible, so the two
+// warpgroups drift out of phase and one tile's MMA / TMEM round trips hide behind the other tile's exponentials.
+constexpr int kPsStage = 2 * kQBytes + kKBytesPad + 4 * kVBytes;   // 93184
+constexpr int kPsOffBar = 2 * kPsStage;
+constexpr int kPsSmem = kPsOffBar + 256 + 1024;
+constexpr uint32_t kPsTile = 256;  // TMEM column stride between the two query tiles
+
+__device__ __forceinline__ void ps_poll_timeout(long long t0) {
+  if (clock64() - t0 > 4000000000LL) {
+    printf("mde: vit_attn_ps_kernel MMA scheduler timed out (block %d)\n", blockIdx.x);
+    __trap();
+  }
+}
+
+#ifdef MDE_ATTN_PROF
+__device__ __forceinline__ unsigned long long gtime() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+#define PS_T(i) do { if (prof_on) tp[i] = gtime(); } while (0)
+#else
+#define PS_T(i) do { } while (0)
+#endif
+
+__global__ void __launch_bounds__(320, 1) vit_attn_ps_kernel(const __grid_constant__ AttnParams p) {
+#ifdef MDE_ATTN_PROF
+  unsigned long long tp[12] = {0};
+  const bool prof_on = (threadIdx.x == 0 || threadIdx.x == 128) && (blockIdx.x == 0 || blockIdx.x == 100);
+  PS_T(0);
+#endif
+  pdl_launch_dependents();
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kPsOffBar);
+  uint64_t* bar_full = bars;        // [2] stage loaded (TMA transaction bytes)
+  uint64_t* bar_empty = bars + 2;   // [2] both tiles' MMAs of the pair in this stage have completed
+  uint64_t* bar_s = bars + 4;       // [2] per tile: S = Q K^T is in TMEM
+  uint64_t* bar_p = bars + 6;       // [2] per tile: P written (4 warp arrivals)
+  uint64_t* bar_o = bars + 8;       // [2] per tile: O = P V is in TMEM
+  uint64_t* bar_free = bars + 10;   // [2] per tile: O read out, the tile's columns may be overwritten (4 warp arrivals)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 12);
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int slabs = p.B * MDE_VIT_HEADS;
+  const int n_items = (slabs - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+
+  if (warp == 9) {
+    if (elect_one()) {
+      tma_prefetch_desc(&p.tmQ);
+      tma_prefetch_desc(&p.tmK);
+      tma_prefetch_desc(&p.tmV);
+      for (int i = 0; i < 2; ++i) {
+        mbar_init(&bar_full[i], 1);
+        mbar_init(&bar_empty[i], 1);
+        mbar_init(&bar_s[i], 1);
+        mbar_init(&bar_p[i], 4);
+        mbar_init(&bar_o[i], 1);
+        mbar_init(&bar_free[i], 4);
+      }
+      fence_barrier_init();
+    }
+    __syncwarp();
+    tmem_alloc(tmem_slot, 512);
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  PS_T(1);
+  pdl_grid_wait();  // the set-up above overlaps the previous kernel's tail
+  PS_T(2);
+
+  if (warp == 8) {
+    // ------------------------------------------------------------ TMA producer
+    if (lane == 0) {
+      for (int it = 0; it < n_items; ++it) {
+        const int s = it & 1;
+        if (it >= 2) mbar_wait(&bar_empty[s], ((it >> 1) - 1) & 1);
+        const int slab = blockIdx.x + it * gridDim.x;
+        const int b = slab / MDE_VIT_HEADS, hd = slab - b * MDE_VIT_HEADS;
+        uint8_t* st = smem + s * kPsStage;
+        mbar_expect_tx(&bar_full[s], 2 * kQBytes + kKBytes + 4 * kVBytes);
+        tma_load_4d(st, &p.tmQ, &bar_full[s], 0, hd, 0, b);
+        tma_load_4d(st + kQBytes, &p.tmQ, &bar_full[s], 0, hd, 128, b);
+        tma_load_4d(st + 2 * kQBytes, &p.tmK, &bar_full[s], 0, hd, 0, b);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) tma_load_3d(st + 2 * kQBytes + kKBytesPad + j * kVBytes, &p.tmV, &bar_full[s], 64 * j, 0, slab);
+      }
+    }
+  } else if (warp == 9) {
+    // ------------------------------------------------------------ MMA issuer (event-driven over the two tiles)
+    if (lane == 0) {
+      constexpr uint32_t idesc_s = umma_idesc_bf16(128, kKeys);
+      constexpr uint32_t idesc_o = umma_idesc_bf16(128, 64);
+      int item[2] = {0, 0};
+      int need_pv[2] = {0, 0};
+      int released = 0;  // stages handed back to the producer so far (pairs whose P V of both tiles has been issued)
+      const long long t0 = clock64();
+      while (item[0] < n_items || item[1] < n_items) {
+#pragma unroll
+        for (int t = 0; t < 2; ++t) {
+          const int i = item[t];
+          if (i >= n_items) continue;
+          const uint32_t t_tile = tmem_base + t * kPsTile;
+          uint8_t* st = smem + (i & 1) * kPsStage;
+          if (!need_pv[t]) {
+            if (!mbar_try_wait(&bar_full[i & 1], (i >> 1) & 1)) continue;
+            if (i > 0 && !mbar_try_wait(&bar_free[t], (i - 1) & 1)) continue;
+            tc_fence_after();
+            const uint64_t da = umma_smem_desc_kmajor<128>(smem_u32(st + t * kQBytes));
+            const uint64_t db = umma_smem_desc_kmajor<128>(smem_u32(st + 2 * kQBytes));
+#pragma unroll
+            for (int k = 0; k < 4; ++k) umma_bf16_ss(t_tile, da + 2 * k, db + 2 * k, idesc_s, k != 0);
+            umma_commit(&bar_s[t]);
+            need_pv[t] = 1;
+          } else {
+            if (!mbar_try_wait(&bar_p[t], i & 1)) continue;
+            tc_fence_after();
+            uint8_t* sV = st + 2 * kQBytes + kKBytesPad;
+#pragma unroll
+            for (int kk = 0; kk < 13; ++kk) {
+              const uint64_t db = umma_smem_desc_kmajor<128>(smem_u32(sV + (kk >> 2) * kVBytes)) + 2 * (kk & 3);
+              umma_bf16_ts(t_tile, t_tile + kTpP + 8 * kk, db, idesc_o, kk != 0);
+            }
+            umma_commit(&bar_o[t]);
+            need_pv[t] = 0;
+            item[t] = i + 1;
+            const int done = item[0] < item[1] ? item[0] : item[1];
+            while (released < done) {
+              umma_commit(&bar_empty[released & 1]);
+              ++released;
+            }
+          }
+        }
+        ps_poll_timeout(t0);
+      }
+    }
+  } else {
+    // ------------------------------------------------------------ softmax / output warpgroups
+    const int t = warp >> 2;  // query tile
+    const uint32_t t_row = tmem_base + t * kPsTile + (static_cast<uint32_t>((warp & 3) * 32) << 16);  // this thread's TMEM lane
+    const int row = t * 128 + (warp & 3) * 32 + lane;  // token index of this thread's query row
+    const bool warp_live = t * 128 + (warp & 3) * 32 < kS;  // warp 7 holds rows 224..255 only: nothing to compute
+    constexpr float kLog2e = 1.4426950408889634f;
+    for (int it = 0; it < n_items; ++it) {
+      const int slab = blockIdx.x + it * gridDim.x;
+      const int b = slab / MDE_VIT_HEADS, hd = slab - b * MDE_VIT_HEADS;
+      mbar_wait(&bar_s[t], it & 1);
+      tc_fence_after();
+      if (it == 0) PS_T(3);
+      if (it == 1) PS_T(8);
+      float inv = 0.0f;
+      if (warp_live) {
+        // pass 1: row maximum over the 197 real keys; the TMEM load of chunk c+1 is in flight while chunk c is reduced
+        float m4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+        uint32_t ra[32], rb[32];
+        tmem_ld_32x32b_x32(t_row, ra);
+#pragma unroll
+        for (int c = 0; c < 6; c += 2) {
+          tmem_ld_wait();
+          tmem_ld_32x32b_x32(t_row + (c + 1) * 32, rb);
+#pragma unroll
+          for (int j = 0; j < 32; ++j) m4[j & 3] = fmaxf(m4[j & 3], __uint_as_float(ra[j]));
+          tmem_ld_wait();
+          if (c + 2 < 6) tmem_ld_32x32b_x32(t_row + (c + 2) * 32, ra);
+#pragma unroll
+          for (int j = 0; j < 32; ++j) m4[j & 3] = fmaxf(m4[j & 3], __uint_as_float(rb[j]));
+        }
+        uint32_t tail[16];
+        tmem_ld_32x32b_x16(t_row + 192, tail);
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < kS - 192; ++j) m4[j & 3] = fmaxf(m4[j & 3], __uint_as_float(tail[j]));
+        const float mxs = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3])) * kLog2e;
+        if (it == 0) PS_T(4);
+
+        // pass 2, last chunk first: exp, row sum, bf16 probabilities back into TMEM columns [104,208) of the tile
+        float s4[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+        tmem_ld_32x32b_x32(t_row + 5 * 32, ra);
+        {
+          uint32_t pk[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float e0 = (2 * j < kS - 192) ? fast_ex2(fmaf(__uint_as_float(tail[2 * j]), kLog2e, -mxs)) : 0.0f;
+            const float e1 = (2 * j + 1 < kS - 192) ? fast_ex2(fmaf(__uint_as_float(tail[2 * j + 1]), kLog2e, -mxs)) : 0.0f;
+            s4[j & 3] += e0 + e1;
+            pk[j] = pack_bf16x2(e0, e1);
+          }
+          tmem_st_32x32b_x8(t_row + kTpP + 96, pk);
+        }
+#pragma unroll
+        for (int c = 5; c >= 0; c -= 2) {
+          uint32_t pk[16];
+          tmem_ld_wait();
+          tmem_ld_32x32b_x32(t_row + (c - 1) * 32, rb);  // scores of chunk c-1: P of chunk c only overwrites columns >= 104 + 16c >= 32c
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            const float e0 = fast_ex2(fmaf(__uint_as_float(ra[2 * j]), kLog2e, -mxs));
+            const float e1 = fast_ex2(fmaf(__uint_as_float(ra[2 * j + 1]), kLog2e, -mxs));
+            s4[j & 3] += e0 + e1;
+            pk[j] = pack_bf16x2(e0, e1);
+          }
+          tmem_ld_wait();  // chunk c-1 is in registers before chunk c's probabilities may land on its columns
+          tmem_st_32x32b_x16(t_row + kTpP + 16 * c, pk);
+          if (c - 2 >= 0) tmem_ld_32x32b_x32(t_row + (c - 2) * 32, ra);
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            const float e0 = fast_ex2(fmaf(__uint_as_float(rb[2 * j]), kLog2e, -mxs));
+            const float e1 = fast_ex2(fmaf(__uint_as_float(rb[2 * j + 1]), kLog2e, -mxs));
+            s4[j & 3] += e0 + e1;
+            pk[j] = pack_bf16x2(e0, e1);
+          }
+          if (c - 2 >= 0) tmem_ld_wait();
+          tmem_st_32x32b_x16(t_row + kTpP + 16 * (c - 1), pk);
+        }
+        tmem_st_wait();
+        inv = 1.0f / ((s4[0] + s4[1]) + (s4[2] + s4[3]));
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&bar_p[t]);
+      if (it == 0) PS_T(5);
+
+      mbar_wait(&bar_o[t], it & 1);
+      tc_fence_after();
+      if (it == 0) PS_T(6);
+      uint32_t o0[32], o1[32];
+      if (warp_live) {
+        tmem_ld_32x32b_x32(t_row, o0);
+        tmem_ld_32x32b_x32(t_row + 32, o1);
+        tmem_ld_wait();
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&bar_free[t]);  // the MMA thread may start the next pair's S on this tile
+      if (warp_live && row < kS) {
+        uint4* dst = reinterpret_cast<uint4*>(p.out + ((size_t)b * kS + row) * MDE_VIT_DIM + hd * 64);
+#pragma unroll
+        for (int g = 0; g < 4; ++g)
+          dst[g] = make_uint4(pack_bf16x2(__uint_as_float(o0[8 * g]) * inv, __uint_as_float(o0[8 * g + 1]) * inv),
+                              pack_bf16x2(__uint_as_float(o0[8 * g + 2]) * inv, __uint_as_float(o0[8 * g + 3]) * inv),
+                              pack_bf16x2(__uint_as_float(o0[8 * g + 4]) * inv, __uint_as_float(o0[8 * g + 5]) * inv),
+                              pack_bf16x2(__uint_as_float(o0[8 * g + 6]) * inv, __uint_as_float(o0[8 * g + 7]) * inv));
+#pragma unroll
+        for (int g = 0; g < 4; ++g)
+          dst[4 + g] = make_uint4(pack_bf16x2(__uint_as_float(o1[8 * g]) * inv, __uint_as_float(o1[8 * g + 1]) * inv),
+                                  pack_bf16x2(__uint_as_float(o1[8 * g + 2]) * inv, __uint_as_float(o1[8 * g + 3]) * inv),
+                                  pack_bf16x2(__uint_as_float(o1[8 * g + 4]) * inv, __uint_as_float(o1[8 * g + 5]) * inv),
+                                  pack_bf16x2(__uint_as_float(o1[8 * g + 6]) * inv, __uint_as_float(o1[8 * g + 7]) * inv));
+      }
+    }
+  }
+  PS_T(7);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  if (warp == 9) tmem_dealloc(tmem_base, 512);
+#ifdef MDE_ATTN_PROF
+  if (prof_on) {
+    PS_T(9);
+    printf("ps blk %d thr %d: setup %llu pdlwait %llu S0 %llu pass1 %llu pass2 %llu PV %llu rest %llu (S1 at %llu) dealloc %llu total %llu ns\n", blockIdx.x, threadIdx.x,
+           tp[1] - tp[0], tp[2] - tp[1], tp[3] - tp[2], tp[4] - tp[3], tp[5] - tp[4], tp[6] - tp[5], tp[7] - tp[6], tp[8] ? tp[8] - tp[2] : 0ull, tp[9] - tp[7], tp[9] - tp[0]);
+  }
+#endif
+}
+
 // ------------------------------------------------------------------ spatial self-attention (enhanced_model.py:20-39)
 constexpr int kSaQ = 8;        // queries per block
 constexpr int kSaMaxG = 224;   // grid positions supported (14x15 = 210, 14x14 = 196)
@@ -478,12 +751,17 @@ extern "C" int mde_vit_attention(const mde_bf16* q, const mde_bf16* k, const mde
     MDE_CHECK_CUDA(cudaFuncSetAttribute(vit_attn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kAttnSmem));
     MDE_CHECK_CUDA(cudaFuncSetAttribute(vit_attn_tp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kTpSmem));
     MDE_CHECK_CUDA(cudaFuncSetAttribute(vit_attn_tp_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    MDE_CHECK_CUDA(cudaFuncSetAttribute(vit_attn_ps_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kPsSmem));
     attr_set = true;
   }
   // MDE_ATTN_SMEM_P=1 selects the shared-memory-P kernel (A/B testing); default: probabilities in TMEM, 2 CTAs per SM
   static const bool smem_p = getenv("MDE_ATTN_SMEM_P") != nullptr && getenv("MDE_ATTN_SMEM_P")[0] == '1';
+  // MDE_ATTN=ps selects the persistent kernel (K/V loaded once for both query tiles; A/B testing: 19.7 us against 18.1 us
+  // at B=32, its 384 (image, head) pairs are 2.6 waves of 148 CTAs); default: one query tile per CTA, 2 CTAs per SM
+  static const bool persistent = getenv("MDE_ATTN") != nullptr && strcmp(getenv("MDE_ATTN"), "ps") == 0;
   if (smem_p) launch_k(vit_attn_kernel, dim3((unsigned)slabs), dim3(256), kAttnSmem, stream, p);
-  else launch_k(vit_attn_tp_kernel, dim3((unsigned)(2 * slabs)), dim3(128), kTpSmem, stream, p);
+  else if (!persistent) launch_k(vit_attn_tp_kernel, dim3((unsigned)(2 * slabs)), dim3(128), kTpSmem, stream, p);
+  else launch_k(vit_attn_ps_kernel, dim3((unsigned)(slabs < (uint64_t)sm_count() ? slabs : (uint64_t)sm_count())), dim3(320), kPsSmem, stream, p);
   MDE_CHECK_LAUNCH();
   return MDE_OK;
 }
