@@ -243,6 +243,52 @@ int mde_refine_pack_inputs(const float* rgb, const float* depth, int B, int H, i
 int mde_refine_output(const mde_f16* feat_padded, int cstride, const float* w32, const float* bias1, const float* depth,
                       const float* gate, int B, int H, int W, float* out, mde_stream_t stream);
 
+/* ======================= callers on either side of the forward path =======================
+
+ * ---- utils/terrain_reconstruction_fixed.py:18-70 TerrainReconstructor.create_point_cloud, :72-108 reconstruct_terrain,
+ *      :168-171 MarsTerrainMapper.infer_depth's disp_to_depth (layers.py:16-25) -----------------------------------------
+ * src f32 [B][H][W]: depth maps, or (from_disp != 0) the model's disparity maps, converted first as
+ *   depth = 1 / (1/max_depth + (1/min_depth - 1/max_depth) * disp)   (float32 steps, as torch evaluates layers.py:21-24).
+ * For every image, the pixels with min_depth < z < max_depth (float32 compare) are back-projected,
+ *   x = (u - cx) * z / fx,  y = (v - cy) * z / fy,  intrinsics4 = {fx, fy, cx, cy} (HOST pointer),
+ * and written COMPACTED IN RASTER ORDER to points[b][0..counts[b])[3]; image b's run starts at element b*H*W*3 of `points`
+ * (capacity B*H*W*3 elements).  points_f64 != 0: float64 points — what NumPy >= 2 produces for the reference's default
+ * (float64) intrinsics, u/v/z being float32; points_f64 == 0: float32 points, every step rounded to float32 (float32
+ * intrinsics).  Both are bit-identical to the NumPy expressions.  rgb (optional, [B][H][W][3] uint8, or float32 when
+ * rgb_f32 != 0) is compacted the same way into colors (:99-104).  counts: int32 [B] on the device.  scratch:
+ * mde_point_cloud_scratch_bytes(B,H,W) bytes.  One pass: 4 B read per pixel, 12/24 B written per surviving point. */
+long long mde_point_cloud_scratch_bytes(int B, int H, int W);
+int mde_point_cloud(const float* src, int B, int H, int W, int from_disp, double min_depth, double max_depth,
+                    const double* intrinsics4, int points_f64, void* points, const void* rgb, int rgb_f32, void* colors,
+                    int* counts, void* scratch, mde_stream_t stream);
+
+/* ---- layers.py:16-25 disp_to_depth as MarsTerrainMapper.infer_depth calls it (terrain_reconstruction_fixed.py:168-171) ----
+ * depth[i] = 1 / (1/max_depth + (1/min_depth - 1/max_depth) * disp[i]); the two scalars are formed in double and rounded to
+ * float32, the multiply, add and divide round to float32 one by one (what torch does for a float32 tensor and Python-float
+ * scalars): bit-identical to the reference on CPU.  16-byte aligned pointers. */
+int mde_disp_to_depth(const float* disp, long long count, double min_depth, double max_depth, float* depth, mde_stream_t stream);
+
+/* ---- models/refinement.py:354-388 DepthQualityEnhancement.temporal_consistency_filter ----
+ * out f64 [count] = sum_n weights[n] * maps[n][i], float32 maps times float64 weights added map by map in float64
+ * (np.sum(stacked * weights[:, None, None], axis=0)); weights are already normalised by the caller (:378-381).
+ * maps / weights are HOST arrays (of device pointers / doubles), n <= MDE_MAX_TEMPORAL_MAPS. */
+#define MDE_MAX_TEMPORAL_MAPS 16
+int mde_temporal_mean(const float* const* maps, const double* weights, int n, long long count, double* out,
+                      mde_stream_t stream);
+
+/* ---- models/refinement.py:190-243 DepthQualityEnhancement.bilateral_depth_filter ----
+ * depth f32 [H][W] -> out f32 [H][W]:  n = (depth - min) / (max - min + 1e-8);  f = bilateral(n);  out = f * (max - min) + min,
+ * min/max taken on the device (no host round trip).  guide == NULL: cv2.bilateralFilter's float32 algorithm (window of
+ * radius <= 7 clipped to a circle, colour weight from a 4096-bin linearly interpolated table of exp(-0.5 (dv/sigma_color)^2)
+ * built from the range of n, BORDER_REFLECT_101; the input is returned when max(n) - min(n) < FLT_EPSILON).  guide != NULL
+ * (uint8 [H][W][3]): cv2.ximgproc.jointBilateralFilter — colour weight joint_lut[|dr|+|dg|+|db|] of the guide, centre
+ * pixel included (joint_lut: f32 [768] = exp(-0.5 (i/sigma_color)^2); ximgproc is not installed in the build image: this
+ * branch restates the published algorithm, parity unpinned).  space_w: f32 [15][15], exp(-0.5 (r/sigma_space)^2) for
+ * r = sqrt(dy^2+dx^2) <= radius, 0 elsewhere.  scratch: MDE_BILATERAL_SCRATCH_FLOATS floats.  out != depth. */
+#define MDE_BILATERAL_SCRATCH_FLOATS 4128
+int mde_bilateral_depth(const float* depth, int H, int W, const uint8_t* guide, float sigma_color, const float* space_w,
+                        const float* joint_lut, float* scratch, float* out, mde_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -2,7 +2,8 @@
 ``models.model.DepthAnything`` / ``models.enhanced_model.EnhancedDepthAnything``)."""
 from .model import DepthAnything, source_scale  # noqa: F401
 from .enhanced_model import EnhancedDepthAnything  # noqa: F401
-from .refinement import MultiScaleDepthFusion, TextureAwareRefinementModule  # noqa: F401
+from .refinement import DepthQualityEnhancement, MultiScaleDepthFusion, TextureAwareRefinementModule  # noqa: F401
+from .terrain import MarsTerrainMapper, TerrainReconstructor  # noqa: F401
 from .layers import disp_to_depth  # noqa: F401
 from .pipeline import BatchPipeline  # noqa: F401
 

@@ -22,8 +22,10 @@ RANGE_SCRATCH_FLOATS = 6 * 8192
 GEMM_LN_MIN_ROWS = 1024  # MDE_GEMM_LN_MIN_ROWS
 MAX_MAPS = 8
 MAX_FUSION_SCALES = 4
+MAX_TEMPORAL_MAPS = 16
+BILATERAL_SCRATCH_FLOATS = 4128
 
-_p, _i, _f = C.c_void_p, C.c_int, C.c_float
+_p, _i, _f, _d, _ll = C.c_void_p, C.c_int, C.c_float, C.c_double, C.c_longlong
 
 
 class MapDesc(C.Structure):
@@ -58,8 +60,13 @@ SIGNATURES = {
     "mde_depth_fusion": [C.POINTER(_p), C.POINTER(_i), C.POINTER(_i), _i, _i, _i, _i, _p, _p, _p, _p, _p, _p],
     "mde_refine_pack_inputs": [_p, _p, _i, _i, _i, _p, _p, _p],
     "mde_refine_output": [_p, _i, _p, _p, _p, _p, _i, _i, _i, _p, _p],
+    "mde_point_cloud_scratch_bytes": [_i, _i, _i],
+    "mde_point_cloud": [_p, _i, _i, _i, _i, _d, _d, C.POINTER(_d), _i, _p, _p, _i, _p, _p, _p, _p],
+    "mde_disp_to_depth": [_p, _ll, _d, _d, _p, _p],
+    "mde_temporal_mean": [C.POINTER(_p), C.POINTER(_d), _i, _ll, _p, _p],
+    "mde_bilateral_depth": [_p, _i, _i, _p, _f, _p, _p, _p, _p, _p],
 }
-_RESTYPES = {"mde_last_error": C.c_char_p}
+_RESTYPES = {"mde_last_error": C.c_char_p, "mde_point_cloud_scratch_bytes": C.c_longlong}
 
 _lock = threading.Lock()
 _lib = None

@@ -199,3 +199,49 @@ def input_stage(x, bn4x3, eps, scratch, affine, raw224, patches):
     L.call("mde_input_stage", _ptr(x, F32), B, H, W, _ptr(bn4x3, F32), float(eps), _ptr(scratch, F32), _ptr(affine, F32), _ptr(raw224, F32),
            _ptr(patches, BF16), _stream())
     return patches
+
+
+def point_cloud(src, intrinsics4, min_depth, max_depth, from_disp=False, f64=True, rgb=None):
+    """terrain_reconstruction_fixed.py:18-108 for a batch: src f32 [B,H,W] (depth, or disparity with ``from_disp``) ->
+    (points [B,H*W,3] f32/f64 capacity buffer, colors or None, counts int32 [B]); image b's points are points[b, :counts[b]]."""
+    B, H, W = src.shape
+    dev = src.device
+    points = torch.empty(B, H * W, 3, device=dev, dtype=torch.float64 if f64 else F32)
+    counts = torch.empty(B, device=dev, dtype=torch.int32)
+    scratch = torch.empty(int(L.load().mde_point_cloud_scratch_bytes(B, H, W)), device=dev, dtype=torch.uint8)
+    colors = None
+    if rgb is not None:
+        if rgb.shape != (B, H, W, 3) or rgb.dtype not in (torch.uint8, F32):
+            raise ValueError(f"rgb must be uint8 or float32 [B,H,W,3] matching the depth maps, got {tuple(rgb.shape)} {rgb.dtype}")
+        colors = torch.empty(B, H * W, 3, device=dev, dtype=rgb.dtype)
+    k4 = (C.c_double * 4)(*[float(v) for v in intrinsics4])
+    L.call("mde_point_cloud", _ptr(src, F32), B, H, W, int(bool(from_disp)), float(min_depth), float(max_depth), k4, int(bool(f64)),
+           _ptr(points), _ptr(rgb), int(rgb is not None and rgb.dtype == F32), _ptr(colors), _ptr(counts, torch.int32), _ptr(scratch), _stream())
+    return points, colors, counts
+
+
+def temporal_mean(maps, weights, out=None):
+    """refinement.py:354-388: maps = list of f32 tensors of one shape, weights = normalised python floats -> f64 tensor."""
+    n = len(maps)
+    ptrs = (C.c_void_p * n)(*[_ptr(m, F32).value for m in maps])
+    w = (C.c_double * n)(*[float(v) for v in weights])
+    out = out if out is not None else torch.empty(maps[0].shape, device=maps[0].device, dtype=torch.float64)
+    L.call("mde_temporal_mean", ptrs, w, n, maps[0].numel(), _ptr(out, torch.float64), _stream())
+    return out
+
+
+def bilateral_depth(depth, sigma_color, space_w, guide=None, joint_lut=None, out=None):
+    """refinement.py:190-243 on the device: depth f32 [H,W]; guide uint8 [H,W,3] selects the joint form."""
+    H, W = depth.shape
+    scratch = torch.empty(L.BILATERAL_SCRATCH_FLOATS, device=depth.device, dtype=F32)
+    out = out if out is not None else torch.empty_like(depth)
+    L.call("mde_bilateral_depth", _ptr(depth, F32), H, W, _ptr(guide, torch.uint8) if guide is not None else _ptr(None), float(sigma_color),
+           _ptr(space_w, F32), _ptr(joint_lut, F32) if joint_lut is not None else _ptr(None), _ptr(scratch, F32), _ptr(out, F32), _stream())
+    return out
+
+
+def disp_to_depth(disp, min_depth, max_depth, out=None):
+    """layers.py:16-25 (depth only) on the device, bit-identical to the torch CPU expression."""
+    out = out if out is not None else torch.empty_like(disp)
+    L.call("mde_disp_to_depth", _ptr(disp, F32), disp.numel(), float(min_depth), float(max_depth), _ptr(out, F32), _stream())
+    return out

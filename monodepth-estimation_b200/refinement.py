@@ -6,10 +6,14 @@ The reference's ``TextureAwareRefinementModule.forward`` raises on every valid i
 (``refinement.py:88`` convolves a 1-channel map with a 3-channel Sobel weight; the
 value it would build is never used), so this implementation computes the live
 arithmetic, ``refinement.py:68-85`` and ``:92-107``.  ``DepthQualityEnhancement``
-(OpenCV/NumPy CPU post-processing, ``refinement.py:185-388``) is out of scope.
+(``refinement.py:185-388``, OpenCV/NumPy CPU post-processing with no caller in the reference;
+SURVEY.md §8(f)#4): ``bilateral_depth_filter`` and ``temporal_consistency_filter`` run on the
+device; ``edge_preserving_smoothing`` (cv2.ximgproc guided filter) and ``fill_depth_holes``
+(scipy connected components) are not built and raise.
 """
 from __future__ import annotations
 
+import numpy as np
 import torch
 import torch.nn as nn
 
@@ -61,3 +65,79 @@ class MultiScaleDepthFusion(nn.Module):
         from .engine import depth_fusion_forward
 
         return depth_fusion_forward(self, depth_scales)
+
+
+def _bilateral_tables(d, sigma_color, sigma_space, joint):
+    """cv2's window: radius d/2 (or round(1.5 sigma_space) for d <= 0), clipped to a circle; weights in double, stored float32."""
+    sigma_color = 1.0 if sigma_color <= 0 else float(sigma_color)
+    sigma_space = 1.0 if sigma_space <= 0 else float(sigma_space)
+    radius = max(int(d) // 2 if d > 0 else int(round(sigma_space * 1.5)), 1)
+    if radius > 7:
+        raise ValueError(f"bilateral window radius {radius} > 7 is not built (the reference uses d = 15)")
+    i, j = np.mgrid[-7:8, -7:8].astype(np.float64)
+    r = np.sqrt(i * i + j * j)
+    space = np.where(r <= radius, np.exp(r * r * (-0.5 / (sigma_space * sigma_space))), 0.0).astype(np.float32)
+    lut = None
+    if joint:
+        k = np.arange(3 * 256, dtype=np.float64)
+        lut = np.exp(k * k * (-0.5 / (sigma_color * sigma_color))).astype(np.float32)
+    return space, lut
+
+
+class DepthQualityEnhancement:
+    """``refinement.py:185-388``: NumPy in, NumPy out like the reference; the arithmetic runs in ``csrc/terrain.cu``."""
+
+    @staticmethod
+    def _device_map(depth_map):
+        a = depth_map.detach().cpu().numpy() if isinstance(depth_map, torch.Tensor) else np.asarray(depth_map)
+        a = np.squeeze(a).astype(np.float32)
+        if a.ndim != 2:
+            raise ValueError(f"expected one depth map, got shape {a.shape}")
+        if not torch.cuda.is_available():
+            raise RuntimeError("DepthQualityEnhancement needs a CUDA device (there is no CPU path)")
+        return torch.from_numpy(np.ascontiguousarray(a)).cuda()
+
+    @staticmethod
+    def bilateral_depth_filter(depth_map, rgb_image=None, sigma_space=15, sigma_color=0.05, sigma_depth=0.05):
+        """``refinement.py:190-243``: min/max normalise, bilateral (``rgb_image`` None) or joint bilateral filter, rescale."""
+        from . import ops
+
+        z = DepthQualityEnhancement._device_map(depth_map)
+        guide = None
+        if rgb_image is not None:
+            rgb = np.squeeze(rgb_image.detach().cpu().numpy() if isinstance(rgb_image, torch.Tensor) else np.asarray(rgb_image))
+            if rgb.dtype != np.uint8:
+                rgb = (rgb * 255).astype(np.uint8)  # :215-217
+            if rgb.shape != (*z.shape, 3):
+                raise ValueError(f"guide image must be [H,W,3] matching the depth map, got {rgb.shape}")
+            guide = torch.from_numpy(np.ascontiguousarray(rgb)).cuda()
+        space, lut = _bilateral_tables(sigma_space, sigma_color if guide is not None else sigma_depth, sigma_space, guide is not None)
+        out = ops.bilateral_depth(z, sigma_color if guide is not None else sigma_depth, torch.from_numpy(space).cuda(), guide,
+                                  None if lut is None else torch.from_numpy(lut).cuda())
+        return out.cpu().numpy()
+
+    @staticmethod
+    def edge_preserving_smoothing(depth_map, rgb_image=None, lambda_param=0.1):
+        raise NotImplementedError("cv2.ximgproc.guidedFilter (refinement.py:245-301) is not built; there is no CPU fallback")
+
+    @staticmethod
+    def fill_depth_holes(depth_map, max_hole_size=10):
+        raise NotImplementedError("connected-component hole filling (refinement.py:303-352) is not built; there is no CPU fallback")
+
+    @staticmethod
+    def temporal_consistency_filter(depth_maps, weights=None):
+        """``refinement.py:354-388``: weighted mean over frames, float64 like ``np.sum(stacked * weights[:, None, None], axis=0)``."""
+        from . import ops
+
+        if len(depth_maps) == 0:
+            return None
+        if len(depth_maps) == 1:
+            return depth_maps[0]
+        maps = [DepthQualityEnhancement._device_map(d) for d in depth_maps]
+        if any(m.shape != maps[0].shape for m in maps):
+            raise ValueError("all depth maps must have the same shape")
+        if weights is None:
+            w = np.ones(len(maps)) / len(maps)
+        else:
+            w = np.array(weights) / np.sum(weights)
+        return ops.temporal_mean(maps, w.astype(np.float64).tolist()).cpu().numpy()
