@@ -49,7 +49,7 @@ struct alignas(64) HaloParams {
 };
 
 template <int BLOCK_N, int ROWB>
-__global__ void __launch_bounds__(kHaloThreads, BLOCK_N <= 32 ? 2 : 1) conv_halo_kernel(const __grid_constant__ HaloParams p) {
+__global__ void __launch_bounds__(kHaloThreads, BLOCK_N <= 16 ? 3 : BLOCK_N <= 32 ? 2 : 1) conv_halo_kernel(const __grid_constant__ HaloParams p) {
   pdl_launch_dependents();
   constexpr int KC = ROWB / 2;
   constexpr int WB_RAW = BLOCK_N * ROWB;
@@ -220,11 +220,19 @@ static int launch_halo(HaloParams& p, int smem_bytes, cudaStream_t stream) {
     MDE_CHECK_CUDA(cudaFuncSetAttribute(conv_halo_kernel<BLOCK_N, ROWB>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
     smem_attr = 1;
   }
-  // persistent CTAs: as many per SM as registers / shared memory / TMEM columns allow (1 for the 64-channel layers)
-  int occ = 1;
-  MDE_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, conv_halo_kernel<BLOCK_N, ROWB>, kHaloThreads, smem_bytes));
+  // persistent CTAs: as many per SM as registers / shared memory / TMEM columns allow (1 for the 64-channel layers).  Computed
+  // here rather than with cudaOccupancyMaxActiveBlocksPerMultiprocessor: that call answered 1 for the first launch of an
+  // instantiation (before the carveout preference had taken effect) and 2 afterwards, so eager and captured runs differed.
+  static int regs_limit = 0;
+  if (regs_limit == 0) {
+    cudaFuncAttributes fa;
+    MDE_CHECK_CUDA(cudaFuncGetAttributes(&fa, conv_halo_kernel<BLOCK_N, ROWB>));
+    const int per_thread = (fa.numRegs + 7) & ~7;
+    regs_limit = std::max(1, 65536 / (per_thread * kHaloThreads));
+  }
   int tmem_cols = 32;
   while (tmem_cols < 2 * p.nblk * BLOCK_N) tmem_cols <<= 1;
+  int occ = std::min(regs_limit, (227 * 1024) / (smem_bytes + 1024));
   occ = std::max(1, std::min(occ, 512 / tmem_cols));
   int grid = sm_count() * occ;
   if (grid > p.total_tiles) grid = p.total_tiles;
@@ -250,19 +258,25 @@ int launch_conv_halo(int f16, const void* in, int B, int h, int w, int cin, int 
   const int chunks = cin / kc;
   const int wb = (block_n * rowb + 1023) & ~1023;
   const int weights_bytes = 9 * chunks * wb;
-  const int budget = 227 * 1024 - 1024 /*align*/ - 1024 /*view overrun pad*/ - 256 /*barriers*/ - weights_bytes;
   int th = 0, stages = 0, stage_bytes = 0;
-  for (int t = 8; t >= 2; t -= 2) {
+  // Low-channel layers are bound by the latency of the epilogue's dependent instruction chain, so resident warps matter more
+  // than pipeline depth: give up halo stages (down to 2) to fit 3 CTAs per SM (N = 16) or 2 (N = 32).  MDE_HALO_OCC overrides.
+  static const int occ_env = getenv("MDE_HALO_OCC") ? atoi(getenv("MDE_HALO_OCC")) : 0;
+  const int occ_target = occ_env > 0 ? occ_env : (block_n <= 16 ? 3 : block_n <= 32 ? 2 : 1);
+  for (int t = 8; t >= 2 && th == 0; t -= 2) {
     const int nblk = t / 2;
     if (2 * nblk * block_n > 512) continue;
     const int sb = ((t + 2) * kHaloPitch * rowb + 1023) & ~1023;
-    int st = budget / sb;
-    if (st > kHaloMaxStages) st = kHaloMaxStages;
-    if (st >= 2) {
-      th = t;
-      stages = st;
-      stage_bytes = sb;
-      break;
+    for (int oc = occ_target; oc >= 1; --oc) {
+      const int per_cta = (227 * 1024) / oc - 1024 /*per-CTA reservation*/ - 1024 /*align*/ - 1024 /*view overrun pad*/ - 256 /*barriers*/ - weights_bytes;
+      int st = per_cta / sb;
+      if (st > kHaloMaxStages) st = kHaloMaxStages;
+      if (st >= 2) {
+        th = t;
+        stages = st;
+        stage_bytes = sb;
+        break;
+      }
     }
   }
   if (th == 0) return MDE_ERR_UNSUPPORTED;
