@@ -129,14 +129,11 @@ __device__ __forceinline__ void epilogue_chunk(const P& p, float (&v)[NCOL], int
     }
     case MDE_EPI_PATCH_EMBED: {
       // A row (b, patch) -> token row b*197 + 1 + patch; + pos_embedding (tv:156); CLS row written by patch 0.
-      // With LayerNorm fusion (p.xb): also the bf16 copy of the row chunk and its (sum, sum of squares) partial.
       const int b = ri.m / 196, pp = ri.m - b * 196;
       const float* pos = reinterpret_cast<const float*>(p.aux0);
       const float4* ps = reinterpret_cast<const float4*>(pos + (size_t)(1 + pp) * MDE_VIT_DIM + n0);
       const size_t trow = (size_t)b * MDE_VIT_SEQ + 1 + pp;
       float4* dst = reinterpret_cast<float4*>(reinterpret_cast<float*>(p.out) + trow * MDE_VIT_DIM + n0);
-      const bool lnf = NCOL == 32 && p.xb != nullptr;  // one statistics slot per 32-column chunk
-      float s1 = 0.0f, s2 = 0.0f;
 #pragma unroll
       for (int j = 0; j < NCOL / 4; ++j) {
         const float4 q4 = __ldg(ps + j);
@@ -145,19 +142,6 @@ __device__ __forceinline__ void epilogue_chunk(const P& p, float (&v)[NCOL], int
         v[4 * j + 2] += q4.z;
         v[4 * j + 3] += q4.w;
         dst[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
-      }
-      if (lnf) {
-#pragma unroll
-        for (int j = 0; j < NCOL; ++j) {
-          s1 += v[j];
-          s2 = fmaf(v[j], v[j], s2);
-        }
-        uint4* xd = reinterpret_cast<uint4*>(reinterpret_cast<bf16*>(p.xb) + trow * MDE_VIT_DIM + n0);
-#pragma unroll
-        for (int j = 0; j < NCOL / 8; ++j)
-          xd[j] = make_uint4(pack_bf16x2(v[8 * j], v[8 * j + 1]), pack_bf16x2(v[8 * j + 2], v[8 * j + 3]),
-                             pack_bf16x2(v[8 * j + 4], v[8 * j + 5]), pack_bf16x2(v[8 * j + 6], v[8 * j + 7]));
-        *reinterpret_cast<float2*>(p.ln_out + ((size_t)(n0 >> 5) * p.ln_rows + trow) * 2) = make_float2(s1, s2);
       }
       if (pp == 0) {
         const float4* cls = reinterpret_cast<const float4*>(reinterpret_cast<const float*>(p.aux1) + n0);
@@ -173,20 +157,6 @@ __device__ __forceinline__ void epilogue_chunk(const P& p, float (&v)[NCOL], int
           c[4 * j + 2] = c4.z + q4.z;
           c[4 * j + 3] = c4.w + q4.w;
           d0[j] = make_float4(c[4 * j], c[4 * j + 1], c[4 * j + 2], c[4 * j + 3]);
-        }
-        if (lnf) {
-          float t1 = 0.0f, t2 = 0.0f;
-#pragma unroll
-          for (int j = 0; j < NCOL; ++j) {
-            t1 += c[j];
-            t2 = fmaf(c[j], c[j], t2);
-          }
-          uint4* xd = reinterpret_cast<uint4*>(reinterpret_cast<bf16*>(p.xb) + crow * MDE_VIT_DIM + n0);
-#pragma unroll
-          for (int j = 0; j < NCOL / 8; ++j)
-            xd[j] = make_uint4(pack_bf16x2(c[8 * j], c[8 * j + 1]), pack_bf16x2(c[8 * j + 2], c[8 * j + 3]),
-                               pack_bf16x2(c[8 * j + 4], c[8 * j + 5]), pack_bf16x2(c[8 * j + 6], c[8 * j + 7]));
-          *reinterpret_cast<float2*>(p.ln_out + ((size_t)(n0 >> 5) * p.ln_rows + crow) * 2) = make_float2(t1, t2);
         }
       }
       break;

@@ -65,11 +65,12 @@ struct alignas(64) Tc2Params {
   int cout, h, w, out_cstride, out_coff, f16, st32;
   // LayerNorm fusion (see LnFuse in common.h)
   void* xb;             // producer: bf16 copy of the fp32 output, row pitch xb_ld
-  float* ln_out;        // producer: [N/32][ln_rows][2] partial (sum, sum of squares) per 32-column chunk (slot-major: coalesced)
+  float* ln_out;        // producer: [N/256][8][M][2] partial (sum, sum of squares), slot-major (coalesced); see ln_slot()
   int ln_rows, xb_ld;
-  const float* ln_in;   // consumer: [ln_slots = K/32][M][2]
+  const float* ln_in;   // consumer: the producer's buffer, [ln_ktiles = K/256][8][M][2]
   const float* ln_cs;   // consumer: [N] column sums of the folded weight
-  int ln_slots;
+  int ln_ktiles;        // consumer: the producer's N / 256
+  int ln_full;          // consumer: the producer's full_items (its tiles >= ln_full were split into four 64-column items)
   float ln_eps, ln_invk;
   long long* prof;      // debug (mde_debug_gemm_prof): per CTA 8 counters of cycles spent waiting / working, or null
 };
@@ -245,24 +246,44 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(k2Threads, 1) tc_gem
         const Item itn = decode_item(p, has_next ? inext : i);
         const int nch = it.bn / cw;
         const int row0 = it.m0 + (int)rank * 128 + q * 32;
-        float mu = 0.0f, rstd = 1.0f;  // LayerNorm of this thread's A row, from the producer's partial sums (fixed order: deterministic)
+        // LayerNorm of this thread's A row from the producer's partial sums.  Slot layout per 256-column producer tile: a whole
+        // tile leaves two partials (epilogue-warp parity 0 / 1 = even / odd 32-column chunks, each summed chunk by chunk), a
+        // tile of the split tail leaves one partial per chunk (slot = chunk).  Both are combined in the SAME order here —
+        // ((c0 + c2) + c4) + c6 plus ((c1 + c3) + c5) + c7 — so the statistics do not depend on how the producer was tiled.
+        float mu = 0.0f, rstd = 1.0f;
         if (LNF && EC == 1 && p.ln_in && row0 + lane < p.M) {
-          // slot-major [K/32][M][2]: a warp reads 32 consecutive rows of one slot = 256 contiguous bytes per instruction
           const float2* st = reinterpret_cast<const float2*>(p.ln_in) + (row0 + lane);
-          float s1 = 0.0f, s2 = 0.0f;
-          for (int t0 = 0; t0 < p.ln_slots; t0 += 8) {  // eight independent loads in flight (host checked ln_slots % 8 == 0), summed in slot order
-            float2 a[8];
+          const int mt = it.m0 >> 8;
+          float2 a0[4], a1[4];
 #pragma unroll
-            for (int u = 0; u < 8; ++u) a[u] = __ldg(st + (size_t)(t0 + u) * p.M);
-#pragma unroll
-            for (int u = 0; u < 8; ++u) {
-              s1 += a[u].x;
-              s2 += a[u].y;
+          for (int nt = 0; nt < 4; ++nt) {  // host checked ln_ktiles <= 4; all loads in flight together
+            a0[nt] = a1[nt] = make_float2(0.0f, 0.0f);
+            if (nt < p.ln_ktiles) {
+              a0[nt] = __ldg(st + (size_t)(nt * 8) * p.M);
+              a1[nt] = __ldg(st + (size_t)(nt * 8 + 1) * p.M);
             }
+          }
+          float s1 = 0.0f, s2 = 0.0f;
+#pragma unroll
+          for (int nt = 0; nt < 4; ++nt) {
+            if (nt >= p.ln_ktiles) break;
+            float2 w0 = a0[nt], w1 = a1[nt];
+            if (mt * p.ln_ktiles + nt >= p.ln_full) {  // split tile (uniform per warp, at most one tile row of the producer)
+              float2 e[6];
+#pragma unroll
+              for (int u = 0; u < 6; ++u) e[u] = __ldg(st + (size_t)(nt * 8 + 2 + u) * p.M);
+              w0.x = ((w0.x + e[0].x) + e[2].x) + e[4].x;
+              w0.y = ((w0.y + e[0].y) + e[2].y) + e[4].y;
+              w1.x = ((w1.x + e[1].x) + e[3].x) + e[5].x;
+              w1.y = ((w1.y + e[1].y) + e[3].y) + e[5].y;
+            }
+            s1 += w0.x + w1.x;
+            s2 += w0.y + w1.y;
           }
           mu = s1 * p.ln_invk;
           rstd = rsqrtf(fmaxf(fmaf(-mu, mu, s2 * p.ln_invk), 0.0f) + p.ln_eps);
         }
+        const float nmr = -mu * rstd;
         MDE_PROF(long long t0 = 0; const bool prof = p.prof && warp == 2 && lane == 0; if (prof) t0 = clk();)
         mbar_wait(&tfull_bar[acc], acc_phase);
         MDE_PROF(if (prof) {
@@ -272,6 +293,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(k2Threads, 1) tc_gem
         })
         tc_fence_after();
         const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * 256;
+        float ls1 = 0.0f, ls2 = 0.0f;  // LayerNorm producer: this row's (sum, sum of squares) over the chunks this warp handles
 #pragma unroll 1
         for (int c = par; c < nch; c += 2, ++g) {
           uint8_t* buf = stg + (g & 1) * k2EpiBufBytes;
@@ -298,6 +320,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(k2Threads, 1) tc_gem
             tmem_ld_wait();
             if (resid) mbar_wait(&rbar[g & 1], (g >> 1) & 1);
             const float4* bp = reinterpret_cast<const float4*>(p.bias + n0);
+            float c1 = 0.0f, c2 = 0.0f;  // this chunk's partial, started from zero (see the consumer: tiling-independent sums)
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
               float4* sp = reinterpret_cast<float4*>(row + ((static_cast<uint32_t>(j) ^ sw) << 4));
@@ -312,6 +335,14 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(k2Threads, 1) tc_gem
                 o.w += r4.w;
               }
               *sp = o;
+              if constexpr (LNF) {
+                c1 += (o.x + o.y) + (o.z + o.w);
+                c2 = fmaf(o.x, o.x, fmaf(o.y, o.y, fmaf(o.z, o.z, fmaf(o.w, o.w, c2))));
+              }
+            }
+            if constexpr (LNF) {
+              ls1 += c1;
+              ls2 += c2;
             }
           } else {
             uint32_t raw[64];
@@ -336,14 +367,17 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(k2Threads, 1) tc_gem
                 for (int j = 0; j < 16; ++j) {
                   const float4 b4 = __ldg(bp + j);
                   float4 a4 = make_float4(__uint_as_float(raw[4 * j]), __uint_as_float(raw[4 * j + 1]), __uint_as_float(raw[4 * j + 2]), __uint_as_float(raw[4 * j + 3]));
-                  if (lnc) {
+                  if (lnc) {  // (acc - mu * colsum) * rstd + bias  ==  acc * rstd + (nmr * colsum + bias),  nmr = -mu * rstd
                     const float4 c4 = __ldg(csp + j);
-                    a4 = make_float4(fmaf(-mu, c4.x, a4.x) * rstd, fmaf(-mu, c4.y, a4.y) * rstd, fmaf(-mu, c4.z, a4.z) * rstd, fmaf(-mu, c4.w, a4.w) * rstd);
+                    a4 = make_float4(fmaf(a4.x, rstd, fmaf(nmr, c4.x, b4.x)), fmaf(a4.y, rstd, fmaf(nmr, c4.y, b4.y)),
+                                     fmaf(a4.z, rstd, fmaf(nmr, c4.z, b4.z)), fmaf(a4.w, rstd, fmaf(nmr, c4.w, b4.w)));
+                  } else {
+                    a4 = make_float4(a4.x + b4.x, a4.y + b4.y, a4.z + b4.z, a4.w + b4.w);
                   }
-                  dst[(size_t)(4 * j) * MDE_VT_PITCH] = __float2bfloat16_rn(a4.x + b4.x);
-                  dst[(size_t)(4 * j + 1) * MDE_VT_PITCH] = __float2bfloat16_rn(a4.y + b4.y);
-                  dst[(size_t)(4 * j + 2) * MDE_VT_PITCH] = __float2bfloat16_rn(a4.z + b4.z);
-                  dst[(size_t)(4 * j + 3) * MDE_VT_PITCH] = __float2bfloat16_rn(a4.w + b4.w);
+                  dst[(size_t)(4 * j) * MDE_VT_PITCH] = __float2bfloat16_rn(a4.x);
+                  dst[(size_t)(4 * j + 1) * MDE_VT_PITCH] = __float2bfloat16_rn(a4.y);
+                  dst[(size_t)(4 * j + 2) * MDE_VT_PITCH] = __float2bfloat16_rn(a4.z);
+                  dst[(size_t)(4 * j + 3) * MDE_VT_PITCH] = __float2bfloat16_rn(a4.w);
                 }
               }
               continue;  // nothing staged, no TMA store for this chunk (g is advanced by the loop header)
@@ -355,16 +389,17 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(k2Threads, 1) tc_gem
               float v[8];
 #pragma unroll
               for (int t = 0; t < 8; ++t) v[t] = __uint_as_float(raw[8 * j + t]);
-              if (lnc) {
-                const float4 c0 = __ldg(csp + 2 * j), c1 = __ldg(csp + 2 * j + 1);
-                const float cs[8] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w};
-#pragma unroll
-                for (int t = 0; t < 8; ++t) v[t] = fmaf(-mu, cs[t], v[t]) * rstd;
-              }
               {
                 const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+                if (lnc) {  // (acc - mu * colsum) * rstd + bias  ==  acc * rstd + (nmr * colsum + bias),  nmr = -mu * rstd
+                  const float4 c0 = __ldg(csp + 2 * j), c1 = __ldg(csp + 2 * j + 1);
+                  const float cs[8] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w};
 #pragma unroll
-                for (int t = 0; t < 8; ++t) v[t] += bb[t];
+                  for (int t = 0; t < 8; ++t) v[t] = fmaf(v[t], rstd, fmaf(nmr, cs[t], bb[t]));
+                } else {
+#pragma unroll
+                  for (int t = 0; t < 8; ++t) v[t] += bb[t];
+                }
               }
               if (gelu) {
 #pragma unroll
@@ -391,8 +426,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(k2Threads, 1) tc_gem
           }
           if (LNF && EC == 0 && p.xb) {
             // LayerNorm producer: bf16 copy of the staged fp32 chunk, read back with lane = four columns so that a warp store
-            // covers four 64-byte row segments (a row-per-thread store would touch 32 lines per instruction), plus the
-            // row's partial sums.  The staged tile is only read here and by the TMA store.
+            // covers four 64-byte row segments (a row-per-thread store would touch 32 lines per instruction).  The staged
+            // tile is only read here and by the TMA store.
             bf16* xb = reinterpret_cast<bf16*>(p.xb);
             const int cc = (lane & 7) * 4;  // lane = four columns: a warp store covers four 64-byte row segments
 #pragma unroll
@@ -402,18 +437,13 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(k2Threads, 1) tc_gem
               if (row0 + rr < p.M)
                 *reinterpret_cast<uint2*>(xb + (size_t)(row0 + rr) * p.xb_ld + n0 + cc) = make_uint2(pack_bf16x2(f.x, f.y), pack_bf16x2(f.z, f.w));
             }
-            if (row0 + lane < p.M) {  // this thread's own row, re-read from the staged tile (keeps the common path free of the sums)
-              float ls1 = 0.0f, ls2 = 0.0f;
-#pragma unroll
-              for (int j = 0; j < 8; ++j) {
-                const float4 o = *reinterpret_cast<const float4*>(row + ((static_cast<uint32_t>(j) ^ sw) << 4));  // logical column order: the sums do not depend on the lane
-                ls1 += (o.x + o.y) + (o.z + o.w);
-                ls2 = fmaf(o.x, o.x, fmaf(o.y, o.y, fmaf(o.z, o.z, fmaf(o.w, o.w, ls2))));
-              }
-              *reinterpret_cast<float2*>(p.ln_out + ((size_t)(n0 >> 5) * p.M + (row0 + lane)) * 2) = make_float2(ls1, ls2);
-            }
             __syncwarp();  // every lane has read the tile before lane 0 may recycle the buffer
           }
+        }
+        if (LNF && EC == 0 && p.xb && row0 + lane < p.M) {
+          // whole tile: slot = parity (even / odd chunks); split tail item (64 columns, one chunk per warp): slot = chunk index
+          const int slot = (it.n0 >> 8) * 8 + (it.bn == 256 ? par : ((it.n0 & 255) >> 5) + par);
+          *reinterpret_cast<float2*>(p.ln_out + ((size_t)slot * p.M + (row0 + lane)) * 2) = make_float2(ls1, ls2);
         }
         tc_fence_before();
         __syncwarp();
@@ -475,8 +505,8 @@ int launch_gemm_pair(const void* A, int lda, const void* W, int ldw, int M, int 
   if (ln) {
     const bool f32res = epilogue == MDE_EPI_BIAS_RESID_F32 || epilogue == MDE_EPI_BIAS_F32 || epilogue == MDE_EPI_PATCH_EMBED;
     if (ln->xb_out || ln->stats_out) {  // producer
-      if (!(ln->xb_out && ln->stats_out) || !f32res || N % 64 != 0 || (uintptr_t)ln->xb_out % 16 || (uintptr_t)ln->stats_out % 16) {
-        set_error("mde_gemm_ln_bf16: xb_out + stats_out need an fp32 epilogue (RESID_F32 / BIAS_F32 / PATCH_EMBED), N %% 64 == 0, 16-byte alignment");
+      if (!(ln->xb_out && ln->stats_out) || !f32res || epilogue == MDE_EPI_PATCH_EMBED || N % 256 != 0 || (uintptr_t)ln->xb_out % 16 || (uintptr_t)ln->stats_out % 16) {
+        set_error("mde_gemm_ln_bf16: xb_out + stats_out need an fp32 TMA epilogue (RESID_F32 / BIAS_F32), N %% 256 == 0, 16-byte alignment");
         return MDE_ERR_BAD_ARGUMENT;
       }
       p.xb = ln->xb_out;
@@ -486,13 +516,17 @@ int launch_gemm_pair(const void* A, int lda, const void* W, int ldw, int M, int 
     }
     if (ln->stats_in || ln->colsum) {  // consumer
       const bool b16 = epilogue == MDE_EPI_BIAS_BF16 || epilogue == MDE_EPI_BIAS_GELU_BF16 || epilogue == MDE_EPI_QKV_SPLIT;
-      if (!(ln->stats_in && ln->colsum) || !b16 || K % 256 != 0 || (uintptr_t)ln->stats_in % 16 || (uintptr_t)ln->colsum % 16) {
-        set_error("mde_gemm_ln_bf16: stats_in + colsum need a bf16 epilogue (BIAS_BF16 / BIAS_GELU_BF16 / QKV_SPLIT), K %% 256 == 0, 16-byte alignment");
+      if (!(ln->stats_in && ln->colsum) || !b16 || K % 256 != 0 || K > 1024 || (uintptr_t)ln->stats_in % 16 || (uintptr_t)ln->colsum % 16) {
+        set_error("mde_gemm_ln_bf16: stats_in + colsum need a bf16 epilogue (BIAS_BF16 / BIAS_GELU_BF16 / QKV_SPLIT), K %% 256 == 0, K <= 1024, 16-byte alignment");
         return MDE_ERR_BAD_ARGUMENT;
       }
       p.ln_in = ln->stats_in;
       p.ln_cs = ln->colsum;
-      p.ln_slots = K / 32;
+      p.ln_ktiles = K / 256;
+      {  // the producer (same M, N = this K) ran launch_gemm_pair's schedule: whole waves of 256x256 tiles, the rest split four ways
+        const int ptiles = ceil_div(M, 256) * p.ln_ktiles, pclusters = sm_count() / 2;
+        p.ln_full = (ptiles / pclusters) * pclusters;
+      }
       p.ln_eps = ln->eps;
       p.ln_invk = 1.0f / (float)K;
     }

@@ -161,16 +161,12 @@ class DepthEngine:
     def _vit(self, ws, w, want=None, on_tap=None):
         enc, B = w["enc"], ws.B
         n = 0
-        # Optional (MDE_LN_FUSION=1): LayerNorm folded into the GEMMs around it when the CTA-pair kernel runs (M >= 1024) — the
-        # producer of the residual stream also writes bf16(x) into ws.h and per-row partial sums, the QKV / fc1 epilogues
-        # normalise.  24 launches fewer, parity-tested, but measured a wash at B=32 (2.456 vs 2.447 ms): the producers are
-        # single-wave GEMMs whose epilogue is exposed (+3.3 us each), the consumers reload row statistics per tile (+5.5 us).
+        # LayerNorm folded into the GEMMs around it when the CTA-pair kernel runs (M >= 1024; MDE_LN_FUSION=0 switches it off): the
+        # producer of the residual stream (out-proj, fc2) also writes bf16(x) into ws.h and per-row partial sums, the QKV / fc1
+        # epilogues normalise.  23 launches fewer per forward (the LayerNorm after the patch embedding stays a kernel).
         fused = ws.B * 197 >= L.GEMM_LN_MIN_ROWS and _LN_FUSION
         prod = dict(xb_out=ws.h, stats_out=ws.lnstats) if fused else {}
-        if fused:
-            ops.gemm_ln(ws.patches, enc["patch_w"], enc["patch_b"], L.EPI_PATCH_EMBED, ws.xa, enc["pos"], enc["cls"], **prod)
-        else:
-            ops.gemm(ws.patches, enc["patch_w"], enc["patch_b"], L.EPI_PATCH_EMBED, ws.xa, enc["pos"], enc["cls"])
+        ops.gemm(ws.patches, enc["patch_w"], enc["patch_b"], L.EPI_PATCH_EMBED, ws.xa, enc["pos"], enc["cls"])
         n += 1
         # residual stream: x_in --(attention)--> x_mid --(MLP)--> x_out.  x_in is dead once the out-proj
         # epilogue has read it, so two working buffers suffice; hooked layers (encoder.py:44-50) write
@@ -183,11 +179,16 @@ class DepthEngine:
             if fused:
                 qw, qb, qcs = ly["qkv_ln"]
                 fw, fb, fcs = ly["fc1_ln"]
-                ops.gemm_ln(ws.h, qw, qb, L.EPI_QKV_SPLIT, ws.q, ws.k, ws.vt, stats_in=ws.lnstats, colsum=qcs)
+                if i == 0:
+                    ops.layernorm(x_in, ly["ln1_w"], ly["ln1_b"], 1e-6, ws.h)
+                    ops.gemm(ws.h, ly["qkv_w"], ly["qkv_b"], L.EPI_QKV_SPLIT, ws.q, ws.k, ws.vt)
+                    n += 1
+                else:
+                    ops.gemm_ln(ws.h, qw, qb, L.EPI_QKV_SPLIT, ws.q, ws.k, ws.vt, stats_in=ws.lnstats, colsum=qcs)
                 ops.vit_attention(ws.q, ws.k, ws.vt, B, ws.attn)
                 ops.gemm_ln(ws.attn, ly["proj_w"], ly["proj_b"], L.EPI_BIAS_RESID_F32, x_mid, x_in, **prod)
                 ops.gemm_ln(ws.h, fw, fb, L.EPI_BIAS_GELU_BF16, ws.mlp, stats_in=ws.lnstats, colsum=fcs)
-                ops.gemm_ln(ws.mlp, ly["fc2_w"], ly["fc2_b"], L.EPI_BIAS_RESID_F32, x_out, x_mid, **prod)
+                ops.gemm_ln(ws.mlp, ly["fc2_w"], ly["fc2_b"], L.EPI_BIAS_RESID_F32, x_out, x_mid, **(prod if i < 11 else {}))  # nothing normalises the last output (tv:157 is discarded)
                 n += 5
             else:
                 ops.layernorm(x_in, ly["ln1_w"], ly["ln1_b"], 1e-6, ws.h)

@@ -79,22 +79,39 @@ def test_gemm_pair_kernel_qkv_split():
 
 
 # --------------------------------------------------------------------------- LayerNorm folded into the neighbouring GEMMs
-@pytest.mark.parametrize("M,K,epi", [(6304, 768, "resid"), (1576, 3072, "resid"), (1100, 768, "f32"), (8 * 196, 768, "patch")])
+def _ln_slots(x, ops):
+    """The statistics layout of mde_gemm_ln_bf16 (include/mde.h) for an fp32 matrix x [M][N]: [N/256][8][M][2].  A producer tile
+    that ran whole leaves two partials (even / odd 32-column chunks), a tile of the split tail one partial per chunk."""
+    M, N = x.shape
+    nt_n = N // 256
+    clusters = ops.sm_count() // 2
+    tiles = (M + 255) // 256 * nt_n
+    full = tiles // clusters * clusters
+    ch = x.double().view(M, nt_n, 8, 32)
+    part = torch.stack([ch.sum(-1), (ch * ch).sum(-1)], -1)  # [M][nt][8][2]
+    st = torch.full((nt_n, 8, M, 2), float("nan"), dtype=torch.float64, device=x.device)
+    for mt in range((M + 255) // 256):
+        r = slice(mt * 256, min(M, mt * 256 + 256))
+        for nt in range(nt_n):
+            if mt * nt_n + nt < full:
+                st[nt, 0, r] = part[r, nt, 0::2].sum(1)
+                st[nt, 1, r] = part[r, nt, 1::2].sum(1)
+            else:
+                st[nt, :, r] = part[r, nt].transpose(0, 1)
+    return st.view(nt_n * 8, M, 2)
+
+
+@pytest.mark.parametrize("M,K,epi", [(6304, 768, "resid"), (1576, 3072, "resid"), (1100, 768, "f32"), (19 * 256, 768, "resid")])
 def test_gemm_ln_producer(M, K, epi):
     """The producer epilogues also emit bf16(x) and per-row (sum, sum of squares) partials of the fp32 output."""
     L, ops = _mods()
     N = 768
     a, w, b = _rand(M, K, seed=201, dtype=BF16), _rand(N, K, seed=202, scale=K ** -0.5, dtype=BF16), _rand(N, seed=203)
-    rows = M // 196 * 197 if epi == "patch" else M
+    rows = M
     out = torch.full((rows, N), float("nan"), device="cuda")
     xb = torch.full((rows + 2, N), 5.0, device="cuda", dtype=BF16)
-    st = torch.full((N // 32, rows, 2), float("nan"), device="cuda")  # chunk-major
-    if epi == "patch":
-        pos, cls = _rand(197, 768, seed=204, scale=0.5), _rand(768, seed=205, scale=0.5)
-        ops.gemm_ln(a, w, b, L.EPI_PATCH_EMBED, out, pos, cls, xb_out=xb, stats_out=st)
-        ref = torch.empty_like(out)
-        ops.gemm(a, w, b, L.EPI_PATCH_EMBED, ref, pos, cls)
-    elif epi == "resid":
+    st = torch.full((N // 32, rows, 2), float("nan"), device="cuda")  # [N/256][8][M][2]
+    if epi == "resid":
         r = _rand(M, N, seed=206)
         ops.gemm_ln(a, w, b, L.EPI_BIAS_RESID_F32, out, r, xb_out=xb, stats_out=st)
         ref = torch.empty_like(out)
@@ -106,9 +123,22 @@ def test_gemm_ln_producer(M, K, epi):
     assert torch.equal(out, ref)  # the fp32 output itself is unchanged
     assert torch.equal(xb[:rows], ref.to(BF16))
     assert float((xb[rows:].float() - 5.0).abs().max()) == 0.0  # rows beyond M untouched
-    chunks = ref.view(rows, N // 32, 32).double()
-    assert max_abs(st[..., 0].t().double(), chunks.sum(-1)) < 1e-4
-    assert rel_l2(st[..., 1].t().double(), (chunks * chunks).sum(-1)) < 1e-6
+    want = _ln_slots(ref, ops)
+    used = ~torch.isnan(want)
+    assert torch.equal(torch.isnan(st), ~used)  # exactly the documented slots are written
+    assert max_abs(st[used[..., 0]][:, 0].double(), want[used[..., 0]][:, 0]) < 2e-4
+    assert rel_l2(st[used[..., 1]][:, 1].double(), want[used[..., 1]][:, 1]) < 1e-6
+
+
+def test_gemm_ln_patch_embed_is_an_error():
+    L, ops = _mods()
+    M = 8 * 196
+    a, w, b = _rand(M, 768, seed=1, dtype=BF16), _rand(768, 768, seed=2, dtype=BF16), _rand(768, seed=3)
+    out = torch.empty(8 * 197, 768, device="cuda")
+    pos, cls = _rand(197, 768, seed=204), _rand(768, seed=205)
+    with pytest.raises(RuntimeError, match="fp32 TMA epilogue"):
+        ops.gemm_ln(a, w, b, L.EPI_PATCH_EMBED, out, pos, cls, xb_out=torch.empty(8 * 197, 768, device="cuda", dtype=BF16),
+                    stats_out=torch.empty(24, 8 * 197, 2, device="cuda"))
 
 
 @pytest.mark.parametrize("M,N,epi", [(6304, 3072, "gelu"), (1576, 2304, "qkv"), (1100, 768, "bf16")])
@@ -122,8 +152,7 @@ def test_gemm_ln_consumer(M, N, epi):
     w, b = _rand(N, K, seed=213, scale=K ** -0.5), _rand(N, seed=214)
     gamma, beta = 1.0 + 0.2 * _rand(K, seed=215), 0.1 * _rand(K, seed=216)
     wf, bf, cs = fold_layernorm(w, b, gamma, beta)
-    ch = x.view(M, K // 32, 32)
-    st = torch.stack([ch.sum(-1), (ch * ch).sum(-1)], -1).transpose(0, 1).contiguous()  # [K/32][M][2]
+    st = _ln_slots(x, ops).float().contiguous()  # [K/256][8][M][2]; unused slots hold NaN and must not be read
     ref = F.layer_norm(x, (K,), gamma, beta, 1e-6) @ w.t() + b
     xb = x.to(BF16)
     if epi == "qkv":

@@ -1,6 +1,7 @@
 """Per-class timing of the ViT linear layers through the C-ABI GEMM: each class is launched `reps` times back to back
 (GPU-bound: one launch is 10-40 us of device time against ~5 us of host time) between two CUDA events.
-usage: python tools/gemm_bench.py [batch] [reps]"""
+usage: python tools/gemm_bench.py [batch] [reps]
+MDE_BENCH_LN=1 times the LayerNorm-fused forms (mde_gemm_ln_bf16: proj/fc2 as producers, qkv/fc1 as consumers) next to the plain ones."""
 import os
 import sys
 
@@ -48,6 +49,23 @@ def main():
         us = e0.elapsed_time(e1) * 1e3 / reps
         total += us
         print(f"{name:5s} M={M} N={N} K={K}: {us:7.2f} us  {2.0 * M * N * K / us / 1e6:7.1f} TFLOP/s")
+        if os.environ.get("MDE_BENCH_LN") == "1":
+            st = torch.zeros(24, M, 2, device=dev, dtype=f32)
+            if epi == L.EPI_BIAS_RESID_F32:
+                kw = dict(xb_out=torch.empty(M, N, device=dev, dtype=bf), stats_out=st)
+            else:
+                st[..., 1] = 1.0
+                kw = dict(stats_in=st, colsum=rnd(N, dt=f32))
+            for _ in range(5):
+                ops.gemm_ln(a, w, bias, epi, *args, **kw)
+            torch.cuda.synchronize()
+            e0.record()
+            for _ in range(reps):
+                ops.gemm_ln(a, w, bias, epi, *args, **kw)
+            e1.record()
+            torch.cuda.synchronize()
+            us2 = e0.elapsed_time(e1) * 1e3 / reps
+            print(f"      LayerNorm-fused ({'producer' if 'xb_out' in kw else 'consumer'}): {us2:7.2f} us  ({us2 - us:+.2f})")
         if os.environ.get("MDE_GEMM_PROF") == "1":  # in-kernel clock64 counters of ONE launch (mde_debug_gemm_prof)
             prof = torch.zeros(148, 8, device=dev, dtype=torch.int64)
             L.call("mde_debug_gemm_prof", prof.data_ptr())
