@@ -309,47 +309,71 @@ __global__ void __launch_bounds__(256) patchify224_kernel(const float* __restric
   }
 }
 
-// ------------------------------------------------------------------ LayerNorm (tv:112,117) fp32 -> bf16, one warp per row
-template <int DIM>
-__global__ void __launch_bounds__(256) layernorm_kernel(const float* __restrict__ x, int rows, const float* __restrict__ gamma,
+// ------------------------------------------------------------------ LayerNorm (tv:112,117) fp32 -> bf16, one warp per R rows
+// R rows per warp with all R*24 loads of a lane in flight before the first reduction: at B = 32 (6304 rows) one row per warp
+// needs 788 blocks for 592 resident slots (4 blocks/SM), i.e. a second, one-third-full wave; R = 2 fits one wave.
+template <int DIM, int R>
+__global__ void __launch_bounds__(256, R == 1 ? 4 : 3) layernorm_kernel(const float* __restrict__ x, int rows, const float* __restrict__ gamma,
                                                         const float* __restrict__ beta, float eps, bf16* __restrict__ out) {
   pdl_launch_dependents();
   pdl_grid_wait();
   constexpr int PER = DIM / 256;  // 8-element groups per lane
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int row = blockIdx.x * 8 + warp;
-  if (row >= rows) return;
-  const float4* xr = reinterpret_cast<const float4*>(x + (size_t)row * DIM);
-  float v[PER * 8];
-  float s = 0.0f;
+  const int row0 = (blockIdx.x * 8 + warp) * R;
+  if (row0 >= rows) return;
+  float v[R][PER * 8];
+  float s[R];
 #pragma unroll
-  for (int j = 0; j < PER; ++j) {
-    const float4 a = __ldg(xr + (j * 32 + lane) * 2), b = __ldg(xr + (j * 32 + lane) * 2 + 1);
-    v[8 * j + 0] = a.x; v[8 * j + 1] = a.y; v[8 * j + 2] = a.z; v[8 * j + 3] = a.w;
-    v[8 * j + 4] = b.x; v[8 * j + 5] = b.y; v[8 * j + 6] = b.z; v[8 * j + 7] = b.w;
+  for (int r = 0; r < R; ++r) {
+    const int row = min(row0 + r, rows - 1);  // a clamped duplicate row is computed and not stored
+    const float4* xr = reinterpret_cast<const float4*>(x + (size_t)row * DIM);
 #pragma unroll
-    for (int k = 0; k < 8; ++k) s += v[8 * j + k];
+    for (int j = 0; j < PER; ++j) {
+      const float4 a = __ldg(xr + (j * 32 + lane) * 2), b = __ldg(xr + (j * 32 + lane) * 2 + 1);
+      v[r][8 * j + 0] = a.x; v[r][8 * j + 1] = a.y; v[r][8 * j + 2] = a.z; v[r][8 * j + 3] = a.w;
+      v[r][8 * j + 4] = b.x; v[r][8 * j + 5] = b.y; v[r][8 * j + 6] = b.z; v[r][8 * j + 7] = b.w;
+    }
   }
-  const float mean = warp_sum(s) * (1.0f / DIM);
-  float q = 0.0f;
 #pragma unroll
-  for (int k = 0; k < PER * 8; ++k) {
-    const float d = v[k] - mean;
-    q = fmaf(d, d, q);
+  for (int r = 0; r < R; ++r) {
+    s[r] = 0.0f;
+#pragma unroll
+    for (int j = 0; j < PER; ++j)
+#pragma unroll
+      for (int k = 0; k < 8; ++k) s[r] += v[r][8 * j + k];
   }
-  const float rstd = 1.0f / sqrtf(warp_sum(q) * (1.0f / DIM) + eps);
+  float mean[R], rstd[R];
+#pragma unroll
+  for (int r = 0; r < R; ++r) mean[r] = warp_sum(s[r]) * (1.0f / DIM);
+#pragma unroll
+  for (int r = 0; r < R; ++r) {
+    float q = 0.0f;
+#pragma unroll
+    for (int k = 0; k < PER * 8; ++k) {
+      const float d = v[r][k] - mean[r];
+      q = fmaf(d, d, q);
+    }
+    s[r] = q;
+  }
+#pragma unroll
+  for (int r = 0; r < R; ++r) rstd[r] = 1.0f / sqrtf(warp_sum(s[r]) * (1.0f / DIM) + eps);
   const float4* g4 = reinterpret_cast<const float4*>(gamma);
   const float4* b4 = reinterpret_cast<const float4*>(beta);
-  uint4* o = reinterpret_cast<uint4*>(out + (size_t)row * DIM);
 #pragma unroll
   for (int j = 0; j < PER; ++j) {
     const int g = (j * 32 + lane) * 2;
     const float4 ga = __ldg(g4 + g), gb = __ldg(g4 + g + 1), ba = __ldg(b4 + g), bb = __ldg(b4 + g + 1);
-    const float y0 = (v[8 * j + 0] - mean) * rstd * ga.x + ba.x, y1 = (v[8 * j + 1] - mean) * rstd * ga.y + ba.y;
-    const float y2 = (v[8 * j + 2] - mean) * rstd * ga.z + ba.z, y3 = (v[8 * j + 3] - mean) * rstd * ga.w + ba.w;
-    const float y4 = (v[8 * j + 4] - mean) * rstd * gb.x + bb.x, y5 = (v[8 * j + 5] - mean) * rstd * gb.y + bb.y;
-    const float y6 = (v[8 * j + 6] - mean) * rstd * gb.z + bb.z, y7 = (v[8 * j + 7] - mean) * rstd * gb.w + bb.w;
-    o[j * 32 + lane] = make_uint4(pack_bf16x2(y0, y1), pack_bf16x2(y2, y3), pack_bf16x2(y4, y5), pack_bf16x2(y6, y7));
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      if (row0 + r >= rows) break;
+      const float m = mean[r], t = rstd[r];
+      const float y0 = (v[r][8 * j + 0] - m) * t * ga.x + ba.x, y1 = (v[r][8 * j + 1] - m) * t * ga.y + ba.y;
+      const float y2 = (v[r][8 * j + 2] - m) * t * ga.z + ba.z, y3 = (v[r][8 * j + 3] - m) * t * ga.w + ba.w;
+      const float y4 = (v[r][8 * j + 4] - m) * t * gb.x + bb.x, y5 = (v[r][8 * j + 5] - m) * t * gb.y + bb.y;
+      const float y6 = (v[r][8 * j + 6] - m) * t * gb.z + bb.z, y7 = (v[r][8 * j + 7] - m) * t * gb.w + bb.w;
+      reinterpret_cast<uint4*>(out + (size_t)(row0 + r) * DIM)[j * 32 + lane] =
+          make_uint4(pack_bf16x2(y0, y1), pack_bf16x2(y2, y3), pack_bf16x2(y4, y5), pack_bf16x2(y6, y7));
+    }
   }
 }
 
@@ -773,7 +797,12 @@ extern "C" int mde_layernorm_bf16(const float* x, int rows, int dim, const float
     set_error("mde_layernorm_bf16: dim=%d not built (768 only)", dim);
     return MDE_ERR_UNSUPPORTED;
   }
-  launch_k(layernorm_kernel<768>, dim3(ceil_div(rows, 8)), dim3(256), 0, stream, x, rows, gamma, beta, eps, reinterpret_cast<bf16*>(out));
+  // one resident wave: 4 blocks of 8 warps per SM (register-limited); rows per warp chosen so that the grid fits it
+  static const int r_env = getenv("MDE_LN_ROWS") ? atoi(getenv("MDE_LN_ROWS")) : 0;
+  const int slots = 4 * sm_count();
+  const int R = r_env > 0 ? r_env : (ceil_div(rows, 8) <= slots ? 1 : 2);
+  if (R == 1) launch_k(layernorm_kernel<768, 1>, dim3(ceil_div(rows, 8)), dim3(256), 0, stream, x, rows, gamma, beta, eps, reinterpret_cast<bf16*>(out));
+  else launch_k(layernorm_kernel<768, 2>, dim3(ceil_div(rows, 16)), dim3(256), 0, stream, x, rows, gamma, beta, eps, reinterpret_cast<bf16*>(out));
   MDE_CHECK_LAUNCH();
   return MDE_OK;
 }
