@@ -159,6 +159,9 @@ def main():
     rank, world, local = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    # host side of one-process-per-GPU: pinned staging buffers on the GPU's own NUMA node (MDE_NUMA_BIND=0 leaves placement to the OS)
+    from monodepth_estimation_b200.sharding import bind_host_to_gpu
+    numa = bind_host_to_gpu(local) if os.environ.get("MDE_NUMA_BIND", "1") != "0" else None
     dist = None
     if world > 1:
         import torch.distributed as dist
@@ -223,7 +226,8 @@ def main():
             "config": {"workload": f"{a.model} model forward, batch {B}/GPU, 3x{S}x{S} fp32 in -> {4 if a.model == 'standard' else 10} fp32 maps out "
                                    f"(BASELINE.json configs[{1 if a.model == 'standard' else 2}])",
                        "global_batch": B * world, "image_size": S, "parallelism": f"image-sharded x{world}, no collective",
-                       "l2": "inputs (403 MB/batch) and outputs (>=537 MB/batch) exceed the 126 MB L2", "weights": "synthetic random-init, seed 0"},
+                       "l2": "inputs (403 MB/batch) and outputs (>=537 MB/batch) exceed the 126 MB L2", "weights": "synthetic random-init, seed 0",
+                       "host_numa_node": None if numa is None else numa[0]},
             "clocks": clocks, "gpu_launches": launches,
             "tensor_frac_of_step": round(value / world * GFLOP_PER_IMAGE[a.model] / 1e3 / pk["bf16_tflops_sustained"], 4)}
 
@@ -271,6 +275,8 @@ def main():
 
         # ---- CPU baseline (rank 0, N=1 only): the oracle port of the reference on the host cores, bounded sample
         if rank == 0 and world == 1:
+            if numa is not None:
+                os.sched_setaffinity(0, numa[1])  # the CPU leg uses every host core again
             v, ms, threads = cpu_forward_rate(a.model, S, 2, 3, 1)
             line["cpu_baseline"] = {"value": round(v, 3), "unit": "images/s", "cores": threads, "kind": "port",
                                     "sample": f"{a.model} forward, batch 2 x 3x{S}x{S} fp32, 3 timed steps after 1 warm-up"}

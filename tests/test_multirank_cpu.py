@@ -54,3 +54,18 @@ def test_world2_gloo_rate_is_total_images_over_slowest_rank():
     assert [g[:2] for g in got] == [(0, 17), (17, 33)]
     full = torch.arange(33 * 4, dtype=torch.float32).view(33, 4)
     assert abs(sum(g[2] for g in got) - float(full.sum())) < 1e-3  # the two slices cover the batch exactly once
+
+
+def test_numa_binding_helpers():
+    """Host side of one-process-per-GPU: cpulist parsing, and no CUDA device / no sysfs entry means 'leave placement alone'."""
+    import os
+
+    from monodepth_estimation_b200 import sharding as S
+
+    assert S._parse_cpulist("0-3,8,10-11\n") == {0, 1, 2, 3, 8, 10, 11}
+    assert S._parse_cpulist("") == set()
+    before = os.sched_getaffinity(0)
+    assert S.gpu_numa_cpus(0, sysfs="/nonexistent") is None
+    if not __import__("torch").cuda.is_available():
+        assert S.bind_host_to_gpu(0) is None
+        assert os.sched_getaffinity(0) == before
