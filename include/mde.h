@@ -184,7 +184,8 @@ int mde_upsample2x_concat_nhwc(const mde_bf16* a, int B, int h, int w, int ca, c
 
 /* ---- enhanced_model.py:95-98: rgb image f32 [B,3,H,W] -> bilinear (align_corners=False) to the gh x gw
  * grid, written as channels [out_coff, out_coff+3) of a padded NHWC bf16 tensor; channels up to
- * out_coff+cfill are zero-filled (K padding of the 259-channel refinement conv). */
+ * out_coff+cfill are zero-filled (K padding of the 259-channel refinement conv).  cfill, out_coff and out_cstride
+ * are multiples of 8 channels (16-byte stores). */
 int mde_rgb_to_grid_nhwc(const float* x, int B, int H, int W, int gh, int gw, mde_bf16* out_padded, int out_cstride,
                          int out_coff, int cfill, mde_stream_t stream);
 

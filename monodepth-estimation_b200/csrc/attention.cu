@@ -639,7 +639,7 @@ __global__ void __launch_bounds__(320, 1) vit_attn_ps_kernel(const __grid_consta
 }
 
 // ------------------------------------------------------------------ spatial self-attention (enhanced_model.py:20-39)
-constexpr int kSaQ = 8;        // queries per block
+constexpr int kSaQ = 16;       // queries per block (two per warp): every block streams all of V once, so fewer, fatter blocks halve the L2 traffic
 constexpr int kSaMaxG = 224;   // grid positions supported (14x15 = 210, 14x14 = 196)
 constexpr int kSaLd = 384;     // row pitch of the fp32 q|k|v projection buffer
 
@@ -655,14 +655,13 @@ __global__ void __launch_bounds__(256) spatial_attn_kernel(const bf16* __restric
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const float* base = qkv + (size_t)b * G * kSaLd;
   for (int i = tid; i < G * 32; i += 256) sK[i >> 5][i & 31] = base[(size_t)(i >> 5) * kSaLd + 32 + (i & 31)];
-  {
-    const int i = tid >> 5, d = tid & 31;
+  for (int t = tid; t < kSaQ * 32; t += 256) {
+    const int i = t >> 5, d = t & 31;
     sQ[i][d] = (q0 + i < G) ? base[(size_t)(q0 + i) * kSaLd + d] : 0.0f;
   }
   __syncthreads();
-  // energy[i][j] = q_i . k_j (no scaling, enhanced_model.py:28); warp i owns query i
-  {
-    const int i = warp;
+  // energy[i][j] = q_i . k_j (no scaling, enhanced_model.py:28); warp w owns queries w and w + 8
+  for (int i = warp; i < kSaQ; i += 8) {
     float mx = -INFINITY;
     for (int j = lane; j < G; j += 32) {
       float e = 0.0f;
@@ -690,14 +689,15 @@ __global__ void __launch_bounds__(256) spatial_attn_kernel(const bf16* __restric
 #pragma unroll
   for (int i = 0; i < kSaQ; ++i) acc[i] = 0.0f;
   const float* vcol = base + 64 + tid;
+#pragma unroll 4
   for (int j = 0; j < G; ++j) {
-    const float v = vcol[(size_t)j * kSaLd];
+    const float v = __ldg(vcol + (size_t)j * kSaLd);
 #pragma unroll
     for (int i = 0; i < kSaQ; ++i) acc[i] = fmaf(sA[i][j], v, acc[i]);
   }
   const float gamma = *gamma_p;
   const int H2 = gh + 2, W2 = gw + 2;
-#pragma unroll 1
+#pragma unroll  // fully unrolled: acc[] stays in registers (a rolled loop indexes it dynamically -> local memory)
   for (int i = 0; i < kSaQ; ++i) {
     const int g = q0 + i;
     if (g >= G) break;

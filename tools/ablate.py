@@ -105,6 +105,8 @@ cases = [
     ("input_stage", {"input_stage": skip}),
     ("resize_maps (output)", {"resize_maps": skip}),
 ]
+if KIND == "enhanced":
+    cases += [("spatial_attention x2", {"spatial_attention": skip}), ("enh_fuse", {"enh_fuse": skip}), ("rgb_to_grid", {"rgb_to_grid": skip})]
 
 
 def gemm_resid(kdim):
