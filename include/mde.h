@@ -290,6 +290,37 @@ int mde_temporal_mean(const float* const* maps, const double* weights, int n, lo
 int mde_bilateral_depth(const float* depth, int H, int W, const uint8_t* guide, float sigma_color, const float* space_w,
                         const float* joint_lut, float* scratch, float* out, mde_stream_t stream);
 
+/* ==== backward of the ViT encoder block (train/mars_adapter.py:131-140 calls loss.backward() through
+ * torchvision's EncoderBlock, tv:110-120).  GEMM-shaped gradients reuse mde_gemm_bf16 on transposed operands:
+ *   dX = dY W    : A = dY [M][N],     W operand = W^T [K][N]
+ *   dW = dY^T X  : A = dY^T [N][Mp],  W operand = X^T [K][Mp],  Mp = M rounded up to a multiple of 64 (zero filled)
+ * Everything below is deterministic (fixed-order reductions, no atomics). ==== */
+
+/* src [R][lds] (f32 when src_is_f32, else bf16) -> dst_t bf16 [C][ldt]: dst_t[c][r] = src[r][c], zero for R <= r < ldt (the K
+ * padding of a dW GEMM); and/or dst_rm bf16 [R][ldr] = cast(src).  Either destination may be NULL. */
+int mde_transpose_bf16(const void* src, int src_is_f32, int R, int C, int lds, mde_bf16* dst_t, int ldt, mde_bf16* dst_rm, int ldr,
+                       mde_stream_t stream);
+
+/* bias gradient of a Linear (tv:113,118): out[c] (+)= sum_r src[r][c]. */
+int mde_colsum_bf16(const mde_bf16* src, int R, int C, int lds, float* out, int accumulate, mde_stream_t stream);
+
+/* nn.GELU (exact erf, tv:118) on a bf16 buffer, and its backward du = dy * (Phi(u) + u phi(u)).  count % 8 == 0. */
+int mde_gelu_bf16(const mde_bf16* u, long long count, mde_bf16* y, mde_stream_t stream);
+int mde_gelu_bwd_bf16(const mde_bf16* u, const mde_bf16* dy, long long count, mde_bf16* du, mde_stream_t stream);
+
+/* LayerNorm backward (tv:112,117; dim = 768): x f32 [rows][dim] (the layer's input), dy bf16 [rows][dim].
+ * dx[r] = rstd (g - mean(g) - xhat mean(g xhat)) with g = dy gamma, plus dres[r] when dres != NULL (the gradient that reaches x
+ * through the residual connection); dgamma / dbeta (+)= column sums of dy xhat / dy.  scratch: mde_layernorm_bwd_scratch_floats(rows). */
+long long mde_layernorm_bwd_scratch_floats(int rows);
+int mde_layernorm_bwd(const float* x, const mde_bf16* dy, const float* gamma, int rows, int dim, float eps, const float* dres, float* dx,
+                      float* dgamma, float* dbeta, int accumulate, float* scratch, mde_stream_t stream);
+
+/* Backward of mde_vit_attention (tv:113): q (pre-scaled by 1/8), k token-major bf16 [B*197][768], vt bf16 [B*12][64][208] as the
+ * forward wrote them, dout bf16 [B*197][768] = gradient of the attention output.  dqkv bf16 [B*197][2304] = (dq | dk | dv) per
+ * token with respect to in_proj's output (dq includes the 1/8), i.e. the dY of the in_proj gradient GEMMs. */
+int mde_vit_attention_bwd(const mde_bf16* q, const mde_bf16* k, const mde_bf16* vt, const mde_bf16* dout, int B, mde_bf16* dqkv,
+                          mde_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -65,8 +65,15 @@ SIGNATURES = {
     "mde_disp_to_depth": [_p, _ll, _d, _d, _p, _p],
     "mde_temporal_mean": [C.POINTER(_p), C.POINTER(_d), _i, _ll, _p, _p],
     "mde_bilateral_depth": [_p, _i, _i, _p, _f, _p, _p, _p, _p, _p],
+    "mde_transpose_bf16": [_p, _i, _i, _i, _i, _p, _i, _p, _i, _p],
+    "mde_colsum_bf16": [_p, _i, _i, _i, _p, _i, _p],
+    "mde_gelu_bf16": [_p, _ll, _p, _p],
+    "mde_gelu_bwd_bf16": [_p, _p, _ll, _p, _p],
+    "mde_layernorm_bwd_scratch_floats": [_i],
+    "mde_layernorm_bwd": [_p, _p, _p, _i, _i, _f, _p, _p, _p, _p, _i, _p, _p],
+    "mde_vit_attention_bwd": [_p, _p, _p, _p, _i, _p, _p],
 }
-_RESTYPES = {"mde_last_error": C.c_char_p, "mde_point_cloud_scratch_bytes": C.c_longlong}
+_RESTYPES = {"mde_last_error": C.c_char_p, "mde_point_cloud_scratch_bytes": C.c_longlong, "mde_layernorm_bwd_scratch_floats": C.c_longlong}
 
 _lock = threading.Lock()
 _lib = None

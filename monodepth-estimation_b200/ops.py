@@ -245,3 +245,53 @@ def disp_to_depth(disp, min_depth, max_depth, out=None):
     out = out if out is not None else torch.empty_like(disp)
     L.call("mde_disp_to_depth", _ptr(disp, F32), disp.numel(), float(min_depth), float(max_depth), _ptr(out, F32), _stream())
     return out
+
+
+# ---------------------------------------------------------------------- backward of the ViT encoder block (csrc/backward.cu)
+def transpose_bf16(src, ldt=None, want_t=True, want_rm=False):
+    """src [R,C] (f32 or bf16, contiguous) -> (dst_t bf16 [C, ldt] zero-padded beyond R | None, dst_rm bf16 [R,C] | None)."""
+    R, Cc = src.shape
+    if src.dtype not in (F32, BF16):
+        raise ValueError("transpose_bf16 takes float32 or bfloat16")
+    ldt = ldt if ldt is not None else (R + 63) // 64 * 64
+    dst_t = torch.empty(Cc, ldt, device=src.device, dtype=BF16) if want_t else None
+    dst_rm = torch.empty(R, Cc, device=src.device, dtype=BF16) if want_rm else None
+    L.call("mde_transpose_bf16", _ptr(src), int(src.dtype == F32), R, Cc, src.stride(0), _ptr(dst_t), ldt, _ptr(dst_rm), Cc, _stream())
+    return dst_t, dst_rm
+
+
+def colsum_bf16(src, out=None, accumulate=False):
+    R, Cc = src.shape
+    out = out if out is not None else torch.empty(Cc, device=src.device, dtype=F32)
+    L.call("mde_colsum_bf16", _ptr(src, BF16), R, Cc, src.stride(0), _ptr(out, F32), int(accumulate), _stream())
+    return out
+
+
+def gelu_bf16(u, out=None):
+    out = out if out is not None else torch.empty_like(u)
+    L.call("mde_gelu_bf16", _ptr(u, BF16), u.numel(), _ptr(out, BF16), _stream())
+    return out
+
+
+def gelu_bwd_bf16(u, dy, out=None):
+    out = out if out is not None else torch.empty_like(u)
+    L.call("mde_gelu_bwd_bf16", _ptr(u, BF16), _ptr(dy, BF16), u.numel(), _ptr(out, BF16), _stream())
+    return out
+
+
+def layernorm_bwd(x, dy, gamma, eps, dres=None, dgamma=None, dbeta=None, accumulate=False):
+    """-> (dx f32 [rows,dim] (+ dres), dgamma f32 [dim], dbeta f32 [dim])"""
+    rows, dim = x.shape
+    dx = torch.empty(rows, dim, device=x.device, dtype=F32)
+    dgamma = dgamma if dgamma is not None else torch.empty(dim, device=x.device, dtype=F32)
+    dbeta = dbeta if dbeta is not None else torch.empty(dim, device=x.device, dtype=F32)
+    scratch = torch.empty(int(L.load().mde_layernorm_bwd_scratch_floats(rows)), device=x.device, dtype=F32)
+    L.call("mde_layernorm_bwd", _ptr(x, F32), _ptr(dy, BF16), _ptr(gamma, F32), rows, dim, float(eps), _ptr(dres, F32) if dres is not None else _ptr(None),
+           _ptr(dx, F32), _ptr(dgamma, F32), _ptr(dbeta, F32), int(accumulate), _ptr(scratch, F32), _stream())
+    return dx, dgamma, dbeta
+
+
+def vit_attention_bwd(q, k, vt, dout, B, out=None):
+    out = out if out is not None else torch.empty(B * L.VIT_SEQ, 3 * L.VIT_DIM, device=q.device, dtype=BF16)
+    L.call("mde_vit_attention_bwd", _ptr(q, BF16), _ptr(k, BF16), _ptr(vt, BF16), _ptr(dout, BF16), B, _ptr(out, BF16), _stream())
+    return out

@@ -1,0 +1,135 @@
+"""GPU: the backward kernels of the ViT encoder block (csrc/backward.cu + training.py) against torch autograd in
+fp32 on the same seeded inputs.  Operands are bf16 with fp32 accumulation, so gradients carry bf16-level error: every test
+states its tolerance."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+from helpers import max_abs, rel_l2
+
+pytestmark = pytest.mark.gpu
+
+BF16 = torch.bfloat16
+
+
+def _mods():
+    from monodepth_estimation_b200 import _lib as L
+    from monodepth_estimation_b200 import ops
+
+    return L, ops
+
+
+def _rand(*shape, seed=0, scale=1.0, dtype=torch.float32):
+    g = torch.Generator(device="cpu").manual_seed(seed)
+    return (torch.randn(*shape, generator=g) * scale).to(dtype).cuda()
+
+
+@pytest.mark.parametrize("R,C,f32", [(1576, 768, True), (197, 2304, False), (70, 40, True), (1576, 3072, False)])
+def test_transpose_cast_pad(R, C, f32):
+    L, ops = _mods()
+    x = _rand(R, C, seed=1, dtype=torch.float32 if f32 else BF16)
+    ldt = (R + 63) // 64 * 64
+    t, rm = ops.transpose_bf16(x, ldt=ldt, want_rm=True)
+    assert torch.equal(rm, x.to(BF16))
+    assert torch.equal(t[:, :R], x.to(BF16).t())
+    assert float(t[:, R:].float().abs().sum()) == 0.0  # the K padding of a dW GEMM must be exact zeros
+
+
+def test_colsum_matches_sum_and_accumulates():
+    L, ops = _mods()
+    x = _rand(1576, 2304, seed=2, dtype=BF16)
+    ref = x.double().sum(0)
+    out = ops.colsum_bf16(x)
+    assert max_abs(out, ref) < 2e-3
+    again = ops.colsum_bf16(x)
+    assert torch.equal(out, again)  # fixed summation order
+    ops.colsum_bf16(x, out=out, accumulate=True)
+    assert max_abs(out, 2 * ref) < 4e-3
+
+
+def test_gelu_forward_and_backward():
+    L, ops = _mods()
+    u = _rand(1576, 3072, seed=3, scale=2.0, dtype=BF16)
+    dy = _rand(1576, 3072, seed=4, dtype=BF16)
+    uf = u.float().requires_grad_(True)
+    y = F.gelu(uf)
+    y.backward(dy.float())
+    assert rel_l2(ops.gelu_bf16(u).float(), y.detach()) < 3e-3
+    assert rel_l2(ops.gelu_bwd_bf16(u, dy).float(), uf.grad) < 3e-3
+
+
+@pytest.mark.parametrize("rows,resid", [(1576, True), (197, False), (65, True)])
+def test_layernorm_backward(rows, resid):
+    L, ops = _mods()
+    x = (_rand(rows, 768, seed=5) * (0.5 + torch.rand(rows, 1, device="cuda")) + 0.2 * _rand(rows, 1, seed=6)).contiguous()
+    gamma, beta = 1.0 + 0.2 * _rand(768, seed=7), 0.1 * _rand(768, seed=8)
+    dy = _rand(rows, 768, seed=9, dtype=BF16)
+    dres = _rand(rows, 768, seed=10) if resid else None
+    xr, gr, br = x.clone().requires_grad_(True), gamma.clone().requires_grad_(True), beta.clone().requires_grad_(True)
+    F.layer_norm(xr, (768,), gr, br, 1e-6).backward(dy.float())
+    dx, dg, db = ops.layernorm_bwd(x, dy, gamma, 1e-6, dres=dres)
+    want = xr.grad + (dres if resid else 0.0)
+    assert rel_l2(dx, want) < 1e-5, rel_l2(dx, want)
+    assert rel_l2(dg, gr.grad) < 1e-5 and rel_l2(db, br.grad) < 1e-5
+    dg2 = dg.clone()
+    ops.layernorm_bwd(x, dy, gamma, 1e-6, dgamma=dg2, dbeta=db.clone(), accumulate=True)
+    assert rel_l2(dg2, 2 * gr.grad) < 1e-5
+
+
+@pytest.mark.parametrize("B", [1, 3])
+def test_attention_backward(B):
+    """dq | dk | dv of softmax(q k^T / 8) v per (image, head), against autograd on the bf16-rounded operands."""
+    L, ops = _mods()
+    M = B * 197
+    h1 = _rand(M, 768, seed=11, dtype=BF16)
+    w, b = _rand(2304, 768, seed=12, scale=768 ** -0.5, dtype=BF16), _rand(2304, seed=13, scale=0.1)
+    q = torch.empty(M, 768, device="cuda", dtype=BF16)
+    k = torch.empty_like(q)
+    vt = torch.zeros(B * 12 * 64 * L.VT_PITCH, device="cuda", dtype=BF16)
+    ops.gemm(h1, w, b, L.EPI_QKV_SPLIT, q, k, vt)  # the layouts exactly as the forward writes them
+    dout = _rand(M, 768, seed=14, dtype=BF16)
+    dqkv = ops.vit_attention_bwd(q, k, vt, dout, B)
+    # reference: unscaled q (= 8 * stored q), k, v as leaves
+    qf = (q.float() * 8.0).view(B, 197, 12, 64).permute(0, 2, 1, 3).clone().requires_grad_(True)
+    kf = k.float().view(B, 197, 12, 64).permute(0, 2, 1, 3).clone().requires_grad_(True)
+    vf = vt.view(B, 12, 64, L.VT_PITCH)[..., :197].float().transpose(-1, -2).clone().requires_grad_(True)
+    o = torch.softmax(qf @ kf.transpose(-1, -2) * 0.125, -1) @ vf
+    o.backward(dout.float().view(B, 197, 12, 64).permute(0, 2, 1, 3))
+    back = lambda t: t.permute(0, 2, 1, 3).reshape(M, 768)
+    got = dqkv.float()
+    assert rel_l2(got[:, :768], back(qf.grad)) < 6e-3, rel_l2(got[:, :768], back(qf.grad))
+    assert rel_l2(got[:, 768:1536], back(kf.grad)) < 6e-3
+    assert rel_l2(got[:, 1536:], back(vf.grad)) < 6e-3
+    assert torch.equal(dqkv, ops.vit_attention_bwd(q, k, vt, dout, B))  # deterministic
+
+
+@pytest.mark.parametrize("B", [2, 8])
+def test_vit_block_backward_matches_autograd(B):
+    """One torchvision EncoderBlock (tv:84-120): forward through the C-ABI kernels, backward through training.ViTBlockTrainer,
+    against torch autograd of the same block in fp32.  B = 8 is config 5's per-GPU batch (M = 1576: the CTA-pair GEMM)."""
+    from torchvision.models.vision_transformer import EncoderBlock
+
+    from monodepth_estimation_b200.training import ViTBlockTrainer
+
+    torch.manual_seed(21)
+    blk = EncoderBlock(12, 768, 3072, 0.0, 0.0).cuda().float()
+    with torch.no_grad():
+        for n, p_ in blk.named_parameters():
+            if n.startswith("ln_"):
+                p_.add_(0.1 * torch.randn_like(p_))
+            elif n.endswith("bias"):
+                p_.normal_(0, 0.05)
+    M = B * 197
+    x = _rand(M, 768, seed=22)
+    dout = _rand(M, 768, seed=23, scale=0.1)
+    xr = x.view(B, 197, 768).clone().requires_grad_(True)
+    y = blk(xr)
+    y.backward(dout.view(B, 197, 768))
+    tr = ViTBlockTrainer(dict(blk.named_parameters()))
+    out = tr.forward(x)
+    assert rel_l2(out, y.detach().reshape(M, 768)) < 4e-3
+    dx, grads = tr.backward(dout)
+    assert rel_l2(dx, xr.grad.reshape(M, 768)) < 1e-2, rel_l2(dx, xr.grad.reshape(M, 768))
+    for n, p_ in blk.named_parameters():
+        e = rel_l2(grads[n], p_.grad)
+        assert grads[n].shape == p_.grad.shape and e < 2e-2, (n, e)
