@@ -296,10 +296,11 @@ int mde_bilateral_depth(const float* depth, int H, int W, const uint8_t* guide, 
  *   dW = dY^T X  : A = dY^T [N][Mp],  W operand = X^T [K][Mp],  Mp = M rounded up to a multiple of 64 (zero filled)
  * Everything below is deterministic (fixed-order reductions, no atomics). ==== */
 
-/* src [R][lds] (f32 when src_is_f32, else bf16) -> dst_t bf16 [C][ldt]: dst_t[c][r] = src[r][c], zero for R <= r < ldt (the K
- * padding of a dW GEMM); and/or dst_rm bf16 [R][ldr] = cast(src).  Either destination may be NULL. */
-int mde_transpose_bf16(const void* src, int src_is_f32, int R, int C, int lds, mde_bf16* dst_t, int ldt, mde_bf16* dst_rm, int ldr,
-                       mde_stream_t stream);
+/* src [R][lds] (f32 when src_is_f32, else bf16) -> dst_t bf16 [C][ldt]: dst_t[c][r] = src[r][c], zero for R <= r < cols_t (the K
+ * padding of a dW GEMM; R <= cols_t <= ldt, columns beyond cols_t are left alone so that row blocks can be transposed side by
+ * side); and/or dst_rm bf16 [R][ldr] = cast(src).  Either destination may be NULL. */
+int mde_transpose_bf16(const void* src, int src_is_f32, int R, int C, int lds, mde_bf16* dst_t, int ldt, int cols_t, mde_bf16* dst_rm,
+                       int ldr, mde_stream_t stream);
 
 /* bias gradient of a Linear (tv:113,118): out[c] (+)= sum_r src[r][c]. */
 int mde_colsum_bf16(const mde_bf16* src, int R, int C, int lds, float* out, int accumulate, mde_stream_t stream);
@@ -314,6 +315,11 @@ int mde_gelu_bwd_bf16(const mde_bf16* u, const mde_bf16* dy, long long count, md
 long long mde_layernorm_bwd_scratch_floats(int rows);
 int mde_layernorm_bwd(const float* x, const mde_bf16* dy, const float* gamma, int rows, int dim, float eps, const float* dres, float* dx,
                       float* dgamma, float* dbeta, int accumulate, float* scratch, mde_stream_t stream);
+
+/* out[i] (+)= sum over b of src[b][i] (gradients of pos_embedding / class_token, tv:156,296: shared by the images of a batch), and
+ * y += a x (the gradient of a hooked block's output is the sum of what its two consumers send back, encoder.py:60-67). */
+int mde_batch_sum_f32(const float* src, int B, long long n, float* out, int accumulate, mde_stream_t stream);
+int mde_axpy_f32(float* y, const float* x, float a, long long n, mde_stream_t stream);
 
 /* Backward of mde_vit_attention (tv:113): q (pre-scaled by 1/8), k token-major bf16 [B*197][768], vt bf16 [B*12][64][208] as the
  * forward wrote them, dout bf16 [B*197][768] = gradient of the attention output.  dqkv bf16 [B*197][2304] = (dq | dk | dv) per

@@ -65,7 +65,9 @@ SIGNATURES = {
     "mde_disp_to_depth": [_p, _ll, _d, _d, _p, _p],
     "mde_temporal_mean": [C.POINTER(_p), C.POINTER(_d), _i, _ll, _p, _p],
     "mde_bilateral_depth": [_p, _i, _i, _p, _f, _p, _p, _p, _p, _p],
-    "mde_transpose_bf16": [_p, _i, _i, _i, _i, _p, _i, _p, _i, _p],
+    "mde_transpose_bf16": [_p, _i, _i, _i, _i, _p, _i, _i, _p, _i, _p],
+    "mde_batch_sum_f32": [_p, _i, _ll, _p, _i, _p],
+    "mde_axpy_f32": [_p, _p, _f, _ll, _p],
     "mde_colsum_bf16": [_p, _i, _i, _i, _p, _i, _p],
     "mde_gelu_bf16": [_p, _ll, _p, _p],
     "mde_gelu_bwd_bf16": [_p, _p, _ll, _p, _p],

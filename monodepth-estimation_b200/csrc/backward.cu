@@ -19,10 +19,10 @@ __device__ __forceinline__ float warp_sum(float v) {
 }
 
 // ------------------------------------------------------------------ transpose (+ cast, + zero-filled K padding)
-// src [R][lds] (float or bf16) -> dst_t bf16 [C][ldt] with dst_t[c][r] = src[r][c] for r < R and 0 for R <= r < ldt;
+// src [R][lds] (float or bf16) -> dst_t bf16 [C][ldt] with dst_t[c][r] = src[r][c] for r < R and 0 for R <= r < cols_t (<= ldt);
 // optionally also dst_rm bf16 [R][ldr] = cast(src).  32x32 tiles through shared memory, both sides coalesced.
 template <class TIn>
-__global__ void __launch_bounds__(256) transpose_pad_kernel(const TIn* __restrict__ src, int R, int C, int lds, bf16* __restrict__ dst_t, int ldt,
+__global__ void __launch_bounds__(256) transpose_pad_kernel(const TIn* __restrict__ src, int R, int C, int lds, bf16* __restrict__ dst_t, int ldt, int cols_t,
                                                             bf16* __restrict__ dst_rm, int ldr) {
   __shared__ float tile[32][33];
   const int c0 = blockIdx.x * 32, r0 = blockIdx.y * 32;
@@ -43,7 +43,7 @@ __global__ void __launch_bounds__(256) transpose_pad_kernel(const TIn* __restric
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
       const int c = c0 + ty + 8 * k, r = r0 + tx;
-      if (c < C && r < ldt) dst_t[(size_t)c * ldt + r] = __float2bfloat16_rn(tile[tx][ty + 8 * k]);
+      if (c < C && r < cols_t) dst_t[(size_t)c * ldt + r] = __float2bfloat16_rn(tile[tx][ty + 8 * k]);
     }
   }
 }
@@ -345,6 +345,18 @@ __global__ void __launch_bounds__(256) vit_attn_bwd_kernel(const bf16* __restric
   }
 }
 
+// out[i] (+)= sum_b src[b][i]  (pos_embedding / class_token gradients: the sum over the images of a batch), fixed order
+__global__ void __launch_bounds__(256) batch_sum_kernel(const float* __restrict__ src, int B, long long n, float* __restrict__ out, int accumulate) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    float t = 0.0f;
+    for (int b = 0; b < B; ++b) t += src[(size_t)b * n + i];
+    out[i] = accumulate ? out[i] + t : t;
+  }
+}
+__global__ void __launch_bounds__(256) axpy_kernel(float* __restrict__ y, const float* __restrict__ x, float a, long long n) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) y[i] = fmaf(a, x[i], y[i]);
+}
+
 static inline int grid_1d(long long items, int threads) {
   long long g = (items + threads - 1) / threads;
   const long long cap = (long long)sm_count() * 16;
@@ -355,19 +367,18 @@ static inline int grid_1d(long long items, int threads) {
 
 using namespace mde;
 
-extern "C" int mde_transpose_bf16(const void* src, int src_is_f32, int R, int C, int lds, mde_bf16* dst_t, int ldt, mde_bf16* dst_rm, int ldr,
+extern "C" int mde_transpose_bf16(const void* src, int src_is_f32, int R, int C, int lds, mde_bf16* dst_t, int ldt, int cols_t, mde_bf16* dst_rm, int ldr,
                                   mde_stream_t stream) {
   MDE_CHECK_ARG(src && R > 0 && C > 0 && lds >= C, "mde_transpose_bf16: bad source geometry");
   MDE_CHECK_ARG(dst_t || dst_rm, "mde_transpose_bf16: no destination");
-  MDE_CHECK_ARG(!dst_t || ldt >= R, "mde_transpose_bf16: ldt=%d < R=%d", ldt, R);
+  MDE_CHECK_ARG(!dst_t || (cols_t >= R && ldt >= cols_t), "mde_transpose_bf16: need R <= cols_t <= ldt (R=%d cols_t=%d ldt=%d)", R, cols_t, ldt);
   MDE_CHECK_ARG(!dst_rm || ldr >= C, "mde_transpose_bf16: ldr=%d < C=%d", ldr, C);
-  const int cols_t = dst_t ? ldt : R;  // tiles must also cover the zero-filled tail R..ldt of the transposed rows
-  const dim3 grid(ceil_div(C, 32), ceil_div(cols_t, 32));
+  const dim3 grid(ceil_div(C, 32), ceil_div(dst_t ? cols_t : R, 32));  // tiles also cover the zero-filled tail R..cols_t of the transposed rows
   if (src_is_f32)
-    transpose_pad_kernel<float><<<grid, 256, 0, stream>>>(static_cast<const float*>(src), R, C, lds, reinterpret_cast<bf16*>(dst_t), ldt,
+    transpose_pad_kernel<float><<<grid, 256, 0, stream>>>(static_cast<const float*>(src), R, C, lds, reinterpret_cast<bf16*>(dst_t), ldt, cols_t,
                                                           reinterpret_cast<bf16*>(dst_rm), ldr);
   else
-    transpose_pad_kernel<bf16><<<grid, 256, 0, stream>>>(static_cast<const bf16*>(src), R, C, lds, reinterpret_cast<bf16*>(dst_t), ldt,
+    transpose_pad_kernel<bf16><<<grid, 256, 0, stream>>>(static_cast<const bf16*>(src), R, C, lds, reinterpret_cast<bf16*>(dst_t), ldt, cols_t,
                                                          reinterpret_cast<bf16*>(dst_rm), ldr);
   MDE_CHECK_LAUNCH();
   return MDE_OK;
@@ -425,6 +436,20 @@ extern "C" int mde_vit_attention_bwd(const mde_bf16* q, const mde_bf16* k, const
   vit_attn_bwd_kernel<<<B * MDE_VIT_HEADS, 256, kAbSmem, stream>>>(reinterpret_cast<const bf16*>(q), reinterpret_cast<const bf16*>(k),
                                                                    reinterpret_cast<const bf16*>(vt), reinterpret_cast<const bf16*>(dout),
                                                                    reinterpret_cast<bf16*>(dqkv));
+  MDE_CHECK_LAUNCH();
+  return MDE_OK;
+}
+
+extern "C" int mde_batch_sum_f32(const float* src, int B, long long n, float* out, int accumulate, mde_stream_t stream) {
+  MDE_CHECK_ARG(src && out && B > 0 && n > 0, "mde_batch_sum_f32: bad arguments");
+  batch_sum_kernel<<<grid_1d(n, 256), 256, 0, stream>>>(src, B, n, out, accumulate);
+  MDE_CHECK_LAUNCH();
+  return MDE_OK;
+}
+
+extern "C" int mde_axpy_f32(float* y, const float* x, float a, long long n, mde_stream_t stream) {
+  MDE_CHECK_ARG(y && x && n > 0, "mde_axpy_f32: bad arguments");
+  axpy_kernel<<<grid_1d(n, 256), 256, 0, stream>>>(y, x, a, n);
   MDE_CHECK_LAUNCH();
   return MDE_OK;
 }

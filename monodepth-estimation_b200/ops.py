@@ -248,16 +248,41 @@ def disp_to_depth(disp, min_depth, max_depth, out=None):
 
 
 # ---------------------------------------------------------------------- backward of the ViT encoder block (csrc/backward.cu)
-def transpose_bf16(src, ldt=None, want_t=True, want_rm=False):
-    """src [R,C] (f32 or bf16, contiguous) -> (dst_t bf16 [C, ldt] zero-padded beyond R | None, dst_rm bf16 [R,C] | None)."""
+def transpose_bf16(src, ldt=None, want_t=True, want_rm=False, dst_t=None, dst_rm=None, col0=0, cols_t=None, row0_rm=0):
+    """src [R,C] (f32 or bf16, rows contiguous) -> (dst_t bf16 [C, ldt] | None, dst_rm bf16 [R,C] | None).  Without ``dst_t`` a new
+    buffer is made and zero-filled beyond R.  With ``dst_t`` given, the block lands at columns [col0, col0+R) and columns up to
+    col0+cols_t are zero-filled (``cols_t`` defaults to R: nothing else is touched), so row blocks can be placed side by side;
+    ``dst_rm`` likewise receives its rows at ``row0_rm``."""
     R, Cc = src.shape
-    if src.dtype not in (F32, BF16):
-        raise ValueError("transpose_bf16 takes float32 or bfloat16")
-    ldt = ldt if ldt is not None else (R + 63) // 64 * 64
-    dst_t = torch.empty(Cc, ldt, device=src.device, dtype=BF16) if want_t else None
-    dst_rm = torch.empty(R, Cc, device=src.device, dtype=BF16) if want_rm else None
-    L.call("mde_transpose_bf16", _ptr(src), int(src.dtype == F32), R, Cc, src.stride(0), _ptr(dst_t), ldt, _ptr(dst_rm), Cc, _stream())
+    if src.dtype not in (F32, BF16) or src.stride(1) != 1:
+        raise ValueError("transpose_bf16 takes float32 or bfloat16 with contiguous rows")
+    if dst_t is None and want_t:
+        ldt = ldt if ldt is not None else (R + 63) // 64 * 64
+        dst_t = torch.empty(Cc, ldt, device=src.device, dtype=BF16)
+        cols_t = ldt
+    elif dst_t is not None:
+        ldt = dst_t.shape[1]
+        cols_t = R if cols_t is None else cols_t
+    if dst_rm is None and want_rm:
+        dst_rm = torch.empty(R, Cc, device=src.device, dtype=BF16)
+    pt = C.c_void_p(_ptr(dst_t, BF16).value + 2 * col0) if dst_t is not None else _ptr(None)
+    pr = C.c_void_p(_ptr(dst_rm, BF16).value + 2 * row0_rm * Cc) if dst_rm is not None else _ptr(None)
+    L.call("mde_transpose_bf16", C.c_void_p(src.data_ptr()), int(src.dtype == F32), R, Cc, src.stride(0), pt, ldt or 0, cols_t or 0, pr, Cc, _stream())
     return dst_t, dst_rm
+
+
+def batch_sum_f32(src, out=None, accumulate=False):
+    """src f32 [B, ...] -> sum over the first dimension, fixed order."""
+    B = src.shape[0]
+    n = src.numel() // B
+    out = out if out is not None else torch.empty(src.shape[1:], device=src.device, dtype=F32)
+    L.call("mde_batch_sum_f32", _ptr(src, F32), B, n, _ptr(out, F32), int(accumulate), _stream())
+    return out
+
+
+def axpy_f32(y, x, a=1.0):
+    L.call("mde_axpy_f32", _ptr(y, F32), _ptr(x, F32), float(a), y.numel(), _stream())
+    return y
 
 
 def colsum_bf16(src, out=None, accumulate=False):

@@ -120,3 +120,89 @@ class ViTBlockTrainer:
         dh1, g["self_attention.in_proj_weight"], g["self_attention.in_proj_bias"] = self._linear_bwd(dqkv, dqkv_t, s["h1"], w["qkv_t"], 768)
         dx_in, g["ln_1.weight"], g["ln_1.bias"] = ops.layernorm_bwd(s["x_in"], dh1, p["ln_1.weight"], 1e-6, dres=dx_mid)
         return dx_in, g
+
+
+HOOKS = (2, 5, 8, 11)  # encoder.py:44-50: forward hooks on these blocks feed the decoder
+
+
+class ViTEncoderTrainer:
+    """torchvision ``VisionTransformer`` as the reference uses it (``encoder.py:29-50,139-147``): patch embedding + class token +
+    position embedding (tv:268-300,156), twelve ``EncoderBlock`` s, the outputs of blocks 2 / 5 / 8 / 11 tapped by forward hooks.
+    The final ``encoder.ln`` and ``heads`` produce a value the reference discards (``encoder.py:38,142``): no gradient, not run.
+
+    ``params``: the VisionTransformer's own ``named_parameters()`` names (``class_token``, ``conv_proj.weight``, ``conv_proj.bias``,
+    ``encoder.pos_embedding``, ``encoder.layers.encoder_layer_<i>.<...>``), i.e. the reference's ``state_dict`` keys without the
+    leading ``encoder.encoder.``.
+    """
+
+    def __init__(self, params: dict):
+        f = lambda k: params[k].detach().to(F32).contiguous()
+        self.p = {k: f(k) for k in ("class_token", "conv_proj.weight", "conv_proj.bias", "encoder.pos_embedding")}
+        self.dev = self.p["class_token"].device
+        if self.dev.type != "cuda":
+            raise RuntimeError("ViTEncoderTrainer needs CUDA tensors (there is no CPU path)")
+        self.blocks = []
+        for i in range(12):
+            pre = f"encoder.layers.encoder_layer_{i}."
+            self.blocks.append(ViTBlockTrainer({n: params[pre + n] for n in _NAMES}))
+        self.repack()
+
+    def repack(self):
+        p = self.p
+        self.patch_w = p["conv_proj.weight"].reshape(768, 768).to(BF16).contiguous()
+        self.pos = p["encoder.pos_embedding"].reshape(197, 768).contiguous()
+        self.cls = p["class_token"].reshape(768).contiguous()
+        self.zero768 = torch.zeros(768, device=self.dev, dtype=F32)
+
+    def forward(self, patches):
+        """patches bf16 [B*196, 768] (row = (image, patch), columns (c, ky, kx): what ``mde_input_stage`` writes) -> the four
+        tapped residual streams, f32 [B*197, 768] each."""
+        if patches.dtype != BF16 or patches.shape[1] != 768 or patches.shape[0] % 196:
+            raise ValueError("patches must be bfloat16 [B*196, 768]")
+        B = patches.shape[0] // 196
+        self.B, self.patches = B, patches.contiguous()
+        x = torch.empty(B * L.VIT_SEQ, 768, device=self.dev, dtype=F32)
+        ops.gemm(self.patches, self.patch_w, self.p["conv_proj.bias"], L.EPI_PATCH_EMBED, x, self.pos, self.cls)
+        taps = []
+        for i, blk in enumerate(self.blocks):
+            x = blk.forward(x)
+            if i in HOOKS:
+                taps.append(x)
+        return taps
+
+    def backward(self, dtaps):
+        """dtaps: four entries (f32 [B*197, 768] or None) = the gradients of the tapped outputs.  Returns {name: fp32 gradient}
+        under the VisionTransformer's parameter names (parameters that received no gradient are absent, as autograd leaves
+        their ``.grad`` at None: blocks above the last tap that matters)."""
+        B, M = self.B, self.B * L.VIT_SEQ
+        grads = {}
+        dx = None
+        for i in range(11, -1, -1):
+            if i in HOOKS and dtaps[HOOKS.index(i)] is not None:
+                d = dtaps[HOOKS.index(i)]
+                dx = d.to(F32).clone() if dx is None else ops.axpy_f32(dx, d.contiguous())
+            if dx is None:
+                continue
+            dx, g = self.blocks[i].backward(dx)
+            for n, v in g.items():
+                grads[f"encoder.layers.encoder_layer_{i}.{n}"] = v
+        if dx is None:
+            return grads
+        # tokens = [class_token ; conv_proj(patches)] + pos_embedding  (tv:288-300, 156)
+        dpos = ops.batch_sum_f32(dx.view(B, L.VIT_SEQ * 768))
+        grads["encoder.pos_embedding"] = dpos.view(1, L.VIT_SEQ, 768)
+        grads["class_token"] = dpos.view(L.VIT_SEQ, 768)[0].clone().view(1, 1, 768)
+        Mp = (B * 196 + 63) // 64 * 64
+        dy_t = torch.empty(768, Mp, device=self.dev, dtype=BF16)
+        dy = torch.empty(B * 196, 768, device=self.dev, dtype=BF16)
+        for b in range(B):  # the patch rows of image b (its class-token row is skipped), placed side by side
+            rows = dx[b * L.VIT_SEQ + 1:(b + 1) * L.VIT_SEQ]
+            last = b == B - 1
+            ops.transpose_bf16(rows, dst_t=dy_t, dst_rm=dy, col0=b * 196, cols_t=(Mp - b * 196) if last else 196, row0_rm=b * 196)
+        p_t, _ = ops.transpose_bf16(self.patches, ldt=Mp)
+        dw = torch.empty(768, 768, device=self.dev, dtype=F32)
+        ops.gemm(dy_t, p_t, self.zero768, L.EPI_BIAS_F32, dw)
+        grads["conv_proj.weight"] = dw.view(768, 3, 16, 16)
+        grads["conv_proj.bias"] = ops.colsum_bf16(dy)
+        self.dpatch_rows = dy  # bf16 [B*196, 768]: dY of conv_proj, kept for the input-stage backward (encoder.normalize)
+        return grads

@@ -133,3 +133,47 @@ def test_vit_block_backward_matches_autograd(B):
     for n, p_ in blk.named_parameters():
         e = rel_l2(grads[n], p_.grad)
         assert grads[n].shape == p_.grad.shape and e < 2e-2, (n, e)
+
+
+def test_vit_encoder_backward_matches_autograd():
+    """The whole torchvision ViT-B/16 as encoder.py uses it (hooks on blocks 2/5/8/11, final ln discarded): gradients of every
+    parameter that autograd reaches, for a loss that reads taps 8 and 11 only — what ('disp', 0) depends on (decoder.py:97-166)."""
+    import torchvision
+
+    from monodepth_estimation_b200.training import HOOKS, ViTEncoderTrainer
+
+    torch.manual_seed(31)
+    B = 2
+    vit = torchvision.models.vit_b_16(weights=None).cuda().float()
+    vit.heads = torch.nn.Identity()
+    with torch.no_grad():
+        vit.class_token.normal_(0, 0.02)
+        for n, p_ in vit.named_parameters():
+            if ".ln" in n or "ln_" in n:
+                p_.add_(0.05 * torch.randn_like(p_))
+    feats = []
+    hooks = [vit.encoder.layers[i].register_forward_hook(lambda m, a, o: feats.append(o)) for i in HOOKS]
+    x224 = _rand(B, 3, 224, 224, seed=32)
+    vit(x224)
+    for h in hooks:
+        h.remove()
+    dt = [None, None, _rand(B * 197, 768, seed=33, scale=0.1), _rand(B * 197, 768, seed=34, scale=0.1)]
+    loss = (feats[2].reshape(-1, 768) * dt[2]).sum() + (feats[3].reshape(-1, 768) * dt[3]).sum()
+    loss.backward()
+
+    patches = x224.view(B, 3, 14, 16, 14, 16).permute(0, 2, 4, 1, 3, 5).reshape(B * 196, 768).to(BF16).contiguous()
+    params = {n: p_ for n, p_ in vit.named_parameters()}
+    tr = ViTEncoderTrainer(params)
+    taps = tr.forward(patches)
+    for i in range(4):
+        assert rel_l2(taps[i], feats[i].detach().reshape(-1, 768)) < 6e-3, i
+    grads = tr.backward(dt)
+    worst = ("", 0.0)
+    for n, p_ in vit.named_parameters():
+        if p_.grad is None:
+            assert n not in grads, n
+            continue
+        e = rel_l2(grads[n], p_.grad)
+        worst = max(worst, (n, e), key=lambda t: t[1])
+        assert grads[n].shape == p_.grad.shape and e < 3e-2, (n, e)
+    print("worst parameter gradient", worst)
