@@ -327,6 +327,51 @@ int mde_axpy_f32(float* y, const float* x, float a, long long n, mde_stream_t st
 int mde_vit_attention_bwd(const mde_bf16* q, const mde_bf16* k, const mde_bf16* vt, const mde_bf16* dout, int B, mde_bf16* dqkv,
                           mde_stream_t stream);
 
+/* ==== the rest of the training step (train/mars_adapter.py:117-153,209-247), train-mode decoder path of ('disp', 0) ====
+ * Train-mode activations are plain fp32 NHWC [B][h][w][C]; a 3x3 convolution is im2col + mde_gemm_bf16 in both directions. */
+
+/* decoder.py:8-19 (pad 1 + 3x3): x f32 [B][h][w][C] -> col bf16 [B*h*w][9C] (k = (ky*3+kx)*C + c) and/or colT bf16 [9C][ldt]
+ * (zero beyond B*h*w: the K padding of the weight-gradient GEMM).  padding = MDE_PAD_REFLECT | MDE_PAD_ZERO. */
+int mde_im2col3x3_bf16(const float* x, int B, int h, int w, int C, int padding, mde_bf16* col, mde_bf16* colT, int ldt, mde_stream_t stream);
+/* the adjoint: dxcol f32 [B*h*w][ldc] -> dx f32 [B][h][w][C] (reflected border rows/columns fold back onto rows 1 and h-2). */
+int mde_col2im3x3_f32(const float* dxcol, int ldc, int B, int h, int w, int C, int padding, float* dx, mde_stream_t stream);
+
+/* nn.BatchNorm2d in train mode + nn.ELU (decoder.py:22-34) on z f32 [N][ldz] (N = B*h*w rows, C channels): batch mean / biased
+ * variance -> mean, rstd (kept for the backward); y f32 [N][C] = ELU(gamma zhat + beta); running_mean / running_var updated
+ * with `momentum` and the unbiased variance when given.  Backward: dy f32 [N][C] -> dz f32 [N][C], dgamma, dbeta. */
+int mde_bn_elu_train_fwd(const float* z, int N, int C, int ldz, const float* gamma, const float* beta, float eps, float momentum, float* run_mean,
+                         float* run_var, float* mean, float* rstd, float* y, mde_stream_t stream);
+int mde_bn_elu_train_bwd(const float* z, int N, int C, int ldz, const float* mean, const float* rstd, const float* gamma, const float* beta,
+                         const float* dy, float* dz, float* dgamma, float* dbeta, mde_stream_t stream);
+
+/* F.interpolate(mode='bilinear') on fp32 NHWC and its adjoint (decoder.py:118-142 align_corners=True; model.py:95-100
+ * align_corners=False).  The destination may be a channel slice [coff, coff+C) of rows ldd wide (the concat of decoder.py:145). */
+int mde_bilinear_nhwc_f32(const float* src, int B, int hs, int ws, int C, float* dst, int hd, int wd, int ldd, int coff, int align_corners,
+                          mde_stream_t stream);
+int mde_bilinear_nhwc_bwd_f32(const float* ddst, int B, int hd, int wd, int C, int ldd, int coff, float* dsrc, int hs, int ws, int align_corners,
+                              mde_stream_t stream);
+
+/* F.instance_norm (encoder.py:167: no affine, biased variance) on x f32 [B][G][C] and its backward; the adjoint of
+ * mde_tokens_to_grid_bf16 (encoder.py:69-110): dgrid f32 [B][G][768] -> dtokens f32 [B][197][768]. */
+int mde_instnorm_f32(const float* x, int B, int G, int C, float eps, float* y, mde_stream_t stream);
+int mde_instnorm_bwd_f32(const float* x, const float* dy, int B, int G, int C, float eps, float* dx, mde_stream_t stream);
+int mde_tokens_to_grid_bwd_f32(const float* dgrid, int B, int strip_cls, int G, float* dtokens, mde_stream_t stream);
+
+/* decoder.py:166 + model.py:63-92: disp = mul * sigmoid(z[i*ldz]) and dz = ddisp * mul * s (1 - s). */
+int mde_sigmoid_head_f32(const float* z, int ldz, long long n, float mul, float* disp, mde_stream_t stream);
+int mde_sigmoid_head_bwd_f32(const float* z, int ldz, const float* ddisp, long long n, float mul, float* dz, mde_stream_t stream);
+
+/* MarsDomainAdapter.compute_losses (train/mars_adapter.py:209-247) with get_smooth_loss (layers.py:202-215): disp f32 [B][H][W] (=
+ * outputs[('disp',0)]), img f32 [B][3][H][W], rnd f32 [B][H][W] = the torch.rand_like draw of :238 (passed in so that both sides
+ * see the same numbers).  losses3 = (total, depth, smoothness), ddisp = d total / d disp.  scratch: mde_depth_loss_scratch_floats(). */
+long long mde_depth_loss_scratch_floats(void);
+int mde_depth_loss(const float* disp, const float* img, const float* rnd, int B, int H, int W, float w_depth, float w_smooth, float* scratch,
+                   float* losses3, float* ddisp, mde_stream_t stream);
+
+/* torch.optim.Adam step (train/mars_adapter.py:52-55,139; defaults: no weight decay, no amsgrad) on n contiguous fp32 values. */
+int mde_adam_step(float* p, const float* g, float* m, float* v, long long n, float lr, float beta1, float beta2, float eps, int step,
+                  mde_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

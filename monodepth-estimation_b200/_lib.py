@@ -74,8 +74,23 @@ SIGNATURES = {
     "mde_layernorm_bwd_scratch_floats": [_i],
     "mde_layernorm_bwd": [_p, _p, _p, _i, _i, _f, _p, _p, _p, _p, _i, _p, _p],
     "mde_vit_attention_bwd": [_p, _p, _p, _p, _i, _p, _p],
+    "mde_im2col3x3_bf16": [_p, _i, _i, _i, _i, _i, _p, _p, _i, _p],
+    "mde_col2im3x3_f32": [_p, _i, _i, _i, _i, _i, _i, _p, _p],
+    "mde_bn_elu_train_fwd": [_p, _i, _i, _i, _p, _p, _f, _f, _p, _p, _p, _p, _p, _p],
+    "mde_bn_elu_train_bwd": [_p, _i, _i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p],
+    "mde_bilinear_nhwc_f32": [_p, _i, _i, _i, _i, _p, _i, _i, _i, _i, _i, _p],
+    "mde_bilinear_nhwc_bwd_f32": [_p, _i, _i, _i, _i, _i, _i, _p, _i, _i, _i, _p],
+    "mde_instnorm_f32": [_p, _i, _i, _i, _f, _p, _p],
+    "mde_instnorm_bwd_f32": [_p, _p, _i, _i, _i, _f, _p, _p],
+    "mde_tokens_to_grid_bwd_f32": [_p, _i, _i, _i, _p, _p],
+    "mde_sigmoid_head_f32": [_p, _i, _ll, _f, _p, _p],
+    "mde_sigmoid_head_bwd_f32": [_p, _i, _p, _ll, _f, _p, _p],
+    "mde_depth_loss_scratch_floats": [],
+    "mde_depth_loss": [_p, _p, _p, _i, _i, _i, _f, _f, _p, _p, _p, _p],
+    "mde_adam_step": [_p, _p, _p, _p, _ll, _f, _f, _f, _f, _i, _p],
 }
-_RESTYPES = {"mde_last_error": C.c_char_p, "mde_point_cloud_scratch_bytes": C.c_longlong, "mde_layernorm_bwd_scratch_floats": C.c_longlong}
+_RESTYPES = {"mde_last_error": C.c_char_p, "mde_point_cloud_scratch_bytes": C.c_longlong, "mde_layernorm_bwd_scratch_floats": C.c_longlong,
+             "mde_depth_loss_scratch_floats": C.c_longlong}
 
 _lock = threading.Lock()
 _lib = None

@@ -320,3 +320,107 @@ def vit_attention_bwd(q, k, vt, dout, B, out=None):
     out = out if out is not None else torch.empty(B * L.VIT_SEQ, 3 * L.VIT_DIM, device=q.device, dtype=BF16)
     L.call("mde_vit_attention_bwd", _ptr(q, BF16), _ptr(k, BF16), _ptr(vt, BF16), _ptr(dout, BF16), B, _ptr(out, BF16), _stream())
     return out
+
+
+# ---------------------------------------------------------------------- the rest of the training step (csrc/train_ops.cu)
+def _f32(*shape, dev):
+    return torch.empty(*shape, device=dev, dtype=F32)
+
+
+def im2col3x3(x, padding, want_col=True, want_colT=True):
+    """x f32 [B,h,w,C] -> (col bf16 [B*h*w, 9C] | None, colT bf16 [9C, ldt] | None) with ldt = B*h*w rounded up to 64."""
+    B, h, w, Cc = x.shape
+    n = B * h * w
+    ldt = (n + 63) // 64 * 64
+    col = torch.empty(n, 9 * Cc, device=x.device, dtype=BF16) if want_col else None
+    colT = torch.empty(9 * Cc, ldt, device=x.device, dtype=BF16) if want_colT else None
+    L.call("mde_im2col3x3_bf16", _ptr(x, F32), B, h, w, Cc, padding, _ptr(col), _ptr(colT), ldt, _stream())
+    return col, colT
+
+
+def col2im3x3(dxcol, B, h, w, Cc, padding):
+    dx = _f32(B, h, w, Cc, dev=dxcol.device)
+    L.call("mde_col2im3x3_f32", _ptr(dxcol, F32), dxcol.shape[1], B, h, w, Cc, padding, _ptr(dx, F32), _stream())
+    return dx
+
+
+def bn_elu_train_fwd(z, Cc, gamma, beta, eps=1e-5, momentum=0.1, run_mean=None, run_var=None):
+    """z f32 [N, ldz>=C] -> (y f32 [N,C], mean [C], rstd [C]); running statistics updated in place when given."""
+    N, ldz = z.shape
+    mean, rstd, y = _f32(Cc, dev=z.device), _f32(Cc, dev=z.device), _f32(N, Cc, dev=z.device)
+    L.call("mde_bn_elu_train_fwd", _ptr(z, F32), N, Cc, ldz, _ptr(gamma, F32), _ptr(beta, F32), float(eps), float(momentum),
+           _ptr(run_mean, F32) if run_mean is not None else _ptr(None), _ptr(run_var, F32) if run_var is not None else _ptr(None),
+           _ptr(mean, F32), _ptr(rstd, F32), _ptr(y, F32), _stream())
+    return y, mean, rstd
+
+
+def bn_elu_train_bwd(z, Cc, mean, rstd, gamma, beta, dy):
+    N, ldz = z.shape
+    dz, dg, db = _f32(N, Cc, dev=z.device), _f32(Cc, dev=z.device), _f32(Cc, dev=z.device)
+    L.call("mde_bn_elu_train_bwd", _ptr(z, F32), N, Cc, ldz, _ptr(mean, F32), _ptr(rstd, F32), _ptr(gamma, F32), _ptr(beta, F32), _ptr(dy, F32),
+           _ptr(dz, F32), _ptr(dg, F32), _ptr(db, F32), _stream())
+    return dz, dg, db
+
+
+def bilinear_nhwc(src, hd, wd, align_corners, dst=None, coff=0):
+    B, hs, ws, Cc = src.shape
+    dst = dst if dst is not None else _f32(B, hd, wd, Cc, dev=src.device)
+    L.call("mde_bilinear_nhwc_f32", _ptr(src, F32), B, hs, ws, Cc, _ptr(dst, F32), hd, wd, dst.shape[-1], coff, int(align_corners), _stream())
+    return dst
+
+
+def bilinear_nhwc_bwd(ddst, hs, ws, align_corners, Cc=None, coff=0):
+    B, hd, wd, ldd = ddst.shape
+    Cc = ldd if Cc is None else Cc
+    dsrc = _f32(B, hs, ws, Cc, dev=ddst.device)
+    L.call("mde_bilinear_nhwc_bwd_f32", _ptr(ddst, F32), B, hd, wd, Cc, ldd, coff, _ptr(dsrc, F32), hs, ws, int(align_corners), _stream())
+    return dsrc
+
+
+def instnorm_f32(x, eps=1e-5):
+    B, G, Cc = x.shape
+    y = torch.empty_like(x)
+    L.call("mde_instnorm_f32", _ptr(x, F32), B, G, Cc, float(eps), _ptr(y, F32), _stream())
+    return y
+
+
+def instnorm_bwd_f32(x, dy, eps=1e-5):
+    B, G, Cc = x.shape
+    dx = torch.empty_like(x)
+    L.call("mde_instnorm_bwd_f32", _ptr(x, F32), _ptr(dy, F32), B, G, Cc, float(eps), _ptr(dx, F32), _stream())
+    return dx
+
+
+def tokens_to_grid_bwd(dgrid, B, strip_cls, G):
+    dtok = _f32(B * L.VIT_SEQ, L.VIT_DIM, dev=dgrid.device)
+    L.call("mde_tokens_to_grid_bwd_f32", _ptr(dgrid, F32), B, int(strip_cls), G, _ptr(dtok, F32), _stream())
+    return dtok
+
+
+def sigmoid_head(z, n, mul):
+    d = _f32(n, dev=z.device)
+    L.call("mde_sigmoid_head_f32", _ptr(z, F32), z.shape[-1], n, float(mul), _ptr(d, F32), _stream())
+    return d
+
+
+def sigmoid_head_bwd(z, ddisp, mul):
+    n = ddisp.numel()
+    dz = _f32(n, dev=z.device)
+    L.call("mde_sigmoid_head_bwd_f32", _ptr(z, F32), z.shape[-1], _ptr(ddisp, F32), n, float(mul), _ptr(dz, F32), _stream())
+    return dz
+
+
+def depth_loss(disp, img, rnd, w_depth=1.0, w_smooth=0.001):
+    """disp f32 [B,1,H,W] or [B,H,W], img f32 [B,3,H,W], rnd f32 like disp -> (losses f32 [3] = total, depth, smoothness; ddisp like disp)."""
+    B, H, W = disp.shape[0], disp.shape[-2], disp.shape[-1]
+    scratch = _f32(int(L.load().mde_depth_loss_scratch_floats()), dev=disp.device)
+    losses, dd = _f32(3, dev=disp.device), torch.empty_like(disp)
+    L.call("mde_depth_loss", _ptr(disp, F32), _ptr(img, F32), _ptr(rnd, F32), B, H, W, float(w_depth), float(w_smooth), _ptr(scratch, F32),
+           _ptr(losses, F32), _ptr(dd, F32), _stream())
+    return losses, dd
+
+
+def adam_step(p, g, m, v, lr, step, beta1=0.9, beta2=0.999, eps=1e-8):
+    L.call("mde_adam_step", _ptr(p, F32), _ptr(g, F32), _ptr(m, F32), _ptr(v, F32), p.numel(), float(lr), float(beta1), float(beta2), float(eps), int(step),
+           _stream())
+    return p

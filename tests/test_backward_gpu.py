@@ -10,6 +10,9 @@ from helpers import max_abs, rel_l2
 pytestmark = pytest.mark.gpu
 
 BF16 = torch.bfloat16
+# the torch side is the fp32 reference: no TF32 in its convolutions / matmuls
+torch.backends.cudnn.allow_tf32 = False
+torch.backends.cuda.matmul.allow_tf32 = False
 
 
 def _mods():
@@ -177,3 +180,117 @@ def test_vit_encoder_backward_matches_autograd():
         worst = max(worst, (n, e), key=lambda t: t[1])
         assert grads[n].shape == p_.grad.shape and e < 3e-2, (n, e)
     print("worst parameter gradient", worst)
+
+
+# --------------------------------------------------------------------------- train-mode decoder path, loss, Adam (csrc/train_ops.cu)
+@pytest.mark.parametrize("pad", ["reflect", "zero"])
+def test_im2col_gemm_is_the_conv_and_col2im_is_its_adjoint(pad):
+    L, ops = _mods()
+    B, h, w, C, Co = 2, 14, 15, 64, 128
+    x = _rand(B, h, w, C, seed=41)
+    wt = _rand(Co, C, 3, 3, seed=42, scale=0.05)
+    mode = L.PAD_REFLECT if pad == "reflect" else L.PAD_ZERO
+    col, colT = ops.im2col3x3(x, mode)
+    n = B * h * w
+    assert torch.equal(colT[:, :n], col.t()) and float(colT[:, n:].float().abs().sum()) == 0.0
+    xn = x.permute(0, 3, 1, 2).clone().requires_grad_(True)
+    xp = F.pad(xn, (1, 1, 1, 1), mode="reflect") if pad == "reflect" else F.pad(xn, (1, 1, 1, 1))
+    ref = F.conv2d(xp, wt)
+    wm = wt.permute(0, 2, 3, 1).reshape(Co, 9 * C)  # k = (ky*3+kx)*C + c
+    got = (col.float() @ wm.t()).view(B, h, w, Co).permute(0, 3, 1, 2)
+    assert rel_l2(got, ref.detach()) < 4e-3
+    dy = _rand(B, Co, h, w, seed=43)
+    ref.backward(dy)
+    dxcol = (dy.permute(0, 2, 3, 1).reshape(n, Co) @ wm).contiguous()  # fp32 here: isolates the col2im fold
+    dx = ops.col2im3x3(dxcol, B, h, w, C, mode)
+    assert rel_l2(dx.permute(0, 3, 1, 2), xn.grad) < 1e-5
+
+
+def test_bn_elu_train_forward_backward_and_running_stats():
+    L, ops = _mods()
+    N, C = 1680, 128
+    z = (_rand(N, C, seed=44) * (0.5 + torch.rand(1, C, device="cuda")) + _rand(1, C, seed=45)).contiguous()
+    bn = torch.nn.BatchNorm2d(C).cuda().train()
+    with torch.no_grad():
+        bn.weight.uniform_(0.5, 1.5)
+        bn.bias.normal_(0, 0.2)
+        bn.running_mean.normal_(0, 0.1)
+        bn.running_var.uniform_(0.5, 1.5)
+    rm, rv = bn.running_mean.clone(), bn.running_var.clone()
+    zr = z.t().reshape(1, C, N, 1).clone().requires_grad_(True)
+    y = F.elu(bn(zr))
+    dy = _rand(N, C, seed=46)
+    y.backward(dy.t().reshape(1, C, N, 1))
+    got, mean, rstd = ops.bn_elu_train_fwd(z, C, bn.weight.detach(), bn.bias.detach(), run_mean=rm, run_var=rv)
+    assert rel_l2(got, y.detach().view(C, N).t()) < 1e-5
+    assert rel_l2(rm, bn.running_mean) < 1e-6 and rel_l2(rv, bn.running_var) < 1e-5
+    dz, dg, db = ops.bn_elu_train_bwd(z, C, mean, rstd, bn.weight.detach(), bn.bias.detach(), dy)
+    assert rel_l2(dz, zr.grad.view(C, N).t()) < 1e-4
+    assert rel_l2(dg, bn.weight.grad) < 1e-4 and rel_l2(db, bn.bias.grad) < 1e-4
+
+
+@pytest.mark.parametrize("hs,ws,hd,wd,align,C", [(14, 15, 28, 30, True, 128), (28, 30, 528, 528, False, 1), (28, 30, 130, 97, False, 1), (14, 15, 28, 30, False, 8)])
+def test_bilinear_forward_and_adjoint(hs, ws, hd, wd, align, C):
+    L, ops = _mods()
+    B = 2
+    x = _rand(B, hs, ws, C, seed=47)
+    xr = x.permute(0, 3, 1, 2).clone().requires_grad_(True)
+    ref = F.interpolate(xr, size=(hd, wd), mode="bilinear", align_corners=align)
+    got = ops.bilinear_nhwc(x, hd, wd, align)
+    assert rel_l2(got.permute(0, 3, 1, 2), ref.detach()) < 1e-5
+    dd = _rand(B, hd, wd, C, seed=48)
+    ref.backward(dd.permute(0, 3, 1, 2))
+    ds = ops.bilinear_nhwc_bwd(dd, hs, ws, align)
+    assert rel_l2(ds.permute(0, 3, 1, 2), xr.grad) < 1e-5
+
+
+def test_instnorm_backward_and_grid_adjoint():
+    L, ops = _mods()
+    B, G, C = 3, 210, 256
+    x = _rand(B, G, C, seed=49) * 2 + 0.3
+    xr = x.permute(0, 2, 1).reshape(B, C, 14, 15).clone().requires_grad_(True)
+    y = F.instance_norm(xr, eps=1e-5)
+    dy = _rand(B, G, C, seed=50)
+    y.backward(dy.permute(0, 2, 1).reshape(B, C, 14, 15))
+    assert rel_l2(ops.instnorm_f32(x).permute(0, 2, 1).reshape(B, C, 14, 15), y.detach()) < 1e-5
+    assert rel_l2(ops.instnorm_bwd_f32(x, dy).permute(0, 2, 1).reshape(B, C, 14, 15), xr.grad) < 1e-4
+    dgrid = _rand(B, G, 768, seed=51)
+    dtok = ops.tokens_to_grid_bwd(dgrid, B, 0, G).view(B, 197, 768)
+    assert torch.equal(dtok, dgrid[:, :197])  # 14x15 grid: CLS kept at cell 0, cells 197..209 are zero padding (encoder.py:90-102)
+    dgrid2 = _rand(B, 196, 768, seed=52)
+    dtok2 = ops.tokens_to_grid_bwd(dgrid2, B, 1, 196).view(B, 197, 768)
+    assert float(dtok2[:, 0].abs().sum()) == 0.0 and torch.equal(dtok2[:, 1:], dgrid2)
+
+
+def test_depth_loss_matches_compute_losses():
+    """MarsDomainAdapter.compute_losses (train/mars_adapter.py:209-247) restated in torch with the rand draw passed in."""
+    L, ops = _mods()
+    B, H, W = 2, 96, 128
+    disp = torch.sigmoid(_rand(B, 1, H, W, seed=53)).contiguous()
+    img = torch.rand(B, 3, H, W, device="cuda")
+    rnd = torch.rand(B, 1, H, W, device="cuda")
+    d = disp.clone().requires_grad_(True)
+    gx = (d[:, :, :, :-1] - d[:, :, :, 1:]).abs() * torch.exp(-(img[:, :, :, :-1] - img[:, :, :, 1:]).abs().mean(1, keepdim=True))
+    gy = (d[:, :, :-1, :] - d[:, :, 1:, :]).abs() * torch.exp(-(img[:, :, :-1, :] - img[:, :, 1:, :]).abs().mean(1, keepdim=True))
+    smooth = 0.001 * (gx.mean() + gy.mean())
+    depth = 1.0 * (d - d.detach() * (0.9 + 0.2 * rnd)).abs().mean()
+    (depth + smooth).backward()
+    losses, dd = ops.depth_loss(disp, img, rnd, 1.0, 0.001)
+    assert abs(float(losses[1]) - float(depth)) < 1e-6 * float(depth) + 1e-9
+    assert abs(float(losses[2]) - float(smooth)) < 1e-5 * float(smooth) + 1e-10
+    assert abs(float(losses[0]) - float(depth + smooth)) < 1e-6 * float(depth + smooth)
+    assert rel_l2(dd, d.grad) < 1e-5
+
+
+def test_adam_step_matches_torch():
+    L, ops = _mods()
+    p0, lr = _rand(100003, seed=54), 1e-4
+    p = torch.nn.Parameter(p0.clone())
+    opt = torch.optim.Adam([p], lr=lr)
+    mine, m, v = p0.clone(), torch.zeros_like(p0), torch.zeros_like(p0)
+    for step in range(1, 4):
+        g = _rand(100003, seed=60 + step)
+        p.grad = g.clone()
+        opt.step()
+        ops.adam_step(mine, g, m, v, lr, step)
+    assert max_abs(mine, p.detach()) < 5e-7  # one ulp at |p| ~ 3
