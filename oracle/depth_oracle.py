@@ -76,10 +76,11 @@ def tokens_to_grid(tok, h, w):
     return tok.reshape(B, h, w, C).permute(0, 3, 1, 2)
 
 
-def input_range_map(sd, p, x):
-    """encoder.py:129-135 — eval BatchNorm2d(3) then the whole-batch range heuristic."""
+def input_range_map(sd, p, x, train=False):
+    """encoder.py:129-135 — BatchNorm2d(3) (eval: running statistics; train: batch statistics, running statistics updated in
+    place as nn.BatchNorm2d does) then the whole-batch range heuristic."""
     x = F.batch_norm(x, sd[p + "normalize.running_mean"], sd[p + "normalize.running_var"],
-                     sd[p + "normalize.weight"], sd[p + "normalize.bias"], False, 0.0, 1e-5)
+                     sd[p + "normalize.weight"], sd[p + "normalize.bias"], train, 0.1 if train else 0.0, 1e-5)
     if x.max() > 1.0:
         x = x / 255.0
     if x.min() >= 0 and x.max() <= 1.0:
@@ -87,10 +88,10 @@ def input_range_map(sd, p, x):
     return x
 
 
-def encoder_forward(sd, x, p="encoder.", want=None):
+def encoder_forward(sd, x, p="encoder.", want=None, train=False):
     """encoder.py:112-187 — returns 4 x [B,256,gh,gw]."""
     H, W = x.shape[2:]
-    x = input_range_map(sd, p, x)
+    x = input_range_map(sd, p, x, train)
     if (H, W) != (224, 224):
         x = F.interpolate(x, size=(224, 224), mode="bilinear", align_corners=False)
     taps = vit_taps(sd, p + "encoder.", x)
@@ -106,29 +107,29 @@ def encoder_forward(sd, x, p="encoder.", want=None):
 
 
 # ----------------------------------------------------------------------- decoder
-def conv_block(sd, p, x):
-    """decoder.py:8-34 — ReflectionPad2d(1), 3x3 conv, eval BatchNorm2d, ELU."""
+def conv_block(sd, p, x, train=False):
+    """decoder.py:8-34 — ReflectionPad2d(1), 3x3 conv, BatchNorm2d (eval, or train: batch statistics), ELU."""
     x = F.conv2d(F.pad(x, (1, 1, 1, 1), mode="reflect"), sd[p + "conv.0.conv.1.weight"], sd[p + "conv.0.conv.1.bias"])
     x = F.batch_norm(x, sd[p + "conv.1.running_mean"], sd[p + "conv.1.running_var"],
-                     sd[p + "conv.1.weight"], sd[p + "conv.1.bias"], False, 0.0, 1e-5)
+                     sd[p + "conv.1.weight"], sd[p + "conv.1.bias"], train, 0.1 if train else 0.0, 1e-5)
     return F.elu(x)
 
 
-def decoder_forward(sd, feats, p="decoder.convs.", want=None):
+def decoder_forward(sd, feats, p="decoder.convs.", want=None, train=False):
     """decoder.py:90-173 — returns {("disp", i): [B,1,28*2^i,30*2^i]} (level sizes for a 14x15 grid)."""
     out = {}
-    x = conv_block(sd, p + "init_conv.", feats[-1])
+    x = conv_block(sd, p + "init_conv.", feats[-1], train)
     for i in range(4):
-        x = conv_block(sd, f"{p}upconv_{i}_0.", x)
+        x = conv_block(sd, f"{p}upconv_{i}_0.", x, train)
         x = F.interpolate(x, size=(x.shape[2] * 2, x.shape[3] * 2), mode="bilinear", align_corners=True)
         if i < 3:
-            s = conv_block(sd, f"{p}skip_{i}.", feats[-(i + 2)])
+            s = conv_block(sd, f"{p}skip_{i}.", feats[-(i + 2)], train)
             if s.shape[2:] != x.shape[2:]:
                 s = F.interpolate(s, size=x.shape[2:], mode="bilinear", align_corners=True)
             x = torch.cat([x, s], dim=1)
-        x = conv_block(sd, f"{p}upconv_{i}_1.", x)
+        x = conv_block(sd, f"{p}upconv_{i}_1.", x, train)
         if i == 3:
-            x = conv_block(sd, p + "mars_adapt.", x)
+            x = conv_block(sd, p + "mars_adapt.", x, train)
         if want is not None:
             want[f"dec_x{i}"] = x
         out[("disp", i)] = torch.sigmoid(F.conv2d(x, sd[f"{p}dispconv_{i}.weight"], sd[f"{p}dispconv_{i}.bias"], padding=1))
@@ -158,11 +159,11 @@ def source_scale(metadata):
     return 1.0
 
 
-def standard_forward(sd, x, metadata=None, want=None):
-    """model.py:32-102 DepthAnything.forward."""
+def standard_forward(sd, x, metadata=None, want=None, train=False):
+    """model.py:32-102 DepthAnything.forward (train=True: the BatchNorms use and update batch statistics, as under model.train())."""
     size = x.shape[2:]
-    feats = encoder_forward(sd, _pad16(x), want=want)
-    out = decoder_forward(sd, feats, want=want)
+    feats = encoder_forward(sd, _pad16(x), want=want, train=train)
+    out = decoder_forward(sd, feats, want=want, train=train)
     if want is not None:
         want["features"] = feats
         want["disp_lowres"] = dict(out)
