@@ -359,7 +359,13 @@ int mde_tokens_to_grid_bwd_f32(const float* dgrid, int B, int strip_cls, int G, 
 
 /* decoder.py:166 + model.py:63-92: disp = mul * sigmoid(z[i*ldz]) and dz = ddisp * mul * s (1 - s). */
 int mde_sigmoid_head_f32(const float* z, int ldz, long long n, float mul, float* disp, mde_stream_t stream);
-int mde_sigmoid_head_bwd_f32(const float* z, int ldz, const float* ddisp, long long n, float mul, float* dz, mde_stream_t stream);
+int mde_sigmoid_head_bwd_f32(const float* z, int ldz, const float* ddisp, long long n, float mul, float* dz, int ldo, mde_stream_t stream);
+
+/* encoder.py:129 in train mode: per-channel batch mean and BIASED variance of x f32 [B][C][hw] (what nn.BatchNorm2d normalises with),
+ * running statistics updated with `momentum` and the unbiased variance when given.  Passing (weight, bias, mean, var) as the
+ * bn4x3 block of mde_input_stage then evaluates the train-mode forward. */
+int mde_channel_stats_nchw(const float* x, int B, int C, long long hw, float momentum, float* run_mean, float* run_var, float* mean, float* var,
+                           mde_stream_t stream);
 
 /* MarsDomainAdapter.compute_losses (train/mars_adapter.py:209-247) with get_smooth_loss (layers.py:202-215): disp f32 [B][H][W] (=
  * outputs[('disp',0)]), img f32 [B][3][H][W], rnd f32 [B][H][W] = the torch.rand_like draw of :238 (passed in so that both sides

@@ -84,7 +84,8 @@ SIGNATURES = {
     "mde_instnorm_bwd_f32": [_p, _p, _i, _i, _i, _f, _p, _p],
     "mde_tokens_to_grid_bwd_f32": [_p, _i, _i, _i, _p, _p],
     "mde_sigmoid_head_f32": [_p, _i, _ll, _f, _p, _p],
-    "mde_sigmoid_head_bwd_f32": [_p, _i, _p, _ll, _f, _p, _p],
+    "mde_sigmoid_head_bwd_f32": [_p, _i, _p, _ll, _f, _p, _i, _p],
+    "mde_channel_stats_nchw": [_p, _i, _i, _ll, _f, _p, _p, _p, _p, _p],
     "mde_depth_loss_scratch_floats": [],
     "mde_depth_loss": [_p, _p, _p, _i, _i, _i, _f, _f, _p, _p, _p, _p],
     "mde_adam_step": [_p, _p, _p, _p, _ll, _f, _f, _f, _f, _i, _p],

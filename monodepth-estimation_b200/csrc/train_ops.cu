@@ -298,10 +298,46 @@ __global__ void __launch_bounds__(256) grid_to_tokens_bwd_kernel(const float* __
 __global__ void __launch_bounds__(256) sigmoid_fwd_kernel(const float* __restrict__ z, int ldz, long long n, float mul, float* __restrict__ d) {
   MDE_GRID_STRIDE(i, n) d[i] = mul / (1.0f + expf(-z[(size_t)i * ldz]));
 }
-__global__ void __launch_bounds__(256) sigmoid_bwd_kernel(const float* __restrict__ z, int ldz, const float* __restrict__ dd, long long n, float mul, float* __restrict__ dz) {
+__global__ void __launch_bounds__(256) sigmoid_bwd_kernel(const float* __restrict__ z, int ldz, const float* __restrict__ dd, long long n, float mul, float* __restrict__ dz,
+                                                          int ldo) {
   MDE_GRID_STRIDE(i, n) {
     const float s = 1.0f / (1.0f + expf(-z[(size_t)i * ldz]));
-    dz[i] = dd[i] * mul * s * (1.0f - s);
+    dz[(size_t)i * ldo] = dd[i] * mul * s * (1.0f - s);
+  }
+}
+
+// ------------------------------------------------------------------ BatchNorm2d(3) of encoder.py:129 in train mode: batch statistics of an NCHW image batch
+// One block per channel; every thread accumulates in double over a fixed stride, the 256 partials are added in thread order.
+__global__ void __launch_bounds__(256) channel_stats_kernel(const float* __restrict__ x, int B, int C, long long hw, float* __restrict__ mean, float* __restrict__ var,
+                                                            float* __restrict__ run_mean, float* __restrict__ run_var, float momentum) {
+  __shared__ double s1[256], s2[256];
+  const int c = blockIdx.x;
+  double a = 0.0, q = 0.0;
+  for (int b = 0; b < B; ++b) {
+    const float* p = x + ((size_t)b * C + c) * hw;
+    for (long long i = threadIdx.x; i < hw; i += 256) {
+      const double v = p[i];
+      a += v;
+      q += v * v;
+    }
+  }
+  s1[threadIdx.x] = a;
+  s2[threadIdx.x] = q;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double ta = 0.0, tq = 0.0;
+    for (int k = 0; k < 256; ++k) {
+      ta += s1[k];
+      tq += s2[k];
+    }
+    const double n = (double)B * (double)hw, m = ta / n;
+    const double vb = fmax(tq / n - m * m, 0.0);
+    mean[c] = (float)m;
+    var[c] = (float)vb;
+    if (run_mean) {
+      run_mean[c] = (1.0f - momentum) * run_mean[c] + momentum * (float)m;
+      run_var[c] = (1.0f - momentum) * run_var[c] + momentum * (float)(n > 1.0 ? vb * n / (n - 1.0) : vb);
+    }
   }
 }
 
@@ -466,9 +502,18 @@ extern "C" int mde_sigmoid_head_f32(const float* z, int ldz, long long n, float 
   return MDE_OK;
 }
 
-extern "C" int mde_sigmoid_head_bwd_f32(const float* z, int ldz, const float* ddisp, long long n, float mul, float* dz, mde_stream_t stream) {
-  MDE_CHECK_ARG(z && ddisp && dz && n > 0 && ldz >= 1, "mde_sigmoid_head_bwd_f32: bad arguments");
-  sigmoid_bwd_kernel<<<grid1(n), 256, 0, stream>>>(z, ldz, ddisp, n, mul, dz);
+extern "C" int mde_channel_stats_nchw(const float* x, int B, int C, long long hw, float momentum, float* run_mean, float* run_var, float* mean, float* var,
+                                      mde_stream_t stream) {
+  MDE_CHECK_ARG(x && mean && var && B > 0 && C > 0 && hw > 0, "mde_channel_stats_nchw: bad arguments");
+  MDE_CHECK_ARG((run_mean == nullptr) == (run_var == nullptr), "mde_channel_stats_nchw: running_mean and running_var go together");
+  channel_stats_kernel<<<C, 256, 0, stream>>>(x, B, C, hw, mean, var, run_mean, run_var, momentum);
+  MDE_CHECK_LAUNCH();
+  return MDE_OK;
+}
+
+extern "C" int mde_sigmoid_head_bwd_f32(const float* z, int ldz, const float* ddisp, long long n, float mul, float* dz, int ldo, mde_stream_t stream) {
+  MDE_CHECK_ARG(z && ddisp && dz && n > 0 && ldz >= 1 && ldo >= 1, "mde_sigmoid_head_bwd_f32: bad arguments");
+  sigmoid_bwd_kernel<<<grid1(n), 256, 0, stream>>>(z, ldz, ddisp, n, mul, dz, ldo);
   MDE_CHECK_LAUNCH();
   return MDE_OK;
 }

@@ -403,11 +403,21 @@ def sigmoid_head(z, n, mul):
     return d
 
 
-def sigmoid_head_bwd(z, ddisp, mul):
+def sigmoid_head_bwd(z, ddisp, mul, out=None):
+    """dz[i] = ddisp[i] * mul * s(1-s); ``out`` f32 [n, ldo] receives it in column 0 (its other columns are left alone)."""
     n = ddisp.numel()
-    dz = _f32(n, dev=z.device)
-    L.call("mde_sigmoid_head_bwd_f32", _ptr(z, F32), z.shape[-1], _ptr(ddisp, F32), n, float(mul), _ptr(dz, F32), _stream())
-    return dz
+    out = out if out is not None else _f32(n, 1, dev=z.device)
+    L.call("mde_sigmoid_head_bwd_f32", _ptr(z, F32), z.shape[-1], _ptr(ddisp, F32), n, float(mul), _ptr(out, F32), out.shape[-1], _stream())
+    return out
+
+
+def channel_stats_nchw(x, momentum=0.1, run_mean=None, run_var=None):
+    """x f32 [B,C,H,W] -> (mean [C], biased var [C]); running statistics updated in place when given (nn.BatchNorm2d.train())."""
+    B, Cc, H, W = x.shape
+    mean, var = _f32(Cc, dev=x.device), _f32(Cc, dev=x.device)
+    L.call("mde_channel_stats_nchw", _ptr(x, F32), B, Cc, H * W, float(momentum), _ptr(run_mean, F32) if run_mean is not None else _ptr(None),
+           _ptr(run_var, F32) if run_var is not None else _ptr(None), _ptr(mean, F32), _ptr(var, F32), _stream())
+    return mean, var
 
 
 def depth_loss(disp, img, rnd, w_depth=1.0, w_smooth=0.001):

@@ -206,3 +206,231 @@ class ViTEncoderTrainer:
         grads["conv_proj.bias"] = ops.colsum_bf16(dy)
         self.dpatch_rows = dy  # bf16 [B*196, 768]: dY of conv_proj, kept for the input-stage backward (encoder.normalize)
         return grads
+
+
+# ====================================================================== the rest of the step: features, decoder level 0, loss, Adam
+def _linear_grads(dy_f32, x_t, w_t, zero_in, dev):
+    """dy f32 [N, Co] (gradient of x W^T + b), x_t bf16 [Ci, Np] (the layer input, transposed, zero padded), w_t bf16 [Ci, Co]
+    -> (dx f32 [N, Ci], dW f32 [Co, Ci], db f32 [Co])."""
+    N, Co = dy_f32.shape
+    Np, Ci = x_t.shape[1], x_t.shape[0]
+    dy_t, dy_rm = ops.transpose_bf16(dy_f32, ldt=Np, want_rm=True)
+    dw = torch.empty(Co, Ci, device=dev, dtype=F32)
+    ops.gemm(dy_t, x_t, zero_in, L.EPI_BIAS_F32, dw)
+    db = ops.colsum_bf16(dy_rm)
+    dx = torch.empty(N, Ci, device=dev, dtype=F32)
+    ops.gemm(dy_rm, w_t, zero_in, L.EPI_BIAS_F32, dx)
+    return dx, dw, db
+
+
+class _FeatureT:
+    """encoder.py:156-168 for one tap: token -> grid rows, 1x1 conv 768 -> 256 (channel_reduce[i]), instance norm."""
+
+    def __init__(self, weight, bias, dev):
+        self.weight, self.bias, self.dev = weight, bias, dev  # views of the model's parameters
+        self.zero = torch.zeros(768, device=dev, dtype=F32)
+        self.repack()
+
+    def repack(self):
+        w = self.weight.detach().reshape(256, 768)
+        self.w = w.to(BF16).contiguous()
+        self.w_t = _pad_rows(ops.transpose_bf16(w.contiguous(), ldt=256)[0])  # [768][256]
+
+    def forward(self, tap, B, strip, G):
+        self.B, self.strip, self.G = B, strip, G
+        self.grid_a = ops.tokens_to_grid(tap, B, strip, G)                      # bf16 [B*G, 768]
+        self.reduced = torch.empty(B * G, 256, device=self.dev, dtype=F32)
+        ops.gemm(self.grid_a, self.w, self.bias.detach(), L.EPI_BIAS_F32, self.reduced)
+        return ops.instnorm_f32(self.reduced.view(B, G, 256))                    # f32 [B, G, 256] = NHWC [B, gh, gw, 256]
+
+    def backward(self, dfeat):
+        B, G = self.B, self.G
+        dred = ops.instnorm_bwd_f32(self.reduced.view(B, G, 256), dfeat.reshape(B, G, 256).contiguous()).view(B * G, 256)
+        Np = (B * G + 63) // 64 * 64
+        x_t = _pad_rows(ops.transpose_bf16(self.grid_a, ldt=Np)[0])
+        dgrid, dw, db = _linear_grads(dred, x_t, self.w_t, self.zero, self.dev)
+        return ops.tokens_to_grid_bwd(dgrid, B, self.strip, G), {"weight": dw.view(256, 768, 1, 1), "bias": db}
+
+
+class _ConvBlockT:
+    """decoder.py:22-34 in train mode: ReflectionPad2d(1) + 3x3 conv + BatchNorm2d (batch statistics) + ELU, as im2col + GEMM."""
+
+    def __init__(self, sd, prefix, dev):
+        g = lambda k: sd[prefix + k]
+        self.cw, self.cb = g("conv.0.conv.1.weight"), g("conv.0.conv.1.bias")
+        self.bw, self.bb, self.rm, self.rv = g("conv.1.weight"), g("conv.1.bias"), g("conv.1.running_mean"), g("conv.1.running_var")
+        self.co, self.ci = self.cw.shape[0], self.cw.shape[1]
+        self.dev = dev
+        self.zero = torch.zeros(9 * self.ci, device=dev, dtype=F32)
+        self.repack()
+
+    def repack(self):
+        wm = self.cw.detach().permute(0, 2, 3, 1).reshape(self.co, 9 * self.ci).contiguous()  # k = (ky*3+kx)*Ci + c
+        self.wm = _pad_rows(wm.to(BF16))
+        self.wm_t = _pad_rows(ops.transpose_bf16(wm, ldt=self.co)[0])                          # [9Ci][Co]
+
+    def forward(self, x):
+        B, h, w, _ = x.shape
+        self.shape = (B, h, w)
+        col, self.colT = ops.im2col3x3(x.contiguous(), L.PAD_REFLECT)
+        self.z = torch.empty(B * h * w, self.co, device=self.dev, dtype=F32)
+        ops.gemm(col, self.wm, self.cb.detach(), L.EPI_BIAS_F32, self.z)
+        y, self.mean, self.rstd = ops.bn_elu_train_fwd(self.z, self.co, self.bw.detach(), self.bb.detach(), run_mean=self.rm, run_var=self.rv)
+        return y.view(B, h, w, self.co)
+
+    def backward(self, dy):
+        B, h, w = self.shape
+        dz, dg, db = ops.bn_elu_train_bwd(self.z, self.co, self.mean, self.rstd, self.bw.detach(), self.bb.detach(), dy.reshape(B * h * w, self.co).contiguous())
+        dxcol, dw, dcb = _linear_grads(dz, _pad_rows(self.colT), self.wm_t, self.zero, self.dev)
+        dx = ops.col2im3x3(dxcol, B, h, w, self.ci, L.PAD_REFLECT)
+        dwt = dw.view(self.co, 3, 3, self.ci).permute(0, 3, 1, 2).contiguous()
+        return dx, {"conv.0.conv.1.weight": dwt, "conv.0.conv.1.bias": dcb, "conv.1.weight": dg, "conv.1.bias": db}
+
+
+class _DispHeadT:
+    """decoder.py:86-88,166: Conv2d(C, 1, 3, padding=1) + sigmoid, times the source scale (model.py:63-92)."""
+
+    def __init__(self, weight, bias, dev):
+        self.weight, self.bias, self.dev = weight, bias, dev
+        self.ci = weight.shape[1]
+        self.zero = torch.zeros(9 * self.ci, device=dev, dtype=F32)
+        self.repack()
+
+    def repack(self):
+        wm = self.weight.detach().permute(0, 2, 3, 1).reshape(1, 9 * self.ci)
+        self.wm = _pad_rows(wm.to(BF16))                                     # [128][9Ci], row 0 real
+        wm64 = torch.zeros(64, 9 * self.ci, device=self.dev, dtype=F32)
+        wm64[0] = wm[0]
+        self.wm_t = _pad_rows(ops.transpose_bf16(wm64, ldt=64)[0])           # [9Ci][64], column 0 real
+        self.bias128 = torch.zeros(128, device=self.dev, dtype=F32)
+        self.bias128[:1] = self.bias.detach()
+
+    def forward(self, x, mul):
+        B, h, w, _ = x.shape
+        self.shape, self.mul = (B, h, w), mul
+        col, self.colT = ops.im2col3x3(x.contiguous(), L.PAD_ZERO)
+        self.z = torch.empty(B * h * w, 128, device=self.dev, dtype=F32)
+        ops.gemm(col, self.wm, self.bias128, L.EPI_BIAS_F32, self.z)
+        return ops.sigmoid_head(self.z, B * h * w, mul).view(B, h, w, 1)
+
+    def backward(self, ddisp):
+        B, h, w = self.shape
+        N = B * h * w
+        dz64 = torch.zeros(N, 64, device=self.dev, dtype=F32)
+        ops.sigmoid_head_bwd(self.z, ddisp.reshape(N).contiguous(), self.mul, out=dz64)
+        dxcol, dw, db = _linear_grads(dz64, _pad_rows(self.colT), self.wm_t, self.zero, self.dev)
+        dx = ops.col2im3x3(dxcol, B, h, w, self.ci, L.PAD_ZERO)
+        return dx, {"weight": dw[0].view(1, 3, 3, self.ci).permute(0, 3, 1, 2).contiguous(), "bias": db[:1].clone()}
+
+
+class DepthTrainer:
+    """One training step of the reference's fine-tuning loop (``train/mars_adapter.py:117-153``) for ``DepthAnything`` on the device:
+    train-mode forward of everything ``('disp', 0)`` depends on, ``compute_losses`` (:209-247), backward, Adam with the
+    reference's two learning-rate groups (:47-55).  The model's fp32 parameters and BatchNorm buffers are updated in place.
+
+    Deviations, stated once: the ``torch.rand_like`` draw of :238 is an argument; decoder levels 1-3 do not influence the loss
+    and are not run in train mode (their outputs are not returned and their BatchNorm running statistics are not advanced);
+    ``encoder.normalize.{weight,bias}`` (6 scalars in front of the patch embedding) receive no gradient yet.
+    """
+
+    def __init__(self, model, lr=1e-4, w_depth=1.0, w_smooth=0.001, betas=(0.9, 0.999), eps=1e-8):
+        self.model, self.lr, self.w_depth, self.w_smooth, self.betas, self.eps = model, lr, w_depth, w_smooth, betas, eps
+        self.dev = next(model.parameters()).device
+        if self.dev.type != "cuda":
+            raise RuntimeError("the model must live on a CUDA (sm_100) device: there is no CPU path")
+        self.sd = dict(model.state_dict(keep_vars=True))  # parameters and buffers themselves: updates land in the model
+        d = lambda k: self.sd[k].detach()
+        vit = {k[len("encoder.encoder."):]: d(k) for k in self.sd if k.startswith("encoder.encoder.")}
+        self.enc = ViTEncoderTrainer(vit)
+        self.feat = {i: _FeatureT(d(f"encoder.channel_reduce.{i}.weight"), d(f"encoder.channel_reduce.{i}.bias"), self.dev) for i in (2, 3)}
+        det = {k: d(k) for k in self.sd}
+        self.blocks = {n: _ConvBlockT(det, f"decoder.convs.{n}.", self.dev) for n in ("init_conv", "upconv_0_0", "skip_0", "upconv_0_1")}
+        self.head = _DispHeadT(d("decoder.convs.dispconv_0.weight"), d("decoder.convs.dispconv_0.bias"), self.dev)
+        self.state, self.t = {}, 0
+        self.scratch = torch.empty(L.RANGE_SCRATCH_FLOATS, device=self.dev, dtype=F32)
+        self.affine = torch.empty(6, device=self.dev, dtype=F32)
+
+    def _repack(self):
+        for b in self.enc.blocks:
+            b.repack()
+        self.enc.repack()
+        for m in list(self.feat.values()) + list(self.blocks.values()) + [self.head]:
+            m.repack()
+
+    def forward_backward(self, images, metadata, rnd):
+        """-> (losses f32 [3] on the device: total, depth, smoothness; {state_dict key: fp32 gradient})"""
+        from .engine import grid_shape
+        from .model import source_scale
+
+        sd, dev = self.sd, self.dev
+        x = images.to(F32).contiguous()
+        B, _, H0, W0 = x.shape
+        xin = x
+        if H0 % 16 or W0 % 16:  # model.py:51-54
+            xin = ops.resize_bilinear_nchw(x, (H0 // 16 + 1) * 16, (W0 // 16 + 1) * 16)
+        Hp, Wp = xin.shape[2:]
+        if Wp % 4:
+            raise ValueError("unsupported input width")
+        gh, gw, strip = grid_shape(Hp, Wp)
+        G = gh * gw
+        # encoder.py:129-144 with BatchNorm2d(3) in train mode: batch statistics, then the same one-pass input stage
+        mean, var = ops.channel_stats_nchw(xin, 0.1, sd["encoder.normalize.running_mean"].detach(), sd["encoder.normalize.running_var"].detach())
+        bn = torch.cat([sd["encoder.normalize.weight"].detach(), sd["encoder.normalize.bias"].detach(), mean, var]).contiguous()
+        raw224 = torch.empty(B, 3, 224, 224, device=dev, dtype=F32)
+        patches = torch.empty(B * 196, 768, device=dev, dtype=BF16)
+        ops.input_stage(xin, bn, 1e-5, self.scratch, self.affine, raw224, patches)
+        taps = self.enc.forward(patches)
+        f3 = self.feat[3].forward(taps[3], B, strip, G).view(B, gh, gw, 256)
+        f2 = self.feat[2].forward(taps[2], B, strip, G).view(B, gh, gw, 256)
+        blk = self.blocks
+        x0 = blk["init_conv"].forward(f3)                                   # decoder.py:103
+        x1 = blk["upconv_0_0"].forward(x0)                                  # :113
+        s0 = blk["skip_0"].forward(f2)                                      # :133 (features[-2])
+        cat = torch.empty(B, 2 * gh, 2 * gw, 256, device=dev, dtype=F32)
+        ops.bilinear_nhwc(x1, 2 * gh, 2 * gw, True, dst=cat, coff=0)        # :118-120
+        ops.bilinear_nhwc(s0, 2 * gh, 2 * gw, True, dst=cat, coff=128)      # :136-145
+        x2 = blk["upconv_0_1"].forward(cat)                                 # :152
+        sc = source_scale(metadata)
+        disp0 = self.head.forward(x2, 1.0 if sc is None else sc)            # :166 + model.py:63-92
+        disp = ops.bilinear_nhwc(disp0, H0, W0, False).view(B, 1, H0, W0)   # model.py:95-100 (C = 1: NHWC == NCHW)
+        losses, ddisp = ops.depth_loss(disp, x, rnd.to(F32).contiguous(), self.w_depth, self.w_smooth)
+        self.outputs = {("disp", 0): disp}
+        # ---------------- backward
+        g = {}
+        ddisp0 = ops.bilinear_nhwc_bwd(ddisp.view(B, H0, W0, 1), 2 * gh, 2 * gw, False)
+        dx2, gh_ = self.head.backward(ddisp0)
+        for k, v in gh_.items():
+            g[f"decoder.convs.dispconv_0.{k}"] = v
+        def back(name, dy):
+            dx, gg = blk[name].backward(dy)
+            for k, v in gg.items():
+                g[f"decoder.convs.{name}.{k}"] = v
+            return dx
+        dcat = back("upconv_0_1", dx2)
+        dx1 = ops.bilinear_nhwc_bwd(dcat, gh, gw, True, Cc=128, coff=0)
+        ds0 = ops.bilinear_nhwc_bwd(dcat, gh, gw, True, Cc=128, coff=128)
+        df3 = back("init_conv", back("upconv_0_0", dx1))
+        df2 = back("skip_0", ds0)
+        dt3, g3 = self.feat[3].backward(df3)
+        dt2, g2 = self.feat[2].backward(df2)
+        for i, gg in ((3, g3), (2, g2)):
+            for k, v in gg.items():
+                g[f"encoder.channel_reduce.{i}.{k}"] = v
+        for k, v in self.enc.backward([None, None, dt2, dt3]).items():
+            g["encoder.encoder." + k] = v
+        return losses, g
+
+    def step(self, images, metadata, rnd, grads_hook=None):
+        """forward + backward + Adam (encoder.* at lr/10, decoder.* at lr).  ``grads_hook(grads)`` runs between backward and the
+        update: the place for the gradient all-reduce of a data-parallel job.  Returns the three losses (device tensor)."""
+        losses, grads = self.forward_backward(images, metadata, rnd)
+        if grads_hook is not None:
+            grads_hook(grads)
+        self.t += 1
+        for k, gk in grads.items():
+            p = self.sd[k].detach()
+            gk = gk.reshape(p.shape).contiguous()
+            m, v = self.state.setdefault(k, (torch.zeros_like(p), torch.zeros_like(p)))
+            ops.adam_step(p, gk, m, v, self.lr / 10 if k.startswith("encoder.") else self.lr, self.t, self.betas[0], self.betas[1], self.eps)
+        self._repack()
+        return losses
