@@ -1,4 +1,4 @@
-"""Backward of the ViT encoder on the device (first part).
+"""The reference's training step on the device (BASELINE config 5).
 
 The reference's training step (``train/mars_adapter.py:131-140``) is ``model(images)`` -> ``compute_losses`` ->
 ``losses['total'].backward()`` -> ``optimizer.step()``; autograd walks torchvision's ``EncoderBlock`` (tv:110-120) twelve
@@ -8,8 +8,9 @@ block input and of the block's twelve parameter tensors under the reference's ``
 
 GEMM-shaped gradients run on the tcgen05 GEMM (``mde_gemm_bf16``) with transposed operands (``csrc/backward.cu`` has the
 transposing casts and everything that is not a GEMM).  Operands are bf16, accumulation and every parameter gradient fp32.
-Scope so far: the encoder blocks.  The decoder / loss backward, Adam and the NCCL gradient all-reduce of config 5 are the next
-pieces; ``DepthAnything.forward`` still raises in ``train()`` mode.
+``DepthTrainer`` (bottom of the file) composes the whole step: train-mode forward of the ``('disp', 0)`` path, ``compute_losses``,
+backward through decoder level 0 / features / ViT, Adam.  ``sharding.allreduce_mean_grads`` is the data-parallel hook.
+``DepthAnything.forward`` itself still raises in ``train()`` mode: training goes through ``DepthTrainer.step``.
 """
 from __future__ import annotations
 

@@ -69,3 +69,40 @@ def test_numa_binding_helpers():
     if not __import__("torch").cuda.is_available():
         assert S.bind_host_to_gpu(0) is None
         assert os.sched_getaffinity(0) == before
+
+
+def _allreduce_worker(rank, world, port, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from monodepth_estimation_b200.sharding import allreduce_mean_grads
+
+    g = torch.Generator().manual_seed(100 + rank)
+    grads = {"b.weight": torch.randn(300, 7, generator=g), "a.bias": torch.randn(5, generator=g), "c": torch.randn(1000, generator=g)}
+    calls = allreduce_mean_grads(grads, dist, bucket_bytes=4096)  # small buckets: several collectives
+    q.put((rank, calls, {k: v.clone() for k, v in grads.items()}))
+    dist.destroy_process_group()
+
+
+def test_gradient_allreduce_averages_over_ranks():
+    """world_size 2, gloo: the bucketed gradient all-reduce of the training step leaves the mean of the ranks' gradients everywhere."""
+    world, port = 2, 29631
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_allreduce_worker, args=(r, world, port, q)) for r in range(world)]
+    for p_ in procs:
+        p_.start()
+    res = sorted([q.get(timeout=120) for _ in range(world)], key=lambda t: t[0])
+    for p_ in procs:
+        p_.join(60)
+    want = {}
+    for k, shape in (("b.weight", (300, 7)), ("a.bias", (5,)), ("c", (1000,))):
+        per_rank = []
+        for r in range(world):
+            g = torch.Generator().manual_seed(100 + r)
+            d = {"b.weight": torch.randn(300, 7, generator=g), "a.bias": torch.randn(5, generator=g), "c": torch.randn(1000, generator=g)}
+            per_rank.append(d[k])
+        want[k] = sum(per_rank) / world
+    for rank, calls, got in res:
+        assert calls >= 2
+        for k in want:
+            assert torch.allclose(got[k], want[k], atol=1e-6), (rank, k)
