@@ -367,6 +367,15 @@ int mde_sigmoid_head_bwd_f32(const float* z, int ldz, const float* ddisp, long l
 int mde_channel_stats_nchw(const float* x, int B, int C, long long hw, float momentum, float* run_mean, float* run_var, float* mean, float* var,
                            mde_stream_t stream);
 
+/* Gradient of encoder.normalize.{weight,bias} (encoder.py:129-137; the six scalars in front of the patch embedding).  dpatches f32
+ * [B*196][768] = gradient of the patch rows mde_input_stage wrote (columns (c, ky, kx): dY of conv_proj times its weight), raw224 /
+ * affine6 / bn4x3 / eps as mde_input_stage saw them.  The range heuristic's scale is a Python branch in the reference (no gradient
+ * through the choice); which one was taken is read back from affine6.  dgamma_dbeta6 = (dweight[3], dbias[3]).
+ * scratch: mde_input_norm_bwd_scratch_floats(B) floats. */
+long long mde_input_norm_bwd_scratch_floats(int B);
+int mde_input_norm_bwd(const float* dpatches, const float* raw224, int B, const float* affine6, const float* bn4x3, float eps, float* scratch,
+                       float* dgamma_dbeta6, mde_stream_t stream);
+
 /* MarsDomainAdapter.compute_losses (train/mars_adapter.py:209-247) with get_smooth_loss (layers.py:202-215): disp f32 [B][H][W] (=
  * outputs[('disp',0)]), img f32 [B][3][H][W], rnd f32 [B][H][W] = the torch.rand_like draw of :238 (passed in so that both sides
  * see the same numbers).  losses3 = (total, depth, smoothness), ddisp = d total / d disp.  scratch: mde_depth_loss_scratch_floats(). */

@@ -87,11 +87,13 @@ SIGNATURES = {
     "mde_sigmoid_head_bwd_f32": [_p, _i, _p, _ll, _f, _p, _i, _p],
     "mde_channel_stats_nchw": [_p, _i, _i, _ll, _f, _p, _p, _p, _p, _p],
     "mde_depth_loss_scratch_floats": [],
+    "mde_input_norm_bwd_scratch_floats": [_i],
+    "mde_input_norm_bwd": [_p, _p, _i, _p, _p, _f, _p, _p, _p],
     "mde_depth_loss": [_p, _p, _p, _i, _i, _i, _f, _f, _p, _p, _p, _p],
     "mde_adam_step": [_p, _p, _p, _p, _ll, _f, _f, _f, _f, _i, _p],
 }
 _RESTYPES = {"mde_last_error": C.c_char_p, "mde_point_cloud_scratch_bytes": C.c_longlong, "mde_layernorm_bwd_scratch_floats": C.c_longlong,
-             "mde_depth_loss_scratch_floats": C.c_longlong}
+             "mde_depth_loss_scratch_floats": C.c_longlong, "mde_input_norm_bwd_scratch_floats": C.c_longlong}
 
 _lock = threading.Lock()
 _lib = None

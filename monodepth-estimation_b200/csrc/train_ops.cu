@@ -341,6 +341,79 @@ __global__ void __launch_bounds__(256) channel_stats_kernel(const float* __restr
   }
 }
 
+// ------------------------------------------------------------------ gradient of encoder.normalize.{weight,bias} (encoder.py:129-137)
+// The input stage is x224[c] = a_c raw224[c] + b_c with a_c = s gamma_c rstd_c, b_c = s (beta_c - mu_c gamma_c rstd_c) + t, where
+// (s, t) is one of (1,0), (1/255,0), (2,-1), (2/255,-1) chosen by the range heuristic (a Python branch in the reference: no
+// gradient through the choice) and mu / rstd are batch statistics of the INPUT (independent of the parameters).  So
+//   dgamma_c = s rstd_c (S2_c - mu_c S1_c),  dbeta_c = s S1_c,  S1_c = sum dX224[c],  S2_c = sum dX224[c] raw224[c].
+// dX224 arrives in patch layout (row = (image, patch), column = (c, ky, kx)): the output of the conv_proj dX GEMM.
+// One block per (image, patch row, channel) writes its two partial sums; the finalize block adds them in a fixed order.
+__global__ void __launch_bounds__(256) input_norm_bwd_kernel(const float* __restrict__ dpatches, const float* __restrict__ raw224, float* __restrict__ part) {
+  __shared__ float r1[256], r2[256];
+  const int c = blockIdx.x % 3, py = (blockIdx.x / 3) % 14, b = blockIdx.x / 42;
+  float s1 = 0.0f, s2 = 0.0f;
+  for (int i = threadIdx.x; i < 16 * 224; i += 256) {
+    const int ky = i / 224, X = i % 224;
+    const float d = dpatches[((size_t)b * 196 + py * 14 + (X >> 4)) * 768 + c * 256 + ky * 16 + (X & 15)];
+    const float v = raw224[(((size_t)b * 3 + c) * 224 + py * 16 + ky) * 224 + X];
+    s1 += d;
+    s2 = fmaf(d, v, s2);
+  }
+  r1[threadIdx.x] = s1;
+  r2[threadIdx.x] = s2;
+  for (int s = 128; s > 0; s >>= 1) {
+    __syncthreads();
+    if ((int)threadIdx.x < s) {
+      r1[threadIdx.x] += r1[threadIdx.x + s];
+      r2[threadIdx.x] += r2[threadIdx.x + s];
+    }
+  }
+  if (threadIdx.x == 0) {
+    part[blockIdx.x * 2] = r1[0];
+    part[blockIdx.x * 2 + 1] = r2[0];
+  }
+}
+
+__global__ void input_norm_bwd_finalize_kernel(const float* __restrict__ part, int nrows, const float* __restrict__ affine6, const float* __restrict__ bn,
+                                               float eps, float* __restrict__ dgamma_dbeta6) {
+  __shared__ double S[3][2];
+  __shared__ float rstd[3];
+  if (threadIdx.x < 3) {
+    const int c = threadIdx.x;
+    double a = 0.0, q = 0.0;
+    for (int r = 0; r < nrows; ++r) {
+      a += part[(r * 3 + c) * 2];
+      q += part[(r * 3 + c) * 2 + 1];
+    }
+    S[c][0] = a;
+    S[c][1] = q;
+    rstd[c] = 1.0f / sqrtf(bn[9 + c] + eps);
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    // which (s, t) did the forward pick?  the candidate that reproduces affine6 (no division: gamma may be 0)
+    const float cs[4] = {1.0f, 1.0f / 255.0f, 2.0f, 2.0f / 255.0f}, ct[4] = {0.0f, 0.0f, -1.0f, -1.0f};
+    int best = 0;
+    float best_err = 3.0e38f;
+    for (int k = 0; k < 4; ++k) {
+      float err = 0.0f;
+      for (int c = 0; c < 3; ++c) {
+        const float a0 = bn[c] * rstd[c], b0 = bn[3 + c] - bn[6 + c] * a0;
+        err += fabsf(cs[k] * a0 - affine6[c]) + fabsf(cs[k] * b0 + ct[k] - affine6[3 + c]);
+      }
+      if (err < best_err) {
+        best_err = err;
+        best = k;
+      }
+    }
+    const double s = cs[best];
+    for (int c = 0; c < 3; ++c) {
+      dgamma_dbeta6[c] = (float)(s * rstd[c] * (S[c][1] - (double)bn[6 + c] * S[c][0]));
+      dgamma_dbeta6[3 + c] = (float)(s * S[c][0]);
+    }
+  }
+}
+
 // ------------------------------------------------------------------ loss (mars_adapter.py:209-247, layers.py:202-215)
 // depth term: mean |disp - target|, target = disp.detach() * (0.9 + 0.2 rnd); smoothness: mean_x(|dx disp| e^{-mean_c |dx img|}) + the
 // same along y.  One pass writes per-block partial sums (fixed order) and the gradient with respect to disp.
@@ -507,6 +580,18 @@ extern "C" int mde_channel_stats_nchw(const float* x, int B, int C, long long hw
   MDE_CHECK_ARG(x && mean && var && B > 0 && C > 0 && hw > 0, "mde_channel_stats_nchw: bad arguments");
   MDE_CHECK_ARG((run_mean == nullptr) == (run_var == nullptr), "mde_channel_stats_nchw: running_mean and running_var go together");
   channel_stats_kernel<<<C, 256, 0, stream>>>(x, B, C, hw, mean, var, run_mean, run_var, momentum);
+  MDE_CHECK_LAUNCH();
+  return MDE_OK;
+}
+
+extern "C" long long mde_input_norm_bwd_scratch_floats(int B) { return (long long)B * 14 * 3 * 2; }
+
+extern "C" int mde_input_norm_bwd(const float* dpatches, const float* raw224, int B, const float* affine6, const float* bn4x3, float eps, float* scratch,
+                                  float* dgamma_dbeta6, mde_stream_t stream) {
+  MDE_CHECK_ARG(dpatches && raw224 && affine6 && bn4x3 && scratch && dgamma_dbeta6 && B > 0, "mde_input_norm_bwd: bad arguments");
+  input_norm_bwd_kernel<<<B * 42, 256, 0, stream>>>(dpatches, raw224, scratch);
+  MDE_CHECK_LAUNCH();
+  input_norm_bwd_finalize_kernel<<<1, 32, 0, stream>>>(scratch, B * 14, affine6, bn4x3, eps, dgamma_dbeta6);
   MDE_CHECK_LAUNCH();
   return MDE_OK;
 }

@@ -420,6 +420,17 @@ def channel_stats_nchw(x, momentum=0.1, run_mean=None, run_var=None):
     return mean, var
 
 
+def input_norm_bwd(dpatches, raw224, affine6, bn4x3, eps=1e-5):
+    """dpatches f32 [B*196, 768], raw224 f32 [B,3,224,224], affine6 / bn4x3 as ``input_stage`` saw them -> f32 [6] = (dweight[3], dbias[3]) of
+    ``encoder.normalize``."""
+    B = raw224.shape[0]
+    scratch = _f32(int(L.load().mde_input_norm_bwd_scratch_floats(B)), dev=raw224.device)
+    out = _f32(6, dev=raw224.device)
+    L.call("mde_input_norm_bwd", _ptr(dpatches, F32), _ptr(raw224, F32), B, _ptr(affine6, F32), _ptr(bn4x3, F32), float(eps), _ptr(scratch, F32),
+           _ptr(out, F32), _stream())
+    return out
+
+
 def depth_loss(disp, img, rnd, w_depth=1.0, w_smooth=0.001):
     """disp f32 [B,1,H,W] or [B,H,W], img f32 [B,3,H,W], rnd f32 like disp -> (losses f32 [3] = total, depth, smoothness; ddisp like disp)."""
     B, H, W = disp.shape[0], disp.shape[-2], disp.shape[-1]

@@ -151,6 +151,7 @@ class ViTEncoderTrainer:
     def repack(self):
         p = self.p
         self.patch_w = p["conv_proj.weight"].reshape(768, 768).to(BF16).contiguous()
+        self.patch_w_t, _ = ops.transpose_bf16(p["conv_proj.weight"].reshape(768, 768), ldt=768)  # [in][out]: dX operand
         self.pos = p["encoder.pos_embedding"].reshape(197, 768).contiguous()
         self.cls = p["class_token"].reshape(768).contiguous()
         self.zero768 = torch.zeros(768, device=self.dev, dtype=F32)
@@ -205,7 +206,9 @@ class ViTEncoderTrainer:
         ops.gemm(dy_t, p_t, self.zero768, L.EPI_BIAS_F32, dw)
         grads["conv_proj.weight"] = dw.view(768, 3, 16, 16)
         grads["conv_proj.bias"] = ops.colsum_bf16(dy)
-        self.dpatch_rows = dy  # bf16 [B*196, 768]: dY of conv_proj, kept for the input-stage backward (encoder.normalize)
+        # gradient of the patch rows themselves (f32 [B*196, 768], columns (c, ky, kx)): the input-stage backward (encoder.normalize) reads it
+        self.dpatches = torch.empty(B * 196, 768, device=self.dev, dtype=F32)
+        ops.gemm(dy, self.patch_w_t, self.zero768, L.EPI_BIAS_F32, self.dpatches)
         return grads
 
 
@@ -330,8 +333,7 @@ class DepthTrainer:
     reference's two learning-rate groups (:47-55).  The model's fp32 parameters and BatchNorm buffers are updated in place.
 
     Deviations, stated once: the ``torch.rand_like`` draw of :238 is an argument; decoder levels 1-3 do not influence the loss
-    and are not run in train mode (their outputs are not returned and their BatchNorm running statistics are not advanced);
-    ``encoder.normalize.{weight,bias}`` (6 scalars in front of the patch embedding) receive no gradient yet.
+    and are not run in train mode (their outputs are not returned and their BatchNorm running statistics are not advanced).
     """
 
     def __init__(self, model, lr=1e-4, w_depth=1.0, w_smooth=0.001, betas=(0.9, 0.999), eps=1e-8):
@@ -419,6 +421,8 @@ class DepthTrainer:
                 g[f"encoder.channel_reduce.{i}.{k}"] = v
         for k, v in self.enc.backward([None, None, dt2, dt3]).items():
             g["encoder.encoder." + k] = v
+        dn = ops.input_norm_bwd(self.enc.dpatches, raw224, self.affine, bn, 1e-5)                    # encoder.py:129-137
+        g["encoder.normalize.weight"], g["encoder.normalize.bias"] = dn[:3].clone(), dn[3:].clone()
         return losses, g
 
     def step(self, images, metadata, rnd, grads_hook=None):

@@ -296,6 +296,40 @@ def test_adam_step_matches_torch():
     assert max_abs(mine, p.detach()) < 5e-7  # one ulp at |p| ~ 3
 
 
+@pytest.mark.parametrize("scale255", [False, True])
+def test_input_norm_bwd_matches_autograd(scale255):
+    """encoder.py:129-137: gradient of the six BatchNorm2d(3) scalars in front of the patch embedding, through the range heuristic
+    (both branches: inputs already in [0, 1] -> 2x - 1; inputs up to 255 -> / 255 first)."""
+    L, ops = _mods()
+    B = 3
+    g = torch.Generator().manual_seed(71)
+    raw = torch.rand(B, 3, 224, 224, generator=g).cuda() * (255.0 if scale255 else 1.0)
+    mean, var = raw.mean((0, 2, 3)), raw.var((0, 2, 3), unbiased=False)
+    # weight / bias that keep the normalised values inside the branch under test
+    w = torch.tensor([0.11, 0.09, 0.1]).cuda() * (255.0 if scale255 else 1.0)
+    b = torch.tensor([0.5, 0.45, 0.55]).cuda() * (255.0 if scale255 else 1.0)
+    bn = torch.cat([w, b, mean, var]).contiguous()
+    scratch = torch.empty(L.RANGE_SCRATCH_FLOATS, device="cuda")
+    affine = torch.empty(6, device="cuda")
+    raw224 = torch.empty(B, 3, 224, 224, device="cuda")
+    patches = torch.empty(B * 196, 768, device="cuda", dtype=torch.bfloat16)
+    ops.input_stage(raw, bn, 1e-5, scratch, affine, raw224, patches)
+    dP = _rand(B * 196, 768, seed=72)
+    got = ops.input_norm_bwd(dP, raw224, affine, bn, 1e-5)
+    wt, bt = w.clone().requires_grad_(True), b.clone().requires_grad_(True)
+    y = torch.nn.functional.batch_norm(raw, None, None, wt, bt, True, 0.1, 1e-5)
+    assert (float(y.max()) > 1.0) == scale255
+    if scale255:
+        y = y / 255.0
+    assert float(y.min()) >= 0.0 and float(y.max()) <= 1.0
+    y = y * 2.0 - 1.0
+    rows = y.view(B, 3, 14, 16, 14, 16).permute(0, 2, 4, 1, 3, 5).reshape(B * 196, 768)  # (image, patch) x (c, ky, kx)
+    assert rel_l2(patches.float(), rows.detach()) < 5e-3
+    (rows * dP).sum().backward()
+    want = torch.cat([wt.grad, bt.grad])
+    assert rel_l2(got, want) < 1e-4, (got, want)
+
+
 def test_training_step_matches_train_oracle():
     """DepthTrainer (train/mars_adapter.py:117-153 on the device) against oracle/train_oracle.py — itself pinned to the real
     reference classes in train() mode (tests/test_train_oracle.py): losses, every parameter gradient, BatchNorm running
@@ -328,7 +362,7 @@ def test_training_step_matches_train_oracle():
     # the smoothness term sums |differences of neighbouring disparities|: bf16-level noise (3e-3) on a map whose neighbours differ by
     # a few per cent is amplified accordingly
     assert abs(got[2] - want_losses["smoothness"]) < 6e-2 * want_losses["smoothness"], (got, want_losses)
-    skipped = {"encoder.normalize.weight", "encoder.normalize.bias"}
+    skipped = set()
     errs = []
     for k, gw in want_grads.items():
         if k in skipped:
