@@ -302,8 +302,12 @@ int mde_bilateral_depth(const float* depth, int H, int W, const uint8_t* guide, 
 int mde_transpose_bf16(const void* src, int src_is_f32, int R, int C, int lds, mde_bf16* dst_t, int ldt, int cols_t, mde_bf16* dst_rm,
                        int ldr, mde_stream_t stream);
 
+/* Scratch of the column reductions below (mde_colsum_bf16, mde_bn_elu_train_fwd / _bwd, mde_channel_stats_nchw): per-chunk
+ * partial sums that a second kernel adds in a fixed order.  8-byte aligned, mde_reduce_scratch_bytes(C) bytes for C columns. */
+long long mde_reduce_scratch_bytes(int C);
+
 /* bias gradient of a Linear (tv:113,118): out[c] (+)= sum_r src[r][c]. */
-int mde_colsum_bf16(const mde_bf16* src, int R, int C, int lds, float* out, int accumulate, mde_stream_t stream);
+int mde_colsum_bf16(const mde_bf16* src, int R, int C, int lds, float* out, int accumulate, void* scratch, mde_stream_t stream);
 
 /* nn.GELU (exact erf, tv:118) on a bf16 buffer, and its backward du = dy * (Phi(u) + u phi(u)).  count % 8 == 0. */
 int mde_gelu_bf16(const mde_bf16* u, long long count, mde_bf16* y, mde_stream_t stream);
@@ -323,8 +327,10 @@ int mde_axpy_f32(float* y, const float* x, float a, long long n, mde_stream_t st
 
 /* Backward of mde_vit_attention (tv:113): q (pre-scaled by 1/8), k token-major bf16 [B*197][768], vt bf16 [B*12][64][208] as the
  * forward wrote them, dout bf16 [B*197][768] = gradient of the attention output.  dqkv bf16 [B*197][2304] = (dq | dk | dv) per
- * token with respect to in_proj's output (dq includes the 1/8), i.e. the dY of the in_proj gradient GEMMs. */
-int mde_vit_attention_bwd(const mde_bf16* q, const mde_bf16* k, const mde_bf16* vt, const mde_bf16* dout, int B, mde_bf16* dqkv,
+ * token with respect to in_proj's output (dq includes the 1/8), i.e. the dY of the in_proj gradient GEMMs.  q, k, dout 16-byte
+ * aligned; scratch: mde_vit_attention_bwd_scratch_floats(B) floats (the softmax row statistics between the two passes). */
+long long mde_vit_attention_bwd_scratch_floats(int B);
+int mde_vit_attention_bwd(const mde_bf16* q, const mde_bf16* k, const mde_bf16* vt, const mde_bf16* dout, int B, mde_bf16* dqkv, float* scratch,
                           mde_stream_t stream);
 
 /* ==== the rest of the training step (train/mars_adapter.py:117-153,209-247), train-mode decoder path of ('disp', 0) ====
@@ -338,11 +344,12 @@ int mde_col2im3x3_f32(const float* dxcol, int ldc, int B, int h, int w, int C, i
 
 /* nn.BatchNorm2d in train mode + nn.ELU (decoder.py:22-34) on z f32 [N][ldz] (N = B*h*w rows, C channels): batch mean / biased
  * variance -> mean, rstd (kept for the backward); y f32 [N][C] = ELU(gamma zhat + beta); running_mean / running_var updated
- * with `momentum` and the unbiased variance when given.  Backward: dy f32 [N][C] -> dz f32 [N][C], dgamma, dbeta. */
+ * with `momentum` and the unbiased variance when given.  Backward: dy f32 [N][C] -> dz f32 [N][C], dgamma, dbeta.
+ * scratch: mde_reduce_scratch_bytes(C). */
 int mde_bn_elu_train_fwd(const float* z, int N, int C, int ldz, const float* gamma, const float* beta, float eps, float momentum, float* run_mean,
-                         float* run_var, float* mean, float* rstd, float* y, mde_stream_t stream);
+                         float* run_var, float* mean, float* rstd, float* y, void* scratch, mde_stream_t stream);
 int mde_bn_elu_train_bwd(const float* z, int N, int C, int ldz, const float* mean, const float* rstd, const float* gamma, const float* beta,
-                         const float* dy, float* dz, float* dgamma, float* dbeta, mde_stream_t stream);
+                         const float* dy, float* dz, float* dgamma, float* dbeta, void* scratch, mde_stream_t stream);
 
 /* F.interpolate(mode='bilinear') on fp32 NHWC and its adjoint (decoder.py:118-142 align_corners=True; model.py:95-100
  * align_corners=False).  The destination may be a channel slice [coff, coff+C) of rows ldd wide (the concat of decoder.py:145). */
@@ -365,7 +372,7 @@ int mde_sigmoid_head_bwd_f32(const float* z, int ldz, const float* ddisp, long l
  * running statistics updated with `momentum` and the unbiased variance when given.  Passing (weight, bias, mean, var) as the
  * bn4x3 block of mde_input_stage then evaluates the train-mode forward. */
 int mde_channel_stats_nchw(const float* x, int B, int C, long long hw, float momentum, float* run_mean, float* run_var, float* mean, float* var,
-                           mde_stream_t stream);
+                           void* scratch, mde_stream_t stream);
 
 /* Gradient of encoder.normalize.{weight,bias} (encoder.py:129-137; the six scalars in front of the patch embedding).  dpatches f32
  * [B*196][768] = gradient of the patch rows mde_input_stage wrote (columns (c, ky, kx): dY of conv_proj times its weight), raw224 /
@@ -386,6 +393,10 @@ int mde_depth_loss(const float* disp, const float* img, const float* rnd, int B,
 /* torch.optim.Adam step (train/mars_adapter.py:52-55,139; defaults: no weight decay, no amsgrad) on n contiguous fp32 values. */
 int mde_adam_step(float* p, const float* g, float* m, float* v, long long n, float lr, float beta1, float beta2, float eps, int step,
                   mde_stream_t stream);
+/* The same update with the step count (>= 1) read from device memory at run time: one captured launch serves every step of a
+ * CUDA graph. */
+int mde_adam_step_dev(float* p, const float* g, float* m, float* v, long long n, float lr, float beta1, float beta2, float eps, const int* step_dev,
+                      mde_stream_t stream);
 
 #ifdef __cplusplus
 }

@@ -68,16 +68,18 @@ SIGNATURES = {
     "mde_transpose_bf16": [_p, _i, _i, _i, _i, _p, _i, _i, _p, _i, _p],
     "mde_batch_sum_f32": [_p, _i, _ll, _p, _i, _p],
     "mde_axpy_f32": [_p, _p, _f, _ll, _p],
-    "mde_colsum_bf16": [_p, _i, _i, _i, _p, _i, _p],
+    "mde_colsum_bf16": [_p, _i, _i, _i, _p, _i, _p, _p],
+    "mde_reduce_scratch_bytes": [_i],
     "mde_gelu_bf16": [_p, _ll, _p, _p],
     "mde_gelu_bwd_bf16": [_p, _p, _ll, _p, _p],
     "mde_layernorm_bwd_scratch_floats": [_i],
     "mde_layernorm_bwd": [_p, _p, _p, _i, _i, _f, _p, _p, _p, _p, _i, _p, _p],
-    "mde_vit_attention_bwd": [_p, _p, _p, _p, _i, _p, _p],
+    "mde_vit_attention_bwd": [_p, _p, _p, _p, _i, _p, _p, _p],
+    "mde_vit_attention_bwd_scratch_floats": [_i],
     "mde_im2col3x3_bf16": [_p, _i, _i, _i, _i, _i, _p, _p, _i, _p],
     "mde_col2im3x3_f32": [_p, _i, _i, _i, _i, _i, _i, _p, _p],
-    "mde_bn_elu_train_fwd": [_p, _i, _i, _i, _p, _p, _f, _f, _p, _p, _p, _p, _p, _p],
-    "mde_bn_elu_train_bwd": [_p, _i, _i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p],
+    "mde_bn_elu_train_fwd": [_p, _i, _i, _i, _p, _p, _f, _f, _p, _p, _p, _p, _p, _p, _p],
+    "mde_bn_elu_train_bwd": [_p, _i, _i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p],
     "mde_bilinear_nhwc_f32": [_p, _i, _i, _i, _i, _p, _i, _i, _i, _i, _i, _p],
     "mde_bilinear_nhwc_bwd_f32": [_p, _i, _i, _i, _i, _i, _i, _p, _i, _i, _i, _p],
     "mde_instnorm_f32": [_p, _i, _i, _i, _f, _p, _p],
@@ -85,15 +87,16 @@ SIGNATURES = {
     "mde_tokens_to_grid_bwd_f32": [_p, _i, _i, _i, _p, _p],
     "mde_sigmoid_head_f32": [_p, _i, _ll, _f, _p, _p],
     "mde_sigmoid_head_bwd_f32": [_p, _i, _p, _ll, _f, _p, _i, _p],
-    "mde_channel_stats_nchw": [_p, _i, _i, _ll, _f, _p, _p, _p, _p, _p],
+    "mde_channel_stats_nchw": [_p, _i, _i, _ll, _f, _p, _p, _p, _p, _p, _p],
     "mde_depth_loss_scratch_floats": [],
     "mde_input_norm_bwd_scratch_floats": [_i],
     "mde_input_norm_bwd": [_p, _p, _i, _p, _p, _f, _p, _p, _p],
     "mde_depth_loss": [_p, _p, _p, _i, _i, _i, _f, _f, _p, _p, _p, _p],
     "mde_adam_step": [_p, _p, _p, _p, _ll, _f, _f, _f, _f, _i, _p],
+    "mde_adam_step_dev": [_p, _p, _p, _p, _ll, _f, _f, _f, _f, _p, _p],
 }
 _RESTYPES = {"mde_last_error": C.c_char_p, "mde_point_cloud_scratch_bytes": C.c_longlong, "mde_layernorm_bwd_scratch_floats": C.c_longlong,
-             "mde_depth_loss_scratch_floats": C.c_longlong, "mde_input_norm_bwd_scratch_floats": C.c_longlong}
+             "mde_depth_loss_scratch_floats": C.c_longlong, "mde_input_norm_bwd_scratch_floats": C.c_longlong, "mde_reduce_scratch_bytes": C.c_longlong, "mde_vit_attention_bwd_scratch_floats": C.c_longlong}
 
 _lock = threading.Lock()
 _lib = None

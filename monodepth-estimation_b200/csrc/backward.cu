@@ -49,21 +49,30 @@ __global__ void __launch_bounds__(256) transpose_pad_kernel(const TIn* __restric
 }
 
 // ------------------------------------------------------------------ bias gradient: out[c] = sum_r src[r][c]
-// One block per 32 columns; warp w adds rows w, w+8, ... (fixed order), the eight partials are added in warp order.
-__global__ void __launch_bounds__(256) colsum_kernel(const bf16* __restrict__ src, int R, int C, int lds, float* __restrict__ out, int accumulate) {
-  __shared__ float part[8][32];
+// Grid (C/32, row chunks); warp w of a block adds rows w, w+8, ... of its chunk (fixed order), the eight partials are added in
+// warp order, the finalize kernel adds the chunks in chunk order.
+__global__ void __launch_bounds__(256) colsum_kernel(const bf16* __restrict__ src, int R, int C, int lds, float* __restrict__ part) {
+  __shared__ float sp[8][32];
   const int c = blockIdx.x * 32 + (threadIdx.x & 31), w = threadIdx.x >> 5;
+  const int per = (R + gridDim.y - 1) / gridDim.y, r0 = blockIdx.y * per, r1 = min(R, r0 + per);
   float s = 0.0f;
   if (c < C)
-    for (int r = w; r < R; r += 8) s += __bfloat162float(src[(size_t)r * lds + c]);
-  part[w][threadIdx.x & 31] = s;
+    for (int r = r0 + w; r < r1; r += 8) s += __bfloat162float(src[(size_t)r * lds + c]);
+  sp[w][threadIdx.x & 31] = s;
   __syncthreads();
   if (w == 0 && c < C) {
     float t = 0.0f;
 #pragma unroll
-    for (int k = 0; k < 8; ++k) t += part[k][threadIdx.x & 31];
-    out[c] = accumulate ? out[c] + t : t;
+    for (int k = 0; k < 8; ++k) t += sp[k][threadIdx.x & 31];
+    part[(size_t)blockIdx.y * C + c] = t;
   }
+}
+__global__ void __launch_bounds__(256) colsum_finalize_kernel(const float* __restrict__ part, int chunks, int C, float* __restrict__ out, int accumulate) {
+  const int c = blockIdx.x * 256 + threadIdx.x;
+  if (c >= C) return;
+  float t = 0.0f;
+  for (int k = 0; k < chunks; ++k) t += part[(size_t)k * C + c];
+  out[c] = accumulate ? out[c] + t : t;
 }
 
 // ------------------------------------------------------------------ exact-erf GELU (tv:118 nn.GELU) forward / backward, bf16
@@ -189,159 +198,183 @@ __global__ void __launch_bounds__(256) ln_bwd_finalize_kernel(const float* __res
 }
 
 // ------------------------------------------------------------------ ViT attention backward (tv:113, 12 heads x 64, S = 197)
-// One block per (image, head).  q (pre-scaled by 1/8, as the QKV epilogue stores it), k: token-major [B*197][768]; vt: [B*12][64][208];
-// dout: gradient of the attention output, token-major [B*197][768].  Writes dqkv [B*197][2304] = (dq | dk | dv) per token, dq with
-// respect to the UNscaled q (what in_proj produced), so it is the A operand of the in_proj gradient GEMMs as is.
+// q (pre-scaled by 1/8, as the QKV epilogue stores it), k: token-major [B*197][768]; vt: [B*12][64][208]; dout: gradient of the
+// attention output, token-major [B*197][768].  Writes dqkv [B*197][2304] = (dq | dk | dv) per token, dq with respect to the
+// UNscaled q (what in_proj produced), so it is the A operand of the in_proj gradient GEMMs as is.
 //   P = softmax(q_s k^T);  dV = P^T dO;  dP = dO V^T;  dS = P o (dP - rowsum(P o dP));  dq = dS k / 8;  dk = dS^T q_s
-// Pass 1, warp per query row: row statistics (max, 1/sum, D = rowsum(P o dP)) and dq.  Pass 2, warp per key row: P and dS of
-// that column recomputed from the statistics, dk and dv.  Shared-memory rows are 33 words apart: lane = row reads are
-// conflict-free, lane = word reads are contiguous.
+// Two launches over a grid (image x head, row chunk).  Pass 1, warp per query row (K and V of the slab in shared memory): row
+// statistics (max, 1/sum, D = rowsum(P o dP)) -> `stats`, and dq.  Pass 2, warp per key row (Q and dO in shared memory): P and
+// dS of that column recomputed from the statistics, dk and dv.  Shared-memory rows are 33 words apart: lane = row reads are
+// conflict-free, lane = word reads are contiguous.  A row's arithmetic does not depend on the chunking.
 constexpr int kAbS = MDE_VIT_SEQ;
 constexpr int kAbLd = 33;  // words (bf16 pairs) per row: 32 + 1 pad
 constexpr int kAbT = (kAbS + 31) / 32;  // 7 row groups per lane
-constexpr int kAbSmem = 4 * kAbS * kAbLd * 4 + 3 * kAbS * 4 + 8 * 2 * 224 * 4;
+constexpr int kAbSmem = 2 * kAbS * kAbLd * 4 + 3 * kAbS * 4 + 8 * 2 * 224 * 4;  // 69 KB; registers allow two blocks per SM
 
 __device__ __forceinline__ float dot2(uint32_t a, uint32_t b, float acc) {
   const __nv_bfloat162 x = *reinterpret_cast<const __nv_bfloat162*>(&a), y = *reinterpret_cast<const __nv_bfloat162*>(&b);
   return fmaf(__high2float(x), __high2float(y), fmaf(__low2float(x), __low2float(y), acc));
 }
+// one 64-wide bf16 row (128 bytes, 16-byte aligned) into 32 registers of every lane (broadcast loads)
+__device__ __forceinline__ void load_row32(const bf16* __restrict__ p, uint32_t (&r)[32]) {
+  const uint4* v = reinterpret_cast<const uint4*>(p);
+#pragma unroll
+  for (int w = 0; w < 8; ++w) {
+    const uint4 t = __ldg(v + w);
+    r[4 * w] = t.x;
+    r[4 * w + 1] = t.y;
+    r[4 * w + 2] = t.z;
+    r[4 * w + 3] = t.w;
+  }
+}
 
-__global__ void __launch_bounds__(256) vit_attn_bwd_kernel(const bf16* __restrict__ q, const bf16* __restrict__ k, const bf16* __restrict__ vt,
-                                                           const bf16* __restrict__ dout, bf16* __restrict__ dqkv) {
+template <int PASS>
+__global__ void __launch_bounds__(256, 2) vit_attn_bwd_kernel(const bf16* __restrict__ q, const bf16* __restrict__ k, const bf16* __restrict__ vt,
+                                                              const bf16* __restrict__ dout, float* __restrict__ stats, bf16* __restrict__ dqkv) {
   extern __shared__ uint32_t sm[];
-  uint32_t* sQ = sm;
-  uint32_t* sK = sQ + kAbS * kAbLd;
-  uint32_t* sV = sK + kAbS * kAbLd;
-  uint32_t* sG = sV + kAbS * kAbLd;  // dO
-  float* sMax = reinterpret_cast<float*>(sG + kAbS * kAbLd);
+  uint32_t* sA = sm;                   // pass 1: K          pass 2: Q
+  uint32_t* sB = sA + kAbS * kAbLd;    // pass 1: V          pass 2: dO
+  float* sMax = reinterpret_cast<float*>(sB + kAbS * kAbLd);
   float* sInv = sMax + kAbS;
   float* sD = sInv + kAbS;
   float* sRow = sD + kAbS;  // [8 warps][2][224]
   const int slab = blockIdx.x, b = slab / MDE_VIT_HEADS, hd = slab - b * MDE_VIT_HEADS;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const size_t tok0 = (size_t)b * kAbS;
-  for (int i = tid; i < kAbS * 32; i += 256) {
-    const int r = i >> 5, w = i & 31;
-    const size_t off = (tok0 + r) * MDE_VIT_DIM + hd * 64 + 2 * w;
-    sQ[r * kAbLd + w] = *reinterpret_cast<const uint32_t*>(q + off);
-    sK[r * kAbLd + w] = *reinterpret_cast<const uint32_t*>(k + off);
-    sG[r * kAbLd + w] = *reinterpret_cast<const uint32_t*>(dout + off);
-  }
-  {  // V^T [64][208] -> sV[token][d]
-    const bf16* vb = vt + (size_t)slab * 64 * MDE_VT_PITCH;
-    bf16* sVh = reinterpret_cast<bf16*>(sV);
-    for (int i = tid; i < 64 * kAbS; i += 256) {
-      const int d = i / kAbS, t = i - d * kAbS;
-      sVh[t * (2 * kAbLd) + d] = vb[(size_t)d * MDE_VT_PITCH + t];
+  const int per = (kAbS + gridDim.y - 1) / gridDim.y, lo = blockIdx.y * per, hi = min(kAbS, lo + per);
+  const bf16* vb = vt + (size_t)slab * 64 * MDE_VT_PITCH;
+  float* st = stats + (size_t)slab * 3 * kAbS;
+  {
+    const bf16* a = PASS == 1 ? k : q;
+    for (int i = tid; i < kAbS * 32; i += 256) {
+      const int r = i >> 5, w = i & 31;
+      const size_t off = (tok0 + r) * MDE_VIT_DIM + hd * 64 + 2 * w;
+      sA[r * kAbLd + w] = *reinterpret_cast<const uint32_t*>(a + off);
+      if (PASS == 2) sB[r * kAbLd + w] = *reinterpret_cast<const uint32_t*>(dout + off);
+    }
+    if (PASS == 1) {  // V^T [64][208] -> sB[token][d]
+      bf16* sVh = reinterpret_cast<bf16*>(sB);
+      for (int i = tid; i < 64 * kAbS; i += 256) {
+        const int d = i / kAbS, t = i - d * kAbS;
+        sVh[t * (2 * kAbLd) + d] = vb[(size_t)d * MDE_VT_PITCH + t];
+      }
+    } else {
+      for (int i = tid; i < kAbS; i += 256) {
+        sMax[i] = st[i];
+        sInv[i] = st[kAbS + i];
+        sD[i] = st[2 * kAbS + i];
+      }
     }
   }
   __syncthreads();
   float* rowA = sRow + warp * 2 * 224;
   float* rowB = rowA + 224;
 
-  // ---- pass 1: query rows
-  for (int i = warp; i < kAbS; i += 8) {
-    uint32_t qi[32], gi[32];
+  if (PASS == 1) {  // ---- query rows
+    const uint32_t* sK = sA;
+    const uint32_t* sV = sB;
+    for (int i = lo + warp; i < hi; i += 8) {
+      uint32_t qi[32], gi[32];
+      load_row32(q + (tok0 + i) * MDE_VIT_DIM + hd * 64, qi);
+      load_row32(dout + (tok0 + i) * MDE_VIT_DIM + hd * 64, gi);
+      float s[kAbT], dp[kAbT];
+      float mx = -INFINITY;
 #pragma unroll
-    for (int w = 0; w < 32; ++w) {
-      qi[w] = sQ[i * kAbLd + w];  // broadcast reads
-      gi[w] = sG[i * kAbLd + w];
-    }
-    float s[kAbT], dp[kAbT];
-    float mx = -INFINITY;
+      for (int t = 0; t < kAbT; ++t) {
+        const int j = lane + 32 * t;
+        s[t] = -INFINITY;
+        dp[t] = 0.0f;
+        if (j < kAbS) {
+          float a = 0.0f, c = 0.0f;
 #pragma unroll
-    for (int t = 0; t < kAbT; ++t) {
-      const int j = lane + 32 * t;
-      s[t] = -INFINITY;
-      dp[t] = 0.0f;
-      if (j < kAbS) {
-        float a = 0.0f, c = 0.0f;
-#pragma unroll
-        for (int w = 0; w < 32; ++w) {
-          a = dot2(qi[w], sK[j * kAbLd + w], a);
-          c = dot2(gi[w], sV[j * kAbLd + w], c);
+          for (int w = 0; w < 32; ++w) {
+            a = dot2(qi[w], sK[j * kAbLd + w], a);
+            c = dot2(gi[w], sV[j * kAbLd + w], c);
+          }
+          s[t] = a;
+          dp[t] = c;
+          mx = fmaxf(mx, a);
         }
-        s[t] = a;
-        dp[t] = c;
-        mx = fmaxf(mx, a);
       }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+      float sum = 0.0f;
+#pragma unroll
+      for (int t = 0; t < kAbT; ++t) {
+        s[t] = (lane + 32 * t < kAbS) ? __expf(s[t] - mx) : 0.0f;
+        sum += s[t];
+      }
+      const float inv = 1.0f / warp_sum(sum);
+      float dd = 0.0f;
+#pragma unroll
+      for (int t = 0; t < kAbT; ++t) {
+        s[t] *= inv;
+        dd = fmaf(s[t], dp[t], dd);
+      }
+      dd = warp_sum(dd);
+      if (lane == 0) {
+        st[i] = mx;
+        st[kAbS + i] = inv;
+        st[2 * kAbS + i] = dd;
+      }
+#pragma unroll
+      for (int t = 0; t < kAbT; ++t)
+        if (lane + 32 * t < kAbS) rowA[lane + 32 * t] = s[t] * (dp[t] - dd);  // dS
+      __syncwarp();
+      float a0 = 0.0f, a1 = 0.0f;  // dq[2*lane], dq[2*lane+1]
+      for (int j = 0; j < kAbS; ++j) {
+        const float ds = rowA[j];
+        const uint32_t kw = sK[j * kAbLd + lane];
+        const __nv_bfloat162 kk = *reinterpret_cast<const __nv_bfloat162*>(&kw);
+        a0 = fmaf(ds, __low2float(kk), a0);
+        a1 = fmaf(ds, __high2float(kk), a1);
+      }
+      *reinterpret_cast<uint32_t*>(dqkv + (tok0 + i) * (3 * MDE_VIT_DIM) + hd * 64 + 2 * lane) = pack_bf16x2(a0 * 0.125f, a1 * 0.125f);
+      __syncwarp();
     }
+  } else {  // ---- key rows
+    const uint32_t* sQ = sA;
+    const uint32_t* sG = sB;
+    for (int j = lo + warp; j < hi; j += 8) {
+      uint32_t kj[32], vj[32];
+      load_row32(k + (tok0 + j) * MDE_VIT_DIM + hd * 64, kj);
+      {  // V row j out of the transposed slab: lane l fetches dims 2l, 2l+1, then 32 broadcasts
+        const uint32_t mine = (uint32_t)__bfloat16_as_ushort(vb[(size_t)(2 * lane) * MDE_VT_PITCH + j]) |
+                              ((uint32_t)__bfloat16_as_ushort(vb[(size_t)(2 * lane + 1) * MDE_VT_PITCH + j]) << 16);
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-    float sum = 0.0f;
+        for (int w = 0; w < 32; ++w) vj[w] = __shfl_sync(0xffffffffu, mine, w);
+      }
 #pragma unroll
-    for (int t = 0; t < kAbT; ++t) {
-      s[t] = (lane + 32 * t < kAbS) ? __expf(s[t] - mx) : 0.0f;
-      sum += s[t];
-    }
-    const float inv = 1.0f / warp_sum(sum);
-    float dd = 0.0f;
+      for (int t = 0; t < kAbT; ++t) {
+        const int i = lane + 32 * t;
+        if (i < kAbS) {
+          float a = 0.0f, c = 0.0f;
 #pragma unroll
-    for (int t = 0; t < kAbT; ++t) {
-      s[t] *= inv;
-      dd = fmaf(s[t], dp[t], dd);
-    }
-    dd = warp_sum(dd);
-    if (lane == 0) {
-      sMax[i] = mx;
-      sInv[i] = inv;
-      sD[i] = dd;
-    }
-#pragma unroll
-    for (int t = 0; t < kAbT; ++t)
-      if (lane + 32 * t < kAbS) rowA[lane + 32 * t] = s[t] * (dp[t] - dd);  // dS
-    __syncwarp();
-    float a0 = 0.0f, a1 = 0.0f;  // dq[2*lane], dq[2*lane+1]
-    for (int j = 0; j < kAbS; ++j) {
-      const float ds = rowA[j];
-      const uint32_t kw = sK[j * kAbLd + lane];
-      const __nv_bfloat162 kk = *reinterpret_cast<const __nv_bfloat162*>(&kw);
-      a0 = fmaf(ds, __low2float(kk), a0);
-      a1 = fmaf(ds, __high2float(kk), a1);
-    }
-    *reinterpret_cast<uint32_t*>(dqkv + (tok0 + i) * (3 * MDE_VIT_DIM) + hd * 64 + 2 * lane) = pack_bf16x2(a0 * 0.125f, a1 * 0.125f);
-    __syncwarp();
-  }
-  __syncthreads();
-
-  // ---- pass 2: key rows
-  for (int j = warp; j < kAbS; j += 8) {
-    uint32_t kj[32], vj[32];
-#pragma unroll
-    for (int w = 0; w < 32; ++w) {
-      kj[w] = sK[j * kAbLd + w];
-      vj[w] = sV[j * kAbLd + w];
-    }
-#pragma unroll
-    for (int t = 0; t < kAbT; ++t) {
-      const int i = lane + 32 * t;
-      if (i < kAbS) {
-        float a = 0.0f, c = 0.0f;
-#pragma unroll
-        for (int w = 0; w < 32; ++w) {
-          a = dot2(kj[w], sQ[i * kAbLd + w], a);
-          c = dot2(vj[w], sG[i * kAbLd + w], c);
+          for (int w = 0; w < 32; ++w) {
+            a = dot2(kj[w], sQ[i * kAbLd + w], a);
+            c = dot2(vj[w], sG[i * kAbLd + w], c);
+          }
+          const float p = __expf(a - sMax[i]) * sInv[i];
+          rowA[i] = p;
+          rowB[i] = p * (c - sD[i]);
         }
-        const float p = __expf(a - sMax[i]) * sInv[i];
-        rowA[i] = p;
-        rowB[i] = p * (c - sD[i]);
       }
+      __syncwarp();
+      float k0 = 0.0f, k1 = 0.0f, v0 = 0.0f, v1 = 0.0f;
+      for (int i = 0; i < kAbS; ++i) {
+        const float p = rowA[i], ds = rowB[i];
+        const uint32_t qw = sQ[i * kAbLd + lane], gw = sG[i * kAbLd + lane];
+        const __nv_bfloat162 qq = *reinterpret_cast<const __nv_bfloat162*>(&qw), gg = *reinterpret_cast<const __nv_bfloat162*>(&gw);
+        k0 = fmaf(ds, __low2float(qq), k0);
+        k1 = fmaf(ds, __high2float(qq), k1);
+        v0 = fmaf(p, __low2float(gg), v0);
+        v1 = fmaf(p, __high2float(gg), v1);
+      }
+      bf16* dst = dqkv + (tok0 + j) * (3 * MDE_VIT_DIM) + hd * 64 + 2 * lane;
+      *reinterpret_cast<uint32_t*>(dst + MDE_VIT_DIM) = pack_bf16x2(k0, k1);
+      *reinterpret_cast<uint32_t*>(dst + 2 * MDE_VIT_DIM) = pack_bf16x2(v0, v1);
+      __syncwarp();
     }
-    __syncwarp();
-    float k0 = 0.0f, k1 = 0.0f, v0 = 0.0f, v1 = 0.0f;
-    for (int i = 0; i < kAbS; ++i) {
-      const float p = rowA[i], ds = rowB[i];
-      const uint32_t qw = sQ[i * kAbLd + lane], gw = sG[i * kAbLd + lane];
-      const __nv_bfloat162 qq = *reinterpret_cast<const __nv_bfloat162*>(&qw), gg = *reinterpret_cast<const __nv_bfloat162*>(&gw);
-      k0 = fmaf(ds, __low2float(qq), k0);
-      k1 = fmaf(ds, __high2float(qq), k1);
-      v0 = fmaf(p, __low2float(gg), v0);
-      v1 = fmaf(p, __high2float(gg), v1);
-    }
-    bf16* dst = dqkv + (tok0 + j) * (3 * MDE_VIT_DIM) + hd * 64 + 2 * lane;
-    *reinterpret_cast<uint32_t*>(dst + MDE_VIT_DIM) = pack_bf16x2(k0, k1);
-    *reinterpret_cast<uint32_t*>(dst + 2 * MDE_VIT_DIM) = pack_bf16x2(v0, v1);
-    __syncwarp();
   }
 }
 
@@ -384,9 +417,13 @@ extern "C" int mde_transpose_bf16(const void* src, int src_is_f32, int R, int C,
   return MDE_OK;
 }
 
-extern "C" int mde_colsum_bf16(const mde_bf16* src, int R, int C, int lds, float* out, int accumulate, mde_stream_t stream) {
-  MDE_CHECK_ARG(src && out && R > 0 && C > 0 && lds >= C, "mde_colsum_bf16: bad arguments");
-  colsum_kernel<<<ceil_div(C, 32), 256, 0, stream>>>(reinterpret_cast<const bf16*>(src), R, C, lds, out, accumulate);
+extern "C" int mde_colsum_bf16(const mde_bf16* src, int R, int C, int lds, float* out, int accumulate, void* scratch, mde_stream_t stream) {
+  MDE_CHECK_ARG(src && out && scratch && R > 0 && C > 0 && lds >= C, "mde_colsum_bf16: bad arguments");
+  int chunks = ceil_div(R, 128);
+  if (chunks > 64) chunks = 64;  // mde_reduce_scratch_bytes(C) holds 64 chunks
+  colsum_kernel<<<dim3(ceil_div(C, 32), chunks), 256, 0, stream>>>(reinterpret_cast<const bf16*>(src), R, C, lds, static_cast<float*>(scratch));
+  MDE_CHECK_LAUNCH();
+  colsum_finalize_kernel<<<ceil_div(C, 256), 256, 0, stream>>>(static_cast<const float*>(scratch), chunks, C, out, accumulate);
   MDE_CHECK_LAUNCH();
   return MDE_OK;
 }
@@ -424,18 +461,29 @@ extern "C" int mde_layernorm_bwd(const float* x, const mde_bf16* dy, const float
   return MDE_OK;
 }
 
-extern "C" int mde_vit_attention_bwd(const mde_bf16* q, const mde_bf16* k, const mde_bf16* vt, const mde_bf16* dout, int B, mde_bf16* dqkv,
+extern "C" long long mde_vit_attention_bwd_scratch_floats(int B) { return (long long)(B > 0 ? B : 0) * MDE_VIT_HEADS * 3 * kAbS; }
+
+extern "C" int mde_vit_attention_bwd(const mde_bf16* q, const mde_bf16* k, const mde_bf16* vt, const mde_bf16* dout, int B, mde_bf16* dqkv, float* scratch,
                                      mde_stream_t stream) {
-  MDE_CHECK_ARG(q && k && vt && dout && dqkv && B > 0, "mde_vit_attention_bwd: bad arguments");
-  MDE_CHECK_ARG(((uintptr_t)q | (uintptr_t)k | (uintptr_t)dout | (uintptr_t)dqkv) % 4 == 0, "mde_vit_attention_bwd: pointers must be 4-byte aligned");
+  MDE_CHECK_ARG(q && k && vt && dout && dqkv && scratch && B > 0, "mde_vit_attention_bwd: bad arguments");
+  MDE_CHECK_ARG(((uintptr_t)q | (uintptr_t)k | (uintptr_t)dout) % 16 == 0 && (uintptr_t)dqkv % 4 == 0, "mde_vit_attention_bwd: q, k, dout must be 16-byte aligned");
   static bool attr = false;
   if (!attr) {
-    MDE_CHECK_CUDA(cudaFuncSetAttribute(vit_attn_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kAbSmem));
+    MDE_CHECK_CUDA(cudaFuncSetAttribute(vit_attn_bwd_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kAbSmem));
+    MDE_CHECK_CUDA(cudaFuncSetAttribute(vit_attn_bwd_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kAbSmem));
     attr = true;
   }
-  vit_attn_bwd_kernel<<<B * MDE_VIT_HEADS, 256, kAbSmem, stream>>>(reinterpret_cast<const bf16*>(q), reinterpret_cast<const bf16*>(k),
-                                                                   reinterpret_cast<const bf16*>(vt), reinterpret_cast<const bf16*>(dout),
-                                                                   reinterpret_cast<bf16*>(dqkv));
+  // row chunks so that the grid is at most one resident wave (two blocks per SM), at least 16 rows (two per warp) each
+  const int slabs = B * MDE_VIT_HEADS;
+  int chunks = 2 * sm_count() / slabs;
+  if (chunks > 12) chunks = 12;
+  if (chunks < 1) chunks = 1;
+  const dim3 grid(slabs, chunks);
+  const bf16 *qq = reinterpret_cast<const bf16*>(q), *kk = reinterpret_cast<const bf16*>(k), *vv = reinterpret_cast<const bf16*>(vt),
+             *gg = reinterpret_cast<const bf16*>(dout);
+  vit_attn_bwd_kernel<1><<<grid, 256, kAbSmem, stream>>>(qq, kk, vv, gg, scratch, reinterpret_cast<bf16*>(dqkv));
+  MDE_CHECK_LAUNCH();
+  vit_attn_bwd_kernel<2><<<grid, 256, kAbSmem, stream>>>(qq, kk, vv, gg, scratch, reinterpret_cast<bf16*>(dqkv));
   MDE_CHECK_LAUNCH();
   return MDE_OK;
 }

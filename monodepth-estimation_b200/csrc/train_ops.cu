@@ -82,44 +82,53 @@ __global__ void __launch_bounds__(256) col2im_kernel(const float* __restrict__ d
 }
 
 // ------------------------------------------------------------------ BatchNorm2d in train mode + ELU (decoder.py:22-34)
-// z f32 [N][C].  stats: per channel mean and 1/sqrt(biased var + eps) over the N rows (two passes: mean, then centred squares);
-// running statistics updated as nn.BatchNorm2d does (momentum, UNBIASED variance).  One block per 32 channels.
-__global__ void __launch_bounds__(256) bn_stats_kernel(const float* __restrict__ z, int N, int C, int ldz, float eps, float* __restrict__ mean, float* __restrict__ rstd,
-                                                       float* __restrict__ run_mean, float* __restrict__ run_var, float momentum) {
-  __shared__ float part[8][32];
-  __shared__ float smean[32];
+// z f32 [N][C].  stats: per channel mean and 1/sqrt(biased var + eps) over the N rows; running statistics updated as
+// nn.BatchNorm2d does (momentum, UNBIASED variance).  Grid (C/32, row chunks): every thread adds its rows in double, the block's
+// eight warps are added in warp order, the finalize kernel adds the chunks in chunk order (deterministic).
+constexpr int kRedChunks = 64;
+static inline int red_chunks(long long rows, int rows_per_chunk_min) {
+  long long c = (rows + rows_per_chunk_min - 1) / rows_per_chunk_min;
+  return (int)(c < 1 ? 1 : (c > kRedChunks ? kRedChunks : c));
+}
+__global__ void __launch_bounds__(256) bn_stats_partial_kernel(const float* __restrict__ z, int N, int C, int ldz, double* __restrict__ part) {
+  __shared__ double p1[8][32], p2[8][32];
   const int l = threadIdx.x & 31, wq = threadIdx.x >> 5, c = blockIdx.x * 32 + l;
-  float s = 0.0f;
+  const int per = (N + gridDim.y - 1) / gridDim.y, r0 = blockIdx.y * per, r1 = min(N, r0 + per);
+  double a = 0.0, q = 0.0;
   if (c < C)
-    for (int r = wq; r < N; r += 8) s += z[(size_t)r * ldz + c];
-  part[wq][l] = s;
-  __syncthreads();
-  if (wq == 0) {
-    float t = 0.0f;
-    for (int k = 0; k < 8; ++k) t += part[k][l];
-    smean[l] = t / (float)N;
-  }
-  __syncthreads();
-  const float m = smean[l];
-  s = 0.0f;
-  if (c < C)
-    for (int r = wq; r < N; r += 8) {
-      const float d = z[(size_t)r * ldz + c] - m;
-      s = fmaf(d, d, s);
+    for (int r = r0 + wq; r < r1; r += 8) {
+      const double v = z[(size_t)r * ldz + c];
+      a += v;
+      q += v * v;
     }
-  __syncthreads();
-  part[wq][l] = s;
+  p1[wq][l] = a;
+  p2[wq][l] = q;
   __syncthreads();
   if (wq == 0 && c < C) {
-    float t = 0.0f;
-    for (int k = 0; k < 8; ++k) t += part[k][l];
-    const float var = t / (float)N;
-    mean[c] = m;
-    rstd[c] = 1.0f / sqrtf(var + eps);
-    if (run_mean) {
-      run_mean[c] = (1.0f - momentum) * run_mean[c] + momentum * m;
-      run_var[c] = (1.0f - momentum) * run_var[c] + momentum * (N > 1 ? t / (float)(N - 1) : var);
+    double ta = 0.0, tq = 0.0;
+    for (int k = 0; k < 8; ++k) {
+      ta += p1[k][l];
+      tq += p2[k][l];
     }
+    part[((size_t)blockIdx.y * C + c) * 2] = ta;
+    part[((size_t)blockIdx.y * C + c) * 2 + 1] = tq;
+  }
+}
+__global__ void __launch_bounds__(256) bn_stats_finalize_kernel(const double* __restrict__ part, int chunks, int N, int C, float eps, float* __restrict__ mean,
+                                                                float* __restrict__ rstd, float* __restrict__ run_mean, float* __restrict__ run_var, float momentum) {
+  const int c = blockIdx.x * 256 + threadIdx.x;
+  if (c >= C) return;
+  double a = 0.0, q = 0.0;
+  for (int k = 0; k < chunks; ++k) {
+    a += part[((size_t)k * C + c) * 2];
+    q += part[((size_t)k * C + c) * 2 + 1];
+  }
+  const double m = a / N, var = fmax(q / N - m * m, 0.0);
+  mean[c] = (float)m;
+  rstd[c] = (float)(1.0 / sqrt(var + (double)eps));
+  if (run_mean) {
+    run_mean[c] = (1.0f - momentum) * run_mean[c] + momentum * (float)m;
+    run_var[c] = (1.0f - momentum) * run_var[c] + momentum * (float)(N > 1 ? var * N / (N - 1.0) : var);
   }
 }
 __global__ void __launch_bounds__(256) bn_elu_apply_kernel(const float* __restrict__ z, long long N, int C, int ldz, const float* __restrict__ mean,
@@ -135,13 +144,14 @@ __global__ void __launch_bounds__(256) bn_elu_apply_kernel(const float* __restri
 // backward: da = dy * ELU'(a); dbeta = sum da; dgamma = sum da zhat; dz = gamma rstd (da - dbeta/N - zhat dgamma/N)
 __global__ void __launch_bounds__(256) bn_elu_bwd_reduce_kernel(const float* __restrict__ z, int N, int C, int ldz, const float* __restrict__ mean,
                                                                 const float* __restrict__ rstd, const float* __restrict__ gamma, const float* __restrict__ beta,
-                                                                const float* __restrict__ dy, float* __restrict__ dgamma, float* __restrict__ dbeta) {
+                                                                const float* __restrict__ dy, double* __restrict__ part) {
   __shared__ float pg[8][32], pb[8][32];
   const int l = threadIdx.x & 31, wq = threadIdx.x >> 5, c = blockIdx.x * 32 + l;
+  const int per = (N + gridDim.y - 1) / gridDim.y, r0 = blockIdx.y * per, r1 = min(N, r0 + per);
   float sg = 0.0f, sb = 0.0f;
   if (c < C) {
     const float m = mean[c], rs = rstd[c], g = gamma[c], be = beta[c];
-    for (int r = wq; r < N; r += 8) {
+    for (int r = r0 + wq; r < r1; r += 8) {
       const float zh = (z[(size_t)r * ldz + c] - m) * rs;
       const float a = fmaf(zh, g, be);
       const float da = dy[(size_t)r * C + c] * (a > 0.0f ? 1.0f : expf(a));
@@ -153,14 +163,25 @@ __global__ void __launch_bounds__(256) bn_elu_bwd_reduce_kernel(const float* __r
   pb[wq][l] = sb;
   __syncthreads();
   if (wq == 0 && c < C) {
-    float tg = 0.0f, tb = 0.0f;
+    double tg = 0.0, tb = 0.0;
     for (int k = 0; k < 8; ++k) {
       tg += pg[k][l];
       tb += pb[k][l];
     }
-    dgamma[c] = tg;
-    dbeta[c] = tb;
+    part[((size_t)blockIdx.y * C + c) * 2] = tg;
+    part[((size_t)blockIdx.y * C + c) * 2 + 1] = tb;
   }
+}
+__global__ void __launch_bounds__(256) bn_elu_bwd_finalize_kernel(const double* __restrict__ part, int chunks, int C, float* __restrict__ dgamma, float* __restrict__ dbeta) {
+  const int c = blockIdx.x * 256 + threadIdx.x;
+  if (c >= C) return;
+  double g = 0.0, b = 0.0;
+  for (int k = 0; k < chunks; ++k) {
+    g += part[((size_t)k * C + c) * 2];
+    b += part[((size_t)k * C + c) * 2 + 1];
+  }
+  dgamma[c] = (float)g;
+  dbeta[c] = (float)b;
 }
 __global__ void __launch_bounds__(256) bn_elu_bwd_apply_kernel(const float* __restrict__ z, long long N, int C, int ldz, const float* __restrict__ mean,
                                                                const float* __restrict__ rstd, const float* __restrict__ gamma, const float* __restrict__ beta,
@@ -307,15 +328,16 @@ __global__ void __launch_bounds__(256) sigmoid_bwd_kernel(const float* __restric
 }
 
 // ------------------------------------------------------------------ BatchNorm2d(3) of encoder.py:129 in train mode: batch statistics of an NCHW image batch
-// One block per channel; every thread accumulates in double over a fixed stride, the 256 partials are added in thread order.
-__global__ void __launch_bounds__(256) channel_stats_kernel(const float* __restrict__ x, int B, int C, long long hw, float* __restrict__ mean, float* __restrict__ var,
-                                                            float* __restrict__ run_mean, float* __restrict__ run_var, float momentum) {
+// Grid (C, chunks of the plane): every thread accumulates in double over a fixed stride, the 256 partials of a block are added in
+// thread order, the finalize kernel adds the chunks in chunk order.
+__global__ void __launch_bounds__(256) channel_stats_partial_kernel(const float* __restrict__ x, int B, int C, long long hw, double* __restrict__ part) {
   __shared__ double s1[256], s2[256];
   const int c = blockIdx.x;
+  const long long per = (hw + gridDim.y - 1) / gridDim.y, lo = blockIdx.y * per, hi = lo + per < hw ? lo + per : hw;
   double a = 0.0, q = 0.0;
   for (int b = 0; b < B; ++b) {
     const float* p = x + ((size_t)b * C + c) * hw;
-    for (long long i = threadIdx.x; i < hw; i += 256) {
+    for (long long i = lo + threadIdx.x; i < hi; i += 256) {
       const double v = p[i];
       a += v;
       q += v * v;
@@ -330,14 +352,26 @@ __global__ void __launch_bounds__(256) channel_stats_kernel(const float* __restr
       ta += s1[k];
       tq += s2[k];
     }
-    const double n = (double)B * (double)hw, m = ta / n;
-    const double vb = fmax(tq / n - m * m, 0.0);
-    mean[c] = (float)m;
-    var[c] = (float)vb;
-    if (run_mean) {
-      run_mean[c] = (1.0f - momentum) * run_mean[c] + momentum * (float)m;
-      run_var[c] = (1.0f - momentum) * run_var[c] + momentum * (float)(n > 1.0 ? vb * n / (n - 1.0) : vb);
-    }
+    part[((size_t)c * gridDim.y + blockIdx.y) * 2] = ta;
+    part[((size_t)c * gridDim.y + blockIdx.y) * 2 + 1] = tq;
+  }
+}
+__global__ void channel_stats_finalize_kernel(const double* __restrict__ part, int chunks, int B, int C, long long hw, float* __restrict__ mean, float* __restrict__ var,
+                                              float* __restrict__ run_mean, float* __restrict__ run_var, float momentum) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  double ta = 0.0, tq = 0.0;
+  for (int k = 0; k < chunks; ++k) {
+    ta += part[((size_t)c * chunks + k) * 2];
+    tq += part[((size_t)c * chunks + k) * 2 + 1];
+  }
+  const double n = (double)B * (double)hw, m = ta / n;
+  const double vb = fmax(tq / n - m * m, 0.0);
+  mean[c] = (float)m;
+  var[c] = (float)vb;
+  if (run_mean) {
+    run_mean[c] = (1.0f - momentum) * run_mean[c] + momentum * (float)m;
+    run_var[c] = (1.0f - momentum) * run_var[c] + momentum * (float)(n > 1.0 ? vb * n / (n - 1.0) : vb);
   }
 }
 
@@ -460,13 +494,25 @@ __global__ void __launch_bounds__(256) depth_loss_kernel(const float* __restrict
     part[(size_t)blockIdx.x * 3 + threadIdx.x] = t;
   }
 }
-__global__ void depth_loss_finalize_kernel(const float* __restrict__ part, int nblocks, int B, int H, int W, float w_depth, float w_smooth, float* __restrict__ out) {
-  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+__global__ void __launch_bounds__(256) depth_loss_finalize_kernel(const float* __restrict__ part, int nblocks, int B, int H, int W, float w_depth, float w_smooth,
+                                                                  float* __restrict__ out) {
+  __shared__ double r[3][256];
   double d = 0.0, sx = 0.0, sy = 0.0;
-  for (int i = 0; i < nblocks; ++i) {
+  for (int i = threadIdx.x; i < nblocks; i += 256) {  // fixed assignment, then the 256 partials in thread order
     d += part[(size_t)i * 3];
     sx += part[(size_t)i * 3 + 1];
     sy += part[(size_t)i * 3 + 2];
+  }
+  r[0][threadIdx.x] = d;
+  r[1][threadIdx.x] = sx;
+  r[2][threadIdx.x] = sy;
+  __syncthreads();
+  if (threadIdx.x != 0) return;
+  d = sx = sy = 0.0;
+  for (int k = 0; k < 256; ++k) {
+    d += r[0][k];
+    sx += r[1][k];
+    sy += r[2][k];
   }
   const double depth = w_depth * d / ((double)B * H * W);
   const double smooth = w_smooth * (sx / ((double)B * H * (W - 1)) + sy / ((double)B * (H - 1) * W));
@@ -476,8 +522,15 @@ __global__ void depth_loss_finalize_kernel(const float* __restrict__ part, int n
 }
 
 // ------------------------------------------------------------------ Adam (torch.optim.Adam defaults: no weight decay, no amsgrad)
+// step_dev != nullptr: the step count lives on the device (a CUDA graph replays the same launch every step) and the bias
+// corrections are evaluated here; otherwise they arrive as arguments.
 __global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v, long long n,
-                                                   float lr, float b1, float b2, float eps, float bc1, float bc2_sqrt) {
+                                                   float lr, float b1, float b2, float eps, float bc1, float bc2_sqrt, const int* __restrict__ step_dev) {
+  if (step_dev) {
+    const float t = (float)*step_dev;
+    bc1 = 1.0f - powf(b1, t);
+    bc2_sqrt = sqrtf(1.0f - powf(b2, t));
+  }
   MDE_GRID_STRIDE(i, n) {
     const float gi = g[i];
     const float mi = fmaf(b1, m[i], (1.0f - b1) * gi);   // exp_avg.lerp_(grad, 1 - beta1)
@@ -510,11 +563,17 @@ extern "C" int mde_col2im3x3_f32(const float* dxcol, int ldc, int B, int h, int 
   return MDE_OK;
 }
 
+extern "C" long long mde_reduce_scratch_bytes(int C) { return (long long)kRedChunks * (C > 0 ? C : 1) * 2 * (long long)sizeof(double); }
+
 extern "C" int mde_bn_elu_train_fwd(const float* z, int N, int C, int ldz, const float* gamma, const float* beta, float eps, float momentum, float* run_mean,
-                                    float* run_var, float* mean, float* rstd, float* y, mde_stream_t stream) {
-  MDE_CHECK_ARG(z && gamma && beta && mean && rstd && y && N > 0 && C > 0 && ldz >= C, "mde_bn_elu_train_fwd: bad arguments");
+                                    float* run_var, float* mean, float* rstd, float* y, void* scratch, mde_stream_t stream) {
+  MDE_CHECK_ARG(z && gamma && beta && mean && rstd && y && scratch && N > 0 && C > 0 && ldz >= C, "mde_bn_elu_train_fwd: bad arguments");
   MDE_CHECK_ARG((run_mean == nullptr) == (run_var == nullptr), "mde_bn_elu_train_fwd: running_mean and running_var go together");
-  bn_stats_kernel<<<ceil_div(C, 32), 256, 0, stream>>>(z, N, C, ldz, eps, mean, rstd, run_mean, run_var, momentum);
+  MDE_CHECK_ARG((uintptr_t)scratch % 8 == 0, "mde_bn_elu_train_fwd: scratch must be 8-byte aligned");
+  const int chunks = red_chunks(N, 64);
+  bn_stats_partial_kernel<<<dim3(ceil_div(C, 32), chunks), 256, 0, stream>>>(z, N, C, ldz, static_cast<double*>(scratch));
+  MDE_CHECK_LAUNCH();
+  bn_stats_finalize_kernel<<<ceil_div(C, 256), 256, 0, stream>>>(static_cast<const double*>(scratch), chunks, N, C, eps, mean, rstd, run_mean, run_var, momentum);
   MDE_CHECK_LAUNCH();
   bn_elu_apply_kernel<<<grid1((long long)N * C), 256, 0, stream>>>(z, N, C, ldz, mean, rstd, gamma, beta, y);
   MDE_CHECK_LAUNCH();
@@ -522,9 +581,13 @@ extern "C" int mde_bn_elu_train_fwd(const float* z, int N, int C, int ldz, const
 }
 
 extern "C" int mde_bn_elu_train_bwd(const float* z, int N, int C, int ldz, const float* mean, const float* rstd, const float* gamma, const float* beta,
-                                    const float* dy, float* dz, float* dgamma, float* dbeta, mde_stream_t stream) {
-  MDE_CHECK_ARG(z && mean && rstd && gamma && beta && dy && dz && dgamma && dbeta && N > 0 && C > 0 && ldz >= C, "mde_bn_elu_train_bwd: bad arguments");
-  bn_elu_bwd_reduce_kernel<<<ceil_div(C, 32), 256, 0, stream>>>(z, N, C, ldz, mean, rstd, gamma, beta, dy, dgamma, dbeta);
+                                    const float* dy, float* dz, float* dgamma, float* dbeta, void* scratch, mde_stream_t stream) {
+  MDE_CHECK_ARG(z && mean && rstd && gamma && beta && dy && dz && dgamma && dbeta && scratch && N > 0 && C > 0 && ldz >= C, "mde_bn_elu_train_bwd: bad arguments");
+  MDE_CHECK_ARG((uintptr_t)scratch % 8 == 0, "mde_bn_elu_train_bwd: scratch must be 8-byte aligned");
+  const int chunks = red_chunks(N, 64);
+  bn_elu_bwd_reduce_kernel<<<dim3(ceil_div(C, 32), chunks), 256, 0, stream>>>(z, N, C, ldz, mean, rstd, gamma, beta, dy, static_cast<double*>(scratch));
+  MDE_CHECK_LAUNCH();
+  bn_elu_bwd_finalize_kernel<<<ceil_div(C, 256), 256, 0, stream>>>(static_cast<const double*>(scratch), chunks, C, dgamma, dbeta);
   MDE_CHECK_LAUNCH();
   bn_elu_bwd_apply_kernel<<<grid1((long long)N * C), 256, 0, stream>>>(z, N, C, ldz, mean, rstd, gamma, beta, dy, dgamma, dbeta, dz);
   MDE_CHECK_LAUNCH();
@@ -576,10 +639,14 @@ extern "C" int mde_sigmoid_head_f32(const float* z, int ldz, long long n, float 
 }
 
 extern "C" int mde_channel_stats_nchw(const float* x, int B, int C, long long hw, float momentum, float* run_mean, float* run_var, float* mean, float* var,
-                                      mde_stream_t stream) {
-  MDE_CHECK_ARG(x && mean && var && B > 0 && C > 0 && hw > 0, "mde_channel_stats_nchw: bad arguments");
+                                      void* scratch, mde_stream_t stream) {
+  MDE_CHECK_ARG(x && mean && var && scratch && B > 0 && C > 0 && hw > 0, "mde_channel_stats_nchw: bad arguments");
   MDE_CHECK_ARG((run_mean == nullptr) == (run_var == nullptr), "mde_channel_stats_nchw: running_mean and running_var go together");
-  channel_stats_kernel<<<C, 256, 0, stream>>>(x, B, C, hw, mean, var, run_mean, run_var, momentum);
+  MDE_CHECK_ARG((uintptr_t)scratch % 8 == 0, "mde_channel_stats_nchw: scratch must be 8-byte aligned");
+  const int chunks = red_chunks(hw, 4096);
+  channel_stats_partial_kernel<<<dim3(C, chunks), 256, 0, stream>>>(x, B, C, hw, static_cast<double*>(scratch));
+  MDE_CHECK_LAUNCH();
+  channel_stats_finalize_kernel<<<ceil_div(C, 64), 64, 0, stream>>>(static_cast<const double*>(scratch), chunks, B, C, hw, mean, var, run_mean, run_var, momentum);
   MDE_CHECK_LAUNCH();
   return MDE_OK;
 }
@@ -611,7 +678,7 @@ extern "C" int mde_depth_loss(const float* disp, const float* img, const float* 
   const int nb = grid1((long long)B * H * W);
   depth_loss_kernel<<<nb, 256, 0, stream>>>(disp, img, rnd, B, H, W, w_depth, w_smooth, scratch, ddisp);
   MDE_CHECK_LAUNCH();
-  depth_loss_finalize_kernel<<<1, 32, 0, stream>>>(scratch, nb, B, H, W, w_depth, w_smooth, losses3);
+  depth_loss_finalize_kernel<<<1, 256, 0, stream>>>(scratch, nb, B, H, W, w_depth, w_smooth, losses3);
   MDE_CHECK_LAUNCH();
   return MDE_OK;
 }
@@ -620,7 +687,15 @@ extern "C" int mde_adam_step(float* p, const float* g, float* m, float* v, long 
                              mde_stream_t stream) {
   MDE_CHECK_ARG(p && g && m && v && n > 0 && step >= 1, "mde_adam_step: bad arguments");
   const float bc1 = 1.0f - powf(beta1, (float)step), bc2 = 1.0f - powf(beta2, (float)step);
-  adam_kernel<<<grid1(n), 256, 0, stream>>>(p, g, m, v, n, lr, beta1, beta2, eps, bc1, sqrtf(bc2));
+  adam_kernel<<<grid1(n), 256, 0, stream>>>(p, g, m, v, n, lr, beta1, beta2, eps, bc1, sqrtf(bc2), nullptr);
+  MDE_CHECK_LAUNCH();
+  return MDE_OK;
+}
+
+extern "C" int mde_adam_step_dev(float* p, const float* g, float* m, float* v, long long n, float lr, float beta1, float beta2, float eps, const int* step_dev,
+                                 mde_stream_t stream) {
+  MDE_CHECK_ARG(p && g && m && v && n > 0 && step_dev, "mde_adam_step_dev: bad arguments");
+  adam_kernel<<<grid1(n), 256, 0, stream>>>(p, g, m, v, n, lr, beta1, beta2, eps, 1.0f, 1.0f, step_dev);
   MDE_CHECK_LAUNCH();
   return MDE_OK;
 }

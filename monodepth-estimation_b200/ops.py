@@ -285,10 +285,15 @@ def axpy_f32(y, x, a=1.0):
     return y
 
 
+def _reduce_scratch(Cc, dev):
+    """per-chunk partial sums of the two-stage column reductions (8-byte aligned: float64 storage)"""
+    return torch.empty(int(L.load().mde_reduce_scratch_bytes(int(Cc))) // 8, device=dev, dtype=torch.float64)
+
+
 def colsum_bf16(src, out=None, accumulate=False):
     R, Cc = src.shape
     out = out if out is not None else torch.empty(Cc, device=src.device, dtype=F32)
-    L.call("mde_colsum_bf16", _ptr(src, BF16), R, Cc, src.stride(0), _ptr(out, F32), int(accumulate), _stream())
+    L.call("mde_colsum_bf16", _ptr(src, BF16), R, Cc, src.stride(0), _ptr(out, F32), int(accumulate), _ptr(_reduce_scratch(Cc, src.device)), _stream())
     return out
 
 
@@ -318,7 +323,8 @@ def layernorm_bwd(x, dy, gamma, eps, dres=None, dgamma=None, dbeta=None, accumul
 
 def vit_attention_bwd(q, k, vt, dout, B, out=None):
     out = out if out is not None else torch.empty(B * L.VIT_SEQ, 3 * L.VIT_DIM, device=q.device, dtype=BF16)
-    L.call("mde_vit_attention_bwd", _ptr(q, BF16), _ptr(k, BF16), _ptr(vt, BF16), _ptr(dout, BF16), B, _ptr(out, BF16), _stream())
+    scratch = torch.empty(int(L.load().mde_vit_attention_bwd_scratch_floats(B)), device=q.device, dtype=F32)
+    L.call("mde_vit_attention_bwd", _ptr(q, BF16), _ptr(k, BF16), _ptr(vt, BF16), _ptr(dout, BF16), B, _ptr(out, BF16), _ptr(scratch, F32), _stream())
     return out
 
 
@@ -350,7 +356,7 @@ def bn_elu_train_fwd(z, Cc, gamma, beta, eps=1e-5, momentum=0.1, run_mean=None, 
     mean, rstd, y = _f32(Cc, dev=z.device), _f32(Cc, dev=z.device), _f32(N, Cc, dev=z.device)
     L.call("mde_bn_elu_train_fwd", _ptr(z, F32), N, Cc, ldz, _ptr(gamma, F32), _ptr(beta, F32), float(eps), float(momentum),
            _ptr(run_mean, F32) if run_mean is not None else _ptr(None), _ptr(run_var, F32) if run_var is not None else _ptr(None),
-           _ptr(mean, F32), _ptr(rstd, F32), _ptr(y, F32), _stream())
+           _ptr(mean, F32), _ptr(rstd, F32), _ptr(y, F32), _ptr(_reduce_scratch(Cc, z.device)), _stream())
     return y, mean, rstd
 
 
@@ -358,7 +364,7 @@ def bn_elu_train_bwd(z, Cc, mean, rstd, gamma, beta, dy):
     N, ldz = z.shape
     dz, dg, db = _f32(N, Cc, dev=z.device), _f32(Cc, dev=z.device), _f32(Cc, dev=z.device)
     L.call("mde_bn_elu_train_bwd", _ptr(z, F32), N, Cc, ldz, _ptr(mean, F32), _ptr(rstd, F32), _ptr(gamma, F32), _ptr(beta, F32), _ptr(dy, F32),
-           _ptr(dz, F32), _ptr(dg, F32), _ptr(db, F32), _stream())
+           _ptr(dz, F32), _ptr(dg, F32), _ptr(db, F32), _ptr(_reduce_scratch(Cc, z.device)), _stream())
     return dz, dg, db
 
 
@@ -416,7 +422,7 @@ def channel_stats_nchw(x, momentum=0.1, run_mean=None, run_var=None):
     B, Cc, H, W = x.shape
     mean, var = _f32(Cc, dev=x.device), _f32(Cc, dev=x.device)
     L.call("mde_channel_stats_nchw", _ptr(x, F32), B, Cc, H * W, float(momentum), _ptr(run_mean, F32) if run_mean is not None else _ptr(None),
-           _ptr(run_var, F32) if run_var is not None else _ptr(None), _ptr(mean, F32), _ptr(var, F32), _stream())
+           _ptr(run_var, F32) if run_var is not None else _ptr(None), _ptr(mean, F32), _ptr(var, F32), _ptr(_reduce_scratch(Cc, x.device)), _stream())
     return mean, var
 
 
@@ -442,6 +448,11 @@ def depth_loss(disp, img, rnd, w_depth=1.0, w_smooth=0.001):
 
 
 def adam_step(p, g, m, v, lr, step, beta1=0.9, beta2=0.999, eps=1e-8):
-    L.call("mde_adam_step", _ptr(p, F32), _ptr(g, F32), _ptr(m, F32), _ptr(v, F32), p.numel(), float(lr), float(beta1), float(beta2), float(eps), int(step),
-           _stream())
+    """``step``: int, or an int32 device tensor holding the step count (read at run time: CUDA-graph replays)."""
+    if torch.is_tensor(step):
+        L.call("mde_adam_step_dev", _ptr(p, F32), _ptr(g, F32), _ptr(m, F32), _ptr(v, F32), p.numel(), float(lr), float(beta1), float(beta2), float(eps),
+               _ptr(step, torch.int32), _stream())
+    else:
+        L.call("mde_adam_step", _ptr(p, F32), _ptr(g, F32), _ptr(m, F32), _ptr(v, F32), p.numel(), float(lr), float(beta1), float(beta2), float(eps), int(step),
+               _stream())
     return p

@@ -336,8 +336,9 @@ class DepthTrainer:
     and are not run in train mode (their outputs are not returned and their BatchNorm running statistics are not advanced).
     """
 
-    def __init__(self, model, lr=1e-4, w_depth=1.0, w_smooth=0.001, betas=(0.9, 0.999), eps=1e-8):
+    def __init__(self, model, lr=1e-4, w_depth=1.0, w_smooth=0.001, betas=(0.9, 0.999), eps=1e-8, graph=True):
         self.model, self.lr, self.w_depth, self.w_smooth, self.betas, self.eps = model, lr, w_depth, w_smooth, betas, eps
+        self.graph, self._graphs = graph, {}
         self.dev = next(model.parameters()).device
         if self.dev.type != "cuda":
             raise RuntimeError("the model must live on a CUDA (sm_100) device: there is no CPU path")
@@ -350,6 +351,7 @@ class DepthTrainer:
         self.blocks = {n: _ConvBlockT(det, f"decoder.convs.{n}.", self.dev) for n in ("init_conv", "upconv_0_0", "skip_0", "upconv_0_1")}
         self.head = _DispHeadT(d("decoder.convs.dispconv_0.weight"), d("decoder.convs.dispconv_0.bias"), self.dev)
         self.state, self.t = {}, 0
+        self.step_dev = torch.zeros(1, device=self.dev, dtype=torch.int32)  # Adam's step count where a replayed graph can read it
         self.scratch = torch.empty(L.RANGE_SCRATCH_FLOATS, device=self.dev, dtype=F32)
         self.affine = torch.empty(6, device=self.dev, dtype=F32)
 
@@ -366,6 +368,7 @@ class DepthTrainer:
         from .model import source_scale
 
         sd, dev = self.sd, self.dev
+        self._repack()  # bf16 operand copies of the current fp32 master parameters
         x = images.to(F32).contiguous()
         B, _, H0, W0 = x.shape
         xin = x
@@ -425,17 +428,60 @@ class DepthTrainer:
         g["encoder.normalize.weight"], g["encoder.normalize.bias"] = dn[:3].clone(), dn[3:].clone()
         return losses, g
 
-    def step(self, images, metadata, rnd, grads_hook=None):
-        """forward + backward + Adam (encoder.* at lr/10, decoder.* at lr).  ``grads_hook(grads)`` runs between backward and the
-        update: the place for the gradient all-reduce of a data-parallel job.  Returns the three losses (device tensor)."""
-        losses, grads = self.forward_backward(images, metadata, rnd)
-        if grads_hook is not None:
-            grads_hook(grads)
-        self.t += 1
+    def _adam(self, grads):
+        """torch.optim.Adam over the reference's two groups (train/mars_adapter.py:47-55): encoder.* at lr/10, decoder.* at lr."""
+        self.step_dev += 1
         for k, gk in grads.items():
             p = self.sd[k].detach()
-            gk = gk.reshape(p.shape).contiguous()
-            m, v = self.state.setdefault(k, (torch.zeros_like(p), torch.zeros_like(p)))
-            ops.adam_step(p, gk, m, v, self.lr / 10 if k.startswith("encoder.") else self.lr, self.t, self.betas[0], self.betas[1], self.eps)
-        self._repack()
-        return losses
+            m, v = self.state[k]
+            ops.adam_step(p, gk.reshape(p.shape).contiguous(), m, v, self.lr / 10 if k.startswith("encoder.") else self.lr, self.step_dev, self.betas[0],
+                          self.betas[1], self.eps)
+
+    def _adam_state(self, grads):
+        for k in grads:
+            if k not in self.state:
+                p = self.sd[k].detach()
+                self.state[k] = (torch.zeros_like(p), torch.zeros_like(p))
+
+    def step(self, images, metadata, rnd, grads_hook=None):
+        """forward + backward + Adam (encoder.* at lr/10, decoder.* at lr).  ``grads_hook(grads)`` runs between backward and the
+        update: the place for the gradient all-reduce of a data-parallel job.  Returns the three losses (device tensor; with
+        ``graph=True`` a buffer the next step overwrites).
+
+        ``graph=True`` (default): the first step of an input shape runs eagerly (one-time initialisation inside the library must
+        not happen under capture); the second captures two CUDA graphs — [re-pack bf16 operands, forward, loss, backward] and
+        [Adam] — and every step from then on is two graph launches around the hook."""
+        from .model import source_scale
+
+        self.t += 1
+        key = (tuple(images.shape), source_scale(metadata))
+        st = self._graphs.get(key) if self.graph else None
+        if st is None:
+            losses, grads = self.forward_backward(images, metadata, rnd)
+            if grads_hook is not None:
+                grads_hook(grads)
+            self._adam_state(grads)
+            self._adam(grads)
+            if self.graph:
+                self._graphs[key] = {}
+            return losses
+        if not st:
+            st["x"], st["rnd"] = torch.empty_like(images, dtype=F32), torch.empty_like(rnd, dtype=F32)
+            st["x"].copy_(images)
+            st["rnd"].copy_(rnd)
+            torch.cuda.synchronize(self.dev)
+            st["fb"] = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(st["fb"]):
+                st["losses"], st["grads"] = self.forward_backward(st["x"], metadata, st["rnd"])
+            self._adam_state(st["grads"])
+            st["adam"] = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(st["adam"]):
+                self._adam(st["grads"])
+        else:
+            st["x"].copy_(images)
+            st["rnd"].copy_(rnd)
+        st["fb"].replay()
+        if grads_hook is not None:
+            grads_hook(st["grads"])
+        st["adam"].replay()
+        return st["losses"]

@@ -398,3 +398,36 @@ def test_training_step_matches_train_oracle():
         assert bad < 0.03, (k, bad)
     untouched = "decoder.convs.upconv_3_1.conv.0.conv.1.weight"  # no gradient reaches levels 1-3: Adam leaves them alone
     assert torch.equal(after[untouched], before[untouched])
+
+
+def test_graph_captured_steps_equal_eager_steps():
+    """DepthTrainer(graph=True) replays two CUDA graphs per step from the third step on; every kernel is deterministic, so four
+    steps (eager, capture, replay, replay) must leave exactly the parameters, Adam moments and running statistics of four eager
+    steps, with different images each step."""
+    import monodepth_estimation_b200 as mde
+    from monodepth_estimation_b200.synth import synth_images, synth_state_dict
+    from monodepth_estimation_b200.training import DepthTrainer
+
+    B, H, W = 2, 176, 240
+    md = {"source": "rover"}
+    results = []
+    for graph in (False, True):
+        m = mde.DepthAnything(pretrained=False)
+        m.load_state_dict(synth_state_dict(m.state_dict(), 0))
+        m = m.cuda()
+        tr = DepthTrainer(m, lr=1e-3, graph=graph)
+        losses = []
+        for i in range(4):
+            x = synth_images(B, H, W, 30 + i).cuda()
+            rnd = torch.rand(B, 1, H, W, generator=torch.Generator().manual_seed(40 + i)).cuda()
+            losses.append(tr.step(x, md, rnd).clone())
+        torch.cuda.synchronize()
+        results.append(({k: v.detach().clone() for k, v in m.state_dict().items()}, torch.stack(losses), tr))
+    (sd_e, l_e, tr_e), (sd_g, l_g, tr_g) = results
+    assert torch.equal(l_e, l_g), (l_e, l_g)
+    assert float((l_e[0] - l_e[3]).abs().max()) > 0  # the steps did something
+    for k in sd_e:
+        assert torch.equal(sd_e[k], sd_g[k]), k
+    assert int(tr_e.step_dev) == int(tr_g.step_dev) == 4
+    for k in tr_e.state:
+        assert torch.equal(tr_e.state[k][1], tr_g.state[k][1]), k

@@ -35,6 +35,7 @@ def main():
     ap.add_argument("--batch", type=int, default=8)
     ap.add_argument("--size", type=int, default=518)
     ap.add_argument("--cpu-steps", type=int, default=1)
+    ap.add_argument("--no-graph", action="store_true", help="eager launches every step (for a per-kernel launch list under ncu)")
     a = ap.parse_args()
     rank, world, local = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
@@ -49,7 +50,7 @@ def main():
     sd0 = synth_state_dict(m.state_dict(), 0)
     m.load_state_dict(sd0)
     m = m.to(dev)
-    tr = DepthTrainer(m, lr=1e-4)
+    tr = DepthTrainer(m, lr=1e-4, graph=not a.no_graph)
     x = synth_images(B, S, S, 77 + rank).to(dev)
     rnd = torch.rand(B, 1, S, S, generator=torch.Generator().manual_seed(5 + rank)).to(dev)
     hook = (lambda g: allreduce_mean_grads(g, dist)) if dist is not None else None
@@ -75,7 +76,8 @@ def main():
     line = {"metric": "train_images_per_sec", "value": round(world * B * a.steps / t, 1), "unit": "images/s", "n_gpus": world, "steps": a.steps,
             "warmup": a.warmup, "ms_per_step": round(t / a.steps * 1e3, 3), "higher_is_better": True, "scaling": "weak", "dtype": "bf16", "data": "synthetic",
             "config": {"workload": f"fine-tuning step (forward + backward + gradient all-reduce + Adam), batch {B}/GPU, 3x{S}x{S} (BASELINE.json configs[4])",
-                       "global_batch": B * world, "collective": "bucketed fp32 gradient all-reduce over NCCL" if world > 1 else "none (one rank)"},
+                       "global_batch": B * world, "collective": "bucketed fp32 gradient all-reduce over NCCL" if world > 1 else "none (one rank)",
+                       "launch": "eager" if a.no_graph else "two CUDA graphs per step (forward+backward, Adam) around the all-reduce"},
             "losses_last_step": [round(float(v), 6) for v in losses.cpu()]}
     if rank == 0 and world == 1 and a.cpu_steps > 0:
         from oracle import train_oracle as T
