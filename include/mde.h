@@ -327,7 +327,7 @@ int mde_axpy_f32(float* y, const float* x, float a, long long n, mde_stream_t st
 
 /* Backward of mde_vit_attention (tv:113): q (pre-scaled by 1/8), k token-major bf16 [B*197][768], vt bf16 [B*12][64][208] as the
  * forward wrote them, dout bf16 [B*197][768] = gradient of the attention output.  dqkv bf16 [B*197][2304] = (dq | dk | dv) per
- * token with respect to in_proj's output (dq includes the 1/8), i.e. the dY of the in_proj gradient GEMMs.  q, k, dout 16-byte
+ * token with respect to in_proj's output (dq includes the 1/8), i.e. the dY of the in_proj gradient GEMMs.  q, k, vt, dout 16-byte
  * aligned; scratch: mde_vit_attention_bwd_scratch_floats(B) floats (the softmax row statistics between the two passes). */
 long long mde_vit_attention_bwd_scratch_floats(int B);
 int mde_vit_attention_bwd(const mde_bf16* q, const mde_bf16* k, const mde_bf16* vt, const mde_bf16* dout, int B, mde_bf16* dqkv, float* scratch,

@@ -118,7 +118,7 @@ __global__ void __launch_bounds__(256) gelu_bwd_kernel(const bf16* __restrict__ 
 // rows), reduces the eight warps through shared memory in warp order and writes ONE partial row per block; ln_bwd_finalize
 // adds the block partials in block order.  Deterministic.
 constexpr int kLnDim = 768;
-constexpr int kLnRowsPerBlock = 64;  // 8 warps x 8 rows
+constexpr int kLnRowsPerBlock = 16;  // 8 warps x 2 rows: ~100 blocks for the 1576 token rows of a batch of 8
 __global__ void __launch_bounds__(256) ln_bwd_kernel(const float* __restrict__ x, const bf16* __restrict__ dy, const float* __restrict__ gamma, int rows,
                                                      float eps, const float* __restrict__ dres, float* __restrict__ dx, float* __restrict__ part) {
   __shared__ float red[8][kLnDim];
@@ -129,7 +129,7 @@ __global__ void __launch_bounds__(256) ln_bwd_kernel(const float* __restrict__ x
   float gm[24];
 #pragma unroll
   for (int k = 0; k < 24; ++k) gm[k] = gamma[k * 32 + lane];
-  for (int rr = 0; rr < 8; ++rr) {
+  for (int rr = 0; rr < kLnRowsPerBlock / 8; ++rr) {
     const int row = blockIdx.x * kLnRowsPerBlock + rr * 8 + warp;
     if (row >= rows) break;
     const float* xr = x + (size_t)row * kLnDim;
@@ -202,178 +202,287 @@ __global__ void __launch_bounds__(256) ln_bwd_finalize_kernel(const float* __res
 // attention output, token-major [B*197][768].  Writes dqkv [B*197][2304] = (dq | dk | dv) per token, dq with respect to the
 // UNscaled q (what in_proj produced), so it is the A operand of the in_proj gradient GEMMs as is.
 //   P = softmax(q_s k^T);  dV = P^T dO;  dP = dO V^T;  dS = P o (dP - rowsum(P o dP));  dq = dS k / 8;  dk = dS^T q_s
-// Two launches over a grid (image x head, row chunk).  Pass 1, warp per query row (K and V of the slab in shared memory): row
-// statistics (max, 1/sum, D = rowsum(P o dP)) -> `stats`, and dq.  Pass 2, warp per key row (Q and dO in shared memory): P and
-// dS of that column recomputed from the statistics, dk and dv.  Shared-memory rows are 33 words apart: lane = row reads are
-// conflict-free, lane = word reads are contiguous.  A row's arithmetic does not depend on the chunking.
+// Warp-level tensor-core MMAs (mma.sync m16n8k16, bf16 operands, fp32 accumulation; 197 tokens do not fill a tcgen05 tile and
+// the products chain through registers).  Two launches over a grid (image x head, 4 row tiles of 16):
+//   pass 1, a warp owns 16 query rows (K and V^T of the slab in shared memory): S, the softmax statistics (max, 1/sum) and
+//           D = rowsum(P o dP) -> `stats`; dS as the A operand straight out of the accumulators; dq = dS K.
+//   pass 2, a warp owns 16 key rows (Q and dO in shared memory): S^T and dP^T per 16-query step, P^T and dS^T rebuilt from the
+//           statistics, dv += P^T dO, dk += dS^T Q.
+// Shared rows are 72 bf16 (36 words) apart: the 32-bit B-fragment reads (bank 4g + t) and the ldmatrix rows are conflict-free.
 constexpr int kAbS = MDE_VIT_SEQ;
-constexpr int kAbLd = 33;  // words (bf16 pairs) per row: 32 + 1 pad
-constexpr int kAbT = (kAbS + 31) / 32;  // 7 row groups per lane
-constexpr int kAbSmem = 2 * kAbS * kAbLd * 4 + 3 * kAbS * 4 + 8 * 2 * 224 * 4;  // 69 KB; registers allow two blocks per SM
+constexpr int kAbSp = 208;                 // 13 tiles of 16
+constexpr int kAbTiles = kAbSp / 16;
+constexpr int kAbPw = 36;                  // row pitch in 32-bit words
+constexpr int kAbVw = 108;                 // pitch of a V^T row (208 keys + 8 pad) in words: ldmatrix rows 12 banks apart
+constexpr int kAbSmem = 2 * kAbSp * kAbPw * 4 + 3 * kAbSp * 4;  // 62.4 KB
+static_assert(MDE_VT_PITCH == kAbSp, "the V^T slab rows are copied 16 bytes at a time");
 
-__device__ __forceinline__ float dot2(uint32_t a, uint32_t b, float acc) {
-  const __nv_bfloat162 x = *reinterpret_cast<const __nv_bfloat162*>(&a), y = *reinterpret_cast<const __nv_bfloat162*>(&b);
-  return fmaf(__high2float(x), __high2float(y), fmaf(__low2float(x), __low2float(y), acc));
+__device__ __forceinline__ void mma_bf16_16816(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};\n"
+               : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+               : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
 }
-// one 64-wide bf16 row (128 bytes, 16-byte aligned) into 32 registers of every lane (broadcast loads)
-__device__ __forceinline__ void load_row32(const bf16* __restrict__ p, uint32_t (&r)[32]) {
-  const uint4* v = reinterpret_cast<const uint4*>(p);
+// four transposed 8x8 bf16 matrices: with rows = k and columns = n in shared memory this yields the B fragments (b0, b1) of two
+// adjacent n-tiles (lane address: row k0 + (lane & 15), column n0 + 8 (lane >> 4))
+__device__ __forceinline__ void ldsm_x4_trans(uint32_t& r0, uint32_t& r1, uint32_t& r2, uint32_t& r3, const void* p) {
+  const uint32_t a = (uint32_t)__cvta_generic_to_shared(p);
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];\n" : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3) : "r"(a));
+}
+// A fragments (4 k-steps of 16) of a 16 x 64 row-major bf16 tile in global memory; rows >= kAbS read as zero
+__device__ __forceinline__ void load_a_tile(const bf16* __restrict__ base, int row_lo, int t, uint32_t (&a)[4][4]) {
+  const bool vlo = row_lo < kAbS, vhi = row_lo + 8 < kAbS;
+  const uint32_t* plo = reinterpret_cast<const uint32_t*>(base + (size_t)row_lo * MDE_VIT_DIM);
+  const uint32_t* phi = reinterpret_cast<const uint32_t*>(base + (size_t)(row_lo + 8) * MDE_VIT_DIM);
 #pragma unroll
-  for (int w = 0; w < 8; ++w) {
-    const uint4 t = __ldg(v + w);
-    r[4 * w] = t.x;
-    r[4 * w + 1] = t.y;
-    r[4 * w + 2] = t.z;
-    r[4 * w + 3] = t.w;
+  for (int kk = 0; kk < 4; ++kk) {
+    a[kk][0] = vlo ? __ldg(plo + kk * 8 + t) : 0u;
+    a[kk][1] = vhi ? __ldg(phi + kk * 8 + t) : 0u;
+    a[kk][2] = vlo ? __ldg(plo + kk * 8 + 4 + t) : 0u;
+    a[kk][3] = vhi ? __ldg(phi + kk * 8 + 4 + t) : 0u;
   }
 }
 
 template <int PASS>
-__global__ void __launch_bounds__(256, 2) vit_attn_bwd_kernel(const bf16* __restrict__ q, const bf16* __restrict__ k, const bf16* __restrict__ vt,
-                                                              const bf16* __restrict__ dout, float* __restrict__ stats, bf16* __restrict__ dqkv) {
-  extern __shared__ uint32_t sm[];
-  uint32_t* sA = sm;                   // pass 1: K          pass 2: Q
-  uint32_t* sB = sA + kAbS * kAbLd;    // pass 1: V          pass 2: dO
-  float* sMax = reinterpret_cast<float*>(sB + kAbS * kAbLd);
-  float* sInv = sMax + kAbS;
-  float* sD = sInv + kAbS;
-  float* sRow = sD + kAbS;  // [8 warps][2][224]
+__global__ void __launch_bounds__(128) vit_attn_bwd_kernel(const bf16* __restrict__ q, const bf16* __restrict__ k, const bf16* __restrict__ vt,
+                                                           const bf16* __restrict__ dout, float* __restrict__ stats, bf16* __restrict__ dqkv) {
+  extern __shared__ __align__(16) uint32_t sm[];
+  uint32_t* sA = sm;                     // pass 1: K [key][d]                  pass 2: Q [query][d]
+  uint32_t* sB = sA + kAbSp * kAbPw;     // pass 1: V^T [d][key], pitch kAbVw   pass 2: dO [query][d]
+  float* sMax = reinterpret_cast<float*>(sB + kAbSp * kAbPw);
+  float* sInv = sMax + kAbSp;
+  float* sD = sInv + kAbSp;
   const int slab = blockIdx.x, b = slab / MDE_VIT_HEADS, hd = slab - b * MDE_VIT_HEADS;
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
   const size_t tok0 = (size_t)b * kAbS;
-  const int per = (kAbS + gridDim.y - 1) / gridDim.y, lo = blockIdx.y * per, hi = min(kAbS, lo + per);
   const bf16* vb = vt + (size_t)slab * 64 * MDE_VT_PITCH;
   float* st = stats + (size_t)slab * 3 * kAbS;
+  const bf16* qh = q + tok0 * MDE_VIT_DIM + hd * 64;
+  const bf16* kh = k + tok0 * MDE_VIT_DIM + hd * 64;
+  const bf16* gh = dout + tok0 * MDE_VIT_DIM + hd * 64;
   {
-    const bf16* a = PASS == 1 ? k : q;
-    for (int i = tid; i < kAbS * 32; i += 256) {
-      const int r = i >> 5, w = i & 31;
-      const size_t off = (tok0 + r) * MDE_VIT_DIM + hd * 64 + 2 * w;
-      sA[r * kAbLd + w] = *reinterpret_cast<const uint32_t*>(a + off);
-      if (PASS == 2) sB[r * kAbLd + w] = *reinterpret_cast<const uint32_t*>(dout + off);
+    const bf16* a = PASS == 1 ? kh : qh;
+    for (int i = tid; i < kAbSp * 8; i += 128) {  // 16-byte pieces; rows 197..207 are zero
+      const int r = i >> 3, c = i & 7;
+      uint4 va = make_uint4(0u, 0u, 0u, 0u), vg = va;
+      if (r < kAbS) {
+        va = __ldg(reinterpret_cast<const uint4*>(a + (size_t)r * MDE_VIT_DIM) + c);
+        if (PASS == 2) vg = __ldg(reinterpret_cast<const uint4*>(gh + (size_t)r * MDE_VIT_DIM) + c);
+      }
+      *reinterpret_cast<uint4*>(sA + r * kAbPw + c * 4) = va;
+      if (PASS == 2) *reinterpret_cast<uint4*>(sB + r * kAbPw + c * 4) = vg;
     }
-    if (PASS == 1) {  // V^T [64][208] -> sB[token][d]
+    if (PASS == 1) {  // V^T [64][208] as stored (rows = d: ldmatrix.trans turns them into B fragments); keys 197..207 zeroed
+      for (int i = tid; i < 64 * (kAbSp / 8); i += 128) {
+        const int d = i / (kAbSp / 8), c = i - d * (kAbSp / 8);
+        *reinterpret_cast<uint4*>(sB + d * kAbVw + c * 4) = __ldg(reinterpret_cast<const uint4*>(vb + (size_t)d * MDE_VT_PITCH) + c);
+      }
+      __syncthreads();
       bf16* sVh = reinterpret_cast<bf16*>(sB);
-      for (int i = tid; i < 64 * kAbS; i += 256) {
-        const int d = i / kAbS, t = i - d * kAbS;
-        sVh[t * (2 * kAbLd) + d] = vb[(size_t)d * MDE_VT_PITCH + t];
+      for (int i = tid; i < 64 * (kAbSp - kAbS); i += 128) {
+        const int d = i / (kAbSp - kAbS), c = i - d * (kAbSp - kAbS);
+        sVh[d * (2 * kAbVw) + kAbS + c] = __float2bfloat16_rn(0.0f);
       }
     } else {
-      for (int i = tid; i < kAbS; i += 256) {
-        sMax[i] = st[i];
-        sInv[i] = st[kAbS + i];
-        sD[i] = st[2 * kAbS + i];
+      for (int i = tid; i < kAbSp; i += 128) {  // padded queries: 1/sum = 0 switches them off
+        const bool ok = i < kAbS;
+        sMax[i] = ok ? st[i] : 0.0f;
+        sInv[i] = ok ? st[kAbS + i] : 0.0f;
+        sD[i] = ok ? st[2 * kAbS + i] : 0.0f;
       }
     }
   }
   __syncthreads();
-  float* rowA = sRow + warp * 2 * 224;
-  float* rowB = rowA + 224;
+  const int mt = blockIdx.y * 4 + warp;
+  if (mt >= kAbTiles) return;
+  const int r_lo = mt * 16 + g, r_hi = r_lo + 8;
 
-  if (PASS == 1) {  // ---- query rows
-    const uint32_t* sK = sA;
-    const uint32_t* sV = sB;
-    for (int i = lo + warp; i < hi; i += 8) {
-      uint32_t qi[32], gi[32];
-      load_row32(q + (tok0 + i) * MDE_VIT_DIM + hd * 64, qi);
-      load_row32(dout + (tok0 + i) * MDE_VIT_DIM + hd * 64, gi);
-      float s[kAbT], dp[kAbT];
-      float mx = -INFINITY;
+  if (PASS == 1) {  // ------------------------------------------------ 16 query rows
+    uint32_t ga[4][4];
+    float P[kAbSp / 8][4];
+    {
+      uint32_t qa[4][4];
+      load_a_tile(qh, r_lo, t, qa);
 #pragma unroll
-      for (int t = 0; t < kAbT; ++t) {
-        const int j = lane + 32 * t;
-        s[t] = -INFINITY;
-        dp[t] = 0.0f;
-        if (j < kAbS) {
-          float a = 0.0f, c = 0.0f;
+      for (int j = 0; j < kAbSp / 8; ++j) {
+        P[j][0] = P[j][1] = P[j][2] = P[j][3] = 0.0f;
+        const uint32_t* kr = sA + (j * 8 + g) * kAbPw + t;
 #pragma unroll
-          for (int w = 0; w < 32; ++w) {
-            a = dot2(qi[w], sK[j * kAbLd + w], a);
-            c = dot2(gi[w], sV[j * kAbLd + w], c);
-          }
-          s[t] = a;
-          dp[t] = c;
-          mx = fmaxf(mx, a);
-        }
+        for (int kk = 0; kk < 4; ++kk) mma_bf16_16816(P[j], qa[kk], kr[kk * 8], kr[kk * 8 + 4]);
       }
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-      float sum = 0.0f;
-#pragma unroll
-      for (int t = 0; t < kAbT; ++t) {
-        s[t] = (lane + 32 * t < kAbS) ? __expf(s[t] - mx) : 0.0f;
-        sum += s[t];
-      }
-      const float inv = 1.0f / warp_sum(sum);
-      float dd = 0.0f;
-#pragma unroll
-      for (int t = 0; t < kAbT; ++t) {
-        s[t] *= inv;
-        dd = fmaf(s[t], dp[t], dd);
-      }
-      dd = warp_sum(dd);
-      if (lane == 0) {
-        st[i] = mx;
-        st[kAbS + i] = inv;
-        st[2 * kAbS + i] = dd;
-      }
-#pragma unroll
-      for (int t = 0; t < kAbT; ++t)
-        if (lane + 32 * t < kAbS) rowA[lane + 32 * t] = s[t] * (dp[t] - dd);  // dS
-      __syncwarp();
-      float a0 = 0.0f, a1 = 0.0f;  // dq[2*lane], dq[2*lane+1]
-      for (int j = 0; j < kAbS; ++j) {
-        const float ds = rowA[j];
-        const uint32_t kw = sK[j * kAbLd + lane];
-        const __nv_bfloat162 kk = *reinterpret_cast<const __nv_bfloat162*>(&kw);
-        a0 = fmaf(ds, __low2float(kk), a0);
-        a1 = fmaf(ds, __high2float(kk), a1);
-      }
-      *reinterpret_cast<uint32_t*>(dqkv + (tok0 + i) * (3 * MDE_VIT_DIM) + hd * 64 + 2 * lane) = pack_bf16x2(a0 * 0.125f, a1 * 0.125f);
-      __syncwarp();
     }
-  } else {  // ---- key rows
-    const uint32_t* sQ = sA;
-    const uint32_t* sG = sB;
-    for (int j = lo + warp; j < hi; j += 8) {
-      uint32_t kj[32], vj[32];
-      load_row32(k + (tok0 + j) * MDE_VIT_DIM + hd * 64, kj);
-      {  // V row j out of the transposed slab: lane l fetches dims 2l, 2l+1, then 32 broadcasts
-        const uint32_t mine = (uint32_t)__bfloat16_as_ushort(vb[(size_t)(2 * lane) * MDE_VT_PITCH + j]) |
-                              ((uint32_t)__bfloat16_as_ushort(vb[(size_t)(2 * lane + 1) * MDE_VT_PITCH + j]) << 16);
+    load_a_tile(gh, r_lo, t, ga);
+    float mlo = -INFINITY, mhi = -INFINITY;
 #pragma unroll
-        for (int w = 0; w < 32; ++w) vj[w] = __shfl_sync(0xffffffffu, mine, w);
+    for (int j = 0; j < kAbSp / 8; ++j) {
+      const int key = j * 8 + 2 * t;
+      if (key >= kAbS) P[j][0] = P[j][2] = -INFINITY;
+      if (key + 1 >= kAbS) P[j][1] = P[j][3] = -INFINITY;
+      mlo = fmaxf(mlo, fmaxf(P[j][0], P[j][1]));
+      mhi = fmaxf(mhi, fmaxf(P[j][2], P[j][3]));
+    }
+    mlo = fmaxf(mlo, __shfl_xor_sync(0xffffffffu, mlo, 1));
+    mlo = fmaxf(mlo, __shfl_xor_sync(0xffffffffu, mlo, 2));
+    mhi = fmaxf(mhi, __shfl_xor_sync(0xffffffffu, mhi, 1));
+    mhi = fmaxf(mhi, __shfl_xor_sync(0xffffffffu, mhi, 2));
+    float slo = 0.0f, shi = 0.0f;
+#pragma unroll
+    for (int j = 0; j < kAbSp / 8; ++j) {
+      P[j][0] = __expf(P[j][0] - mlo);
+      P[j][1] = __expf(P[j][1] - mlo);
+      P[j][2] = __expf(P[j][2] - mhi);
+      P[j][3] = __expf(P[j][3] - mhi);
+      slo += P[j][0] + P[j][1];
+      shi += P[j][2] + P[j][3];
+    }
+    slo += __shfl_xor_sync(0xffffffffu, slo, 1);
+    slo += __shfl_xor_sync(0xffffffffu, slo, 2);
+    shi += __shfl_xor_sync(0xffffffffu, shi, 1);
+    shi += __shfl_xor_sync(0xffffffffu, shi, 2);
+    const float ilo = 1.0f / slo, ihi = 1.0f / shi;
+    float dlo = 0.0f, dhi = 0.0f;  // D = rowsum(P o dP)
+    const uint32_t* vrow = sB + (lane & 15) * kAbVw + (lane >> 4) * 4;  // + kk * 16 rows, + kp * 8 words
+#pragma unroll
+    for (int kp = 0; kp < kAbTiles; ++kp) {
+      float dp[2][4] = {{0.0f, 0.0f, 0.0f, 0.0f}, {0.0f, 0.0f, 0.0f, 0.0f}};
+#pragma unroll
+      for (int kk = 0; kk < 4; ++kk) {
+        uint32_t b0, b1, b2, b3;
+        ldsm_x4_trans(b0, b1, b2, b3, vrow + kk * 16 * kAbVw + kp * 8);
+        mma_bf16_16816(dp[0], ga[kk], b0, b1);
+        mma_bf16_16816(dp[1], ga[kk], b2, b3);
       }
 #pragma unroll
-      for (int t = 0; t < kAbT; ++t) {
-        const int i = lane + 32 * t;
-        if (i < kAbS) {
-          float a = 0.0f, c = 0.0f;
+      for (int h = 0; h < 2; ++h) {
+        const int j = 2 * kp + h;
+        P[j][0] *= ilo;
+        P[j][1] *= ilo;
+        P[j][2] *= ihi;
+        P[j][3] *= ihi;
+        dlo = fmaf(P[j][0], dp[h][0], fmaf(P[j][1], dp[h][1], dlo));
+        dhi = fmaf(P[j][2], dp[h][2], fmaf(P[j][3], dp[h][3], dhi));
+      }
+    }
+    dlo += __shfl_xor_sync(0xffffffffu, dlo, 1);
+    dlo += __shfl_xor_sync(0xffffffffu, dlo, 2);
+    dhi += __shfl_xor_sync(0xffffffffu, dhi, 1);
+    dhi += __shfl_xor_sync(0xffffffffu, dhi, 2);
+    if (t == 0) {
+      if (r_lo < kAbS) {
+        st[r_lo] = mlo;
+        st[kAbS + r_lo] = ilo;
+        st[2 * kAbS + r_lo] = dlo;
+      }
+      if (r_hi < kAbS) {
+        st[r_hi] = mhi;
+        st[kAbS + r_hi] = ihi;
+        st[2 * kAbS + r_hi] = dhi;
+      }
+    }
+    float dq[8][4];
 #pragma unroll
-          for (int w = 0; w < 32; ++w) {
-            a = dot2(kj[w], sQ[i * kAbLd + w], a);
-            c = dot2(vj[w], sG[i * kAbLd + w], c);
-          }
-          const float p = __expf(a - sMax[i]) * sInv[i];
-          rowA[i] = p;
-          rowB[i] = p * (c - sD[i]);
+    for (int n = 0; n < 8; ++n) dq[n][0] = dq[n][1] = dq[n][2] = dq[n][3] = 0.0f;
+#pragma unroll
+    for (int kp = 0; kp < kAbTiles; ++kp) {  // 16 keys per step: dP again (cheaper than keeping it), dS, dq += dS K
+      uint32_t a[4];
+      float dp[2][4] = {{0.0f, 0.0f, 0.0f, 0.0f}, {0.0f, 0.0f, 0.0f, 0.0f}};
+#pragma unroll
+      for (int kk = 0; kk < 4; ++kk) {
+        uint32_t b0, b1, b2, b3;
+        ldsm_x4_trans(b0, b1, b2, b3, vrow + kk * 16 * kAbVw + kp * 8);
+        mma_bf16_16816(dp[0], ga[kk], b0, b1);
+        mma_bf16_16816(dp[1], ga[kk], b2, b3);
+      }
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const int j = 2 * kp + h;
+        a[2 * h] = pack_bf16x2(P[j][0] * (dp[h][0] - dlo), P[j][1] * (dp[h][1] - dlo));
+        a[2 * h + 1] = pack_bf16x2(P[j][2] * (dp[h][2] - dhi), P[j][3] * (dp[h][3] - dhi));
+      }
+      const uint32_t* krow = sA + (kp * 16 + (lane & 15)) * kAbPw + (lane >> 4) * 4;
+#pragma unroll
+      for (int np = 0; np < 4; ++np) {
+        uint32_t b0, b1, b2, b3;
+        ldsm_x4_trans(b0, b1, b2, b3, krow + np * 8);
+        mma_bf16_16816(dq[2 * np], a, b0, b1);
+        mma_bf16_16816(dq[2 * np + 1], a, b2, b3);
+      }
+    }
+    bf16* olo = dqkv + (tok0 + r_lo) * (3 * MDE_VIT_DIM) + hd * 64 + 2 * t;
+    bf16* ohi = dqkv + (tok0 + r_hi) * (3 * MDE_VIT_DIM) + hd * 64 + 2 * t;
+#pragma unroll
+    for (int n = 0; n < 8; ++n) {
+      if (r_lo < kAbS) *reinterpret_cast<uint32_t*>(olo + n * 8) = pack_bf16x2(dq[n][0] * 0.125f, dq[n][1] * 0.125f);
+      if (r_hi < kAbS) *reinterpret_cast<uint32_t*>(ohi + n * 8) = pack_bf16x2(dq[n][2] * 0.125f, dq[n][3] * 0.125f);
+    }
+  } else {  // -------------------------------------------------------- 16 key rows
+    uint32_t ka[4][4], va[4][4];
+    load_a_tile(kh, r_lo, t, ka);
+    {
+      const bool vlo = r_lo < kAbS, vhi = r_hi < kAbS;
+      const unsigned short* vs = reinterpret_cast<const unsigned short*>(vb);
+      auto ld2 = [&](int d, int key, bool ok) -> uint32_t {
+        return ok ? ((uint32_t)vs[(size_t)d * MDE_VT_PITCH + key] | ((uint32_t)vs[(size_t)(d + 1) * MDE_VT_PITCH + key] << 16)) : 0u;
+      };
+#pragma unroll
+      for (int kk = 0; kk < 4; ++kk) {
+        va[kk][0] = ld2(kk * 16 + 2 * t, r_lo, vlo);
+        va[kk][1] = ld2(kk * 16 + 2 * t, r_hi, vhi);
+        va[kk][2] = ld2(kk * 16 + 8 + 2 * t, r_lo, vlo);
+        va[kk][3] = ld2(kk * 16 + 8 + 2 * t, r_hi, vhi);
+      }
+    }
+    float dk[8][4], dv[8][4];
+#pragma unroll
+    for (int n = 0; n < 8; ++n) {
+      dk[n][0] = dk[n][1] = dk[n][2] = dk[n][3] = 0.0f;
+      dv[n][0] = dv[n][1] = dv[n][2] = dv[n][3] = 0.0f;
+    }
+#pragma unroll 1
+    for (int qp = 0; qp < kAbTiles; ++qp) {  // 16 queries per step
+      uint32_t pa[4], da[4];
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const int j = 2 * qp + h;
+        float sT[4] = {0.0f, 0.0f, 0.0f, 0.0f}, dp[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+        const uint32_t* qr = sA + (j * 8 + g) * kAbPw + t;
+        const uint32_t* gr = sB + (j * 8 + g) * kAbPw + t;
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk) {
+          mma_bf16_16816(sT, ka[kk], qr[kk * 8], qr[kk * 8 + 4]);
+          mma_bf16_16816(dp, va[kk], gr[kk * 8], gr[kk * 8 + 4]);
         }
+        const int q0 = j * 8 + 2 * t;
+        const float m0 = sMax[q0], m1 = sMax[q0 + 1], i0 = sInv[q0], i1 = sInv[q0 + 1], d0 = sD[q0], d1 = sD[q0 + 1];
+        const float p0 = __expf(sT[0] - m0) * i0, p1 = __expf(sT[1] - m1) * i1, p2 = __expf(sT[2] - m0) * i0, p3 = __expf(sT[3] - m1) * i1;
+        pa[2 * h] = pack_bf16x2(p0, p1);
+        pa[2 * h + 1] = pack_bf16x2(p2, p3);
+        da[2 * h] = pack_bf16x2(p0 * (dp[0] - d0), p1 * (dp[1] - d1));
+        da[2 * h + 1] = pack_bf16x2(p2 * (dp[2] - d0), p3 * (dp[3] - d1));
       }
-      __syncwarp();
-      float k0 = 0.0f, k1 = 0.0f, v0 = 0.0f, v1 = 0.0f;
-      for (int i = 0; i < kAbS; ++i) {
-        const float p = rowA[i], ds = rowB[i];
-        const uint32_t qw = sQ[i * kAbLd + lane], gw = sG[i * kAbLd + lane];
-        const __nv_bfloat162 qq = *reinterpret_cast<const __nv_bfloat162*>(&qw), gg = *reinterpret_cast<const __nv_bfloat162*>(&gw);
-        k0 = fmaf(ds, __low2float(qq), k0);
-        k1 = fmaf(ds, __high2float(qq), k1);
-        v0 = fmaf(p, __low2float(gg), v0);
-        v1 = fmaf(p, __high2float(gg), v1);
+      const int roff = (qp * 16 + (lane & 15)) * kAbPw + (lane >> 4) * 4;
+#pragma unroll
+      for (int np = 0; np < 4; ++np) {
+        uint32_t b0, b1, b2, b3;
+        ldsm_x4_trans(b0, b1, b2, b3, sB + roff + np * 8);  // dO [k = query][n = d]
+        mma_bf16_16816(dv[2 * np], pa, b0, b1);
+        mma_bf16_16816(dv[2 * np + 1], pa, b2, b3);
+        ldsm_x4_trans(b0, b1, b2, b3, sA + roff + np * 8);  // Q
+        mma_bf16_16816(dk[2 * np], da, b0, b1);
+        mma_bf16_16816(dk[2 * np + 1], da, b2, b3);
       }
-      bf16* dst = dqkv + (tok0 + j) * (3 * MDE_VIT_DIM) + hd * 64 + 2 * lane;
-      *reinterpret_cast<uint32_t*>(dst + MDE_VIT_DIM) = pack_bf16x2(k0, k1);
-      *reinterpret_cast<uint32_t*>(dst + 2 * MDE_VIT_DIM) = pack_bf16x2(v0, v1);
-      __syncwarp();
+    }
+    bf16* olo = dqkv + (tok0 + r_lo) * (3 * MDE_VIT_DIM) + MDE_VIT_DIM + hd * 64 + 2 * t;
+    bf16* ohi = dqkv + (tok0 + r_hi) * (3 * MDE_VIT_DIM) + MDE_VIT_DIM + hd * 64 + 2 * t;
+#pragma unroll
+    for (int n = 0; n < 8; ++n) {
+      if (r_lo < kAbS) {
+        *reinterpret_cast<uint32_t*>(olo + n * 8) = pack_bf16x2(dk[n][0], dk[n][1]);
+        *reinterpret_cast<uint32_t*>(olo + MDE_VIT_DIM + n * 8) = pack_bf16x2(dv[n][0], dv[n][1]);
+      }
+      if (r_hi < kAbS) {
+        *reinterpret_cast<uint32_t*>(ohi + n * 8) = pack_bf16x2(dk[n][2], dk[n][3]);
+        *reinterpret_cast<uint32_t*>(ohi + MDE_VIT_DIM + n * 8) = pack_bf16x2(dv[n][2], dv[n][3]);
+      }
     }
   }
 }
@@ -466,24 +575,20 @@ extern "C" long long mde_vit_attention_bwd_scratch_floats(int B) { return (long 
 extern "C" int mde_vit_attention_bwd(const mde_bf16* q, const mde_bf16* k, const mde_bf16* vt, const mde_bf16* dout, int B, mde_bf16* dqkv, float* scratch,
                                      mde_stream_t stream) {
   MDE_CHECK_ARG(q && k && vt && dout && dqkv && scratch && B > 0, "mde_vit_attention_bwd: bad arguments");
-  MDE_CHECK_ARG(((uintptr_t)q | (uintptr_t)k | (uintptr_t)dout) % 16 == 0 && (uintptr_t)dqkv % 4 == 0, "mde_vit_attention_bwd: q, k, dout must be 16-byte aligned");
+  MDE_CHECK_ARG(((uintptr_t)q | (uintptr_t)k | (uintptr_t)vt | (uintptr_t)dout) % 16 == 0 && (uintptr_t)dqkv % 4 == 0,
+                "mde_vit_attention_bwd: q, k, vt, dout must be 16-byte aligned");
   static bool attr = false;
   if (!attr) {
     MDE_CHECK_CUDA(cudaFuncSetAttribute(vit_attn_bwd_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kAbSmem));
     MDE_CHECK_CUDA(cudaFuncSetAttribute(vit_attn_bwd_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kAbSmem));
     attr = true;
   }
-  // row chunks so that the grid is at most one resident wave (two blocks per SM), at least 16 rows (two per warp) each
-  const int slabs = B * MDE_VIT_HEADS;
-  int chunks = 2 * sm_count() / slabs;
-  if (chunks > 12) chunks = 12;
-  if (chunks < 1) chunks = 1;
-  const dim3 grid(slabs, chunks);
+  const dim3 grid(B * MDE_VIT_HEADS, (kAbTiles + 3) / 4);
   const bf16 *qq = reinterpret_cast<const bf16*>(q), *kk = reinterpret_cast<const bf16*>(k), *vv = reinterpret_cast<const bf16*>(vt),
              *gg = reinterpret_cast<const bf16*>(dout);
-  vit_attn_bwd_kernel<1><<<grid, 256, kAbSmem, stream>>>(qq, kk, vv, gg, scratch, reinterpret_cast<bf16*>(dqkv));
+  vit_attn_bwd_kernel<1><<<grid, 128, kAbSmem, stream>>>(qq, kk, vv, gg, scratch, reinterpret_cast<bf16*>(dqkv));
   MDE_CHECK_LAUNCH();
-  vit_attn_bwd_kernel<2><<<grid, 256, kAbSmem, stream>>>(qq, kk, vv, gg, scratch, reinterpret_cast<bf16*>(dqkv));
+  vit_attn_bwd_kernel<2><<<grid, 128, kAbSmem, stream>>>(qq, kk, vv, gg, scratch, reinterpret_cast<bf16*>(dqkv));
   MDE_CHECK_LAUNCH();
   return MDE_OK;
 }
