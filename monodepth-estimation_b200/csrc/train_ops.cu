@@ -236,6 +236,17 @@ __global__ void __launch_bounds__(256) bilinear_bwd_kernel(const float* __restri
     const int x = (int)(p % ws), y = (int)((p / ws) % hs), b = (int)(p / ((long long)ws * hs));
     const int Y0 = max(0, (int)floorf((y - 1) * ry) - 2), Y1 = min(hd - 1, (int)ceilf((y + 2) * ry) + 2);
     const int X0 = max(0, (int)floorf((x - 1) * rx) - 2), X1 = min(wd - 1, (int)ceilf((x + 2) * rx) + 2);
+    // the horizontal weights do not depend on the row: evaluated once (windows wider than the buffer fall back to recomputing)
+    constexpr int kWx = 40;
+    float wxs[kWx];
+    const bool cached = X1 - X0 < kWx;
+    if (cached)
+      for (int X = X0; X <= X1; ++X) {
+        int e0, e1;
+        float lx;
+        src_idx(X, ws, wd, align, e0, e1, lx);
+        wxs[X - X0] = (e0 == x ? 1.0f - lx : 0.0f) + (e1 == x ? lx : 0.0f);
+      }
     float acc = 0.0f;
     for (int Y = Y0; Y <= Y1; ++Y) {
       int a0, a1;
@@ -245,10 +256,15 @@ __global__ void __launch_bounds__(256) bilinear_bwd_kernel(const float* __restri
       if (wy == 0.0f) continue;
       float row = 0.0f;
       for (int X = X0; X <= X1; ++X) {
-        int e0, e1;
-        float lx;
-        src_idx(X, ws, wd, align, e0, e1, lx);
-        const float wx = (e0 == x ? 1.0f - lx : 0.0f) + (e1 == x ? lx : 0.0f);
+        float wx;
+        if (cached) {
+          wx = wxs[X - X0];
+        } else {
+          int e0, e1;
+          float lx;
+          src_idx(X, ws, wd, align, e0, e1, lx);
+          wx = (e0 == x ? 1.0f - lx : 0.0f) + (e1 == x ? lx : 0.0f);
+        }
         if (wx != 0.0f) row = fmaf(wx, dd[(((size_t)b * hd + Y) * wd + X) * ldd + coff + c], row);
       }
       acc = fmaf(wy, row, acc);
@@ -257,50 +273,70 @@ __global__ void __launch_bounds__(256) bilinear_bwd_kernel(const float* __restri
   }
 }
 
-// ------------------------------------------------------------------ instance norm backward (encoder.py:167), x f32 [B][G][C], no affine
+// ------------------------------------------------------------------ instance norm (encoder.py:167) and its backward, x f32 [B][G][C], no affine
+// One block per (32 channels, image): lane = channel, the eight warps stride the G grid positions; the eight partial sums are added
+// in warp order.  sum8 returns the total to every thread of the block.
+__device__ __forceinline__ float instnorm_sum8(float v, float (*buf)[32], int w, int l) {
+  __syncthreads();  // the previous round's readers are done
+  buf[w][l] = v;
+  __syncthreads();
+  float t = 0.0f;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) t += buf[k][l];
+  return t;
+}
 __global__ void __launch_bounds__(256) instnorm_bwd_kernel(const float* __restrict__ x, const float* __restrict__ dy, int G, int C, float eps, float* __restrict__ dx) {
-  const int c = blockIdx.x * 256 + threadIdx.x, b = blockIdx.y;
-  if (c >= C) return;
-  const float* xb = x + (size_t)b * G * C + c;
-  const float* db = dy + (size_t)b * G * C + c;
+  __shared__ float buf[8][32];
+  const int l = threadIdx.x & 31, w = threadIdx.x >> 5, c = blockIdx.x * 32 + l, b = blockIdx.y;
+  const bool ok = c < C;
+  const float* xb = x + (size_t)b * G * C + (ok ? c : 0);
+  const float* db = dy + (size_t)b * G * C + (ok ? c : 0);
   float s = 0.0f;
-  for (int g = 0; g < G; ++g) s += xb[(size_t)g * C];
-  const float m = s / (float)G;
+  if (ok)
+    for (int g = w; g < G; g += 8) s += xb[(size_t)g * C];
+  const float m = instnorm_sum8(s, buf, w, l) / (float)G;
   float q = 0.0f;
-  for (int g = 0; g < G; ++g) {
-    const float d = xb[(size_t)g * C] - m;
-    q = fmaf(d, d, q);
-  }
-  const float rs = 1.0f / sqrtf(q / (float)G + eps);
+  if (ok)
+    for (int g = w; g < G; g += 8) {
+      const float d = xb[(size_t)g * C] - m;
+      q = fmaf(d, d, q);
+    }
+  const float rs = 1.0f / sqrtf(instnorm_sum8(q, buf, w, l) / (float)G + eps);
   float sd = 0.0f, sdy = 0.0f;
-  for (int g = 0; g < G; ++g) {
-    const float yh = (xb[(size_t)g * C] - m) * rs, d = db[(size_t)g * C];
-    sd += d;
-    sdy = fmaf(d, yh, sdy);
-  }
-  sd /= (float)G;
-  sdy /= (float)G;
+  if (ok)
+    for (int g = w; g < G; g += 8) {
+      const float yh = (xb[(size_t)g * C] - m) * rs, d = db[(size_t)g * C];
+      sd += d;
+      sdy = fmaf(d, yh, sdy);
+    }
+  sd = instnorm_sum8(sd, buf, w, l) / (float)G;
+  sdy = instnorm_sum8(sdy, buf, w, l) / (float)G;
+  if (!ok) return;
   float* ob = dx + (size_t)b * G * C + c;
-  for (int g = 0; g < G; ++g) {
+  for (int g = w; g < G; g += 8) {
     const float yh = (xb[(size_t)g * C] - m) * rs;
     ob[(size_t)g * C] = rs * (db[(size_t)g * C] - sd - yh * sdy);
   }
 }
 __global__ void __launch_bounds__(256) instnorm_fwd_kernel(const float* __restrict__ x, int G, int C, float eps, float* __restrict__ y) {
-  const int c = blockIdx.x * 256 + threadIdx.x, b = blockIdx.y;
-  if (c >= C) return;
-  const float* xb = x + (size_t)b * G * C + c;
+  __shared__ float buf[8][32];
+  const int l = threadIdx.x & 31, w = threadIdx.x >> 5, c = blockIdx.x * 32 + l, b = blockIdx.y;
+  const bool ok = c < C;
+  const float* xb = x + (size_t)b * G * C + (ok ? c : 0);
   float s = 0.0f;
-  for (int g = 0; g < G; ++g) s += xb[(size_t)g * C];
-  const float m = s / (float)G;
+  if (ok)
+    for (int g = w; g < G; g += 8) s += xb[(size_t)g * C];
+  const float m = instnorm_sum8(s, buf, w, l) / (float)G;
   float q = 0.0f;
-  for (int g = 0; g < G; ++g) {
-    const float d = xb[(size_t)g * C] - m;
-    q = fmaf(d, d, q);
-  }
-  const float rs = 1.0f / sqrtf(q / (float)G + eps);
+  if (ok)
+    for (int g = w; g < G; g += 8) {
+      const float d = xb[(size_t)g * C] - m;
+      q = fmaf(d, d, q);
+    }
+  const float rs = 1.0f / sqrtf(instnorm_sum8(q, buf, w, l) / (float)G + eps);
+  if (!ok) return;
   float* ob = y + (size_t)b * G * C + c;
-  for (int g = 0; g < G; ++g) ob[(size_t)g * C] = (xb[(size_t)g * C] - m) * rs;
+  for (int g = w; g < G; g += 8) ob[(size_t)g * C] = (xb[(size_t)g * C] - m) * rs;
 }
 // adjoint of mde_tokens_to_grid_bf16 (encoder.py:69-110): grid rows g < T go back to token g + strip, zero-padded cells and (when
 // stripped) the class token receive nothing.  dgrid f32 [B][G][768] -> dtok f32 [B][197][768]
@@ -612,14 +648,14 @@ extern "C" int mde_bilinear_nhwc_bwd_f32(const float* ddst, int B, int hd, int w
 
 extern "C" int mde_instnorm_f32(const float* x, int B, int G, int C, float eps, float* y, mde_stream_t stream) {
   MDE_CHECK_ARG(x && y && B > 0 && G > 0 && C > 0, "mde_instnorm_f32: bad arguments");
-  instnorm_fwd_kernel<<<dim3(ceil_div(C, 256), B), 256, 0, stream>>>(x, G, C, eps, y);
+  instnorm_fwd_kernel<<<dim3(ceil_div(C, 32), B), 256, 0, stream>>>(x, G, C, eps, y);
   MDE_CHECK_LAUNCH();
   return MDE_OK;
 }
 
 extern "C" int mde_instnorm_bwd_f32(const float* x, const float* dy, int B, int G, int C, float eps, float* dx, mde_stream_t stream) {
   MDE_CHECK_ARG(x && dy && dx && B > 0 && G > 0 && C > 0, "mde_instnorm_bwd_f32: bad arguments");
-  instnorm_bwd_kernel<<<dim3(ceil_div(C, 256), B), 256, 0, stream>>>(x, dy, G, C, eps, dx);
+  instnorm_bwd_kernel<<<dim3(ceil_div(C, 32), B), 256, 0, stream>>>(x, dy, G, C, eps, dx);
   MDE_CHECK_LAUNCH();
   return MDE_OK;
 }
