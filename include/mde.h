@@ -355,8 +355,10 @@ int mde_bn_elu_train_bwd(const float* z, int N, int C, int ldz, const float* mea
  * align_corners=False).  The destination may be a channel slice [coff, coff+C) of rows ldd wide (the concat of decoder.py:145). */
 int mde_bilinear_nhwc_f32(const float* src, int B, int hs, int ws, int C, float* dst, int hd, int wd, int ldd, int coff, int align_corners,
                           mde_stream_t stream);
+/* scratch: NULL (one gather kernel), or B*hd*ws*C floats: two separable gathers (along x, then y; same order of additions), which
+ * is what a large magnification with few source pixels wants (the disparity map back from the input size to level 0). */
 int mde_bilinear_nhwc_bwd_f32(const float* ddst, int B, int hd, int wd, int C, int ldd, int coff, float* dsrc, int hs, int ws, int align_corners,
-                              mde_stream_t stream);
+                              float* scratch, mde_stream_t stream);
 
 /* F.instance_norm (encoder.py:167: no affine, biased variance) on x f32 [B][G][C] and its backward; the adjoint of
  * mde_tokens_to_grid_bf16 (encoder.py:69-110): dgrid f32 [B][G][768] -> dtokens f32 [B][197][768]. */

@@ -81,7 +81,7 @@ SIGNATURES = {
     "mde_bn_elu_train_fwd": [_p, _i, _i, _i, _p, _p, _f, _f, _p, _p, _p, _p, _p, _p, _p],
     "mde_bn_elu_train_bwd": [_p, _i, _i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p],
     "mde_bilinear_nhwc_f32": [_p, _i, _i, _i, _i, _p, _i, _i, _i, _i, _i, _p],
-    "mde_bilinear_nhwc_bwd_f32": [_p, _i, _i, _i, _i, _i, _i, _p, _i, _i, _i, _p],
+    "mde_bilinear_nhwc_bwd_f32": [_p, _i, _i, _i, _i, _i, _i, _p, _i, _i, _i, _p, _p],
     "mde_instnorm_f32": [_p, _i, _i, _i, _f, _p, _p],
     "mde_instnorm_bwd_f32": [_p, _p, _i, _i, _i, _f, _p, _p],
     "mde_tokens_to_grid_bwd_f32": [_p, _i, _i, _i, _p, _p],

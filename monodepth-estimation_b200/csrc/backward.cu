@@ -184,14 +184,25 @@ __global__ void __launch_bounds__(256) ln_bwd_kernel(const float* __restrict__ x
     __syncthreads();
   }
 }
+// one block per 32 columns: warp w adds the partials w, w + 8, ... of its lane's column, the eight sums are added in warp order
 __global__ void __launch_bounds__(256) ln_bwd_finalize_kernel(const float* __restrict__ part, int nblocks, float* __restrict__ dgamma, float* __restrict__ dbeta,
                                                               int accumulate) {
-  const int c = blockIdx.x * 256 + threadIdx.x;
-  if (c >= kLnDim) return;
+  __shared__ float sg[8][32], sb[8][32];
+  const int l = threadIdx.x & 31, w = threadIdx.x >> 5, c = blockIdx.x * 32 + l;
   float g = 0.0f, b = 0.0f;
-  for (int i = 0; i < nblocks; ++i) {
+  for (int i = w; i < nblocks; i += 8) {
     g += part[((size_t)i * 2) * kLnDim + c];
     b += part[((size_t)i * 2 + 1) * kLnDim + c];
+  }
+  sg[w][l] = g;
+  sb[w][l] = b;
+  __syncthreads();
+  if (w != 0) return;
+  g = b = 0.0f;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    g += sg[k][l];
+    b += sb[k][l];
   }
   dgamma[c] = accumulate ? dgamma[c] + g : g;
   dbeta[c] = accumulate ? dbeta[c] + b : b;
@@ -565,7 +576,7 @@ extern "C" int mde_layernorm_bwd(const float* x, const mde_bf16* dy, const float
   const int nb = ceil_div(rows, kLnRowsPerBlock);
   ln_bwd_kernel<<<nb, 256, 0, stream>>>(x, reinterpret_cast<const bf16*>(dy), gamma, rows, eps, dres, dx, scratch);
   MDE_CHECK_LAUNCH();
-  ln_bwd_finalize_kernel<<<ceil_div(kLnDim, 256), 256, 0, stream>>>(scratch, nb, dgamma, dbeta, accumulate);
+  ln_bwd_finalize_kernel<<<kLnDim / 32, 256, 0, stream>>>(scratch, nb, dgamma, dbeta, accumulate);
   MDE_CHECK_LAUNCH();
   return MDE_OK;
 }

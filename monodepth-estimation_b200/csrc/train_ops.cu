@@ -236,17 +236,6 @@ __global__ void __launch_bounds__(256) bilinear_bwd_kernel(const float* __restri
     const int x = (int)(p % ws), y = (int)((p / ws) % hs), b = (int)(p / ((long long)ws * hs));
     const int Y0 = max(0, (int)floorf((y - 1) * ry) - 2), Y1 = min(hd - 1, (int)ceilf((y + 2) * ry) + 2);
     const int X0 = max(0, (int)floorf((x - 1) * rx) - 2), X1 = min(wd - 1, (int)ceilf((x + 2) * rx) + 2);
-    // the horizontal weights do not depend on the row: evaluated once (windows wider than the buffer fall back to recomputing)
-    constexpr int kWx = 40;
-    float wxs[kWx];
-    const bool cached = X1 - X0 < kWx;
-    if (cached)
-      for (int X = X0; X <= X1; ++X) {
-        int e0, e1;
-        float lx;
-        src_idx(X, ws, wd, align, e0, e1, lx);
-        wxs[X - X0] = (e0 == x ? 1.0f - lx : 0.0f) + (e1 == x ? lx : 0.0f);
-      }
     float acc = 0.0f;
     for (int Y = Y0; Y <= Y1; ++Y) {
       int a0, a1;
@@ -256,18 +245,56 @@ __global__ void __launch_bounds__(256) bilinear_bwd_kernel(const float* __restri
       if (wy == 0.0f) continue;
       float row = 0.0f;
       for (int X = X0; X <= X1; ++X) {
-        float wx;
-        if (cached) {
-          wx = wxs[X - X0];
-        } else {
-          int e0, e1;
-          float lx;
-          src_idx(X, ws, wd, align, e0, e1, lx);
-          wx = (e0 == x ? 1.0f - lx : 0.0f) + (e1 == x ? lx : 0.0f);
-        }
+        int e0, e1;
+        float lx;
+        src_idx(X, ws, wd, align, e0, e1, lx);
+        const float wx = (e0 == x ? 1.0f - lx : 0.0f) + (e1 == x ? lx : 0.0f);
         if (wx != 0.0f) row = fmaf(wx, dd[(((size_t)b * hd + Y) * wd + X) * ldd + coff + c], row);
       }
       acc = fmaf(wy, row, acc);
+    }
+    ds[i] = acc;
+  }
+}
+
+// The same adjoint in two separable steps for large magnifications (the disparity map back from the input size to the decoder's
+// level-0 grid: every source pixel collects ~(2 hd/hs)^2 destination pixels and there are few source pixels): first along x into
+// tmp [B][hd][ws][C], then along y.  The order of the additions is the direct kernel's (row sums, then the sum over rows).
+__global__ void __launch_bounds__(256) bilinear_bwd_x_kernel(const float* __restrict__ dd, int B, int hd, int wd, int C, int ldd, int coff, float* __restrict__ tmp, int ws,
+                                                             int align) {
+  const float rx = (float)wd / (float)ws;
+  MDE_GRID_STRIDE(i, (long long)B * hd * ws * C) {
+    const int c = (int)(i % C);
+    const long long p = i / C;
+    const int x = (int)(p % ws);
+    const long long bY = p / ws;  // b * hd + Y
+    const int X0 = max(0, (int)floorf((x - 1) * rx) - 2), X1 = min(wd - 1, (int)ceilf((x + 2) * rx) + 2);
+    float row = 0.0f;
+    for (int X = X0; X <= X1; ++X) {
+      int e0, e1;
+      float lx;
+      src_idx(X, ws, wd, align, e0, e1, lx);
+      const float wx = (e0 == x ? 1.0f - lx : 0.0f) + (e1 == x ? lx : 0.0f);
+      if (wx != 0.0f) row = fmaf(wx, dd[((size_t)bY * wd + X) * ldd + coff + c], row);
+    }
+    tmp[i] = row;
+  }
+}
+__global__ void __launch_bounds__(256) bilinear_bwd_y_kernel(const float* __restrict__ tmp, int B, int hd, int C, float* __restrict__ ds, int hs, int ws, int align) {
+  const float ry = (float)hd / (float)hs;
+  MDE_GRID_STRIDE(i, (long long)B * hs * ws * C) {
+    const int c = (int)(i % C);
+    const long long p = i / C;
+    const int x = (int)(p % ws), y = (int)((p / ws) % hs), b = (int)(p / ((long long)ws * hs));
+    const int Y0 = max(0, (int)floorf((y - 1) * ry) - 2), Y1 = min(hd - 1, (int)ceilf((y + 2) * ry) + 2);
+    float acc = 0.0f;
+    for (int Y = Y0; Y <= Y1; ++Y) {
+      int a0, a1;
+      float ly;
+      src_idx(Y, hs, hd, align, a0, a1, ly);
+      const float wy = (a0 == y ? 1.0f - ly : 0.0f) + (a1 == y ? ly : 0.0f);
+      if (wy == 0.0f) continue;
+      acc = fmaf(wy, tmp[(((size_t)b * hd + Y) * ws + x) * C + c], acc);
     }
     ds[i] = acc;
   }
@@ -561,20 +588,42 @@ __global__ void __launch_bounds__(256) depth_loss_finalize_kernel(const float* _
 // step_dev != nullptr: the step count lives on the device (a CUDA graph replays the same launch every step) and the bias
 // corrections are evaluated here; otherwise they arrive as arguments.
 __global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v, long long n,
-                                                   float lr, float b1, float b2, float eps, float bc1, float bc2_sqrt, const int* __restrict__ step_dev) {
+                                                   float lr, float b1, float b2, float eps, float bc1, float bc2_sqrt, const int* __restrict__ step_dev, int vec4) {
   if (step_dev) {
     const float t = (float)*step_dev;
     bc1 = 1.0f - powf(b1, t);
     bc2_sqrt = sqrtf(1.0f - powf(b2, t));
   }
+  auto upd = [&](float& pi, float gi, float& mi, float& vi) {
+    mi = fmaf(b1, mi, (1.0f - b1) * gi);   // exp_avg.lerp_(grad, 1 - beta1)
+    vi = fmaf(b2, vi, (1.0f - b2) * gi * gi);
+    const float denom = sqrtf(vi) / bc2_sqrt + eps;
+    pi -= (lr / bc1) * (mi / denom);
+  };
+  if (vec4) {  // n % 4 == 0 and 16-byte aligned pointers: 128-bit accesses
+    float4* p4 = reinterpret_cast<float4*>(p);
+    float4* m4 = reinterpret_cast<float4*>(m);
+    float4* v4 = reinterpret_cast<float4*>(v);
+    const float4* g4 = reinterpret_cast<const float4*>(g);
+    MDE_GRID_STRIDE(i, n / 4) {
+      float4 pp = p4[i], mm = m4[i], vv = v4[i];
+      const float4 gg = g4[i];
+      upd(pp.x, gg.x, mm.x, vv.x);
+      upd(pp.y, gg.y, mm.y, vv.y);
+      upd(pp.z, gg.z, mm.z, vv.z);
+      upd(pp.w, gg.w, mm.w, vv.w);
+      p4[i] = pp;
+      m4[i] = mm;
+      v4[i] = vv;
+    }
+    return;
+  }
   MDE_GRID_STRIDE(i, n) {
-    const float gi = g[i];
-    const float mi = fmaf(b1, m[i], (1.0f - b1) * gi);   // exp_avg.lerp_(grad, 1 - beta1)
-    const float vi = fmaf(b2, v[i], (1.0f - b2) * gi * gi);
+    float pi = p[i], mi = m[i], vi = v[i];
+    upd(pi, g[i], mi, vi);
+    p[i] = pi;
     m[i] = mi;
     v[i] = vi;
-    const float denom = sqrtf(vi) / bc2_sqrt + eps;
-    p[i] -= (lr / bc1) * (mi / denom);
   }
 }
 
@@ -639,8 +688,15 @@ extern "C" int mde_bilinear_nhwc_f32(const float* src, int B, int hs, int ws, in
 }
 
 extern "C" int mde_bilinear_nhwc_bwd_f32(const float* ddst, int B, int hd, int wd, int C, int ldd, int coff, float* dsrc, int hs, int ws, int align_corners,
-                                         mde_stream_t stream) {
+                                         float* scratch, mde_stream_t stream) {
   MDE_CHECK_ARG(ddst && dsrc && B > 0 && hs > 0 && ws > 0 && hd > 0 && wd > 0 && C > 0 && coff >= 0 && coff + C <= ldd, "mde_bilinear_nhwc_bwd_f32: bad arguments");
+  if (scratch) {  // separable: B*hd*ws*C floats of scratch
+    bilinear_bwd_x_kernel<<<grid1((long long)B * hd * ws * C), 256, 0, stream>>>(ddst, B, hd, wd, C, ldd, coff, scratch, ws, align_corners);
+    MDE_CHECK_LAUNCH();
+    bilinear_bwd_y_kernel<<<grid1((long long)B * hs * ws * C), 256, 0, stream>>>(scratch, B, hd, C, dsrc, hs, ws, align_corners);
+    MDE_CHECK_LAUNCH();
+    return MDE_OK;
+  }
   bilinear_bwd_kernel<<<grid1((long long)B * hs * ws * C), 256, 0, stream>>>(ddst, B, hd, wd, C, ldd, coff, dsrc, hs, ws, align_corners);
   MDE_CHECK_LAUNCH();
   return MDE_OK;
@@ -719,11 +775,16 @@ extern "C" int mde_depth_loss(const float* disp, const float* img, const float* 
   return MDE_OK;
 }
 
+static inline int adam_vec4(const float* p, const float* g, const float* m, const float* v, long long n) {
+  return n % 4 == 0 && ((uintptr_t)p | (uintptr_t)g | (uintptr_t)m | (uintptr_t)v) % 16 == 0;
+}
+
 extern "C" int mde_adam_step(float* p, const float* g, float* m, float* v, long long n, float lr, float beta1, float beta2, float eps, int step,
                              mde_stream_t stream) {
   MDE_CHECK_ARG(p && g && m && v && n > 0 && step >= 1, "mde_adam_step: bad arguments");
   const float bc1 = 1.0f - powf(beta1, (float)step), bc2 = 1.0f - powf(beta2, (float)step);
-  adam_kernel<<<grid1(n), 256, 0, stream>>>(p, g, m, v, n, lr, beta1, beta2, eps, bc1, sqrtf(bc2), nullptr);
+  const int vec4 = adam_vec4(p, g, m, v, n);
+  adam_kernel<<<grid1(vec4 ? n / 4 : n), 256, 0, stream>>>(p, g, m, v, n, lr, beta1, beta2, eps, bc1, sqrtf(bc2), nullptr, vec4);
   MDE_CHECK_LAUNCH();
   return MDE_OK;
 }
@@ -731,7 +792,8 @@ extern "C" int mde_adam_step(float* p, const float* g, float* m, float* v, long 
 extern "C" int mde_adam_step_dev(float* p, const float* g, float* m, float* v, long long n, float lr, float beta1, float beta2, float eps, const int* step_dev,
                                  mde_stream_t stream) {
   MDE_CHECK_ARG(p && g && m && v && n > 0 && step_dev, "mde_adam_step_dev: bad arguments");
-  adam_kernel<<<grid1(n), 256, 0, stream>>>(p, g, m, v, n, lr, beta1, beta2, eps, 1.0f, 1.0f, step_dev);
+  const int vec4 = adam_vec4(p, g, m, v, n);
+  adam_kernel<<<grid1(vec4 ? n / 4 : n), 256, 0, stream>>>(p, g, m, v, n, lr, beta1, beta2, eps, 1.0f, 1.0f, step_dev, vec4);
   MDE_CHECK_LAUNCH();
   return MDE_OK;
 }

@@ -379,7 +379,9 @@ def bilinear_nhwc_bwd(ddst, hs, ws, align_corners, Cc=None, coff=0):
     B, hd, wd, ldd = ddst.shape
     Cc = ldd if Cc is None else Cc
     dsrc = _f32(B, hs, ws, Cc, dev=ddst.device)
-    L.call("mde_bilinear_nhwc_bwd_f32", _ptr(ddst, F32), B, hd, wd, Cc, ldd, coff, _ptr(dsrc, F32), hs, ws, int(align_corners), _stream())
+    scratch = _f32(B * hd * ws * Cc, dev=ddst.device) if hd >= 4 * hs and wd >= 4 * ws else None  # large magnification: separable form
+    L.call("mde_bilinear_nhwc_bwd_f32", _ptr(ddst, F32), B, hd, wd, Cc, ldd, coff, _ptr(dsrc, F32), hs, ws, int(align_corners),
+           _ptr(scratch, F32) if scratch is not None else _ptr(None), _stream())
     return dsrc
 
 
