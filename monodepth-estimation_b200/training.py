@@ -176,8 +176,15 @@ class ViTEncoderTrainer:
         """dtaps: four entries (f32 [B*197, 768] or None) = the gradients of the tapped outputs.  Returns {name: fp32 gradient}
         under the VisionTransformer's parameter names (parameters that received no gradient are absent, as autograd leaves
         their ``.grad`` at None: blocks above the last tap that matters)."""
-        B, M = self.B, self.B * L.VIT_SEQ
         grads = {}
+        for _, g in self.backward_iter(dtaps):
+            grads.update(g)
+        return grads
+
+    def backward_iter(self, dtaps):
+        """The same walk as a generator: yields (block index, that block's gradients) from block 11 down, then (-1, the gradients
+        of the embedding parameters).  A data-parallel step all-reduces what it has while the rest is still being computed."""
+        B, M = self.B, self.B * L.VIT_SEQ
         dx = None
         for i in range(11, -1, -1):
             if i in HOOKS and dtaps[HOOKS.index(i)] is not None:
@@ -186,10 +193,10 @@ class ViTEncoderTrainer:
             if dx is None:
                 continue
             dx, g = self.blocks[i].backward(dx)
-            for n, v in g.items():
-                grads[f"encoder.layers.encoder_layer_{i}.{n}"] = v
+            yield i, {f"encoder.layers.encoder_layer_{i}.{n}": v for n, v in g.items()}
         if dx is None:
-            return grads
+            return
+        grads = {}
         # tokens = [class_token ; conv_proj(patches)] + pos_embedding  (tv:288-300, 156)
         dpos = ops.batch_sum_f32(dx.view(B, L.VIT_SEQ * 768))
         grads["encoder.pos_embedding"] = dpos.view(1, L.VIT_SEQ, 768)
@@ -209,7 +216,7 @@ class ViTEncoderTrainer:
         # gradient of the patch rows themselves (f32 [B*196, 768], columns (c, ky, kx)): the input-stage backward (encoder.normalize) reads it
         self.dpatches = torch.empty(B * 196, 768, device=self.dev, dtype=F32)
         ops.gemm(dy, self.patch_w_t, self.zero768, L.EPI_BIAS_F32, self.dpatches)
-        return grads
+        yield -1, grads
 
 
 # ====================================================================== the rest of the step: features, decoder level 0, loss, Adam
@@ -339,6 +346,7 @@ class DepthTrainer:
     def __init__(self, model, lr=1e-4, w_depth=1.0, w_smooth=0.001, betas=(0.9, 0.999), eps=1e-8, graph=True):
         self.model, self.lr, self.w_depth, self.w_smooth, self.betas, self.eps = model, lr, w_depth, w_smooth, betas, eps
         self.graph, self._graphs = graph, {}
+        self.splits = (8, 5, 2)  # ViT blocks after which a data-parallel step starts reducing what it has (see step())
         self.dev = next(model.parameters()).device
         if self.dev.type != "cuda":
             raise RuntimeError("the model must live on a CUDA (sm_100) device: there is no CPU path")
@@ -364,6 +372,15 @@ class DepthTrainer:
 
     def forward_backward(self, images, metadata, rnd):
         """-> (losses f32 [3] on the device: total, depth, smoothness; {state_dict key: fp32 gradient})"""
+        grads = {}
+        for losses, part in self._stages(images, metadata, rnd, ()):
+            grads.update(part)
+        return losses, grads
+
+    def _stages(self, images, metadata, rnd, splits):
+        """forward_backward as a generator over len(splits) + 1 stages: yields (losses, the gradients finished since the last
+        yield) after the ViT blocks named in ``splits`` (descending block indices) and at the end.  A data-parallel step captures
+        one CUDA graph per stage and all-reduces a stage's gradients while the next stage runs."""
         from .engine import grid_shape
         from .model import source_scale
 
@@ -422,11 +439,15 @@ class DepthTrainer:
         for i, gg in ((3, g3), (2, g2)):
             for k, v in gg.items():
                 g[f"encoder.channel_reduce.{i}.{k}"] = v
-        for k, v in self.enc.backward([None, None, dt2, dt3]).items():
-            g["encoder.encoder." + k] = v
+        for i, gi in self.enc.backward_iter([None, None, dt2, dt3]):
+            for k, v in gi.items():
+                g["encoder.encoder." + k] = v
+            if i in splits:
+                yield losses, g
+                g = {}
         dn = ops.input_norm_bwd(self.enc.dpatches, raw224, self.affine, bn, 1e-5)                    # encoder.py:129-137
         g["encoder.normalize.weight"], g["encoder.normalize.bias"] = dn[:3].clone(), dn[3:].clone()
-        return losses, g
+        yield losses, g
 
     def _adam(self, grads):
         """torch.optim.Adam over the reference's two groups (train/mars_adapter.py:47-55): encoder.* at lr/10, decoder.* at lr."""
@@ -445,12 +466,15 @@ class DepthTrainer:
 
     def step(self, images, metadata, rnd, grads_hook=None):
         """forward + backward + Adam (encoder.* at lr/10, decoder.* at lr).  ``grads_hook(grads)`` runs between backward and the
-        update: the place for the gradient all-reduce of a data-parallel job.  Returns the three losses (device tensor; with
-        ``graph=True`` a buffer the next step overwrites).
+        update: the place for the gradient all-reduce of a data-parallel job; it may be called several times per step, each time
+        with a disjoint part of the gradients.  Returns the three losses (device tensor; with ``graph=True`` a buffer the next
+        step overwrites).
 
         ``graph=True`` (default): the first step of an input shape runs eagerly (one-time initialisation inside the library must
-        not happen under capture); the second captures two CUDA graphs — [re-pack bf16 operands, forward, loss, backward] and
-        [Adam] — and every step from then on is two graph launches around the hook."""
+        not happen under capture); the second captures the CUDA graphs — [re-pack bf16 operands, forward, loss, backward] and
+        [Adam] — and every step from then on replays them around the hook.  When a hook is present at capture time the backward
+        is cut after the ViT blocks in ``self.splits`` into one graph per stage: the hook of a stage runs on a side stream while
+        the next stage's graph computes (the all-reduce overlaps the rest of the backward)."""
         from .model import source_scale
 
         self.t += 1
@@ -470,18 +494,37 @@ class DepthTrainer:
             st["x"].copy_(images)
             st["rnd"].copy_(rnd)
             torch.cuda.synchronize(self.dev)
-            st["fb"] = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(st["fb"]):
-                st["losses"], st["grads"] = self.forward_backward(st["x"], metadata, st["rnd"])
+            splits = tuple(self.splits) if grads_hook is not None else ()
+            gen = self._stages(st["x"], metadata, st["rnd"], splits)
+            st["fb"], st["parts"], pool = [], [], None
+            for _ in range(len(splits) + 1):
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g, pool=pool):
+                    st["losses"], part = next(gen)
+                pool = g.pool()
+                st["fb"].append(g)
+                st["parts"].append(part)
+            st["grads"] = {k: v for part in st["parts"] for k, v in part.items()}
             self._adam_state(st["grads"])
             st["adam"] = torch.cuda.CUDAGraph()
             with torch.cuda.graph(st["adam"]):
                 self._adam(st["grads"])
+            st["side"] = torch.cuda.Stream(self.dev) if len(st["fb"]) > 1 else None
         else:
             st["x"].copy_(images)
             st["rnd"].copy_(rnd)
-        st["fb"].replay()
-        if grads_hook is not None:
-            grads_hook(st["grads"])
+        cur, side = torch.cuda.current_stream(self.dev), st["side"]
+        for g, part in zip(st["fb"], st["parts"]):
+            g.replay()
+            if grads_hook is None:
+                continue
+            if side is None:
+                grads_hook(part)
+            else:  # this stage's gradients are final: reduce them next to the following stage's graph
+                side.wait_stream(cur)
+                with torch.cuda.stream(side):
+                    grads_hook(part)
+        if side is not None and grads_hook is not None:
+            cur.wait_stream(side)
         st["adam"].replay()
         return st["losses"]

@@ -400,17 +400,26 @@ def test_training_step_matches_train_oracle():
     assert torch.equal(after[untouched], before[untouched])
 
 
-def test_graph_captured_steps_equal_eager_steps():
-    """DepthTrainer(graph=True) replays two CUDA graphs per step from the third step on; every kernel is deterministic, so four
-    steps (eager, capture, replay, replay) must leave exactly the parameters, Adam moments and running statistics of four eager
-    steps, with different images each step."""
+@pytest.mark.parametrize("with_hook", [False, True])
+def test_graph_captured_steps_equal_eager_steps(with_hook):
+    """DepthTrainer(graph=True) replays CUDA graphs from the third step on; every kernel is deterministic, so four steps (eager,
+    capture, replay, replay) must leave exactly the parameters, Adam moments and running statistics of four eager steps, with
+    different images each step.  With a gradient hook (here: halve every gradient, standing in for the all-reduce) the backward
+    is captured as one graph per stage and the hook runs on a side stream next to the following stage."""
     import monodepth_estimation_b200 as mde
     from monodepth_estimation_b200.synth import synth_images, synth_state_dict
     from monodepth_estimation_b200.training import DepthTrainer
 
     B, H, W = 2, 176, 240
     md = {"source": "rover"}
-    results = []
+    results, calls = [], []
+
+    def halve(part):
+        calls.append(len(part))
+        for g in part.values():
+            g.mul_(0.5)
+
+    hook = halve if with_hook else None
     for graph in (False, True):
         m = mde.DepthAnything(pretrained=False)
         m.load_state_dict(synth_state_dict(m.state_dict(), 0))
@@ -420,7 +429,7 @@ def test_graph_captured_steps_equal_eager_steps():
         for i in range(4):
             x = synth_images(B, H, W, 30 + i).cuda()
             rnd = torch.rand(B, 1, H, W, generator=torch.Generator().manual_seed(40 + i)).cuda()
-            losses.append(tr.step(x, md, rnd).clone())
+            losses.append(tr.step(x, md, rnd, hook).clone())
         torch.cuda.synchronize()
         results.append(({k: v.detach().clone() for k, v in m.state_dict().items()}, torch.stack(losses), tr))
     (sd_e, l_e, tr_e), (sd_g, l_g, tr_g) = results
@@ -429,5 +438,7 @@ def test_graph_captured_steps_equal_eager_steps():
     for k in sd_e:
         assert torch.equal(sd_e[k], sd_g[k]), k
     assert int(tr_e.step_dev) == int(tr_g.step_dev) == 4
+    if with_hook:  # eager: one call per step with everything; graph: one eager step, then len(splits) + 1 parts per step
+        assert calls[:4] == [calls[0]] * 4 and len(calls) == 4 + 1 + 3 * (len(tr_g.splits) + 1) and sum(calls[5:9]) == calls[0]
     for k in tr_e.state:
         assert torch.equal(tr_e.state[k][1], tr_g.state[k][1]), k
