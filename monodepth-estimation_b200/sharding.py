@@ -78,13 +78,30 @@ def allreduce_mean_grads(grads: dict, dist=None, bucket_bytes: int = 64 << 20):
     single-device: train/mars_adapter.py:138-140).  Gradients are packed in a fixed (sorted-key) order into flat fp32 buckets of
     about `bucket_bytes`, each bucket is all-reduced once (NCCL over NVLink on the GPU box, gloo in the CPU tests) and divided by
     the world size, then copied back.  Few large collectives instead of ~170 small ones: on NVSwitch the cost is launch latency,
-    not link bandwidth.  Every rank must hold the same keys.  In place; returns the number of collectives issued."""
+    not link bandwidth.  On NCCL the default is instead ONE grouped launch over the gradient tensors in place (no packing copies;
+    ``MDE_ALLREDUCE=bucket`` selects the bucket path).  Every rank must hold the same keys.  In place; returns the number of
+    collectives issued."""
     import torch
 
     if dist is None or not dist.is_initialized() or dist.get_world_size() == 1:
         return 0
     world = dist.get_world_size()
     keys = sorted(grads)
+    import os
+
+    if (dist.get_backend() == "nccl" and os.environ.get("MDE_ALLREDUCE", "coalesced") == "coalesced"
+            and all(g.is_cuda and g.is_contiguous() and g.dtype == torch.float32 for g in grads.values())):
+        # NCCL: one grouped launch over the gradients where they lie (ncclGroupStart/End around per-tensor all-reduces, averaging
+        # inside the collective): no packing copies, nothing but the collective competes with the backward for HBM
+        try:
+            from torch.distributed.distributed_c10d import _coalescing_manager
+
+            with _coalescing_manager(device=grads[keys[0]].device):
+                for k in keys:
+                    dist.all_reduce(grads[k], op=dist.ReduceOp.AVG)
+            return 1
+        except (ImportError, TypeError):
+            pass
     calls, i = 0, 0
     while i < len(keys):
         j, size = i, 0

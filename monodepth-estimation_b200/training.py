@@ -346,7 +346,10 @@ class DepthTrainer:
     def __init__(self, model, lr=1e-4, w_depth=1.0, w_smooth=0.001, betas=(0.9, 0.999), eps=1e-8, graph=True):
         self.model, self.lr, self.w_depth, self.w_smooth, self.betas, self.eps = model, lr, w_depth, w_smooth, betas, eps
         self.graph, self._graphs = graph, {}
-        self.splits = (8, 5, 2)  # ViT blocks after which a data-parallel step starts reducing what it has (see step())
+        # ViT blocks after which a data-parallel step starts reducing what it has (see step()); MDE_TRAIN_SPLITS="9,6,3" overrides
+        import os
+        env = os.environ.get("MDE_TRAIN_SPLITS")
+        self.splits = tuple(int(v) for v in env.split(",") if v != "") if env is not None else (8, 5, 2)
         self.dev = next(model.parameters()).device
         if self.dev.type != "cuda":
             raise RuntimeError("the model must live on a CUDA (sm_100) device: there is no CPU path")

@@ -76,7 +76,7 @@ def main():
     line = {"metric": "train_images_per_sec", "value": round(world * B * a.steps / t, 1), "unit": "images/s", "n_gpus": world, "steps": a.steps,
             "warmup": a.warmup, "ms_per_step": round(t / a.steps * 1e3, 3), "higher_is_better": True, "scaling": "weak", "dtype": "bf16", "data": "synthetic",
             "config": {"workload": f"fine-tuning step (forward + backward + gradient all-reduce + Adam), batch {B}/GPU, 3x{S}x{S} (BASELINE.json configs[4])",
-                       "global_batch": B * world, "collective": "bucketed fp32 gradient all-reduce over NCCL" if world > 1 else "none (one rank)",
+                       "global_batch": B * world, "collective": "fp32 gradient all-reduce over NCCL (one grouped in-place launch per backward stage, overlapped with the next stage)" if world > 1 else "none (one rank)",
                        "launch": "eager" if a.no_graph else "two CUDA graphs per step (forward+backward, Adam) around the all-reduce"},
             "losses_last_step": [round(float(v), 6) for v in losses.cpu()]}
     if rank == 0 and world == 1 and a.cpu_steps > 0:
