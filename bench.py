@@ -154,7 +154,7 @@ def main():
     import monodepth_estimation_b200 as mde
     from monodepth_estimation_b200 import ops
     from monodepth_estimation_b200.sharding import whole_job_rate
-    from monodepth_estimation_b200.synth import synth_images, synth_state_dict
+    from monodepth_estimation_b200.synth import bench_batch, synth_images, synth_state_dict
 
     rank, world, local = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
@@ -182,8 +182,7 @@ def main():
         return m.eval().to(dev)
 
     # one image set per rank (seeded by rank); a batch is 403 MB, i.e. > the 126 MB L2, so no step can be served from cache
-    base = synth_images(min(B, 4), S, S, 1234 + rank)
-    x_host = base.repeat((B + base.shape[0] - 1) // base.shape[0], 1, 1, 1)[:B].contiguous().pin_memory()
+    x_host = bench_batch(B, S, rank).pin_memory()
     x_dev = x_host.to(dev, non_blocking=True)
 
     def timed(model, steps, warmup, feed_host):

@@ -60,6 +60,17 @@ enum mde_padding { MDE_PAD_REFLECT = 0, MDE_PAD_ZERO = 1 };
 
 int mde_version(void);
 const char* mde_last_error(void);
+
+/* Device scratch one forward of `batch` images of height x width needs (kernels never allocate; a host binding
+ * this header sizes its workspace with this call).  The sum of every intermediate of the path — ViT residual stream and taps,
+ * q/k/v, MLP hidden, grid features, decoder activations, low-resolution heads (+ the enhanced extras) — each rounded up to 256
+ * bytes; the Python host (engine.Workspace) allocates exactly these buffers.  Returns a negative mde_status for a size the path
+ * does not serve. */
+typedef struct mde_workspace_cfg {
+  int batch, height, width; /* the INPUT size (the pad-to-/16 resize of model.py:51-54 is applied inside) */
+  int enhanced;             /* 0: models/model.py, 1: models/enhanced_model.py */
+} mde_workspace_cfg;
+long long mde_workspace_bytes(const mde_workspace_cfg* cfg);
 /* MDE_OK iff the current CUDA device is compute capability 10.x. */
 int mde_device_check(void);
 /* Number of SMs of the current device (148 on B200). */
@@ -82,6 +93,10 @@ int mde_resize_bilinear_nchw(const float* src, int B, int C, int Hs, int Ws, flo
  * i.e. `torch.from_numpy(np.array(img)).float().permute(2,0,1) / 255.0` evaluated on the device (IEEE fp32 division,
  * bit-identical to the host expression) so the host->device copy moves 1 byte per sample instead of 4. H*W % 4 == 0. */
 int mde_u8hwc_to_f32chw(const uint8_t* src, int B, int H, int W, float* dst, mde_stream_t stream);
+
+/* ---- caller side, output direction (run_mars_depth.py:131-147 reads outputs[("disp",0)] back with .cpu()): fp32 -> IEEE fp16,
+ * round-to-nearest, saturating — halves the device->host copy of a result map; n values, any n. */
+int mde_f32_to_f16(const float* src, long long n, mde_f16* dst, mde_stream_t stream);
 
 /* ---- encoder.py:139-144 + tv:_process_input: resize to 224^2 (bilinear, align_corners=False),
  * apply affine6, and lay the result out as the patch-embedding GEMM's A operand:
@@ -399,6 +414,22 @@ int mde_adam_step(float* p, const float* g, float* m, float* v, long long n, flo
  * CUDA graph. */
 int mde_adam_step_dev(float* p, const float* g, float* m, float* v, long long n, float lr, float beta1, float beta2, float eps, const int* step_dev,
                       mde_stream_t stream);
+
+/* Multi-tensor Adam: one launch for every parameter tensor.  table_dev[t] (DEVICE memory) names tensor t's parameter, gradient and
+ * the two moment buffers (fp32, contiguous), its length and its learning-rate group; chunk_start_dev[0..n_tensors] is the prefix sum
+ * of ceil(n / mde_adam_chunk_elems()) (n_chunks = its last entry).  lr_groups_dev[group] is read on the device at run time, so a
+ * learning-rate schedule (train/mars_adapter.py:47-61: two groups, StepLR) takes effect between replays of a captured graph. */
+typedef struct mde_adam_tensor {
+  float* p;
+  const float* g;
+  float* m;
+  float* v;
+  long long n;
+  long long group;
+} mde_adam_tensor;
+int mde_adam_chunk_elems(void);
+int mde_adam_multi(const mde_adam_tensor* table_dev, int n_tensors, const int* chunk_start_dev, int n_chunks, const float* lr_groups_dev,
+                   float beta1, float beta2, float eps, const int* step_dev, mde_stream_t stream);
 
 #ifdef __cplusplus
 }

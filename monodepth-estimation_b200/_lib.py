@@ -28,6 +28,10 @@ BILATERAL_SCRATCH_FLOATS = 4128
 _p, _i, _f, _d, _ll = C.c_void_p, C.c_int, C.c_float, C.c_double, C.c_longlong
 
 
+class WorkspaceCfg(C.Structure):
+    _fields_ = [("batch", _i), ("height", _i), ("width", _i), ("enhanced", _i)]
+
+
 class MapDesc(C.Structure):
     _fields_ = [("src", _p), ("hs", _i), ("ws", _i), ("mul", _f), ("dst_disp", _p), ("dst_disp2", _p), ("dst_depth", _p)]
 
@@ -41,6 +45,8 @@ SIGNATURES = {
     "mde_input_range": [_p, _i, _i, _i, _p, _f, _p, _p, _p],
     "mde_resize_bilinear_nchw": [_p, _i, _i, _i, _i, _p, _i, _i, _p],
     "mde_u8hwc_to_f32chw": [_p, _i, _i, _i, _p, _p],
+    "mde_f32_to_f16": [_p, _ll, _p, _p],
+    "mde_workspace_bytes": [_p],
     "mde_preprocess_patchify": [_p, _i, _i, _i, _p, _p, _p],
     "mde_input_stage": [_p, _i, _i, _i, _p, _f, _p, _p, _p, _p, _p],
     "mde_gemm_bf16": [_p, _i, _p, _i, _i, _i, _i, _i, _p, _p, _i, _p, _p, _p],
@@ -94,8 +100,10 @@ SIGNATURES = {
     "mde_depth_loss": [_p, _p, _p, _i, _i, _i, _f, _f, _p, _p, _p, _p],
     "mde_adam_step": [_p, _p, _p, _p, _ll, _f, _f, _f, _f, _i, _p],
     "mde_adam_step_dev": [_p, _p, _p, _p, _ll, _f, _f, _f, _f, _p, _p],
+    "mde_adam_chunk_elems": [],
+    "mde_adam_multi": [_p, _i, _p, _i, _p, _f, _f, _f, _p, _p],
 }
-_RESTYPES = {"mde_last_error": C.c_char_p, "mde_point_cloud_scratch_bytes": C.c_longlong, "mde_layernorm_bwd_scratch_floats": C.c_longlong,
+_RESTYPES = {"mde_last_error": C.c_char_p, "mde_workspace_bytes": C.c_longlong, "mde_point_cloud_scratch_bytes": C.c_longlong, "mde_layernorm_bwd_scratch_floats": C.c_longlong,
              "mde_depth_loss_scratch_floats": C.c_longlong, "mde_input_norm_bwd_scratch_floats": C.c_longlong, "mde_reduce_scratch_bytes": C.c_longlong, "mde_vit_attention_bwd_scratch_floats": C.c_longlong}
 
 _lock = threading.Lock()

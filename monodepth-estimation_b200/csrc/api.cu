@@ -107,3 +107,73 @@ extern "C" int mde_device_check(void) {
   }
   return MDE_OK;
 }
+
+// Mirrors engine.Workspace buffer for buffer (tests/test_dropin_cpu.py compares the two on the meta device).
+extern "C" long long mde_workspace_bytes(const mde_workspace_cfg* cfg) {
+  if (!cfg || cfg->batch <= 0 || cfg->height <= 0 || cfg->width <= 0) {
+    mde::set_error("mde_workspace_bytes: bad configuration");
+    return MDE_ERR_BAD_ARGUMENT;
+  }
+  const long long B = cfg->batch;
+  long long Hp = cfg->height, Wp = cfg->width;
+  const bool padded = Hp % 16 || Wp % 16;
+  if (padded) {
+    Hp = (Hp / 16 + 1) * 16;
+    Wp = (Wp / 16 + 1) * 16;
+  }
+  long long gh = Hp / 16, gw = Wp / 16;
+  if (gh * gw == 197 || (Hp * Wp) % 4) {
+    mde::set_error("mde_workspace_bytes: unsupported input size");
+    return MDE_ERR_UNSUPPORTED;
+  }
+  if (gh * gw != 196) gh = 14, gw = 15;  // encoder.py:69-110 for 197 tokens
+  const long long G = gh * gw, M = B * MDE_VIT_SEQ, P = (gh + 2) * (gw + 2);
+  long long total = 0;
+  auto add = [&](long long bytes) { total += (bytes + 255) / 256 * 256; };
+  if (padded) add(B * 3 * Hp * Wp * 4);                 // xp
+  add((long long)MDE_RANGE_SCRATCH_FLOATS * 4);          // scratch
+  add(6 * 4);                                            // affine
+  add(B * 196 * 768 * 2);                                // patches
+  add(B * 3 * 224 * 224 * 4);                            // raw224
+  for (int i = 0; i < 6; ++i) add(M * 768 * 4);          // xa, xb, taps[4]
+  add(M * 768 * 2);                                      // h
+  add(24 * M * 2 * 4);                                   // lnstats
+  add(B * 12 * MDE_VIT_SEQ * 64 * 2);                    // q
+  add(B * 12 * MDE_VIT_SEQ * 64 * 2);                    // k
+  add(B * 12 * 64 * MDE_VT_PITCH * 2);                   // vt
+  add(M * 768 * 2);                                      // attn
+  add(M * 3072 * 2);                                     // mlp
+  for (int i = 0; i < 4; ++i) add(B * G * 768 * 2);      // grid_a
+  for (int i = 0; i < 4; ++i) add(B * G * 256 * 4);      // reduced
+  add(B * P * (cfg->enhanced ? 320 : 256) * 2);          // feats[0]
+  for (int i = 0; i < 3; ++i) add(B * P * 256 * 2);      // feats[1..3]
+  add(B * P * 256 * 2);                                  // d_init
+  static const int ch[5] = {256, 128, 64, 32, 16};
+  long long h = gh, w = gw;
+  for (int i = 0; i < 4; ++i) {
+    const long long co = ch[i + 1];
+    add(B * (h + 2) * (w + 2) * co * 2);                 // d_a
+    if (i < 3) add(B * P * co * 2);                      // d_s
+    h *= 2;
+    w *= 2;
+    add(B * (h + 2) * (w + 2) * co * (i < 3 ? 2 : 1) * 2);  // d_cat
+    add(B * (h + 2) * (w + 2) * co * 2);                 // d_x
+    add(B * h * w * 4);                                  // disp
+  }
+  add(B * (h + 2) * (w + 2) * 16 * 2);                   // d_x3b
+  if (cfg->enhanced) {
+    for (int i = 0; i < 2; ++i) {
+      add(B * G * 256 * 2);                              // flat
+      add(B * G * 384 * 4);                              // qkv
+      add(B * P * 256 * 2);                              // enh
+    }
+    add(B * P * 128 * 2);                                // u1
+    add(B * P * 128 * 2);                                // u2
+    add(B * P * 256 * 2);                                // r1
+    add(B * P * 128 * 2);                                // r2
+    add(B * gh * gw * 4);                                // unc
+    add(B * gh * gw * 4);                                // refn
+    add(B * 4 * gh * gw * 4);                            // fused
+  }
+  return total;
+}

@@ -903,6 +903,30 @@ extern "C" int mde_u8hwc_to_f32chw(const uint8_t* src, int B, int H, int W, floa
   return MDE_OK;
 }
 
+__global__ void __launch_bounds__(256) f32_to_f16_kernel(const float* __restrict__ src, long long n, uint16_t* __restrict__ dst) {
+  pdl_launch_dependents();
+  pdl_grid_wait();
+  const long long n8 = n >> 3;
+  const float4* s4 = reinterpret_cast<const float4*>(src);
+  uint4* d4 = reinterpret_cast<uint4*>(dst);
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (long long)gridDim.x * blockDim.x) {
+    const float4 a = __ldcs(s4 + 2 * i), b = __ldcs(s4 + 2 * i + 1);
+    __stcs(d4 + i, make_uint4(pack_f16x2(a.x, a.y), pack_f16x2(a.z, a.w), pack_f16x2(b.x, b.y), pack_f16x2(b.z, b.w)));
+  }
+  if (blockIdx.x == 0 && threadIdx.x < (n & 7)) {
+    const long long i = (n8 << 3) + threadIdx.x;
+    dst[i] = static_cast<uint16_t>(pack_f16x2(src[i], 0.0f) & 0xFFFFu);
+  }
+}
+
+extern "C" int mde_f32_to_f16(const float* src, long long n, mde_f16* dst, mde_stream_t stream) {
+  MDE_CHECK_ARG(src && dst && n > 0, "mde_f32_to_f16: bad arguments");
+  MDE_CHECK_ARG((uintptr_t)src % 16 == 0 && (uintptr_t)dst % 16 == 0, "mde_f32_to_f16: pointers must be 16-byte aligned");
+  launch_k(f32_to_f16_kernel, dim3(grid_for(n >> 3, 256)), dim3(256), 0, stream, src, n, dst);
+  MDE_CHECK_LAUNCH();
+  return MDE_OK;
+}
+
 extern "C" int mde_input_stage(const float* x, int B, int H, int W, const float* bn4x3, float eps, float* scratch, float* affine6,
                                float* raw224, mde_bf16* patches, mde_stream_t stream) {
   MDE_CHECK_ARG(x && bn4x3 && scratch && affine6 && raw224 && patches, "mde_input_stage: null pointer");

@@ -35,7 +35,9 @@ def grid_shape(Hp: int, Wp: int):
 
 
 def _fingerprint(module):
-    return tuple((t.data_ptr(), t._version, t.device.index) for t in list(module.parameters()) + list(module.buffers()))
+    """Identity of the weights the packed copies were made from.  ``_mde_gen`` is bumped by code that rewrites parameters through
+    raw pointers (training.DepthTrainer), which ``tensor._version`` cannot see."""
+    return (module.__dict__.get("_mde_gen", 0),) + tuple((t.data_ptr(), t._version, t.device.index) for t in list(module.parameters()) + list(module.buffers()))
 
 
 _LN_FUSION = os.environ.get("MDE_LN_FUSION") == "1"  # opt-in, see DepthEngine._vit
@@ -54,8 +56,14 @@ class Workspace:
         gh, gw = self.gh, self.gw
         G = gh * gw
         M = B * L.VIT_SEQ
-        e = lambda *s, dt=BF16: torch.empty(*s, device=dev, dtype=dt)
-        z = lambda *s, dt=BF16: torch.zeros(*s, device=dev, dtype=dt)
+        self.nbytes = 0  # sum of the buffers below, each rounded up to 256 bytes == mde_workspace_bytes() (tests/test_dropin_cpu.py)
+
+        def e(*s, dt=BF16, zero=False):
+            t = (torch.zeros if zero else torch.empty)(*s, device=dev, dtype=dt)
+            self.nbytes += (t.numel() * t.element_size() + 255) // 256 * 256
+            return t
+
+        z = lambda *s, dt=BF16: e(*s, dt=dt, zero=True)
         self.xp = e(B, 3, Hp, Wp, dt=F32) if (Hp, Wp) != (H0, W0) else None
         self.scratch = e(L.RANGE_SCRATCH_FLOATS, dt=F32)
         self.affine = e(6, dt=F32)

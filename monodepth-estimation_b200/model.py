@@ -52,8 +52,8 @@ class _EngineMixin:
     def _check_input(self, x):
         if self.training:
             raise RuntimeError(
-                "this implementation covers the inference forward only (BatchNorm running statistics); "
-                "call model.eval() first — the training step is SURVEY.md §8(f)#1, not built"
+                "model(x) is the inference forward (BatchNorm running statistics): call model.eval() first.  The training step "
+                "(train/mars_adapter.py:117-153) runs through monodepth_estimation_b200.training.DepthTrainer(model).step(...)"
             )
         if not (isinstance(x, torch.Tensor) and x.dim() == 4 and x.shape[1] == 3):
             raise ValueError(f"expected an image batch [B,3,H,W], got {getattr(x, 'shape', type(x))}")

@@ -40,6 +40,21 @@ def sm_count() -> int:
     return int(L.load().mde_sm_count())
 
 
+def workspace_bytes(batch: int, height: int, width: int, enhanced: bool) -> int:
+    """``mde_workspace_bytes``: device scratch of one forward (what ``engine.Workspace`` allocates).  No device work."""
+    cfg = L.WorkspaceCfg(int(batch), int(height), int(width), int(bool(enhanced)))
+    n = int(L.load().mde_workspace_bytes(C.byref(cfg)))
+    if n < 0:
+        L.check(n, "mde_workspace_bytes")
+    return n
+
+
+def f32_to_f16(src, out=None):
+    out = out if out is not None else torch.empty(src.shape, device=src.device, dtype=F16)
+    L.call("mde_f32_to_f16", _ptr(src, F32), src.numel(), _ptr(out, F16), _stream())
+    return out
+
+
 def input_range(x, bn4x3, eps, scratch=None, affine=None):
     B, _, H, W = x.shape
     scratch = scratch if scratch is not None else torch.empty(L.RANGE_SCRATCH_FLOATS, device=x.device, dtype=F32)
@@ -458,3 +473,29 @@ def adam_step(p, g, m, v, lr, step, beta1=0.9, beta2=0.999, eps=1e-8):
         L.call("mde_adam_step", _ptr(p, F32), _ptr(g, F32), _ptr(m, F32), _ptr(v, F32), p.numel(), float(lr), float(beta1), float(beta2), float(eps), int(step),
                _stream())
     return p
+
+
+class AdamPlan:
+    """Device tables of ``mde_adam_multi`` for a fixed set of (parameter, gradient, exp_avg, exp_avg_sq, group) tensors: built once
+    (the pointers are baked in, as a captured CUDA graph needs anyway), launched once per step."""
+
+    def __init__(self, entries):
+        chunk = int(L.load().mde_adam_chunk_elems())
+        rows, starts, total = [], [0], 0
+        self.keep = []
+        for p, g, m, v, group in entries:
+            for t in (p, g, m, v):
+                if not (t.is_cuda and t.is_contiguous() and t.dtype == F32 and t.numel() == p.numel()):
+                    raise ValueError("Adam tensors must be contiguous fp32 CUDA tensors of one size")
+            rows.append([p.data_ptr(), g.data_ptr(), m.data_ptr(), v.data_ptr(), p.numel(), int(group)])
+            total += (p.numel() + chunk - 1) // chunk
+            starts.append(total)
+            self.keep.append((p, g, m, v))
+        dev = entries[0][0].device
+        self.table = torch.tensor(rows, dtype=torch.int64).to(dev)
+        self.starts = torch.tensor(starts, dtype=torch.int32).to(dev)
+        self.n, self.chunks = len(rows), total
+
+    def step(self, lr_groups, step_dev, beta1=0.9, beta2=0.999, eps=1e-8):
+        L.call("mde_adam_multi", _ptr(self.table, torch.int64), self.n, _ptr(self.starts, torch.int32), self.chunks, _ptr(lr_groups, F32),
+               float(beta1), float(beta2), float(eps), _ptr(step_dev, torch.int32), _stream())

@@ -82,3 +82,10 @@ def synth_images(batch: int, height: int, width: int, seed: int = 1234, kind: st
     elif kind != "unit":
         raise ValueError(kind)
     return torch.from_numpy(img)
+
+
+def bench_batch(batch: int, size: int, rank: int = 0) -> torch.Tensor:
+    """The benchmark's input batch (bench.py and the parity tests at the benchmarked configurations share it): up to four
+    distinct synthetic images per rank, repeated to `batch` — at 1024 px a batch of 32 is 403 MB, well past the 126 MB L2."""
+    base = synth_images(min(batch, 4), size, size, 1234 + rank)
+    return base.repeat((batch + base.shape[0] - 1) // base.shape[0], 1, 1, 1)[:batch].contiguous()

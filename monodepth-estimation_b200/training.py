@@ -363,6 +363,12 @@ class DepthTrainer:
         self.head = _DispHeadT(d("decoder.convs.dispconv_0.weight"), d("decoder.convs.dispconv_0.bias"), self.dev)
         self.state, self.t = {}, 0
         self.step_dev = torch.zeros(1, device=self.dev, dtype=torch.int32)  # Adam's step count where a replayed graph can read it
+        # the two learning rates (train/mars_adapter.py:47-55: encoder.* at lr / 10, the rest at lr) live on the device too: a
+        # captured Adam graph reads them at run time, so set_lr() / a StepLR schedule (:57-61) takes effect on the next step
+        self.lr_dev = torch.tensor([lr / 10, lr], device=self.dev, dtype=F32)
+        # BatchNorm layers that run in train mode here: their num_batches_tracked advances once per step, as nn.BatchNorm2d does
+        self.nbt = [self.sd[k] for k in (["encoder.normalize.num_batches_tracked"] +
+                                         [f"decoder.convs.{n}.conv.1.num_batches_tracked" for n in ("init_conv", "upconv_0_0", "skip_0", "upconv_0_1")])]
         self.scratch = torch.empty(L.RANGE_SCRATCH_FLOATS, device=self.dev, dtype=F32)
         self.affine = torch.empty(6, device=self.dev, dtype=F32)
 
@@ -452,14 +458,37 @@ class DepthTrainer:
         g["encoder.normalize.weight"], g["encoder.normalize.bias"] = dn[:3].clone(), dn[3:].clone()
         yield losses, g
 
-    def _adam(self, grads):
-        """torch.optim.Adam over the reference's two groups (train/mars_adapter.py:47-55): encoder.* at lr/10, decoder.* at lr."""
+    def set_lr(self, lr: float):
+        """Change the base learning rate (group 0 = encoder.* gets lr / 10).  Safe between replays of the captured step."""
+        self.lr = float(lr)
+        self.lr_dev.copy_(torch.tensor([self.lr / 10, self.lr], dtype=F32), non_blocking=False)
+
+    def lr_scheduler_step(self, epoch: int, step_size: int = 5, gamma: float = 0.5, base_lr: float | None = None):
+        """torch.optim.lr_scheduler.StepLR as the reference configures it (train/mars_adapter.py:57-61): lr = base * gamma^(epoch // step_size)."""
+        if base_lr is not None:
+            self._base_lr = float(base_lr)
+        base = self.__dict__.setdefault("_base_lr", self.lr)
+        self.set_lr(base * gamma ** (epoch // step_size))
+
+    def _adam(self, grads, plan=None):
+        """torch.optim.Adam over the reference's two groups (train/mars_adapter.py:47-55): encoder.* at lr/10, decoder.* at lr.
+        One multi-tensor launch (``mde_adam_multi``); ``plan`` caches its device tables when the gradient buffers are stable."""
         self.step_dev += 1
+        torch._foreach_add_(self.nbt, 1)
+        if plan is None:
+            plan = self._adam_plan(grads)
+        plan.step(self.lr_dev, self.step_dev, self.betas[0], self.betas[1], self.eps)
+        return plan
+
+    def _adam_plan(self, grads):
+        entries = []
         for k, gk in grads.items():
             p = self.sd[k].detach()
             m, v = self.state[k]
-            ops.adam_step(p, gk.reshape(p.shape).contiguous(), m, v, self.lr / 10 if k.startswith("encoder.") else self.lr, self.step_dev, self.betas[0],
-                          self.betas[1], self.eps)
+            if not gk.is_contiguous() or gk.numel() != p.numel():
+                raise RuntimeError(f"gradient of {k} must be a contiguous tensor of the parameter's size (its pointer is baked into the Adam table)")
+            entries.append((p, gk.view(p.shape), m, v, 0 if k.startswith("encoder.") else 1))
+        return ops.AdamPlan(entries)
 
     def _adam_state(self, grads):
         for k in grads:
@@ -489,6 +518,7 @@ class DepthTrainer:
                 grads_hook(grads)
             self._adam_state(grads)
             self._adam(grads)
+            self._invalidate_inference()
             if self.graph:
                 self._graphs[key] = {}
             return losses
@@ -509,9 +539,10 @@ class DepthTrainer:
                 st["parts"].append(part)
             st["grads"] = {k: v for part in st["parts"] for k, v in part.items()}
             self._adam_state(st["grads"])
+            st["adam_plan"] = self._adam_plan(st["grads"])  # gradient buffers live in the graphs' pool: pointers are stable
             st["adam"] = torch.cuda.CUDAGraph()
             with torch.cuda.graph(st["adam"]):
-                self._adam(st["grads"])
+                self._adam(st["grads"], st["adam_plan"])
             st["side"] = torch.cuda.Stream(self.dev) if len(st["fb"]) > 1 else None
         else:
             st["x"].copy_(images)
@@ -530,4 +561,12 @@ class DepthTrainer:
         if side is not None and grads_hook is not None:
             cur.wait_stream(side)
         st["adam"].replay()
+        self._invalidate_inference()
         return st["losses"]
+
+    def _invalidate_inference(self):
+        """Parameters and BatchNorm buffers were just rewritten through raw pointers (tensor._version did not move): bump the
+        module's generation so that the inference engine re-packs its bf16 weights and drops its CUDA graphs on the next
+        ``model.eval(); model(x)`` (engine._fingerprint)."""
+        d = self.model.__dict__
+        d["_mde_gen"] = d.get("_mde_gen", 0) + 1

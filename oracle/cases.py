@@ -16,6 +16,7 @@ CASES = {
     "enh_1024_b1_rover":      ("enhanced", 1, 1024, 1024, "unit", {"source": "rover"}, 0, 24),
     "std_1024_b1_rover":      ("standard", 1, 1024, 1024, "unit", {"source": "rover"}, 0, 25),
     "cfg4_256_b1_rover":      ("config4",  1, 256, 256, "unit",   {"source": "rover"}, 0, 31),
+    "cfg4_1024_b1_rover":     ("config4",  1, 1024, 1024, "unit", {"source": "rover"}, 0, 32),  # BASELINE.json config 4 at its own size
 }
 
 # stand-alone refinement.py module cases: name -> (H, W, rgb H, rgb W, seed)

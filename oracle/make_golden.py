@@ -5,6 +5,7 @@ not exist on the GPU box) on the deterministic synthetic weights/inputs of
 ``oracle/depth_oracle.py`` against them while doing so.
 
     python oracle/make_golden.py            # writes tests/golden, prints max deviations
+    python oracle/make_golden.py --only cfg4_1024_b1_rover   # (re)generate the named model cases only
 
 Each .npz holds, per output map, a strided subsample (``cases.stride_for``) plus the
 full-map mean/std/min/max in float64, and the torch/torchvision versions used.
@@ -68,12 +69,15 @@ def ref_refine_live(m, depth, rgb):
 
 
 def main():
+    only = set(sys.argv[sys.argv.index("--only") + 1:]) if "--only" in sys.argv else None
     os.makedirs(GOLD, exist_ok=True)
     torch.manual_seed(0)
     models = {}
     worst = 0.0
     with torch.no_grad():
         for name, (kind, B, H, W, ikind, md, wseed, iseed) in CASES.items():
+            if only is not None and name not in only:
+                continue
             base = "enhanced" if kind == "config4" else kind
             mk = (base, wseed)
             if mk not in models:
@@ -103,7 +107,7 @@ def main():
                 print(f"{name:28s} {str(k):24s} oracle-vs-reference max_abs {ma:.3e} rel_l2 {rl:.3e}")
             np.savez_compressed(os.path.join(GOLD, name + ".npz"), **pack(out))
 
-        for name, (H, W, rh, rw, seed) in REFINE_CASES.items():
+        for name, (H, W, rh, rw, seed) in ({} if only is not None else REFINE_CASES).items():
             rf = RefRefine().eval()
             rf.load_state_dict(synth_state_dict(rf.state_dict(), seed))
             depth = synth_images(1, H, W, seed, "unit")[:, :1].contiguous()
@@ -119,7 +123,7 @@ def main():
             worst = max(worst, dev(got, want)[1])
             np.savez_compressed(os.path.join(GOLD, name + ".npz"), **pack({"refined": want}))
 
-        for name, (H, W, seed) in FUSION_CASES.items():
+        for name, (H, W, seed) in ({} if only is not None else FUSION_CASES).items():
             fu = RefFusion().eval()
             fu.load_state_dict(synth_state_dict(fu.state_dict(), seed))
             maps = {("disp", s): synth_images(1, H >> s, W >> s, seed + s, "unit")[:, :1].contiguous() for s in range(4)}

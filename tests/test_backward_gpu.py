@@ -442,3 +442,92 @@ def test_graph_captured_steps_equal_eager_steps(with_hook):
         assert calls[:4] == [calls[0]] * 4 and len(calls) == 4 + 1 + 3 * (len(tr_g.splits) + 1) and sum(calls[5:9]) == calls[0]
     for k in tr_e.state:
         assert torch.equal(tr_e.state[k][1], tr_g.state[k][1]), k
+
+
+def test_adam_multi_matches_torch_and_reads_lr_from_the_device():
+    """mde_adam_multi: ONE launch over tensors of ragged sizes (vector path, unaligned tails, a 1-element tensor), two
+    learning-rate groups read from device memory — so a schedule change between steps takes effect without re-building anything
+    (train/mars_adapter.py:47-61)."""
+    L, ops = _mods()
+    sizes = [100003, 4096, 7, 1, 768 * 3072, 12289]
+    ps = [torch.nn.Parameter(_rand(n, seed=100 + i)) for i, n in enumerate(sizes)]
+    groups = [i % 2 for i in range(len(sizes))]
+    lrs = [1e-5, 1e-4]
+    opt = torch.optim.Adam([{"params": [p for p, g in zip(ps, groups) if g == 0], "lr": lrs[0]},
+                            {"params": [p for p, g in zip(ps, groups) if g == 1], "lr": lrs[1]}])
+    mine = [p.detach().clone() for p in ps]
+    gbuf = [torch.empty_like(p) for p in mine]
+    ms, vs = [torch.zeros_like(p) for p in mine], [torch.zeros_like(p) for p in mine]
+    plan = ops.AdamPlan([(p, g, m, v, grp) for p, g, m, v, grp in zip(mine, gbuf, ms, vs, groups)])
+    lr_dev = torch.tensor(lrs, device="cuda")
+    step_dev = torch.zeros(1, device="cuda", dtype=torch.int32)
+    for step in range(1, 5):
+        if step == 3:  # StepLR fires: both groups halve
+            for gparam in opt.param_groups:
+                gparam["lr"] *= 0.5
+            lr_dev.mul_(0.5)
+        for i, p in enumerate(ps):
+            g = _rand(sizes[i], seed=200 + 10 * step + i)
+            p.grad = g.clone()
+            gbuf[i].copy_(g)
+        opt.step()
+        step_dev += 1
+        plan.step(lr_dev, step_dev)
+    for a, p in zip(mine, ps):
+        assert max_abs(a, p.detach()) < 1e-6
+
+
+def test_inference_after_training_uses_the_new_weights():
+    """DepthTrainer rewrites parameters and running statistics through raw pointers, so tensor._version does not
+    move; the engine must still re-pack.  infer -> train -> infer must equal a fresh model loaded from the new state_dict."""
+    import monodepth_estimation_b200 as mde
+    from monodepth_estimation_b200.synth import synth_images, synth_state_dict
+    from monodepth_estimation_b200.training import DepthTrainer
+
+    m = mde.DepthAnything(pretrained=False)
+    m.load_state_dict(synth_state_dict(m.state_dict(), 0))
+    m = m.cuda().eval()
+    x = synth_images(2, 176, 240, 5).cuda()
+    md = {"source": "rover"}
+    before = m(x, md)[("disp", 0)].clone()
+    m(x, md)  # graph replay path is live
+    tr = DepthTrainer(m, lr=1e-2)
+    rnd = torch.rand(2, 1, 176, 240, generator=torch.Generator().manual_seed(9)).cuda()
+    for _ in range(3):  # eager, capture, replay
+        m.train()
+        tr.step(x, md, rnd)
+        m.eval()
+        after = m(x, md)[("disp", 0)].clone()
+        fresh = mde.DepthAnything(pretrained=False)
+        fresh.load_state_dict({k: v.detach().cpu().clone() for k, v in m.state_dict().items()})
+        want = fresh.cuda().eval()(x, md)[("disp", 0)]
+        assert torch.equal(after, want)
+    assert not torch.equal(after, before)
+    nbt = m.state_dict()["decoder.convs.init_conv.conv.1.num_batches_tracked"]
+    assert int(nbt) == 3 and int(m.state_dict()["encoder.normalize.num_batches_tracked"]) == 3
+
+
+def test_learning_rate_change_reaches_the_captured_step():
+    """the learning rate is read from device memory by the captured Adam launch; lr = 0 must freeze the weights."""
+    import monodepth_estimation_b200 as mde
+    from monodepth_estimation_b200.synth import synth_images, synth_state_dict
+    from monodepth_estimation_b200.training import DepthTrainer
+
+    m = mde.DepthAnything(pretrained=False)
+    m.load_state_dict(synth_state_dict(m.state_dict(), 0))
+    m = m.cuda()
+    tr = DepthTrainer(m, lr=1e-3)
+    x = synth_images(2, 176, 240, 6).cuda()
+    rnd = torch.rand(2, 1, 176, 240, generator=torch.Generator().manual_seed(3)).cuda()
+    key = "decoder.convs.upconv_0_1.conv.0.conv.1.weight"
+    for _ in range(3):
+        tr.step(x, None, rnd)  # third step replays the graphs
+    w3 = m.state_dict()[key].clone()
+    tr.set_lr(0.0)
+    tr.step(x, None, rnd)
+    assert torch.equal(m.state_dict()[key], w3)
+    tr.lr_scheduler_step(epoch=5, step_size=5, gamma=0.5, base_lr=1e-3)  # StepLR: 1e-3 * 0.5
+    assert abs(tr.lr - 5e-4) < 1e-12
+    tr.step(x, None, rnd)
+    d = (m.state_dict()[key] - w3).abs().max()
+    assert 0 < float(d) <= 5e-4 * 1.5  # moved, by at most ~lr (Adam's per-step bound once the moments are warm: <= lr * (1 + small))

@@ -25,6 +25,19 @@ def test_library_exports_every_declared_symbol():
     assert lib.mde_version() >= 100
 
 
+@pytest.mark.parametrize("cfg", [(1, 224, 224, False), (2, 518, 518, True), (32, 1024, 1024, False), (32, 1024, 1024, True), (3, 256, 320, True)])
+def test_workspace_bytes_matches_the_python_workspace(cfg):
+    """mde_workspace_bytes(cfg) is what a C/C++ host sizes its scratch with; engine.Workspace allocates exactly that."""
+    from monodepth_estimation_b200 import ops
+    from monodepth_estimation_b200.engine import Workspace
+
+    B, H, W, enh = cfg
+    ws = Workspace(torch.device("meta"), B, H, W, enh)
+    assert ops.workspace_bytes(B, H, W, enh) == ws.nbytes
+    with pytest.raises(RuntimeError):
+        ops.workspace_bytes(0, 224, 224, False)
+
+
 def test_no_cpu_fallback_and_train_mode_raises():
     m = mde.DepthAnything(pretrained=False)
     with pytest.raises(RuntimeError):

@@ -6,25 +6,11 @@ fp32 accumulate, vs the fp32 reference)."""
 import pytest
 import torch
 
-from helpers import DEPTH_REL_L2, UNCERTAINTY_MAX_ABS, cached_model, load_golden, max_abs, rel_l2, synth_images
+from helpers import DEPTH_REL_L2, UNCERTAINTY_MAX_ABS, cached_model, check_outputs, load_golden, max_abs, rel_l2, synth_images
 from oracle import depth_oracle as O
 from oracle.cases import CASES, key_name, stride_for
 
 pytestmark = pytest.mark.gpu
-
-
-def check_outputs(got, ref, where):
-    assert set(got) == set(ref), (set(got) ^ set(ref))
-    for k in ref:
-        g, r = got[k].float().cpu(), ref[k]
-        assert g.shape == r.shape, (k, g.shape, r.shape)
-        assert torch.isfinite(g).all(), k
-        if k[0] == "uncertainty":
-            assert max_abs(g, r) <= UNCERTAINTY_MAX_ABS, (where, k, max_abs(g, r))
-        else:
-            assert rel_l2(g, r) <= DEPTH_REL_L2, (where, k, rel_l2(g, r))
-        if k[0] == "disp":  # what the callers compute, run_mars_depth.py:137
-            assert rel_l2(1 / g.clamp(min=1e-6), 1 / r.clamp(min=1e-6)) <= DEPTH_REL_L2, (where, k, "1/disp")
 
 
 @pytest.mark.parametrize("name", ["std_224_b2_none", "std_256x320_b1_ingalt", "std_256_b1_byte_other", "std_256_b1_signed_none",
@@ -49,15 +35,7 @@ def test_model_vs_reference_golden(name):
     gold = load_golden(name)
     m = cached_model(kind, wseed, "cuda")
     got = m(synth_images(B, H, W, iseed, ikind).cuda(), md)
-    for k, v in got.items():
-        n = key_name(k)
-        ref = torch.from_numpy(gold[n])
-        sy, sx = stride_for(v.shape[2]), stride_for(v.shape[3])
-        g = v[:, :, ::sy, ::sx].float().cpu()
-        if k[0] == "uncertainty":
-            assert max_abs(g, ref) <= UNCERTAINTY_MAX_ABS, (k, max_abs(g, ref))
-        else:
-            assert rel_l2(g, ref) <= DEPTH_REL_L2, (k, rel_l2(g, ref))
+    check_outputs(got, gold, "golden:" + name, subsample=True)
 
 
 @pytest.mark.parametrize("kind", ["standard", "enhanced"])
