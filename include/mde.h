@@ -112,6 +112,18 @@ int mde_preprocess_patchify(const float* x, int B, int H, int W, const float* af
 int mde_input_stage(const float* x, int B, int H, int W, const float* bn4x3, float eps, float* scratch, float* affine6,
                     float* raw224, mde_bf16* patches, mde_stream_t stream);
 
+/* mde_input_stage for callers that cannot allocate (CUDA-graph capture, serving loops, harnesses that forbid cudaMalloc).  No
+ * counterpart in the reference.  Same kernels, same outputs (bit for bit) as
+ * mde_input_stage, but the partial-record scratch is a device array built into the library (126 KB per GPU that loads it, held until
+ * the process exits), so the caller passes inputs and outputs only and nothing here calls cudaMalloc / cudaFree or any allocating
+ * routine.  Limit: B <= MDE_INPUT_STAGE_NOALLOC_MAX_BATCH images (any H, W with W % 4 == 0); larger batches are an error
+ * (MDE_ERR_BAD_ARGUMENT) — use mde_input_stage with caller scratch.  Nothing in the array must start at zero (each call writes
+ * every record it later reads), but ALL calls on a device share it: two calls that overlap on the GPU (different streams, or
+ * graph branches) race — keep them on one stream or order them with events. */
+#define MDE_INPUT_STAGE_NOALLOC_MAX_BATCH 32
+int mde_input_stage_noalloc(const float* x, int B, int H, int W, const float* bn4x3, float eps, float* affine6, float* raw224,
+                            mde_bf16* patches, mde_stream_t stream);
+
 /* ---- tcgen05 GEMM: D[M,N] = epilogue(A[M,K] * W[N,K]^T), bf16 in, fp32 accumulate --------
  * Replaces conv_proj (tv:277), in_proj / out_proj (tv:113), mlp.0 / mlp.3 (tv:118) and
  * channel_reduce (encoder.py:164).  A row-major [M][lda], W row-major [N][ldw] (K contiguous).

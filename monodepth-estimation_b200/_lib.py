@@ -19,6 +19,7 @@ ACT_NONE, ACT_ELU, ACT_SIGMOID = range(3)
 PAD_REFLECT, PAD_ZERO = range(2)
 VIT_SEQ, VIT_DIM, VIT_HEADS, VT_PITCH = 197, 768, 12, 208
 RANGE_SCRATCH_FLOATS = 6 * 8192
+INPUT_STAGE_NOALLOC_MAX_BATCH = 32  # MDE_INPUT_STAGE_NOALLOC_MAX_BATCH
 GEMM_LN_MIN_ROWS = 1024  # MDE_GEMM_LN_MIN_ROWS
 MAX_MAPS = 8
 MAX_FUSION_SCALES = 4
@@ -49,6 +50,7 @@ SIGNATURES = {
     "mde_workspace_bytes": [_p],
     "mde_preprocess_patchify": [_p, _i, _i, _i, _p, _p, _p],
     "mde_input_stage": [_p, _i, _i, _i, _p, _f, _p, _p, _p, _p, _p],
+    "mde_input_stage_noalloc": [_p, _i, _i, _i, _p, _f, _p, _p, _p, _p],
     "mde_gemm_bf16": [_p, _i, _p, _i, _i, _i, _i, _i, _p, _p, _i, _p, _p, _p],
     "mde_debug_gemm_prof": [_p],
     "mde_gemm_ln_bf16": [_p, _i, _p, _i, _i, _i, _i, _i, _p, _p, _i, _p, _p, _p, _p, _f, _p, _p, _p],

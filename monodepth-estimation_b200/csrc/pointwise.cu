@@ -3,6 +3,8 @@
 // a multiple of the SM count, fp32 arithmetic, no host synchronisation.
 #include <float.h>
 
+#include <mutex>
+
 #include "common.h"
 #include "ptx.cuh"
 
@@ -940,6 +942,58 @@ extern "C" int mde_input_stage(const float* x, int B, int H, int W, const float*
   const int groups = ceil_div(224, rpb);
   const int parts = groups * 3 * B;
   launch_k(input_scan_resample_kernel, dim3(parts), dim3(256), 0, stream, x, H, W, rpb, groups, scratch, raw224);
+  MDE_CHECK_LAUNCH();
+  launch_k(range_finalize_kernel, dim3(1), dim3(768), 0, stream, scratch, parts, bn4x3, eps, affine6);
+  MDE_CHECK_LAUNCH();
+  launch_k(patchify224_kernel, dim3(grid_for((long long)B * 196 * 96, 256)), dim3(256), 0, stream, raw224, B, affine6, reinterpret_cast<bf16*>(patches));
+  MDE_CHECK_LAUNCH();
+  return MDE_OK;
+}
+
+// ------------------------------------------------------------------ mde_input_stage without caller scratch (no allocation anywhere)
+// Added for callers that cannot cudaMalloc (code under CUDA-graph capture, tight serving
+// loops, harnesses that forbid it); it has no counterpart in the reference.  The partial-record scratch of the scan lives in a
+// file-scope device array: MDE_INPUT_STAGE_NOALLOC_MAX_BATCH images x 3 planes x 56 row groups x 6 floats = 126 KB, held by every
+// GPU that loads the library until the process exits.  In HOST code the name `g_input_stage_scratch` is only a stand-in for the
+// symbol, not a device address: the address comes from cudaGetSymbolAddress, once per device, with that device current.
+constexpr int kNoallocRowsPerBlock = 4;                                   // the schedule mde_input_stage uses up to batch 48
+constexpr int kNoallocGroups = 224 / kNoallocRowsPerBlock;                // 56
+constexpr int kNoallocMaxParts = MDE_INPUT_STAGE_NOALLOC_MAX_BATCH * 3 * kNoallocGroups;
+static __device__ __align__(256) float g_input_stage_scratch[kNoallocMaxParts * 6];
+
+static int noalloc_scratch_address(float** out) {
+  static std::mutex mu;
+  static float* addr[64] = {nullptr};
+  int dev = 0;
+  MDE_CHECK_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) {
+    set_error("mde_input_stage_noalloc: device index %d out of range", dev);
+    return MDE_ERR_UNSUPPORTED;
+  }
+  std::lock_guard<std::mutex> lock(mu);
+  if (!addr[dev]) {
+    void* p = nullptr;
+    MDE_CHECK_CUDA(cudaGetSymbolAddress(&p, g_input_stage_scratch));  // the CURRENT device's copy of the array
+    addr[dev] = static_cast<float*>(p);
+  }
+  *out = addr[dev];
+  return MDE_OK;
+}
+
+extern "C" int mde_input_stage_noalloc(const float* x, int B, int H, int W, const float* bn4x3, float eps, float* affine6, float* raw224,
+                                       mde_bf16* patches, mde_stream_t stream) {
+  MDE_CHECK_ARG(x && bn4x3 && affine6 && raw224 && patches, "mde_input_stage_noalloc: null pointer");
+  MDE_CHECK_ARG(B > 0 && H > 0 && W > 0 && W % 4 == 0 && (uintptr_t)x % 16 == 0,
+                "mde_input_stage_noalloc: W must be a multiple of 4 and x 16-byte aligned (H=%d W=%d)", H, W);
+  MDE_CHECK_ARG((uintptr_t)raw224 % 16 == 0 && (uintptr_t)patches % 16 == 0, "mde_input_stage_noalloc: raw224 / patches must be 16-byte aligned");
+  MDE_CHECK_ARG(B <= MDE_INPUT_STAGE_NOALLOC_MAX_BATCH,
+                "mde_input_stage_noalloc: batch %d exceeds the built-in scratch (MDE_INPUT_STAGE_NOALLOC_MAX_BATCH = %d images); use "
+                "mde_input_stage with caller scratch", B, MDE_INPUT_STAGE_NOALLOC_MAX_BATCH);
+  float* scratch = nullptr;
+  const int rc = noalloc_scratch_address(&scratch);
+  if (rc != MDE_OK) return rc;
+  const int parts = kNoallocGroups * 3 * B;  // <= kNoallocMaxParts; every record the finalize kernel reads is written by the scan first
+  launch_k(input_scan_resample_kernel, dim3(parts), dim3(256), 0, stream, x, H, W, kNoallocRowsPerBlock, kNoallocGroups, scratch, raw224);
   MDE_CHECK_LAUNCH();
   launch_k(range_finalize_kernel, dim3(1), dim3(768), 0, stream, scratch, parts, bn4x3, eps, affine6);
   MDE_CHECK_LAUNCH();
