@@ -317,6 +317,23 @@ int mde_temporal_mean(const float* const* maps, const double* weights, int n, lo
 int mde_bilateral_depth(const float* depth, int H, int W, const uint8_t* guide, float sigma_color, const float* space_w,
                         const float* joint_lut, float* scratch, float* out, mde_stream_t stream);
 
+/* DepthQualityEnhancement.fill_depth_holes (models/refinement.py:301-352) on one map depth f32 [H][W]: pixels that are not finite
+ * or <= 0 are holes; every 4-connected hole of at most max_hole_size^2 pixels is filled with the median of the ORIGINAL map over its
+ * ring (3 cross-shaped binary dilations of the hole minus the hole: np.median semantics, NaN if the ring holds a NaN), then every
+ * originally invalid pixel takes the 3x3 median (replicated border, cv2.medianBlur) of that result.  max_hole_size 0..13 (the
+ * reference's default is 10).  scratch: mde_fill_depth_holes_scratch_bytes(H, W) bytes, 256-byte aligned.  out may not alias depth. */
+long long mde_fill_depth_holes_scratch_bytes(int H, int W);
+int mde_fill_depth_holes(const float* depth, int H, int W, int max_hole_size, void* scratch, float* out, mde_stream_t stream);
+
+/* DepthQualityEnhancement.edge_preserving_smoothing (models/refinement.py:244-299): min/max-normalise depth f32 [H][W], guided filter
+ * (cv2.ximgproc.guidedFilter: box-filter form of He et al., window 2*radius+1, BORDER_REFLECT) with guide = the normalised map
+ * (rgb == NULL) or the 8-bit grey image of rgb u8 [H][W][3] (cv2.cvtColor RGB2GRAY), regulariser eps, then back to the map's range.
+ * The reference passes radius = min(H, W) / 16 and eps = lambda_param.  opencv-contrib is absent from the build image: the filter
+ * follows the published algorithm ("parity unpinned").  scratch: mde_guided_filter_scratch_bytes(H, W) bytes, 256-byte aligned. */
+long long mde_guided_filter_scratch_bytes(int H, int W);
+int mde_guided_filter_depth(const float* depth, int H, int W, const uint8_t* rgb, int radius, float eps, void* scratch, float* out,
+                            mde_stream_t stream);
+
 /* ==== backward of the ViT encoder block (train/mars_adapter.py:131-140 calls loss.backward() through
  * torchvision's EncoderBlock, tv:110-120).  GEMM-shaped gradients reuse mde_gemm_bf16 on transposed operands:
  *   dX = dY W    : A = dY [M][N],     W operand = W^T [K][N]

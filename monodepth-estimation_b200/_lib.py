@@ -73,6 +73,10 @@ SIGNATURES = {
     "mde_disp_to_depth": [_p, _ll, _d, _d, _p, _p],
     "mde_temporal_mean": [C.POINTER(_p), C.POINTER(_d), _i, _ll, _p, _p],
     "mde_bilateral_depth": [_p, _i, _i, _p, _f, _p, _p, _p, _p, _p],
+    "mde_fill_depth_holes_scratch_bytes": [_i, _i],
+    "mde_fill_depth_holes": [_p, _i, _i, _i, _p, _p, _p],
+    "mde_guided_filter_scratch_bytes": [_i, _i],
+    "mde_guided_filter_depth": [_p, _i, _i, _p, _i, _f, _p, _p, _p],
     "mde_transpose_bf16": [_p, _i, _i, _i, _i, _p, _i, _i, _p, _i, _p],
     "mde_batch_sum_f32": [_p, _i, _ll, _p, _i, _p],
     "mde_axpy_f32": [_p, _p, _f, _ll, _p],
@@ -105,7 +109,7 @@ SIGNATURES = {
     "mde_adam_chunk_elems": [],
     "mde_adam_multi": [_p, _i, _p, _i, _p, _f, _f, _f, _p, _p],
 }
-_RESTYPES = {"mde_last_error": C.c_char_p, "mde_workspace_bytes": C.c_longlong, "mde_point_cloud_scratch_bytes": C.c_longlong, "mde_layernorm_bwd_scratch_floats": C.c_longlong,
+_RESTYPES = {"mde_last_error": C.c_char_p, "mde_fill_depth_holes_scratch_bytes": C.c_longlong, "mde_guided_filter_scratch_bytes": C.c_longlong, "mde_workspace_bytes": C.c_longlong, "mde_point_cloud_scratch_bytes": C.c_longlong, "mde_layernorm_bwd_scratch_floats": C.c_longlong,
              "mde_depth_loss_scratch_floats": C.c_longlong, "mde_input_norm_bwd_scratch_floats": C.c_longlong, "mde_reduce_scratch_bytes": C.c_longlong, "mde_vit_attention_bwd_scratch_floats": C.c_longlong}
 
 _lock = threading.Lock()

@@ -255,6 +255,27 @@ def bilateral_depth(depth, sigma_color, space_w, guide=None, joint_lut=None, out
     return out
 
 
+def fill_depth_holes(depth, max_hole_size=10, out=None):
+    """refinement.py:301-352 on the device: depth f32 [H,W] -> filled f32 [H,W]."""
+    H, W = depth.shape
+    n = int(L.load().mde_fill_depth_holes_scratch_bytes(H, W))
+    scratch = torch.empty(n, device=depth.device, dtype=torch.uint8)
+    out = out if out is not None else torch.empty_like(depth)
+    L.call("mde_fill_depth_holes", _ptr(depth, F32), H, W, int(max_hole_size), _ptr(scratch, torch.uint8), _ptr(out, F32), _stream())
+    return out
+
+
+def guided_filter_depth(depth, radius, eps, rgb=None, out=None):
+    """refinement.py:244-299 on the device: depth f32 [H,W], rgb uint8 [H,W,3] or None (self-guided)."""
+    H, W = depth.shape
+    n = int(L.load().mde_guided_filter_scratch_bytes(H, W))
+    scratch = torch.empty(n, device=depth.device, dtype=torch.uint8)
+    out = out if out is not None else torch.empty_like(depth)
+    L.call("mde_guided_filter_depth", _ptr(depth, F32), H, W, _ptr(rgb, torch.uint8) if rgb is not None else _ptr(None), int(radius), float(eps),
+           _ptr(scratch, torch.uint8), _ptr(out, F32), _stream())
+    return out
+
+
 def disp_to_depth(disp, min_depth, max_depth, out=None):
     """layers.py:16-25 (depth only) on the device, bit-identical to the torch CPU expression."""
     out = out if out is not None else torch.empty_like(disp)

@@ -7,9 +7,9 @@ The reference's ``TextureAwareRefinementModule.forward`` raises on every valid i
 value it would build is never used), so this implementation computes the live
 arithmetic, ``refinement.py:68-85`` and ``:92-107``.  ``DepthQualityEnhancement``
 (``refinement.py:185-388``, OpenCV/NumPy CPU post-processing with no caller in the reference;
-SURVEY.md §8(f)#4): ``bilateral_depth_filter`` and ``temporal_consistency_filter`` run on the
-device; ``edge_preserving_smoothing`` (cv2.ximgproc guided filter) and ``fill_depth_holes``
-(scipy connected components) are not built and raise.
+SURVEY.md §8(f)#4): all four filters run on the device (``csrc/terrain.cu``, ``csrc/depth_filters.cu``).
+``edge_preserving_smoothing`` and the joint branch of ``bilateral_depth_filter`` call ``cv2.ximgproc`` in the
+reference (opencv-contrib, absent from the build image): they follow the published algorithms, parity unpinned.
 """
 from __future__ import annotations
 
@@ -118,11 +118,31 @@ class DepthQualityEnhancement:
 
     @staticmethod
     def edge_preserving_smoothing(depth_map, rgb_image=None, lambda_param=0.1):
-        raise NotImplementedError("cv2.ximgproc.guidedFilter (refinement.py:245-301) is not built; there is no CPU fallback")
+        """``refinement.py:244-299``: min/max normalise, guided filter (guide = grey image, or the map itself), radius
+        ``min(H, W) // 16``, rescale."""
+        from . import ops
+
+        z = DepthQualityEnhancement._device_map(depth_map)
+        guide = None
+        if rgb_image is not None:
+            rgb = np.squeeze(rgb_image.detach().cpu().numpy() if isinstance(rgb_image, torch.Tensor) else np.asarray(rgb_image))
+            if rgb.dtype != np.uint8:
+                rgb = (rgb * 255).astype(np.uint8)  # :268-269
+            if rgb.ndim == 2:  # :272-275: a one-channel guide is used as it is
+                rgb = np.repeat(rgb[..., None], 3, axis=2)  # (9798 + 19235 + 3735) g + 16384 >> 15 == g: the grey conversion is the identity
+            if rgb.shape != (*z.shape, 3):
+                raise ValueError(f"guide image must be [H,W,3] or [H,W] matching the depth map, got {rgb.shape}")
+            guide = torch.from_numpy(np.ascontiguousarray(rgb)).cuda()
+        return ops.guided_filter_depth(z, min(z.shape) // 16, lambda_param, guide).cpu().numpy()
 
     @staticmethod
     def fill_depth_holes(depth_map, max_hole_size=10):
-        raise NotImplementedError("connected-component hole filling (refinement.py:303-352) is not built; there is no CPU fallback")
+        """``refinement.py:301-352``: fill every 4-connected hole (non-finite or <= 0) of at most ``max_hole_size``^2 pixels with the
+        median of its ring, then a 3x3 median over what was invalid."""
+        from . import ops
+
+        z = DepthQualityEnhancement._device_map(depth_map)
+        return ops.fill_depth_holes(z, max_hole_size).cpu().numpy()
 
     @staticmethod
     def temporal_consistency_filter(depth_maps, weights=None):

@@ -23,7 +23,8 @@ for name in ("matplotlib", "matplotlib.pyplot", "mpl_toolkits", "mpl_toolkits.mp
 sys.modules["mpl_toolkits.mplot3d"].Axes3D = object
 
 from oracle import terrain_oracle as T  # noqa: E402
-from oracle.terrain_cases import BILATERAL_CASES, PC_CASES, TEMPORAL_CASES, pc_inputs, temporal_inputs  # noqa: E402
+from oracle.terrain_cases import (BILATERAL_CASES, GUIDED_CASES, HOLE_CASES, PC_CASES, TEMPORAL_CASES, guided_inputs, hole_inputs,  # noqa: E402
+                                  pc_inputs, temporal_inputs)
 
 from models.refinement import DepthQualityEnhancement as RefDQE  # noqa: E402
 from utils.terrain_reconstruction_fixed import MarsTerrainMapper as RefMapper  # noqa: E402
@@ -94,6 +95,33 @@ def main():
         print(f"{name:24s} oracle vs reference (cv2 {__import__('cv2').__version__}): max abs / range {err:.2e}")
         assert err < 2e-6, (name, err)
         rec[f"{name}__out"] = want.astype(np.float32)
+    for name, case in HOLE_CASES.items():
+        depth = hole_inputs(case)
+        with np.errstate(invalid="ignore"):
+            want = RefDQE.fill_depth_holes(depth, case["max_hole_size"])
+            got = T.fill_depth_holes(depth, case["max_hole_size"])
+            got2 = T.fill_depth_holes_numpy(depth, case["max_hole_size"])
+        assert same(got, want), name
+        ok = T.nan_free_windows(T.fill_depth_holes(depth, case["max_hole_size"], return_prefilter=True)[1])
+        assert case.get("nan_ring") or ok.all(), name
+        assert same(np.where(ok, got2, 0), np.where(ok, want, 0)), name  # the library-free restatement computes the same thing
+        n_bad = int((~np.isfinite(depth) | (depth <= 0)).sum())
+        print(f"{name:24s} {n_bad} invalid pixels: oracle (and its NumPy-only form) bit-identical to the reference")
+        rec[f"{name}__out"] = want
+    # edge_preserving_smoothing needs cv2.ximgproc (opencv-contrib): absent, the reference method cannot run -> parity unpinned.
+    # What CAN be pinned is its grey conversion: cv2.cvtColor is in the installed cv2.
+    import cv2
+
+    for name, case in GUIDED_CASES.items():
+        depth, rgb = guided_inputs(case)
+        try:
+            RefDQE.edge_preserving_smoothing(depth, rgb, case["lam"])
+            raise SystemExit("cv2.ximgproc unexpectedly present: pin the guided filter against it")
+        except AttributeError as e:
+            print(f"{name:24s} reference raises as documented ({str(e)[:60]}): unpinned")
+        if rgb is not None:
+            assert np.array_equal(T.rgb_to_gray_u8(rgb), cv2.cvtColor(rgb, cv2.COLOR_RGB2GRAY)), name
+        rec[f"{name}__oracle"] = T.edge_preserving_smoothing(depth, rgb, case["lam"])  # the oracle's own output (regression vector, not a pin)
     np.savez_compressed(os.path.join(GOLD, "terrain_golden.npz"), **rec)
     print("wrote", os.path.join(GOLD, "terrain_golden.npz"))
 

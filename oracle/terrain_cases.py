@@ -2,7 +2,7 @@
 tests (re-create the same inputs and compare against the stored results)."""
 import numpy as np
 
-from oracle.terrain_oracle import synth_depth
+from oracle.terrain_oracle import synth_depth, synth_holes
 
 PC_CASES = {
     "pc_default_37x53":   dict(H=37, W=53, seed=51, min_depth=0.1, max_depth=100.0, K=None),
@@ -20,6 +20,34 @@ BILATERAL_CASES = {
     "bilateral_64x80":   dict(H=64, W=80, seed=71),
     "bilateral_45x33_x10": dict(H=45, W=33, seed=72, mul=10.0, kw=dict(sigma_space=9, sigma_depth=0.1)),
 }
+
+
+HOLE_CASES = {
+    "holes_96x128":        dict(H=96, W=128, seed=81, max_hole_size=10),
+    "holes_70x90_max4":    dict(H=70, W=90, seed=82, max_hole_size=4),
+    "holes_64x64_nonan":   dict(H=64, W=64, seed=83, max_hole_size=10, nan_small=False),
+    "holes_80x80_nanring": dict(H=80, W=80, seed=84, max_hole_size=10, nan_ring=True),  # compared where the blur window is NaN-free
+}
+GUIDED_CASES = {
+    "guided_self_80x112":  dict(H=80, W=112, seed=91, rgb=False, lam=0.1),
+    "guided_rgb_64x96":    dict(H=64, W=96, seed=92, rgb=True, lam=0.1),
+    "guided_self_48x48":   dict(H=48, W=48, seed=93, rgb=False, lam=0.01),
+}
+
+
+def hole_inputs(case):
+    return synth_holes(case["H"], case["W"], case["seed"], case.get("nan_small", True), case.get("nan_ring", False))
+
+
+def guided_inputs(case):
+    depth = synth_depth(case["H"], case["W"], case["seed"], holes=False)
+    rgb = None
+    if case["rgb"]:
+        rng = np.random.Generator(np.random.PCG64(case["seed"] + 1000))
+        yy, xx = np.mgrid[0:case["H"], 0:case["W"]]
+        base = (96 + 64 * np.sin(xx / 9.0) + 48 * (xx > case["W"] // 2))[..., None]
+        rgb = np.clip(base + rng.integers(-20, 20, (case["H"], case["W"], 3)), 0, 255).astype(np.uint8)
+    return depth, rgb
 
 
 def pc_inputs(case):

@@ -146,6 +146,172 @@ def bilateral_depth_filter(depth_map, rgb_image=None, sigma_space=15, sigma_colo
     return filtered * (depth_max - depth_min) + depth_min
 
 
+def fill_depth_holes(depth_map, max_hole_size=10, return_prefilter=False):
+    """models/refinement.py:301-352, line by line, with the reference's own third-party calls (scipy.ndimage.label /
+    binary_dilation with their default cross-shaped structuring element, cv2.medianBlur ksize 3) — both are installed in the build
+    image and on the GPU box.  Pinned bit-exactly against the reference method (oracle/make_golden_terrain.py)."""
+    import cv2
+    import scipy.ndimage as ndimage
+
+    depth_map = np.squeeze(depth_map).astype(np.float32)
+    invalid_mask = ~np.isfinite(depth_map) | (depth_map <= 0)
+    filled = depth_map.copy()
+    labeled, num = ndimage.label(invalid_mask)
+    for i in range(1, num + 1):
+        component = labeled == i
+        if np.sum(component) > max_hole_size * max_hole_size:
+            continue
+        neighbor_mask = ndimage.binary_dilation(component, iterations=3) & ~component
+        if np.any(neighbor_mask):
+            filled[component] = np.median(depth_map[neighbor_mask])
+    prefilter = filled.copy()
+    final = cv2.medianBlur(filled.copy(), 3)
+    filled[invalid_mask] = final[invalid_mask]
+    return (filled, prefilter) if return_prefilter else filled
+
+
+def nan_free_windows(prefilter):
+    """Pixels whose 3x3 window (replicated border) of the pre-blur map holds no NaN: where cv2.medianBlur's result is defined
+    (with a NaN in the window it depends on OpenCV's SIMD min/max operand order, which nothing specifies)."""
+    H, W = prefilter.shape
+    pad = np.pad(np.isnan(prefilter), 1, mode="edge")
+    bad = np.zeros((H, W), bool)
+    for dy in range(3):
+        for dx in range(3):
+            bad |= pad[dy:dy + H, dx:dx + W]
+    return ~bad
+
+
+def fill_depth_holes_numpy(depth_map, max_hole_size=10):
+    """The same function WITHOUT scipy / cv2 (plain NumPy: flood-fill labelling, Manhattan-distance-3 ring, np.median, 3x3 median
+    with replicated border): states what the two library calls compute, and is what the device kernels implement.  Checked against
+    ``fill_depth_holes`` in tests/test_terrain_oracle.py."""
+    d = np.squeeze(depth_map).astype(np.float32)
+    H, W = d.shape
+    invalid = ~np.isfinite(d) | (d <= 0)
+    label = np.zeros((H, W), np.int32)
+    comps = []
+    for y in range(H):
+        for x in range(W):
+            if invalid[y, x] and label[y, x] == 0:
+                comps.append([])
+                stack = [(y, x)]
+                label[y, x] = len(comps)
+                while stack:
+                    cy, cx = stack.pop()
+                    comps[-1].append((cy, cx))
+                    for ny, nx in ((cy - 1, cx), (cy + 1, cx), (cy, cx - 1), (cy, cx + 1)):
+                        if 0 <= ny < H and 0 <= nx < W and invalid[ny, nx] and label[ny, nx] == 0:
+                            label[ny, nx] = len(comps)
+                            stack.append((ny, nx))
+    filled = d.copy()
+    for ci, px in enumerate(comps, 1):
+        if len(px) > max_hole_size * max_hole_size:
+            continue
+        ring = set()
+        for cy, cx in px:
+            for dy in range(-3, 4):
+                for dx in range(-(3 - abs(dy)), 3 - abs(dy) + 1):
+                    ny, nx = cy + dy, cx + dx
+                    if 0 <= ny < H and 0 <= nx < W and label[ny, nx] != ci:
+                        ring.add((ny, nx))
+        if ring:
+            with np.errstate(invalid="ignore"):
+                med = np.median(np.array([d[p] for p in sorted(ring)], dtype=np.float32))
+            for cy, cx in px:
+                filled[cy, cx] = med
+    pad = np.pad(filled, 1, mode="edge")
+    win = np.stack([pad[dy:dy + H, dx:dx + W] for dy in range(3) for dx in range(3)], axis=0)
+    blur = np.sort(win, axis=0)[4]  # NaN-free windows only: callers compare where no NaN reaches the window
+    out = filled.copy()
+    out[invalid] = blur[invalid]
+    return out
+
+
+def rgb_to_gray_u8(rgb):
+    """cv2.cvtColor(rgb, cv2.COLOR_RGB2GRAY) for uint8 (opencv-python 4.13): 15-bit fixed point, (9798 R + 19235 G + 3735 B + 16384) >> 15
+    (checked against cv2 in tests/test_terrain_oracle.py)."""
+    r = rgb.astype(np.int64)
+    return ((9798 * r[..., 0] + 19235 * r[..., 1] + 3735 * r[..., 2] + 16384) >> 15).astype(np.uint8)
+
+
+def _box_mean_reflect(a, r):
+    """cv2.boxFilter(ksize 2r+1, normalised, BORDER_REFLECT) in float64."""
+    if r == 0:
+        return a.astype(np.float64)
+    p = np.pad(a.astype(np.float64), r, mode="symmetric")  # numpy 'symmetric' == cv2.BORDER_REFLECT (fedcba|abcdef|fedcba)
+    c = np.cumsum(np.cumsum(np.pad(p, ((1, 0), (1, 0))), axis=0), axis=1)
+    k = 2 * r + 1
+    H, W = a.shape
+    s = c[k:k + H, k:k + W] - c[0:H, k:k + W] - c[k:k + H, 0:W] + c[0:H, 0:W]
+    return s / float(k * k)
+
+
+def guided_filter_gray(guide, src, radius, eps):
+    """cv2.ximgproc.guidedFilter, one-channel guide (He, Sun, Tang: "Guided Image Filtering", box-filter form): opencv-contrib is
+    NOT installed, so this restates the published algorithm in float64 — parity unpinned."""
+    I, p = guide.astype(np.float64), src.astype(np.float64)
+    mI, mp = _box_mean_reflect(I, radius), _box_mean_reflect(p, radius)
+    var = _box_mean_reflect(I * I, radius) - mI * mI
+    cov = _box_mean_reflect(I * p, radius) - mI * mp
+    a = cov / (var + eps)
+    b = mp - a * mI
+    # the device keeps a and b as float32 planes between the two box passes, as OpenCV's CV_32F implementation does
+    a, b = a.astype(np.float32), b.astype(np.float32)
+    return (_box_mean_reflect(a, radius) * I + _box_mean_reflect(b, radius)).astype(np.float32)
+
+
+def edge_preserving_smoothing(depth_map, rgb_image=None, lambda_param=0.1):
+    """models/refinement.py:244-299 with guided_filter_gray in place of cv2.ximgproc.guidedFilter."""
+    depth_map = np.squeeze(depth_map).astype(np.float32)
+    depth_min = np.min(depth_map)
+    depth_max = np.max(depth_map)
+    normalized = (depth_map - depth_min) / (depth_max - depth_min + 1e-8)
+    radius = min(depth_map.shape) // 16
+    if rgb_image is not None:
+        rgb = np.squeeze(rgb_image)
+        if rgb.dtype != np.uint8:
+            rgb = (rgb * 255).astype(np.uint8)
+        guide = rgb_to_gray_u8(rgb) if rgb.ndim == 3 else rgb
+        smoothed = guided_filter_gray(guide.astype(np.float32), normalized, radius, lambda_param)
+    else:
+        smoothed = guided_filter_gray(normalized, normalized, radius, lambda_param)
+    return smoothed * (depth_max - depth_min) + depth_min
+
+
+def synth_holes(h, w, seed, nan_small=True, nan_ring=False):
+    """Depth map with holes of every kind fill_depth_holes distinguishes: single invalid pixels and small blobs (0, negative, +inf,
+    and — nan_small — NaN), each isolated so that no other hole lies within its ring, two blobs larger than 10 x 10 (kept as holes,
+    value 0 so that the 3x3 median around them stays NaN-free), a long thin blob, a blob in a corner and one on the bottom border.
+    nan_ring adds a 3x3 zero blob two pixels away from a NaN blob: its ring then holds NaN and np.median makes the fill value NaN."""
+    rng = np.random.Generator(np.random.PCG64(seed))
+    z = synth_depth(h, w, seed, holes=False)
+    special = [(h // 2, w // 2, 12, 11, 0.0),      # 132 px > 100: stays a hole
+               (2, max(0, w - 30), 3, 26, -1.0),    # 78 px, long and thin: filled (at max_hole_size 10), wide window
+               (0, 0, 2, 3, 0.0),                   # corner
+               (h - 1, w // 3, 1, 4, 0.0)]          # bottom border
+    taken = np.zeros((h, w), bool)
+    for y, x, hh, ww, v in special:
+        z[y:y + hh, x:x + ww] = v
+        taken[max(0, y - 8):y + hh + 8, max(0, x - 8):x + ww + 8] = True
+    vals = [0.0, -1.5, np.inf] + ([np.nan] if nan_small else [])
+    k = 0
+    for y in range(6, h - 12, 14):
+        for x in range(6, w - 12, 14):
+            hh, ww = int(rng.integers(1, 5)), int(rng.integers(1, 5))
+            if taken[y:y + hh + 1, x:x + ww].any():
+                continue
+            z[y:y + hh, x:x + ww] = vals[k % len(vals)]
+            if k % 5 == 0:
+                z[y + hh, x] = vals[k % len(vals)]  # an L-shaped component
+            k += 1
+    if nan_ring:
+        y, x = h - 10, w - 12
+        z[y:y + 3, x:x + 2] = np.nan
+        z[y:y + 3, x + 4:x + 7] = 0.0  # 3x3: the window of its centre pixel is all-NaN after the fill, whatever the blur's NaN order
+    return z.astype(np.float32)
+
+
 def synth_depth(h, w, seed, holes=True):
     """Deterministic test depth map: smooth ramp + texture + a step edge, with out-of-range pixels (<= min_depth, >= max_depth,
     NaN) sprinkled in so the validity filter has something to reject."""

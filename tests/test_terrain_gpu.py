@@ -8,7 +8,8 @@ import torch
 
 from helpers import cached_model, load_golden, synth_images
 from oracle import terrain_oracle as T
-from oracle.terrain_cases import BILATERAL_CASES, PC_CASES, TEMPORAL_CASES, pc_inputs, temporal_inputs
+from oracle.terrain_cases import (BILATERAL_CASES, GUIDED_CASES, HOLE_CASES, PC_CASES, TEMPORAL_CASES, guided_inputs, hole_inputs, pc_inputs,
+                                  temporal_inputs)
 
 import monodepth_estimation_b200 as mde
 from monodepth_estimation_b200 import ops
@@ -164,3 +165,71 @@ def test_terrain_errors_are_loud():
         mde.TerrainReconstructor(min_depth=5.0, max_depth=1.0).create_point_cloud(np.ones((8, 8), np.float32))
     with pytest.raises(ValueError):
         mde.DepthQualityEnhancement.bilateral_depth_filter(np.ones((8, 8), np.float32), np.zeros((8, 9, 3), np.uint8))
+
+
+# --------------------------------------------------------------------------- fill_depth_holes / edge_preserving_smoothing
+@pytest.mark.parametrize("name", list(HOLE_CASES))
+def test_fill_depth_holes_vs_reference_golden(name):
+    """DepthQualityEnhancement.fill_depth_holes on the device (union-find labelling, ring median, 3x3 median) against the vectors
+    of the REAL reference method: bit-exact (only selections and one fp32 mean of two values).  Where a NaN reaches the 3x3 blur
+    window cv2's result is not specified (holes_80x80_nanring): those pixels are left out, except an all-NaN window."""
+    case = HOLE_CASES[name]
+    depth = hole_inputs(case)
+    got = mde.DepthQualityEnhancement.fill_depth_holes(depth, case["max_hole_size"])
+    want = GOLD[f"{name}__out"]
+    assert got.dtype == np.float32 and got.shape == want.shape
+    with np.errstate(invalid="ignore"):
+        pre = T.fill_depth_holes(depth, case["max_hole_size"], return_prefilter=True)[1]
+    ok = T.nan_free_windows(pre)
+    assert case.get("nan_ring") or ok.all()
+    assert np.array_equal(np.where(ok, got, 0), np.where(ok, want, 0), equal_nan=True)
+    if case.get("nan_ring"):  # the 3x3 zero blob next to the NaN blob got a NaN fill value (np.median semantics): its centre's window is all NaN
+        y, x = case["H"] - 10, case["W"] - 12
+        assert np.isnan(pre[y:y + 3, x + 4:x + 7]).all() and np.isnan(got[y + 1, x + 5]) and np.isnan(want[y + 1, x + 5])
+
+
+@pytest.mark.parametrize("H,W,frac,mhs", [(257, 263, 0.02, 10), (48, 512, 0.3, 3), (33, 47, 0.0, 10), (40, 40, 1.0, 10), (1024, 1024, 0.0003, 10), (50, 60, 0.45, 13)])
+def test_fill_depth_holes_vs_oracle_random(H, W, frac, mhs):
+    """Random salt holes (many components, merged blobs, percolating masks at 45 %), no hole at all, an all-invalid map, the
+    full 1024 px size: against the oracle (scipy + cv2, as the reference calls them)."""
+    rng = np.random.Generator(np.random.PCG64(H * 7 + W))
+    d = T.synth_depth(H, W, H + W, holes=False)
+    r = rng.random((H, W))
+    d[r < frac] = 0.0
+    d[(r >= frac) & (r < frac * 1.2)] = -2.0
+    want = T.fill_depth_holes(d, mhs)
+    got = ops.fill_depth_holes(torch.from_numpy(d).cuda(), mhs).cpu().numpy()
+    assert np.array_equal(got, want)
+
+
+def test_fill_depth_holes_rejects_unbuilt_sizes():
+    with pytest.raises(RuntimeError):
+        ops.fill_depth_holes(torch.ones(8, 8).cuda(), 14)
+
+
+@pytest.mark.parametrize("name", list(GUIDED_CASES))
+def test_guided_filter_vs_oracle(name):
+    """edge_preserving_smoothing against the restated guided filter (float64 NumPy; cv2.ximgproc is absent: parity unpinned).
+    Tolerance 2e-5 of the map's range: the device keeps a, b as fp32 planes like the oracle and sums in double."""
+    case = GUIDED_CASES[name]
+    depth, rgb = guided_inputs(case)
+    got = mde.DepthQualityEnhancement.edge_preserving_smoothing(depth, rgb, case["lam"])
+    want = T.edge_preserving_smoothing(depth, rgb, case["lam"])
+    assert got.dtype == np.float32 and got.shape == want.shape
+    span = float(depth.max() - depth.min())
+    assert float(np.abs(got - want).max()) <= 2e-5 * span, float(np.abs(got - want).max()) / span
+    if rgb is not None:  # float [0,1] guide takes the (rgb * 255).astype(uint8) branch (refinement.py:268-269)
+        got_f = mde.DepthQualityEnhancement.edge_preserving_smoothing(depth, (rgb / 255.0).astype(np.float32), case["lam"])
+        want_f = T.edge_preserving_smoothing(depth, (rgb / 255.0).astype(np.float32), case["lam"])
+        assert float(np.abs(got_f - want_f).max()) <= 2e-5 * span
+
+
+def test_guided_filter_full_size_and_grey_guide():
+    d = T.synth_depth(512, 640, 7, holes=False)
+    want = T.edge_preserving_smoothing(d)
+    got = mde.DepthQualityEnhancement.edge_preserving_smoothing(d)
+    assert float(np.abs(got - want).max()) <= 2e-5 * float(d.max() - d.min())
+    g = (np.random.Generator(np.random.PCG64(3)).integers(0, 256, d.shape)).astype(np.uint8)
+    want = T.edge_preserving_smoothing(d, g)
+    got = mde.DepthQualityEnhancement.edge_preserving_smoothing(d, g)
+    assert float(np.abs(got - want).max()) <= 2e-5 * float(d.max() - d.min())
