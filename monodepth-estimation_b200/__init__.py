@@ -7,5 +7,6 @@ from .terrain import MarsTerrainMapper, TerrainReconstructor  # noqa: F401
 from .layers import disp_to_depth  # noqa: F401
 from .pipeline import BatchPipeline  # noqa: F401
 from .composition import EnhancedWithRefinement  # noqa: F401
+from .runner import run_depth_estimation  # noqa: F401
 
 __version__ = "0.1.0"
