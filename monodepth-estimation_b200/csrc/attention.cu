@@ -220,7 +220,23 @@ constexpr int kTpSmem = kTpOffBar + 64 + 1024;
 constexpr uint32_t kTpTmemCols = 256;
 constexpr uint32_t kTpP = 104;  // first TMEM column of P (208 keys x bf16 = 104 columns)
 
+#ifdef MDE_ATTN_PROF
+__device__ __forceinline__ unsigned long long gtime() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+#define PS_T(i) do { if (prof_on) tp[i] = gtime(); } while (0)
+#else
+#define PS_T(i) do { } while (0)
+#endif
+
 __global__ void __launch_bounds__(128, 2) vit_attn_tp_kernel(const __grid_constant__ AttnParams p) {
+#ifdef MDE_ATTN_PROF
+  unsigned long long tp[12] = {0};
+  const bool prof_on = threadIdx.x == 0 && (blockIdx.x == 0 || blockIdx.x == 295 || blockIdx.x == 300 || blockIdx.x == 700);
+  PS_T(0);
+#endif
   pdl_launch_dependents();
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
@@ -253,7 +269,9 @@ __global__ void __launch_bounds__(128, 2) vit_attn_tp_kernel(const __grid_consta
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  PS_T(1);
   pdl_grid_wait();  // the set-up above overlaps the previous kernel's tail
+  PS_T(2);
 
   if (tid == 0) {
     mbar_expect_tx(bar_load, kQBytes + kKBytes + 4 * kVBytes);
@@ -262,6 +280,7 @@ __global__ void __launch_bounds__(128, 2) vit_attn_tp_kernel(const __grid_consta
 #pragma unroll
     for (int j = 0; j < 4; ++j) tma_load_3d(sV + j * kVBytes, &p.tmV, bar_load, 64 * j, 0, slab);
     mbar_wait(bar_load, 0);
+    PS_T(3);
     tc_fence_after();
     // ---- S = Q K^T  (128 x 208, K = 64)
     constexpr uint32_t idesc_s = umma_idesc_bf16(128, kKeys);
@@ -273,6 +292,7 @@ __global__ void __launch_bounds__(128, 2) vit_attn_tp_kernel(const __grid_consta
   }
   mbar_wait(bar_s, 0);
   tc_fence_after();
+  PS_T(4);
 
   const uint32_t t_row = tmem_base + (static_cast<uint32_t>(warp * 32) << 16);  // this thread's TMEM lane
   constexpr float kLog2e = 1.4426950408889634f;
@@ -295,6 +315,7 @@ __global__ void __launch_bounds__(128, 2) vit_attn_tp_kernel(const __grid_consta
   for (int j = 0; j < kS - 192; ++j) m4[j & 3] = fmaxf(m4[j & 3], __uint_as_float(tail[j]));
   const float mx = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3]));
   const float mxs = mx * kLog2e;
+  PS_T(5);
 
   // ---- pass 2, last chunk first: exp, row sum, bf16 probabilities back into TMEM
   float s4[4] = {0.0f, 0.0f, 0.0f, 0.0f};  // partial row sums (fixed assignment of columns to partials: deterministic)
@@ -328,6 +349,7 @@ __global__ void __launch_bounds__(128, 2) vit_attn_tp_kernel(const __grid_consta
   const float inv = 1.0f / ((s4[0] + s4[1]) + (s4[2] + s4[3]));
   tc_fence_before();
   __syncthreads();
+  PS_T(6);
 
   // ---- O = P V  (128 x 64, K = 208 = 13 x 16): A from TMEM, B = V^T tiles in shared memory
   if (tid == 0) {
@@ -342,6 +364,7 @@ __global__ void __launch_bounds__(128, 2) vit_attn_tp_kernel(const __grid_consta
   }
   mbar_wait(bar_o, 0);
   tc_fence_after();
+  PS_T(7);
 
   const int t = mt * 128 + tid;
 #pragma unroll 1
@@ -363,6 +386,13 @@ __global__ void __launch_bounds__(128, 2) vit_attn_tp_kernel(const __grid_consta
   __syncthreads();
   tc_fence_after();
   if (warp == 0) tmem_dealloc(tmem_base, kTpTmemCols);
+#ifdef MDE_ATTN_PROF
+  if (prof_on) {
+    PS_T(8);
+    printf("tp blk %d: setup %llu pdlwait %llu load %llu S %llu pass1 %llu pass2 %llu PV %llu epi+dealloc %llu total %llu ns (start %llu)\n", blockIdx.x, tp[1] - tp[0],
+           tp[2] - tp[1], tp[3] - tp[2], tp[4] - tp[3], tp[5] - tp[4], tp[6] - tp[5], tp[7] - tp[6], tp[8] - tp[7], tp[8] - tp[0], tp[0] % 1000000ull);
+  }
+#endif
 }
 
 // ------------------------------------------------------------------ ViT attention, persistent and pipelined
@@ -385,16 +415,6 @@ __device__ __forceinline__ void ps_poll_timeout(long long t0) {
   }
 }
 
-#ifdef MDE_ATTN_PROF
-__device__ __forceinline__ unsigned long long gtime() {
-  unsigned long long t;
-  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-  return t;
-}
-#define PS_T(i) do { if (prof_on) tp[i] = gtime(); } while (0)
-#else
-#define PS_T(i) do { } while (0)
-#endif
 
 __global__ void __launch_bounds__(320, 1) vit_attn_ps_kernel(const __grid_constant__ AttnParams p) {
 #ifdef MDE_ATTN_PROF

@@ -20,6 +20,11 @@
 // sub-tile in a private, 128B-swizzled shared-memory buffer and moves it with TMA: the residual arrives by TMA LOAD
 // one chunk ahead, bias/activation/residual are applied in place, and a TMA STORE (bulk group) writes it out while
 // the warp is already on its next chunk.  No LSU global traffic, full-line writes, rows >= M clipped by the tensor map.
+//
+// Residual layers (out-proj, fc2): the residual and the bias are loaded INTO the accumulator before the tile's MMAs start
+// (TMA load -> shared -> tcgen05.st by the epilogue warps, while the previous tile's MMAs run; the first MMA then accumulates),
+// so the epilogue of such a tile is TMEM -> shared -> TMA store only.  With the residual fetched inside the epilogue every
+// 32-column chunk waited ~1 us for its load: 5.3 us per tile on the un-overlapped tail of proj / fc2 (in-kernel counters, r02b).
 #include <stdio.h>
 #include <stdlib.h>
 
@@ -104,6 +109,21 @@ __device__ __forceinline__ Item decode_item(const Tc2Params& p, int i) {
   return it;
 }
 
+// Bias values of one epilogue warp's columns, one column per lane: the warp owns the chunks par, par + 2, ... of the item (`my` of
+// them); b[jj] = bias of column `lane` of its jj-th 32-column chunk (fp32 epilogues), or b[2 jj + h] = column 32 h + lane of its
+// jj-th 64-column chunk (bf16 epilogues).  Four coalesced loads per item instead of 8-16 float4 loads per chunk and lane.
+__device__ __forceinline__ void lane_bias32(const float* bias, int n0, int par, int my, int lane, float (&b)[4]) {
+#pragma unroll
+  for (int jj = 0; jj < 4; ++jj) b[jj] = jj < my ? __ldg(bias + n0 + (par + 2 * jj) * 32 + lane) : 0.0f;
+}
+__device__ __forceinline__ void lane_bias64(const float* bias, int n0, int par, int my, int lane, float (&b)[4]) {
+#pragma unroll
+  for (int jj = 0; jj < 2; ++jj) {
+    b[2 * jj] = jj < my ? __ldg(bias + n0 + (par + 2 * jj) * 64 + lane) : 0.0f;
+    b[2 * jj + 1] = jj < my ? __ldg(bias + n0 + (par + 2 * jj) * 64 + 32 + lane) : 0.0f;
+  }
+}
+
 // LNF = 1 adds the LayerNorm-fusion code (producer: bf16 copy + row sums, consumer: normalising epilogue); the default
 // instantiation carries none of it (the extra registers / instructions cost ~0.6 us per launch even when never executed).
 // EC = epilogue class: 0 fp32 through TMA (bias / bias + residual), 1 bf16 through TMA (bias / GELU / QKV split), 2 direct stores
@@ -111,6 +131,7 @@ __device__ __forceinline__ Item decode_item(const Tc2Params& p, int i) {
 template <int LNF, int EC>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(k2Threads, 1) tc_gemm2_kernel(const __grid_constant__ Tc2Params p) {
   pdl_launch_dependents();
+  MDE_PROF(const long long t_start = clk();)
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
   const int stages = p.stages;
@@ -119,8 +140,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(k2Threads, 1) tc_gem
   uint64_t* empty_bar = full_bar + stages;
   uint64_t* tfull_bar = empty_bar + stages;
   uint64_t* tempty_bar = tfull_bar + 2;
-  uint64_t* res_bar = tempty_bar + 2;  // [k2EpiWarps][2] residual-chunk arrival barriers
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(res_bar + 2 * k2EpiWarps);
+  uint64_t* res_bar = tempty_bar + 2;  // [k2EpiWarps][4] residual-chunk arrival barriers (2 staging buffers + 2 borrowed slots)
+  uint64_t* init_bar = res_bar + 4 * k2EpiWarps;  // the epilogue warps no longer need the pipeline stages they borrowed (count 8)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(init_bar + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t rank = cluster_ctarank();
@@ -146,7 +168,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(k2Threads, 1) tc_gem
         mbar_init(&tfull_bar[a], 1);    // pair commit (multicast)
         mbar_init(&tempty_bar[a], 16);  // 8 epilogue warps x 2 CTAs (only the leader's copy is waited on)
       }
-      for (int a = 0; a < 2 * k2EpiWarps; ++a) mbar_init(&res_bar[a], 1);
+      for (int a = 0; a < 4 * k2EpiWarps; ++a) mbar_init(&res_bar[a], 1);
+      mbar_init(init_bar, k2EpiWarps);
       fence_barrier_init();
     }
     __syncwarp();
@@ -157,12 +180,14 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(k2Threads, 1) tc_gem
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   pdl_grid_wait();  // everything above (barriers, TMEM, descriptor prefetch) overlaps the previous kernel's tail
+  MDE_PROF(if (p.prof && threadIdx.x == 0) p.prof[blockIdx.x * 8 + 6] = clk() - t_start;)  // prologue incl. the wait for the previous kernel
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer (both CTAs)
     if (elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
+      bool borrow = EC == 0 && p.epi == MDE_EPI_BIAS_RESID_F32 && stages >= 4;
       for (int i = cluster_id; i < p.total_items; i += num_clusters) {
         const Item it = decode_item(p, i);
         const int half = it.bn >> 1;
@@ -170,6 +195,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(k2Threads, 1) tc_gem
         const uint32_t tx = 2u * (k2ABytes + half * 128);
         for (int kb = 0; kb < p.k_blocks; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
+          if (borrow && stage == stages - 2) {  // first pass only: stages - 2 and stages - 1 hold residual chunks of the first item
+            mbar_wait(init_bar, 0);
+            borrow = false;
+          }
           uint8_t* sa = smem + (size_t)stage * k2StageBytes;
           if (leader) mbar_expect_tx(&full_bar[stage], tx);
           tma_load_2d_pair(sa, &p.tmA, &full_bar[stage], kb * 64, it.m0 + (int)rank * 128);
@@ -186,11 +215,12 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(k2Threads, 1) tc_gem
     if (leader && elect_one()) {
       int stage = 0, acc = 0;
       uint32_t phase = 0, acc_phase = 0;
+      const bool pre_acc = EC == 0 && p.epi == MDE_EPI_BIAS_RESID_F32;  // accumulator pre-loaded with residual + bias
       for (int i = cluster_id; i < p.total_items; i += num_clusters) {
         const Item it = decode_item(p, i);
         const uint32_t idesc = umma_idesc_bf16(256, it.bn);
         MDE_PROF(long long t0 = 0; if (p.prof) t0 = clk();)
-        mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
+        mbar_wait(&tempty_bar[acc], pre_acc ? acc_phase : (acc_phase ^ 1));  // pre_acc: the epilogue warps arrive after initialising the buffer
         MDE_PROF(if (p.prof) p.prof[blockIdx.x * 8 + 0] += clk() - t0;)  // MMA thread waiting for a free accumulator (epilogue behind)
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * 256;
@@ -203,7 +233,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(k2Threads, 1) tc_gem
           const uint64_t da = umma_smem_desc_kmajor<128>(sa);
           const uint64_t db = umma_smem_desc_kmajor<128>(sa + k2ABytes);
 #pragma unroll
-          for (int k = 0; k < 4; ++k) umma_bf16_ss_pair(d_tmem, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+          for (int k = 0; k < 4; ++k) umma_bf16_ss_pair(d_tmem, da + 2 * k, db + 2 * k, idesc, pre_acc || (kb | k) != 0);
           umma_commit_pair(&empty_bar[stage]);
           if (++stage == stages) {
             stage = 0;
@@ -214,6 +244,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(k2Threads, 1) tc_gem
         acc ^= 1;
         if (acc == 0) acc_phase ^= 1;
       }
+      MDE_PROF(if (p.prof) p.prof[blockIdx.x * 8 + 7] = clk() - t_start;)  // last MMA issued (since kernel start)
     }
   } else {
     // ------------------------------------------------------------------ epilogue warps (both CTAs)
@@ -225,21 +256,115 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(k2Threads, 1) tc_gem
     if constexpr (EC != 2) {
       const int ew = warp - 2;
       uint8_t* stg = staging + ew * 2 * k2EpiBufBytes;
-      uint64_t* rbar = res_bar + ew * 2;
+      uint64_t* rbar = res_bar + ew * 4;
       const bool resid = EC == 0 && p.epi == MDE_EPI_BIAS_RESID_F32;
       constexpr bool f32out = EC == 0;
       const int cw = f32out ? 32 : 64;  // columns per 128-byte chunk
       const uint32_t sw = static_cast<uint32_t>(lane & 7);
-      uint32_t g = 0;  // chunks this warp has processed: staging buffer = g & 1, residual barrier parity = (g >> 1) & 1
-      // lane 0: TMA-load the residual sub-tile of (item, chunk) into the buffer chunk number `gg` will use
-      auto load_resid = [&](const Item& it2, int c2, uint32_t gg) {
-        uint64_t* b = &rbar[gg & 1];
-        mbar_expect_tx(b, k2EpiBufBytes);
-        tma_load_2d(stg + (gg & 1) * k2EpiBufBytes, &p.tmRes, b, it2.n0 + c2 * cw, it2.m0 + (int)rank * 128 + q * 32);
+      uint32_t g = 0;   // output chunks this warp has staged: staging buffer = g & 1
+      uint32_t rph = 0;  // bit b: parity of the next completion of residual barrier b (staging buffer b) to wait for
+      // Residual layers: (residual + bias) of item `it2` -> accumulator buffer `acc2`, then arrive on tempty (the MMA thread
+      // starts the item when all 16 epilogue warps of the pair have).  Two TMA loads in flight per warp.
+      auto init_acc = [&](const Item& it2, int acc2) {
+        const int my = ((it2.bn >> 5) - par + 1) >> 1;  // this warp's 32-column chunks: par, par + 2, ...
+        const int row02 = it2.m0 + (int)rank * 128 + q * 32;
+        const uint32_t ta = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc2 * 256;
+        auto load = [&](int j) {  // lane 0: chunk j of this warp -> staging buffer j & 1
+          uint64_t* b = &rbar[j & 1];
+          mbar_expect_tx(b, k2EpiBufBytes);
+          tma_load_2d(stg + (j & 1) * k2EpiBufBytes, &p.tmRes, b, it2.n0 + (par + 2 * j) * 32, row02);
+        };
+        if (lane == 0) {
+          bulk_wait_read<0>();  // the stores of the previous drain no longer read the staging buffers
+          if (my > 0) load(0);
+          if (my > 1) load(1);
+        }
+        float bq[4];
+        lane_bias32(p.bias, it2.n0, par, my, lane, bq);  // in flight together with the residual loads
+        __syncwarp();
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          if (j >= my) break;
+          const int c = par + 2 * j, b = j & 1;
+          mbar_wait(&rbar[b], (rph >> b) & 1);
+          rph ^= 1u << b;
+          const uint8_t* row = stg + b * k2EpiBufBytes + lane * 128;
+          uint32_t v[32];
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            const float4 r4 = *reinterpret_cast<const float4*>(row + ((static_cast<uint32_t>(u) ^ sw) << 4));
+            v[4 * u] = __float_as_uint(r4.x + __shfl_sync(0xffffffffu, bq[j], 4 * u));
+            v[4 * u + 1] = __float_as_uint(r4.y + __shfl_sync(0xffffffffu, bq[j], 4 * u + 1));
+            v[4 * u + 2] = __float_as_uint(r4.z + __shfl_sync(0xffffffffu, bq[j], 4 * u + 2));
+            v[4 * u + 3] = __float_as_uint(r4.w + __shfl_sync(0xffffffffu, bq[j], 4 * u + 3));
+          }
+          tmem_st_32x32b_x32(ta + c * 32, v);
+          __syncwarp();  // every lane has read the buffer
+          if (lane == 0 && j + 2 < my) load(j + 2);
+        }
+        tmem_st_wait();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive_cluster(&tempty_bar[acc2], 0);
+      };
+      // The first item's residual: all (up to four) chunks of the warp in flight at once — two in the warp's staging buffers, two in
+      // 4 KB slots of pipeline stages `stages - 2` and `stages - 1`, which the producer leaves alone until init_bar completes
+      // (the MMAs cannot start before this buffer is initialised anyway).  One TMA round trip instead of two on the critical path.
+      auto init_first = [&](const Item& it2) {
+        const int my = ((it2.bn >> 5) - par + 1) >> 1;
+        const int row02 = it2.m0 + (int)rank * 128 + q * 32;
+        const uint32_t ta = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
+        uint8_t* bufs[4] = {stg, stg + k2EpiBufBytes, smem + (size_t)(stages - 2) * k2StageBytes + ew * k2EpiBufBytes,
+                            smem + (size_t)(stages - 1) * k2StageBytes + ew * k2EpiBufBytes};
+        if (lane == 0) {
+          for (int j = 0; j < my; ++j) {
+            // chunks 0, 1 -> staging buffers (barriers 0, 1), chunks 2, 3 -> borrowed slots (barriers 2, 3)
+            mbar_expect_tx(&rbar[j], k2EpiBufBytes);
+            tma_load_2d(bufs[j], &p.tmRes, &rbar[j], it2.n0 + (par + 2 * j) * 32, row02);
+          }
+        }
+        float bq[4];
+        lane_bias32(p.bias, it2.n0, par, my, lane, bq);  // in flight together with the residual loads
+        __syncwarp();
+        // consume the borrowed slots first, so that the producer gets its stages back as early as possible
+#pragma unroll
+        for (int o = 0; o < 4; ++o) {
+          const int j = (o + 2) & 3;  // 2, 3, 0, 1
+          if (j < my) {
+            const int c = par + 2 * j;
+            mbar_wait(&rbar[j], 0);
+            if (j < 2) rph ^= 1u << j;
+            const uint8_t* row = bufs[j] + lane * 128;
+            uint32_t v[32];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+              const float4 r4 = *reinterpret_cast<const float4*>(row + ((static_cast<uint32_t>(u) ^ sw) << 4));
+              v[4 * u] = __float_as_uint(r4.x + __shfl_sync(0xffffffffu, bq[j], 4 * u));
+              v[4 * u + 1] = __float_as_uint(r4.y + __shfl_sync(0xffffffffu, bq[j], 4 * u + 1));
+              v[4 * u + 2] = __float_as_uint(r4.z + __shfl_sync(0xffffffffu, bq[j], 4 * u + 2));
+              v[4 * u + 3] = __float_as_uint(r4.w + __shfl_sync(0xffffffffu, bq[j], 4 * u + 3));
+            }
+            tmem_st_32x32b_x32(ta + c * 32, v);
+          }
+          if (o == 1) {  // both borrowed slots have been read (or were never used)
+            __syncwarp();
+            if (lane == 0) mbar_arrive(init_bar);
+          }
+        }
+        tmem_st_wait();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive_cluster(&tempty_bar[0], 0);
       };
       int i = cluster_id;
       Item it = decode_item(p, i < p.total_items ? i : 0);
-      if (resid && i < p.total_items && par < it.bn / cw && lane == 0) load_resid(it, par, g);
+      if (resid) {  // the first two items' buffers (the MMA thread waits for them)
+        if (i < p.total_items) {
+          if (stages >= 4) init_first(it);
+          else init_acc(it, 0);
+        }
+        if (i + num_clusters < p.total_items) init_acc(decode_item(p, i + num_clusters), 1);
+      }
       while (i < p.total_items) {
         const int inext = i + num_clusters;
         const bool has_next = inext < p.total_items;
@@ -285,6 +410,13 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(k2Threads, 1) tc_gem
         }
         const float nmr = -mu * rstd;
         MDE_PROF(long long t0 = 0; const bool prof = p.prof && warp == 2 && lane == 0; if (prof) t0 = clk();)
+        // this warp's bias values, one column per lane and 32-column group (shuffled to the row owners below): loaded once per item
+        // and BEFORE the wait, so that no chunk pays an L2 round trip for them (r02c: ~0.5 us per chunk, serialised behind the waits)
+        float bq[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+        if (!resid) {
+          if (f32out) lane_bias32(p.bias, it.n0, par, (nch - par + 1) >> 1, lane, bq);
+          else lane_bias64(p.bias, it.n0, par, (nch - par + 1) >> 1, lane, bq);
+        }
         mbar_wait(&tfull_bar[acc], acc_phase);
         MDE_PROF(if (prof) {
           const long long t1 = clk();
@@ -302,37 +434,22 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(k2Threads, 1) tc_gem
           if constexpr (f32out) {
             uint32_t raw[32];
             tmem_ld_32x32b_x32(taddr + c * 32, raw);
-            if (lane == 0) {
-              if (resid) {
-                // the other buffer (chunk g+1's) was last read by the store of chunk g-1: wait for it, then prefetch into it
-                if (c + 2 < nch) {
-                  bulk_wait_read<0>();
-                  load_resid(it, c + 2, g + 1);
-                } else if (has_next && par < itn.bn / cw) {
-                  bulk_wait_read<0>();
-                  load_resid(itn, par, g + 1);
-                }
-              } else {
-                bulk_wait_read<1>();  // this buffer's previous store (chunk g-2) has finished reading it
-              }
-            }
+            if (lane == 0) bulk_wait_read<1>();  // this buffer's previous store (chunk g-2) has finished reading it
             __syncwarp();
             tmem_ld_wait();
-            if (resid) mbar_wait(&rbar[g & 1], (g >> 1) & 1);
-            const float4* bp = reinterpret_cast<const float4*>(p.bias + n0);
+            const int jj = (c - par) >> 1;
+            const float bsel = jj == 0 ? bq[0] : (jj == 1 ? bq[1] : (jj == 2 ? bq[2] : bq[3]));
             float c1 = 0.0f, c2 = 0.0f;  // this chunk's partial, started from zero (see the consumer: tiling-independent sums)
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
               float4* sp = reinterpret_cast<float4*>(row + ((static_cast<uint32_t>(j) ^ sw) << 4));
-              const float4 b4 = __ldg(bp + j);
-              float4 o = make_float4(__uint_as_float(raw[4 * j]) + b4.x, __uint_as_float(raw[4 * j + 1]) + b4.y,
-                                     __uint_as_float(raw[4 * j + 2]) + b4.z, __uint_as_float(raw[4 * j + 3]) + b4.w);
-              if (resid) {
-                const float4 r4 = *sp;
-                o.x += r4.x;
-                o.y += r4.y;
-                o.z += r4.z;
-                o.w += r4.w;
+              float4 o = make_float4(__uint_as_float(raw[4 * j]), __uint_as_float(raw[4 * j + 1]), __uint_as_float(raw[4 * j + 2]),
+                                     __uint_as_float(raw[4 * j + 3]));
+              if (!resid) {  // residual layers: bias and residual are already in the accumulator (init_acc)
+                o.x += __shfl_sync(0xffffffffu, bsel, 4 * j);
+                o.y += __shfl_sync(0xffffffffu, bsel, 4 * j + 1);
+                o.z += __shfl_sync(0xffffffffu, bsel, 4 * j + 2);
+                o.w += __shfl_sync(0xffffffffu, bsel, 4 * j + 3);
               }
               *sp = o;
               if constexpr (LNF) {
@@ -351,7 +468,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(k2Threads, 1) tc_gem
             if (lane == 0) bulk_wait_read<1>();
             __syncwarp();
             tmem_ld_wait();
-            const float4* bp = reinterpret_cast<const float4*>(p.bias + n0);
+            const int jj = (c - par) >> 1;
+            const float blo = jj == 0 ? bq[0] : bq[2], bhi = jj == 0 ? bq[1] : bq[3];  // bias of columns [0,32) / [32,64) of this chunk, by lane
             const bool lnc = LNF && p.ln_in != nullptr;  // LayerNorm consumer: (acc - mean * colsum) * rstd + bias
             const float4* csp = reinterpret_cast<const float4*>(p.ln_cs + n0);
             const bool gelu = p.epi == MDE_EPI_BIAS_GELU_BF16;
@@ -359,13 +477,17 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(k2Threads, 1) tc_gem
             if (which == 2) {
               // V goes out transposed, vt[b*12+head][d][token]: consecutive lanes hold consecutive tokens -> coalesced 2-byte stores
               const int m = row0 + lane;
-              if (m < p.M) {
-                const int bb = m / MDE_VIT_SEQ, t = m - bb * MDE_VIT_SEQ;
+              const bool live = m < p.M;  // the shuffles below need every lane: only the stores are guarded
+              {
+                const int mm = live ? m : 0;
+                const int bb = mm / MDE_VIT_SEQ, t = mm - bb * MDE_VIT_SEQ;
                 const int cc = n0 - 2 * MDE_VIT_DIM;  // = head * 64
                 bf16* dst = reinterpret_cast<bf16*>(const_cast<void*>(p.aux1)) + ((size_t)bb * MDE_VIT_DIM + cc) * MDE_VT_PITCH + t;
 #pragma unroll
                 for (int j = 0; j < 16; ++j) {
-                  const float4 b4 = __ldg(bp + j);
+                  const float bsrc = j < 8 ? blo : bhi;
+                  const float4 b4 = make_float4(__shfl_sync(0xffffffffu, bsrc, (4 * j) & 31), __shfl_sync(0xffffffffu, bsrc, (4 * j + 1) & 31),
+                                                __shfl_sync(0xffffffffu, bsrc, (4 * j + 2) & 31), __shfl_sync(0xffffffffu, bsrc, (4 * j + 3) & 31));
                   float4 a4 = make_float4(__uint_as_float(raw[4 * j]), __uint_as_float(raw[4 * j + 1]), __uint_as_float(raw[4 * j + 2]), __uint_as_float(raw[4 * j + 3]));
                   if (lnc) {  // (acc - mu * colsum) * rstd + bias  ==  acc * rstd + (nmr * colsum + bias),  nmr = -mu * rstd
                     const float4 c4 = __ldg(csp + j);
@@ -374,10 +496,12 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(k2Threads, 1) tc_gem
                   } else {
                     a4 = make_float4(a4.x + b4.x, a4.y + b4.y, a4.z + b4.z, a4.w + b4.w);
                   }
-                  dst[(size_t)(4 * j) * MDE_VT_PITCH] = __float2bfloat16_rn(a4.x);
-                  dst[(size_t)(4 * j + 1) * MDE_VT_PITCH] = __float2bfloat16_rn(a4.y);
-                  dst[(size_t)(4 * j + 2) * MDE_VT_PITCH] = __float2bfloat16_rn(a4.z);
-                  dst[(size_t)(4 * j + 3) * MDE_VT_PITCH] = __float2bfloat16_rn(a4.w);
+                  if (live) {
+                    dst[(size_t)(4 * j) * MDE_VT_PITCH] = __float2bfloat16_rn(a4.x);
+                    dst[(size_t)(4 * j + 1) * MDE_VT_PITCH] = __float2bfloat16_rn(a4.y);
+                    dst[(size_t)(4 * j + 2) * MDE_VT_PITCH] = __float2bfloat16_rn(a4.z);
+                    dst[(size_t)(4 * j + 3) * MDE_VT_PITCH] = __float2bfloat16_rn(a4.w);
+                  }
                 }
               }
               continue;  // nothing staged, no TMA store for this chunk (g is advanced by the loop header)
@@ -385,12 +509,13 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(k2Threads, 1) tc_gem
             const float qs = (p.epi == MDE_EPI_QKV_SPLIT && which == 0) ? 0.125f : 1.0f;  // 1/sqrt(64) folded into q
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
-              const float4 b0 = __ldg(bp + 2 * j), b1 = __ldg(bp + 2 * j + 1);
               float v[8];
 #pragma unroll
               for (int t = 0; t < 8; ++t) v[t] = __uint_as_float(raw[8 * j + t]);
               {
-                const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+                float bb[8];
+#pragma unroll
+                for (int t = 0; t < 8; ++t) bb[t] = __shfl_sync(0xffffffffu, j < 4 ? blo : bhi, (8 * j + t) & 31);
                 if (lnc) {  // (acc - mu * colsum) * rstd + bias  ==  acc * rstd + (nmr * colsum + bias),  nmr = -mu * rstd
                   const float4 c0 = __ldg(csp + 2 * j), c1 = __ldg(csp + 2 * j + 1);
                   const float cs[8] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w};
@@ -447,7 +572,11 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(k2Threads, 1) tc_gem
         }
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive_cluster(&tempty_bar[acc], 0);  // the leader's MMA thread owns the accumulator ring
+        if (resid) {  // drained: load the residual of the item that will use this buffer next (two items ahead), then arrive
+          if (inext + num_clusters < p.total_items) init_acc(decode_item(p, inext + num_clusters), acc);
+        } else if (lane == 0) {
+          mbar_arrive_cluster(&tempty_bar[acc], 0);  // the leader's MMA thread owns the accumulator ring
+        }
         MDE_PROF(if (prof) {
           p.prof[blockIdx.x * 8 + 3] += clk() - t0;  // epilogue warp 2 working on the tile
           p.prof[blockIdx.x * 8 + 4] += 1;           // tiles
@@ -493,6 +622,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(k2Threads, 1) tc_gem
   cluster_sync_all();  // both CTAs are done with each other's shared memory / TMEM
   tc_fence_after();
   if (warp == 1) tmem_dealloc_pair(tmem_base, k2TmemCols);
+  MDE_PROF(if (p.prof && threadIdx.x == 0) p.prof[blockIdx.x * 8 + 5] = clk() - t_start;)  // CTA lifetime
 }
 
 // ------------------------------------------------------------------------------------ host side

@@ -1,3 +1,4 @@
 cd $GRAFT_REPO_ROOT
-timeout 600 python -m pytest tests/test_pipeline_gpu.py -m gpu -x -q > gpurun_out/c7_runner.log 2>&1; echo "exit $?"
-tail -25 gpurun_out/c7_runner.log
+timeout 1500 python -m pytest tests -m gpu -x -q > gpurun_out/c13_all.log 2>&1; echo "all exit $?"
+tail -4 gpurun_out/c13_all.log
+timeout 300 python bench.py --no-extras --steps 30 --warmup 5 > gpurun_out/c13_bench.json 2> gpurun_out/c13_bench.err; cat gpurun_out/c13_bench.json | head -c 400

@@ -76,7 +76,9 @@ def main():
             lead, both = pr[0::2], pr
             print(f"      per CTA (us, mean/max): MMA waits accumulator {lead[:, 0].mean():.2f}/{lead[:, 0].max():.2f}, MMA waits operands "
                   f"{lead[:, 1].mean():.2f}/{lead[:, 1].max():.2f}, epilogue waits MMA {both[:, 2].mean():.2f}/{both[:, 2].max():.2f}, epilogue works "
-                  f"{both[:, 3].mean():.2f}/{both[:, 3].max():.2f} over {both[:, 4].mean():.2f} tiles, CTA lifetime {both[:, 5].mean():.2f}/{both[:, 5].max():.2f}")
+                  f"{both[:, 3].mean():.2f}/{both[:, 3].max():.2f} over {both[:, 4].mean():.2f} tiles, CTA lifetime {both[:, 5].mean():.2f}/{both[:, 5].max():.2f}, "
+                  f"prologue {both[:, 6].mean():.2f}/{both[:, 6].max():.2f}, last MMA issued at {lead[:, 7].mean():.2f}/{lead[:, 7].max():.2f}")
+            print("      lifetime per cluster (us):", " ".join(f"{v:.1f}" for v in lead[:, 5].tolist()[:12]), "...", " ".join(f"{v:.1f}" for v in lead[:, 5].tolist()[-4:]))
     print(f"per ViT layer (4 GEMMs): {total:.1f} us; x12 = {total * 12 / 1e3:.3f} ms")
 
 
