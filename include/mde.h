@@ -209,6 +209,13 @@ int mde_conv_nhwc_f16(const mde_f16* in, int B, int h, int w, int cin, int in_cs
 int mde_upsample2x_concat_nhwc(const mde_bf16* a, int B, int h, int w, int ca, const mde_bf16* s, int hs, int ws,
                                int cs, mde_bf16* out, mde_stream_t stream);
 
+/* ---- decoder.py:139-168 for the last level (i = 3) as one kernel: x2 bilinear upsample (align_corners=True) of src (padded NHWC
+ * bf16 [B][h+2][w+2][16], the output of upconv_3_0), upconv_3_1 and mars_adapt (3x3, reflection pad, eval BatchNorm folded, ELU),
+ * dispconv_3 (3x3, zero pad) + sigmoid -> out f32 [B][2h][2w].  w1, w2, w3: packed [16][(ky*3+kx)*16 + c] bf16 (w3: row 0 = the
+ * single output channel), b1, b2, b3: f32 [16].  Intermediates never leave shared memory. */
+int mde_decoder_tail16(const mde_bf16* src_padded, int B, int h, int w, const mde_bf16* w1, const float* b1, const mde_bf16* w2, const float* b2,
+                       const mde_bf16* w3, const float* b3, float* out, mde_stream_t stream);
+
 /* ---- enhanced_model.py:95-98: rgb image f32 [B,3,H,W] -> bilinear (align_corners=False) to the gh x gw
  * grid, written as channels [out_coff, out_coff+3) of a padded NHWC bf16 tensor; channels up to
  * out_coff+cfill are zero-filled (K padding of the 259-channel refinement conv).  cfill, out_coff and out_cstride

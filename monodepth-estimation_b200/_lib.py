@@ -61,6 +61,7 @@ SIGNATURES = {
     "mde_conv_nhwc": [_p, _i, _i, _i, _i, _i, _p, _p, _i, _i, _i, _i, _p, _i, _i, _p, _p],
     "mde_conv_nhwc_f16": [_p, _i, _i, _i, _i, _i, _p, _p, _i, _i, _i, _i, _p, _i, _i, _p, _p],
     "mde_upsample2x_concat_nhwc": [_p, _i, _i, _i, _i, _p, _i, _i, _i, _p, _p],
+    "mde_decoder_tail16": [_p, _i, _i, _i, _p, _p, _p, _p, _p, _p, _p, _p],
     "mde_rgb_to_grid_nhwc": [_p, _i, _i, _i, _i, _i, _p, _i, _i, _i, _p],
     "mde_resize_maps": [C.POINTER(MapDesc), _i, _i, _i, _i, _f, _f, _p],
     "mde_spatial_attention": [_p, _p, _i, _i, _i, _p, _p, _p],

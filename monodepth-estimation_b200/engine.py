@@ -41,6 +41,9 @@ def _fingerprint(module):
 
 
 _LN_FUSION = os.environ.get("MDE_LN_FUSION") == "1"  # opt-in, see DepthEngine._vit
+# MDE_FUSED_TAIL=1: last decoder level as one kernel (csrc/decoder_tail.cu).  Opt-in: correct (tests/test_kernels_gpu.py) but slower than
+# the four tcgen05 launches it replaces (202 vs 141 us at batch 32: warp-level mma.sync runs at 1/8 of the tcgen05 rate, profiles/r02_experiments.md)
+_FUSED_TAIL = os.environ.get("MDE_FUSED_TAIL", "0") == "1"
 
 class Workspace:
     """All intermediates of one forward for a fixed (B, Hp, Wp); allocated once."""
@@ -271,6 +274,11 @@ class DepthEngine:
         for i in range(4):
             ci, co = DEC_CH[i], DEC_CH[i + 1]
             self._conv(x, h, w_, ci, dec[f"upconv_{i}_0"], co, L.ACT_ELU, out=ws.d_a[i])
+            if i == 3 and _FUSED_TAIL:
+                # upsample x2 + upconv_3_1 + mars_adapt + dispconv_3 + sigmoid: one kernel, intermediates stay in shared memory
+                ops.decoder_tail16(ws.d_a[3], h, w_, dec["upconv_3_1"], dec["mars_adapt"], dec["dispconv_3"], ws.disp[3])
+                n += 2
+                break
             s = ws.d_s[i] if i < 3 else None  # skip branch: computed with its feature (_feature)
             ops.upsample2x_concat(ws.d_a[i], h, w_, s, gh, gw, ws.d_cat[i])
             h, w_ = 2 * h, 2 * w_

@@ -146,6 +146,16 @@ def upsample2x_concat(a, h, w, s, hs, ws, out):
     return out
 
 
+def decoder_tail16(src_padded, h, w, wb1, wb2, wb3, out):
+    """decoder.py:139-168, level 3: upsample x2 + upconv_3_1 + mars_adapt + dispconv_3 + sigmoid in one kernel."""
+    B = src_padded.shape[0]
+    if src_padded.shape[-1] != 16 or any(t[0].shape != (16, 144) for t in (wb1, wb2, wb3)):
+        raise ValueError("decoder_tail16 serves the 16-channel last decoder level only")
+    L.call("mde_decoder_tail16", _ptr(src_padded, BF16), B, h, w, _ptr(wb1[0], BF16), _ptr(wb1[1], F32), _ptr(wb2[0], BF16), _ptr(wb2[1], F32),
+           _ptr(wb3[0], BF16), _ptr(wb3[1], F32), _ptr(out, F32), _stream())
+    return out
+
+
 def rgb_to_grid(x, gh, gw, out_padded, out_coff, cfill):
     B, _, H, W = x.shape
     L.call("mde_rgb_to_grid_nhwc", _ptr(x, F32), B, H, W, gh, gw, _ptr(out_padded, BF16), out_padded.shape[-1], out_coff, cfill, _stream())

@@ -321,6 +321,46 @@ def test_conv_head_f32_out(B, h, w, cin):
     assert max_abs(out, ref[:, 0]) < 2e-5, max_abs(out, ref[:, 0])
 
 
+@pytest.mark.parametrize("B,h,w", [(1, 112, 120), (2, 112, 112), (3, 20, 27), (1, 8, 16), (2, 9, 5)])
+def test_decoder_tail16_vs_torch_and_unfused_path(B, h, w):
+    """mde_decoder_tail16 (decoder.py:139-168, level 3: upsample x2, upconv_3_1, mars_adapt, dispconv_3 + sigmoid in one kernel)
+    against (a) a plain fp32 torch statement with the same bf16 rounding points and (b) the four-launch path it replaces.
+    Shapes: the real level (112x120 -> 224x240), the 14x14-grid level, sizes that are not tile multiples, maps smaller than a tile."""
+    L, ops = _mods()
+    from monodepth_estimation_b200.packing import pack_conv
+
+    x = _rand(B, 16, h, w, seed=60)
+    ws_, bs_ = [], []
+    for k, cout in enumerate((16, 16, 1)):
+        ws_.append(_rand(cout, 16, 3, 3, seed=61 + k, scale=(16 * 9) ** -0.5 * 1.5))
+        bs_.append(_rand(cout, seed=64 + k, scale=0.1))
+    packed = [pack_conv(wt, bs) for wt, bs in zip(ws_, bs_)]
+    xp = to_padded_nhwc(x)
+    out = torch.full((B, 2 * h, 2 * w), float("nan"), device="cuda")
+    ops.decoder_tail16(xp, h, w, packed[0], packed[1], packed[2], out)
+    torch.cuda.synchronize()
+    assert torch.isfinite(out).all()
+    # (a) torch fp32 with bf16-rounded operands / activations
+    r = lambda t: t.to(BF16).float()
+    wr = [p[0][:c].float().view(c, 3, 3, 16).permute(0, 3, 1, 2) for p, c in zip(packed, (16, 16, 1))]
+    t = r(F.interpolate(r(x), size=(2 * h, 2 * w), mode="bilinear", align_corners=True))
+    t = r(F.elu(F.conv2d(F.pad(t, (1, 1, 1, 1), mode="reflect"), wr[0], bs_[0])))
+    t = r(F.elu(F.conv2d(F.pad(t, (1, 1, 1, 1), mode="reflect"), wr[1], bs_[1])))
+    ref = torch.sigmoid(F.conv2d(t, wr[2], bs_[2], padding=1))[:, 0]
+    assert max_abs(out, ref) < 4e-3, max_abs(out, ref)  # bf16 re-rounding of two intermediate maps (1 ulp flips), sigmoid slope <= 1/4
+    assert rel_l2(out, ref) < 1.5e-3, rel_l2(out, ref)
+    # (b) the unfused path: upsample2x_concat + three conv launches
+    cat = torch.empty(B, 2 * h + 2, 2 * w + 2, 16, device="cuda", dtype=BF16)
+    ops.upsample2x_concat(xp, h, w, None, 0, 0, cat)
+    a1, a2 = torch.empty_like(cat), torch.empty_like(cat)
+    ops.conv_nhwc(cat, 2 * h, 2 * w, 16, packed[0][0], packed[0][1], 16, 3, L.PAD_REFLECT, L.ACT_ELU, out_bf16=a1)
+    ops.conv_nhwc(a1, 2 * h, 2 * w, 16, packed[1][0], packed[1][1], 16, 3, L.PAD_REFLECT, L.ACT_ELU, out_bf16=a2)
+    old = torch.empty(B, 2 * h, 2 * w, device="cuda")
+    ops.conv_nhwc(a2, 2 * h, 2 * w, 16, packed[2][0], packed[2][1], 1, 3, L.PAD_ZERO, L.ACT_SIGMOID, out_f32=old)
+    assert max_abs(out, old) < 4e-3, max_abs(out, old)
+    assert rel_l2(out, old) < 1.5e-3, rel_l2(out, old)
+
+
 def test_conv_folded_batchnorm_and_channel_offset():
     L, ops = _mods()
     from monodepth_estimation_b200.packing import pack_conv
