@@ -132,9 +132,15 @@ def load(build_if_needed: bool = True):
 
             try:
                 build()
-            except Exception:
-                if not os.path.exists(SO_PATH):
-                    raise
+            except Exception as e:
+                # Falling back to an existing libmde.so is only sound when it was built from the sources as they are now: a stale
+                # binary would make every parity result describe code that is no longer checked in.
+                from .build import OUT, is_stale
+
+                if SO_PATH != OUT:  # MDE_LIB_PATH names an A/B build: the in-tree build is irrelevant
+                    pass
+                elif not os.path.exists(SO_PATH) or is_stale():
+                    raise MdeError(f"building libmde.so failed and no up-to-date binary exists ({SO_PATH}): {e}") from e
         if not os.path.exists(SO_PATH):
             raise MdeError(f"{SO_PATH} is missing: run `python monodepth-estimation_b200/build.py` (needs nvcc)")
         lib = C.CDLL(SO_PATH)

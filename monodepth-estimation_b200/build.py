@@ -37,10 +37,21 @@ def _stale(target: str, deps: list[str]) -> bool:
     return any(os.path.getmtime(d) > t for d in deps)
 
 
-def build(force: bool = False, verbose: bool = False) -> str:
+def _inputs():
     srcs = [os.path.join(CSRC, s) for s in SOURCES if os.path.exists(os.path.join(CSRC, s))]
     headers = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".h", ".cuh"))]
     headers.append(os.path.join(os.path.dirname(HERE), "include", "mde.h"))
+    return srcs, headers
+
+
+def is_stale() -> bool:
+    """True when libmde.so is missing or older than any source / header it is built from."""
+    srcs, headers = _inputs()
+    return _stale(OUT, srcs + headers)
+
+
+def build(force: bool = False, verbose: bool = False) -> str:
+    srcs, headers = _inputs()
     if not force and not _stale(OUT, srcs + headers):
         return OUT
     os.makedirs(OBJ_DIR, exist_ok=True)

@@ -91,20 +91,49 @@ class _ViT(nn.Module):
         nn.init.zeros_(self.conv_proj.bias)
 
 
+def _imagenet_vit_state_dict():
+    """The ImageNet ViT-B/16 weights the reference loads at ``encoder.py:32-33`` (``vit_b_16(weights=ViT_B_16_Weights.IMAGENET1K_V1)``, ``encoder.py:32``),
+    read from torchvision's LOCAL checkpoint cache only (``torch.hub`` directory) — this build never downloads.  None if absent."""
+    import os
+
+    try:
+        from torchvision.models import ViT_B_16_Weights
+
+        url = ViT_B_16_Weights.IMAGENET1K_V1.url
+        path = os.path.join(torch.hub.get_dir(), "checkpoints", os.path.basename(url))
+    except Exception:
+        return None
+    if not os.path.exists(path):
+        return None
+    return torch.load(path, map_location="cpu", weights_only=True)
+
+
 class DepthAnythingEncoder(nn.Module):
     """Mirror of ``models/encoder.py:16`` — ViT-B/16 taps at blocks 2/5/8/11,
     1x1 768->256 channel reduction and instance norm.  The arithmetic lives in
     ``engine.DepthEngine``; this class owns the parameters."""
 
+    def _load_imagenet_vit(self):
+        """``pretrained=True`` (the reference's default, ``encoder.py:21,32``): copy the ImageNet weights into the mirror ViT.  The
+        reference downloads them; here they must already sit in torchvision's local cache — otherwise fail loudly."""
+        sd = _imagenet_vit_state_dict()
+        if sd is None:
+            raise RuntimeError(
+                "pretrained=True needs the ImageNet ViT-B/16 checkpoint (vit_b_16-c867db91.pth) in torch.hub's checkpoint cache: the "
+                "reference downloads it (encoder.py:32), this build never uses the network — construct with pretrained=False and load a state_dict"
+            )
+        own = self.encoder.state_dict()
+        missing = [k for k in own if k not in sd]
+        if missing:
+            raise RuntimeError(f"cached ViT checkpoint lacks {missing[:3]}...")
+        self.encoder.load_state_dict({k: sd[k] for k in own})  # the 'heads.*' entries are dropped (heads = Identity, encoder.py:38)
+
     def __init__(self, pretrained: bool = True):
         super().__init__()
-        if pretrained:
-            raise RuntimeError(
-                "pretrained=True needs the ImageNet ViT-B/16 checkpoint (network download in the reference, "
-                "encoder.py:33); load a state_dict instead"
-            )
         self.num_ch_enc = np.array([256, 256, 256, 256])
         self.encoder = _ViT()
+        if pretrained:
+            self._load_imagenet_vit()
         self.hook_layer_indices = list(HOOK_LAYERS)
         self.channel_reduce = nn.ModuleList([nn.Conv2d(VIT_HIDDEN, 256, 1) for _ in range(4)])
         self.normalize = nn.BatchNorm2d(3)

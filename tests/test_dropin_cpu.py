@@ -46,7 +46,7 @@ def test_no_cpu_fallback_and_train_mode_raises():
     with pytest.raises(RuntimeError):
         m(torch.rand(1, 3, 224, 224))  # CPU: the product path has no fallback
     with pytest.raises(RuntimeError):
-        mde.DepthAnything(pretrained=True)  # needs the ImageNet checkpoint (network)
+        mde.DepthAnything(pretrained=True)  # the ImageNet checkpoint is not in the local cache, and nothing is ever downloaded
 
 
 def test_product_never_imports_oracle():
@@ -80,3 +80,36 @@ def test_state_dict_and_init_identical_to_reference():
             assert a[k].shape == b[k].shape and torch.equal(a[k], b[k]), k
     m = mde.EnhancedDepthAnything(pretrained=False)
     assert sum(p.numel() for p in m.encoder.parameters()) > 8e7 and len(list(m.decoder.parameters())) > 0  # train/mars_adapter.py:49-50
+
+
+def test_pretrained_default_loads_the_cached_imagenet_vit(tmp_path, monkeypatch):
+    """The reference's default constructor (pretrained=True, encoder.py:21,32) works when torchvision's checkpoint is in the local
+    torch.hub cache: the mirror ViT then holds exactly those tensors (the 768->1000 head is dropped, encoder.py:38)."""
+    from torchvision.models import ViT_B_16_Weights
+    from torchvision.models.vision_transformer import vit_b_16
+
+    torch.manual_seed(3)
+    tv = vit_b_16(weights=None)
+    ck = tmp_path / "hub" / "checkpoints"
+    ck.mkdir(parents=True)
+    torch.save(tv.state_dict(), ck / os.path.basename(ViT_B_16_Weights.IMAGENET1K_V1.url))
+    monkeypatch.setattr(torch.hub, "get_dir", lambda: str(tmp_path / "hub"))
+    m = mde.DepthAnything()  # pretrained=True
+    got = m.encoder.encoder.state_dict()
+    want = {k: v for k, v in tv.state_dict().items() if not k.startswith("heads.")}
+    assert set(got) == set(want)
+    assert all(torch.equal(got[k], want[k]) for k in want)
+
+
+def test_stale_library_is_not_silently_reused(monkeypatch):
+    """if the build fails while the sources are newer than libmde.so, load() must raise instead of binding the old binary."""
+    from monodepth_estimation_b200 import _lib
+    from monodepth_estimation_b200 import build as B
+
+    monkeypatch.setattr(_lib, "_lib", None)
+    monkeypatch.setattr(B, "build", lambda *a, **k: (_ for _ in ()).throw(RuntimeError("nvcc failed")))
+    monkeypatch.setattr(B, "is_stale", lambda: True)
+    with pytest.raises(_lib.MdeError, match="no up-to-date binary"):
+        _lib.load()
+    monkeypatch.setattr(B, "is_stale", lambda: False)  # binary matches the sources (e.g. a box without nvcc): fine
+    assert _lib.load().mde_version() >= 100
