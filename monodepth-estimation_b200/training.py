@@ -298,6 +298,43 @@ class _ConvBlockT:
         return dx, {"conv.0.conv.1.weight": dwt, "conv.0.conv.1.bias": dcb, "conv.1.weight": dg, "conv.1.bias": db}
 
 
+def _to_padded_bf16(y_nhwc):
+    """fp32 NHWC -> bf16 padded NHWC with the reflected border the inference conv kernels read (layout glue, torch ops)."""
+    import torch.nn.functional as F
+
+    B, h, w, Cc = y_nhwc.shape  # reflection over (h, w) with the channel axis innermost: a 3-D reflection pad with no padding on the last axis
+    return F.pad(y_nhwc.reshape(1, B, h, w, Cc), (0, 0, 1, 1, 1, 1), mode="reflect").view(B, h + 2, w + 2, Cc).to(BF16)
+
+
+class _ConvBlockStatsT:
+    """decoder.py:22-34 in train mode, FORWARD ONLY, for the decoder levels whose outputs the loss never sees (levels 1-3): the
+    reference still runs them under ``model.train()``, so their BatchNorm running statistics advance every step.  The 3x3
+    convolution runs on the inference kernels (``mde_conv_nhwc``, BatchNorm NOT folded, no activation, bf16 out), the batch
+    statistics / running-statistic update / normalisation / ELU on ``mde_bn_elu_train_fwd``."""
+
+    def __init__(self, sd, prefix, dev):
+        g = lambda k: sd[prefix + k]
+        self.cw, self.cb = g("conv.0.conv.1.weight"), g("conv.0.conv.1.bias")
+        self.bw, self.bb, self.rm, self.rv = g("conv.1.weight"), g("conv.1.bias"), g("conv.1.running_mean"), g("conv.1.running_var")
+        self.co, self.ci = self.cw.shape[0], self.cw.shape[1]
+        self.dev = dev
+        self.repack()
+
+    def repack(self):
+        from .packing import pack_conv
+
+        self.wp, self.bp = pack_conv(self.cw.detach(), self.cb.detach())
+
+    def forward(self, xp, h, w):
+        """xp: bf16 padded NHWC [B, h+2, w+2, ci] -> bf16 padded NHWC [B, h+2, w+2, co]."""
+        B = xp.shape[0]
+        z = torch.empty(B, h + 2, w + 2, self.co, device=self.dev, dtype=BF16)
+        ops.conv_nhwc(xp, h, w, self.ci, self.wp, self.bp, self.co, 3, L.PAD_REFLECT, L.ACT_NONE, out_bf16=z)
+        zf = z[:, 1:-1, 1:-1, :].float().reshape(B * h * w, self.co)
+        y, _, _ = ops.bn_elu_train_fwd(zf, self.co, self.bw.detach(), self.bb.detach(), run_mean=self.rm, run_var=self.rv)
+        return _to_padded_bf16(y.view(B, h, w, self.co))
+
+
 class _DispHeadT:
     """decoder.py:86-88,166: Conv2d(C, 1, 3, padding=1) + sigmoid, times the source scale (model.py:63-92)."""
 
@@ -339,11 +376,12 @@ class DepthTrainer:
     train-mode forward of everything ``('disp', 0)`` depends on, ``compute_losses`` (:209-247), backward, Adam with the
     reference's two learning-rate groups (:47-55).  The model's fp32 parameters and BatchNorm buffers are updated in place.
 
-    Deviations, stated once: the ``torch.rand_like`` draw of :238 is an argument; decoder levels 1-3 do not influence the loss
-    and are not run in train mode (their outputs are not returned and their BatchNorm running statistics are not advanced).
+    Decoder levels 1-3 do not influence the loss; they are run forward-only in train mode (``full_decoder=True``, the default) so that
+    every BatchNorm buffer — running statistics and ``num_batches_tracked`` — ends the step as ``model.train(); model(x)`` leaves it
+    in the reference.  Deviations, stated once: the ``torch.rand_like`` draw of :238 is an argument; only ``('disp', 0)`` is returned.
     """
 
-    def __init__(self, model, lr=1e-4, w_depth=1.0, w_smooth=0.001, betas=(0.9, 0.999), eps=1e-8, graph=True):
+    def __init__(self, model, lr=1e-4, w_depth=1.0, w_smooth=0.001, betas=(0.9, 0.999), eps=1e-8, graph=True, full_decoder=True):
         self.model, self.lr, self.w_depth, self.w_smooth, self.betas, self.eps = model, lr, w_depth, w_smooth, betas, eps
         self.graph, self._graphs = graph, {}
         # ViT blocks after which a data-parallel step starts reducing what it has (see step()); MDE_TRAIN_SPLITS="9,6,3" overrides
@@ -357,10 +395,15 @@ class DepthTrainer:
         d = lambda k: self.sd[k].detach()
         vit = {k[len("encoder.encoder."):]: d(k) for k in self.sd if k.startswith("encoder.encoder.")}
         self.enc = ViTEncoderTrainer(vit)
-        self.feat = {i: _FeatureT(d(f"encoder.channel_reduce.{i}.weight"), d(f"encoder.channel_reduce.{i}.bias"), self.dev) for i in (2, 3)}
+        self.full_decoder = full_decoder
+        self.feat = {i: _FeatureT(d(f"encoder.channel_reduce.{i}.weight"), d(f"encoder.channel_reduce.{i}.bias"), self.dev)
+                     for i in ((0, 1, 2, 3) if full_decoder else (2, 3))}
         det = {k: d(k) for k in self.sd}
         self.blocks = {n: _ConvBlockT(det, f"decoder.convs.{n}.", self.dev) for n in ("init_conv", "upconv_0_0", "skip_0", "upconv_0_1")}
         self.head = _DispHeadT(d("decoder.convs.dispconv_0.weight"), d("decoder.convs.dispconv_0.bias"), self.dev)
+        # decoder levels 1-3 (decoder.py:106-168): forward only, for their BatchNorm running statistics
+        self._stats_names = ["upconv_1_0", "skip_1", "upconv_1_1", "upconv_2_0", "skip_2", "upconv_2_1", "upconv_3_0", "upconv_3_1", "mars_adapt"] if full_decoder else []
+        self.stats_blocks = {n: _ConvBlockStatsT(det, f"decoder.convs.{n}.", self.dev) for n in self._stats_names}
         self.state, self.t = {}, 0
         self.step_dev = torch.zeros(1, device=self.dev, dtype=torch.int32)  # Adam's step count where a replayed graph can read it
         # the two learning rates (train/mars_adapter.py:47-55: encoder.* at lr / 10, the rest at lr) live on the device too: a
@@ -368,7 +411,7 @@ class DepthTrainer:
         self.lr_dev = torch.tensor([lr / 10, lr], device=self.dev, dtype=F32)
         # BatchNorm layers that run in train mode here: their num_batches_tracked advances once per step, as nn.BatchNorm2d does
         self.nbt = [self.sd[k] for k in (["encoder.normalize.num_batches_tracked"] +
-                                         [f"decoder.convs.{n}.conv.1.num_batches_tracked" for n in ("init_conv", "upconv_0_0", "skip_0", "upconv_0_1")])]
+                                         [f"decoder.convs.{n}.conv.1.num_batches_tracked" for n in ["init_conv", "upconv_0_0", "skip_0", "upconv_0_1"] + self._stats_names])]
         self.scratch = torch.empty(L.RANGE_SCRATCH_FLOATS, device=self.dev, dtype=F32)
         self.affine = torch.empty(6, device=self.dev, dtype=F32)
 
@@ -376,7 +419,7 @@ class DepthTrainer:
         for b in self.enc.blocks:
             b.repack()
         self.enc.repack()
-        for m in list(self.feat.values()) + list(self.blocks.values()) + [self.head]:
+        for m in list(self.feat.values()) + list(self.blocks.values()) + [self.head] + list(self.stats_blocks.values()):
             m.repack()
 
     def forward_backward(self, images, metadata, rnd):
@@ -411,6 +454,7 @@ class DepthTrainer:
         raw224 = torch.empty(B, 3, 224, 224, device=dev, dtype=F32)
         patches = torch.empty(B * 196, 768, device=dev, dtype=BF16)
         ops.input_stage(xin, bn, 1e-5, self.scratch, self.affine, raw224, patches)
+        torch._foreach_add_(self.nbt, 1)  # nn.BatchNorm2d.forward in train mode: num_batches_tracked += 1, once per forward
         taps = self.enc.forward(patches)
         f3 = self.feat[3].forward(taps[3], B, strip, G).view(B, gh, gw, 256)
         f2 = self.feat[2].forward(taps[2], B, strip, G).view(B, gh, gw, 256)
@@ -422,6 +466,8 @@ class DepthTrainer:
         ops.bilinear_nhwc(x1, 2 * gh, 2 * gw, True, dst=cat, coff=0)        # :118-120
         ops.bilinear_nhwc(s0, 2 * gh, 2 * gw, True, dst=cat, coff=128)      # :136-145
         x2 = blk["upconv_0_1"].forward(cat)                                 # :152
+        if self.full_decoder:
+            self._decoder_stats_forward(x2, taps, B, strip, gh, gw)
         sc = source_scale(metadata)
         disp0 = self.head.forward(x2, 1.0 if sc is None else sc)            # :166 + model.py:63-92
         disp = ops.bilinear_nhwc(disp0, H0, W0, False).view(B, 1, H0, W0)   # model.py:95-100 (C = 1: NHWC == NCHW)
@@ -458,6 +504,24 @@ class DepthTrainer:
         g["encoder.normalize.weight"], g["encoder.normalize.bias"] = dn[:3].clone(), dn[3:].clone()
         yield losses, g
 
+    def _decoder_stats_forward(self, x2, taps, B, strip, gh, gw):
+        """decoder.py:106-168 for levels 1-3 in train mode: their outputs do not reach the loss (only ('disp', 0) does,
+        train/mars_adapter.py:219), but ``model.train(); model(x)`` runs them, so every BatchNorm there sees one batch per step."""
+        G = gh * gw
+        sb = self.stats_blocks
+        feats = {i: _to_padded_bf16(self.feat[i].forward(taps[i], B, strip, G).view(B, gh, gw, 256)) for i in (0, 1)}
+        xp = _to_padded_bf16(x2)
+        h, w = 2 * gh, 2 * gw
+        for i in (1, 2, 3):
+            a = sb[f"upconv_{i}_0"].forward(xp, h, w)                                    # :113
+            s = sb[f"skip_{i}"].forward(feats[2 - i], gh, gw) if i < 3 else None           # :126-137 (features[-(i+2)])
+            cat = torch.empty(B, 2 * h + 2, 2 * w + 2, a.shape[-1] * (2 if i < 3 else 1), device=self.dev, dtype=BF16)
+            ops.upsample2x_concat(a, h, w, s, gh, gw, cat)                                 # :118-145
+            h, w = 2 * h, 2 * w
+            xp = sb[f"upconv_{i}_1"].forward(cat, h, w)                                   # :152
+            if i == 3:
+                xp = sb["mars_adapt"].forward(xp, h, w)                                   # :157-158
+
     def set_lr(self, lr: float):
         """Change the base learning rate (group 0 = encoder.* gets lr / 10).  Safe between replays of the captured step."""
         self.lr = float(lr)
@@ -474,7 +538,6 @@ class DepthTrainer:
         """torch.optim.Adam over the reference's two groups (train/mars_adapter.py:47-55): encoder.* at lr/10, decoder.* at lr.
         One multi-tensor launch (``mde_adam_multi``); ``plan`` caches its device tables when the gradient buffers are stable."""
         self.step_dev += 1
-        torch._foreach_add_(self.nbt, 1)
         if plan is None:
             plan = self._adam_plan(grads)
         plan.step(self.lr_dev, self.step_dev, self.betas[0], self.betas[1], self.eps)

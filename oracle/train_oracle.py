@@ -45,6 +45,9 @@ def loss_and_grads(sd, images, metadata, rnd, w_depth=1.0, w_smooth=0.001):
     losses["total"].backward()
     grads = {k: v.grad for k, v in leaves.items() if v.requires_grad and v.grad is not None}
     buffers = {k: v.detach() for k, v in leaves.items() if is_buffer(k)}
+    for k in buffers:  # nn.BatchNorm2d.forward in train mode: every BatchNorm of the model runs once per step (encoder.normalize + 13 ConvBlocks)
+        if k.endswith("num_batches_tracked"):
+            buffers[k] = buffers[k] + 1
     return {k: float(v) for k, v in losses.items()}, grads, buffers
 
 

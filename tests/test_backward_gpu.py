@@ -379,9 +379,21 @@ def test_training_step_matches_train_oracle():
     print("losses", got, "largest gradient errors", [(k, round(e, 4)) for e, k in errs[:12]], "median", errs[len(errs) // 2][0])
     assert errs[0][0] < 5e-2, errs[:5]
     assert set(grads) <= set(want_grads), set(grads) - set(want_grads)
-    for k in ("decoder.convs.init_conv.conv.1.running_mean", "decoder.convs.upconv_0_1.conv.1.running_var", "encoder.normalize.running_mean",
-              "encoder.normalize.running_var"):
-        assert rel_l2(m.state_dict()[k], want_buffers[k]) < 2e-2, k
+    # every BatchNorm buffer of the model after ONE train-mode forward, as model.train(); model(x) leaves them in the reference:
+    # encoder.normalize + all 13 decoder ConvBlocks (levels 1-3 run forward-only: decoder.py:106-168), num_batches_tracked included
+    sd_now = m.state_dict()
+    n_stats = 0
+    worst = ("", 0.0)
+    for k, wb in want_buffers.items():
+        if k.endswith(("running_mean", "running_var")):
+            e = rel_l2(sd_now[k], wb)
+            worst = max(worst, (k, e), key=lambda t: t[1])
+            assert e < 2e-2, (k, e)
+            n_stats += 1
+        elif k.endswith("num_batches_tracked"):
+            assert int(sd_now[k]) == int(wb) == 1, k
+    assert n_stats == 28, n_stats
+    print("worst running statistic", worst)
     # ---- one optimizer step (train/mars_adapter.py:47-55,139): Adam, encoder.* at lr/10, decoder.* at lr
     before = {k: v.detach().clone() for k, v in m.state_dict().items()}
     tr.step(x.cuda(), md, rnd.cuda())

@@ -57,3 +57,6 @@ def test_train_oracle_matches_reference_train_mode():
     for k, b in ref.named_buffers():
         if k.endswith(("running_mean", "running_var")):
             assert rel_l2(buffers[k], b) < 1e-5, k
+        elif k.endswith("num_batches_tracked"):
+            assert int(buffers[k]) == int(b) == 1, k
+    assert sum(k.endswith("num_batches_tracked") for k in buffers) == 14
