@@ -15,7 +15,8 @@
 // the low-channel layers (small shared-memory footprint) several CTAs per SM: with one warp per scheduler the
 // dependent-issue latency of the ELU/pack/store chain, not HBM, bounded the 16-channel layers (r01g: 113 us for 17 us of traffic).  The epilogue itself is shared with tc_gemm.cu: bias,
 // folded BN, ELU/sigmoid, bf16/fp16 padded-NHWC store with reflected border, or fp32 head.  Two accumulator sets in TMEM overlap the epilogue of tile
-// i with the MMAs of tile i+1.
+// i with the MMAs of tile i+1.  (A finer hand-off, one tcgen05.commit per 128-pixel MMA block, measured 8-12 % SLOWER on every
+// layer shape, r02: profiles/r02_experiments.md.)
 #include <stdlib.h>
 
 #include <algorithm>
@@ -129,7 +130,14 @@ __global__ void __launch_bounds__(kHaloThreads, BLOCK_N <= 16 ? 3 : BLOCK_N <= 3
     // ------------------------------------------------------------------ MMA issuer
     if (elect_one()) {
       const uint32_t idesc = p.f16 ? umma_idesc_f16(128, BLOCK_N) : umma_idesc_bf16(128, BLOCK_N);
-      const uint32_t w_base = smem_u32(sW);
+      // Shared-memory descriptors differ only in their start-address field (bits 0..13, address >> 4; every address here is below
+      // 256 KB, so sums never carry out of the field): build one per operand and ADD the stage / block / tap / k-step offsets
+      // instead of rebuilding a descriptor (~15 instructions) per MMA.
+      const uint64_t da0 = umma_smem_desc_kmajor<ROWB>(smem_u32(sH));
+      const uint64_t db0 = umma_smem_desc_kmajor<ROWB>(smem_u32(sW));
+      const uint32_t stage_step = (uint32_t)p.stage_bytes >> 4;
+      const uint32_t wchunk_step = (uint32_t)WB >> 4, wtap_step = (uint32_t)(p.chunks * WB) >> 4;
+      constexpr uint32_t kBlkStep = (128 * ROWB) >> 4;
       int stage = 0, acc = 0;
       uint32_t phase = 0, acc_phase = 0;
       mbar_wait(w_bar, 0);
@@ -139,14 +147,16 @@ __global__ void __launch_bounds__(kHaloThreads, BLOCK_N <= 16 ? 3 : BLOCK_N <= 3
         for (int c = 0; c < p.chunks; ++c) {
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after();
-          const uint32_t a_base = smem_u32(sH + (size_t)stage * p.stage_bytes);
+          const uint64_t da_s = da0 + (uint32_t)stage * stage_step;
+          const uint64_t db_c = db0 + (uint32_t)c * wchunk_step;
           for (int j = 0; j < ((p.dbg & 2) ? 0 : p.nblk); ++j) {
             const uint32_t d_tmem = tmem_base + (uint32_t)((acc * p.nblk + j) * BLOCK_N);
+            const uint64_t da_b = da_s + (uint32_t)j * kBlkStep;
 #pragma unroll
             for (int t = 0; t < 9; ++t) {
               const int dy = t / 3, dx = t - 3 * dy;
-              const uint64_t da = umma_smem_desc_kmajor<ROWB>(a_base + (uint32_t)((128 * j + dy * kHaloPitch + dx) * ROWB));
-              const uint64_t db = umma_smem_desc_kmajor<ROWB>(w_base + (uint32_t)((t * p.chunks + c) * WB));
+              const uint64_t da = da_b + (uint32_t)(((dy * kHaloPitch + dx) * ROWB) >> 4);
+              const uint64_t db = db_c + (uint32_t)t * wtap_step;
 #pragma unroll
               for (int k = 0; k < KC / 16; ++k) umma_bf16_ss(d_tmem, da + 2 * k, db + 2 * k, idesc, (c | t | k) != 0);
             }

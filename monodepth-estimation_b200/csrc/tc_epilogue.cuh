@@ -45,10 +45,11 @@ __device__ __forceinline__ void epilogue_conv(const P& p, float (&v)[NCOL], int 
   uint32_t pk[NCOL / 2];
 #pragma unroll
   for (int j = 0; j < NCOL / 2; ++j) pk[j] = p.f16 ? pack_f16x2(v[2 * j], v[2 * j + 1]) : pack_bf16x2(v[2 * j], v[2 * j + 1]);
-  const int H2 = p.h + 2, W2 = p.w + 2;
-  bf16* obase = reinterpret_cast<bf16*>(p.out) + p.out_coff + n0;
-  auto store_px = [&](int Y, int X) {  // padded coordinates
-    uint4* dst = reinterpret_cast<uint4*>(obase + (((size_t)ri.b * H2 + Y) * W2 + X) * p.out_cstride);
+  const int W2 = p.w + 2;
+  // interior pixel (y, x) lives at padded (y + 1, x + 1)
+  bf16* px = reinterpret_cast<bf16*>(p.out) + p.out_coff + n0 + (((size_t)ri.b * (p.h + 2) + ri.y + 1) * W2 + ri.x + 1) * p.out_cstride;
+  auto store_at = [&](int dpix) {  // this pixel's channels, dpix padded pixels away
+    uint4* dst = reinterpret_cast<uint4*>(px + (ptrdiff_t)dpix * p.out_cstride);
     if (p.st32) {  // 32-byte stores (host checked alignment and cout % 16 == 0)
 #pragma unroll
       for (int j = 0; j < NCOL / 16; ++j)
@@ -61,20 +62,22 @@ __device__ __forceinline__ void epilogue_conv(const P& p, float (&v)[NCOL], int 
         if (8 * j < nv) dst[j] = make_uint4(pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
     }
   };
-  store_px(ri.y + 1, ri.x + 1);  // interior pixel
-  // the reflected border copies this pixel owns (rows 1 / h-2 -> padded rows 0 / h+1, same for columns): rare path
-  const bool by = ri.y == 1 || ri.y == p.h - 2, bx = ri.x == 1 || ri.x == p.w - 2;
-  if (by || bx) {
-#pragma unroll 1
-    for (int iy = 0; iy < 3; ++iy) {
-      const int Y = iy == 0 ? ri.y + 1 : iy == 1 ? (ri.y == 1 ? 0 : -1) : (ri.y == p.h - 2 ? p.h + 1 : -1);
-      if (Y < 0) continue;
-#pragma unroll 1
-      for (int ix = 0; ix < 3; ++ix) {
-        const int X = ix == 0 ? ri.x + 1 : ix == 1 ? (ri.x == 1 ? 0 : -1) : (ri.x == p.w - 2 ? p.w + 1 : -1);
-        if (X < 0 || (iy == 0 && ix == 0)) continue;
-        store_px(Y, X);
-      }
+  store_at(0);
+  // the reflected border copies this pixel owns: column 1 -> padded column 0, column w-2 -> padded column w+1, same for rows, and
+  // the corner copies where both hold.  Straight-line code: a loop over the 3x3 candidates cost the border tiles a third more time.
+  const bool xl = ri.x == 1, xr = ri.x == p.w - 2, yt = ri.y == 1, yb = ri.y == p.h - 2;
+  if (xl | xr | yt | yb) {
+    if (xl) store_at(-2);
+    if (xr) store_at(2);
+    if (yt) {
+      store_at(-2 * W2);
+      if (xl) store_at(-2 * W2 - 2);
+      if (xr) store_at(-2 * W2 + 2);
+    }
+    if (yb) {
+      store_at(2 * W2);
+      if (xl) store_at(2 * W2 - 2);
+      if (xr) store_at(2 * W2 + 2);
     }
   }
 }

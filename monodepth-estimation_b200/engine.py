@@ -44,6 +44,8 @@ _LN_FUSION = os.environ.get("MDE_LN_FUSION") == "1"  # opt-in, see DepthEngine._
 # MDE_FUSED_TAIL=1: last decoder level as one kernel (csrc/decoder_tail.cu).  Opt-in: correct (tests/test_kernels_gpu.py) but slower than
 # the four tcgen05 launches it replaces (202 vs 141 us at batch 32: warp-level mma.sync runs at 1/8 of the tcgen05 rate, profiles/r02_experiments.md)
 _FUSED_TAIL = os.environ.get("MDE_FUSED_TAIL", "0") == "1"
+# the 1-channel heads of decoder levels 0-2 run on the side stream (MDE_SIDE_HEADS=0: in line, for A/B timing)
+_SIDE_HEADS = os.environ.get("MDE_SIDE_HEADS", "1") == "1"
 
 class Workspace:
     """All intermediates of one forward for a fixed (B, Hp, Wp); allocated once."""
@@ -268,6 +270,8 @@ class DepthEngine:
         """decoder.py:90-173."""
         dec, gh, gw = w["dec"], ws.gh, ws.gw
         n = 0
+        main = torch.cuda.current_stream()
+        side = self.side if _SIDE_HEADS else None
         self._conv(feats[3], gh, gw, 256, dec["init_conv"], 256, L.ACT_ELU, out=ws.d_init)
         n += 1
         x, h, w_ = ws.d_init, gh, gw
@@ -289,8 +293,16 @@ class DepthEngine:
                 self._conv(x, h, w_, 16, dec["mars_adapt"], 16, L.ACT_ELU, out=ws.d_x3b)
                 x = ws.d_x3b
                 n += 1
-            self._conv(x, h, w_, co, dec[f"dispconv_{i}"], 1, L.ACT_SIGMOID, out_f32=ws.disp[i], pad=L.PAD_ZERO)
+            if i < 3 and side is not None:
+                # the heads of levels 0-2 feed only the output stage: off the critical path, next to the next level's convs
+                side.wait_stream(main)
+                with torch.cuda.stream(side):
+                    self._conv(x, h, w_, co, dec[f"dispconv_{i}"], 1, L.ACT_SIGMOID, out_f32=ws.disp[i], pad=L.PAD_ZERO)
+            else:
+                self._conv(x, h, w_, co, dec[f"dispconv_{i}"], 1, L.ACT_SIGMOID, out_f32=ws.disp[i], pad=L.PAD_ZERO)
             n += 1
+        if side is not None:
+            main.wait_stream(side)
         return n
 
     def _body(self, ws, w, scale, want=None):

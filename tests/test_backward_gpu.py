@@ -330,16 +330,18 @@ def test_input_norm_bwd_matches_autograd(scale255):
     assert rel_l2(got, want) < 1e-4, (got, want)
 
 
-def test_training_step_matches_train_oracle():
+@pytest.mark.parametrize("B,H,W", [(2, 176, 240), (8, 518, 518)], ids=["b2_176x240", "config5_b8_518"])
+def test_training_step_matches_train_oracle(B, H, W):
     """DepthTrainer (train/mars_adapter.py:117-153 on the device) against oracle/train_oracle.py — itself pinned to the real
     reference classes in train() mode (tests/test_train_oracle.py): losses, every parameter gradient, BatchNorm running
-    statistics, and the parameters after one Adam step."""
+    statistics, and the parameters after one Adam step.  The second case is BASELINE.json configs[4] (B=8 at 518x518)."""
     import monodepth_estimation_b200 as mde
+    from helpers import ledger_add
     from monodepth_estimation_b200.synth import synth_images, synth_state_dict
     from monodepth_estimation_b200.training import DepthTrainer
     from oracle import train_oracle as T
 
-    B, H, W = 2, 176, 240
+    case = f"train:b{B}_{H}x{W}"
     m = mde.DepthAnything(pretrained=False)
     sd0 = synth_state_dict(m.state_dict(), 0)
     # F.instance_norm (encoder.py:167) divides by the spread of a channel ACROSS grid positions.  With the stock random init every
@@ -358,6 +360,8 @@ def test_training_step_matches_train_oracle():
     tr = DepthTrainer(m, lr=1e-4)
     losses, grads = tr.forward_backward(x.cuda(), md, rnd.cuda())
     got = [float(v) for v in losses.cpu()]
+    ledger_add(case, "loss/depth", "rel", abs(got[1] - want_losses["depth"]) / want_losses["depth"], 2e-2, "training step")
+    ledger_add(case, "loss/smoothness", "rel", abs(got[2] - want_losses["smoothness"]) / want_losses["smoothness"], 6e-2, "training step")
     assert abs(got[1] - want_losses["depth"]) < 2e-2 * want_losses["depth"], (got, want_losses)
     # the smoothness term sums |differences of neighbouring disparities|: bf16-level noise (3e-3) on a map whose neighbours differ by
     # a few per cent is amplified accordingly
@@ -377,6 +381,8 @@ def test_training_step_matches_train_oracle():
     errs.sort(reverse=True)
     print("non-ViT gradient errors", [(k.replace("decoder.convs.", "d."), round(e, 4)) for e, k in errs if "encoder.encoder." not in k])
     print("losses", got, "largest gradient errors", [(k, round(e, 4)) for e, k in errs[:12]], "median", errs[len(errs) // 2][0])
+    ledger_add(case, "grad/" + errs[0][1], "rel_l2", errs[0][0], 5e-2, "training step: worst parameter gradient")
+    ledger_add(case, "grad/median", "rel_l2", errs[len(errs) // 2][0], 5e-2, "training step: median parameter gradient")
     assert errs[0][0] < 5e-2, errs[:5]
     assert set(grads) <= set(want_grads), set(grads) - set(want_grads)
     # every BatchNorm buffer of the model after ONE train-mode forward, as model.train(); model(x) leaves them in the reference:
@@ -393,6 +399,7 @@ def test_training_step_matches_train_oracle():
         elif k.endswith("num_batches_tracked"):
             assert int(sd_now[k]) == int(wb) == 1, k
     assert n_stats == 28, n_stats
+    ledger_add(case, "bn/" + worst[0], "rel_l2", worst[1], 2e-2, "training step: worst BatchNorm running statistic")
     print("worst running statistic", worst)
     # ---- one optimizer step (train/mars_adapter.py:47-55,139): Adam, encoder.* at lr/10, decoder.* at lr
     before = {k: v.detach().clone() for k, v in m.state_dict().items()}
