@@ -10,8 +10,8 @@
 // addresses, no data movement.  The hardware swizzle is a function of the shared-memory address bits, so a view that
 // starts at any 16-byte-aligned row of a TMA-written tile stays consistent with how TMA laid the tile out.
 //
-// Warp roles (320 threads): warp 0 TMA producer (weights once, then one halo box per tile and channel chunk), warp 1
-// TMEM allocator + MMA issuer, warps 2..9 epilogue — two warps per TMEM lane quarter taking alternate MMA blocks, and for
+// Warp roles: warp 0 TMA producer (weights once, then one halo box per tile and channel chunk), warp 1
+// TMEM allocator + MMA issuer, warps 2.. epilogue — two or four warps per TMEM lane quarter dealing out the MMA blocks and column chunks, and for
 // the low-channel layers (small shared-memory footprint) several CTAs per SM: with one warp per scheduler the
 // dependent-issue latency of the ELU/pack/store chain, not HBM, bounded the 16-channel layers (r01g: 113 us for 17 us of traffic).  The epilogue itself is shared with tc_gemm.cu: bias,
 // folded BN, ELU/sigmoid, bf16/fp16 padded-NHWC store with reflected border, or fp32 head.  Two accumulator sets in TMEM overlap the epilogue of tile
@@ -29,8 +29,17 @@ namespace mde {
 
 constexpr int kHaloPitch = 64;  // halo tile width in pixels
 constexpr int kHaloTW = 62;     // real outputs per tile row
-constexpr int kHaloThreads = 320;
-constexpr int kHaloEpiWarps = 8;
+// Epilogue warps per CTA.  The 128-channel layers run ONE CTA per SM (TMEM: 2 x 2 blocks x 128 columns), and with 8 epilogue
+// warps that is two warps per scheduler for ~9 instructions (one of them MUFU) per output element: 16 warps, four per TMEM lane
+// quarter, took the 16->128 layer at 512x512x4 from 131 to 111 us (r02).  N = 64 measured no better with 12 or 16 (89.6 / 89.0 / 91.7 us).
+__host__ __device__ constexpr int halo_epi_warps(int block_n) {
+#ifdef MDE_HALO_EPIW
+  return block_n >= 128 ? MDE_HALO_EPIW : 8;
+#else
+  return block_n >= 128 ? 16 : 8;
+#endif
+}
+__host__ __device__ constexpr int halo_threads(int block_n) { return 64 + 32 * halo_epi_warps(block_n); }
 constexpr int kHaloMaxStages = 4;
 
 struct alignas(64) HaloParams {
@@ -50,7 +59,7 @@ struct alignas(64) HaloParams {
 };
 
 template <int BLOCK_N, int ROWB>
-__global__ void __launch_bounds__(kHaloThreads, BLOCK_N <= 16 ? 3 : BLOCK_N <= 32 ? 2 : 1) conv_halo_kernel(const __grid_constant__ HaloParams p) {
+__global__ void __launch_bounds__(halo_threads(BLOCK_N), BLOCK_N <= 16 ? 3 : BLOCK_N <= 32 ? 2 : 1) conv_halo_kernel(const __grid_constant__ HaloParams p) {
   pdl_launch_dependents();
   constexpr int KC = ROWB / 2;
   constexpr int WB_RAW = BLOCK_N * ROWB;
@@ -87,7 +96,7 @@ __global__ void __launch_bounds__(kHaloThreads, BLOCK_N <= 16 ? 3 : BLOCK_N <= 3
       }
       for (int a = 0; a < 2; ++a) {
         mbar_init(&tfull_bar[a], 1);
-        mbar_init(&tempty_bar[a], kHaloEpiWarps);
+        mbar_init(&tempty_bar[a], halo_epi_warps(BLOCK_N));
       }
       mbar_init(w_bar, 1);
       fence_barrier_init();
@@ -175,7 +184,8 @@ __global__ void __launch_bounds__(kHaloThreads, BLOCK_N <= 16 ? 3 : BLOCK_N <= 3
   } else {
     // ------------------------------------------------------------------ epilogue warps
     const int q = warp & 3;
-    const int half = (warp - 2) >> 2;  // the two warps of a lane quarter take alternate MMA blocks
+    const int sub = (warp - 2) >> 2;  // the warps of a lane quarter deal out the (MMA block, column chunk) items of a tile
+    constexpr int kSubs = halo_epi_warps(BLOCK_N) / 4, kChunks = BLOCK_N / NCOL;
     int acc = 0;
     uint32_t acc_phase = 0;
     for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
@@ -183,7 +193,8 @@ __global__ void __launch_bounds__(kHaloThreads, BLOCK_N <= 16 ? 3 : BLOCK_N <= 3
       const int y0 = (r / p.tiles_x) * p.th, x0 = (r % p.tiles_x) * kHaloTW;
       mbar_wait(&tfull_bar[acc], acc_phase);
       tc_fence_after();
-      for (int j = half; j < ((p.dbg & 1) ? 0 : p.nblk); j += 2) {
+      for (int i = sub; i < ((p.dbg & 1) ? 0 : p.nblk * kChunks); i += kSubs) {
+        const int j = i / kChunks, c = i - j * kChunks;
         const int o = 128 * j + q * 32 + lane;
         const int yy = o >> 6, xx = o & 63;
         RowInfo ri;
@@ -194,18 +205,15 @@ __global__ void __launch_bounds__(kHaloThreads, BLOCK_N <= 16 ? 3 : BLOCK_N <= 3
         ri.valid = xx < kHaloTW && ri.y < p.h && ri.x < p.w && !(p.dbg & 4);
         if (p.dbg & 16) ri.b = 0, ri.y = 2, ri.x = 2;  // every lane stores to one pixel: same instructions, no store traffic
         const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + (uint32_t)((acc * p.nblk + j) * BLOCK_N);
-#pragma unroll 1
-        for (int c = 0; c < BLOCK_N / NCOL; ++c) {
-          uint32_t raw[NCOL];
-          if constexpr (NCOL == 32) tmem_ld_32x32b_x32(taddr + c * NCOL, raw);
-          else tmem_ld_32x32b_x16(taddr + c * NCOL, raw);
-          tmem_ld_wait();
-          float v[NCOL];
+        uint32_t raw[NCOL];
+        if constexpr (NCOL == 32) tmem_ld_32x32b_x32(taddr + c * NCOL, raw);
+        else tmem_ld_32x32b_x16(taddr + c * NCOL, raw);
+        tmem_ld_wait();
+        float v[NCOL];
 #pragma unroll
-          for (int jj = 0; jj < NCOL; ++jj) v[jj] = __uint_as_float(raw[jj]);
-          add_bias<NCOL, HaloParams>(p, v, c * NCOL);
-          if (ri.valid) epilogue_conv<NCOL, HaloParams>(p, v, c * NCOL, ri);
-        }
+        for (int jj = 0; jj < NCOL; ++jj) v[jj] = __uint_as_float(raw[jj]);
+        add_bias<NCOL, HaloParams>(p, v, c * NCOL);
+        if (ri.valid) epilogue_conv<NCOL, HaloParams>(p, v, c * NCOL, ri);
       }
       tc_fence_before();
       __syncwarp();
@@ -238,7 +246,7 @@ static int launch_halo(HaloParams& p, int smem_bytes, cudaStream_t stream) {
     cudaFuncAttributes fa;
     MDE_CHECK_CUDA(cudaFuncGetAttributes(&fa, conv_halo_kernel<BLOCK_N, ROWB>));
     const int per_thread = (fa.numRegs + 7) & ~7;
-    regs_limit = std::max(1, 65536 / (per_thread * kHaloThreads));
+    regs_limit = std::max(1, 65536 / (per_thread * halo_threads(BLOCK_N)));
   }
   int tmem_cols = 32;
   while (tmem_cols < 2 * p.nblk * BLOCK_N) tmem_cols <<= 1;
@@ -246,7 +254,7 @@ static int launch_halo(HaloParams& p, int smem_bytes, cudaStream_t stream) {
   occ = std::max(1, std::min(occ, 512 / tmem_cols));
   int grid = sm_count() * occ;
   if (grid > p.total_tiles) grid = p.total_tiles;
-  launch_k(conv_halo_kernel<BLOCK_N, ROWB>, dim3(grid), dim3(kHaloThreads), smem_bytes, stream, p);
+  launch_k(conv_halo_kernel<BLOCK_N, ROWB>, dim3(grid), dim3(halo_threads(BLOCK_N)), smem_bytes, stream, p);
   MDE_CHECK_LAUNCH();
   return MDE_OK;
 }

@@ -16,6 +16,13 @@ struct RowInfo {
   int b, y, x;  // conv pixel
 };
 
+#ifdef MDE_STORE_EXPERIMENT  // tools/build_variant.sh only: what would fully coalesced stores of the same bytes cost?
+template <class P>
+__device__ __forceinline__ auto dbg_of(const P& p, int) -> decltype(p.dbg) { return p.dbg; }
+template <class P>
+__device__ __forceinline__ int dbg_of(const P&, long) { return 0; }
+#endif
+
 // conv epilogue proper (after the bias add): activation, then a bf16/fp16 padded-NHWC store with the reflected border copies
 // the pixel owns, or an fp32 NHWC head.  conv_halo.cu calls it directly (no GEMM cases in its instruction stream).
 template <int NCOL, class P>
@@ -50,6 +57,17 @@ __device__ __forceinline__ void epilogue_conv(const P& p, float (&v)[NCOL], int 
   bf16* px = reinterpret_cast<bf16*>(p.out) + p.out_coff + n0 + (((size_t)ri.b * (p.h + 2) + ri.y + 1) * W2 + ri.x + 1) * p.out_cstride;
   auto store_at = [&](int dpix) {  // this pixel's channels, dpix padded pixels away
     uint4* dst = reinterpret_cast<uint4*>(px + (ptrdiff_t)dpix * p.out_cstride);
+#ifdef MDE_STORE_EXPERIMENT
+    if (dbg_of(p, 0) & 64) {  // WRONG RESULTS, timing only: the warp's stores land on one contiguous KB per instruction
+      const unsigned long long b0 = __shfl_sync(__activemask(), (unsigned long long)dst, __ffs(__activemask()) - 1);
+      uint4* d2 = reinterpret_cast<uint4*>(b0) + (threadIdx.x & 31) * 2;
+#pragma unroll
+      for (int j = 0; j < NCOL / 16; ++j)
+        st_global_v8(d2 + 64 * j, make_uint4(pk[8 * j], pk[8 * j + 1], pk[8 * j + 2], pk[8 * j + 3]),
+                     make_uint4(pk[8 * j + 4], pk[8 * j + 5], pk[8 * j + 6], pk[8 * j + 7]));
+      return;
+    }
+#endif
     if (p.st32) {  // 32-byte stores (host checked alignment and cout % 16 == 0)
 #pragma unroll
       for (int j = 0; j < NCOL / 16; ++j)
