@@ -300,7 +300,17 @@ static int gemm_impl(const mde_bf16* A, int lda, const mde_bf16* W, int ldw, int
 
   TcParams p;
   memset(&p, 0, sizeof(p));
-  const int block_n = (N % 256 == 0) ? 256 : 128;
+  // Tile width: 256 (or 128) columns when that already gives every SM a tile; otherwise halve it down to 64 — at batch 4 the
+  // N = 768 layers were 21 CTAs of 128 x 256 on 148 SMs, 31 us per launch and 44 % of the forward (profiles/r02e_launch_summary_b4.txt).
+  // A is re-read once per column tile, from L2.  MDE_GEMM_BLOCK_N overrides (A/B timing).
+  int block_n = (N % 256 == 0) ? 256 : 128;
+  static const int bn_env = getenv("MDE_GEMM_BLOCK_N") ? atoi(getenv("MDE_GEMM_BLOCK_N")) : 0;
+  if (bn_env > 0 && N % bn_env == 0) {
+    block_n = bn_env;
+  } else {
+    const int want = (sm_count() * 4) / 5;
+    while (block_n > 64 && N % (block_n / 2) == 0 && ceil_div(M, kBlockM) * (N / block_n) < want) block_n /= 2;
+  }
   {
     const uint64_t dims[2] = {(uint64_t)K, (uint64_t)M};
     const uint64_t strides[1] = {(uint64_t)lda * 2};
