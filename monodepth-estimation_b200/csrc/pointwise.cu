@@ -525,6 +525,99 @@ __global__ void __launch_bounds__(256) upsample_concat_kernel(const bf16* __rest
   }
 }
 
+// Faster form for channel counts whose 8-channel groups are a power of two (every decoder level: 16 / 64 / 128 / 256 channels).
+// A block owns R padded output rows of one image.  Phase 1 blends the two source rows of each output row VERTICALLY into shared
+// memory as fp32 (both sources, at source width: 7.7 KB + <= 7.7 KB per row at every level), phase 2 produces each 8-channel
+// output group from two shared-memory pixels with one lerp: the horizontal index arithmetic is done once per thread and reused
+// for the R rows, and the four 16-byte global loads + 32 conversions per output group of the row-per-block kernel become four
+// shared-memory reads.  (r02 ablation: the four launches cost 77 us of the 2.17 ms step for 35 us of traffic.)
+template <int R>
+__global__ void __launch_bounds__(256) upsample_concat_rows_kernel(const bf16* __restrict__ a, int B, int h, int w, int ca, const bf16* __restrict__ s,
+                                                                   int hs, int ws, int cs, bf16* __restrict__ out, int lg_groups) {
+  pdl_launch_dependents();
+  extern __shared__ float4 ucr_smem[];
+  const int Ho = 2 * h, Wo = 2 * w, ct = ca + cs, groups = 1 << lg_groups, ga = ca >> 3;
+  const int rows_total = Ho + 2, bpi = (rows_total + R - 1) / R;
+  const int b = blockIdx.x / bpi, Y0 = (blockIdx.x - b * bpi) * R;
+  const int nrows = min(R, rows_total - Y0);
+  const int na8 = (w * ca) >> 3, ns8 = (ws * cs) >> 3, row_f4 = 2 * (na8 + ns8);
+  const float sya = (float)(h - 1) / (float)(Ho - 1), sys = cs ? (float)(hs - 1) / (float)(Ho - 1) : 0.0f;
+  pdl_grid_wait();
+  // per-row source rows and weights first (R is a compile-time constant: these live in registers), then ONE pass over the source
+  // elements with the R rows innermost, so a thread has 2R independent 16-byte loads in flight instead of two
+  const uint4 *a0[R], *a1[R], *s0[R], *s1[R];
+  float lya[R], lys[R];
+#pragma unroll
+  for (int r = 0; r < R; ++r) {
+    const int oy = reflect_idx(min(Y0 + r, rows_total - 1) - 1, Ho);
+    int y0, y1;
+    src_index_act(sya, oy, h, y0, y1, lya[r]);
+    // interior of a padded source row is contiguous: element x * C + c sits at (x + 1) * C + c of the row
+    a0[r] = reinterpret_cast<const uint4*>(a + (((size_t)b * (h + 2) + y0 + 1) * (w + 2) + 1) * ca);
+    a1[r] = reinterpret_cast<const uint4*>(a + (((size_t)b * (h + 2) + y1 + 1) * (w + 2) + 1) * ca);
+    s0[r] = s1[r] = nullptr;
+    lys[r] = 0.0f;
+    if (cs) {
+      src_index_act(sys, oy, hs, y0, y1, lys[r]);
+      s0[r] = reinterpret_cast<const uint4*>(s + (((size_t)b * (hs + 2) + y0 + 1) * (ws + 2) + 1) * cs);
+      s1[r] = reinterpret_cast<const uint4*>(s + (((size_t)b * (hs + 2) + y1 + 1) * (ws + 2) + 1) * cs);
+    }
+  }
+  for (int i = threadIdx.x; i < na8 + ns8; i += 256) {
+    const bool isa = i < na8;
+    const int k = isa ? i : i - na8;
+    uint4 u0[R], u1[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      u0[r] = __ldg((isa ? a0[r] : s0[r]) + k);
+      u1[r] = __ldg((isa ? a1[r] : s1[r]) + k);
+    }
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      const float ly = isa ? lya[r] : lys[r];
+      float f0[8], f1[8];
+      bf16x8_to_float(u0[r], f0);
+      bf16x8_to_float(u1[r], f1);
+#pragma unroll
+      for (int c = 0; c < 8; ++c) f0[c] = (1.0f - ly) * f0[c] + ly * f1[c];
+      float4* dst = ucr_smem + (size_t)r * row_f4;
+      dst[2 * i] = make_float4(f0[0], f0[1], f0[2], f0[3]);
+      dst[2 * i + 1] = make_float4(f0[4], f0[5], f0[6], f0[7]);
+    }
+  }
+  __syncthreads();
+  const float sxa = (float)(w - 1) / (float)(Wo - 1), sxs = cs ? (float)(ws - 1) / (float)(Wo - 1) : 0.0f;
+  const int items = (Wo + 2) << lg_groups;
+  bf16* orow0 = out + ((size_t)b * rows_total + Y0) * (Wo + 2) * ct;
+  const size_t row_elems = (size_t)(Wo + 2) * ct;
+  for (int i = threadIdx.x; i < items; i += 256) {
+    const int Xp = i >> lg_groups, grp = i & (groups - 1);
+    const int ox = reflect_idx(Xp - 1, Wo);
+    int x0, x1, i0, i1;
+    float lx;
+    if (grp < ga) {
+      src_index_act(sxa, ox, w, x0, x1, lx);
+      i0 = (x0 * ca + (grp << 3)) >> 2;
+      i1 = (x1 * ca + (grp << 3)) >> 2;
+    } else {
+      src_index_act(sxs, ox, ws, x0, x1, lx);
+      i0 = 2 * na8 + ((x0 * cs + ((grp - ga) << 3)) >> 2);
+      i1 = 2 * na8 + ((x1 * cs + ((grp - ga) << 3)) >> 2);
+    }
+    const float l0 = 1.0f - lx;
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      if (r < nrows) {
+        const float4* row = ucr_smem + (size_t)r * row_f4;
+        const float4 p0 = row[i0], p1 = row[i0 + 1], q0 = row[i1], q1 = row[i1 + 1];
+        *reinterpret_cast<uint4*>(orow0 + r * row_elems + (size_t)i * 8) =
+            make_uint4(pack_bf16x2(l0 * p0.x + lx * q0.x, l0 * p0.y + lx * q0.y), pack_bf16x2(l0 * p0.z + lx * q0.z, l0 * p0.w + lx * q0.w),
+                       pack_bf16x2(l0 * p1.x + lx * q1.x, l0 * p1.y + lx * q1.y), pack_bf16x2(l0 * p1.z + lx * q1.z, l0 * p1.w + lx * q1.w));
+      }
+    }
+  }
+}
+
 // ------------------------------------------------------------------ rgb -> grid channels of a padded NHWC buffer (enhanced_model.py:95-98)
 __global__ void __launch_bounds__(256) rgb_to_grid_kernel(const float* __restrict__ x, int B, int H, int W, int gh, int gw, bf16* __restrict__ out,
                                                           int cstride, int coff, int cfill) {
@@ -635,18 +728,23 @@ __global__ void __launch_bounds__(256) resize_maps_kernel(const __grid_constant_
 // The four consecutive pixels of a thread then fall into at most two adjacent source intervals, so each pixel is
 // wa*s[i] + wb*s[i+1] + wc*s[i+2] with per-thread constant weights (one of wa, wc is zero): 3 shared-memory reads and 12
 // FP instructions per 16-byte store, rows fully unrolled so every address is base + immediate.
+#ifndef MDE_UP3_ROWS
+#define MDE_UP3_ROWS 16
+#endif
+constexpr int kUp3Rows = MDE_UP3_ROWS;  // output rows per block (r02, 32 images x 4 maps at 1024 px: 4 rows 120 us, 8 rows 101, 16 rows 92.5, 32 rows 103)
+constexpr int kUp3MaxSrcW = 344;        // 3 * ws < W: covers outputs up to 1032 px wide (wider ones take the generic kernel)
 __global__ void __launch_bounds__(256) resize_maps_up3_kernel(const __grid_constant__ MapTable tab, int B, int H, int W, float min_disp, float disp_range) {
   pdl_launch_dependents();
   pdl_grid_wait();
-  __shared__ float srow[kRowsPerBlock][kMaxSrcW + 2];
+  __shared__ float srow[kUp3Rows][kUp3MaxSrcW + 2];
   const int mi = blockIdx.z / B, b = blockIdx.z - mi * B;
   const mde_map_desc& d = tab.m[mi];
   const int ws = d.ws, hs = d.hs;
   const float sh = (float)hs / (float)H;
   const float mul = d.mul;
   const float* src = d.src + (size_t)b * hs * ws;
-  const int Y0 = blockIdx.y * kRowsPerBlock;
-  const int nrows = min(kRowsPerBlock, H - Y0);
+  const int Y0 = blockIdx.y * kUp3Rows;
+  const int nrows = min(kUp3Rows, H - Y0);
   for (int r = 0; r < nrows; ++r) {
     int y0, y1;
     float ly;
@@ -683,9 +781,9 @@ __global__ void __launch_bounds__(256) resize_maps_up3_kernel(const __grid_const
   float* d2 = d.dst_disp2 ? d.dst_disp2 + off0 : nullptr;
   float* dz = d.dst_depth ? d.dst_depth + off0 : nullptr;
 #pragma unroll
-  for (int r = 0; r < kRowsPerBlock; ++r) {
+  for (int r = 0; r < kUp3Rows; ++r) {
     if (r < nrows) {
-      const float a = sp[r * (kMaxSrcW + 2)], bb = sp[r * (kMaxSrcW + 2) + 1], c = sp[r * (kMaxSrcW + 2) + 2];
+      const float a = sp[r * (kUp3MaxSrcW + 2)], bb = sp[r * (kUp3MaxSrcW + 2) + 1], c = sp[r * (kUp3MaxSrcW + 2) + 2];
       float o[4];
 #pragma unroll
       for (int j = 0; j < 4; ++j) o[j] = fmaf(wc[j], c, fmaf(wb[j], bb, wa[j] * a));
@@ -843,6 +941,34 @@ extern "C" int mde_upsample2x_concat_nhwc(const mde_bf16* a, int B, int h, int w
   MDE_CHECK_ARG((s == nullptr) == (cs == 0) && cs % 8 == 0, "mde_upsample2x_concat_nhwc: skip tensor / cs mismatch");
   if (s) MDE_CHECK_ARG(hs >= 2 && ws >= 2, "mde_upsample2x_concat_nhwc: bad skip size");
   MDE_CHECK_ARG((long long)B * (2 * h + 2) < (1ll << 31), "mde_upsample2x_concat_nhwc: too many rows");
+  {
+    const int groups = (ca + cs) >> 3;
+    static const bool rows_off = getenv("MDE_UPCAT_ROWS") != nullptr && getenv("MDE_UPCAT_ROWS")[0] == '0';
+    // rows per block: as many as still leave ~4 blocks per SM (the low-resolution levels have few rows: 960 at 28 x 30 x 32 images)
+    int R = 4;
+    while (R > 1 && (long long)B * ceil_div(2 * h + 2, R) < 4ll * sm_count()) R >>= 1;
+    const size_t smem = (size_t)R * ((size_t)w * ca + (size_t)ws * cs) * sizeof(float);
+    if (!rows_off && groups > 0 && (groups & (groups - 1)) == 0 && smem <= 100 * 1024) {
+      static bool attr = false;
+      if (!attr) {
+        MDE_CHECK_CUDA(cudaFuncSetAttribute(upsample_concat_rows_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+        MDE_CHECK_CUDA(cudaFuncSetAttribute(upsample_concat_rows_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+        MDE_CHECK_CUDA(cudaFuncSetAttribute(upsample_concat_rows_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+        attr = true;
+      }
+      int lg = 0;
+      while ((1 << lg) < groups) ++lg;
+      const dim3 grid(B * ceil_div(2 * h + 2, R));
+#define MDE_UPCAT_CASE(RR)                                                                                                                        \
+  if (R == RR)                                                                                                                                    \
+    launch_k(upsample_concat_rows_kernel<RR>, grid, dim3(256), smem, stream, reinterpret_cast<const bf16*>(a), B, h, w, ca, reinterpret_cast<const bf16*>(s), \
+             hs, ws, cs, reinterpret_cast<bf16*>(out), lg);
+      MDE_UPCAT_CASE(4) MDE_UPCAT_CASE(2) MDE_UPCAT_CASE(1)
+#undef MDE_UPCAT_CASE
+      MDE_CHECK_LAUNCH();
+      return MDE_OK;
+    }
+  }
   launch_k(upsample_concat_kernel, dim3(B * (2 * h + 2)), dim3(256), 0, stream, reinterpret_cast<const bf16*>(a), B, h, w, ca, reinterpret_cast<const bf16*>(s),
                                                                    hs, ws, cs, reinterpret_cast<bf16*>(out));
   MDE_CHECK_LAUNCH();
@@ -874,9 +1000,9 @@ extern "C" int mde_resize_maps(const mde_map_desc* maps, int n_maps, int B, int 
   const float range = max_disp - min_disp;
   MDE_CHECK_ARG(H <= 65535 && (long long)n_maps * B <= 65535, "mde_resize_maps: H and n_maps*B must be <= 65535");
   bool up3 = vec;
-  for (int i = 0; i < n_maps; ++i) up3 = up3 && 3 * maps[i].ws < W;
+  for (int i = 0; i < n_maps; ++i) up3 = up3 && 3 * maps[i].ws < W && maps[i].ws <= kUp3MaxSrcW;
   if (up3) {
-    launch_k(resize_maps_up3_kernel, dim3(ceil_div(W / 4, 256), ceil_div(H, kRowsPerBlock), n_maps * B), dim3(256), 0, stream, tab, B, H, W, min_disp, range);
+    launch_k(resize_maps_up3_kernel, dim3(ceil_div(W / 4, 256), ceil_div(H, kUp3Rows), n_maps * B), dim3(256), 0, stream, tab, B, H, W, min_disp, range);
   } else if (vec) {
     launch_k(resize_maps_kernel<true>, dim3(ceil_div(W / 4, 256), ceil_div(H, kRowsPerBlock), n_maps * B), dim3(256), 0, stream, tab, B, H, W, min_disp, range);
   } else {

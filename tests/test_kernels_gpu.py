@@ -379,7 +379,8 @@ def test_conv_folded_batchnorm_and_channel_offset():
     assert float(got[:, :64].abs().max()) == 0.0 and float(got[:, 192:].abs().max()) == 0.0
 
 
-@pytest.mark.parametrize("B,h,w,ca,cs", [(2, 14, 15, 128, 128), (1, 28, 30, 64, 64), (1, 112, 120, 16, 0), (1, 14, 14, 32, 32)])
+@pytest.mark.parametrize("B,h,w,ca,cs", [(2, 14, 15, 128, 128), (1, 28, 30, 64, 64), (1, 112, 120, 16, 0), (1, 14, 14, 32, 32), (3, 56, 60, 32, 32),
+                                           (1, 14, 15, 16, 8)])  # the last one (3 channel groups) takes the row-per-block kernel
 def test_upsample_concat(B, h, w, ca, cs):
     _, ops = _mods()
     a = _rand(B, ca, h, w, seed=70)

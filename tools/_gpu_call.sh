@@ -1,5 +1,6 @@
 cd $GRAFT_REPO_ROOT
-for b in 6 8 12 16; do
-timeout 300 python bench.py --batch $b --no-extras --steps 50 --warmup 5 2>> gpurun_out/c37_err.txt | python -c "import json,sys; d=json.loads(sys.stdin.read()); print('batch $b pair', d['value'], d['ms_per_step'])"
-MDE_GEMM_1CTA=1 timeout 300 python bench.py --batch $b --no-extras --steps 50 --warmup 5 2>> gpurun_out/c37_err.txt | python -c "import json,sys; d=json.loads(sys.stdin.read()); print('batch $b 1cta', d['value'], d['ms_per_step'])"
+timeout 900 python -m pytest tests/test_kernels_gpu.py tests/test_forward_gpu.py tests/test_parity_bench_gpu.py -x -q -m gpu 2>&1 | tail -3
+for i in 1 2; do
+timeout 300 python bench.py --no-extras --steps 30 --warmup 5 2>> gpurun_out/c42_err.txt | python -c "import json,sys; d=json.loads(sys.stdin.read()); print('new', d['value'], d['ms_per_step'])"
+MDE_UPCAT_ROWS=0 timeout 300 python bench.py --no-extras --steps 30 --warmup 5 2>> gpurun_out/c42_err.txt | python -c "import json,sys; d=json.loads(sys.stdin.read()); print('old upcat', d['value'], d['ms_per_step'])"
 done
