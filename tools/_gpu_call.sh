@@ -1,6 +1,6 @@
 cd $GRAFT_REPO_ROOT
-timeout 900 python -m pytest tests/test_kernels_gpu.py tests/test_forward_gpu.py tests/test_parity_bench_gpu.py -x -q -m gpu 2>&1 | tail -3
+timeout 300 python -m pytest tests/test_kernels_gpu.py -x -q -m gpu -k "attention" 2>&1 | tail -2
 for i in 1 2; do
-timeout 300 python bench.py --no-extras --steps 30 --warmup 5 2>> gpurun_out/c42_err.txt | python -c "import json,sys; d=json.loads(sys.stdin.read()); print('new', d['value'], d['ms_per_step'])"
-MDE_UPCAT_ROWS=0 timeout 300 python bench.py --no-extras --steps 30 --warmup 5 2>> gpurun_out/c42_err.txt | python -c "import json,sys; d=json.loads(sys.stdin.read()); print('old upcat', d['value'], d['ms_per_step'])"
+timeout 300 python bench.py --no-extras --steps 30 --warmup 5 2>> gpurun_out/c43_err.txt | python -c "import json,sys; d=json.loads(sys.stdin.read()); print('f16 exp', d['value'], d['ms_per_step'])"
+MDE_LIB_PATH=tools/_libmde_expf32.so timeout 300 python bench.py --no-extras --steps 30 --warmup 5 2>> gpurun_out/c43_err.txt | python -c "import json,sys; d=json.loads(sys.stdin.read()); print('f32 exp', d['value'], d['ms_per_step'])"
 done
