@@ -387,7 +387,10 @@ def bench_forward(a, env):
     line["e2e"] = {"value": round(world * B * a.steps / te, 1), "unit": "images/s", "h2d_bytes_per_step": x_u8.numel(), "d2h_bytes_per_step": B * S * S * 2,
                    "ms_per_step": round(te / a.steps * 1e3, 4),
                    "how": f"mde.BatchPipeline: uint8 [B,H,W,3] pinned host batches in (the decoder's output, run_mars_depth.py:94-100), {out_key} read back "
-                          "as fp16 into pinned host memory; H2D(i+1), forward(i), D2H(i-1) overlap on three streams"}
+                          "as fp16 into pinned host memory; H2D(i+1), forward(i), D2H(i-1) overlap on three streams.  The pipeline calls "
+                          "model.forward_keys: the uint8 image goes straight into the input kernel (pixel = float(u8)/255 there, bit-identical "
+                          "to converting first), the whole encoder + decoder runs as in `value`, and only the requested map is resized to full "
+                          "resolution, written as fp16 by the output kernel (config 4: the composed callable takes the fp32 image and returns every map)"}
     tf = timed_pipeline(x_host, torch.float32)
     line["e2e_f32"] = {"value": round(world * B * a.steps / tf, 1), "unit": "images/s", "h2d_bytes_per_step": x_host.numel() * 4,
                        "d2h_bytes_per_step": B * S * S * 4, "ms_per_step": round(tf / a.steps * 1e3, 4),

@@ -112,6 +112,13 @@ int mde_preprocess_patchify(const float* x, int B, int H, int W, const float* af
 int mde_input_stage(const float* x, int B, int H, int W, const float* bn4x3, float eps, float* scratch, float* affine6,
                     float* raw224, mde_bf16* patches, mde_stream_t stream);
 
+/* mde_input_stage fed with the image decoder's output: x_hwc uint8 [B][H][W][3] (run_mars_depth.py:94-100, np.array(PIL image)).
+ * A pixel is float(u8) / 255 (the caller-side expression of :100-103, same IEEE division), so affine6, raw224 and patches are
+ * bit-identical to mde_u8hwc_to_f32chw followed by mde_input_stage, while the image is read once at 3 bytes per pixel and no
+ * fp32 copy of it is ever written.  W % 4 == 0, x_hwc 4-byte aligned. */
+int mde_input_stage_u8(const uint8_t* x_hwc, int B, int H, int W, const float* bn4x3, float eps, float* scratch, float* affine6,
+                       float* raw224, mde_bf16* patches, mde_stream_t stream);
+
 /* mde_input_stage for callers that cannot allocate (CUDA-graph capture, serving loops, harnesses that forbid cudaMalloc).  No
  * counterpart in the reference.  Same kernels, same outputs (bit for bit) as
  * mde_input_stage, but the partial-record scratch is a device array built into the library (126 KB per GPU that loads it, held until
@@ -222,6 +229,9 @@ int mde_decoder_tail16(const mde_bf16* src_padded, int B, int h, int w, const md
  * are multiples of 8 channels (16-byte stores). */
 int mde_rgb_to_grid_nhwc(const float* x, int B, int H, int W, int gh, int gw, mde_bf16* out_padded, int out_cstride,
                          int out_coff, int cfill, mde_stream_t stream);
+/* The same from the 8-bit HWC image (pixel = float(u8) / 255, bit-identical to the fp32 form after mde_u8hwc_to_f32chw). */
+int mde_rgb_to_grid_nhwc_u8(const uint8_t* x_hwc, int B, int H, int W, int gh, int gw, mde_bf16* out_padded, int out_cstride,
+                            int out_coff, int cfill, mde_stream_t stream);
 
 /* ---- output stage: model.py:89-100, enhanced_model.py:266-277, layers.py:16-25 ----------
  * For each of n_maps low-resolution fp32 maps [B][hs][ws]: multiply by `mul`, resize to
@@ -234,6 +244,8 @@ typedef struct mde_map_desc {
   float* dst_disp;  /* may be NULL */
   float* dst_disp2; /* optional second copy (("disp_fused",0) aliases ("disp",0)), may be NULL */
   float* dst_depth; /* may be NULL */
+  mde_f16* dst_half; /* optional IEEE fp16 copy of the resized disparity (round to nearest, saturating), may be NULL: what
+                        BatchPipeline(out_dtype=float16) sends over the host link — no reference counterpart */
 } mde_map_desc;
 #define MDE_MAX_MAPS 8
 int mde_resize_maps(const mde_map_desc* maps, int n_maps, int B, int H, int W, float min_disp, float max_disp,

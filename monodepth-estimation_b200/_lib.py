@@ -34,7 +34,7 @@ class WorkspaceCfg(C.Structure):
 
 
 class MapDesc(C.Structure):
-    _fields_ = [("src", _p), ("hs", _i), ("ws", _i), ("mul", _f), ("dst_disp", _p), ("dst_disp2", _p), ("dst_depth", _p)]
+    _fields_ = [("src", _p), ("hs", _i), ("ws", _i), ("mul", _f), ("dst_disp", _p), ("dst_disp2", _p), ("dst_depth", _p), ("dst_half", _p)]
 
 
 # name -> argtypes (every function returns int status unless listed in _RESTYPES)
@@ -50,6 +50,7 @@ SIGNATURES = {
     "mde_workspace_bytes": [_p],
     "mde_preprocess_patchify": [_p, _i, _i, _i, _p, _p, _p],
     "mde_input_stage": [_p, _i, _i, _i, _p, _f, _p, _p, _p, _p, _p],
+    "mde_input_stage_u8": [_p, _i, _i, _i, _p, _f, _p, _p, _p, _p, _p],
     "mde_input_stage_noalloc": [_p, _i, _i, _i, _p, _f, _p, _p, _p, _p],
     "mde_gemm_bf16": [_p, _i, _p, _i, _i, _i, _i, _i, _p, _p, _i, _p, _p, _p],
     "mde_debug_gemm_prof": [_p],
@@ -63,6 +64,7 @@ SIGNATURES = {
     "mde_upsample2x_concat_nhwc": [_p, _i, _i, _i, _i, _p, _i, _i, _i, _p, _p],
     "mde_decoder_tail16": [_p, _i, _i, _i, _p, _p, _p, _p, _p, _p, _p, _p],
     "mde_rgb_to_grid_nhwc": [_p, _i, _i, _i, _i, _i, _p, _i, _i, _i, _p],
+    "mde_rgb_to_grid_nhwc_u8": [_p, _i, _i, _i, _i, _i, _p, _i, _i, _i, _p],
     "mde_resize_maps": [C.POINTER(MapDesc), _i, _i, _i, _i, _f, _f, _p],
     "mde_spatial_attention": [_p, _p, _i, _i, _i, _p, _p, _p],
     "mde_enh_fuse": [_p, _p, _p, _p, _i, _i, _i, _i, _i, _f, _p, _p, _p],

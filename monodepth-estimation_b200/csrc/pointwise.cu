@@ -618,8 +618,93 @@ __global__ void __launch_bounds__(256) upsample_concat_rows_kernel(const bf16* _
   }
 }
 
+// The same stage fed with the decoder's 8-bit HWC image (run_mars_depth.py:94-103: np.array(PIL) -> float()/255 -> permute): min/max
+// are taken on the packed bytes (monotonic under the division, so float(min)/255 is the min of the floats), the resampled 224 px
+// raster is computed from float(u8)/255 with the SAME IEEE division and the same expression as the fp32 kernel, i.e. the outputs
+// are bit-identical to mde_u8hwc_to_f32chw + mde_input_stage while reading 3 bytes per pixel instead of writing 12 and reading 12.
+// A block owns `rpb` output rows of ALL THREE channels of one image.
+__global__ void __launch_bounds__(256) input_scan_resample_u8_kernel(const uint8_t* __restrict__ x, int H, int W, int rpb, int groups,
+                                                                     float* __restrict__ partials, float* __restrict__ raw224) {
+  pdl_launch_dependents();
+  pdl_grid_wait();
+  const int grp = blockIdx.x % groups, b = blockIdx.x / groups;
+  const int oy0 = grp * rpb, oy1 = min(224, oy0 + rpb);
+  const float sh = (float)H / 224.0f, sw = (float)W / 224.0f;
+  const uint8_t* img = x + (size_t)b * H * W * 3;
+  const int lo = scan_row_start(sh, oy0, H), hi = scan_row_start(sh, oy1, H);
+  // bytes of 4 pixels: r0 g0 b0 r1 | g1 b1 r2 g2 | b2 r3 g3 b3 — one packed min and max per word position
+  uint32_t mn0 = 0xffffffffu, mn1 = 0xffffffffu, mn2 = 0xffffffffu, mx0 = 0, mx1 = 0, mx2 = 0;
+  {
+    const uint32_t* p = reinterpret_cast<const uint32_t*>(img + (size_t)lo * W * 3);  // host checked W % 4 == 0 and 4-byte alignment
+    const int n = (hi - lo) * (W >> 2);                                               // groups of 4 pixels = 3 words
+    for (int i0 = threadIdx.x; i0 < n; i0 += 4 * 256) {
+      uint32_t w[4][3];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int i = min(i0 + u * 256, n - 1);  // past the end: re-read the last group (neutral)
+        w[u][0] = __ldg(p + 3 * i);
+        w[u][1] = __ldg(p + 3 * i + 1);
+        w[u][2] = __ldg(p + 3 * i + 2);
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        mn0 = __vminu4(mn0, w[u][0]); mx0 = __vmaxu4(mx0, w[u][0]);
+        mn1 = __vminu4(mn1, w[u][1]); mx1 = __vmaxu4(mx1, w[u][1]);
+        mn2 = __vminu4(mn2, w[u][2]); mx2 = __vmaxu4(mx2, w[u][2]);
+      }
+    }
+  }
+  auto byte_of = [](uint32_t v, int k) { return (v >> (8 * k)) & 255u; };
+  uint32_t cmn[3], cmx[3];
+  cmn[0] = min(min(byte_of(mn0, 0), byte_of(mn0, 3)), min(byte_of(mn1, 2), byte_of(mn2, 1)));
+  cmn[1] = min(min(byte_of(mn0, 1), byte_of(mn1, 0)), min(byte_of(mn1, 3), byte_of(mn2, 2)));
+  cmn[2] = min(min(byte_of(mn0, 2), byte_of(mn1, 1)), min(byte_of(mn2, 0), byte_of(mn2, 3)));
+  cmx[0] = max(max(byte_of(mx0, 0), byte_of(mx0, 3)), max(byte_of(mx1, 2), byte_of(mx2, 1)));
+  cmx[1] = max(max(byte_of(mx0, 1), byte_of(mx1, 0)), max(byte_of(mx1, 3), byte_of(mx2, 2)));
+  cmx[2] = max(max(byte_of(mx0, 2), byte_of(mx1, 1)), max(byte_of(mx2, 0), byte_of(mx2, 3)));
+  __shared__ uint32_t red[8][6];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+#pragma unroll
+  for (int c = 0; c < 3; ++c) {
+    cmn[c] = __reduce_min_sync(0xffffffffu, cmn[c]);
+    cmx[c] = __reduce_max_sync(0xffffffffu, cmx[c]);
+  }
+  if (lane == 0) {
+#pragma unroll
+    for (int c = 0; c < 3; ++c) red[warp][c] = cmn[c], red[warp][3 + c] = cmx[c];
+  }
+  __syncthreads();
+  if (threadIdx.x < 6) {
+    const int k = threadIdx.x;
+    uint32_t r = red[0][k];
+    for (int w = 1; w < 8; ++w) r = k < 3 ? min(r, red[w][k]) : max(r, red[w][k]);
+    partials[(size_t)blockIdx.x * 6 + k] = __fdiv_rn((float)r, 255.0f);
+  }
+  // resample this block's output rows (torch bilinear, align_corners=False) from float(u8) / 255
+  const int ox = threadIdx.x;
+  if (ox >= 224) return;
+  int x0, x1;
+  float lx;
+  src_index_acf(sw, ox, W, x0, x1, lx);
+  for (int oy = oy0; oy < oy1; ++oy) {
+    int y0, y1;
+    float ly;
+    src_index_acf(sh, oy, H, y0, y1, ly);
+    const uint8_t* r0 = img + (size_t)y0 * W * 3;
+    const uint8_t* r1 = img + (size_t)y1 * W * 3;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      const float v00 = __fdiv_rn((float)__ldg(r0 + 3 * x0 + c), 255.0f), v01 = __fdiv_rn((float)__ldg(r0 + 3 * x1 + c), 255.0f);
+      const float v10 = __fdiv_rn((float)__ldg(r1 + 3 * x0 + c), 255.0f), v11 = __fdiv_rn((float)__ldg(r1 + 3 * x1 + c), 255.0f);
+      raw224[(((size_t)b * 3 + c) * 224 + oy) * 224 + ox] = (1.0f - ly) * ((1.0f - lx) * v00 + lx * v01) + ly * ((1.0f - lx) * v10 + lx * v11);
+    }
+  }
+}
+
 // ------------------------------------------------------------------ rgb -> grid channels of a padded NHWC buffer (enhanced_model.py:95-98)
-__global__ void __launch_bounds__(256) rgb_to_grid_kernel(const float* __restrict__ x, int B, int H, int W, int gh, int gw, bf16* __restrict__ out,
+// U8 = true: x is the 8-bit HWC image and a pixel is float(u8) / 255 (the caller-side expression, same IEEE division)
+template <bool U8>
+__global__ void __launch_bounds__(256) rgb_to_grid_kernel(const void* __restrict__ xv, int B, int H, int W, int gh, int gw, bf16* __restrict__ out,
                                                           int cstride, int coff, int cfill) {
   pdl_launch_dependents();
   pdl_grid_wait();
@@ -640,9 +725,21 @@ __global__ void __launch_bounds__(256) rgb_to_grid_kernel(const float* __restric
       float v[3];
 #pragma unroll
       for (int c = 0; c < 3; ++c) {
-        const float* p = x + ((size_t)b * 3 + c) * H * W;
-        v[c] = (1.0f - ly) * ((1.0f - lx) * __ldg(p + (size_t)y0 * W + x0) + lx * __ldg(p + (size_t)y0 * W + x1)) +
-               ly * ((1.0f - lx) * __ldg(p + (size_t)y1 * W + x0) + lx * __ldg(p + (size_t)y1 * W + x1));
+        float v00, v01, v10, v11;
+        if constexpr (U8) {
+          const uint8_t* p = reinterpret_cast<const uint8_t*>(xv) + (size_t)b * H * W * 3 + c;
+          v00 = __fdiv_rn((float)__ldg(p + ((size_t)y0 * W + x0) * 3), 255.0f);
+          v01 = __fdiv_rn((float)__ldg(p + ((size_t)y0 * W + x1) * 3), 255.0f);
+          v10 = __fdiv_rn((float)__ldg(p + ((size_t)y1 * W + x0) * 3), 255.0f);
+          v11 = __fdiv_rn((float)__ldg(p + ((size_t)y1 * W + x1) * 3), 255.0f);
+        } else {
+          const float* p = reinterpret_cast<const float*>(xv) + ((size_t)b * 3 + c) * H * W;
+          v00 = __ldg(p + (size_t)y0 * W + x0);
+          v01 = __ldg(p + (size_t)y0 * W + x1);
+          v10 = __ldg(p + (size_t)y1 * W + x0);
+          v11 = __ldg(p + (size_t)y1 * W + x1);
+        }
+        v[c] = (1.0f - ly) * ((1.0f - lx) * v00 + lx * v01) + ly * ((1.0f - lx) * v10 + lx * v11);
       }
       o.x = pack_bf16x2(v[0], v[1]);
       o.y = pack_bf16x2(v[2], 0.0f);
@@ -713,10 +810,12 @@ __global__ void __launch_bounds__(256) resize_maps_kernel(const __grid_constant_
       dep[j] = d.dst_depth ? fast_rcp(fmaf(disp_range, o[j], min_disp)) : 0.0f;
     }
     if constexpr (VEC4) {
+      if (d.dst_half) __stcs(reinterpret_cast<uint2*>(reinterpret_cast<uint16_t*>(d.dst_half) + off), make_uint2(pack_f16x2(o[0], o[1]), pack_f16x2(o[2], o[3])));
       if (d.dst_disp) __stcs(reinterpret_cast<float4*>(d.dst_disp + off), make_float4(o[0], o[1], o[2], o[3]));
       if (d.dst_disp2) __stcs(reinterpret_cast<float4*>(d.dst_disp2 + off), make_float4(o[0], o[1], o[2], o[3]));
       if (d.dst_depth) __stcs(reinterpret_cast<float4*>(d.dst_depth + off), make_float4(dep[0], dep[1], dep[2], dep[3]));
     } else {
+      if (d.dst_half) reinterpret_cast<uint16_t*>(d.dst_half)[off] = static_cast<uint16_t>(pack_f16x2(o[0], 0.0f) & 0xFFFFu);
       if (d.dst_disp) d.dst_disp[off] = o[0];
       if (d.dst_disp2) d.dst_disp2[off] = o[0];
       if (d.dst_depth) d.dst_depth[off] = dep[0];
@@ -780,6 +879,7 @@ __global__ void __launch_bounds__(256) resize_maps_up3_kernel(const __grid_const
   float* dd = d.dst_disp ? d.dst_disp + off0 : nullptr;
   float* d2 = d.dst_disp2 ? d.dst_disp2 + off0 : nullptr;
   float* dz = d.dst_depth ? d.dst_depth + off0 : nullptr;
+  uint16_t* dh = d.dst_half ? reinterpret_cast<uint16_t*>(d.dst_half) + off0 : nullptr;
 #pragma unroll
   for (int r = 0; r < kUp3Rows; ++r) {
     if (r < nrows) {
@@ -787,6 +887,7 @@ __global__ void __launch_bounds__(256) resize_maps_up3_kernel(const __grid_const
       float o[4];
 #pragma unroll
       for (int j = 0; j < 4; ++j) o[j] = fmaf(wc[j], c, fmaf(wb[j], bb, wa[j] * a));
+      if (dh) __stcs(reinterpret_cast<uint2*>(dh + (size_t)r * W), make_uint2(pack_f16x2(o[0], o[1]), pack_f16x2(o[2], o[3])));
       if (dd) __stcs(reinterpret_cast<float4*>(dd + (size_t)r * W), make_float4(o[0], o[1], o[2], o[3]));
       if (d2) __stcs(reinterpret_cast<float4*>(d2 + (size_t)r * W), make_float4(o[0], o[1], o[2], o[3]));
       if (dz)
@@ -980,8 +1081,19 @@ extern "C" int mde_rgb_to_grid_nhwc(const float* x, int B, int H, int W, int gh,
   MDE_CHECK_ARG(x && out_padded && B > 0 && cfill >= 8 && out_coff + cfill <= out_cstride, "mde_rgb_to_grid_nhwc: bad arguments");
   MDE_CHECK_ARG(cfill % 8 == 0 && out_coff % 8 == 0 && out_cstride % 8 == 0 && (uintptr_t)out_padded % 16 == 0,
                 "mde_rgb_to_grid_nhwc: cfill, out_coff and out_cstride must be multiples of 8 channels (16-byte stores)");
-  launch_k(rgb_to_grid_kernel, dim3(grid_for((long long)B * gh * gw * (cfill / 8), 256)), dim3(256), 0, stream, x, B, H, W, gh, gw, reinterpret_cast<bf16*>(out_padded),
-                                                                               out_cstride, out_coff, cfill);
+  launch_k(rgb_to_grid_kernel<false>, dim3(grid_for((long long)B * gh * gw * (cfill / 8), 256)), dim3(256), 0, stream, static_cast<const void*>(x), B, H, W, gh, gw,
+           reinterpret_cast<bf16*>(out_padded), out_cstride, out_coff, cfill);
+  MDE_CHECK_LAUNCH();
+  return MDE_OK;
+}
+
+extern "C" int mde_rgb_to_grid_nhwc_u8(const uint8_t* x_hwc, int B, int H, int W, int gh, int gw, mde_bf16* out_padded, int out_cstride, int out_coff,
+                                       int cfill, mde_stream_t stream) {
+  MDE_CHECK_ARG(x_hwc && out_padded && B > 0 && cfill >= 8 && out_coff + cfill <= out_cstride, "mde_rgb_to_grid_nhwc_u8: bad arguments");
+  MDE_CHECK_ARG(cfill % 8 == 0 && out_coff % 8 == 0 && out_cstride % 8 == 0 && (uintptr_t)out_padded % 16 == 0,
+                "mde_rgb_to_grid_nhwc_u8: cfill, out_coff and out_cstride must be multiples of 8 channels (16-byte stores)");
+  launch_k(rgb_to_grid_kernel<true>, dim3(grid_for((long long)B * gh * gw * (cfill / 8), 256)), dim3(256), 0, stream, static_cast<const void*>(x_hwc), B, H, W, gh, gw,
+           reinterpret_cast<bf16*>(out_padded), out_cstride, out_coff, cfill);
   MDE_CHECK_LAUNCH();
   return MDE_OK;
 }
@@ -995,20 +1107,32 @@ extern "C" int mde_resize_maps(const mde_map_desc* maps, int n_maps, int B, int 
     tab.m[i] = maps[i];
     MDE_CHECK_ARG(maps[i].src && maps[i].hs > 0 && maps[i].ws > 0 && maps[i].ws <= kMaxSrcW, "mde_resize_maps: map %d has no source or is wider than %d", i, kMaxSrcW);
     const uintptr_t al = (uintptr_t)maps[i].dst_disp | (uintptr_t)maps[i].dst_disp2 | (uintptr_t)maps[i].dst_depth;
-    if (al % 16 != 0) vec = false;
+    if (al % 16 != 0 || (uintptr_t)maps[i].dst_half % 8 != 0) vec = false;
   }
   const float range = max_disp - min_disp;
   MDE_CHECK_ARG(H <= 65535 && (long long)n_maps * B <= 65535, "mde_resize_maps: H and n_maps*B must be <= 65535");
-  bool up3 = vec;
-  for (int i = 0; i < n_maps; ++i) up3 = up3 && 3 * maps[i].ws < W && maps[i].ws <= kUp3MaxSrcW;
-  if (up3) {
-    launch_k(resize_maps_up3_kernel, dim3(ceil_div(W / 4, 256), ceil_div(H, kUp3Rows), n_maps * B), dim3(256), 0, stream, tab, B, H, W, min_disp, range);
-  } else if (vec) {
-    launch_k(resize_maps_kernel<true>, dim3(ceil_div(W / 4, 256), ceil_div(H, kRowsPerBlock), n_maps * B), dim3(256), 0, stream, tab, B, H, W, min_disp, range);
-  } else {
+  if (!vec) {
     launch_k(resize_maps_kernel<false>, dim3(ceil_div(W, 256), ceil_div(H, kRowsPerBlock), n_maps * B), dim3(256), 0, stream, tab, B, H, W, min_disp, range);
+    MDE_CHECK_LAUNCH();
+    return MDE_OK;
   }
-  MDE_CHECK_LAUNCH();
+  // The kernel is chosen PER MAP (>= 3x horizontal upscaling takes the 3-tap form), never per call: the two forms round
+  // differently, and a map must come out the same whichever other maps are requested with it (model.forward_keys).
+  MapTable fast, slow;
+  fast.n = slow.n = 0;
+  for (int i = 0; i < n_maps; ++i) {
+    const bool up3 = 3 * maps[i].ws < W && maps[i].ws <= kUp3MaxSrcW;
+    MapTable& t = up3 ? fast : slow;
+    t.m[t.n++] = maps[i];
+  }
+  if (fast.n) {
+    launch_k(resize_maps_up3_kernel, dim3(ceil_div(W / 4, 256), ceil_div(H, kUp3Rows), fast.n * B), dim3(256), 0, stream, fast, B, H, W, min_disp, range);
+    MDE_CHECK_LAUNCH();
+  }
+  if (slow.n) {
+    launch_k(resize_maps_kernel<true>, dim3(ceil_div(W / 4, 256), ceil_div(H, kRowsPerBlock), slow.n * B), dim3(256), 0, stream, slow, B, H, W, min_disp, range);
+    MDE_CHECK_LAUNCH();
+  }
   return MDE_OK;
 }
 
@@ -1068,6 +1192,26 @@ extern "C" int mde_input_stage(const float* x, int B, int H, int W, const float*
   const int groups = ceil_div(224, rpb);
   const int parts = groups * 3 * B;
   launch_k(input_scan_resample_kernel, dim3(parts), dim3(256), 0, stream, x, H, W, rpb, groups, scratch, raw224);
+  MDE_CHECK_LAUNCH();
+  launch_k(range_finalize_kernel, dim3(1), dim3(768), 0, stream, scratch, parts, bn4x3, eps, affine6);
+  MDE_CHECK_LAUNCH();
+  launch_k(patchify224_kernel, dim3(grid_for((long long)B * 196 * 96, 256)), dim3(256), 0, stream, raw224, B, affine6, reinterpret_cast<bf16*>(patches));
+  MDE_CHECK_LAUNCH();
+  return MDE_OK;
+}
+
+extern "C" int mde_input_stage_u8(const uint8_t* x_hwc, int B, int H, int W, const float* bn4x3, float eps, float* scratch, float* affine6,
+                                  float* raw224, mde_bf16* patches, mde_stream_t stream) {
+  MDE_CHECK_ARG(x_hwc && bn4x3 && scratch && affine6 && raw224 && patches, "mde_input_stage_u8: null pointer");
+  MDE_CHECK_ARG(B > 0 && H > 0 && W > 0 && W % 4 == 0 && (uintptr_t)x_hwc % 4 == 0, "mde_input_stage_u8: W must be a multiple of 4 and x 4-byte aligned (H=%d W=%d)", H, W);
+  MDE_CHECK_ARG((uintptr_t)raw224 % 16 == 0 && (uintptr_t)patches % 16 == 0, "mde_input_stage_u8: raw224 / patches must be 16-byte aligned");
+  const int max_parts = MDE_RANGE_SCRATCH_FLOATS / 6;
+  int rpb = ceil_div(224 * B, max_parts);  // output rows per block (all three channels): as few as the partials buffer allows, at least 2
+  if (rpb < 2) rpb = 2;
+  MDE_CHECK_ARG(rpb <= 224, "mde_input_stage_u8: batch %d too large for the partials buffer", B);
+  const int groups = ceil_div(224, rpb);
+  const int parts = groups * B;
+  launch_k(input_scan_resample_u8_kernel, dim3(parts), dim3(256), 0, stream, x_hwc, H, W, rpb, groups, scratch, raw224);
   MDE_CHECK_LAUNCH();
   launch_k(range_finalize_kernel, dim3(1), dim3(768), 0, stream, scratch, parts, bn4x3, eps, affine6);
   MDE_CHECK_LAUNCH();

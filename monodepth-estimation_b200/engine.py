@@ -157,6 +157,11 @@ class DepthEngine:
     # ------------------------------------------------------------------ stages
     def _pre(self, ws, w, x):
         """pad-to-/16 resize (model.py:51-54), range heuristic (encoder.py:129-135), resize->224 + patchify."""
+        if x.dtype == torch.uint8:  # the decoder's [B,H,W,3] image: one pass at 3 bytes per pixel, no fp32 copy (forward() checked H, W % 16 == 0)
+            ops.input_stage_u8(x, w["enc"]["bn4x3"], 1e-5, ws.scratch, ws.affine, ws.raw224, ws.patches)
+            if self.enhanced:
+                ops.rgb_to_grid_u8(x, ws.gh, ws.gw, ws.feats[0], 256, 64)
+            return 3 + self.enhanced
         xin = x
         if ws.xp is not None:
             xin = ops.resize_bilinear_nchw(x, ws.Hp, ws.Wp, out=ws.xp)
@@ -334,43 +339,88 @@ class DepthEngine:
             n += 1
         return n
 
-    def _post(self, ws, scale):
-        """model.py:89-100 / enhanced_model.py:266-277 + layers.py:16-25 — one kernel writes every output map."""
+    def _post(self, ws, scale, keys=None, half=False, out_buffers=None):
+        """model.py:89-100 / enhanced_model.py:266-277 + layers.py:16-25 — one kernel writes every output map.
+
+        ``keys`` (no reference counterpart; the caller-side pipeline's entry): produce only these outputs — the low-resolution maps
+        are all computed, but a full-resolution map nobody reads is 4 MB per image of HBM writes.  ``half``: disparity-type keys are
+        written as IEEE fp16 by the same kernel (round to nearest of the fp32 value, i.e. identical to ``ops.f32_to_f16`` of the
+        fp32 map); ``out_buffers``: {key: preallocated tensor of the right dtype} to write into."""
         B, H0, W0 = ws.B, ws.H0, ws.W0
         dev = ws.scratch.device
-        new = lambda: torch.empty(B, 1, H0, W0, device=dev, dtype=F32)
         mul = 1.0 if scale is None else scale
-        out = {}
         if not self.enhanced:
-            maps = []
-            for i in range(4):
-                out[("disp", i)] = new()
-                maps.append((ws.disp[i], mul, out[("disp", i)], None))
-            ops.resize_maps(maps, B, H0, W0)
-            return out, 1
-        for i in range(4):
-            out[("disp", i)] = new()
-        out[("uncertainty", 0)] = new()
-        out[("disp_unrefined", 0)] = new()
-        # ("disp_fused",0) holds the same values as ("disp",0) (enhanced_model.py:259-263); one buffer, two keys
-        out[("disp_fused", 0)] = out[("disp", 0)]
-        for i in range(4):
-            out[("depth", i)] = new()
-        maps = [(ws.fused, 1.0, out[("disp", 0)], out[("depth", 0)])]
-        maps += [(ws.disp[i], mul, out[("disp", i)], out[("depth", i)]) for i in (1, 2, 3)]
-        maps += [(ws.unc, 1.0, out[("uncertainty", 0)], None), (ws.disp[0], 1.0, out[("disp_unrefined", 0)], None)]
-        ops.resize_maps(maps, B, H0, W0, 1 / 100.0, 1 / 0.1)
-        return out, 1
+            sources = [(ws.disp[i], mul, (("disp", i),), None) for i in range(4)]
+            rng = (0.01, 10.0)
+        else:
+            # ("disp_fused",0) holds the same values as ("disp",0) (enhanced_model.py:259-263); one buffer, two keys
+            sources = [(ws.fused, 1.0, (("disp", 0), ("disp_fused", 0)), ("depth", 0))]
+            sources += [(ws.disp[i], mul, (("disp", i),), ("depth", i)) for i in (1, 2, 3)]
+            sources += [(ws.unc, 1.0, (("uncertainty", 0),), None), (ws.disp[0], 1.0, (("disp_unrefined", 0),), None)]
+            rng = (1 / 100.0, 1 / 0.1)
+        if keys is not None:
+            known = {k for _, _, dk, zk in sources for k in dk + ((zk,) if zk else ())}
+            bad = [k for k in keys if k not in known]
+            if bad:
+                raise KeyError(f"unknown output key(s) {bad}; this model produces {sorted(known)}")
+        bufs = out_buffers or {}
+
+        def new(key, dt):
+            t = bufs.get(key)
+            if t is None:
+                return torch.empty(B, 1, H0, W0, device=dev, dtype=dt)
+            if t.dtype != dt or tuple(t.shape) != (B, 1, H0, W0) or t.device != dev or not t.is_contiguous():
+                raise ValueError(f"out_buffers[{key}] must be a contiguous {dt} tensor [{B},1,{H0},{W0}] on {dev}")
+            return t
+
+        out, maps, to_half = {}, [], []
+        for src, m, disp_keys, depth_key in sources:
+            wd = [k for k in disp_keys if keys is None or k in keys]
+            wz = depth_key is not None and (keys is None or depth_key in keys)
+            if not wd and not wz:
+                continue
+            dd = dh = dz = None
+            if wd:
+                if half:
+                    dh = new(wd[0], F16)
+                else:
+                    dd = new(wd[0], F32)
+                for k in wd:
+                    out[k] = dh if half else dd
+            if wz:
+                dz = new(depth_key, F32) if not half else torch.empty(B, 1, H0, W0, device=dev, dtype=F32)
+                if half:
+                    to_half.append((depth_key, dz))
+                else:
+                    out[depth_key] = dz
+            maps.append((src, m, dd, dz, dh))
+        n = 0
+        for i in range(0, len(maps), L.MAX_MAPS):
+            ops.resize_maps(maps[i:i + L.MAX_MAPS], B, H0, W0, *rng)
+            n += 1
+        for k, dz in to_half:  # depth maps have no fused fp16 form: convert (rare: the pipeline's default keys are disparities)
+            out[k] = ops.f32_to_f16(dz, new(k, F16))
+            n += 1
+        return out, n
 
     # ------------------------------------------------------------------ forward
-    def forward(self, x, scale, want=None):
+    def forward(self, x, scale, want=None, keys=None, half=False, out_buffers=None):
         w = self.weights()
         dev = next(self.module.parameters()).device
         if not x.is_cuda or x.device != dev:
             raise RuntimeError(f"input is on {x.device} but the model is on {dev}")
-        if x.dtype != F32 or not x.is_contiguous():
-            x = x.to(F32).contiguous()
-        B, _, H0, W0 = x.shape
+        if x.dtype == torch.uint8:  # [B,H,W,3] as decoded (run_mars_depth.py:97-100); a pixel is float(u8)/255
+            if x.dim() != 4 or x.shape[-1] != 3:
+                raise ValueError("uint8 input must be [B,H,W,3]")
+            x = x.contiguous()
+            B, H0, W0, _ = x.shape
+            if H0 % 16 or W0 % 16:  # the pad-to-/16 resize (model.py:51-54) works on the fp32 image
+                with torch.cuda.device(dev):
+                    x = ops.u8hwc_to_f32chw(x, torch.empty(B, 3, H0, W0, device=dev, dtype=F32))
+        else:
+            if x.dtype != F32 or not x.is_contiguous():
+                x = x.to(F32).contiguous()
+            B, _, H0, W0 = x.shape
         with torch.cuda.device(dev):
             ws = self.workspace(dev, B, H0, W0)
             if self.overlap and (self.side is None or self.side.device != dev):
@@ -388,7 +438,7 @@ class DepthEngine:
                     ws.graph, ws.graph_scale = g, scale
                 ws.graph.replay()
                 n += ws.body_launches
-            out, k = self._post(ws, scale)
+            out, k = self._post(ws, scale, keys, half, out_buffers)
             self.launches_per_forward = n + k
             if want is not None:
                 want["ws"] = ws

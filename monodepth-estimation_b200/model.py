@@ -49,6 +49,27 @@ class _EngineMixin:
             self.__dict__["_engine"] = eng
         return eng
 
+    @torch.no_grad()
+    def forward_keys(self, x, metadata=None, keys=(("disp", 0),), out_dtype=torch.float32, out_buffers=None):
+        """The forward for callers that know which outputs they read (no counterpart in the reference, whose ``forward`` always
+        returns every map; used by ``BatchPipeline`` / ``run_depth_estimation``, where only ``("disp", 0)`` and the uncertainty
+        cross the host link).  Same values as ``forward(x, metadata)[key]`` for every requested key.
+
+        ``x``: float32 ``[B,3,H,W]`` as in ``forward``, or the decoder's uint8 ``[B,H,W,3]`` image — a pixel then is
+        ``float(u8) / 255`` exactly as ``run_mars_depth.py:100-103`` computes it, evaluated inside the input kernel (3 bytes read
+        per pixel, no fp32 copy of the image).  ``out_dtype=torch.float16`` returns the maps rounded to IEEE fp16 by the output
+        kernel itself; ``out_buffers`` ({key: tensor}) makes it write into caller-owned tensors."""
+        if out_dtype not in (torch.float32, torch.float16):
+            raise ValueError("out_dtype must be torch.float32 or torch.float16")
+        if x.dtype == torch.uint8:
+            if self.training:
+                self._check_input(torch.empty(1, 3, 224, 224))  # raises the train-mode error
+            if not (x.dim() == 4 and x.shape[-1] == 3):
+                raise ValueError(f"expected a uint8 image batch [B,H,W,3], got {tuple(x.shape)}")
+        else:
+            self._check_input(x)
+        return self._get_engine().forward(x, source_scale(metadata), None, tuple(keys), out_dtype == torch.float16, out_buffers)
+
     def _check_input(self, x):
         if self.training:
             raise RuntimeError(

@@ -163,15 +163,19 @@ def rgb_to_grid(x, gh, gw, out_padded, out_coff, cfill):
 
 
 def resize_maps(maps, B, H, W, min_disp=0.01, max_disp=10.0):
-    """maps: list of (src [B,hs,ws] f32, mul, dst_disp|None, dst_depth|None)."""
+    """maps: list of (src [B,hs,ws] f32, mul, dst_disp|None, dst_depth|None[, dst_half|None]); dst_half is an fp16 tensor that
+    receives the resized disparity rounded to nearest (the host-link format of BatchPipeline)."""
     arr = (L.MapDesc * len(maps))()
-    for i, (src, mul, dd, dz) in enumerate(maps):
+    for i, m in enumerate(maps):
+        src, mul, dd, dz = m[:4]
+        dh = m[4] if len(m) > 4 else None
         arr[i].src = src.data_ptr()
         arr[i].hs, arr[i].ws = src.shape[-2], src.shape[-1]
         arr[i].mul = float(mul)
         arr[i].dst_disp = dd.data_ptr() if dd is not None else None
         arr[i].dst_disp2 = None
         arr[i].dst_depth = dz.data_ptr() if dz is not None else None
+        arr[i].dst_half = _ptr(dh, F16).value if dh is not None else None
     L.call("mde_resize_maps", arr, len(maps), B, H, W, float(min_disp), float(max_disp), _stream())
 
 
@@ -224,6 +228,20 @@ def input_stage(x, bn4x3, eps, scratch, affine, raw224, patches):
     L.call("mde_input_stage", _ptr(x, F32), B, H, W, _ptr(bn4x3, F32), float(eps), _ptr(scratch, F32), _ptr(affine, F32), _ptr(raw224, F32),
            _ptr(patches, BF16), _stream())
     return patches
+
+
+def input_stage_u8(x_hwc, bn4x3, eps, scratch, affine, raw224, patches):
+    """mde_input_stage from the uint8 [B,H,W,3] image (pixel = float(u8)/255): bit-identical outputs, 3 bytes read per pixel."""
+    B, H, W, _ = x_hwc.shape
+    L.call("mde_input_stage_u8", _ptr(x_hwc, torch.uint8), B, H, W, _ptr(bn4x3, F32), float(eps), _ptr(scratch, F32), _ptr(affine, F32), _ptr(raw224, F32),
+           _ptr(patches, BF16), _stream())
+    return patches
+
+
+def rgb_to_grid_u8(x_hwc, gh, gw, out_padded, out_coff, cfill):
+    B, H, W, _ = x_hwc.shape
+    L.call("mde_rgb_to_grid_nhwc_u8", _ptr(x_hwc, torch.uint8), B, H, W, gh, gw, _ptr(out_padded, BF16), out_padded.shape[-1], out_coff, cfill, _stream())
+    return out_padded
 
 
 def point_cloud(src, intrinsics4, min_depth, max_depth, from_disp=False, f64=True, rgb=None):

@@ -15,11 +15,12 @@ host never blocks inside the loop except to hand a finished result back.  PCIe i
 Two host formats are accepted:
   * ``float32 [B,3,H,W]`` — exactly what the reference callers build on the host (``run_mars_depth.py:100-104``);
   * ``uint8 [B,H,W,3]``   — what the image decoder produces (``np.array(PIL image)``, ``:97-100``); the
-    ``float()/255`` + HWC->CHW step then runs on the device (``mde_u8hwc_to_f32chw``: same IEEE fp32 division,
-    bit-identical to the host expression) and the H2D copy is 4x smaller.
+    ``float()/255`` step then happens inside the input kernel (``mde_input_stage_u8``: same IEEE fp32 division,
+    bit-identical to the host expression; no fp32 copy of the image is written) and the H2D copy is 4x smaller.
 
-``out_dtype=torch.float16`` hands the requested maps back as IEEE fp16 (``mde_f32_to_f16`` on the compute stream, round to
-nearest: relative error <= 4.9e-4, inside the 1e-2 bar) so the D2H copy is 2 bytes per pixel instead of 4 — what the
+Only the maps named in ``keys`` are resized to full resolution (``model.forward_keys``): the reference's loop reads
+``("disp", 0)`` and the uncertainty, nothing else.  ``out_dtype=torch.float16`` makes the output kernel write them as IEEE fp16
+(round to nearest: relative error <= 4.9e-4, inside the 1e-2 bar) so the D2H copy is 2 bytes per pixel instead of 4 — what the
 reference's callers do next with the map is an 8-bit colour-mapped PNG / a 16-bit depth image (``run_mars_depth.py:139-147``).
 """
 from __future__ import annotations
@@ -46,6 +47,7 @@ class BatchPipeline:
             raise RuntimeError("the model must live on a CUDA device")
         with torch.cuda.device(self.dev):
             self.s_in, self.s_out = torch.cuda.Stream(), torch.cuda.Stream()
+        self._lean = hasattr(model, "forward_keys")  # DepthAnything / EnhancedDepthAnything: u8 input kernel, key-filtered output kernel
         self._slots = None
         self._sig = None
 
@@ -68,9 +70,10 @@ class BatchPipeline:
         for _ in range(self.depth):
             s = {"raw": torch.empty(batch.shape, device=self.dev, dtype=batch.dtype), "in_ready": ev(), "in_free": ev(), "done": ev(), "copied": ev(),
                  "host": {k: torch.empty(B, 1, H, W, dtype=self.out_dtype).pin_memory() for k in self.keys}, "busy": False}
-            if self.out_dtype != F32:
-                s["half"] = {k: torch.empty(B, 1, H, W, device=self.dev, dtype=self.out_dtype) for k in self.keys}
-            s["x"] = s["raw"] if batch.dtype == F32 else torch.empty(B, 3, H, W, device=self.dev, dtype=F32)
+            # the output kernel writes straight into the slot's device buffers (their previous D2H is waited for before reuse)
+            s["dev"] = {k: torch.empty(B, 1, H, W, device=self.dev, dtype=self.out_dtype) for k in self.keys}
+            if not self._lean and batch.dtype == torch.uint8:  # composed callables take the fp32 image
+                s["x"] = torch.empty(B, 3, H, W, device=self.dev, dtype=F32)
             self._slots.append(s)
         self._sig = sig
 
@@ -96,18 +99,20 @@ class BatchPipeline:
                     s["raw"].copy_(hb, non_blocking=True)
                     s["in_ready"].record(self.s_in)
                 compute.wait_event(s["in_ready"])
-                if s["raw"].dtype == torch.uint8:
-                    ops.u8hwc_to_f32chw(s["raw"], s["x"])
-                out = self.model(s["x"], metadata)
+                # uint8 batches go to the input kernel as they are (a pixel is float(u8)/255 there); only the requested maps are
+                # resized to full resolution, in the requested dtype, into this slot's buffers
+                if self._lean:
+                    out = self.model.forward_keys(s["raw"], metadata, self.keys, self.out_dtype, s["dev"])
+                else:  # any other callable with the reference's forward(x, metadata) -> dict contract (composition.EnhancedWithRefinement)
+                    x = ops.u8hwc_to_f32chw(s["raw"], s["x"]) if s["raw"].dtype == torch.uint8 else s["raw"]
+                    full = self.model(x, metadata)
+                    out = {k: (ops.f32_to_f16(full[k], s["dev"][k]) if self.out_dtype != F32 else s["dev"][k].copy_(full[k])) for k in self.keys}
                 s["in_free"].record(compute)
-                if self.out_dtype != F32:  # the slot's fp16 buffers are free again: its previous D2H was waited for above (busy)
-                    out = {k: ops.f32_to_f16(out[k], s["half"][k]) for k in self.keys}
                 s["done"].record(compute)
                 with torch.cuda.stream(self.s_out):
                     self.s_out.wait_event(s["done"])
                     for k in self.keys:
                         s["host"][k].copy_(out[k], non_blocking=True)
-                        out[k].record_stream(self.s_out)
                     s["copied"].record(self.s_out)
                 s["busy"] = True
                 pending.append((i, s))

@@ -135,3 +135,52 @@ def test_run_depth_estimation_matches_the_reference_loop(tmp_path, kind, batch_s
             assert r["uncertainty"] is None
         name = os.path.splitext(os.path.basename(p))[0]
         assert np.array_equal(np.load(os.path.join(out_dir, name, f"{name}_depth.npy")), r["depth"])
+
+
+@pytest.mark.parametrize("B,H,W", [(3, 320, 256), (2, 1024, 1024), (1, 224, 228)])
+def test_input_stage_u8_is_bit_identical_to_convert_then_fp32_stage(B, H, W):
+    """mde_input_stage_u8 (the decoder's HWC bytes, pixel = float(u8)/255 inside the kernel) against mde_u8hwc_to_f32chw followed by
+    mde_input_stage: the affine map of the range heuristic, the raw 224 px raster and the bf16 patch rows, bit for bit."""
+    from monodepth_estimation_b200 import _lib as L
+
+    g = torch.Generator().manual_seed(H + W)
+    u8 = torch.randint(3, 250, (B, H, W, 3), dtype=torch.uint8, generator=g)
+    u8[0, 5, 7, 1], u8[B - 1, H - 1, W - 1, 2] = 255, 0  # the extremes sit in single pixels
+    u8 = u8.cuda()
+    bn = torch.tensor([1.1, 0.9, 1.0, 0.01, -0.02, 0.0, 0.05, 0.0, -0.05, 1.2, 0.8, 1.0], device="cuda")
+    outs = []
+    for fused in (False, True):
+        scratch = torch.empty(L.RANGE_SCRATCH_FLOATS, device="cuda")
+        affine, raw = torch.empty(6, device="cuda"), torch.empty(B, 3, 224, 224, device="cuda")
+        patches = torch.empty(B * 196, 768, device="cuda", dtype=torch.bfloat16)
+        if fused:
+            ops.input_stage_u8(u8, bn, 1e-5, scratch, affine, raw, patches)
+        else:
+            ops.input_stage(ops.u8hwc_to_f32chw(u8), bn, 1e-5, scratch, affine, raw, patches)
+        outs.append((affine, raw, patches))
+    for a, b in zip(*outs):
+        assert torch.equal(a, b)
+
+
+def test_forward_keys_subsets_dtypes_and_fallbacks():
+    """model.forward_keys: a subset of the maps, uint8 input (also at a size that needs the pad-to-/16 resize, where the image is
+    converted first), fp16 output written by the output kernel (disparities) or converted (depth), caller-owned buffers."""
+    m = cached_model("enhanced", 0, "cuda")
+    md = {"source": "ingenuity", "height": 12.0}
+    for H, W in ((192, 256), (200, 250)):
+        u8 = (synth_images(2, H, W, 77).permute(0, 2, 3, 1) * 255.0).round().to(torch.uint8).contiguous()
+        ref = m((u8.float().permute(0, 3, 1, 2) / 255.0).contiguous().cuda(), md)
+        keys = (("disp", 0), ("disp_fused", 0), ("uncertainty", 0), ("depth", 1), ("disp_unrefined", 0))
+        got = m.forward_keys(u8.cuda(), md, keys)
+        assert set(got) == set(keys)
+        for k in keys:
+            assert torch.equal(got[k], ref[k]), (H, W, k)
+        buf = {("disp", 0): torch.empty(2, 1, H, W, device="cuda", dtype=torch.float16)}
+        half = m.forward_keys(u8.cuda(), md, (("disp", 0), ("depth", 0)), torch.float16, buf)
+        assert half[("disp", 0)] is buf[("disp", 0)]
+        for k in half:
+            assert half[k].dtype == torch.float16 and torch.equal(half[k], ref[k].to(torch.float16)), (H, W, k)
+    with pytest.raises(KeyError):
+        m.forward_keys(u8.cuda(), md, (("disp", 7),))
+    with pytest.raises(ValueError):
+        m.forward_keys(u8.cuda(), md, (("disp", 0),), torch.float16, {("disp", 0): torch.empty(2, 1, 8, 8, device="cuda", dtype=torch.float16)})
