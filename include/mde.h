@@ -159,6 +159,16 @@ int mde_gemm_ln_bf16(const mde_bf16* A, int lda, const mde_bf16* W, int ldw, int
                      const float* ln_stats_in, const float* ln_colsum, float ln_eps, mde_bf16* xb_out, float* ln_stats_out,
                      mde_stream_t stream);
 
+/* ---- torchvision MLPBlock + residual (tv:117-119) as ONE launch -------------------------------------------------------------
+ * out[M][D] (f32) = resid + gelu(a[M][D] * w1[Hd][D]^T + b1) * w2[D][Hd]^T + b2, bf16 operands, fp32 accumulation; the GELU output
+ * is written to `hidden` [M][Hd] bf16 (caller scratch) and read back by the second product, whose tiles start as soon as the 256-row
+ * block they read is complete (csrc/tc_mlp.cu).  Same arithmetic as mde_gemm_bf16(MDE_EPI_BIAS_GELU_BF16) followed by
+ * mde_gemm_bf16(MDE_EPI_BIAS_RESID_F32): bit-identical results.  M >= 256 (at most 64 row blocks of 256), D and Hd multiples of 256,
+ * Hd a multiple of D.  sync: 128 uint32 of device memory, ALL ZERO on entry; zero again when the kernel ends.  Two calls that
+ * overlap on the GPU must not share a sync buffer. */
+int mde_mlp_bf16(const mde_bf16* a, int lda, const mde_bf16* w1, const float* b1, mde_bf16* hidden, int ldh, const mde_bf16* w2,
+                 const float* b2, const float* resid, float* out, int ldo, int M, int D, int Hd, unsigned* sync, mde_stream_t stream);
+
 /* Development hook (tools/gemm_prof.py): while `counters` (device, 8 x int64 per CTA, zeroed by the caller) is set, the
  * CTA-pair GEMM adds clock64 deltas per CTA: [0] MMA thread waiting for a free accumulator, [1] MMA thread waiting for
  * operands, [2] epilogue warp waiting for an accumulator, [3] epilogue warp working, [4] tiles, [5] CTA lifetime.

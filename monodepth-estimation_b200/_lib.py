@@ -53,6 +53,7 @@ SIGNATURES = {
     "mde_input_stage_u8": [_p, _i, _i, _i, _p, _f, _p, _p, _p, _p, _p],
     "mde_input_stage_noalloc": [_p, _i, _i, _i, _p, _f, _p, _p, _p, _p],
     "mde_gemm_bf16": [_p, _i, _p, _i, _i, _i, _i, _i, _p, _p, _i, _p, _p, _p],
+    "mde_mlp_bf16": [_p, _i, _p, _p, _p, _i, _p, _p, _p, _p, _i, _i, _i, _i, _p, _p],
     "mde_debug_gemm_prof": [_p],
     "mde_gemm_ln_bf16": [_p, _i, _p, _i, _i, _i, _i, _i, _p, _p, _i, _p, _p, _p, _p, _f, _p, _p, _p],
     "mde_layernorm_bf16": [_p, _i, _i, _p, _p, _f, _p, _p],

@@ -143,6 +143,7 @@ extern "C" long long mde_workspace_bytes(const mde_workspace_cfg* cfg) {
   add(B * 12 * 64 * MDE_VT_PITCH * 2);                   // vt
   add(M * 768 * 2);                                      // attn
   add(M * 3072 * 2);                                     // mlp
+  add(128 * 4);                                          // mlp_sync
   for (int i = 0; i < 4; ++i) add(B * G * 768 * 2);      // grid_a
   for (int i = 0; i < 4; ++i) add(B * G * 256 * 4);      // reduced
   add(B * P * (cfg->enhanced ? 320 : 256) * 2);          // feats[0]

@@ -46,6 +46,10 @@ _LN_FUSION = os.environ.get("MDE_LN_FUSION") == "1"  # opt-in, see DepthEngine._
 _FUSED_TAIL = os.environ.get("MDE_FUSED_TAIL", "0") == "1"
 # the 1-channel heads of decoder levels 0-2 run on the side stream (MDE_SIDE_HEADS=0: in line, for A/B timing)
 _SIDE_HEADS = os.environ.get("MDE_SIDE_HEADS", "1") == "1"
+# MDE_FUSED_MLP=1: fc1 + fc2 of a ViT layer in one persistent launch (csrc/tc_mlp.cu).  Opt-in: bit-identical to the two GEMMs
+# (tests/test_kernels_gpu.py) and equally fast back to back (60 us per layer at batch 32), but 1.3 us per layer SLOWER inside the
+# captured step (2.173 vs 2.157 ms): profiles/r02_experiments.md has the in-kernel time line and why the overlap does not pay
+_FUSED_MLP = os.environ.get("MDE_FUSED_MLP", "0") == "1"
 
 class Workspace:
     """All intermediates of one forward for a fixed (B, Hp, Wp); allocated once."""
@@ -82,6 +86,7 @@ class Workspace:
         self.vt = z(B * 12 * 64 * L.VT_PITCH)
         self.attn = e(M, 768)
         self.mlp = e(M, 3072)
+        self.mlp_sync = e(128, dt=torch.int32, zero=True)  # row-block counters of the fused MLP kernel (all zero between launches)
         self.grid_a = [e(B * G, 768) for _ in range(4)]  # per tap: the side stream works on tap i while the ViT runs on
         self.reduced = [e(B * G, 256, dt=F32) for _ in range(4)]
         c0 = 320 if enhanced else 256  # feature 0 carries the 3 rgb + 61 zero channels of the refinement conv
@@ -214,8 +219,13 @@ class DepthEngine:
                 ops.vit_attention(ws.q, ws.k, ws.vt, B, ws.attn)
                 ops.gemm(ws.attn, ly["proj_w"], ly["proj_b"], L.EPI_BIAS_RESID_F32, x_mid, x_in)
                 ops.layernorm(x_mid, ly["ln2_w"], ly["ln2_b"], 1e-6, ws.h)
-                ops.gemm(ws.h, ly["fc1_w"], ly["fc1_b"], L.EPI_BIAS_GELU_BF16, ws.mlp)
-                ops.gemm(ws.mlp, ly["fc2_w"], ly["fc2_b"], L.EPI_BIAS_RESID_F32, x_out, x_mid)
+                if _FUSED_MLP and ws.h.shape[0] >= L.GEMM_LN_MIN_ROWS:
+                    # fc1 + GELU + fc2 + residual as ONE persistent kernel: fc2 tiles start per finished 256-row block (csrc/tc_mlp.cu)
+                    ops.mlp(ws.h, ly["fc1_w"], ly["fc1_b"], ws.mlp, ly["fc2_w"], ly["fc2_b"], x_mid, x_out, ws.mlp_sync)
+                    n -= 1
+                else:
+                    ops.gemm(ws.h, ly["fc1_w"], ly["fc1_b"], L.EPI_BIAS_GELU_BF16, ws.mlp)
+                    ops.gemm(ws.mlp, ly["fc2_w"], ly["fc2_b"], L.EPI_BIAS_RESID_F32, x_out, x_mid)
                 n += 7
             if want is not None and i == 0:
                 want["block0_q"] = ws.q.clone()

@@ -139,6 +139,18 @@ def conv_nhwc(inp, h, w, cin, wpacked, bias, cout, ksize, padding, act, out_bf16
     return out_bf16 if out_bf16 is not None else out_f32
 
 
+def mlp(a, w1, b1, hidden, w2, b2, resid, out, sync):
+    """tv:117-118 + the residual add (tv:119) in one launch: out = resid + (gelu(a @ w1.T + b1) @ w2.T + b2).  ``hidden`` [M, Hd] bf16 is
+    scratch (it holds the GELU output afterwards), ``sync`` an int32 [128] buffer that is all zero before and after the call."""
+    M, D = a.shape
+    Hd = w1.shape[0]
+    if w1.shape != (Hd, D) or w2.shape != (D, Hd) or hidden.shape != (M, Hd) or resid.shape != (M, D) or out.shape != (M, D) or sync.numel() < 128:
+        raise ValueError("mlp: shape mismatch")
+    L.call("mde_mlp_bf16", _ptr(a, BF16), a.stride(0), _ptr(w1, BF16), _ptr(b1, F32), _ptr(hidden, BF16), hidden.stride(0), _ptr(w2, BF16), _ptr(b2, F32),
+           _ptr(resid, F32), _ptr(out, F32), out.stride(0), M, D, Hd, _ptr(sync, torch.int32), _stream())
+    return out
+
+
 def upsample2x_concat(a, h, w, s, hs, ws, out):
     B, ca = a.shape[0], a.shape[-1]
     cs = 0 if s is None else s.shape[-1]

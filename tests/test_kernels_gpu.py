@@ -529,3 +529,32 @@ def test_enh_fuse():
     wts = torch.softmax(fw, 0)
     ref = sum(wts[i] * (s[i] if i == 0 else F.interpolate(s[i], size=(2 * gh, 2 * gw), mode="bilinear", align_corners=False)) for i in range(3))
     assert max_abs(fused.unsqueeze(1), ref) < 2e-6
+
+
+@pytest.mark.parametrize("M", [6304, 3152, 1576, 1024])
+def test_fused_mlp_equals_the_two_gemms(M):
+    """mde_mlp_bf16 (fc1 + GELU + fc2 + residual in one persistent launch, fc2 tiles released per finished 256-row block) against
+    mde_gemm_bf16 x 2: the same MMAs in the same order and the same epilogue arithmetic, so the results are bit-identical; the
+    row-block counters are zero again afterwards, also after back-to-back launches."""
+    L, ops = _mods()
+    D, Hd = 768, 3072
+    a = _rand(M, D, seed=90).to(BF16)
+    w1, b1 = _rand(Hd, D, seed=91, scale=D ** -0.5).to(BF16), _rand(Hd, seed=92, scale=0.1)
+    w2, b2 = _rand(D, Hd, seed=93, scale=Hd ** -0.5).to(BF16), _rand(D, seed=94, scale=0.1)
+    resid = _rand(M, D, seed=95)
+    hid_ref = torch.empty(M, Hd, device="cuda", dtype=BF16)
+    out_ref = torch.empty(M, D, device="cuda")
+    ops.gemm(a, w1, b1, L.EPI_BIAS_GELU_BF16, hid_ref)
+    ops.gemm(hid_ref, w2, b2, L.EPI_BIAS_RESID_F32, out_ref, resid)
+    sync = torch.zeros(128, device="cuda", dtype=torch.int32)
+    for rep in range(3):
+        hid = torch.full((M, Hd), float("nan"), device="cuda", dtype=BF16)
+        out = torch.full((M, D), float("nan"), device="cuda")
+        ops.mlp(a, w1, b1, hid, w2, b2, resid, out, sync)
+        torch.cuda.synchronize()
+        assert int(sync.abs().sum()) == 0, rep
+        assert torch.equal(hid, hid_ref), rep
+        assert torch.equal(out, out_ref), (rep, rel_l2(out, out_ref))
+    # and against torch (bf16 operands, fp32 accumulation, the exact-erf GELU the epilogue approximates to 2.5e-5)
+    ref = resid + torch.nn.functional.gelu(a.float() @ w1.float().t() + b1).to(BF16).float() @ w2.float().t() + b2
+    assert rel_l2(out, ref) < 2e-3, rel_l2(out, ref)
