@@ -214,7 +214,7 @@ def run_reference(a):
             "e2e": {"value": round(v, 3), "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     if a.model == "standard":
         line["cpu_baseline"]["config1"] = cpu_config1(threads)
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # ------------------------------------------------------------------------------------ B200 arm
@@ -289,8 +289,32 @@ def b2b_seconds(torch, fn, reps=20, warm=3):
     return e0.elapsed_time(e1) * 1e-3 / reps
 
 
+_REAL_STDOUT = None
+
+
+def _quiet_stdout():
+    """The contract is ONE JSON line on stdout.  Libraries print there too (NCCL's version banner under torchrun): from here on
+    file descriptor 1 points at stderr, and emit() writes the line to the real stdout."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(line):
+    data = (json.dumps(line) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        sys.stdout.flush()
+        os.write(_REAL_STDOUT, data)
+
+
 def main():
     a = parse()
+    _quiet_stdout()
     if a.impl == "reference":
         return run_reference(a)
 
@@ -300,7 +324,7 @@ def main():
     env = Env()
     line = bench_train(a, env) if a.model == "train" else bench_forward(a, env)
     if env.rank == 0:
-        print(json.dumps(line), flush=True)
+        emit(line)
     if env.dist is not None:
         env.dist.destroy_process_group()
 
