@@ -1,3 +1,9 @@
 cd $GRAFT_REPO_ROOT
-timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus 8 --steps 20 --warmup 3 > gpurun_out/r02h_bench_8gpu.json 2> gpurun_out/r02h_bench_8gpu_err.txt; echo rc=$?
-tail -c 600 gpurun_out/r02h_bench_8gpu.json
+for bn in 0 64 128 256; do
+echo "BLOCK_N=$bn"
+MDE_CONV_BLOCK_N=$bn python tools/conv_bench.py 256 256 14 15 32 50
+MDE_CONV_BLOCK_N=$bn python tools/conv_bench.py 256 128 14 15 32 50
+MDE_CONV_BLOCK_N=$bn python tools/conv_bench.py 256 128 28 30 32 50
+MDE_CONV_BLOCK_N=$bn python tools/conv_bench.py 128 64 28 30 32 50
+done > gpurun_out/convbn.txt 2>&1
+cat gpurun_out/convbn.txt
