@@ -16,7 +16,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libmde.so")
 OBJ_DIR = os.path.join(HERE, "build")
-SOURCES = ["api.cu", "tc_gemm.cu", "tc_gemm2.cu", "tc_mlp.cu", "conv_halo.cu", "decoder_tail.cu", "attention.cu", "pointwise.cu", "refine.cu", "terrain.cu", "depth_filters.cu", "backward.cu", "train_ops.cu"]
+SOURCES = ["api.cu", "tc_gemm.cu", "tc_gemm2.cu", "tc_mlp.cu", "conv_halo.cu", "conv_small.cu", "decoder_tail.cu", "attention.cu", "pointwise.cu", "refine.cu", "terrain.cu", "depth_filters.cu", "backward.cu", "train_ops.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr",

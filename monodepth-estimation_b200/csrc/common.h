@@ -68,6 +68,10 @@ int launch_gemm_pair(const void* A, int lda, const void* W, int ldw, int M, int 
 // geometry not served there, the caller uses the tap-shifted kernel.
 int launch_conv_halo(int f16, const void* in, int B, int h, int w, int cin, int in_cstride, const void* wpacked, const float* bias, int cout,
                      int padding, int activation, void* out_bf16, int out_cstride, int out_coff, float* out_f32, cudaStream_t stream);
+// 3x3 conv on maps narrower than 48 px with cin % 64 == 0, cout % 32 == 0, bf16 output (conv_small.cu): halo tile + streamed weights.
+// MDE_OK after launching, MDE_ERR_UNSUPPORTED (no error set) if the geometry is not served.
+int launch_conv_small(int f16, const void* in, int B, int h, int w, int cin, int in_cstride, const void* wpacked, const float* bias, int cout,
+                      int padding, int activation, void* out_bf16, int out_cstride, int out_coff, cudaStream_t stream);
 
 // Kernel launch, with programmatic dependent launch unless MDE_PDL=0 (see pdl_enabled()).  Errors are picked up
 // by MDE_CHECK_LAUNCH() at the call site.

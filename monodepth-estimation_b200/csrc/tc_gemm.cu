@@ -393,6 +393,10 @@ static int conv_nhwc_impl(int f16, const mde_bf16* in, int B, int h, int w, int 
     const int rc = launch_conv_halo(f16, in, B, h, w, cin, in_cstride, wpacked, bias, cout, padding, activation, out_bf16, out_cstride, out_coff,
                                     out_f32, stream);
     if (rc != MDE_ERR_UNSUPPORTED) return rc;
+    if (out_bf16) {  // small maps, wide channels: halo tile + streamed weights (conv_small.cu)
+      const int rc2 = launch_conv_small(f16, in, B, h, w, cin, in_cstride, wpacked, bias, cout, padding, activation, out_bf16, out_cstride, out_coff, stream);
+      if (rc2 != MDE_ERR_UNSUPPORTED) return rc2;
+    }
   }
 
   // spatial tile: 128 output pixels = th rows x tw columns

@@ -279,6 +279,9 @@ CONV_CASES = [
     (2, 14, 14, 256, 64, 3, "reflect", "sigmoid"),
     (1, 14, 15, 320, 256, 3, "zero", "elu"),
     (2, 14, 15, 128, 16, 1, "zero", "none"),
+    (40, 14, 15, 128, 64, 3, "reflect", "elu"),   # conv_small.cu: more tiles than SMs (persistent loop), two chunks
+    (1, 44, 40, 64, 64, 3, "reflect", "elu"),     # conv_small.cu: several row tiles per image, one chunk
+    (3, 30, 28, 192, 96, 3, "zero", "none"),      # conv_small.cu: 32-column tiles (cout % 64 != 0), three chunks
 ]
 
 
