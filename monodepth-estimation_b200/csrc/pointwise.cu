@@ -244,15 +244,19 @@ __global__ void __launch_bounds__(256) input_scan_resample_kernel(const float* _
   {
     const float4* p4 = reinterpret_cast<const float4*>(pl + (size_t)lo * W);  // host checked W % 4 == 0 and 16-byte alignment
     const int n4 = (hi - lo) * (W >> 2);
-    for (int i0 = threadIdx.x; i0 < n4; i0 += 4 * 256) {
-      float4 v[4];
+#ifndef MDE_SCAN_UNROLL
+#define MDE_SCAN_UNROLL 8
+#endif
+    constexpr int U = MDE_SCAN_UNROLL;  // independent 16-byte loads in flight per thread (r02, 32 x 3 x 1024^2: 2 / 4 / 8 -> 85.6 / 85.9 / 79.0 us)
+    for (int i0 = threadIdx.x; i0 < n4; i0 += U * 256) {
+      float4 v[U];
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
+      for (int u = 0; u < U; ++u) {
         const int i = i0 + u * 256;
         v[u] = __ldg(p4 + min(i, n4 - 1));  // past the end: re-read the last vector (neutral for min and max)
       }
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
+      for (int u = 0; u < U; ++u) {
         mn = fminf(mn, fminf(fminf(v[u].x, v[u].y), fminf(v[u].z, v[u].w)));
         mx = fmaxf(mx, fmaxf(fmaxf(v[u].x, v[u].y), fmaxf(v[u].z, v[u].w)));
       }
@@ -1186,7 +1190,7 @@ extern "C" int mde_input_stage(const float* x, int B, int H, int W, const float*
   MDE_CHECK_ARG((uintptr_t)raw224 % 16 == 0 && (uintptr_t)patches % 16 == 0, "mde_input_stage: raw224 / patches must be 16-byte aligned");
   const int max_parts = MDE_RANGE_SCRATCH_FLOATS / 6;
   int rpb = ceil_div(224 * 3 * B, max_parts);  // output rows per block: as few as the partials buffer allows, at least kMinRows
-  static const int kMinRows = getenv("MDE_SCAN_ROWS") ? atoi(getenv("MDE_SCAN_ROWS")) : 4;
+  static const int kMinRows = getenv("MDE_SCAN_ROWS") ? atoi(getenv("MDE_SCAN_ROWS")) : 3;  // r02: 3 rows 77.0 us, 4 rows 79.0, 6 rows 92.7 (with 8 loads in flight)
   if (rpb < kMinRows) rpb = kMinRows;
   MDE_CHECK_ARG(rpb <= 224, "mde_input_stage: batch %d too large for the partials buffer", B);
   const int groups = ceil_div(224, rpb);
