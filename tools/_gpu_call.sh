@@ -1,3 +1,8 @@
 cd $GRAFT_REPO_ROOT
-( python tools/io_bench.py; MDE_LIB_PATH=tools/_libmde_scan16.so python tools/io_bench.py; python tools/io_bench.py 8 1024; python tools/io_bench.py 4 518 ) > gpurun_out/scan2.txt 2>&1; cat gpurun_out/scan2.txt
-timeout 600 python -m pytest tests/test_kernels_gpu.py tests/test_zz_no_alloc.py tests/test_forward_gpu.py -x -q -m gpu 2>&1 | tail -2
+timeout 1500 python -m pytest tests -x -q -m gpu 2>&1 | tail -3
+timeout 600 python bench.py > gpurun_out/r02i_bench.json 2> gpurun_out/r02i_bench_err.txt; echo bench rc=$?
+timeout 300 python bench.py --model enhanced --no-extras > gpurun_out/r02i_enhanced.json 2>> gpurun_out/r02i_bench_err.txt; echo enh rc=$?
+timeout 300 python bench.py --model config4 --no-extras > gpurun_out/r02i_config4_b16.json 2>> gpurun_out/r02i_bench_err.txt; echo c4 rc=$?
+timeout 300 python bench.py --model train --no-extras > gpurun_out/r02i_train_bench.json 2>> gpurun_out/r02i_bench_err.txt; echo train rc=$?
+timeout 300 python bench.py --batch 4 --no-extras > gpurun_out/r02i_standard_b4.json 2>> gpurun_out/r02i_bench_err.txt; echo b4 rc=$?
+python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -1
