@@ -243,10 +243,11 @@ __global__ void __launch_bounds__(128, 2) vit_attn_tp_kernel(const __grid_consta
   uint8_t* sQ = smem;
   uint8_t* sK = smem + kTpOffK;
   uint8_t* sV = smem + kTpOffV;
-  uint64_t* bar_load = reinterpret_cast<uint64_t*>(smem + kTpOffBar);
+  uint64_t* bar_load = reinterpret_cast<uint64_t*>(smem + kTpOffBar);  // Q and K have landed
   uint64_t* bar_s = bar_load + 1;
   uint64_t* bar_o = bar_load + 2;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_load + 3);
+  uint64_t* bar_v = bar_load + 3;  // V^T has landed (needed only by P V: S = Q K^T and the softmax start without it)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_load + 4);
 
   const int tid = threadIdx.x, warp = tid >> 5;
   const int slab = blockIdx.x >> 1, mt = blockIdx.x & 1;  // (image, head), query tile
@@ -260,6 +261,7 @@ __global__ void __launch_bounds__(128, 2) vit_attn_tp_kernel(const __grid_consta
       mbar_init(bar_load, 1);
       mbar_init(bar_s, 1);
       mbar_init(bar_o, 1);
+      mbar_init(bar_v, 1);
       fence_barrier_init();
     }
     __syncwarp();
@@ -274,11 +276,12 @@ __global__ void __launch_bounds__(128, 2) vit_attn_tp_kernel(const __grid_consta
   PS_T(2);
 
   if (tid == 0) {
-    mbar_expect_tx(bar_load, kQBytes + kKBytes + 4 * kVBytes);
+    mbar_expect_tx(bar_load, kQBytes + kKBytes);
     tma_load_4d(sQ, &p.tmQ, bar_load, 0, hd, mt * 128, b);
     tma_load_4d(sK, &p.tmK, bar_load, 0, hd, 0, b);
+    mbar_expect_tx(bar_v, 4 * kVBytes);
 #pragma unroll
-    for (int j = 0; j < 4; ++j) tma_load_3d(sV + j * kVBytes, &p.tmV, bar_load, 64 * j, 0, slab);
+    for (int j = 0; j < 4; ++j) tma_load_3d(sV + j * kVBytes, &p.tmV, bar_v, 64 * j, 0, slab);
     mbar_wait(bar_load, 0);
     PS_T(3);
     tc_fence_after();
@@ -353,6 +356,7 @@ __global__ void __launch_bounds__(128, 2) vit_attn_tp_kernel(const __grid_consta
 
   // ---- O = P V  (128 x 64, K = 208 = 13 x 16): A from TMEM, B = V^T tiles in shared memory
   if (tid == 0) {
+    mbar_wait(bar_v, 0);
     tc_fence_after();
     constexpr uint32_t idesc_o = umma_idesc_bf16(128, 64);
 #pragma unroll

@@ -1,8 +1,6 @@
 cd $GRAFT_REPO_ROOT
-timeout 1500 python -m pytest tests -x -q -m gpu 2>&1 | tail -3
-timeout 600 python bench.py > gpurun_out/r02i_bench.json 2> gpurun_out/r02i_bench_err.txt; echo bench rc=$?
-timeout 300 python bench.py --model enhanced --no-extras > gpurun_out/r02i_enhanced.json 2>> gpurun_out/r02i_bench_err.txt; echo enh rc=$?
-timeout 300 python bench.py --model config4 --no-extras > gpurun_out/r02i_config4_b16.json 2>> gpurun_out/r02i_bench_err.txt; echo c4 rc=$?
-timeout 300 python bench.py --model train --no-extras > gpurun_out/r02i_train_bench.json 2>> gpurun_out/r02i_bench_err.txt; echo train rc=$?
-timeout 300 python bench.py --batch 4 --no-extras > gpurun_out/r02i_standard_b4.json 2>> gpurun_out/r02i_bench_err.txt; echo b4 rc=$?
-python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -1
+timeout 300 python -m pytest tests/test_kernels_gpu.py -x -q -m gpu -k "attention" 2>&1 | tail -2
+for i in 1 2; do
+timeout 300 python bench.py --no-extras --steps 30 --warmup 5 2>> gpurun_out/c65_err.txt | python -c "import json,sys; d=json.loads(sys.stdin.read()); print('split load barrier', d['value'], d['ms_per_step'])"
+MDE_LIB_PATH=tools/_libmde_base2.so timeout 300 python bench.py --no-extras --steps 30 --warmup 5 2>> gpurun_out/c65_err.txt | python -c "import json,sys; d=json.loads(sys.stdin.read()); print('one barrier', d['value'], d['ms_per_step'])"
+done
