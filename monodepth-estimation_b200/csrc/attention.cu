@@ -32,6 +32,7 @@ constexpr uint32_t kTmemTile = 256;  // column stride between the two query tile
 
 struct alignas(64) AttnParams {
   CUtensorMap tmQ, tmK, tmV;
+  CUtensorMap tmO;  // the output viewed like q: box {64 d, 1 head, 128 tokens, 1 image}; tokens >= 197 of a box are clipped by the store
   bf16* out;
   int B;
 };
@@ -370,21 +371,33 @@ __global__ void __launch_bounds__(128, 2) vit_attn_tp_kernel(const __grid_consta
   tc_fence_after();
   PS_T(7);
 
-  const int t = mt * 128 + tid;
-#pragma unroll 1
-  for (int c = 0; c < 2; ++c) {
-    uint32_t r[32];
-    tmem_ld_32x32b_x32(t_row + c * 32, r);
-    tmem_ld_wait();
-    if (t < kS) {
-      uint4* dst = reinterpret_cast<uint4*>(p.out + ((size_t)b * kS + t) * MDE_VIT_DIM + hd * 64 + c * 32);
+  // O * (1 / rowsum) -> bf16 into the Q tile's shared memory (Q was consumed by S = Q K^T), in the 128-byte swizzle the store
+  // expects; ONE TMA store writes the 128 x 64 tile as full lines and clips the rows past token 196 (the per-thread stores it
+  // replaces touched 32 different lines per instruction).
+  {
+    uint8_t* orow = sQ + tid * 128;
+    const uint32_t sw = static_cast<uint32_t>(tid & 7);
+#pragma unroll
+    for (int c = 0; c < 2; ++c) {
+      uint32_t r[32];
+      tmem_ld_32x32b_x32(t_row + c * 32, r);
+      tmem_ld_wait();
 #pragma unroll
       for (int g = 0; g < 4; ++g)
-        dst[g] = make_uint4(pack_bf16x2(__uint_as_float(r[8 * g]) * inv, __uint_as_float(r[8 * g + 1]) * inv),
-                            pack_bf16x2(__uint_as_float(r[8 * g + 2]) * inv, __uint_as_float(r[8 * g + 3]) * inv),
-                            pack_bf16x2(__uint_as_float(r[8 * g + 4]) * inv, __uint_as_float(r[8 * g + 5]) * inv),
-                            pack_bf16x2(__uint_as_float(r[8 * g + 6]) * inv, __uint_as_float(r[8 * g + 7]) * inv));
+        *reinterpret_cast<uint4*>(orow + ((static_cast<uint32_t>(4 * c + g) ^ sw) << 4)) =
+            make_uint4(pack_bf16x2(__uint_as_float(r[8 * g]) * inv, __uint_as_float(r[8 * g + 1]) * inv),
+                       pack_bf16x2(__uint_as_float(r[8 * g + 2]) * inv, __uint_as_float(r[8 * g + 3]) * inv),
+                       pack_bf16x2(__uint_as_float(r[8 * g + 4]) * inv, __uint_as_float(r[8 * g + 5]) * inv),
+                       pack_bf16x2(__uint_as_float(r[8 * g + 6]) * inv, __uint_as_float(r[8 * g + 7]) * inv));
     }
+    fence_proxy_async_smem();
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (tid == 0) {
+    tma_store_4d(&p.tmO, sQ, 0, hd, mt * 128, b);
+    bulk_commit();
+    bulk_wait_all<0>();  // complete (not only read out of shared memory): the next kernel reads this tile right after the grid ends
   }
   tc_fence_before();
   __syncthreads();
@@ -759,6 +772,8 @@ extern "C" int mde_vit_attention(const mde_bf16* q, const mde_bf16* k, const mde
     int rc = encode_tmap_bf16(&p.tmQ, q, 4, dims, strides, boxq, 128);
     if (rc != MDE_OK) return rc;
     rc = encode_tmap_bf16(&p.tmK, k, 4, dims, strides, boxk, 128);
+    if (rc != MDE_OK) return rc;
+    rc = encode_tmap_bf16(&p.tmO, out, 4, dims, strides, boxq, 128);  // the output has q's layout
     if (rc != MDE_OK) return rc;
   }
   {
