@@ -303,18 +303,23 @@ __global__ void __launch_bounds__(128, 2) vit_attn_tp_kernel(const __grid_consta
 
   // ---- pass 1: row maximum over the 197 real keys (four independent chains: a thread is alone with its row, so the
   // dependent-issue latency of one 197-long fmax chain was ~0.4 us of every CTA)
+  // Both passes keep the TMEM load of the NEXT 32-column chunk in flight while the current one is reduced / exponentiated (a thread
+  // is alone with its row: an un-overlapped tcgen05.ld round trip per chunk was a third of the second pass).
   float m4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
-#pragma unroll 1
-  for (int c = 0; c < 6; ++c) {
-    uint32_t r[32];
-    tmem_ld_32x32b_x32(t_row + c * 32, r);
-    tmem_ld_wait();
-#pragma unroll
-    for (int j = 0; j < 32; ++j) m4[j & 3] = fmaxf(m4[j & 3], __uint_as_float(r[j]));
-  }
   uint32_t tail[16];
-  tmem_ld_32x32b_x16(t_row + 192, tail);
-  tmem_ld_wait();
+  {
+    uint32_t r[2][32];
+    tmem_ld_32x32b_x32(t_row, r[0]);
+#pragma unroll
+    for (int c = 0; c < 6; ++c) {
+      tmem_ld_wait();
+      if (c + 1 < 6) tmem_ld_32x32b_x32(t_row + (c + 1) * 32, r[(c + 1) & 1]);
+      else tmem_ld_32x32b_x16(t_row + 192, tail);
+#pragma unroll
+      for (int j = 0; j < 32; ++j) m4[j & 3] = fmaxf(m4[j & 3], __uint_as_float(r[c & 1][j]));
+    }
+    tmem_ld_wait();
+  }
 #pragma unroll
   for (int j = 0; j < kS - 192; ++j) m4[j & 3] = fmaxf(m4[j & 3], __uint_as_float(tail[j]));
   const float mx = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3]));
@@ -324,6 +329,8 @@ __global__ void __launch_bounds__(128, 2) vit_attn_tp_kernel(const __grid_consta
   // ---- pass 2, last chunk first: exp, row sum, bf16 probabilities back into TMEM
   float s4[4] = {0.0f, 0.0f, 0.0f, 0.0f};  // partial row sums (fixed assignment of columns to partials: deterministic)
   {
+    uint32_t r[2][32];
+    tmem_ld_32x32b_x32(t_row + 5 * 32, r[1]);  // chunk 5 on its way while the tail is exponentiated
     uint32_t pk[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
@@ -333,21 +340,21 @@ __global__ void __launch_bounds__(128, 2) vit_attn_tp_kernel(const __grid_consta
       pk[j] = pack_bf16x2(e0, e1);
     }
     tmem_st_32x32b_x8(t_row + kTpP + 96, pk);
-  }
-#pragma unroll 1
-  for (int c = 5; c >= 0; --c) {
-    uint32_t r[32];
-    tmem_ld_32x32b_x32(t_row + c * 32, r);
-    tmem_ld_wait();
-    uint32_t pk[16];
 #pragma unroll
-    for (int j = 0; j < 16; ++j) {
-      const float e0 = fast_ex2(fmaf(__uint_as_float(r[2 * j]), kLog2e, -mxs));
-      const float e1 = fast_ex2(fmaf(__uint_as_float(r[2 * j + 1]), kLog2e, -mxs));
-      s4[j & 3] += e0 + e1;
-      pk[j] = pack_bf16x2(e0, e1);
+    for (int c = 5; c >= 0; --c) {
+      tmem_ld_wait();
+      // the next chunk's scores (columns 32 (c-1) ..) lie below everything written so far (P columns >= 104 + 16 c)
+      if (c > 0) tmem_ld_32x32b_x32(t_row + (c - 1) * 32, r[(c - 1) & 1]);
+      uint32_t pc[16];
+#pragma unroll
+      for (int j = 0; j < 16; ++j) {
+        const float e0 = fast_ex2(fmaf(__uint_as_float(r[c & 1][2 * j]), kLog2e, -mxs));
+        const float e1 = fast_ex2(fmaf(__uint_as_float(r[c & 1][2 * j + 1]), kLog2e, -mxs));
+        s4[j & 3] += e0 + e1;
+        pc[j] = pack_bf16x2(e0, e1);
+      }
+      tmem_st_32x32b_x16(t_row + kTpP + 16 * c, pc);  // columns >= 104 + 16c: scores there (>= 32c) are already in registers
     }
-    tmem_st_32x32b_x16(t_row + kTpP + 16 * c, pk);  // columns >= 104 + 16c: scores there (>= 32c) are already consumed
   }
   tmem_st_wait();
   const float inv = 1.0f / ((s4[0] + s4[1]) + (s4[2] + s4[3]));
