@@ -264,6 +264,14 @@ __global__ void __launch_bounds__(128, 2) vit_attn_tp_kernel(const __grid_consta
       mbar_init(bar_o, 1);
       mbar_init(bar_v, 1);
       fence_barrier_init();
+      // the loads go out before the TMEM allocation and the block-wide sync below: their round trip is the head of the CTA's chain
+      pdl_grid_wait();
+      mbar_expect_tx(bar_load, kQBytes + kKBytes);
+      tma_load_4d(sQ, &p.tmQ, bar_load, 0, hd, mt * 128, b);
+      tma_load_4d(sK, &p.tmK, bar_load, 0, hd, 0, b);
+      mbar_expect_tx(bar_v, 4 * kVBytes);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) tma_load_3d(sV + j * kVBytes, &p.tmV, bar_v, 64 * j, 0, slab);
     }
     __syncwarp();
     tmem_alloc(tmem_slot, kTpTmemCols);
@@ -277,12 +285,6 @@ __global__ void __launch_bounds__(128, 2) vit_attn_tp_kernel(const __grid_consta
   PS_T(2);
 
   if (tid == 0) {
-    mbar_expect_tx(bar_load, kQBytes + kKBytes);
-    tma_load_4d(sQ, &p.tmQ, bar_load, 0, hd, mt * 128, b);
-    tma_load_4d(sK, &p.tmK, bar_load, 0, hd, 0, b);
-    mbar_expect_tx(bar_v, 4 * kVBytes);
-#pragma unroll
-    for (int j = 0; j < 4; ++j) tma_load_3d(sV + j * kVBytes, &p.tmV, bar_v, 64 * j, 0, slab);
     mbar_wait(bar_load, 0);
     PS_T(3);
     tc_fence_after();
@@ -404,7 +406,7 @@ __global__ void __launch_bounds__(128, 2) vit_attn_tp_kernel(const __grid_consta
   if (tid == 0) {
     tma_store_4d(&p.tmO, sQ, 0, hd, mt * 128, b);
     bulk_commit();
-    bulk_wait_all<0>();  // complete (not only read out of shared memory): the next kernel reads this tile right after the grid ends
+    bulk_wait_exit<0>();
   }
   tc_fence_before();
   __syncthreads();
@@ -417,6 +419,203 @@ __global__ void __launch_bounds__(128, 2) vit_attn_tp_kernel(const __grid_consta
            tp[2] - tp[1], tp[3] - tp[2], tp[4] - tp[3], tp[5] - tp[4], tp[6] - tp[5], tp[7] - tp[6], tp[8] - tp[7], tp[8] - tp[0], tp[0] % 1000000ull);
   }
 #endif
+}
+
+// ------------------------------------------------------------------ ViT attention, probabilities in TMEM, TWO threads per query row
+// vit_attn_tp_kernel with 256 threads: warps w and w + 4 share TMEM lane quarter w & 3 (a warp may only touch the lanes of its
+// quarter), and each takes half of the row's 208 score columns — half 0 keys [0,96), half 1 keys [96,208).  A thread alone with its
+// row is a ~400-instruction dependent chain per pass; two threads halve it and give every scheduler four softmax warps per CTA pair
+// instead of two.  The halves exchange the row maximum (one named barrier per lane quarter) and the row sum through shared memory.
+// Probabilities: half 0 writes keys [0,96) into the 48 unused columns [208,256); half 1 writes keys [96,208) into [152,208), over
+// scores that only half 1 reads and has already taken (last chunk first), so the halves never wait for each other inside a pass.
+constexpr int kT2OffX = kTpOffBar + 64;                   // float [2][2][128]: row maximum, row sum per half
+constexpr int kT2Smem = kT2OffX + 2048 + 1024;
+constexpr uint32_t kT2P0 = 208, kT2P1 = 152;             // first TMEM column of the probabilities of half 0 / half 1
+
+__global__ void __launch_bounds__(256, 2) vit_attn_tp2_kernel(const __grid_constant__ AttnParams p) {
+  pdl_launch_dependents();
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
+  uint8_t* sQ = smem;
+  uint8_t* sK = smem + kTpOffK;
+  uint8_t* sV = smem + kTpOffV;
+  uint64_t* bar_load = reinterpret_cast<uint64_t*>(smem + kTpOffBar);  // Q and K have landed
+  uint64_t* bar_s = bar_load + 1;
+  uint64_t* bar_o = bar_load + 2;
+  uint64_t* bar_v = bar_load + 3;  // V^T has landed (needed only by P V)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_load + 4);
+  float* xmax = reinterpret_cast<float*>(smem + kT2OffX);  // [2][128]
+  float* xsum = xmax + 256;                                // [2][128]
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int qt = warp & 3, half = warp >> 2;  // TMEM lane quarter, column half (warp-uniform)
+  const int row = qt * 32 + lane;             // query row of the tile = TMEM lane
+  const int slab = blockIdx.x >> 1, mt = blockIdx.x & 1;
+  const int b = slab / MDE_VIT_HEADS, hd = slab - b * MDE_VIT_HEADS;
+
+  if (warp == 0) {
+    if (elect_one()) {
+      tma_prefetch_desc(&p.tmQ);
+      tma_prefetch_desc(&p.tmK);
+      tma_prefetch_desc(&p.tmV);
+      mbar_init(bar_load, 1);
+      mbar_init(bar_s, 1);
+      mbar_init(bar_o, 1);
+      mbar_init(bar_v, 1);
+      fence_barrier_init();
+      // the loads go out before the TMEM allocation and the block-wide sync below: their round trip is the head of the CTA's chain
+      pdl_grid_wait();
+      mbar_expect_tx(bar_load, kQBytes + kKBytes);
+      tma_load_4d(sQ, &p.tmQ, bar_load, 0, hd, mt * 128, b);
+      tma_load_4d(sK, &p.tmK, bar_load, 0, hd, 0, b);
+      mbar_expect_tx(bar_v, 4 * kVBytes);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) tma_load_3d(sV + j * kVBytes, &p.tmV, bar_v, 64 * j, 0, slab);
+    }
+    __syncwarp();
+    tmem_alloc(tmem_slot, kTpTmemCols);
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  pdl_grid_wait();
+
+  if (tid == 0) {
+    mbar_wait(bar_load, 0);
+    tc_fence_after();
+    constexpr uint32_t idesc_s = umma_idesc_bf16(128, kKeys);
+    const uint64_t da = umma_smem_desc_kmajor<128>(smem_u32(sQ));
+    const uint64_t db = umma_smem_desc_kmajor<128>(smem_u32(sK));
+#pragma unroll
+    for (int k = 0; k < 4; ++k) umma_bf16_ss(tmem_base, da + 2 * k, db + 2 * k, idesc_s, k != 0);
+    umma_commit(bar_s);
+  }
+  mbar_wait(bar_s, 0);
+  tc_fence_after();
+
+  const uint32_t t_row = tmem_base + (static_cast<uint32_t>(qt * 32) << 16);
+  const uint32_t t_s = t_row + half * 96;  // this half's three 32-column score chunks; half 1 also owns the tail [192,197)
+  constexpr float kLog2e = 1.4426950408889634f;
+  constexpr int kTail = kS - 192;  // 5 real keys in the last chunk
+
+  // ---- pass 1: maximum over this half's keys, next chunk's tcgen05.ld in flight while the current one is reduced
+  float m4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+  {
+    uint32_t r[2][32];
+    tmem_ld_32x32b_x32(t_s, r[0]);
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      tmem_ld_wait();
+      if (c + 1 < 3) tmem_ld_32x32b_x32(t_s + (c + 1) * 32, r[(c + 1) & 1]);
+#pragma unroll
+      for (int j = 0; j < 32; ++j) m4[j & 3] = fmaxf(m4[j & 3], __uint_as_float(r[c & 1][j]));
+    }
+    if (half) {
+      uint32_t tl[8];
+      tmem_ld_32x32b_x8(t_row + 192, tl);
+      tmem_ld_wait();
+#pragma unroll
+      for (int j = 0; j < kTail; ++j) m4[j & 3] = fmaxf(m4[j & 3], __uint_as_float(tl[j]));
+    }
+  }
+  float mx = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3]));
+  xmax[half * 128 + row] = mx;
+  switch (qt) {  // the two warps of this lane quarter meet on their own named barrier (immediate ids: 5 barriers per CTA, not 16)
+    case 0: named_bar_sync<1, 64>(); break;
+    case 1: named_bar_sync<2, 64>(); break;
+    case 2: named_bar_sync<3, 64>(); break;
+    default: named_bar_sync<4, 64>(); break;
+  }
+  mx = fmaxf(mx, xmax[(half ^ 1) * 128 + row]);
+  const float mxs = mx * kLog2e;
+
+  // ---- pass 2, last chunk first: exp, partial row sum, bf16 probabilities into this half's TMEM columns
+  float s4[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+  {
+    const uint32_t t_p = t_row + (half ? kT2P1 : kT2P0);
+    uint32_t r[2][32];
+    tmem_ld_32x32b_x32(t_s + 64, r[0]);
+    if (half) {  // keys [192,208): five real ones, the rest zero — P columns [200,208), over scores nobody needs
+      uint32_t tl[8];
+      tmem_ld_32x32b_x8(t_row + 192, tl);
+      tmem_ld_wait();  // (also completes the chunk load above)
+      uint32_t pk[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float e0 = (2 * j < kTail) ? fast_ex2(fmaf(__uint_as_float(tl[(2 * j) & 7]), kLog2e, -mxs)) : 0.0f;
+        const float e1 = (2 * j + 1 < kTail) ? fast_ex2(fmaf(__uint_as_float(tl[(2 * j + 1) & 7]), kLog2e, -mxs)) : 0.0f;
+        s4[j & 3] += e0 + e1;
+        pk[j] = pack_bf16x2(e0, e1);
+      }
+      tmem_st_32x32b_x8(t_row + kT2P1 + 48, pk);
+    }
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+      const int c = 2 - i;
+      tmem_ld_wait();
+      if (c > 0) tmem_ld_32x32b_x32(t_s + (c - 1) * 32, r[(i + 1) & 1]);
+      uint32_t pc[16];
+#pragma unroll
+      for (int j = 0; j < 16; ++j) {
+        const float e0 = fast_ex2(fmaf(__uint_as_float(r[i & 1][2 * j]), kLog2e, -mxs));
+        const float e1 = fast_ex2(fmaf(__uint_as_float(r[i & 1][2 * j + 1]), kLog2e, -mxs));
+        s4[j & 3] += e0 + e1;
+        pc[j] = pack_bf16x2(e0, e1);
+      }
+      // half 1: columns [152 + 16c, +16) hold scores of its chunks c.. (already in registers) or of the tail (done above)
+      tmem_st_32x32b_x16(t_p + 16 * c, pc);
+    }
+  }
+  tmem_st_wait();
+  xsum[half * 128 + row] = (s4[0] + s4[1]) + (s4[2] + s4[3]);
+  tc_fence_before();
+  __syncthreads();
+
+  // ---- O = P V  (128 x 64, K = 208 = 13 x 16): A from TMEM (k-steps 0..5 at [208,256), 6..12 at [152,208)), B = V^T in shared memory
+  if (tid == 0) {
+    mbar_wait(bar_v, 0);
+    tc_fence_after();
+    constexpr uint32_t idesc_o = umma_idesc_bf16(128, 64);
+#pragma unroll
+    for (int kk = 0; kk < 13; ++kk) {
+      const uint64_t db = umma_smem_desc_kmajor<128>(smem_u32(sV + (kk >> 2) * kVBytes)) + 2 * (kk & 3);
+      const uint32_t a_col = kk < 6 ? kT2P0 + 8 * kk : kT2P1 + 8 * (kk - 6);
+      umma_bf16_ts(tmem_base, tmem_base + a_col, db, idesc_o, kk != 0);
+    }
+    umma_commit(bar_o);
+  }
+  const float inv = 1.0f / (xsum[row] + xsum[128 + row]);  // half 0 + half 1 in both threads of the row: same bits
+  mbar_wait(bar_o, 0);
+  tc_fence_after();
+
+  // O * (1 / row sum) -> bf16 into the Q tile's shared memory (128-byte swizzle), this half's 32 of the 64 columns; one TMA store
+  {
+    uint8_t* orow = sQ + row * 128;
+    const uint32_t sw = static_cast<uint32_t>(row & 7);
+    uint32_t r[32];
+    tmem_ld_32x32b_x32(t_row + half * 32, r);
+    tmem_ld_wait();
+#pragma unroll
+    for (int g = 0; g < 4; ++g)
+      *reinterpret_cast<uint4*>(orow + ((static_cast<uint32_t>(4 * half + g) ^ sw) << 4)) =
+          make_uint4(pack_bf16x2(__uint_as_float(r[8 * g]) * inv, __uint_as_float(r[8 * g + 1]) * inv),
+                     pack_bf16x2(__uint_as_float(r[8 * g + 2]) * inv, __uint_as_float(r[8 * g + 3]) * inv),
+                     pack_bf16x2(__uint_as_float(r[8 * g + 4]) * inv, __uint_as_float(r[8 * g + 5]) * inv),
+                     pack_bf16x2(__uint_as_float(r[8 * g + 6]) * inv, __uint_as_float(r[8 * g + 7]) * inv));
+    fence_proxy_async_smem();
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (tid == 0) {
+    tma_store_4d(&p.tmO, sQ, 0, hd, mt * 128, b);
+    bulk_commit();
+    bulk_wait_exit<0>();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  if (warp == 0) tmem_dealloc(tmem_base, kTpTmemCols);
 }
 
 // ------------------------------------------------------------------ ViT attention, persistent and pipelined
@@ -798,6 +997,8 @@ extern "C" int mde_vit_attention(const mde_bf16* q, const mde_bf16* k, const mde
     MDE_CHECK_CUDA(cudaFuncSetAttribute(vit_attn_tp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kTpSmem));
     MDE_CHECK_CUDA(cudaFuncSetAttribute(vit_attn_tp_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
     MDE_CHECK_CUDA(cudaFuncSetAttribute(vit_attn_ps_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kPsSmem));
+    MDE_CHECK_CUDA(cudaFuncSetAttribute(vit_attn_tp2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kT2Smem));
+    MDE_CHECK_CUDA(cudaFuncSetAttribute(vit_attn_tp2_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
     attr_set = true;
   }
   // MDE_ATTN_SMEM_P=1 selects the shared-memory-P kernel (A/B testing); default: probabilities in TMEM, 2 CTAs per SM
@@ -805,7 +1006,10 @@ extern "C" int mde_vit_attention(const mde_bf16* q, const mde_bf16* k, const mde
   // MDE_ATTN=ps selects the persistent kernel (K/V loaded once for both query tiles; A/B testing: 19.7 us against 18.1 us
   // at B=32, its 384 (image, head) pairs are 2.6 waves of 148 CTAs); default: one query tile per CTA, 2 CTAs per SM
   static const bool persistent = getenv("MDE_ATTN") != nullptr && strcmp(getenv("MDE_ATTN"), "ps") == 0;
+  // MDE_ATTN_TP2=1 selects the two-threads-per-row kernel (A/B testing: 2.0990 ms per step against 2.0919 with one thread per row)
+  static const bool two_per_row = getenv("MDE_ATTN_TP2") != nullptr && getenv("MDE_ATTN_TP2")[0] == '1';
   if (smem_p) launch_k(vit_attn_kernel, dim3((unsigned)slabs), dim3(256), kAttnSmem, stream, p);
+  else if (!persistent && two_per_row) launch_k(vit_attn_tp2_kernel, dim3((unsigned)(2 * slabs)), dim3(256), kT2Smem, stream, p);
   else if (!persistent) launch_k(vit_attn_tp_kernel, dim3((unsigned)(2 * slabs)), dim3(128), kTpSmem, stream, p);
   else launch_k(vit_attn_ps_kernel, dim3((unsigned)(slabs < (uint64_t)sm_count() ? slabs : (uint64_t)sm_count())), dim3(320), kPsSmem, stream, p);
   MDE_CHECK_LAUNCH();

@@ -120,6 +120,16 @@ template <int N>
 __device__ __forceinline__ void bulk_wait_all() {
   asm volatile("cp.async.bulk.wait_group %0;" ::"n"(N) : "memory");
 }
+// Last wait of a CTA that has bulk stores in flight: they must have READ shared memory before the CTA gives it up; the writes
+// themselves are performed by the time the grid completes (what the next kernel's griddepcontrol.wait / stream order waits for).
+template <int N>
+__device__ __forceinline__ void bulk_wait_exit() {
+#ifdef MDE_EXIT_WAIT_ALL
+  bulk_wait_all<N>();
+#else
+  bulk_wait_read<N>();
+#endif
+}
 
 // ----------------------------------------------------------------------------- tcgen05
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
@@ -171,6 +181,15 @@ __device__ __forceinline__ void tmem_ld_32x32b_x16(uint32_t taddr, uint32_t (&r)
       : "r"(taddr)
       : "memory");
 }
+__device__ __forceinline__ void tmem_ld_32x32b_x8(uint32_t taddr, uint32_t (&r)[8]) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+               : "r"(taddr)
+               : "memory");
+}
+// bar.sync on a named barrier: `threads` (a multiple of 32) threads of the CTA meet on barrier `id` (1..15; 0 is __syncthreads)
+template <int ID, int THREADS>
+__device__ __forceinline__ void named_bar_sync() { asm volatile("bar.sync %0, %1;" ::"n"(ID), "n"(THREADS) : "memory"); }
 // registers -> TMEM, 32 lanes x 32 bit, x16 / x8 columns (thread i writes lane i of the warp's lane quarter)
 __device__ __forceinline__ void tmem_st_32x32b_x16(uint32_t taddr, const uint32_t (&r)[16]) {
   asm volatile("tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};"

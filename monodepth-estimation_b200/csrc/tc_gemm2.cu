@@ -586,7 +586,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(k2Threads, 1) tc_gem
         i = inext;
         it = itn;
       }
-      if (lane == 0) bulk_wait_all<0>();  // every store has left shared memory and is globally performed
+      if (lane == 0) bulk_wait_exit<0>();  // every store has left shared memory
       __syncwarp();
     } else {
       for (int i = cluster_id; i < p.total_items; i += num_clusters) {
