@@ -161,5 +161,11 @@ def check(status: int, what: str = ""):
         raise MdeError(f"{what} failed with status {status}: {msg.decode() if msg else '?'}")
 
 
+# Number of compute entry points called so far (every ``call`` launches at least one kernel of libmde.so): callers take
+# differences around a region — e.g. the trainer around its graph capture — to report how many launches a step replays.
+N_CALLS = [0]
+
+
 def call(name: str, *args):
+    N_CALLS[0] += 1
     check(getattr(load(), name)(*args), name)

@@ -384,6 +384,7 @@ class DepthTrainer:
     def __init__(self, model, lr=1e-4, w_depth=1.0, w_smooth=0.001, betas=(0.9, 0.999), eps=1e-8, graph=True, full_decoder=True):
         self.model, self.lr, self.w_depth, self.w_smooth, self.betas, self.eps = model, lr, w_depth, w_smooth, betas, eps
         self.graph, self._graphs = graph, {}
+        self.launches_per_step = 0  # set when the step's graphs are captured
         # ViT blocks after which a data-parallel step starts reducing what it has (see step()); MDE_TRAIN_SPLITS="9,6,3" overrides
         import os
         env = os.environ.get("MDE_TRAIN_SPLITS")
@@ -591,6 +592,7 @@ class DepthTrainer:
             st["rnd"].copy_(rnd)
             torch.cuda.synchronize(self.dev)
             splits = tuple(self.splits) if grads_hook is not None else ()
+            calls0 = L.N_CALLS[0]
             gen = self._stages(st["x"], metadata, st["rnd"], splits)
             st["fb"], st["parts"], pool = [], [], None
             for _ in range(len(splits) + 1):
@@ -607,6 +609,8 @@ class DepthTrainer:
             with torch.cuda.graph(st["adam"]):
                 self._adam(st["grads"], st["adam_plan"])
             st["side"] = torch.cuda.Stream(self.dev) if len(st["fb"]) > 1 else None
+            # library entry points captured into the step's graphs (each launches >= 1 kernel): what one replayed step launches
+            self.launches_per_step = L.N_CALLS[0] - calls0
         else:
             st["x"].copy_(images)
             st["rnd"].copy_(rnd)
