@@ -322,11 +322,18 @@ template <int DIM, int R>
 __global__ void __launch_bounds__(256, R == 1 ? 4 : 3) layernorm_kernel(const float* __restrict__ x, int rows, const float* __restrict__ gamma,
                                                         const float* __restrict__ beta, float eps, bf16* __restrict__ out) {
   pdl_launch_dependents();
-  pdl_grid_wait();
   constexpr int PER = DIM / 256;  // 8-element groups per lane
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int row0 = (blockIdx.x * 8 + warp) * R;
-  if (row0 >= rows) return;
+  // gamma / beta are parameters, not written by the previous kernel: they go to shared memory while this kernel still waits for it
+  // (read straight from global memory after the reductions, their L2 round trip sat on every block's critical path)
+  __shared__ float4 s_gb[2][DIM / 4];
+  if (threadIdx.x < DIM / 4) {
+    s_gb[0][threadIdx.x] = __ldg(reinterpret_cast<const float4*>(gamma) + threadIdx.x);
+    s_gb[1][threadIdx.x] = __ldg(reinterpret_cast<const float4*>(beta) + threadIdx.x);
+  }
+  pdl_grid_wait();
+  const int row0 = min((blockIdx.x * 8 + warp) * R, rows - 1);  // a warp past the end computes the last row again and stores nothing
+  const bool live0 = (blockIdx.x * 8 + warp) * R < rows;
   float v[R][PER * 8];
   float s[R];
 #pragma unroll
@@ -363,15 +370,14 @@ __global__ void __launch_bounds__(256, R == 1 ? 4 : 3) layernorm_kernel(const fl
   }
 #pragma unroll
   for (int r = 0; r < R; ++r) rstd[r] = 1.0f / sqrtf(warp_sum(s[r]) * (1.0f / DIM) + eps);
-  const float4* g4 = reinterpret_cast<const float4*>(gamma);
-  const float4* b4 = reinterpret_cast<const float4*>(beta);
+  __syncthreads();  // s_gb is complete (its loads were issued before everything else)
 #pragma unroll
   for (int j = 0; j < PER; ++j) {
     const int g = (j * 32 + lane) * 2;
-    const float4 ga = __ldg(g4 + g), gb = __ldg(g4 + g + 1), ba = __ldg(b4 + g), bb = __ldg(b4 + g + 1);
+    const float4 ga = s_gb[0][g], gb = s_gb[0][g + 1], ba = s_gb[1][g], bb = s_gb[1][g + 1];
 #pragma unroll
     for (int r = 0; r < R; ++r) {
-      if (row0 + r >= rows) break;
+      if (!live0 || row0 + r >= rows) break;
       const float m = mean[r], t = rstd[r];
       const float y0 = (v[r][8 * j + 0] - m) * t * ga.x + ba.x, y1 = (v[r][8 * j + 1] - m) * t * ga.y + ba.y;
       const float y2 = (v[r][8 * j + 2] - m) * t * ga.z + ba.z, y3 = (v[r][8 * j + 3] - m) * t * ga.w + ba.w;

@@ -1,14 +1,6 @@
 cd $GRAFT_REPO_ROOT
-mkdir -p gpurun_out/r02j
-timeout 1500 python -m pytest tests -x -q -m gpu 2>&1 | tail -3 | tee gpurun_out/r02j/pytest_gpu.txt
-timeout 600 python bench.py > gpurun_out/r02j/bench.json 2> gpurun_out/r02j/bench_err.txt; echo "bench rc=$?"
-timeout 300 python bench.py --model enhanced --no-extras > gpurun_out/r02j/enhanced.json 2>> gpurun_out/r02j/bench_err.txt
-timeout 300 python bench.py --model config4 --no-extras > gpurun_out/r02j/config4_b16.json 2>> gpurun_out/r02j/bench_err.txt
-timeout 300 python bench.py --model train --no-extras > gpurun_out/r02j/train.json 2>> gpurun_out/r02j/bench_err.txt
-timeout 300 python bench.py --batch 4 --no-extras > gpurun_out/r02j/standard_b4.json 2>> gpurun_out/r02j/bench_err.txt
-python -c "
-import json
-for f in ('bench','enhanced','config4_b16','train','standard_b4'):
-    d=json.load(open('gpurun_out/r02j/%s.json'%f)); print(f, d['value'], d['ms_per_step'], d.get('gpu_launches'), (d.get('e2e') or {}).get('value'))
-"
-timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none --launch-skip 300 -c 400 --csv --log-file gpurun_out/r02j/launches.csv python bench.py --no-extras --steps 2 --warmup 3 > gpurun_out/r02j/ncu_stdout.txt 2>&1; echo "ncu rc=$?"
+timeout 600 python -m pytest tests/test_kernels_gpu.py -x -q -m gpu -k "layernorm or vit" 2>&1 | tail -1
+for i in 1 2; do
+timeout 300 python bench.py --no-extras --steps 30 --warmup 5 2>> gpurun_out/c75_err.txt | python -c "import json,sys; d=json.loads(sys.stdin.read()); print('LN prefetch', d['value'], d['ms_per_step'])"
+MDE_LIB_PATH=tools/_libmde_base2.so timeout 300 python bench.py --no-extras --steps 30 --warmup 5 2>> gpurun_out/c75_err.txt | python -c "import json,sys; d=json.loads(sys.stdin.read()); print('before', d['value'], d['ms_per_step'])"
+done
