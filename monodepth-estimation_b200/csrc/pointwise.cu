@@ -327,9 +327,10 @@ __global__ void __launch_bounds__(256, R == 1 ? 4 : 3) layernorm_kernel(const fl
   // gamma / beta are parameters, not written by the previous kernel: they go to shared memory while this kernel still waits for it
   // (read straight from global memory after the reductions, their L2 round trip sat on every block's critical path)
   __shared__ float4 s_gb[2][DIM / 4];
-  if (threadIdx.x < DIM / 4) {
-    s_gb[0][threadIdx.x] = __ldg(reinterpret_cast<const float4*>(gamma) + threadIdx.x);
-    s_gb[1][threadIdx.x] = __ldg(reinterpret_cast<const float4*>(beta) + threadIdx.x);
+  float4 pg = make_float4(0.0f, 0.0f, 0.0f, 0.0f), pb = pg;
+  if (threadIdx.x < DIM / 4) {  // in flight across the wait and the row loads; stored to shared memory once those are issued
+    pg = ld_param_now_f4(reinterpret_cast<const float4*>(gamma) + threadIdx.x);
+    pb = ld_param_now_f4(reinterpret_cast<const float4*>(beta) + threadIdx.x);
   }
   pdl_grid_wait();
   const int row0 = min((blockIdx.x * 8 + warp) * R, rows - 1);  // a warp past the end computes the last row again and stores nothing
@@ -342,10 +343,14 @@ __global__ void __launch_bounds__(256, R == 1 ? 4 : 3) layernorm_kernel(const fl
     const float4* xr = reinterpret_cast<const float4*>(x + (size_t)row * DIM);
 #pragma unroll
     for (int j = 0; j < PER; ++j) {
-      const float4 a = __ldg(xr + (j * 32 + lane) * 2), b = __ldg(xr + (j * 32 + lane) * 2 + 1);
+      const float4 a = ld_after_wait_f4(xr + (j * 32 + lane) * 2), b = ld_after_wait_f4(xr + (j * 32 + lane) * 2 + 1);  // not __ldg: see ptx.cuh
       v[r][8 * j + 0] = a.x; v[r][8 * j + 1] = a.y; v[r][8 * j + 2] = a.z; v[r][8 * j + 3] = a.w;
       v[r][8 * j + 4] = b.x; v[r][8 * j + 5] = b.y; v[r][8 * j + 6] = b.z; v[r][8 * j + 7] = b.w;
     }
+  }
+  if (threadIdx.x < DIM / 4) {
+    s_gb[0][threadIdx.x] = pg;
+    s_gb[1][threadIdx.x] = pb;
   }
 #pragma unroll
   for (int r = 0; r < R; ++r) {

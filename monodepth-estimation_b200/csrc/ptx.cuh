@@ -74,6 +74,21 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
 // or still reads.  pdl_launch_dependents() lets the NEXT kernel do the same; both are no-ops without the attribute.
 __device__ __forceinline__ void pdl_grid_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+// A load of data the PREVIOUS kernel produced, in a kernel that does work before pdl_grid_wait(): `__ldg` / const __restrict__ loads
+// are "read-only for the kernel's lifetime" to the compiler, which then schedules them ABOVE the wait (seen in SASS: LDG.CONSTANT
+// before ACQBULK, wrong results under PDL).  A volatile asm load keeps its place relative to the (volatile) wait.
+// A parameter load that must be ISSUED where it is written (before the wait): ptxas sinks plain and .nc loads below the wait (or
+// anywhere else it likes); a volatile load (LDG.STRONG.SYS, served by L2) stays put.
+__device__ __forceinline__ float4 ld_param_now_f4(const float4* p) {
+  float4 v;
+  asm volatile("ld.volatile.global.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ float4 ld_after_wait_f4(const float4* p) {
+  float4 v;
+  asm volatile("ld.global.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+  return v;
+}
 
 // ----------------------------------------------------------------------------- TMA
 __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* m) {
