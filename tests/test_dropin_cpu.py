@@ -113,3 +113,50 @@ def test_stale_library_is_not_silently_reused(monkeypatch):
         _lib.load()
     monkeypatch.setattr(B, "is_stale", lambda: False)  # binary matches the sources (e.g. a box without nvcc): fine
     assert _lib.load().mde_version() >= 100
+
+
+def test_no_load_of_predecessor_data_is_scheduled_above_the_pdl_wait():
+    """Every kernel runs under programmatic dependent launch: whatever it reads of its predecessor's output must come after
+    griddepcontrol.wait (SASS: ACQBULK).  The compiler is free to move `__ldg` / const __restrict__ loads above that instruction —
+    it did, in the LayerNorm kernel, once code was placed before the wait (wrong activations under PDL, correct in isolation) — so
+    the built library is checked: before ACQBULK a kernel may only touch shared memory (generic LD.E / ATOMS / SYNCS), issue the
+    volatile parameter loads of ptx.cuh's ld_param_now_f4 (LDG...STRONG.SYS), or be a kernel known to pre-load weights there."""
+    import shutil
+    import subprocess
+
+    from monodepth_estimation_b200 import _lib as L
+
+    cuobjdump = shutil.which("cuobjdump") or "/usr/local/cuda/bin/cuobjdump"
+    if not os.path.exists(cuobjdump):
+        pytest.skip("cuobjdump not available")
+    L.load()
+    sass = subprocess.run([cuobjdump, "-sass", L.SO_PATH], capture_output=True, text=True, check=True).stdout
+    weights_before_wait = ("decoder_tail_kernel",)  # stages its three layers' weights in shared memory before the wait, by design
+    offenders, kernels, fn, waited = [], 0, None, False
+    for line in sass.splitlines():
+        m = re.search(r"Function : (\S+)", line)
+        if m:
+            fn, waited = m.group(1), False
+            continue
+        m = re.match(r"\s+/\*([0-9a-f]{4,5})\*/\s+(.*?);", line)
+        if not m or fn is None:
+            continue
+        ins = m.group(2)
+        if "ACQBULK" in ins:
+            waited, kernels = True, kernels + 1
+        elif not waited and re.sub(r"^@!?U?P\d+\s+", "", ins).split()[0].split(".")[0] in ("LDG", "STG", "RED", "ATOM", "ATOMG", "UTMALDG", "UBLKCP"):
+            if "STRONG.SYS" in ins or any(k in fn for k in weights_before_wait):
+                continue
+            offenders.append((fn, m.group(1), ins.strip()))
+    # kernels without ACQBULK never reach `waited`; their instructions are not "before the wait", so drop them
+    with_wait = set()
+    fn = None
+    for line in sass.splitlines():
+        m = re.search(r"Function : (\S+)", line)
+        if m:
+            fn = m.group(1)
+        elif "ACQBULK" in line and fn:
+            with_wait.add(fn)
+    offenders = [o for o in offenders if o[0] in with_wait]
+    assert kernels >= 60, kernels  # the library's kernels do carry the wait (guards against a silent change of the mnemonic)
+    assert not offenders, offenders[:8]
