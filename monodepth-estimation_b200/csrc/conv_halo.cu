@@ -108,13 +108,17 @@ __global__ void __launch_bounds__(halo_threads(BLOCK_N), BLOCK_N <= 16 ? 3 : BLO
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  // The 3x3 weight set is a parameter, not the previous kernel's output: it is requested BEFORE the grid-dependency wait, so a CTA
+  // that became resident while the previous kernel drains has its weights in shared memory when the wait ends.
+  if (warp == 0 && elect_one()) {
+    mbar_expect_tx(w_bar, (uint32_t)(wtiles * WB_RAW));
+    for (int t = 0; t < wtiles; ++t) tma_load_2d(sW + (size_t)t * WB, &p.tmB, w_bar, t * KC, 0);
+  }
   pdl_grid_wait();  // the set-up above overlaps the previous kernel's tail
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
     if (elect_one()) {
-      mbar_expect_tx(w_bar, (uint32_t)(wtiles * WB_RAW));
-      for (int t = 0; t < wtiles; ++t) tma_load_2d(sW + (size_t)t * WB, &p.tmB, w_bar, t * KC, 0);
       int stage = 0;
       uint32_t phase = 0;
       for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
