@@ -96,28 +96,45 @@ __global__ void __launch_bounds__(256) minmax_kernel(const float4* __restrict__ 
 __global__ void __launch_bounds__(768) range_finalize_kernel(const float* __restrict__ partials, int nparts, const float* __restrict__ bn, float eps,
                                       float* __restrict__ affine6) {
   pdl_launch_dependents();
+  // One block on the critical path of every forward (input scan -> this -> patchify): the BatchNorm parameters are requested before
+  // the wait, every thread keeps 8 partials in flight (a single block cannot hide the L2 latency of a one-load-at-a-time loop: 56
+  // round trips before), and the 128 threads of a statistic are combined by shuffles + ONE block-wide sync (the shared-memory tree
+  // took eight).  min / max are order-independent: the result is bit-identical.
+  __shared__ float s_bn[12];
+  __shared__ float s_w[24];
+  float bnv = 0.0f;
+  if (threadIdx.x < 12) bnv = ld_param_now_f32(bn + threadIdx.x);
   pdl_grid_wait();
-  // 768 threads (a multiple of 6): thread t reads floats t, t+768, ... (coalesced, all of statistic t % 6), then a
-  // shared-memory tree whose strides stay multiples of 6
-  __shared__ float st[768];
   {
-    const int k = threadIdx.x % 6;
-    float r = k < 3 ? FLT_MAX : -FLT_MAX;
-    for (int i = threadIdx.x; i < nparts * 6; i += 768) {
-      const float v = partials[i];
-      r = k < 3 ? fminf(r, v) : fmaxf(r, v);
-    }
-    st[threadIdx.x] = r;
-    for (int s = 384; s >= 6; s >>= 1) {
-      __syncthreads();
-      if ((int)threadIdx.x < s) {
-        const float u = st[threadIdx.x], v = st[threadIdx.x + s];
-        st[threadIdx.x] = k < 3 ? fminf(u, v) : fmaxf(u, v);
+    const int k = threadIdx.x >> 7, j0 = threadIdx.x & 127;  // statistic (0..2 minima, 3..5 maxima), first partial
+    const bool is_min = k < 3;
+    float r = is_min ? FLT_MAX : -FLT_MAX;
+    for (int j = j0; j < nparts; j += 128 * 8) {
+      float v[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int jj = j + 128 * u;
+        v[u] = jj < nparts ? ld_after_wait_f32(partials + (size_t)jj * 6 + k) : r;  // not a read-only load: see ptx.cuh
       }
+#pragma unroll
+      for (int u = 0; u < 8; ++u) r = is_min ? fminf(r, v[u]) : fmaxf(r, v[u]);
     }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const float t = __shfl_xor_sync(0xffffffffu, r, o);
+      r = is_min ? fminf(r, t) : fmaxf(r, t);
+    }
+    if ((threadIdx.x & 31) == 0) s_w[threadIdx.x >> 5] = r;  // warps 4k .. 4k+3 hold statistic k
+    if (threadIdx.x < 12) s_bn[threadIdx.x] = bnv;
   }
   __syncthreads();
   if (threadIdx.x == 0) {
+    float st[6];
+    for (int k = 0; k < 6; ++k) {
+      const float u0 = s_w[4 * k], u1 = s_w[4 * k + 1], u2 = s_w[4 * k + 2], u3 = s_w[4 * k + 3];
+      st[k] = k < 3 ? fminf(fminf(u0, u1), fminf(u2, u3)) : fmaxf(fmaxf(u0, u1), fmaxf(u2, u3));
+    }
+    const float* bn = s_bn;
     float a[3], b[3], gmin = FLT_MAX, gmax = -FLT_MAX;
     for (int c = 0; c < 3; ++c) {
       const float w = bn[c], bias = bn[3 + c], mean = bn[6 + c], var = bn[9 + c];
