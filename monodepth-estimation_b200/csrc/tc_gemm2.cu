@@ -127,7 +127,9 @@ __device__ __forceinline__ void lane_bias64(const float* bias, int n0, int par, 
 // LNF = 1 adds the LayerNorm-fusion code (producer: bf16 copy + row sums, consumer: normalising epilogue); the default
 // instantiation carries none of it (the extra registers / instructions cost ~0.6 us per launch even when never executed).
 // EC = epilogue class: 0 fp32 through TMA (bias / bias + residual), 1 bf16 through TMA (bias / GELU / QKV split), 2 direct stores
-// (patch embed): each instantiation carries only its own epilogue code.
+// (patch embed with the LayerNorm-fusion producer), 3 patch embed through TMA (fp32 + position embedding, token rows b*197 + 1 + patch
+// addressed through a 3-D tensor map whose bounds clip a 32-row chunk at the image boundary): each instantiation carries only its own
+// epilogue code.
 template <int LNF, int EC>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(k2Threads, 1) tc_gemm2_kernel(const __grid_constant__ Tc2Params p) {
   pdl_launch_dependents();
@@ -258,7 +260,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(k2Threads, 1) tc_gem
       uint8_t* stg = staging + ew * 2 * k2EpiBufBytes;
       uint64_t* rbar = res_bar + ew * 4;
       const bool resid = EC == 0 && p.epi == MDE_EPI_BIAS_RESID_F32;
-      constexpr bool f32out = EC == 0;
+      constexpr bool f32out = EC == 0 || EC == 3;
       const int cw = f32out ? 32 : 64;  // columns per 128-byte chunk
       const uint32_t sw = static_cast<uint32_t>(lane & 7);
       uint32_t g = 0;   // output chunks this warp has staged: staging buffer = g & 1
@@ -371,6 +373,14 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(k2Threads, 1) tc_gem
         const Item itn = decode_item(p, has_next ? inext : i);
         const int nch = it.bn / cw;
         const int row0 = it.m0 + (int)rank * 128 + q * 32;
+        [[maybe_unused]] const float4* pe_row = nullptr;  // EC == 3: this thread's position-embedding row
+        [[maybe_unused]] int pe_patch = -1, pe_img = 0;
+        if constexpr (EC == 3) {
+          const int m = min(row0 + lane, p.M - 1);  // rows past M are computed on a clamped row and clipped by the store
+          pe_img = m / 196;
+          pe_patch = row0 + lane < p.M ? m - pe_img * 196 : -1;
+          pe_row = reinterpret_cast<const float4*>(reinterpret_cast<const float*>(p.aux0) + (size_t)(1 + m - pe_img * 196) * MDE_VIT_DIM);
+        }
         // LayerNorm of this thread's A row from the producer's partial sums.  Slot layout per 256-column producer tile: a whole
         // tile leaves two partials (epilogue-warp parity 0 / 1 = even / odd 32-column chunks, each summed chunk by chunk), a
         // tile of the split tail leaves one partial per chunk (slot = chunk).  Both are combined in the SAME order here —
@@ -450,6 +460,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(k2Threads, 1) tc_gem
                 o.y += __shfl_sync(0xffffffffu, bsel, 4 * j + 1);
                 o.z += __shfl_sync(0xffffffffu, bsel, 4 * j + 2);
                 o.w += __shfl_sync(0xffffffffu, bsel, 4 * j + 3);
+              }
+              if constexpr (EC == 3) {  // + pos_embedding[1 + patch] (tv:156); a parameter, 128 contiguous bytes per row and chunk
+                const float4 q4 = __ldg(pe_row + (n0 >> 2) + j);
+                o.x += q4.x; o.y += q4.y; o.z += q4.z; o.w += q4.w;
               }
               *sp = o;
               if constexpr (LNF) {
@@ -540,6 +554,27 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(k2Threads, 1) tc_gem
           }
           fence_proxy_async_smem();  // generic-proxy writes -> visible to the TMA engine
           __syncwarp();
+          if constexpr (EC == 3) {
+            if (lane == 0) {
+              // token rows of image b start at patch 0 -> coordinate 0 of a map over tokens 1..196: a chunk that crosses into the next
+              // image is stored twice, each store clipped by the map's bounds to its own image's rows
+              const int b0 = row0 / 196, t0 = row0 - b0 * 196;
+              tma_store_3d(&p.tmOut, buf, n0, t0, b0);
+              if (t0 + 32 > 196) tma_store_3d(&p.tmOut, buf, n0, t0 - 196, b0 + 1);
+              bulk_commit();
+            }
+            if (pe_patch == 0) {  // the image's CLS row = class_token + pos_embedding[0] (tv:287-289), these 32 columns
+              const float4* cls = reinterpret_cast<const float4*>(reinterpret_cast<const float*>(p.aux1) + n0);
+              const float4* p0 = reinterpret_cast<const float4*>(reinterpret_cast<const float*>(p.aux0) + n0);
+              float4* d0 = reinterpret_cast<float4*>(reinterpret_cast<float*>(p.out) + (size_t)pe_img * MDE_VIT_SEQ * MDE_VIT_DIM + n0);
+#pragma unroll
+              for (int j = 0; j < 8; ++j) {
+                const float4 c4 = __ldg(cls + j), q4 = __ldg(p0 + j);
+                d0[j] = make_float4(c4.x + q4.x, c4.y + q4.y, c4.z + q4.z, c4.w + q4.w);
+              }
+            }
+            continue;
+          }
           if (lane == 0) {
             if (p.epi == MDE_EPI_QKV_SPLIT) {  // q -> tmOut, k -> tmRes, both token-major [B*197][768]
               const int which = n0 / MDE_VIT_DIM;
@@ -694,6 +729,19 @@ int launch_gemm_pair(const void* A, int lda, const void* W, int ldw, int M, int 
   p.aux1 = aux1;
   p.tma_epi = epilogue <= MDE_EPI_BIAS_F32 || epilogue == MDE_EPI_QKV_SPLIT;
   p.out_elt = (epilogue == MDE_EPI_BIAS_RESID_F32 || epilogue == MDE_EPI_BIAS_F32) ? 4 : 2;
+  static const bool pe_direct = getenv("MDE_PATCH_EMBED_DIRECT") != nullptr && getenv("MDE_PATCH_EMBED_DIRECT")[0] == '1';  // A/B timing
+  const bool pe_tma = epilogue == MDE_EPI_PATCH_EMBED && !p.xb && !p.ln_in && !pe_direct && M % 196 == 0 && ldo == MDE_VIT_DIM && N == MDE_VIT_DIM &&
+                      (uintptr_t)out % 16 == 0 && (uintptr_t)aux0 % 16 == 0 && (uintptr_t)aux1 % 16 == 0;
+  if (pe_tma) {
+    // tokens 1..196 of every image: [768 columns][196 patches][B images], image pitch 197 rows — rows that do not exist are clipped
+    const uint64_t dims[3] = {(uint64_t)MDE_VIT_DIM, 196, (uint64_t)(M / 196)};
+    const uint64_t strides[2] = {(uint64_t)MDE_VIT_DIM * 4, (uint64_t)MDE_VIT_SEQ * MDE_VIT_DIM * 4};
+    const uint32_t box[3] = {32, 32, 1};
+    int rc = encode_tmap(&p.tmOut, 4, reinterpret_cast<const float*>(out) + MDE_VIT_DIM, 3, dims, strides, box, 128);
+    if (rc != MDE_OK) return rc;
+    p.tmRes = p.tmOut;  // unused, but prefetched
+    p.out_elt = 4;
+  }
   if (p.tma_epi) {
     const bool qkv = epilogue == MDE_EPI_QKV_SPLIT;
     const int out_cols = qkv ? MDE_VIT_DIM : N, out_ld = qkv ? MDE_VIT_DIM : ldo;
@@ -721,16 +769,16 @@ int launch_gemm_pair(const void* A, int lda, const void* W, int ldw, int M, int 
   static bool attr_set = false;
   if (!attr_set) {
 #define MDE_G2_ATTR(L_, E_) MDE_CHECK_CUDA(cudaFuncSetAttribute(tc_gemm2_kernel<L_, E_>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
-    MDE_G2_ATTR(0, 0) MDE_G2_ATTR(0, 1) MDE_G2_ATTR(0, 2) MDE_G2_ATTR(1, 0) MDE_G2_ATTR(1, 1) MDE_G2_ATTR(1, 2)
+    MDE_G2_ATTR(0, 0) MDE_G2_ATTR(0, 1) MDE_G2_ATTR(0, 2) MDE_G2_ATTR(0, 3) MDE_G2_ATTR(1, 0) MDE_G2_ATTR(1, 1) MDE_G2_ATTR(1, 2)
 #undef MDE_G2_ATTR
     attr_set = true;
   }
   const int grid = 2 * std::min(clusters, p.total_items);
-  const int ec = !p.tma_epi ? 2 : (p.out_elt == 4 ? 0 : 1);
+  const int ec = pe_tma ? 3 : (!p.tma_epi ? 2 : (p.out_elt == 4 ? 0 : 1));
   const int lnf = (p.xb || p.ln_in) ? 1 : 0;
 #define MDE_G2_CASE(L_, E_) \
   if (lnf == L_ && ec == E_) launch_k(tc_gemm2_kernel<L_, E_>, dim3(grid), dim3(k2Threads), smem_bytes, stream, p);
-  MDE_G2_CASE(0, 0) MDE_G2_CASE(0, 1) MDE_G2_CASE(0, 2) MDE_G2_CASE(1, 0) MDE_G2_CASE(1, 1) MDE_G2_CASE(1, 2)
+  MDE_G2_CASE(0, 0) MDE_G2_CASE(0, 1) MDE_G2_CASE(0, 2) MDE_G2_CASE(0, 3) MDE_G2_CASE(1, 0) MDE_G2_CASE(1, 1) MDE_G2_CASE(1, 2)
 #undef MDE_G2_CASE
   MDE_CHECK_LAUNCH();
   return MDE_OK;
