@@ -128,7 +128,7 @@ __device__ __forceinline__ void lane_bias64(const float* bias, int n0, int par, 
 // instantiation carries none of it (the extra registers / instructions cost ~0.6 us per launch even when never executed).
 // EC = epilogue class: 0 fp32 through TMA (bias / bias + residual), 1 bf16 through TMA (bias / GELU / QKV split), 2 direct stores
 // (patch embed with the LayerNorm-fusion producer), 3 patch embed through TMA (fp32 + position embedding, token rows b*197 + 1 + patch
-// addressed through a 3-D tensor map whose bounds clip a 32-row chunk at the image boundary): each instantiation carries only its own
+// addressed through a 3-D tensor map whose bounds clip a 32-row chunk at the end of its image): each instantiation carries only its own
 // epilogue code.
 template <int LNF, int EC>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(k2Threads, 1) tc_gemm2_kernel(const __grid_constant__ Tc2Params p) {
@@ -559,8 +559,11 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(k2Threads, 1) tc_gem
               // token rows of image b start at patch 0 -> coordinate 0 of a map over tokens 1..196: a chunk that crosses into the next
               // image is stored twice, each store clipped by the map's bounds to its own image's rows
               const int b0 = row0 / 196, t0 = row0 - b0 * 196;
-              tma_store_3d(&p.tmOut, buf, n0, t0, b0);
-              if (t0 + 32 > 196) tma_store_3d(&p.tmOut, buf, n0, t0 - 196, b0 + 1);
+              tma_store_3d(&p.tmOut, buf, n0, t0, b0);  // rows past patch 195 of image b0 are clipped by the map
+              // the rest of a chunk that crosses into image b0 + 1 (a multiple of 4 rows, 196 = 4 x 49): 4-row boxes from the matching
+              // rows of the staging buffer (tmRes = the same tensor with a {32, 4, 1} box).  A single store at the negative row
+              // coordinate t0 - 196 would be the obvious way — it raises "illegal instruction" (measured; bring-up notes in r02_experiments.md)
+              for (int r = 196 - t0; r < 32; r += 4) tma_store_3d(&p.tmRes, buf + r * 128, n0, r - (196 - t0), b0 + 1);
               bulk_commit();
             }
             if (pe_patch == 0) {  // the image's CLS row = class_token + pos_embedding[0] (tv:287-289), these 32 columns
@@ -730,7 +733,7 @@ int launch_gemm_pair(const void* A, int lda, const void* W, int ldw, int M, int 
   p.tma_epi = epilogue <= MDE_EPI_BIAS_F32 || epilogue == MDE_EPI_QKV_SPLIT;
   p.out_elt = (epilogue == MDE_EPI_BIAS_RESID_F32 || epilogue == MDE_EPI_BIAS_F32) ? 4 : 2;
   static const bool pe_direct = getenv("MDE_PATCH_EMBED_DIRECT") != nullptr && getenv("MDE_PATCH_EMBED_DIRECT")[0] == '1';  // A/B timing
-  const bool pe_tma = epilogue == MDE_EPI_PATCH_EMBED && !p.xb && !p.ln_in && !pe_direct && M % 196 == 0 && ldo == MDE_VIT_DIM && N == MDE_VIT_DIM &&
+  const bool pe_tma = epilogue == MDE_EPI_PATCH_EMBED && !p.xb && !p.ln_in && !pe_direct && M % 196 == 0 && N == MDE_VIT_DIM &&  // (the output pitch of this epilogue is MDE_VIT_DIM by definition: ldo is not used)
                       (uintptr_t)out % 16 == 0 && (uintptr_t)aux0 % 16 == 0 && (uintptr_t)aux1 % 16 == 0;
   if (pe_tma) {
     // tokens 1..196 of every image: [768 columns][196 patches][B images], image pitch 197 rows — rows that do not exist are clipped
@@ -739,7 +742,9 @@ int launch_gemm_pair(const void* A, int lda, const void* W, int ldw, int M, int 
     const uint32_t box[3] = {32, 32, 1};
     int rc = encode_tmap(&p.tmOut, 4, reinterpret_cast<const float*>(out) + MDE_VIT_DIM, 3, dims, strides, box, 128);
     if (rc != MDE_OK) return rc;
-    p.tmRes = p.tmOut;  // unused, but prefetched
+    const uint32_t box4[3] = {32, 4, 1};  // the part of a chunk that belongs to the NEXT image goes out in 4-row pieces
+    rc = encode_tmap(&p.tmRes, 4, reinterpret_cast<const float*>(out) + MDE_VIT_DIM, 3, dims, strides, box4, 128);
+    if (rc != MDE_OK) return rc;
     p.out_elt = 4;
   }
   if (p.tma_epi) {

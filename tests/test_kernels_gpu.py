@@ -211,16 +211,18 @@ def test_gemm_residual_f32_and_row_tail():
     assert float((out[M:] - 7.0).abs().max()) == 0.0  # rows beyond M untouched
 
 
-def test_gemm_patch_embed_epilogue():
+@pytest.mark.parametrize("B", [3, 8, 32])  # 1-CTA kernel; CTA-pair kernel with the TMA epilogue (split tail items only; whole tiles + tail)
+def test_gemm_patch_embed_epilogue(B):
     L, ops = _mods()
-    B = 3
     a, w, b = _rand(B * 196, 768, seed=11, dtype=BF16), _rand(768, 768, seed=12, scale=768 ** -0.5, dtype=BF16), _rand(768, seed=13)
     pos, cls = _rand(197, 768, seed=14, scale=0.02), _rand(768, seed=15, scale=0.02)
-    out = torch.empty(B * 197, 768, device="cuda")
+    out = torch.full((B * 197 + 3, 768), 7.0, device="cuda")
     ops.gemm(a, w, b, L.EPI_PATCH_EMBED, out, pos, cls)
     tok = (a.float() @ w.float().t() + b).view(B, 196, 768)
     ref = torch.cat([cls.view(1, 1, 768).expand(B, -1, -1), tok], 1) + pos
-    assert rel_l2(out.view(B, 197, 768), ref) < 1e-5
+    assert rel_l2(out[:B * 197].view(B, 197, 768), ref) < 1e-5
+    assert max_abs(out[:B * 197].view(B, 197, 768), ref) < 1e-3  # every token row of every image (a missing row would keep its 7.0)
+    assert float((out[B * 197:] - 7.0).abs().max()) == 0.0  # nothing past the last image
 
 
 def test_gemm_qkv_split_epilogue():

@@ -18,7 +18,7 @@ echo "launch list rc=$?"
 ncu --set full --clock-control none --import-source on -k 'regex:tc_gemm2_kernel|vit_attn|layernorm_kernel' -s 91 -c 7 \
     -o $OUT/${TAG}_vit -f $CMD > $OUT/${TAG}_ncu2.log 2>&1
 echo "vit capture rc=$?"
-ncu --set full --clock-control none --import-source on -k 'regex:resize_maps|input_scan_resample_kernel|patchify224_kernel|upsample_concat_kernel|conv_halo_kernel|instnorm_kernel|tc_gemm_kernel' -s 0 -c 30 \
+ncu --set full --clock-control none --import-source on -k 'regex:resize_maps|input_scan_resample_kernel|patchify224_kernel|upsample_concat|conv_halo_kernel|conv_small_kernel|instnorm_kernel|tokens_to_grid|range_finalize|tc_gemm_kernel' -s 0 -c 45 \
     -o $OUT/${TAG}_hbm -f $CMD > $OUT/${TAG}_ncu3.log 2>&1
 echo "hbm/conv capture rc=$?"
 ls -la $OUT
